@@ -1,0 +1,18 @@
+"""Named constructor-kwarg sets for AMDModel_New (model_AMD.py:1667-1721)."""
+
+# scripts/amd_new.sh:37-67 + AMD_N factory (model_AMD.py:3151-3161): 695 M parameters.
+DEFAULT = dict(
+    image_inchannel=4, image_height=32, image_width=32, video_frames=16, scheduler_num_step=1000,
+    use_filter=True, use_grey=False, use_camera_down=True, use_regularizers=False, use_camera=True, use_object=True,
+    object_motion_token_num=8, object_motion_token_channel=16, object_enc_num_layers=8,
+    camera_motion_token_num=8, camera_motion_token_channel=8, camera_enc_num_layers=8,
+    enc_nhead=8, enc_ndim=64, motion_need_norm_out=False, motion_token_num=40, need_motion_transformer=False,
+    diffusion_model_type="spatial", diffusion_attn_head_dim=64, diffusion_attn_num_heads=16,
+    diffusion_out_channels=4, diffusion_num_layers=12, image_patch_size=2, motion_patch_size=1,
+)
+
+# SURVEY §8d config 1 ("Small", 14.1 M parameters) — the CPU-runnable parity case.
+SMALL = dict(DEFAULT, object_enc_num_layers=2, camera_enc_num_layers=2, enc_nhead=2,
+             diffusion_attn_num_heads=4, diffusion_num_layers=2)
+
+CONFIGS = {"default": DEFAULT, "small": SMALL}
