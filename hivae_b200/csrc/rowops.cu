@@ -1,0 +1,239 @@
+// Bandwidth-bound row kernels: LayerNorm/adaLN modulate, timestep sinusoid, elementwise helpers,
+// residual-frame scatter/gather.  One warp per token row, 128-bit accesses, shuffle reductions.
+#include "hv_common.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// y = (LN(x) * w + b) * (1 + scale) + shift          (model/modules.py:881-928, 697, 710)
+template <int MAXNV, typename OutT>
+__global__ void __launch_bounds__(256) ln_modulate_kernel(
+    const float* __restrict__ res, long long rows, HvRowMap map, int D,
+    const float* __restrict__ ln_w, const float* __restrict__ ln_b, float eps,
+    const float* __restrict__ ada, long long ada_ld, int shift_col_mot, int scale_col_mot,
+    int shift_col_img, int scale_col_img, int img_start, int img_len, int cond_div, int cond_mul,
+    OutT* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const long long r = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    const int nv = D >> 7;  // float4 per lane
+    int frame, abs_i;
+    const long long rr = map.res_row(r, frame, abs_i);
+    const float4* xp = reinterpret_cast<const float4*>(res + rr * D);
+    float4 v[MAXNV];
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < MAXNV; ++j)
+        if (j < nv) {
+            v[j] = xp[j * 32 + lane];
+            sum += (v[j].x + v[j].y) + (v[j].z + v[j].w);
+        }
+    const float mean = hv_warp_sum(sum) / (float)D;
+    float sq = 0.f;
+#pragma unroll
+    for (int j = 0; j < MAXNV; ++j)
+        if (j < nv) {
+            float a = v[j].x - mean, b = v[j].y - mean, c = v[j].z - mean, d = v[j].w - mean;
+            sq += (a * a + b * b) + (c * c + d * d);
+        }
+    const float rstd = rsqrtf(hv_warp_sum(sq) / (float)D + eps);
+    const float4 *sh = nullptr, *sc = nullptr;
+    if (ada != nullptr) {
+        const bool img = (abs_i >= img_start) && (abs_i < img_start + img_len);
+        const float* arow = ada + (long long)((frame / cond_div) * cond_mul) * ada_ld;
+        sh = reinterpret_cast<const float4*>(arow + (img ? shift_col_img : shift_col_mot));
+        sc = reinterpret_cast<const float4*>(arow + (img ? scale_col_img : scale_col_mot));
+    }
+    const float4* wp = reinterpret_cast<const float4*>(ln_w);
+    const float4* bp = reinterpret_cast<const float4*>(ln_b);
+#pragma unroll
+    for (int j = 0; j < MAXNV; ++j)
+        if (j < nv) {
+            const int c4 = j * 32 + lane;
+            float4 y;
+            y.x = (v[j].x - mean) * rstd; y.y = (v[j].y - mean) * rstd;
+            y.z = (v[j].z - mean) * rstd; y.w = (v[j].w - mean) * rstd;
+            if (wp) { float4 w = wp[c4]; y.x *= w.x; y.y *= w.y; y.z *= w.z; y.w *= w.w; }
+            if (bp) { float4 b = bp[c4]; y.x += b.x; y.y += b.y; y.z += b.z; y.w += b.w; }
+            if (sh) {
+                float4 s = sc[c4], t = sh[c4];
+                y.x = y.x * (1.f + s.x) + t.x; y.y = y.y * (1.f + s.y) + t.y;
+                y.z = y.z * (1.f + s.z) + t.z; y.w = y.w * (1.f + s.w) + t.w;
+            }
+            if constexpr (sizeof(OutT) == 4) {
+                reinterpret_cast<float4*>(out + r * D)[c4] = y;
+            } else {
+                uint2 pk = make_uint2(hv_pack_bf16(y.x, y.y), hv_pack_bf16(y.z, y.w));
+                reinterpret_cast<uint2*>(out + r * D)[c4] = pk;
+            }
+        }
+}
+
+extern "C" int hv_ln_modulate(const float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D,
+                              const float* ln_w, const float* ln_b, float eps,
+                              const float* ada, int64_t ada_ld, int shift_col_mot, int scale_col_mot,
+                              int shift_col_img, int scale_col_img, int img_start, int img_len,
+                              int cond_div, int cond_mul, void* out, int out_dtype, void* stream) {
+    HV_REQUIRE(D > 0 && D % 128 == 0 && D <= 2048, "hv_ln_modulate: D=%d must be a multiple of 128 and <= 2048", D);
+    HV_REQUIRE(frames >= 0 && L >= 0 && row_off >= 0 && row_off + L <= frame_rows, "hv_ln_modulate: bad row range");
+    HV_REQUIRE(out_dtype == HV_F32 || out_dtype == HV_BF16, "hv_ln_modulate: bad out dtype");
+    if (ada) {
+        HV_REQUIRE(cond_div > 0, "hv_ln_modulate: cond_div must be > 0");
+        HV_REQUIRE(((shift_col_mot | scale_col_mot | shift_col_img | scale_col_img) & 3) == 0 && ada_ld % 4 == 0,
+                   "hv_ln_modulate: adaLN column offsets / ld must be multiples of 4");
+    }
+    const long long rows = (long long)frames * L;
+    if (rows == 0) return HV_OK;
+    HvRowMap map{L, (long long)frame_rows, row_off};
+    const int nv = D / 128;
+    dim3 grid((unsigned)((rows + 7) / 8)), block(256);
+    cudaStream_t st = hv_stream(stream);
+#define LN_LAUNCH(MAXNV, T)                                                                                   \
+    ln_modulate_kernel<MAXNV, T><<<grid, block, 0, st>>>(res, rows, map, D, ln_w, ln_b, eps, ada, ada_ld,     \
+        shift_col_mot, scale_col_mot, shift_col_img, scale_col_img, img_start, img_len, cond_div, cond_mul, (T*)out)
+    if (out_dtype == HV_F32) {
+        if (nv <= 4) LN_LAUNCH(4, float); else if (nv <= 8) LN_LAUNCH(8, float); else LN_LAUNCH(16, float);
+    } else {
+        if (nv <= 4) LN_LAUNCH(4, __nv_bfloat16); else if (nv <= 8) LN_LAUNCH(8, __nv_bfloat16); else LN_LAUNCH(16, __nv_bfloat16);
+    }
+#undef LN_LAUNCH
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Timesteps(dim, flip_sin_to_cos=True, freq_shift=0): [cos | sin], freq_i = exp(-ln(1e4) i / half)
+template <typename OutT>
+__global__ void timestep_embed_kernel(const float* __restrict__ t, long long rows, int dim, OutT* __restrict__ out) {
+    const int half = dim >> 1;
+    const long long total = rows * half;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const long long r = idx / half;
+        const int i = (int)(idx - r * half);
+        const float f = expf(-9.210340371976184f * (float)i / (float)half);
+        const float a = t[r] * f;
+        float s, c;
+        sincosf(a, &s, &c);
+        hv_st(out + r * dim + i, c);
+        hv_st(out + r * dim + half + i, s);
+    }
+}
+
+extern "C" int hv_timestep_embed(const float* t, int64_t rows, int dim, void* out, int out_dtype, void* stream) {
+    HV_REQUIRE(dim > 0 && dim % 2 == 0 && rows >= 0, "hv_timestep_embed: bad sizes");
+    if (rows == 0) return HV_OK;
+    long long total = rows * (dim / 2);
+    int grid = (int)((total + 255) / 256);
+    if (grid > 148 * 8) grid = 148 * 8;
+    if (out_dtype == HV_F32) timestep_embed_kernel<float><<<grid, 256, 0, hv_stream(stream)>>>(t, rows, dim, (float*)out);
+    else if (out_dtype == HV_BF16) timestep_embed_kernel<__nv_bfloat16><<<grid, 256, 0, hv_stream(stream)>>>(t, rows, dim, (__nv_bfloat16*)out);
+    else HV_REQUIRE(false, "hv_timestep_embed: bad dtype");
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+template <typename InT, typename OutT, int OP>  // OP 0: copy/convert, 1: silu
+__global__ void unary_kernel(const InT* __restrict__ x, OutT* __restrict__ y, long long n) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        float v = hv_ld(x + i);
+        if (OP == 1) v = hv_silu_f(v);
+        hv_st(y + i, v);
+    }
+}
+
+template <int OP>
+static int unary_launch(const void* x, int in_dtype, void* y, int out_dtype, int64_t n, void* stream) {
+    HV_REQUIRE(n >= 0, "unary: negative size");
+    if (n == 0) return HV_OK;
+    int grid = (int)((n + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    cudaStream_t st = hv_stream(stream);
+    if (in_dtype == HV_F32 && out_dtype == HV_F32) unary_kernel<float, float, OP><<<grid, 256, 0, st>>>((const float*)x, (float*)y, n);
+    else if (in_dtype == HV_F32 && out_dtype == HV_BF16) unary_kernel<float, __nv_bfloat16, OP><<<grid, 256, 0, st>>>((const float*)x, (__nv_bfloat16*)y, n);
+    else if (in_dtype == HV_BF16 && out_dtype == HV_F32) unary_kernel<__nv_bfloat16, float, OP><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, (float*)y, n);
+    else if (in_dtype == HV_BF16 && out_dtype == HV_BF16) unary_kernel<__nv_bfloat16, __nv_bfloat16, OP><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n);
+    else HV_REQUIRE(false, "unary: bad dtype");
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+extern "C" int hv_silu(const void* x, int in_dtype, void* y, int out_dtype, int64_t n, void* stream) {
+    return unary_launch<1>(x, in_dtype, y, out_dtype, n, stream);
+}
+extern "C" int hv_convert(const void* x, int in_dtype, void* y, int out_dtype, int64_t n, void* stream) {
+    return unary_launch<0>(x, in_dtype, y, out_dtype, n, stream);
+}
+
+__global__ void axpy_kernel(float a, const float* __restrict__ x, float* __restrict__ y, long long n) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        y[i] = fmaf(a, x[i], y[i]);
+}
+extern "C" int hv_axpy(float a, const float* x, float* y, int64_t n, void* stream) {
+    HV_REQUIRE(n >= 0, "hv_axpy: negative size");
+    if (n == 0) return HV_OK;
+    int grid = (int)((n + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    axpy_kernel<<<grid, 256, 0, hv_stream(stream)>>>(a, x, y, n);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// res[f*frame_rows + row_off + i, :] = src[f*src_stride_f + i*src_stride_i, :] (+ add[i, :])
+// (row strides in rows of D floats; src_stride_f = 0 broadcasts one token set to every frame)
+__global__ void rows_scatter_kernel(const float* __restrict__ src, long long sf, long long si, const float* __restrict__ add,
+                                    float* __restrict__ res, long long rows, HvRowMap map, int D) {
+    const int d4 = D >> 2;
+    const long long total = rows * d4;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const long long r = idx / d4;
+        const int c = (int)(idx - r * d4);
+        int frame, abs_i;
+        const long long rr = map.res_row(r, frame, abs_i);
+        const int i = abs_i - map.row_off;
+        float4 v = reinterpret_cast<const float4*>(src + ((long long)frame * sf + (long long)i * si) * D)[c];
+        if (add) {
+            float4 a = reinterpret_cast<const float4*>(add + (long long)i * D)[c];
+            v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+        }
+        reinterpret_cast<float4*>(res + rr * D)[c] = v;
+    }
+}
+extern "C" int hv_rows_scatter(const float* src, int64_t src_stride_f, int64_t src_stride_i, const float* add,
+                               float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D, void* stream) {
+    HV_REQUIRE(D > 0 && D % 4 == 0, "hv_rows_scatter: D must be a multiple of 4");
+    HV_REQUIRE(frames >= 0 && L >= 0 && row_off >= 0 && row_off + L <= frame_rows, "hv_rows_scatter: bad row range");
+    const long long rows = (long long)frames * L;
+    if (rows == 0) return HV_OK;
+    long long total = rows * (D / 4);
+    int grid = (int)((total + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    HvRowMap map{L, (long long)frame_rows, row_off};
+    rows_scatter_kernel<<<grid, 256, 0, hv_stream(stream)>>>(src, src_stride_f, src_stride_i, add, res, rows, map, D);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+__global__ void rows_gather_kernel(const float* __restrict__ res, long long rows, HvRowMap map, int D, float* __restrict__ out) {
+    const int d4 = D >> 2;
+    const long long total = rows * d4;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const long long r = idx / d4;
+        const int c = (int)(idx - r * d4);
+        int frame, abs_i;
+        const long long rr = map.res_row(r, frame, abs_i);
+        reinterpret_cast<float4*>(out + r * D)[c] = reinterpret_cast<const float4*>(res + rr * D)[c];
+    }
+}
+extern "C" int hv_rows_gather(const float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D,
+                              float* out, void* stream) {
+    HV_REQUIRE(D > 0 && D % 4 == 0, "hv_rows_gather: D must be a multiple of 4");
+    HV_REQUIRE(frames >= 0 && L >= 0 && row_off >= 0 && row_off + L <= frame_rows, "hv_rows_gather: bad row range");
+    const long long rows = (long long)frames * L;
+    if (rows == 0) return HV_OK;
+    long long total = rows * (D / 4);
+    int grid = (int)((total + 255) / 256);
+    if (grid > 148 * 16) grid = 148 * 16;
+    HvRowMap map{L, (long long)frame_rows, row_off};
+    rows_gather_kernel<<<grid, 256, 0, hv_stream(stream)>>>(res, rows, map, D, out);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}

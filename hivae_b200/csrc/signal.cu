@@ -1,0 +1,299 @@
+// Haar DWT / IDWT (model/wavelet.py) and the 3-D Gaussian frequency split
+// (model/frequency_utils.py) — HBM-bound, 128-bit vectorised kernels.
+#include "hv_common.cuh"
+
+// ---------------------------------------------------------------------------------------------
+// The reference evaluates every add/sub in the tensor's own dtype; for bf16 that means a
+// rounding after each op.  R<T>() reproduces that so results are bit-exact in both dtypes.
+template <typename T> __device__ __forceinline__ float hv_rnd(float v);
+template <> __device__ __forceinline__ float hv_rnd<float>(float v) { return v; }
+template <> __device__ __forceinline__ float hv_rnd<__nv_bfloat16>(float v) { return __bfloat162float(__float2bfloat16(v)); }
+
+template <typename T> struct Vec16 { static constexpr int N = 16 / sizeof(T); };
+
+template <typename T>
+__device__ __forceinline__ void load16(const T* p, float (&v)[16 / sizeof(T)]) {
+    uint4 raw = *reinterpret_cast<const uint4*>(p);
+    if constexpr (sizeof(T) == 4) {
+        v[0] = __uint_as_float(raw.x); v[1] = __uint_as_float(raw.y);
+        v[2] = __uint_as_float(raw.z); v[3] = __uint_as_float(raw.w);
+    } else {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { float2 f = __bfloat1622float2(h[i]); v[2 * i] = f.x; v[2 * i + 1] = f.y; }
+    }
+}
+template <typename T>
+__device__ __forceinline__ void store16(T* p, const float (&v)[16 / sizeof(T)]) {
+    uint4 raw;
+    if constexpr (sizeof(T) == 4) {
+        raw.x = __float_as_uint(v[0]); raw.y = __float_as_uint(v[1]);
+        raw.z = __float_as_uint(v[2]); raw.w = __float_as_uint(v[3]);
+    } else {
+        raw.x = hv_pack_bf16(v[0], v[1]); raw.y = hv_pack_bf16(v[2], v[3]);
+        raw.z = hv_pack_bf16(v[4], v[5]); raw.w = hv_pack_bf16(v[6], v[7]);
+    }
+    *reinterpret_cast<uint4*>(p) = raw;
+}
+
+// one 2x2 Haar butterfly, op order identical to wavelet.py:15-24
+template <typename T>
+__device__ __forceinline__ void haar_fwd(float p00, float p10, float p01, float p11,
+                                         float& ll, float& hl, float& lh, float& hh) {
+    float x1 = p00 * 0.5f, x2 = p10 * 0.5f, x3 = p01 * 0.5f, x4 = p11 * 0.5f;  // exact in both dtypes
+    ll = hv_rnd<T>(hv_rnd<T>(hv_rnd<T>(x1 + x2) + x3) + x4);
+    hl = hv_rnd<T>(hv_rnd<T>(hv_rnd<T>(-x1 - x2) + x3) + x4);
+    lh = hv_rnd<T>(hv_rnd<T>(hv_rnd<T>(-x1 + x2) - x3) + x4);
+    hh = hv_rnd<T>(hv_rnd<T>(hv_rnd<T>(x1 - x2) - x3) + x4);
+}
+
+// Vector path: each thread produces VEC output columns of one output row (2 rows x 2*VEC inputs).
+template <typename T>
+__global__ void __launch_bounds__(256) dwt2_haar_vec_kernel(const T* __restrict__ x, T* __restrict__ ll, T* __restrict__ hl,
+                                                            T* __restrict__ lh, T* __restrict__ hh,
+                                                            long long planes, int H, int W) {
+    constexpr int VEC = Vec16<T>::N;
+    const int h2 = H >> 1, w2 = W >> 1, wv = w2 / VEC;
+    const long long total = planes * h2 * wv;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        int cv = (int)(idx % wv);
+        long long t = idx / wv;
+        int i = (int)(t % h2);
+        long long pl = t / h2;
+        const T* r0 = x + (pl * H + 2 * i) * (long long)W + 2 * cv * VEC;
+        const T* r1 = r0 + W;
+        float a0[VEC], a1[VEC], b0[VEC], b1[VEC];
+        load16<T>(r0, a0); load16<T>(r0 + VEC, a1);
+        load16<T>(r1, b0); load16<T>(r1 + VEC, b1);
+        float oll[VEC], ohl[VEC], olh[VEC], ohh[VEC];
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            // input column 2j / 2j+1 of the 2*VEC-wide strip
+            float p00 = (2 * j < VEC) ? a0[(2 * j) % VEC] : a1[(2 * j) % VEC];
+            float p01 = (2 * j + 1 < VEC) ? a0[(2 * j + 1) % VEC] : a1[(2 * j + 1) % VEC];
+            float p10 = (2 * j < VEC) ? b0[(2 * j) % VEC] : b1[(2 * j) % VEC];
+            float p11 = (2 * j + 1 < VEC) ? b0[(2 * j + 1) % VEC] : b1[(2 * j + 1) % VEC];
+            haar_fwd<T>(p00, p10, p01, p11, oll[j], ohl[j], olh[j], ohh[j]);
+        }
+        long long o = (pl * h2 + i) * (long long)w2 + (long long)cv * VEC;
+        store16<T>(ll + o, oll); store16<T>(hl + o, ohl); store16<T>(lh + o, olh); store16<T>(hh + o, ohh);
+    }
+}
+
+// Scalar path for widths that are not a multiple of 2*VEC (ragged inputs).
+template <typename T>
+__global__ void __launch_bounds__(256) dwt2_haar_scalar_kernel(const T* __restrict__ x, T* __restrict__ ll, T* __restrict__ hl,
+                                                               T* __restrict__ lh, T* __restrict__ hh,
+                                                               long long planes, int H, int W) {
+    const int h2 = H >> 1, w2 = W >> 1;
+    const long long total = planes * h2 * w2;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        int j = (int)(idx % w2);
+        long long t = idx / w2;
+        int i = (int)(t % h2);
+        long long pl = t / h2;
+        const T* r0 = x + (pl * H + 2 * i) * (long long)W + 2 * j;
+        float a, b, c, d;
+        haar_fwd<T>(hv_ld(r0), hv_ld(r0 + W), hv_ld(r0 + 1), hv_ld(r0 + W + 1), a, b, c, d);
+        hv_st(ll + idx, a); hv_st(hl + idx, b); hv_st(lh + idx, c); hv_st(hh + idx, d);
+    }
+}
+
+template <typename T>
+__device__ __forceinline__ void haar_inv(float a, float b, float c, float d, float& o00, float& o10, float& o01, float& o11) {
+    float x1 = a * 0.5f, x2 = b * 0.5f, x3 = c * 0.5f, x4 = d * 0.5f;
+    o00 = hv_rnd<T>(hv_rnd<T>(hv_rnd<T>(x1 - x2) - x3) + x4);  // h[0::2,0::2]  wavelet.py:43
+    o10 = hv_rnd<T>(hv_rnd<T>(hv_rnd<T>(x1 - x2) + x3) - x4);  // h[1::2,0::2]
+    o01 = hv_rnd<T>(hv_rnd<T>(hv_rnd<T>(x1 + x2) - x3) - x4);  // h[0::2,1::2]
+    o11 = hv_rnd<T>(hv_rnd<T>(hv_rnd<T>(x1 + x2) + x3) + x4);  // h[1::2,1::2]
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) idwt2_haar_vec_kernel(const T* __restrict__ ll, const T* __restrict__ hl,
+                                                             const T* __restrict__ lh, const T* __restrict__ hh,
+                                                             float* __restrict__ out, long long planes, int h, int w) {
+    constexpr int VEC = Vec16<T>::N;
+    const int wv = w / VEC;
+    const long long total = planes * h * wv;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        int cv = (int)(idx % wv);
+        long long t = idx / wv;
+        int i = (int)(t % h);
+        long long pl = t / h;
+        long long o = (pl * h + i) * (long long)w + (long long)cv * VEC;
+        float a[VEC], b[VEC], c[VEC], d[VEC];
+        load16<T>(ll + o, a); load16<T>(hl + o, b); load16<T>(lh + o, c); load16<T>(hh + o, d);
+        float r0[2 * VEC], r1[2 * VEC];
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) haar_inv<T>(a[j], b[j], c[j], d[j], r0[2 * j], r1[2 * j], r0[2 * j + 1], r1[2 * j + 1]);
+        float* p0 = out + (pl * 2 * h + 2 * i) * (long long)(2 * w) + (long long)cv * 2 * VEC;
+        float* p1 = p0 + 2 * w;
+#pragma unroll
+        for (int q = 0; q < 2 * VEC / 4; ++q) {
+            *reinterpret_cast<float4*>(p0 + 4 * q) = make_float4(r0[4 * q], r0[4 * q + 1], r0[4 * q + 2], r0[4 * q + 3]);
+            *reinterpret_cast<float4*>(p1 + 4 * q) = make_float4(r1[4 * q], r1[4 * q + 1], r1[4 * q + 2], r1[4 * q + 3]);
+        }
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) idwt2_haar_scalar_kernel(const T* __restrict__ ll, const T* __restrict__ hl,
+                                                                const T* __restrict__ lh, const T* __restrict__ hh,
+                                                                float* __restrict__ out, long long planes, int h, int w) {
+    const long long total = planes * h * w;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        int j = (int)(idx % w);
+        long long t = idx / w;
+        int i = (int)(t % h);
+        long long pl = t / h;
+        float o00, o10, o01, o11;
+        haar_inv<T>(hv_ld(ll + idx), hv_ld(hl + idx), hv_ld(lh + idx), hv_ld(hh + idx), o00, o10, o01, o11);
+        float* p0 = out + (pl * 2 * h + 2 * i) * (long long)(2 * w) + 2 * j;
+        p0[0] = o00; p0[1] = o01; p0[2 * w] = o10; p0[2 * w + 1] = o11;
+    }
+}
+
+static int grid_for(long long total, int block) {
+    long long need = (total + block - 1) / block;
+    long long cap = (long long)hv_num_sms() * 8;  // 8 resident 256-thread CTAs per SM
+    if (need < 1) need = 1;
+    return (int)(need < cap ? need : cap);
+}
+
+template <typename T>
+static int dwt_launch(const void* x, void* ll, void* hl, void* lh, void* hh, int64_t planes, int H, int W, cudaStream_t st) {
+    constexpr int VEC = Vec16<T>::N;
+    const bool vec_ok = (W % (2 * VEC) == 0) && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(ll) |
+                        reinterpret_cast<uintptr_t>(hl) | reinterpret_cast<uintptr_t>(lh) | reinterpret_cast<uintptr_t>(hh)) % 16 == 0);
+    if (vec_ok) {
+        long long total = planes * (H / 2) * (W / 2 / VEC);
+        dwt2_haar_vec_kernel<T><<<grid_for(total, 256), 256, 0, st>>>((const T*)x, (T*)ll, (T*)hl, (T*)lh, (T*)hh, planes, H, W);
+    } else {
+        long long total = planes * (H / 2) * (W / 2);
+        dwt2_haar_scalar_kernel<T><<<grid_for(total, 256), 256, 0, st>>>((const T*)x, (T*)ll, (T*)hl, (T*)lh, (T*)hh, planes, H, W);
+    }
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+extern "C" int hv_dwt2_haar(const void* x, void* ll, void* hl, void* lh, void* hh,
+                            int64_t planes, int H, int W, int dtype, void* stream) {
+    HV_REQUIRE(planes >= 0 && H >= 0 && W >= 0, "hv_dwt2_haar: negative size");
+    HV_REQUIRE(H % 2 == 0 && W % 2 == 0, "hv_dwt2_haar: H and W must be even (got %d x %d)", H, W);
+    if (planes == 0 || H == 0 || W == 0) return HV_OK;
+    if (dtype == HV_F32) return dwt_launch<float>(x, ll, hl, lh, hh, planes, H, W, hv_stream(stream));
+    if (dtype == HV_BF16) return dwt_launch<__nv_bfloat16>(x, ll, hl, lh, hh, planes, H, W, hv_stream(stream));
+    HV_REQUIRE(false, "hv_dwt2_haar: bad dtype %d", dtype);
+}
+
+template <typename T>
+static int idwt_launch(const void* ll, const void* hl, const void* lh, const void* hh, float* out,
+                       int64_t planes, int h, int w, cudaStream_t st) {
+    constexpr int VEC = Vec16<T>::N;
+    const bool vec_ok = (w % VEC == 0) && ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(ll) |
+                        reinterpret_cast<uintptr_t>(hl) | reinterpret_cast<uintptr_t>(lh) | reinterpret_cast<uintptr_t>(hh)) % 16 == 0);
+    if (vec_ok) {
+        long long total = planes * h * (w / VEC);
+        idwt2_haar_vec_kernel<T><<<grid_for(total, 256), 256, 0, st>>>((const T*)ll, (const T*)hl, (const T*)lh, (const T*)hh, out, planes, h, w);
+    } else {
+        long long total = planes * h * w;
+        idwt2_haar_scalar_kernel<T><<<grid_for(total, 256), 256, 0, st>>>((const T*)ll, (const T*)hl, (const T*)lh, (const T*)hh, out, planes, h, w);
+    }
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+extern "C" int hv_idwt2_haar(const void* ll, const void* hl, const void* lh, const void* hh, float* out,
+                             int64_t planes, int h, int w, int dtype_in, void* stream) {
+    HV_REQUIRE(planes >= 0 && h >= 0 && w >= 0, "hv_idwt2_haar: negative size");
+    if (planes == 0 || h == 0 || w == 0) return HV_OK;
+    if (dtype_in == HV_F32) return idwt_launch<float>(ll, hl, lh, hh, out, planes, h, w, hv_stream(stream));
+    if (dtype_in == HV_BF16) return idwt_launch<__nv_bfloat16>(ll, hl, lh, hh, out, planes, h, w, hv_stream(stream));
+    HV_REQUIRE(false, "hv_idwt2_haar: bad dtype %d", dtype_in);
+}
+
+// ---------------------------------------------------------------------------------------------
+// 3-D Gaussian low/high split.  One CTA owns one T x H x W volume in shared memory (row pitch
+// W+1 floats -> conflict-free line access along every axis) and applies the three circulant
+// matrices in place, one axis at a time; each thread owns whole lines, held in registers.
+template <int MAXN>
+__device__ __forceinline__ void circ_line(float* line, int stride, int N, const float* __restrict__ C) {
+    float xr[MAXN];
+#pragma unroll
+    for (int k = 0; k < MAXN; ++k) xr[k] = (k < N) ? line[k * stride] : 0.0f;
+    for (int i = 0; i < N; ++i) {
+        const float4* row = reinterpret_cast<const float4*>(C + i * MAXN);
+        float acc = 0.0f;
+#pragma unroll
+        for (int k4 = 0; k4 < MAXN / 4; ++k4) {
+            float4 c = row[k4];  // broadcast read, zero-padded beyond N
+            acc = fmaf(c.x, xr[4 * k4], acc); acc = fmaf(c.y, xr[4 * k4 + 1], acc);
+            acc = fmaf(c.z, xr[4 * k4 + 2], acc); acc = fmaf(c.w, xr[4 * k4 + 3], acc);
+        }
+        line[i * stride] = acc;
+    }
+}
+
+template <int MAXN>
+__global__ void __launch_bounds__(256) freq_split3d_kernel(const float* __restrict__ x, const float* __restrict__ ct,
+                                                           const float* __restrict__ ch, const float* __restrict__ cw,
+                                                           float* __restrict__ lo, float* __restrict__ hi,
+                                                           int T, int H, int W) {
+    extern __shared__ __align__(16) float smem[];
+    float* sct = smem;                 // T rows x MAXN
+    float* sch = sct + MAXN * MAXN;
+    float* scw = sch + MAXN * MAXN;
+    float* vol = scw + MAXN * MAXN;    // T*H rows, pitch W+1
+    const int P = W + 1;
+    const long long nvol = (long long)T * H * W;
+    const float* xv = x + blockIdx.x * nvol;
+    for (int i = threadIdx.x; i < 3 * MAXN * MAXN; i += blockDim.x) smem[i] = 0.0f;
+    __syncthreads();
+    for (int i = threadIdx.x; i < T * T; i += blockDim.x) sct[(i / T) * MAXN + i % T] = ct[i];
+    for (int i = threadIdx.x; i < H * H; i += blockDim.x) sch[(i / H) * MAXN + i % H] = ch[i];
+    for (int i = threadIdx.x; i < W * W; i += blockDim.x) scw[(i / W) * MAXN + i % W] = cw[i];
+    for (long long i = threadIdx.x; i < nvol; i += blockDim.x) vol[(i / W) * P + i % W] = xv[i];
+    __syncthreads();
+    // W axis: line = (t,h), element stride 1, consecutive threads -> pitch P apart (conflict-free)
+    for (int l = threadIdx.x; l < T * H; l += blockDim.x) circ_line<MAXN>(vol + l * P, 1, W, scw);
+    __syncthreads();
+    // H axis: line = (t,w), stride P
+    for (int l = threadIdx.x; l < T * W; l += blockDim.x) circ_line<MAXN>(vol + (l / W) * H * P + l % W, P, H, sch);
+    __syncthreads();
+    // T axis: line = (h,w), stride H*P
+    for (int l = threadIdx.x; l < H * W; l += blockDim.x) circ_line<MAXN>(vol + (l / W) * P + l % W, H * P, T, sct);
+    __syncthreads();
+    float* lov = lo + blockIdx.x * nvol;
+    float* hiv = hi + blockIdx.x * nvol;
+    for (long long i = threadIdx.x; i < nvol; i += blockDim.x) {
+        float l = vol[(i / W) * P + i % W];
+        lov[i] = l;
+        hiv[i] = xv[i] - l;
+    }
+}
+
+extern "C" int hv_freq_split3d(const float* x, const float* ct, const float* ch, const float* cw,
+                               float* lo, float* hi, int64_t vols, int T, int H, int W, void* stream) {
+    HV_REQUIRE(vols >= 0 && T > 0 && H > 0 && W > 0, "hv_freq_split3d: bad sizes");
+    if (vols == 0) return HV_OK;
+    int maxn = T > H ? T : H;
+    maxn = maxn > W ? maxn : W;
+    HV_REQUIRE(maxn <= 64, "hv_freq_split3d: axis length %d > 64 unsupported", maxn);
+    const int MAXN = maxn <= 32 ? 32 : 64;
+    size_t smem = (size_t)(3 * MAXN * MAXN + (size_t)T * H * (W + 1)) * sizeof(float);
+    HV_REQUIRE(smem <= 227 * 1024, "hv_freq_split3d: volume %dx%dx%d needs %zu B of shared memory (> 227 KB)", T, H, W, smem);
+    cudaStream_t st = hv_stream(stream);
+    if (MAXN == 32) {
+        HV_CUDA(cudaFuncSetAttribute(freq_split3d_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        freq_split3d_kernel<32><<<(unsigned)vols, 256, smem, st>>>(x, ct, ch, cw, lo, hi, T, H, W);
+    } else {
+        HV_CUDA(cudaFuncSetAttribute(freq_split3d_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        freq_split3d_kernel<64><<<(unsigned)vols, 256, smem, st>>>(x, ct, ch, cw, lo, hi, T, H, W);
+    }
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}

@@ -1,0 +1,256 @@
+"""AMDModel_New — the model-level API of the reference (model/model_AMD.py:1663-2838) on the
+hivae_b200 kernels: same constructor kwargs, same state-dict keys (a reference `model.safetensors`
+loads unchanged), same encode / decode / sample / forward signatures and return conventions.
+
+Supported configuration = the one every shipped script uses (scripts/amd_new.sh:37-67):
+diffusion_model_type='spatial', use_grey=False, use_regularizers=False,
+need_motion_transformer=False; use_filter / use_camera_down / use_camera / use_object free.
+"""
+import inspect
+import json
+import os
+
+import numpy as np
+import torch
+from torch import nn
+
+from . import engine, ops
+from .frequency_utils import freq_split_gauss
+from .rectified_flow import RectifiedFlow
+from .transformer import (AMDDiffusionTransformerModelImgSpatialTempMotion, MotionEncoderLearnTokenOnlyTemporalTransformer,
+                          MotionEncoderLearnTokenTransformer)
+
+
+def l2(pre, gt):
+    """model/loss.py:13-14."""
+    return torch.nn.functional.mse_loss(pre, gt)
+
+
+class _ConfigModel(nn.Module):
+    """The slice of diffusers' ConfigMixin/ModelMixin the reference relies on
+    (train_amd.py:175,224; amd_inference.py:99-107): records kwargs, from_config / save_config."""
+    config_name = "config.json"
+
+    def _register(self, frame):
+        sig = inspect.signature(type(self).__init__).parameters
+        self.config = {k: frame[k] for k in sig if k not in ("self", "kwargs") and k in frame}
+
+    @classmethod
+    def from_config(cls, config, **kwargs):
+        cfg = {k: v for k, v in dict(config).items() if not k.startswith("_")}
+        cfg.update(kwargs)
+        return cls(**cfg)
+
+    @classmethod
+    def load_config(cls, path, **kwargs):
+        p = path if path.endswith(".json") else os.path.join(path, cls.config_name)
+        with open(p) as f:
+            return json.load(f)
+
+    def save_config(self, save_directory, **kwargs):
+        os.makedirs(save_directory, exist_ok=True)
+        with open(os.path.join(save_directory, self.config_name), "w") as f:
+            json.dump({"_class_name": type(self).__name__, **self.config}, f, indent=2)
+
+    @property
+    def device(self):
+        return next(self.parameters()).device
+
+    @property
+    def dtype(self):
+        return next(self.parameters()).dtype
+
+
+class AMDModel_New(_ConfigModel):
+    _supports_gradient_checkpointing = True
+
+    def __init__(self, image_inchannel=4, image_height=32, image_width=32, video_frames=16, scheduler_num_step=1000,
+                 use_filter=False, filter_num=0.4, use_grey=False, use_camera_down=False, use_regularizers=False,
+                 use_motiontemporal=True, klloss_weight=0.005, use_mask=False, motion_type="plus", use_camera=True,
+                 use_object=True, object_motion_token_num=12, object_motion_token_channel=128, object_enc_num_layers=8,
+                 enc_nhead=8, enc_ndim=64, enc_dropout=0.0, motion_need_norm_out=False, camera_motion_token_num=12,
+                 camera_motion_token_channel=128, camera_enc_num_layers=8, motion_token_num=12, motion_token_channel=128,
+                 need_motion_transformer=False, motion_transformer_attn_head_dim=64, motion_transformer_attn_num_heads=16,
+                 motion_transformer_num_layers=4, diffusion_model_type="default", diffusion_attn_head_dim=64,
+                 diffusion_attn_num_heads=16, diffusion_out_channels=4, diffusion_num_layers=16, image_patch_size=2,
+                 motion_patch_size=1, motion_drop_ratio=0.0, extract_motion_with_motion_transformer=False, **kwargs):
+        super().__init__()
+        self._register(locals())
+        if diffusion_model_type != "spatial":
+            raise NotImplementedError("hivae_b200 implements diffusion_model_type='spatial' (the shipped AMD_N recipe)")
+        if use_grey or need_motion_transformer or use_regularizers:
+            raise NotImplementedError("use_grey / need_motion_transformer / use_regularizers are outside the hot path")
+        self.num_step = scheduler_num_step
+        self.scheduler = RectifiedFlow(num_steps=scheduler_num_step)
+        self.diffusion_model_type = diffusion_model_type
+        self.target_frame = video_frames
+        self.camera_motion_token_channel = camera_motion_token_channel
+        self.object_motion_token_channel = object_motion_token_channel
+        self.motion_token_channel = motion_token_channel
+        self.filter_num, self.use_camera, self.use_object = filter_num, use_camera, use_object
+        self.use_filter, self.use_grey, self.use_camera_down = use_filter, use_grey, use_camera_down
+        if use_camera:
+            ch, cw = (image_height // 4, image_width // 4) if use_camera_down else (image_height, image_width)
+            self.camera_motion_encoder = MotionEncoderLearnTokenOnlyTemporalTransformer(
+                img_height=ch, img_width=cw, img_inchannel=image_inchannel, img_patch_size=image_patch_size,
+                motion_token_num=camera_motion_token_num, motion_channel=camera_motion_token_channel,
+                need_norm_out=motion_need_norm_out, video_frames=self.target_frame, num_attention_heads=enc_nhead,
+                attention_head_dim=enc_ndim, num_layers=camera_enc_num_layers, dropout=enc_dropout, attention_bias=True)
+        if use_object:
+            self.object_motion_encoder = MotionEncoderLearnTokenTransformer(
+                img_height=image_height, img_width=image_width, img_inchannel=image_inchannel,
+                img_patch_size=image_patch_size, motion_token_num=object_motion_token_num,
+                motion_channel=object_motion_token_channel, need_norm_out=motion_need_norm_out,
+                num_attention_heads=enc_nhead, attention_head_dim=enc_ndim, num_layers=object_enc_num_layers,
+                dropout=enc_dropout, attention_bias=True)
+        if use_camera_down:
+            self.camera_down = nn.Sequential(
+                nn.Conv2d(in_channels=4, out_channels=16, kernel_size=3, stride=2, padding=1),
+                nn.Conv2d(in_channels=16, out_channels=4, kernel_size=3, stride=1, padding=1),
+                nn.MaxPool2d(kernel_size=2, stride=2, padding=0))
+        self.diffusion_transformer = AMDDiffusionTransformerModelImgSpatialTempMotion(
+            num_attention_heads=diffusion_attn_num_heads, attention_head_dim=diffusion_attn_head_dim,
+            out_channels=diffusion_out_channels, num_layers=diffusion_num_layers, use_camera=use_camera,
+            use_object=use_object, image_width=image_width, image_height=image_height, image_patch_size=image_patch_size,
+            image_in_channels=image_inchannel * 2, motion_token_num=motion_token_num,
+            camera_motion_in_channels=camera_motion_token_channel, object_motion_in_channels=object_motion_token_channel,
+            motion_target_num_frame=self.target_frame)
+
+    # ------------------------------------------------------------------ helpers
+    def set_compute_dtype(self, dtype):
+        """bf16 = the reference's autocast(bf16) semantics (bf16 GEMM/attention operands, fp32
+        accumulation, fp32 LayerNorm statistics and residual stream); fp32 = the parity mode."""
+        for m in self.modules():
+            m.hv_compute_dtype = dtype
+        return self
+
+    def _camera_down(self, x):
+        c0, c1 = self.camera_down[0], self.camera_down[1]
+        f = lambda t: t.detach().float().contiguous()
+        y = ops.conv3x3(x, f(c0.weight), f(c0.bias), 2)
+        y = ops.conv3x3(y, f(c1.weight), f(c1.bias), 1)
+        return ops.maxpool2(y)
+
+    def _encode(self, video, ref_img, d_lo, camera_mask_ratio=None, object_mask_ratio=None):
+        """shared front half of forward / sample / encode (model_AMD.py:1877-1944, 2037-2095, 2391-2455)"""
+        n, t, c, h, w = video.shape
+        assert video.shape == ref_img.shape, f"video.shape:{video.shape}should be equal to ref_img.shape:{ref_img.shape}"
+        rv = torch.cat([ref_img, video], dim=1).float().contiguous()  # (n, 2t, c, h, w)
+        cam = osrc = otgt = None
+        if self.use_filter:
+            # n t c h w -> n c t h w: the FFT volume is (2t, h, w) per (n, c)
+            vol = rv.permute(0, 2, 1, 3, 4).contiguous()
+            lo, _hi = freq_split_gauss(vol, d_lo, d_lo)
+            lf_video = lo.permute(0, 2, 1, 3, 4)[:, t:].contiguous()  # low-frequency target half
+            if self.use_camera:
+                if self.use_camera_down:
+                    lf = self._camera_down(lf_video.view(n * t, c, h, w))
+                    lf_video = lf.view(n, t, *lf.shape[1:])
+                cam = self.camera_motion_encoder(lf_video, camera_mask_ratio)
+            if self.use_object:
+                obj = self.object_motion_encoder(rv, object_mask_ratio)  # NOTE: unfiltered input (model_AMD.py:1926)
+                osrc, otgt = obj[:, :t].flatten(0, 1).contiguous(), obj[:, t:].flatten(0, 1).contiguous()
+                assert osrc.shape == otgt.shape
+        else:
+            # reference path without the filter only drives the camera encoder (model_AMD.py:1936-1944)
+            x = rv
+            if self.use_camera_down:
+                y = self._camera_down(x.view(n * 2 * t, c, h, w))
+                x = y.view(n, 2 * t, *y.shape[1:])
+            cam = self.camera_motion_encoder(x[:, t:].contiguous(), camera_mask_ratio)
+        return cam, osrc, otgt
+
+    def prepare_timestep(self, batch_size, device, time_step=None):
+        if time_step is not None:
+            return time_step.to(device)
+        return torch.randint(0, self.num_step + 1, (batch_size,)).to(device)
+
+    def _dit(self, zi, zt, time_step, cam, osrc, otgt):
+        dt_ = self.diffusion_transformer
+        M = dt_.set_motion(zi.shape[0], zi.device, cam if self.use_camera else None,
+                           osrc if self.use_object else None, otgt if self.use_object else None)
+        pre = torch.empty_like(zt)
+        dt_.run(M, zi, zt, time_step, pre=pre)
+        return pre
+
+    # ------------------------------------------------------------------ public API
+    @torch.no_grad()
+    def forward(self, video, ref_img, video_grey=None, ref_img_grey=None, time_step=None, return_meta_info=False,
+                camera_mask_ratio=None, object_mask_ratio=None):
+        """Training-step forward (model_AMD.py:1844-2017), inference kernels only (no autograd yet):
+        returns (pre, vel, {'loss','diff_loss','rec_loss'})."""
+        n, t, c, h, w = video.shape
+        device = video.device
+        cam, osrc, otgt = self._encode(video, ref_img, 0.6, camera_mask_ratio, object_mask_ratio)
+        zi, zj = ref_img.flatten(0, 1).float().contiguous(), video.flatten(0, 1).float().contiguous()
+        if time_step is None:
+            time_step = self.prepare_timestep(batch_size=zj.shape[0], device=device)
+        # 'spatial' mode redraws one step per clip (model_AMD.py:1962-1964)
+        time_step = self.prepare_timestep(batch_size=n, device=device).repeat_interleave(t)
+        zt, vel = self.scheduler.get_train_tuple(z1=zj, time_step=time_step)
+        zt = zt.contiguous()
+        pre = self._dit(zi, zt, time_step.float(), cam, osrc, otgt)
+        diff_loss = l2(pre, vel)
+        rec_loss = l2(self.scheduler.get_target_with_zt_vel(zt, pre, time_step), zj)
+        if return_meta_info:
+            return {"zi": zi, "zj": zj, "zt": zt, "pre": pre, "time_step": time_step}
+        return pre, vel, {"loss": diff_loss, "diff_loss": diff_loss, "rec_loss": rec_loss}
+
+    @torch.no_grad()
+    def encode(self, video, ref_img, video_grey=None, ref_img_grey=None, camera_mask_ratio=None, object_mask_ratio=None):
+        """model_AMD.py:2379-2462 -> (camera_target_motion (n,t,s,dc), object_source_motion, object_target_motion (n*t,l,do))."""
+        return self._encode(video, ref_img, 0.6, camera_mask_ratio, object_mask_ratio)
+
+    @torch.no_grad()
+    def decode(self, video, ref_img, camera_target_motion, object_source_motion, object_target_motion, time_step=None,
+               start_step=None, sample_step=50, return_meta_info=False):
+        """Euler sampling loop (model_AMD.py:2464-2536): (zi, zt, zj), each (n,t,c,h,w)."""
+        if start_step is None:
+            raise ValueError("decode() needs start_step (the reference raises a TypeError here, model_AMD.py:2476)")
+        n, t = video.shape[:2]
+        zi, zj = ref_img.flatten(0, 1).float().contiguous(), video.flatten(0, 1).float().contiguous()
+        time_step = torch.ones((zj.shape[0],), device=video.device) * start_step
+        zt, _vel = self.scheduler.get_train_tuple(z1=zj, time_step=time_step)
+        zt = zt.contiguous().clone()
+        step_seq = np.linspace(0, start_step, num=sample_step + 1, endpoint=True, dtype=int)
+        step_seq = list(reversed(step_seq[1:]))
+        dt = 1.0 / sample_step
+        dit = self.diffusion_transformer
+        M = dit.set_motion(zi.shape[0], zi.device, camera_target_motion if self.use_camera else None,
+                           object_source_motion if self.use_object else None,
+                           object_target_motion if self.use_object else None)
+        pre_cache, sample_cache = [], []
+        ts = torch.empty(zt.shape[0], dtype=torch.float32, device=zt.device)
+        for i in step_seq:
+            ts.fill_(float(i))
+            pre = torch.empty_like(zt) if return_meta_info else None
+            dit.run(M, zi, zt, ts, pre=pre, zt=zt, dt=dt)  # zt += dt * pre fused into the head kernel
+            if return_meta_info:
+                pre_cache.append(pre)
+                sample_cache.append(zt.clone())
+        shp = (n, t) + tuple(zi.shape[1:])
+        zi, zt, zj = zi.view(shp), zt.view(shp), zj.view(shp)
+        if return_meta_info:
+            return {"zi": zi, "zj": zj, "sample": zt, "pre_cache": pre_cache, "sample_cache": sample_cache,
+                    "step_seq": step_seq}
+        return zi, zt, zj
+
+    @torch.no_grad()
+    def sample(self, video, ref_img, video_grey=None, ref_img_grey=None, sample_step=50, object_mask_ratio=None,
+               camera_mask_ratio=None, start_step=None, return_meta_info=False):
+        """encode + decode (model_AMD.py:2020-2195)."""
+        if start_step is None:
+            start_step = self.scheduler.num_step
+        assert start_step <= self.scheduler.num_step, "start_step cant be larger than scheduler.num_step"
+        cam, osrc, otgt = self._encode(video, ref_img, 0.6, camera_mask_ratio, object_mask_ratio)
+        return self.decode(video, ref_img, cam, osrc, otgt, start_step=start_step, sample_step=sample_step,
+                           return_meta_info=return_meta_info)
+
+
+def AMD_N(**kwargs):
+    """model_AMD.py:3151-3161."""
+    return AMDModel_New(enc_nhead=8, enc_ndim=64, diffusion_attn_head_dim=64, diffusion_attn_num_heads=16,
+                        diffusion_out_channels=4, diffusion_num_layers=12, **kwargs)
+
+
+AMD_models = {"AMD_N": AMD_N}

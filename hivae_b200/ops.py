@@ -1,0 +1,266 @@
+"""Torch-tensor facing wrappers over the C ABI (pointer + size marshalling only).
+
+PyTorch is used for device memory and streams; every computation below is one of the
+hand-written sm_100a kernels behind include/hivae_b200.h.
+"""
+import ctypes as C
+from dataclasses import dataclass
+
+import torch
+
+from . import _lib
+from ._lib import HV_BF16, HV_F32, EPI_GELU, EPI_QKNORM, EPI_RESIDUAL, EPI_STORE, HvEpilogue, HvSeqMap  # noqa: F401
+
+
+def _dt(t):
+    if t.dtype == torch.float32:
+        return HV_F32
+    if t.dtype == torch.bfloat16:
+        return HV_BF16
+    raise TypeError("hivae_b200 supports float32 / bfloat16 tensors, got %s" % t.dtype)
+
+
+def _dtc(dtype):
+    return HV_F32 if dtype == torch.float32 else HV_BF16
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _chk_cuda(*ts):
+    _lib.require_device()
+    for t in ts:
+        if t is not None:
+            if not t.is_cuda:
+                raise RuntimeError("hivae_b200 ops need CUDA tensors (no CPU fallback)")
+            if not t.is_contiguous():
+                raise RuntimeError("hivae_b200 ops need contiguous tensors")
+
+
+def launch_count():
+    return int(_lib.load().hv_launch_count())
+
+
+# ------------------------------------------------------------------ wavelet / frequency
+def dwt2_haar(x):
+    """(B,C,H,W) -> LL, HL, LH, HH each (B,C,H/2,W/2), dtype preserved (wavelet.py:13-27)."""
+    _chk_cuda(x)
+    B, Cc, H, W = x.shape
+    outs = [torch.empty(B, Cc, H // 2, W // 2, dtype=x.dtype, device=x.device) for _ in range(4)]
+    _lib.check(_lib.load().hv_dwt2_haar(_p(x), *[_p(o) for o in outs], B * Cc, H, W, _dt(x), _stream()))
+    return tuple(outs)
+
+
+def idwt2_haar(ll, hl, lh, hh):
+    """four (B,C,h,w) sub-bands -> (B,C,2h,2w) fp32 (wavelet.py:31-48)."""
+    _chk_cuda(ll, hl, lh, hh)
+    B, Cc, h, w = ll.shape
+    out = torch.empty(B, Cc, 2 * h, 2 * w, dtype=torch.float32, device=ll.device)
+    _lib.check(_lib.load().hv_idwt2_haar(_p(ll), _p(hl), _p(lh), _p(hh), _p(out), B * Cc, h, w, _dt(ll), _stream()))
+    return out
+
+
+def freq_split3d(x, ct, ch, cw):
+    """x (..., T, H, W) fp32 -> (low, high) via the three circulant matrices."""
+    _chk_cuda(x, ct, ch, cw)
+    T, H, W = x.shape[-3:]
+    vols = x.numel() // (T * H * W) if x.numel() else 0
+    lo, hi = torch.empty_like(x), torch.empty_like(x)
+    _lib.check(_lib.load().hv_freq_split3d(_p(x), _p(ct), _p(ch), _p(cw), _p(lo), _p(hi), vols, T, H, W, _stream()))
+    return lo, hi
+
+
+# ------------------------------------------------------------------ row addressing
+@dataclass
+class Rows:
+    """Row range [row_off, row_off+L) of every frame of an fp32 residual buffer
+    res: (frames, frame_rows, D).  Rows in [img_start, img_start+img_len) are image rows."""
+    res: torch.Tensor
+    row_off: int
+    L: int
+    img_start: int = 0
+    img_len: int = 0
+
+    @property
+    def frames(self):
+        return self.res.shape[0]
+
+    @property
+    def frame_rows(self):
+        return self.res.shape[1]
+
+    @property
+    def D(self):
+        return self.res.shape[2]
+
+    @property
+    def M(self):
+        return self.frames * self.L
+
+
+@dataclass
+class Ada:
+    """adaLN table (rows, ld) fp32 = Linear(SiLU(temb)); the conditioning row of frame f is
+    (f // cond_div) * cond_mul."""
+    table: torch.Tensor
+    cond_div: int = 1
+    cond_mul: int = 1
+
+
+def ln_modulate(rows, ln_w, ln_b, eps, out, ada=None, shift_mot=0, scale_mot=0, shift_img=0, scale_img=0):
+    _chk_cuda(rows.res, ln_w, ln_b, out)
+    t = ada.table if ada is not None else None
+    _lib.check(_lib.load().hv_ln_modulate(
+        _p(rows.res), rows.frames, rows.frame_rows, rows.row_off, rows.L, rows.D, _p(ln_w), _p(ln_b), float(eps),
+        _p(t), t.shape[1] if t is not None else 0, shift_mot, scale_mot, shift_img, scale_img,
+        rows.img_start, rows.img_len, ada.cond_div if ada else 1, ada.cond_mul if ada else 1,
+        _p(out), _dt(out), _stream()))
+    return out
+
+
+def patch_embed(in1, in2, p, w, bias, pos, tpos, out, frame_rows, row_off, D):
+    _chk_cuda(in1, in2, w, bias, pos, tpos, out)
+    frames, C1, H, W = in1.shape
+    C2 = in2.shape[1] if in2 is not None else 0
+    _lib.check(_lib.load().hv_patch_embed(_p(in1), C1, _p(in2), C2, frames, H, W, p, _p(w), _p(bias), _p(pos), _p(tpos),
+                                          tpos.shape[0] if tpos is not None else 1, _p(out), _dt(out), frame_rows, row_off, D,
+                                          _stream()))
+    return out
+
+
+def final_head(rows, n1w, n1b, n2w, n2b, eps, ada, shift_col, scale_col, w, bias, C_out, p, Wp, pre, zt, dt):
+    _chk_cuda(rows.res, w, bias, pre, zt)
+    t = ada.table if ada is not None else None
+    _lib.check(_lib.load().hv_final_head(_p(rows.res), rows.frames, rows.frame_rows, rows.row_off, rows.L, rows.D,
+                                         _p(n1w), _p(n1b), _p(n2w), _p(n2b), float(eps), _p(t),
+                                         t.shape[1] if t is not None else 0, shift_col, scale_col, _p(w), _p(bias),
+                                         C_out, p, Wp, _p(pre), _p(zt), float(dt), _stream()))
+
+
+def timestep_embed(t, dim, out):
+    _chk_cuda(t, out)
+    _lib.check(_lib.load().hv_timestep_embed(_p(t), t.numel(), dim, _p(out), _dt(out), _stream()))
+    return out
+
+
+def silu(x, out):
+    _chk_cuda(x, out)
+    _lib.check(_lib.load().hv_silu(_p(x), _dt(x), _p(out), _dt(out), x.numel(), _stream()))
+    return out
+
+
+def convert(x, out):
+    _chk_cuda(x, out)
+    _lib.check(_lib.load().hv_convert(_p(x), _dt(x), _p(out), _dt(out), x.numel(), _stream()))
+    return out
+
+
+def axpy(a, x, y):
+    _chk_cuda(x, y)
+    _lib.check(_lib.load().hv_axpy(float(a), _p(x), _p(y), x.numel(), _stream()))
+    return y
+
+
+def rows_scatter(src, stride_f, stride_i, add, rows):
+    _chk_cuda(src, add, rows.res)
+    _lib.check(_lib.load().hv_rows_scatter(_p(src), stride_f, stride_i, _p(add), _p(rows.res), rows.frames, rows.frame_rows,
+                                           rows.row_off, rows.L, rows.D, _stream()))
+
+
+def rows_gather(rows, out):
+    _chk_cuda(rows.res, out)
+    _lib.check(_lib.load().hv_rows_gather(_p(rows.res), rows.frames, rows.frame_rows, rows.row_off, rows.L, rows.D, _p(out),
+                                          _stream()))
+    return out
+
+
+def conv3x3(x, w, bias, stride):
+    _chk_cuda(x, w, bias)
+    B, Cin, H, W = x.shape
+    Cout = w.shape[0]
+    Ho, Wo = (H + 2 - 3) // stride + 1, (W + 2 - 3) // stride + 1
+    y = torch.empty(B, Cout, Ho, Wo, dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().hv_conv3x3(_p(x), _p(w), _p(bias), _p(y), B, Cin, Cout, H, W, stride, _stream()))
+    return y
+
+
+def maxpool2(x):
+    _chk_cuda(x)
+    B, Cc, H, W = x.shape
+    y = torch.empty(B, Cc, H // 2, W // 2, dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().hv_maxpool2(_p(x), _p(y), B * Cc, H, W, _stream()))
+    return y
+
+
+def rope_(q, k, batch, L, heads, head_dim, start_pos=0, base=10000.0):
+    _chk_cuda(q, k)
+    _lib.check(_lib.load().hv_rope(_p(q), _p(k), batch, L, heads, head_dim, heads * head_dim, start_pos, float(base), _stream()))
+
+
+# ------------------------------------------------------------------ GEMM
+def epi_store(out, bias=None, gelu=False):
+    e = HvEpilogue()
+    e.mode = EPI_GELU if gelu else EPI_STORE
+    e.out_dtype, e.out, e.ldo, e.bias = _dt(out), out.data_ptr(), out.stride(0), (bias.data_ptr() if bias is not None else None)
+    return e
+
+
+def epi_qknorm(out, bias, qn_w, qn_b, kn_w, kn_b, q_cols, k_cols, eps=1e-6):
+    e = epi_store(out, bias)
+    e.mode = EPI_QKNORM
+    e.qn_w = qn_w.data_ptr() if qn_w is not None else None
+    e.qn_b = qn_b.data_ptr() if qn_b is not None else None
+    e.kn_w = kn_w.data_ptr() if kn_w is not None else None
+    e.kn_b = kn_b.data_ptr() if kn_b is not None else None
+    e.q_cols, e.k_cols, e.qk_eps = q_cols, k_cols, eps
+    return e
+
+
+def epi_residual(rows, bias=None, ada=None, gate_mot=0, gate_img=0):
+    e = HvEpilogue()
+    e.mode = EPI_RESIDUAL
+    e.bias = bias.data_ptr() if bias is not None else None
+    e.res, e.L, e.frame_rows, e.row_off = rows.res.data_ptr(), rows.L, rows.frame_rows, rows.row_off
+    e.img_start, e.img_len = rows.img_start, rows.img_len
+    if ada is not None:
+        e.gate, e.gate_ld = ada.table.data_ptr(), ada.table.shape[1]
+        e.gate_col_mot, e.gate_col_img, e.cond_div, e.cond_mul = gate_mot, gate_img, ada.cond_div, ada.cond_mul
+    else:
+        e.cond_div = e.cond_mul = 1
+    return e
+
+
+def linear(A, W, epi):
+    """epilogue(A[M,K] @ W[N,K]^T).  bf16 x bf16 -> tcgen05 GEMM; anything with fp32 W -> fp32 SIMT GEMM."""
+    _chk_cuda(A, W)
+    M, K = A.shape
+    N = W.shape[0]
+    assert W.shape[1] == K, (A.shape, W.shape)
+    lib = _lib.load()
+    if W.dtype == torch.bfloat16:
+        if A.dtype != torch.bfloat16:
+            raise TypeError("bf16 weights need bf16 activations")
+        _lib.check(lib.hv_linear_bf16(_p(A), A.stride(0), _p(W), W.stride(0), M, N, K, C.byref(epi), _stream()))
+    else:
+        _lib.check(lib.hv_linear_f32(_p(A), _dt(A), A.stride(0), _p(W), W.stride(0), M, N, K, C.byref(epi), _stream()))
+
+
+# ------------------------------------------------------------------ attention
+def seq_map(sdiv, sa, sb, sc):
+    m = HvSeqMap()
+    m.sdiv, m.sa, m.sb, m.sc = sdiv, sa, sb, sc
+    return m
+
+
+def attention(q, k, v, out, seqs, heads, hd, Lq, Lkv, qmap, kvmap, scale, mask=None):
+    """q/k/v/out are 2-D (rows, cols) views whose column 0 is head 0; row strides are taken from the views."""
+    _lib.require_device()
+    _lib.check(_lib.load().hv_attention(_p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0),
+                                        _dt(q), seqs, heads, hd, Lq, Lkv, C.byref(qmap), C.byref(kvmap), float(scale),
+                                        _p(mask), _stream()))
+    return out

@@ -1,0 +1,380 @@
+"""Motion encoders and the default rectified-flow DiT with the reference's class names, kwargs and
+state-dict keys (reference: model/transformer.py:36-192, 406-586, 1746-2043), running on the
+hivae_b200 sm_100a kernels.  No tensor is transposed between the spatial and temporal blocks: the
+'(n t) s d <-> (n s) t d' regrouping of the reference is expressed as strided sequence maps.
+"""
+from typing import Optional, Union
+
+import numpy as np
+import torch
+from torch import nn
+
+from . import embeddings as E
+from . import engine, ops
+from .engine import AdaPack, Ctx
+from .modules import (AdaLayerNorm, AMDTransformerBlock, BasicCrossTransformerBlock, BasicDiTBlock,
+                      BasicTransformerBlock, PatchEmbed)
+from .ops import Ada, Rows
+
+
+class Timesteps(nn.Module):
+    """diffusers Timesteps (parameter-free)."""
+
+    def __init__(self, num_channels, flip_sin_to_cos, downscale_freq_shift):
+        super().__init__()
+        if not flip_sin_to_cos or downscale_freq_shift != 0:
+            raise NotImplementedError("only flip_sin_to_cos=True, freq_shift=0 (the reference's setting)")
+        self.num_channels = num_channels
+
+
+class TimestepEmbedding(nn.Module):
+    """diffusers TimestepEmbedding parameter layout: linear_1 -> SiLU -> linear_2."""
+
+    def __init__(self, in_channels, time_embed_dim, act_fn="silu"):
+        super().__init__()
+        if act_fn != "silu":
+            raise NotImplementedError(act_fn)
+        self.linear_1 = nn.Linear(in_channels, time_embed_dim)
+        self.act = nn.SiLU()
+        self.linear_2 = nn.Linear(time_embed_dim, time_embed_dim)
+
+
+class _Prepared:
+    pass
+
+
+class _HvModule(nn.Module):
+    """caches the prepared (packed) weights per (device, compute dtype, parameter versions)"""
+
+    def _prepared(self, device):
+        dtype = engine.compute_dtype_for(self)
+        key = (torch.device(device), dtype, sum(p._version for p in self.parameters()))
+        if getattr(self, "_hv_key", None) != key:
+            self._hv_P = self._prepare(Ctx(device, dtype))
+            self._hv_key = key
+        return self._hv_P
+
+    def _patch_params(self, ctx, pe):
+        w = ctx.f32(pe.proj.weight)
+        return w.reshape(w.shape[0], -1).contiguous(), ctx.f32(pe.proj.bias)
+
+
+def _final_norm_out(need_norm_out, m):
+    if need_norm_out:  # rarely-used option (motion_need_norm_out=False in every shipped script)
+        m = torch.nn.functional.layer_norm(m, (m.shape[-1],))
+    return m
+
+
+# ================================================================================================
+class MotionEncoderLearnTokenTransformer(_HvModule):
+    """Object-motion encoder (transformer.py:36-162): learnable tokens || patch tokens -> blocks ->
+    first tokens -> LN -> Linear."""
+
+    def __init__(self, img_height=32, img_width=32, img_inchannel=4, img_patch_size=2, motion_token_num=12,
+                 motion_channel=128, need_norm_out=True, num_attention_heads=12, attention_head_dim=64, num_layers=8,
+                 freq_shift=0, dropout=0.0, attention_bias=True, activation_fn="gelu-approximate",
+                 norm_elementwise_affine=True, norm_eps=1e-5, spatial_interpolation_scale=1.0,
+                 temporal_interpolation_scale=1.0):
+        super().__init__()
+        hidden_dim = num_attention_heads * attention_head_dim
+        iph, ipw = img_height // img_patch_size, img_width // img_patch_size
+        self.img_token_len = iph * ipw
+        self.motion_token = nn.Parameter(torch.randn(1, motion_token_num, motion_channel) * 0.02)
+        self.motion_embed = nn.Linear(motion_channel, hidden_dim)
+        self.patch_embed = PatchEmbed(img_patch_size, img_inchannel, hidden_dim)
+        self.embedding_dropout = nn.Dropout(dropout)
+        self.register_buffer("pos_embedding", E.table(E.sincos_2d(hidden_dim, iph, ipw)), persistent=False)
+        self.transformer_blocks = nn.ModuleList([
+            BasicTransformerBlock(dim=hidden_dim, num_attention_heads=num_attention_heads,
+                                  attention_head_dim=attention_head_dim, dropout=dropout, activation_fn=activation_fn,
+                                  attention_bias=attention_bias, norm_elementwise_affine=norm_elementwise_affine,
+                                  norm_eps=norm_eps) for _ in range(num_layers)])
+        self.norm_final = nn.LayerNorm(hidden_dim, eps=norm_eps, elementwise_affine=norm_elementwise_affine)
+        self.proj_out = nn.Linear(hidden_dim, motion_channel)
+        self.need_norm_out = need_norm_out
+        if need_norm_out:
+            self.norm_out = nn.LayerNorm(motion_channel, eps=norm_eps, elementwise_affine=False)
+        self.gradient_checkpointing = False
+
+    def _prepare(self, ctx):
+        P = _Prepared()
+        P.ctx = ctx
+        P.blocks = [engine.prepare_block(ctx, b, "basic") for b in self.transformer_blocks]
+        P.pw, P.pb = self._patch_params(ctx, self.patch_embed)
+        P.pos = ctx.f32(self.pos_embedding[0])
+        P.tok = ctx.f32(self.motion_token[0])
+        P.ew, P.eb = ctx.f32(self.motion_embed.weight), ctx.f32(self.motion_embed.bias)
+        P.nfw, P.nfb = ctx.f32(self.norm_final.weight), ctx.f32(self.norm_final.bias)
+        P.ow, P.ob = ctx.f32(self.proj_out.weight), ctx.f32(self.proj_out.bias)
+        return P
+
+    @torch.no_grad()
+    def forward(self, img_hidden_states, mask_ratio=None):
+        if mask_ratio is not None:
+            raise NotImplementedError("random token masking (train-time augmentation, transformer.py:164-192) is out of scope")
+        N, T, C, H, W = img_hidden_states.shape
+        P = self._prepared(img_hidden_states.device)
+        ctx = P.ctx
+        D, p = P.ew.shape[0], self.patch_embed.patch_size
+        Lm, S = P.tok.shape[0], self.img_token_len
+        assert S == (H // p) * (W // p), "img_token_len should be equal!"
+        frames, FR = N * T, Lm + S
+        x = img_hidden_states.reshape(frames, C, H, W).float().contiguous()
+        res = ctx.buf("enc_res", (frames, FR, D), torch.float32)
+        tok = engine.small_linear(ctx, P.tok, P.ew, P.eb, "enc_tok")          # (Lm, D), same for every frame
+        ops.rows_scatter(tok, 0, 1, None, Rows(res, 0, Lm))
+        ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, None, res, FR, Lm, D)
+        rows, geom = Rows(res, 0, FR), engine.dense_geom(frames, FR)
+        for bp in P.blocks:
+            engine.run_block(ctx, bp, rows, geom)
+        mrows = Rows(res, 0, Lm)
+        y = ops.ln_modulate(mrows, P.nfw, P.nfb, self.norm_final.eps, ctx.buf("enc_fin", (frames * Lm, D), torch.float32))
+        m = engine.small_linear(ctx, y, P.ow, P.ob, "enc_out").view(N, T, Lm, -1).clone()
+        return _final_norm_out(self.need_norm_out, m)
+
+
+# ================================================================================================
+class MotionEncoderLearnTokenOnlyTemporalTransformer(_HvModule):
+    """Camera-motion encoder (transformer.py:406-556): per spatial location, T learnable temporal
+    queries cross-attend to that location's T image tokens."""
+
+    def __init__(self, img_height=32, img_width=32, img_inchannel=4, img_patch_size=2, motion_token_num=12,
+                 motion_channel=128, need_norm_out=True, video_frames=16, num_attention_heads=12, attention_head_dim=64,
+                 num_layers=8, freq_shift=0, dropout=0.0, attention_bias=True, activation_fn="gelu-approximate",
+                 norm_elementwise_affine=True, norm_eps=1e-5, spatial_interpolation_scale=1.0,
+                 temporal_interpolation_scale=1.0):
+        super().__init__()
+        hidden_dim = num_attention_heads * attention_head_dim
+        iph, ipw = img_height // img_patch_size, img_width // img_patch_size
+        self.img_token_len = iph * ipw
+        self.video_frames = video_frames
+        self.motion_token = nn.Parameter(torch.randn(1, motion_token_num, motion_channel) * 0.02)
+        self.motion_embed = nn.Linear(motion_channel, hidden_dim)
+        self.patch_embed = PatchEmbed(img_patch_size, img_inchannel, hidden_dim)
+        self.embedding_dropout = nn.Dropout(dropout)
+        self.register_buffer("pos_embedding", E.table(E.sincos_2d(hidden_dim, iph, ipw)), persistent=False)
+        self.register_buffer("motion_temporal_embedding", E.table(E.sincos_1d(hidden_dim, np.arange(video_frames))),
+                             persistent=False)
+        self.transformer_blocks = nn.ModuleList([
+            BasicCrossTransformerBlock(dim=hidden_dim, cross_dim=hidden_dim, num_attention_heads=num_attention_heads,
+                                       attention_head_dim=attention_head_dim, dropout=dropout, activation_fn=activation_fn,
+                                       attention_bias=attention_bias, norm_elementwise_affine=norm_elementwise_affine,
+                                       norm_eps=norm_eps) for _ in range(num_layers)])
+        self.norm_final = nn.LayerNorm(hidden_dim, eps=norm_eps, elementwise_affine=norm_elementwise_affine)
+        self.proj_out = nn.Linear(hidden_dim, motion_channel)
+        self.need_norm_out = need_norm_out
+        if need_norm_out:
+            self.norm_out = nn.LayerNorm(motion_channel, eps=norm_eps, elementwise_affine=False)
+        self.gradient_checkpointing = False
+
+    def _prepare(self, ctx):
+        P = _Prepared()
+        P.ctx = ctx
+        P.blocks = [engine.prepare_block(ctx, b, "cross") for b in self.transformer_blocks]
+        P.pw, P.pb = self._patch_params(ctx, self.patch_embed)
+        P.pos = ctx.f32(self.pos_embedding[0])
+        P.tpos = ctx.f32(self.motion_temporal_embedding[0])
+        P.tok = ctx.f32(self.motion_token[0])
+        P.ew, P.eb = ctx.f32(self.motion_embed.weight), ctx.f32(self.motion_embed.bias)
+        P.nfw, P.nfb = ctx.f32(self.norm_final.weight), ctx.f32(self.norm_final.bias)
+        P.ow, P.ob = ctx.f32(self.proj_out.weight), ctx.f32(self.proj_out.bias)
+        P.tabs = {}
+        return P
+
+    @staticmethod
+    def _token_table(P, ctx, T, S, D):
+        """weights-only table of the initial query tokens of one clip, cached per T"""
+        if T not in P.tabs:
+            t0 = P.tok.shape[0]
+            rep = T // t0
+            tok = engine.small_linear(ctx, P.tok, P.ew, P.eb, "cam_tok")  # (t0, D)
+            tab = torch.empty(1, T * S, D, dtype=torch.float32, device=ctx.device)
+            for t in range(T):
+                ops.rows_scatter(tok[t // rep:t // rep + 1], 0, 0, P.tpos[t:t + 1], Rows(tab, t * S, S))
+            P.tabs[T] = tab
+        return P.tabs[T]
+
+    @torch.no_grad()
+    def forward(self, img_hidden_states, mask_ratio=None):
+        if mask_ratio is not None:
+            raise NotImplementedError("random token masking (transformer.py:558-586) is out of scope")
+        N, T, C, H, W = img_hidden_states.shape
+        P = self._prepared(img_hidden_states.device)
+        ctx = P.ctx
+        D, p = P.ew.shape[0], self.patch_embed.patch_size
+        S, t0 = self.img_token_len, P.tok.shape[0]
+        assert S == (H // p) * (W // p), "img_token_len should be equal!"
+        assert T <= self.video_frames and T % t0 == 0
+        x = img_hidden_states.reshape(N * T, C, H, W).float().contiguous()
+        # image K/V tokens, dense rows ordered (n, t, s), + 2-D sincos + temporal sincos  (506-514)
+        img = ctx.buf("cam_img", (N * T * S, D))
+        ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, P.tpos[:T].contiguous(), img.view(N * T, S, D), S, 0, D)
+        # motion queries: token (t) = embed(motion_token)[t // (T/t0)] + temporal[t], identical for all (n, s)  (521-531)
+        res = ctx.buf("cam_res", (N * T, S, D), torch.float32)                            # rows ordered (n, t, s)
+        block = Rows(res.view(N, T * S, D), 0, T * S)
+        tab = self._token_table(P, ctx, T, S, D)  # (T*S, D): row t*S + s = tok[t // (T/t0)] + temporal[t]
+        ops.rows_scatter(tab.view(T * S, D), 0, 1, None, block)
+        rows = Rows(res, 0, S)
+        geom = engine.strided_geom(N, S, T)
+        for bp in P.blocks:
+            engine.run_block(ctx, bp, rows, geom, kv_dense=img)
+        y = ops.ln_modulate(rows, P.nfw, P.nfb, self.norm_final.eps, ctx.buf("cam_fin", (N * T * S, D), torch.float32))
+        m = engine.small_linear(ctx, y, P.ow, P.ob, "cam_out").view(N, T, S, -1).clone()  # already 'n t s c'
+        return _final_norm_out(self.need_norm_out, m)
+
+
+# ================================================================================================
+class AMDDiffusionTransformerModelImgSpatialTempMotion(_HvModule):
+    """Default rectified-flow denoiser (transformer.py:1746-2043): per layer an object joint block
+    (image + object tokens), a camera joint block (image + camera tokens) and a temporal block."""
+
+    _supports_gradient_checkpointing = True
+
+    def __init__(self, num_attention_heads=20, attention_head_dim=64, out_channels: Optional[int] = 4, num_layers=12,
+                 use_camera=False, use_object=False, image_width=32, image_height=32, image_patch_size=2,
+                 image_in_channels: Optional[int] = 4, motion_token_num=12, camera_motion_in_channels: Optional[int] = 16,
+                 object_motion_in_channels: Optional[int] = 64, motion_target_num_frame=16, flip_sin_to_cos=True,
+                 freq_shift=0, time_embed_dim=512, dropout=0.0, attention_bias=True, temporal_compression_ratio=4,
+                 activation_fn="gelu-approximate", timestep_activation_fn="silu", norm_elementwise_affine=True,
+                 norm_eps=1e-5, spatial_interpolation_scale=1.0, temporal_interpolation_scale=1.0):
+        super().__init__()
+        hidden_dim = num_attention_heads * attention_head_dim
+        iph, ipw = image_height // image_patch_size, image_width // image_patch_size
+        self.image_patch_size, self.out_channels = image_patch_size, out_channels
+        self.target_frame = motion_target_num_frame
+        self.use_camera, self.use_object = use_camera, use_object
+        self.image_patch_embed = PatchEmbed(patch_size=image_patch_size, in_channels=image_in_channels,
+                                            embed_dim=hidden_dim, bias=True)
+        self.embedding_dropout = nn.Dropout(dropout)
+        self.register_buffer("pos_embedding", E.table(E.sincos_2d(hidden_dim, iph, ipw)), persistent=False)
+        self.register_buffer("motion_pos_embedding", E.table(E.sincos_1d(hidden_dim, np.arange(2 + 2 * motion_token_num))),
+                             persistent=False)
+        self.register_buffer("img_temporal_embedding", E.table(E.sincos_1d(hidden_dim, np.arange(self.target_frame))),
+                             persistent=False)
+        self.time_proj = Timesteps(hidden_dim, flip_sin_to_cos, freq_shift)
+        self.time_embedding = TimestepEmbedding(hidden_dim, time_embed_dim, timestep_activation_fn)
+        blk = dict(dim=hidden_dim, num_attention_heads=num_attention_heads, attention_head_dim=attention_head_dim,
+                   time_embed_dim=time_embed_dim, dropout=dropout, activation_fn=activation_fn,
+                   attention_bias=attention_bias, norm_elementwise_affine=norm_elementwise_affine, norm_eps=norm_eps)
+        if use_camera:
+            self.camera_motion_patch_embed = nn.Linear(camera_motion_in_channels, hidden_dim)
+            self.camera_transformer_blocks = nn.ModuleList([AMDTransformerBlock(**blk) for _ in range(num_layers)])
+        if use_object:
+            self.source_token = nn.Parameter(torch.zeros(1, 1, hidden_dim), requires_grad=True)
+            self.target_token = nn.Parameter(torch.zeros(1, 1, hidden_dim), requires_grad=True)
+            self.object_motion_patch_embed = nn.Linear(object_motion_in_channels, hidden_dim)
+            self.object_transformer_blocks = nn.ModuleList([AMDTransformerBlock(**blk) for _ in range(num_layers)])
+        self.spatial_blocks = nn.ModuleList([BasicDiTBlock(**blk) for _ in range(num_layers)])
+        self.norm_final = nn.LayerNorm(hidden_dim, norm_eps, norm_elementwise_affine)
+        self.norm_out = AdaLayerNorm(embedding_dim=time_embed_dim, output_dim=2 * hidden_dim,
+                                     norm_elementwise_affine=norm_elementwise_affine, norm_eps=norm_eps, chunk_dim=1)
+        self.proj_out = nn.Linear(hidden_dim, image_patch_size * image_patch_size * out_channels)
+        self.gradient_checkpointing = False
+
+    def _prepare(self, ctx):
+        P = _Prepared()
+        P.ctx = ctx
+        n = len(self.spatial_blocks)
+        P.obj = [engine.prepare_block(ctx, b, "joint") for b in self.object_transformer_blocks] if self.use_object else [None] * n
+        P.cam = [engine.prepare_block(ctx, b, "joint") for b in self.camera_transformer_blocks] if self.use_camera else [None] * n
+        P.sp = [engine.prepare_block(ctx, b, "dit") for b in self.spatial_blocks]
+        order = [bp for trio in zip(P.obj, P.cam, P.sp) for bp in trio if bp is not None]
+        P.ada = AdaPack(ctx, order, extra=[(self.norm_out.linear.weight, self.norm_out.linear.bias)])
+        P.pw, P.pb = self._patch_params(ctx, self.image_patch_embed)
+        P.pos, P.tpos = ctx.f32(self.pos_embedding[0]), ctx.f32(self.img_temporal_embedding[0])
+        P.mpos = ctx.f32(self.motion_pos_embedding[0])
+        te = self.time_embedding
+        P.tw1, P.tb1 = ctx.weight(te.linear_1.weight), ctx.f32(te.linear_1.bias)
+        P.tw2, P.tb2 = ctx.weight(te.linear_2.weight), ctx.f32(te.linear_2.bias)
+        if self.use_camera:
+            P.cw, P.cb = ctx.f32(self.camera_motion_patch_embed.weight), ctx.f32(self.camera_motion_patch_embed.bias)
+        if self.use_object:
+            P.ow, P.ob = ctx.f32(self.object_motion_patch_embed.weight), ctx.f32(self.object_motion_patch_embed.bias)
+            P.stok, P.ttok = ctx.f32(self.source_token[0]), ctx.f32(self.target_token[0])
+        P.nfw, P.nfb = ctx.f32(self.norm_final.weight), ctx.f32(self.norm_final.bias)
+        P.now, P.nob = ctx.f32(self.norm_out.norm.weight), ctx.f32(self.norm_out.norm.bias)
+        P.hw, P.hb = ctx.f32(self.proj_out.weight), ctx.f32(self.proj_out.bias)
+        return P
+
+    # -- step 1 (once per decode): embed the motion tokens ---------------------------------------
+    def set_motion(self, N, device, camera=None, obj_src=None, obj_tgt=None):
+        """Builds the per-frame initial motion token rows (transformer.py:1947-1980); they do not
+        depend on the timestep or on z_t, so a sampling loop computes them once."""
+        P = self._prepared(device)
+        ctx = P.ctx
+        D = P.hw.shape[1]
+        M = _Prepared()
+        M.Lo = M.Lc = 0
+        if obj_src is not None:
+            l = obj_tgt.shape[1]
+            M.Lo = 2 * l + 2
+            M.obj = ctx.buf("dit_minit_obj", (N, M.Lo, D), torch.float32)
+            src = engine.small_linear(ctx, obj_src.reshape(N * l, -1).float().contiguous(), P.ow, P.ob, "dit_osrc")
+            ops.rows_scatter(src, l, 1, P.mpos[1:1 + l], Rows(M.obj, 1, l))
+            tgt = engine.small_linear(ctx, obj_tgt.reshape(N * l, -1).float().contiguous(), P.ow, P.ob, "dit_otgt")
+            ops.rows_scatter(tgt, l, 1, P.mpos[l + 2:2 * l + 2], Rows(M.obj, l + 2, l))
+            ops.rows_scatter(P.stok, 0, 0, P.mpos[0:1], Rows(M.obj, 0, 1))
+            ops.rows_scatter(P.ttok, 0, 0, P.mpos[l + 1:l + 2], Rows(M.obj, l + 1, 1))
+        if camera is not None:
+            M.Lc = camera.shape[2]
+            cam = camera.reshape(N * M.Lc, -1).float().contiguous()  # 'n t s d -> (n t) s d'
+            M.cam = engine.small_linear(ctx, cam, P.cw, P.cb, "dit_minit_cam")
+        return M
+
+    # -- step 2 (every Euler step) -----------------------------------------------------------------
+    def run(self, M, in1, in2, timestep, pre=None, zt=None, dt=0.0):
+        """One denoiser evaluation.  in1 (+ in2) are the NCHW channel groups of the image input
+        (zi, zt — the torch.cat of model_AMD.py:2178 is folded into the patch-embed kernel);
+        writes the prediction to `pre` and/or applies zt += dt * pre in place."""
+        N, _, Hi, Wi = in1.shape
+        P = self._prepared(in1.device)
+        ctx = P.ctx
+        T, p = self.target_frame, self.image_patch_size
+        n = N // T
+        D = P.hw.shape[1]
+        S = (Hi // p) * (Wi // p)
+        Lo, Lc = M.Lo, M.Lc
+        FR = Lo + S + Lc
+        res = ctx.buf("dit_res", (N, FR, D), torch.float32)
+        ops.patch_embed(in1, in2, p, P.pw, P.pb, P.pos, P.tpos, res, FR, Lo, D)
+        if Lo:
+            ops.rows_scatter(M.obj.view(N * Lo, D), Lo, 1, None, Rows(res, 0, Lo))
+        if Lc:
+            ops.rows_scatter(M.cam, Lc, 1, None, Rows(res, Lo + S, Lc))
+        # timestep embedding -> temb -> every adaLN table of the step in ONE GEMM
+        ts = timestep.to(device=in1.device, dtype=torch.float32).contiguous()
+        te = ops.timestep_embed(ts, D, ctx.buf("dit_te", (N, D)))
+        h = engine.small_linear(ctx, te, P.tw1, P.tb1, "dit_te_h")
+        hs = ops.silu(h, ctx.buf("dit_te_hs", h.shape))
+        emb = engine.small_linear(ctx, hs, P.tw2, P.tb2, "dit_emb")
+        table = P.ada.table(ctx, emb, "dit_ada")
+        ada_f, ada_s = Ada(table, 1, 1), Ada(table, T, T)  # emb per frame / emb of frame 0 of the clip (1943-1945)
+        obj_rows = Rows(res, 0, Lo + S, img_start=Lo, img_len=S)
+        cam_rows = Rows(res, Lo, S + Lc, img_start=Lo, img_len=S)
+        img_rows = Rows(res, Lo, S, img_start=Lo, img_len=S)
+        g_obj, g_cam = engine.dense_geom(N, Lo + S), engine.dense_geom(N, S + Lc)
+        g_tmp = engine.strided_geom(n, S, T)
+        for bo, bc, bs in zip(P.obj, P.cam, P.sp):
+            if Lo:
+                engine.run_block(ctx, bo, obj_rows, g_obj, ada_f)
+            if Lc:
+                engine.run_block(ctx, bc, cam_rows, g_cam, ada_f)
+            engine.run_block(ctx, bs, img_rows, g_tmp, ada_s)
+        off = P.ada.extra_off[0]
+        ops.final_head(img_rows, P.nfw, P.nfb, P.now, P.nob, self.norm_final.eps, ada_f, off, off + D,
+                       P.hw, P.hb, self.out_channels, p, Wi // p, pre, zt, dt)
+        return pre
+
+    @torch.no_grad()
+    def forward(self, image_hidden_states, timestep: Union[int, float, torch.Tensor], timestep_cond=None,
+                camera_motion_target_hidden_states=None, object_motion_source_hidden_states=None,
+                object_motion_target_hidden_states=None, return_dict=True):
+        N, Ci, Hi, Wi = image_hidden_states.shape
+        x = image_hidden_states.float().contiguous()
+        M = self.set_motion(N, x.device, camera_motion_target_hidden_states, object_motion_source_hidden_states,
+                            object_motion_target_hidden_states)
+        if not torch.is_tensor(timestep):
+            timestep = torch.full((N,), float(timestep), device=x.device)
+        pre = torch.empty(N, self.out_channels, Hi, Wi, dtype=torch.float32, device=x.device)
+        self.run(M, x, None, timestep, pre=pre)
+        return pre.to(image_hidden_states.dtype)

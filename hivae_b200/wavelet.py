@@ -1,0 +1,51 @@
+"""Haar DWT / IDWT with the reference's API (model/wavelet.py) on the sm_100a kernels."""
+import torch
+from torch import nn
+
+from . import ops
+
+
+def dwt_init(x):
+    """(B,C,H,W) -> (x_LL, x_HL, x_LH, x_HH), dtype preserved (wavelet.py:13-27)."""
+    return ops.dwt2_haar(x.contiguous())
+
+
+def iwt_init(x):
+    """x = cat(LL,HL,LH,HH) on dim 0 -> (B,C,2h,2w), always fp32 (wavelet.py:31-48)."""
+    x = x.contiguous()
+    B = x.shape[0] // 4
+    return ops.idwt2_haar(x[0:B], x[B:2 * B], x[2 * B:3 * B], x[3 * B:4 * B])
+
+
+class DWT(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.requires_grad = False
+
+    def forward(self, x):
+        return dwt_init(x)
+
+
+class IWT(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.requires_grad = False
+
+    def forward(self, x):
+        return iwt_init(x)
+
+
+def dwt_pyramid(x, levels):
+    """Multi-level analysis (the caller-side recursion on LL of frenquence_wavelet.py:86-89).
+    Returns ([(HL, LH, HH) per level], LL of the last level)."""
+    bands, ll = [], x
+    for _ in range(levels):
+        ll, hl, lh, hh = dwt_init(ll)
+        bands.append((hl, lh, hh))
+    return bands, ll
+
+
+def iwt_pyramid(bands, ll):
+    for hl, lh, hh in reversed(bands):
+        ll = ops.idwt2_haar(ll.contiguous(), hl, lh, hh)
+    return ll

@@ -1,0 +1,196 @@
+/*
+ * hivae_b200 — C ABI of the B200 (sm_100a) hot path of Hi-VAE.
+ *
+ * Drop-in boundary: the reference (HuaizeLiu/Hi-VAE) has no FFI
+ * layer of its own — its hot path is torch.nn.Module code that resolves to
+ * cuBLASLt / SDPA / cuFFT / ATen library kernels.  Every entry point below names
+ * the reference call site (path:line under /root/reference) whose device work it
+ * replaces.  The Python host package `hivae_b200/` binds these symbols with
+ * ctypes and mirrors the reference's nn.Module API.
+ *
+ * Conventions
+ *   - plain pointers + sizes, no torch types; all pointers are DEVICE pointers
+ *     unless the name ends in `_host`;
+ *   - every function returns 0 on success, a negative HV_E* code on failure;
+ *     `hv_last_error()` returns a thread-local message;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - no function allocates device memory; the caller owns inputs and outputs;
+ *   - dtype codes: HV_F32 = 0, HV_BF16 = 1.
+ *
+ * Row addressing ("frames")
+ *   Token streams live in an fp32 residual buffer laid out as `frames` frames of
+ *   `frame_rows` rows x D columns.  A kernel works on the row range
+ *   [row_off, row_off+L) of every frame; the "dense" matrix it reads/writes has
+ *   frames*L rows, dense row r <-> (frame f = r / L, i = r % L) <-> residual row
+ *   f*frame_rows + row_off + i.  Rows whose absolute in-frame index lies in
+ *   [img_start, img_start+img_len) are "image" rows, all others "motion" rows
+ *   (AMDTransformerBlock's two modulation sets, model/modules.py:1065-1109).
+ */
+#ifndef HIVAE_B200_H
+#define HIVAE_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HV_F32 0
+#define HV_BF16 1
+
+#define HV_OK 0
+#define HV_EINVAL (-1)   /* bad argument / unsupported shape */
+#define HV_ECUDA (-2)    /* CUDA runtime or driver error     */
+#define HV_EARCH (-3)    /* device is not sm_100             */
+
+const char* hv_last_error(void);
+int hv_version(void);
+/* 0 if the current device is compute capability 10.x, HV_EARCH otherwise. */
+int hv_check_device(void);
+/* number of kernels launched by this library since process start (bench `gpu_launches`). */
+int64_t hv_launch_count(void);
+
+/* ------------------------------------------------------------------ wavelet
+ * model/wavelet.py:13-27 (dwt_init): one level of 2-D Haar analysis over
+ * `planes` = B*C images of H x W (both even).  Outputs are planes x H/2 x W/2. */
+int hv_dwt2_haar(const void* x, void* ll, void* hl, void* lh, void* hh,
+                 int64_t planes, int H, int W, int dtype, void* stream);
+/* model/wavelet.py:31-48 (iwt_init): inverse; the four sub-bands are the four
+ * dim-0 quarters of the reference's input.  Output is ALWAYS fp32 (wavelet.py:40-41). */
+int hv_idwt2_haar(const void* ll, const void* hl, const void* lh, const void* hh, float* out,
+                  int64_t planes, int h, int w, int dtype_in, void* stream);
+
+/* ------------------------------------------------------------------ frequency split
+ * model/frequency_utils.py:84-108 (freq_3d_filter) with the Gaussian mask of
+ * frequency_utils.py:45-81.  Because the mask is real, even and separable (even
+ * T,H,W), ifftn(fftn(x)*LPF).real equals three 1-D circular convolutions;
+ * ct/ch/cw are the T x T, H x H, W x W circulant matrices (fp32, row-major) the
+ * host derives from the mask.  x, lo, hi: vols x T x H x W fp32; hi = x - lo.
+ * Requires T*H*W*4 bytes <= 200 KB (one volume per CTA in shared memory). */
+int hv_freq_split3d(const float* x, const float* ct, const float* ch, const float* cw,
+                    float* lo, float* hi, int64_t vols, int T, int H, int W, void* stream);
+
+/* ------------------------------------------------------------------ row kernels
+ * LayerNorm (+ optional adaLN modulate) of residual rows -> dense activation.
+ *   y = (LN(x) * ln_w + ln_b) * (1 + scale) + shift
+ * Replaces nn.LayerNorm / AMDLayerNormZero / AMDLayerNormZero_OneVariable
+ * (model/modules.py:697,710,881-928) and the torch.cat of the two streams
+ * (modules.py:1088,1103).  `ada` (may be NULL) is the fp32 table
+ * Linear(SiLU(temb)) with row stride ada_ld; the conditioning row of frame f is
+ * (f / cond_div) * cond_mul; shift/scale column offsets are given per segment. */
+int hv_ln_modulate(const float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D,
+                   const float* ln_w, const float* ln_b, float eps,
+                   const float* ada, int64_t ada_ld, int shift_col_mot, int scale_col_mot,
+                   int shift_col_img, int scale_col_img, int img_start, int img_len,
+                   int cond_div, int cond_mul, void* out, int out_dtype, void* stream);
+
+/* PatchEmbed (model/modules.py:858-879) = Conv2d(k=s=p) + bias, fused with the
+ * 2-D sincos and temporal sincos adds of transformer.py:1985-1988 / 130-141 /
+ * 506-514.  Input channels come from two NCHW tensors (in1: C1 channels, in2: C2
+ * channels, in2 may be NULL) — the torch.cat((zi,zt),1) of model_AMD.py:2178.
+ * Token (f, s) is written to row f*frame_rows + row_off + s of `out` (fp32 or
+ * bf16, row stride D).  pos: S x D fp32 or NULL; tpos: Tmod x D fp32 or NULL,
+ * indexed by f % Tmod.  w: D x (C1+C2) x p x p fp32; bias: D. */
+int hv_patch_embed(const float* in1, int C1, const float* in2, int C2, int64_t frames, int H, int W, int p,
+                   const float* w, const float* bias, const float* pos, const float* tpos, int Tmod,
+                   void* out, int out_dtype, int64_t frame_rows, int row_off, int D, void* stream);
+
+/* DiT head (model/transformer.py:2032-2041): norm_final -> AdaLayerNorm(chunk_dim=1,
+ * order shift,scale; modules.py:1001-1012) -> Linear(D -> C*p*p) -> unpatchify with
+ * (c,p,q) feature order -> optional Euler update zt += dt*pre (model_AMD.py:2156).
+ * pre / zt: frames x C x H x W fp32 (zt may be NULL). */
+int hv_final_head(const float* res, int64_t frames, int64_t frame_rows, int row_off, int S, int D,
+                  const float* n1_w, const float* n1_b, const float* n2_w, const float* n2_b, float eps,
+                  const float* ada, int64_t ada_ld, int shift_col, int scale_col,
+                  const float* w, const float* bias, int C, int p, int Wp,
+                  float* pre, float* zt, float dt, void* stream);
+
+/* Timesteps(dim, flip_sin_to_cos=True, freq_shift=0) (diffusers; call site
+ * model/transformer.py:1939): out[r] = [cos(t*f_i) | sin(t*f_i)], fp32 or bf16. */
+int hv_timestep_embed(const float* t, int64_t rows, int dim, void* out, int out_dtype, void* stream);
+
+/* elementwise helpers: y = silu(x) (adaLN / TimestepEmbedding activations),
+ * dtype conversion, y = a*x + y, strided row gather/scatter between a dense
+ * matrix and residual frames (builds the token streams of transformer.py:1971-1979). */
+int hv_silu(const void* x, int in_dtype, void* y, int out_dtype, int64_t n, void* stream);
+int hv_convert(const void* x, int in_dtype, void* y, int out_dtype, int64_t n, void* stream);
+int hv_axpy(float a, const float* x, float* y, int64_t n, void* stream);
+/* res[f*frame_rows + row_off + i, :] = src[f*src_stride_f + i*src_stride_i, :] + add[i, :]
+ * (strides in rows of D floats; src_stride_f = 0 broadcasts one token set; add may be NULL, L x D). */
+int hv_rows_scatter(const float* src, int64_t src_stride_f, int64_t src_stride_i, const float* add,
+                    float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D, void* stream);
+/* dense fp32 out[(f*L+i), :] = res[f*frame_rows + row_off + i, :] */
+int hv_rows_gather(const float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D,
+                   float* out, void* stream);
+
+/* camera_down (model/model_AMD.py:1788-1793): direct 3x3 convolution (NCHW fp32,
+ * zero padding 1, stride 1 or 2) and 2x2 max-pool. */
+int hv_conv3x3(const float* x, const float* w, const float* bias, float* y,
+               int64_t B, int Cin, int Cout, int H, int W, int stride, void* stream);
+int hv_maxpool2(const float* x, float* y, int64_t planes, int H, int W, void* stream);
+
+/* RoPE of model/attention.py:39-62 applied in place to q and k rows:
+ * pairs (2i,2i+1) of every head rotated by angle (start_pos+pos) * base^(-2i/head_dim). */
+int hv_rope(float* q, float* k, int64_t batch, int L, int heads, int head_dim, int64_t ld,
+            int start_pos, float base, void* stream);
+
+/* ------------------------------------------------------------------ GEMM + fused epilogues
+ * out = epilogue(A[M,K] @ W[N,K]^T)   (nn.Linear layout, W row-major N x K).
+ * Replaces the to_q/to_k/to_v/to_out Linears of diffusers Attention, FeedForward's
+ * two Linears, the adaLN / time-embedding Linears and proj_out
+ * (call sites model/modules.py:699-719,894,901; transformer.py:1940-1941,2036). */
+typedef struct HvEpilogue {
+    int mode;            /* HV_EPI_* */
+    int out_dtype;       /* HV_F32 / HV_BF16 (modes STORE, GELU, QKNORM) */
+    void* out;           /* dense output, row stride ldo elements */
+    int64_t ldo;
+    const float* bias;   /* N or NULL */
+    /* HV_EPI_RESIDUAL: res[row(r), :] += gate * (acc + bias) */
+    float* res;
+    int L;
+    int64_t frame_rows;
+    int row_off;
+    const float* gate;   /* adaLN table or NULL (plain residual add) */
+    int64_t gate_ld;
+    int gate_col_mot, gate_col_img;
+    int img_start, img_len;
+    int cond_div, cond_mul;
+    /* HV_EPI_QKNORM: per-head (64-wide) LayerNorm on q columns [0,q_cols) and k columns
+     * [q_cols, q_cols+k_cols); remaining columns (v) stored as-is.
+     * (diffusers Attention norm_q/norm_k, eps 1e-6, model/modules.py:703-704) */
+    const float *qn_w, *qn_b, *kn_w, *kn_b;
+    int q_cols, k_cols;
+    float qk_eps;
+} HvEpilogue;
+
+#define HV_EPI_STORE 0
+#define HV_EPI_GELU 1      /* gelu(tanh) — FeedForward "gelu-approximate" */
+#define HV_EPI_RESIDUAL 2
+#define HV_EPI_QKNORM 3
+
+/* fp32 SIMT GEMM (parity mode and skinny/tiny-K linears). A: fp32 or bf16, W fp32. */
+int hv_linear_f32(const void* A, int a_dtype, int64_t lda, const float* W, int64_t ldw,
+                  int64_t M, int N, int K, const HvEpilogue* epi, void* stream);
+/* bf16 tcgen05/TMEM GEMM fed by TMA (fp32 accumulate). A, W bf16; K % 8 == 0,
+ * lda/ldw % 8 == 0, 16-byte aligned bases. */
+int hv_linear_bf16(const void* A, int64_t lda, const void* W, int64_t ldw,
+                   int64_t M, int N, int K, const HvEpilogue* epi, void* stream);
+
+/* ------------------------------------------------------------------ attention
+ * softmax(Q K^T * scale) V per (sequence, head), head_dim = hd, no dropout
+ * (F.scaled_dot_product_attention inside diffusers AttnProcessor2_0; call sites
+ * model/modules.py:699-707,794-803,1043-1051,1138-1146; model/attention.py:105-112).
+ * Row of token i of sequence s:  (s / sdiv)*sa + (s % sdiv)*sb + i*sc  (separately
+ * for the q/out side and the k/v side).  q/k/v/out point at column 0 of head 0;
+ * head h starts at column h*hd.  mask: optional Lq x Lkv fp32, entries == 0 are
+ * filled with -1e9 before the softmax (attention.py:108-109).  dtype applies to
+ * q,k,v,out. */
+typedef struct HvSeqMap { int sdiv; int64_t sa, sb, sc; } HvSeqMap;
+int hv_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                 void* out, int64_t ldo, int dtype, int64_t seqs, int heads, int hd, int Lq, int Lkv,
+                 const HvSeqMap* qmap, const HvSeqMap* kvmap, float scale, const float* mask, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HIVAE_B200_H */

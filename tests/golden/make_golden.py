@@ -164,6 +164,9 @@ def main():
         cfg = configs.DEFAULT
         m, sd = build_ref_model(ref, cfg, seed=0)
         orc = O.AMDOracle(sd, cfg["enc_nhead"], cfg["diffusion_attn_num_heads"], 16, 2, cfg["motion_token_num"])
+        import json
+        with open(os.path.join(OUT, "state_dict_keys_default.json"), "w") as f:
+            json.dump({k: list(v_.shape) for k, v_ in m.state_dict().items()}, f, indent=0)
         cam, osrc, otgt = m.encode(video, ref_img)
         ocam, oosrc, ootgt = orc.encode(video, ref_img)
         check("default encode camera", ocam, cam, 1e-4), check("default encode obj", ootgt, otgt, 1e-4)

@@ -1,0 +1,211 @@
+"""CPU tier (-m "not gpu"): the oracle against the committed golden vectors (generated from the
+unmodified reference, tests/golden/make_golden.py), host-side logic, and the C-ABI surface."""
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import amd_oracle as O
+from hivae_b200 import configs, synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+torch.set_grad_enabled(False)
+
+
+def rel(a, b):
+    return float((a - b).abs().max() / (b.abs().max() + 1e-12))
+
+
+# ------------------------------------------------------------------ oracle vs golden
+def test_oracle_signal_ops(golden):
+    g = golden("signal_ops")
+    for name, o in zip(("LL", "HL", "LH", "HH"), O.haar_dwt2(g["dwt_x"])):
+        assert torch.equal(o, g["dwt_" + name])
+    bands = torch.cat([g["dwt_LL"], g["dwt_HL"], g["dwt_LH"], g["dwt_HH"]], 0)
+    assert torch.equal(O.haar_idwt2(bands), g["iwt_out"])
+    assert rel(g["iwt_out"], g["dwt_x"]) < 1e-6  # DWT -> IWT round trip
+    for d in (5, 6):
+        lo, hi = O.freq_split3d(g["freq_x"], O.gaussian_lpf([32, 32, 32], d / 10, d / 10))
+        assert rel(lo, g["freq_lo_%d" % d]) < 1e-6 and rel(hi, g["freq_hi_%d" % d]) < 1e-6
+        assert rel(lo + hi, g["freq_x"]) < 1e-5
+    zt, tgt = O.rf_train_tuple(g["rf_z1"], g["rf_ts"], g["rf_z0"])
+    assert torch.equal(zt, g["rf_zt"]) and torch.equal(tgt, g["rf_target"])
+    assert torch.equal(O.rf_target(zt, tgt, g["rf_ts"]), g["rf_rec"])
+
+
+def test_oracle_haar_pyramid_roundtrip():
+    x = torch.randn(2, 3, 64, 48, generator=torch.Generator().manual_seed(0))
+    for levels in (1, 2, 3):
+        bands, ll = O.haar_pyramid(x, levels)
+        assert ll.shape[-2:] == (64 >> levels, 48 >> levels)
+        assert rel(O.haar_pyramid_inverse(bands, ll), x) < 1e-6
+
+
+def test_oracle_blocks(golden):
+    g = golden("blocks")
+    D, H = 128, 2
+    xh, xe, te = g["x_hid"], g["x_enc"], g["temb"]
+    from hivae_b200 import modules as M
+    blocks = {"basic": M.BasicTransformerBlock(D, H, 64, attention_bias=True),
+              "cross": M.BasicCrossTransformerBlock(D, D, H, 64, attention_bias=True),
+              "joint": M.AMDTransformerBlock(D, H, 64, 512, attention_bias=True),
+              "dit": M.BasicDiTBlock(D, H, 64, 512, attention_bias=True)}
+    for name, blk in blocks.items():
+        # the product modules expose exactly the reference's parameter names -> same synthetic weights
+        sd = {"b." + k: v for k, v in synth.synth_state_dict(((k, v.shape) for k, v in blk.state_dict().items()), 11).items()}
+        if name == "basic":
+            assert rel(O.basic_block(sd, "b", xe, H), g["basic_out"]) < 2e-5
+        elif name == "cross":
+            assert rel(O.basic_block(sd, "b", xh, H, enc=xe), g["cross_out"]) < 2e-5
+        elif name == "joint":
+            oh, oe = O.joint_block(sd, "b", xh, xe, te, H)
+            assert rel(oh, g["joint_hid"]) < 2e-5 and rel(oe, g["joint_enc"]) < 2e-5
+        else:
+            assert rel(O.dit_block(sd, "b", xe, te, H), g["dit_out"]) < 2e-5
+
+
+def _small_oracle():
+    import hivae_b200 as hv
+    cfg = configs.SMALL
+    m = hv.AMDModel_New(**cfg)
+    sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 0)
+    return O.AMDOracle(sd, cfg["enc_nhead"], cfg["diffusion_attn_num_heads"], 16, 2, cfg["motion_token_num"]), m, sd
+
+
+def test_oracle_small_model(golden):
+    """BASELINE.json config 1: small AMD encoder + rectified-flow decoder, fp32 CPU, one clip."""
+    g = golden("small_model")
+    orc, _, _ = _small_oracle()
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(1, seed=1))
+    cam, osrc, otgt = orc.encode(video, ref_img)
+    assert rel(cam, g["camera"]) < 1e-5 and rel(osrc, g["obj_src"]) < 1e-5 and rel(otgt, g["obj_tgt"]) < 1e-5
+    trace = []
+    zi, zt, zj = orc.decode(video, ref_img, cam, osrc, otgt, 1000, 4, z0=g["z0"], trace=trace)
+    for i, p in enumerate(trace):
+        assert rel(p, g["pre_%d" % i]) < 1e-5
+    assert rel(zt, g["zt"]) < 1e-5
+    assert abs(O.psnr(zt, zj) - O.psnr(g["zt"], zj)) < 0.05
+    ts = torch.tensor([437.0]).repeat_interleave(16)
+    pre, vel, ld = orc.forward(video, ref_img, ts, g["z0"])
+    assert rel(pre, g["fwd_pre"]) < 1e-5 and rel(vel, g["fwd_vel"]) < 1e-6
+    assert abs(float(ld["loss"]) - float(g["fwd_loss"][0])) < 1e-5 * float(g["fwd_loss"][0])
+
+
+def test_oracle_rope_attention(golden):
+    g = golden("signal_ops")
+    sd = synth.synth_state_dict([("wq.weight", (128, 128)), ("wq.bias", (128,)), ("wk.weight", (128, 128)), ("wk.bias", (128,)),
+                                 ("wv.weight", (128, 128)), ("wv.bias", (128,)), ("out.weight", (128, 128)), ("out.bias", (128,))], 3)
+    x = g["ropeattn_x"]
+    args = (x, sd["wq.weight"], sd["wq.bias"], sd["wk.weight"], sd["wk.bias"], sd["wv.weight"], sd["wv.bias"], 4, 40)
+    assert rel(O.rope_attention(*args), g["ropeattn_rope"]) < 1e-5
+    assert rel(O.rope_attention(*args, inference=False), g["ropeattn_norope"]) < 1e-5
+    assert rel(O.rope_attention(*args, mask=torch.tril(torch.ones(24, 24)), start_pos=3), g["ropeattn_rope_mask"]) < 1e-5
+
+
+# ------------------------------------------------------------------ host logic (no GPU)
+def test_state_dict_keys_match_reference():
+    """drop-in contract: a reference model.safetensors must load unchanged."""
+    import hivae_b200 as hv
+    with open(os.path.join(ROOT, "tests", "golden", "state_dict_keys_default.json")) as f:
+        ref = json.load(f)
+    m = hv.AMD_models["AMD_N"](**{k: v for k, v in configs.DEFAULT.items()
+                                  if k not in ("enc_nhead", "enc_ndim", "diffusion_attn_head_dim", "diffusion_attn_num_heads",
+                                               "diffusion_out_channels", "diffusion_num_layers")})
+    mine = {k: list(v.shape) for k, v in m.state_dict().items()}
+    assert mine == ref
+    assert abs(sum(int(np.prod(s)) for s in mine.values()) - 695.00e6) < 0.01e6
+
+
+def test_sincos_tables_match_oracle():
+    from hivae_b200 import embeddings as E
+    assert np.array_equal(E.sincos_2d(256, 16, 16), O.sincos_2d(256, 16, 16))
+    assert np.array_equal(E.sincos_2d(128, 4, 4), O.sincos_2d(128, 4, 4))
+    assert np.array_equal(E.sincos_1d(512, np.arange(82)), O.sincos_1d(512, np.arange(82)))
+
+
+def test_circulant_factorisation_equals_fft_split(golden):
+    """the separable circular-convolution form used by the CUDA kernel == the reference's FFT split"""
+    from hivae_b200 import frequency_utils as F
+    g = golden("signal_ops")
+    x = g["freq_x"].double()
+    for d in (0.5, 0.6):
+        ct, ch, cw = (torch.from_numpy(F._circulant(F._gauss_1d(32, d))) for _ in range(3))
+        lo = torch.einsum("ai,bj,ck,...ijk->...abc", ct, ch, cw, x)
+        assert rel(lo.float(), g["freq_lo_%d" % int(d * 10)]) < 1e-6
+    x2 = g["freq2_x"].double()  # ragged even sizes, anisotropic cut-offs, untagged mask -> rank-1 factorisation path
+    lpf2 = O.gaussian_lpf([8, 12, 20], 0.3, 0.3)
+    mats = [torch.from_numpy(F._circulant(v)) for v in F._factor_mask(lpf2)]
+    lo2 = torch.einsum("ai,bj,ck,...ijk->...abc", *mats, x2)
+    assert rel(lo2.float(), O.freq_split3d(g["freq2_x"], lpf2)[0]) < 1e-6
+    with pytest.raises(NotImplementedError):
+        F._circulant(F._gauss_1d(7, 0.5))
+    m = F.gaussian_low_pass_filter([32, 32, 32], 0.6, 0.6)
+    assert torch.equal(m, O.gaussian_lpf([32, 32, 32], 0.6, 0.6)) and m._hv_gauss == (0.6, 0.6)
+    assert torch.count_nonzero(F.gaussian_low_pass_filter([4, 4, 4], 0.0, 0.5)) == 0
+
+
+def test_rectified_flow_host(golden):
+    from hivae_b200 import RectifiedFlow
+    g = golden("signal_ops")
+    rf = RectifiedFlow(1000)
+    zt, tgt = rf.get_train_tuple(z0=g["rf_z0"], z1=g["rf_z1"], time_step=g["rf_ts"])
+    assert torch.equal(zt, g["rf_zt"]) and torch.equal(tgt, g["rf_target"])
+    assert torch.equal(rf.get_target_with_zt_vel(zt, tgt, g["rf_ts"]), g["rf_rec"])
+    out = rf.sample_loop(lambda z, t: torch.ones_like(z), torch.zeros(2, 1, 2, 2), sample_step=4)
+    assert torch.allclose(out, torch.ones(2, 1, 2, 2))  # 4 Euler steps of dt = 1/4
+    assert O.sample_steps(1000, 4) == [1000, 750, 500, 250]
+
+
+def test_config_roundtrip(tmp_path):
+    import hivae_b200 as hv
+    m = hv.AMDModel_New(**configs.SMALL)
+    m.save_config(str(tmp_path))
+    cfg = hv.AMDModel_New.load_config(str(tmp_path))
+    m2 = hv.AMDModel_New.from_config(cfg)
+    assert [k for k, _ in m2.state_dict().items()] == [k for k, _ in m.state_dict().items()]
+    with pytest.raises(NotImplementedError):
+        hv.AMDModel_New(**dict(configs.SMALL, diffusion_model_type="default"))
+
+
+def test_synth_weights_are_order_independent():
+    a = synth.synth_state_dict([("x.weight", (4, 8)), ("y.norm.weight", (8,))], 0)
+    b = synth.synth_state_dict([("y.norm.weight", (8,)), ("x.weight", (4, 8))], 0)
+    assert torch.equal(a["x.weight"], b["x.weight"]) and torch.equal(a["y.norm.weight"], b["y.norm.weight"])
+    assert abs(float(a["y.norm.weight"].mean()) - 1.0) < 0.2
+
+
+# ------------------------------------------------------------------ C-ABI surface
+def test_cabi_exports_every_declared_symbol():
+    from hivae_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "hivae_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(hv_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) >= 20
+    lib = _lib.load()
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+    assert lib.hv_version() == 100
+    assert isinstance(lib.hv_last_error(), bytes)
+
+
+def test_no_cpu_fallback():
+    """the product path must fail loudly without a GPU, never fall back to torch/CPU"""
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import hivae_b200 as hv
+    with pytest.raises(RuntimeError):
+        hv.dwt_init(torch.randn(1, 1, 4, 4))
+    with pytest.raises(RuntimeError):
+        hv.BasicTransformerBlock(128, 2, 64, attention_bias=True)(torch.randn(1, 4, 128))
+
+
+def test_product_does_not_import_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "hivae_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle|import_module\(.oracle", src, flags=re.M), f
