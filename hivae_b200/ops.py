@@ -46,13 +46,46 @@ def launch_count():
     return int(_lib.load().hv_launch_count())
 
 
+# ------------------------------------------------------------------ per-launch timing (bench.py roofline leg)
+PROFILE = None  # set to a list to record (kernel, flops, bytes, start_event, end_event) per launch
+
+
+def _prof(name, flops=0.0, nbytes=0.0):
+    if PROFILE is None:
+        return None
+    e0 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    return (name, float(flops), float(nbytes), e0)
+
+
+def _prof_end(tok):
+    if tok is not None:
+        e1 = torch.cuda.Event(enable_timing=True)
+        e1.record()
+        PROFILE.append(tok + (e1,))
+
+
+def profile_summary(records):
+    """{kernel: {launches, ms, flops, bytes}} from a PROFILE list (call after a device synchronize)."""
+    out = {}
+    for name, fl, nb, e0, e1 in records:
+        d = out.setdefault(name, {"launches": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+        d["launches"] += 1
+        d["ms"] += e0.elapsed_time(e1)
+        d["flops"] += fl
+        d["bytes"] += nb
+    return out
+
+
 # ------------------------------------------------------------------ wavelet / frequency
 def dwt2_haar(x):
     """(B,C,H,W) -> LL, HL, LH, HH each (B,C,H/2,W/2), dtype preserved (wavelet.py:13-27)."""
     _chk_cuda(x)
     B, Cc, H, W = x.shape
     outs = [torch.empty(B, Cc, H // 2, W // 2, dtype=x.dtype, device=x.device) for _ in range(4)]
+    tok = _prof("dwt2_haar", 0, 2 * x.numel() * x.element_size())
     _lib.check(_lib.load().hv_dwt2_haar(_p(x), *[_p(o) for o in outs], B * Cc, H, W, _dt(x), _stream()))
+    _prof_end(tok)
     return tuple(outs)
 
 
@@ -61,7 +94,9 @@ def idwt2_haar(ll, hl, lh, hh):
     _chk_cuda(ll, hl, lh, hh)
     B, Cc, h, w = ll.shape
     out = torch.empty(B, Cc, 2 * h, 2 * w, dtype=torch.float32, device=ll.device)
+    tok = _prof("idwt2_haar", 0, 4 * ll.numel() * ll.element_size() + out.numel() * 4)
     _lib.check(_lib.load().hv_idwt2_haar(_p(ll), _p(hl), _p(lh), _p(hh), _p(out), B * Cc, h, w, _dt(ll), _stream()))
+    _prof_end(tok)
     return out
 
 
@@ -71,7 +106,9 @@ def freq_split3d(x, ct, ch, cw):
     T, H, W = x.shape[-3:]
     vols = x.numel() // (T * H * W) if x.numel() else 0
     lo, hi = torch.empty_like(x), torch.empty_like(x)
+    tok = _prof("freq_split3d", 0, 3 * x.numel() * 4)
     _lib.check(_lib.load().hv_freq_split3d(_p(x), _p(ct), _p(ch), _p(cw), _p(lo), _p(hi), vols, T, H, W, _stream()))
+    _prof_end(tok)
     return lo, hi
 
 
@@ -115,11 +152,13 @@ class Ada:
 def ln_modulate(rows, ln_w, ln_b, eps, out, ada=None, shift_mot=0, scale_mot=0, shift_img=0, scale_img=0):
     _chk_cuda(rows.res, ln_w, ln_b, out)
     t = ada.table if ada is not None else None
+    tok = _prof("ln_modulate", 0, rows.M * rows.D * (4 + out.element_size()))
     _lib.check(_lib.load().hv_ln_modulate(
         _p(rows.res), rows.frames, rows.frame_rows, rows.row_off, rows.L, rows.D, _p(ln_w), _p(ln_b), float(eps),
         _p(t), t.shape[1] if t is not None else 0, shift_mot, scale_mot, shift_img, scale_img,
         rows.img_start, rows.img_len, ada.cond_div if ada else 1, ada.cond_mul if ada else 1,
         _p(out), _dt(out), _stream()))
+    _prof_end(tok)
     return out
 
 
@@ -237,7 +276,10 @@ def epi_residual(rows, bias=None, ada=None, gate_mot=0, gate_img=0):
 
 def linear(A, W, epi):
     """epilogue(A[M,K] @ W[N,K]^T).  bf16 x bf16 -> tcgen05 GEMM; anything with fp32 W -> fp32 SIMT GEMM."""
-    _chk_cuda(A, W)
+    _lib.require_device()
+    for t in (A, W):  # row-strided 2-D views (column slices of a wider matrix) are fine: ld is passed explicitly
+        if not t.is_cuda or t.dim() != 2 or (t.shape[1] > 1 and t.stride(1) != 1):
+            raise RuntimeError("hivae_b200.linear needs 2-D CUDA tensors with unit column stride (no CPU fallback)")
     M, K = A.shape
     N = W.shape[0]
     assert W.shape[1] == K, (A.shape, W.shape)
@@ -245,9 +287,12 @@ def linear(A, W, epi):
     if W.dtype == torch.bfloat16:
         if A.dtype != torch.bfloat16:
             raise TypeError("bf16 weights need bf16 activations")
+        tok = _prof("gemm_tc", 2.0 * M * N * K, 2.0 * (M * K + N * K + M * N))
         _lib.check(lib.hv_linear_bf16(_p(A), A.stride(0), _p(W), W.stride(0), M, N, K, C.byref(epi), _stream()))
     else:
+        tok = _prof("gemm_simt", 2.0 * M * N * K, 4.0 * (M * K + N * K + M * N))
         _lib.check(lib.hv_linear_f32(_p(A), _dt(A), A.stride(0), _p(W), W.stride(0), M, N, K, C.byref(epi), _stream()))
+    _prof_end(tok)
 
 
 # ------------------------------------------------------------------ attention
@@ -260,7 +305,9 @@ def seq_map(sdiv, sa, sb, sc):
 def attention(q, k, v, out, seqs, heads, hd, Lq, Lkv, qmap, kvmap, scale, mask=None):
     """q/k/v/out are 2-D (rows, cols) views whose column 0 is head 0; row strides are taken from the views."""
     _lib.require_device()
+    tok = _prof("attention", 4.0 * seqs * heads * Lq * Lkv * hd, q.element_size() * heads * hd * seqs * (2.0 * Lq + 2.0 * Lkv))
     _lib.check(_lib.load().hv_attention(_p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0),
                                         _dt(q), seqs, heads, hd, Lq, Lkv, C.byref(qmap), C.byref(kvmap), float(scale),
                                         _p(mask), _stream()))
+    _prof_end(tok)
     return out

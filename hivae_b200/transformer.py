@@ -188,9 +188,11 @@ class MotionEncoderLearnTokenOnlyTemporalTransformer(_HvModule):
             t0 = P.tok.shape[0]
             rep = T // t0
             tok = engine.small_linear(ctx, P.tok, P.ew, P.eb, "cam_tok")  # (t0, D)
+            tt = torch.empty(1, T, D, dtype=torch.float32, device=ctx.device)  # tt[t] = tok[t // rep] + temporal[t]
+            for f in range(t0):
+                ops.rows_scatter(tok[f:f + 1], 0, 0, P.tpos[f * rep:(f + 1) * rep].contiguous(), Rows(tt, f * rep, rep))
             tab = torch.empty(1, T * S, D, dtype=torch.float32, device=ctx.device)
-            for t in range(T):
-                ops.rows_scatter(tok[t // rep:t // rep + 1], 0, 0, P.tpos[t:t + 1], Rows(tab, t * S, S))
+            ops.rows_scatter(tt.view(T, D), 1, 0, None, Rows(tab.view(T, S, D), 0, S))  # broadcast over s
             P.tabs[T] = tab
         return P.tabs[T]
 

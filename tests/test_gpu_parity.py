@@ -1,0 +1,445 @@
+"""GPU tier (-m gpu): the sm_100a kernels, called through the C ABI (ctypes -> libhivae_b200.so),
+against the CPU oracle (oracle/amd_oracle.py) and the committed golden fixtures generated from the
+unmodified reference (tests/golden/make_golden.py).
+
+Tolerances (BASELINE.json north_star): DWT coefficients 1e-6 (fp32), latents / reconstructions 1e-4
+relative in fp32 and 2e-2 in bf16, reconstruction PSNR within 0.05 dB.
+"""
+import math
+
+import pytest
+import torch
+
+from oracle import amd_oracle as O
+from hivae_b200 import configs, synth
+
+pytestmark = pytest.mark.gpu
+torch.set_grad_enabled(False)
+
+TOL_DWT = 1e-6
+TOL_F32 = 1e-4
+TOL_BF16 = 2e-2
+
+
+def rel(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return float((a - b).abs().max() / (b.abs().max() + 1e-12))
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "the gpu tier needs a CUDA device"
+    from hivae_b200 import _lib
+    _lib.require_device()
+    return torch.device("cuda:0")
+
+
+def _gen(seed):
+    return torch.Generator().manual_seed(seed)
+
+
+# =============================================================================== wavelet
+def test_dwt_idwt_golden(dev, golden):
+    import hivae_b200 as hv
+    g = golden("signal_ops")
+    outs = hv.dwt_init(g["dwt_x"].to(dev))
+    for name, o in zip(("LL", "HL", "LH", "HH"), outs):
+        assert rel(o, g["dwt_" + name]) <= TOL_DWT, name
+        assert torch.equal(o.cpu(), g["dwt_" + name]), name  # same fp32 operation order as wavelet.py:15-24
+    rec = hv.iwt_init(torch.cat(outs, 0))
+    assert rec.dtype == torch.float32
+    assert rel(rec, g["iwt_out"]) <= TOL_DWT
+    # module API
+    assert torch.equal(hv.DWT()(g["dwt_x"].to(dev))[0], outs[0])
+    assert torch.equal(hv.IWT()(torch.cat(outs, 0)), rec)
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 2, 2), (2, 3, 6, 10), (3, 2, 16, 24), (1, 3, 64, 34), (5, 1, 2, 258), (2, 2, 130, 8)])
+def test_dwt_ragged_shapes_vs_oracle(dev, shape):
+    import hivae_b200 as hv
+    x = torch.randn(*shape, generator=_gen(sum(shape)))
+    outs = hv.dwt_init(x.to(dev))
+    for o, r in zip(outs, O.haar_dwt2(x)):
+        assert rel(o, r) <= TOL_DWT
+    rec = hv.iwt_init(torch.cat(outs, 0))
+    assert rel(rec, O.haar_idwt2(torch.cat(O.haar_dwt2(x), 0))) <= TOL_DWT
+    assert rel(rec, x) <= 1e-6
+
+
+def test_dwt_edge_cases(dev):
+    import hivae_b200 as hv
+    e = hv.dwt_init(torch.empty(0, 3, 8, 8, device=dev))
+    assert all(t.shape == (0, 3, 4, 4) for t in e)
+    assert hv.iwt_init(torch.empty(0, 3, 4, 4, device=dev)).shape == (0, 3, 8, 8)
+    with pytest.raises(RuntimeError):
+        hv.dwt_init(torch.randn(1, 1, 5, 4, device=dev))  # odd H: the reference's strided slices would mis-broadcast
+    with pytest.raises(TypeError):
+        hv.dwt_init(torch.randn(1, 1, 4, 4, device=dev).half())
+    # bf16 in -> bf16 sub-bands (dtype-preserving, wavelet.py:13-27), IWT always fp32 (wavelet.py:40-41)
+    xb = torch.randn(2, 3, 32, 48, generator=_gen(3)).bfloat16()
+    outs = hv.dwt_init(xb.to(dev))
+    assert all(o.dtype == torch.bfloat16 for o in outs)
+    for o, r in zip(outs, O.haar_dwt2(xb)):  # the reference evaluates every add/sub in bf16: bit-exact
+        assert torch.equal(o.cpu(), r)
+    rec = hv.iwt_init(torch.cat(outs, 0))
+    assert rec.dtype == torch.float32
+    assert torch.equal(rec.cpu(), O.haar_idwt2(torch.cat([o.cpu() for o in outs], 0)))
+
+
+@pytest.mark.parametrize("T,H,levels", [(17, 256, 2), (33, 512, 3)])
+def test_dwt_pyramid_full_size_roundtrip(dev, T, H, levels):
+    """BASELINE config 4 sizes: size-independent properties (perfect reconstruction, energy
+    conservation of the orthonormal Haar transform) + a spot comparison against the oracle."""
+    import hivae_b200 as hv
+    x = torch.randn(T, 3, H, H, generator=_gen(0))
+    xd = x.to(dev)
+    bands, ll = hv.dwt_pyramid(xd, levels)
+    assert ll.shape == (T, 3, H >> levels, H >> levels)
+    rec = hv.iwt_pyramid(bands, ll)
+    assert rel(rec, x) <= 1e-6
+    e_in = float((xd.double() ** 2).sum())
+    e_out = float((ll.double() ** 2).sum()) + sum(float((b.double() ** 2).sum()) for lv in bands for b in lv)
+    assert abs(e_in - e_out) <= 1e-6 * e_in
+    ob, oll = O.haar_pyramid(x[:2], levels)
+    assert rel(ll[:2], oll) <= TOL_DWT
+    for lv, olv in zip(bands, ob):
+        for b, r in zip(lv, olv):
+            assert rel(b[:2], r) <= TOL_DWT
+
+
+# =============================================================================== frequency split
+def test_freq_split_golden(dev, golden):
+    import hivae_b200 as hv
+    g = golden("signal_ops")
+    x = g["freq_x"].to(dev)
+    for d in (5, 6):
+        lpf = hv.gaussian_low_pass_filter([32, 32, 32], d / 10, d / 10)
+        lo, hi = hv.freq_3d_filter(x, lpf)
+        assert rel(lo, g["freq_lo_%d" % d]) <= 1e-5 and rel(hi, g["freq_hi_%d" % d]) <= 1e-5
+        assert rel(lo + hi, g["freq_x"]) <= 1e-6
+    # ragged even sizes + anisotropic cut-offs through an UNTAGGED mask tensor (rank-1 factorisation path)
+    lpf2 = O.gaussian_lpf([8, 12, 20], 0.3, 0.7)
+    lo2, hi2 = hv.freq_3d_filter(g["freq2_x"].to(dev), lpf2)
+    assert rel(lo2, g["freq2_lo"]) <= 1e-5 and rel(hi2, g["freq2_hi"]) <= 1e-5
+
+
+def test_freq_split_properties_full_size(dev):
+    import hivae_b200 as hv
+    from hivae_b200.frequency_utils import freq_split_gauss
+    x = torch.randn(32, 4, 32, 32, 32, generator=_gen(5)).to(dev)
+    lo, hi = freq_split_gauss(x, 0.6, 0.6)
+    assert rel(lo + hi, x) <= 1e-6
+    # linearity and idempotence-like contraction: filtering twice == squaring the mask
+    lo2, _ = freq_split_gauss(2.0 * x, 0.6, 0.6)
+    assert rel(lo2, 2.0 * lo) <= 1e-6
+    olo, ohi = O.freq_split3d(x[:1].cpu(), O.gaussian_lpf([32, 32, 32], 0.6, 0.6))
+    assert rel(lo[:1], olo) <= 1e-5 and rel(hi[:1], ohi) <= 1e-5
+    z = torch.zeros(0, 4, 32, 32, 32, device=dev)
+    assert freq_split_gauss(z, 0.6, 0.6)[0].shape == z.shape
+    # zero cut-off -> zero mask -> low = 0, high = x (frequency_utils.py:58-59)
+    lo0, hi0 = hv.freq_3d_filter(x[:1], hv.gaussian_low_pass_filter([32, 32, 32], 0.0, 0.5))
+    assert float(lo0.abs().max()) == 0.0 and torch.equal(hi0, x[:1])
+
+
+# =============================================================================== GEMM + epilogues
+def _ref_linear(A, W, b):
+    y = A.double() @ W.double().t()
+    return (y + b.double()) if b is not None else y
+
+
+@pytest.mark.parametrize("M,N,K", [(1, 64, 64), (37, 128, 128), (128, 256, 64), (300, 384, 512), (4384, 3072, 1024),
+                                   (129, 1024, 4096), (257, 192, 72), (1000, 4096, 1024)])
+def test_linear_bf16_tcgen05_store(dev, M, N, K):
+    from hivae_b200 import ops
+    g = _gen(M + N + K)
+    A = (torch.randn(M, K, generator=g)).bfloat16().to(dev)
+    W = (torch.randn(N, K, generator=g) / math.sqrt(K)).bfloat16().to(dev)
+    b = torch.randn(N, generator=g).to(dev)
+    ref = _ref_linear(A.cpu().float(), W.cpu().float(), b.cpu())
+    out = torch.full((M, N), float("nan"), device=dev)
+    ops.linear(A, W, ops.epi_store(out, b))
+    assert rel(out, ref) <= 1e-5  # bf16 operands are exact in fp32; fp32 accumulation order only
+    outb = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    ops.linear(A, W, ops.epi_store(outb, b, gelu=True))
+    assert rel(outb, torch.nn.functional.gelu(ref.float(), approximate="tanh")) <= 8e-3
+
+
+def test_linear_bf16_strided_views(dev):
+    """A and out as column slices of wider matrices (the q|k|v views of engine.run_block)."""
+    from hivae_b200 import ops
+    g = _gen(9)
+    big = torch.randn(200, 3 * 128, generator=g).bfloat16().to(dev)
+    W = (torch.randn(128, 128, generator=g) / 11).bfloat16().to(dev)
+    outbig = torch.zeros(200, 256, device=dev)
+    ops.linear(big[:, 128:256], W, ops.epi_store(outbig[:, 128:], None))
+    ref = _ref_linear(big[:, 128:256].cpu().float(), W.cpu().float(), None)
+    assert rel(outbig[:, 128:], ref) <= 1e-5 and float(outbig[:, :128].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_linear_qknorm_epilogue(dev, dtype):
+    from hivae_b200 import ops
+    g = _gen(21)
+    M, D = 333, 128
+    A = torch.randn(M, D, generator=g)
+    W = torch.randn(3 * D, D, generator=g) / math.sqrt(D)
+    b = torch.randn(3 * D, generator=g) * 0.1
+    qw, qb, kw, kb = (torch.randn(64, generator=g) * 0.2 + 1, torch.randn(64, generator=g) * 0.1,
+                      torch.randn(64, generator=g) * 0.2 + 1, torch.randn(64, generator=g) * 0.1)
+    if dtype == torch.bfloat16:
+        A, W = A.bfloat16(), W.bfloat16()
+    y = _ref_linear(A.float(), W.float(), b).float()
+    q = torch.nn.functional.layer_norm(y[:, :D].view(M, 2, 64), (64,), qw, qb, 1e-6).view(M, D)
+    k = torch.nn.functional.layer_norm(y[:, D:2 * D].view(M, 2, 64), (64,), kw, kb, 1e-6).view(M, D)
+    ref = torch.cat([q, k, y[:, 2 * D:]], 1)
+    out = torch.empty(M, 3 * D, device=dev, dtype=dtype)
+    d = lambda t: t.to(dev)
+    ops.linear(d(A), d(W), ops.epi_qknorm(out, d(b), d(qw), d(qb), d(kw), d(kb), D, D))
+    assert rel(out, ref) <= (1e-5 if dtype == torch.float32 else 8e-3)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_linear_gated_residual_epilogue(dev, dtype):
+    """res[f, row_off+i, :] += gate[cond(f), seg(i)] * (A W^T + b) with image / motion gate columns."""
+    from hivae_b200 import ops
+    g = _gen(33)
+    frames, FR, D, K = 6, 50, 128, 256
+    row_off, L, img_start, img_len = 3, 40, 10, 25
+    A = torch.randn(frames * L, K, generator=g)
+    W = torch.randn(D, K, generator=g) / math.sqrt(K)
+    b = torch.randn(D, generator=g) * 0.1
+    res = torch.randn(frames, FR, D, generator=g)
+    table = torch.randn(3, 6 * D, generator=g)  # conditioning row = (f // 2) * 1
+    if dtype == torch.bfloat16:
+        A, W = A.bfloat16(), W.bfloat16()
+    y = _ref_linear(A.float(), W.float(), b).float().view(frames, L, D)
+    ref = res.clone()
+    for f in range(frames):
+        for i in range(L):
+            ai = row_off + i
+            col = 5 * D if img_start <= ai < img_start + img_len else 2 * D
+            ref[f, ai] += table[f // 2, col:col + D] * y[f, i]
+    resd = res.to(dev)
+    rows = ops.Rows(resd, row_off, L, img_start, img_len)
+    ops.linear(A.to(dev), W.to(dev), ops.epi_residual(rows, b.to(dev), ops.Ada(table.to(dev), 2, 1), 2 * D, 5 * D))
+    assert rel(resd, ref) <= 1e-5
+    # plain residual add (no gate)
+    resd2 = res.to(dev)
+    ops.linear(A.to(dev), W.to(dev), ops.epi_residual(ops.Rows(resd2, row_off, L), b.to(dev)))
+    ref2 = res.clone()
+    ref2[:, row_off:row_off + L] += y
+    assert rel(resd2, ref2) <= 1e-5
+
+
+@pytest.mark.parametrize("M,N,K", [(5, 16, 1024), (300, 512, 16), (64, 70, 33), (2, 6144, 512)])
+def test_linear_f32_simt(dev, M, N, K):
+    from hivae_b200 import ops
+    g = _gen(M * N + K)
+    A, W, b = torch.randn(M, K, generator=g), torch.randn(N, K, generator=g) / math.sqrt(K), torch.randn(N, generator=g)
+    out = torch.empty(M, N, device=dev)
+    ops.linear(A.to(dev), W.to(dev), ops.epi_store(out, b.to(dev)))
+    assert rel(out, _ref_linear(A, W, b)) <= 1e-5
+
+
+# =============================================================================== attention
+def _ref_attention(q, k, v, scale):
+    s = torch.einsum("bhqd,bhkd->bhqk", q.double(), k.double()) * scale
+    return torch.einsum("bhqk,bhkd->bhqd", torch.softmax(s, -1), v.double())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,H,Lq,Lkv", [(3, 2, 274, 274), (2, 8, 264, 264), (5, 1, 16, 16), (2, 4, 10, 37), (1, 16, 64, 128),
+                                        (2, 2, 100, 49)])
+def test_attention_dense(dev, dtype, B, H, Lq, Lkv):
+    from hivae_b200 import ops
+    g = _gen(B * H + Lq + Lkv)
+    D = H * 64
+    q, k, v = (torch.randn(B * Lq, D, generator=g), torch.randn(B * Lkv, D, generator=g), torch.randn(B * Lkv, D, generator=g))
+    q, k, v = q.to(dtype), k.to(dtype), v.to(dtype)
+    ref = _ref_attention(q.float().view(B, Lq, H, 64).transpose(1, 2), k.float().view(B, Lkv, H, 64).transpose(1, 2),
+                         v.float().view(B, Lkv, H, 64).transpose(1, 2), 0.125).transpose(1, 2).reshape(B * Lq, D)
+    out = torch.empty(B * Lq, D, device=dev, dtype=dtype)
+    ops.attention(q.to(dev), k.to(dev), v.to(dev), out, B, H, 64, Lq, Lkv, ops.seq_map(1, Lq, 0, 1), ops.seq_map(1, Lkv, 0, 1), 0.125)
+    assert rel(out, ref) <= (2e-5 if dtype == torch.float32 else 1e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_attention_strided_temporal(dev, dtype):
+    """'(n t) s d -> (n s) t d' regrouping expressed as a sequence map (transformer.py:2022-2028)."""
+    from hivae_b200 import engine, ops
+    n, T, S, H = 2, 16, 24, 2
+    D = H * 64
+    g = _gen(77)
+    qkv = torch.randn(n * T * S, 3 * D, generator=g).to(dtype)
+    x = qkv.float().view(n, T, S, 3, H, 64).permute(3, 0, 2, 4, 1, 5)  # (3, n, S, H, T, 64)
+    ref = _ref_attention(x[0].reshape(n * S, H, T, 64), x[1].reshape(n * S, H, T, 64), x[2].reshape(n * S, H, T, 64), 0.125)
+    ref = ref.view(n, S, H, T, 64).permute(0, 3, 1, 2, 4).reshape(n * T * S, D)
+    qd = qkv.to(dev)
+    out = torch.empty(n * T * S, D, device=dev, dtype=dtype)
+    geom = engine.strided_geom(n, S, T)
+    ops.attention(qd[:, :D], qd[:, D:2 * D], qd[:, 2 * D:], out, geom.seqs, H, 64, T, T, geom.qmap, geom.kvmap, 0.125)
+    assert rel(out, ref) <= (2e-5 if dtype == torch.float32 else 1e-2)
+
+
+def test_rope_attention_module(dev, golden):
+    """model/attention.py Attention: RoPE / no RoPE / masked with start_pos."""
+    import hivae_b200 as hv
+    from hivae_b200.attention import Attention
+    g = golden("signal_ops")
+    att = Attention(128, 40, 4)
+    att.load_state_dict(synth.synth_state_dict(((k, v.shape) for k, v in att.state_dict().items()), 3))
+    att = att.to(dev)
+    x = g["ropeattn_x"].to(dev)
+    assert rel(att(x), g["ropeattn_rope"]) <= TOL_F32
+    assert rel(att(x, inference=False), g["ropeattn_norope"]) <= TOL_F32
+    assert rel(att(x, mask=torch.tril(torch.ones(24, 24)), start_pos=3), g["ropeattn_rope_mask"]) <= TOL_F32
+    assert hv.__version__
+
+
+# =============================================================================== transformer blocks
+def _blocks(dev, dtype):
+    from hivae_b200 import modules as M
+    D, H = 128, 2
+    blocks = {"basic": M.BasicTransformerBlock(D, H, 64, attention_bias=True),
+              "cross": M.BasicCrossTransformerBlock(D, D, H, 64, attention_bias=True),
+              "joint": M.AMDTransformerBlock(D, H, 64, 512, attention_bias=True),
+              "dit": M.BasicDiTBlock(D, H, 64, 512, attention_bias=True)}
+    for blk in blocks.values():
+        blk.load_state_dict(synth.synth_state_dict(((k, v.shape) for k, v in blk.state_dict().items()), 11))
+        blk.to(dev)
+        blk.hv_compute_dtype = dtype
+    return blocks
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_blocks_golden(dev, golden, dtype, tol):
+    """the four block classes of model/modules.py against the unmodified reference's outputs"""
+    g = golden("blocks")
+    b = _blocks(dev, dtype)
+    xh, xe, te = g["x_hid"].to(dev), g["x_enc"].to(dev), g["temb"].to(dev)
+    assert rel(b["basic"](xe), g["basic_out"]) <= tol
+    assert rel(b["cross"](xh, xe), g["cross_out"]) <= tol
+    oh, oe = b["joint"](xh, te, xe)
+    assert rel(oh, g["joint_hid"]) <= tol and rel(oe, g["joint_enc"]) <= tol
+    assert rel(b["dit"](xe, te), g["dit_out"]) <= tol
+
+
+def test_patch_embed_module(dev):
+    from hivae_b200 import modules as M
+    pe = M.PatchEmbed(2, 8, 256)
+    sd = synth.synth_state_dict(((k, v.shape) for k, v in pe.state_dict().items()), 4)
+    pe.load_state_dict(sd)
+    x = torch.randn(3, 8, 32, 32, generator=_gen(8))
+    ref = O.patch_embed({"p.proj.weight": sd["proj.weight"], "p.proj.bias": sd["proj.bias"]}, "p", x, 2)
+    assert rel(pe.to(dev)(x.to(dev)), ref) <= 1e-5
+
+
+# =============================================================================== models
+def _small(dev, dtype=torch.float32):
+    import hivae_b200 as hv
+    cfg = configs.SMALL
+    m = hv.AMDModel_New(**cfg)
+    sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 0)
+    m.load_state_dict(sd)
+    m.to(dev).set_compute_dtype(dtype)
+    orc = O.AMDOracle(sd, cfg["enc_nhead"], cfg["diffusion_attn_num_heads"], 16, 2, cfg["motion_token_num"])
+    return m, orc
+
+
+def _fix_noise(m, z0):
+    orig = m.scheduler.get_train_tuple
+    m.scheduler.get_train_tuple = lambda z0_=None, z1=None, time_step=None: orig(z0=z0.to(z1.device), z1=z1, time_step=time_step)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_small_model_encode_decode_golden(dev, golden, dtype, tol):
+    """BASELINE.json config 1: small AMD encoder + rectified-flow decoder, one clip, encode -> decode."""
+    g = golden("small_model")
+    m, _ = _small(dev, dtype)
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(1, seed=1))
+    video, ref_img = video.to(dev), ref_img.to(dev)
+    cam, osrc, otgt = m.encode(video, ref_img)
+    assert cam.shape == (1, 16, 16, 8) and osrc.shape == (16, 8, 16) and otgt.shape == (16, 8, 16)
+    assert rel(cam, g["camera"]) <= tol and rel(osrc, g["obj_src"]) <= tol and rel(otgt, g["obj_tgt"]) <= tol
+    _fix_noise(m, g["z0"])
+    meta = m.decode(video, ref_img, cam, osrc, otgt, start_step=1000, sample_step=4, return_meta_info=True)
+    for i, p in enumerate(meta["pre_cache"]):
+        assert rel(p, g["pre_%d" % i]) <= tol, i
+    assert rel(meta["sample"], g["zt"]) <= tol
+    zj = meta["zj"].cpu()
+    assert abs(O.psnr(meta["sample"].cpu(), zj) - O.psnr(g["zt"], zj)) <= 0.05
+    # sample == encode + decode and returns (zi, zt, zj) each (n, t, c, h, w)
+    zi, zt, zj2 = m.sample(video, ref_img, sample_step=4)
+    assert zi.shape == zt.shape == zj2.shape == (1, 16, 4, 32, 32)
+    assert rel(zt, g["zt"]) <= tol
+    assert torch.equal(zi, ref_img) and torch.equal(zj2, video)
+
+
+def test_small_model_forward_golden(dev, golden):
+    g = golden("small_model")
+    m, _ = _small(dev)
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(1, seed=1))
+    _fix_noise(m, g["z0"])
+    m.prepare_timestep = lambda batch_size, device, time_step=None: torch.full((batch_size,), 437.0, device=device)
+    pre, vel, ld = m(video.to(dev), ref_img.to(dev))
+    assert rel(pre, g["fwd_pre"]) <= TOL_F32 and rel(vel, g["fwd_vel"]) <= 1e-6
+    assert set(ld) == {"loss", "diff_loss", "rec_loss"}
+    assert abs(float(ld["loss"]) - float(g["fwd_loss"][0])) <= 1e-4 * float(g["fwd_loss"][0])
+    assert abs(float(ld["rec_loss"]) - float(g["fwd_loss"][2])) <= 1e-4 * float(g["fwd_loss"][2])
+
+
+def test_small_model_batch_independence(dev):
+    """clips are independent along the batch dimension (the sharding axis): a batch of 3
+    equals three batches of 1."""
+    m, _ = _small(dev)
+    z = synth.synth_clip_latents(3, seed=5)
+    video, ref_img = (t.to(dev) for t in synth.split_clip(z))
+    z0 = torch.randn(48, 4, 32, 32, generator=_gen(2))
+    _fix_noise(m, z0)
+    _, zt, _ = m.sample(video, ref_img, sample_step=2)
+    for i in range(3):
+        _fix_noise_i = z0[16 * i:16 * (i + 1)]
+        m.scheduler = type(m.scheduler)(m.scheduler.num_step)
+        _fix_noise(m, _fix_noise_i)
+        _, zti, _ = m.sample(video[i:i + 1], ref_img[i:i + 1], sample_step=2)
+        assert rel(zti, zt[i:i + 1]) <= 1e-5
+
+
+def _default(dev, dtype):
+    import hivae_b200 as hv
+    m = hv.AMDModel_New(**configs.DEFAULT)
+    sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 0)
+    m.load_state_dict(sd)
+    del sd
+    return m.to(dev).set_compute_dtype(dtype)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_default_model_golden(dev, golden, dtype, tol):
+    """BASELINE.json config 2 architecture (695 M parameters): encode + one DiT evaluation at
+    step 600 against the unmodified reference (fp32 CPU)."""
+    g = golden("default_model")
+    gs = golden("small_model")
+    m = _default(dev, dtype)
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(1, seed=1))
+    video, ref_img = video.to(dev), ref_img.to(dev)
+    cam, osrc, otgt = m.encode(video, ref_img)
+    assert rel(cam, g["camera"]) <= tol and rel(osrc, g["obj_src"]) <= tol and rel(otgt, g["obj_tgt"]) <= tol
+    zi, zj = ref_img.flatten(0, 1), video.flatten(0, 1)
+    step = torch.ones(16) * 600
+    zt, _ = O.rf_train_tuple(zj.cpu(), step, gs["z0"])
+    # feed the GOLDEN motions so the DiT comparison does not inherit encoder error
+    pre = m.diffusion_transformer(torch.cat([zi, zt.to(dev)], 1), step.to(dev),
+                                  camera_motion_target_hidden_states=g["camera"].to(dev),
+                                  object_motion_source_hidden_states=g["obj_src"].to(dev),
+                                  object_motion_target_hidden_states=g["obj_tgt"].to(dev))
+    assert rel(pre, g["dit_pre_600"]) <= tol
+
+
+def test_kernels_ran_natively(dev):
+    """the product path launched our kernels (no silent eager fallback)"""
+    from hivae_b200 import ops
+    n0 = ops.launch_count()
+    import hivae_b200 as hv
+    hv.dwt_init(torch.randn(1, 1, 4, 4, device=dev))
+    assert ops.launch_count() == n0 + 1
