@@ -18,12 +18,119 @@
 
 namespace {
 
-constexpr int BM = 128, BK = 64, STAGES = 4, THREADS = 192;
+constexpr int BM = 128, BK = 64, STAGES = 4;
+constexpr int EPI_WARPS = 8, THREADS = 64 + 32 * EPI_WARPS;  // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
+constexpr int STAGING_BYTES = EPI_WARPS * 32 * 32 * 4;       // one 32x32 fp32 transpose tile per epilogue warp
 
 template <int BN> constexpr int stage_bytes() { return (BM + BN) * BK * 2; }
-template <int BN> constexpr int smem_bytes() { return STAGES * stage_bytes<BN>() + 1024; }
+template <int BN> constexpr int smem_bytes() { return STAGES * stage_bytes<BN>() + STAGING_BYTES + 1024; }
 
-template <int BN, bool EPI64>
+__device__ __forceinline__ float gelu_tanh_fast(float x) {
+    // tanh.approx (MUFU): 2^-11 relative error, far below the bf16 rounding of the stored value
+    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+    float u = k0 * fmaf(k1 * x * x, x, x), t;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+    return 0.5f * x * (1.0f + t);
+}
+
+// 32x32 fp32 tile, 16-byte chunk c of row r at chunk c ^ (r & 7): conflict-free for "thread = row" float4
+// writes and for "8 lanes = one row" float4 reads.
+__device__ __forceinline__ float4* stage_ptr(float* stage, int r, int c) {
+    return reinterpret_cast<float4*>(stage + r * 32 + ((c ^ (r & 7)) << 2));
+}
+
+// Epilogue of one 32-row x 32-column block owned by one warp.  `acc` holds the columns [col0, col0+32) of
+// row (row0 + lane), bias / activation / QK-norm already applied.  The block is transposed through shared
+// memory so that global accesses are row-contiguous (128 B per row for fp32, 64 B for bf16).
+template <int MODE>
+__device__ __forceinline__ void epi_block_out(const HvEpiDev& d, float* stage, int lane, long long row0, long long M,
+                                              int col0, int N, const float (&acc)[32], long long res_off, long long gate_off) {
+    const HvEpilogue& e = d.e;
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+        *stage_ptr(stage, lane, k) = make_float4(acc[4 * k], acc[4 * k + 1], acc[4 * k + 2], acc[4 * k + 3]);
+    __syncwarp();
+    const bool full = d.vec_ok && (col0 + 32 <= N);
+    if (MODE == HV_EPI_RESIDUAL) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int rr = 4 * i + (lane >> 3), cc = lane & 7;
+            const long long ro = __shfl_sync(0xffffffffu, res_off, rr);
+            const long long go = __shfl_sync(0xffffffffu, gate_off, rr);
+            const float4 v = *stage_ptr(stage, rr, cc);
+            const int col = col0 + 4 * cc;
+            if (row0 + rr < M) {
+                float* o = e.res + ro + col;
+                const float* g = e.gate ? e.gate + go + col : nullptr;
+                if (full) {
+                    float4 x = *reinterpret_cast<float4*>(o);
+                    const float4 gg = g ? __ldg(reinterpret_cast<const float4*>(g)) : make_float4(1.f, 1.f, 1.f, 1.f);
+                    x.x = fmaf(gg.x, v.x, x.x); x.y = fmaf(gg.y, v.y, x.y); x.z = fmaf(gg.z, v.z, x.z); x.w = fmaf(gg.w, v.w, x.w);
+                    *reinterpret_cast<float4*>(o) = x;
+                } else {
+                    const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) if (col + j < N) o[j] = fmaf(g ? g[j] : 1.f, vv[j], o[j]);
+                }
+            }
+        }
+    } else if (e.out_dtype == HV_F32) {
+        float* out = reinterpret_cast<float*>(e.out);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int rr = 4 * i + (lane >> 3), cc = lane & 7;
+            const float4 v = *stage_ptr(stage, rr, cc);
+            const int col = col0 + 4 * cc;
+            if (row0 + rr < M) {
+                float* o = out + (row0 + rr) * e.ldo + col;
+                if (full) {
+                    *reinterpret_cast<float4*>(o) = v;
+                } else {
+                    const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) if (col + j < N) o[j] = vv[j];
+                }
+            }
+        }
+    } else {
+        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(e.out);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int rr = 8 * i + (lane >> 2), cc = lane & 3;
+            const float4 v0 = *stage_ptr(stage, rr, 2 * cc), v1 = *stage_ptr(stage, rr, 2 * cc + 1);
+            const int col = col0 + 8 * cc;
+            if (row0 + rr < M) {
+                __nv_bfloat16* o = out + (row0 + rr) * e.ldo + col;
+                if (full) {
+                    *reinterpret_cast<uint4*>(o) = make_uint4(hv_pack_bf16(v0.x, v0.y), hv_pack_bf16(v0.z, v0.w),
+                                                              hv_pack_bf16(v1.x, v1.y), hv_pack_bf16(v1.z, v1.w));
+                } else {
+                    const float vv[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) if (col + j < N) o[j] = __float2bfloat16(vv[j]);
+                }
+            }
+        }
+    }
+    __syncwarp();  // the staging tile is reused by the next block
+}
+
+__device__ __forceinline__ void epi_add_bias(const HvEpiDev& d, int col0, int N, float (&acc)[32]) {
+    const float* bias = d.e.bias;
+    if (!bias) return;
+    if (d.vec_ok && col0 + 32 <= N) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(bias + col0 + j));
+            acc[j] += b.x; acc[j + 1] += b.y; acc[j + 2] += b.z; acc[j + 3] += b.w;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (col0 + j < N) acc[j] += __ldg(bias + col0 + j);
+    }
+}
+
+template <int BN, int MODE>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                long long M, int N, int K, const __grid_constant__ HvEpiDev epi) {
@@ -48,7 +155,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
 #pragma unroll
-        for (int a = 0; a < 2; ++a) { tc::mbar_init(&tmem_full_bar[a], 1); tc::mbar_init(&tmem_empty_bar[a], 4); }
+        for (int a = 0; a < 2; ++a) { tc::mbar_init(&tmem_full_bar[a], 1); tc::mbar_init(&tmem_empty_bar[a], EPI_WARPS); }
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(&tmem_slot, TMEM_COLS);
@@ -98,30 +205,90 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         }
     } else {
         // ===================================================== epilogue warps
-        const int q = warp & 3;  // TMEM lane quarter this warp may access
+        const int ew = warp - 2;
+        const int q = warp & 3;    // TMEM lane quarter this warp may access (hardware rule: warp id % 4)
+        const int half = ew >> 2;  // which half of the tile's columns
+        constexpr int HALF = BN / 2;
+        float* stage = reinterpret_cast<float*>(smem + STAGES * stage_bytes<BN>()) + ew * 1024;
+        const HvEpilogue& e = epi.e;
         int a = 0; uint32_t aph = 0;
-        constexpr int NC = EPI64 ? 64 : 32;
         for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
             const long long m0 = (t / n_blocks) * BM;
-            const int n0 = (int)(t % n_blocks) * BN;
+            const int n0 = (int)(t % n_blocks) * BN + half * HALF;
+            const long long row0 = m0 + q * 32, r = row0 + lane;
+            long long res_off = 0, gate_off = 0;
+            if (MODE == HV_EPI_RESIDUAL && r < M) {
+                HvRowMap map{e.L, (long long)e.frame_rows, e.row_off};
+                int frame, abs_i;
+                res_off = map.res_row(r, frame, abs_i) * N;
+                if (e.gate) {
+                    const bool img = (abs_i >= e.img_start) && (abs_i < e.img_start + e.img_len);
+                    gate_off = (long long)((frame / e.cond_div) * e.cond_mul) * e.gate_ld + (img ? e.gate_col_img : e.gate_col_mot);
+                }
+            }
+            if (MODE == HV_EPI_RESIDUAL) {
+                // pull this warp's 32 x HALF residual block into L2 while the tile's MMAs are still running
+#pragma unroll
+                for (int i = 0; i < HALF / 32; ++i) {
+                    const int li = lane + 32 * i, rr = li / (HALF / 32), seg = li % (HALF / 32);
+                    const long long ro = __shfl_sync(0xffffffffu, res_off, rr);
+                    if (row0 + rr < M && n0 + seg * 32 < N)
+                        asm volatile("prefetch.global.L2 [%0];" ::"l"(e.res + ro + n0 + seg * 32));
+                }
+            }
             tc::mbar_wait(&tmem_full_bar[a], aph);
             tc::fence_after_sync();
-            const long long r = m0 + q * 32 + lane;
-            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN);
+            const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(a * BN + half * HALF);
+            if (MODE == HV_EPI_QKNORM) {
 #pragma unroll 1
-            for (int c = 0; c < BN; c += NC) {
-                if (n0 + c >= N) break;  // warp-uniform
-                float acc[NC];
-                if constexpr (EPI64) {
+                for (int c = 0; c < HALF; c += 64) {
+                    const int col0 = n0 + c;
+                    if (col0 >= N) break;  // warp-uniform
                     float lo[32], hi[32];
                     tc::tmem_ld32(taddr + c, lo);
                     tc::tmem_ld32(taddr + c + 32, hi);
+                    epi_add_bias(epi, col0, N, lo);
+                    epi_add_bias(epi, col0 + 32, N, hi);
+                    const float *w = nullptr, *b = nullptr;
+                    if (col0 < e.q_cols) { w = e.qn_w; b = e.qn_b; }
+                    else if (col0 < e.q_cols + e.k_cols) { w = e.kn_w; b = e.kn_b; }
+                    if (w) {  // per-head LayerNorm over the 64 columns of this thread's row
+                        float s = 0.f;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) { acc[j] = lo[j]; acc[32 + j] = hi[j]; }
-                } else {
-                    tc::tmem_ld32(taddr + c, acc);
+                        for (int j = 0; j < 32; ++j) s += lo[j] + hi[j];
+                        const float mean = s * (1.f / 64.f);
+                        float v = 0.f;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) { float t0 = lo[j] - mean, t1 = hi[j] - mean; v = fmaf(t0, t0, v); v = fmaf(t1, t1, v); }
+                        const float rstd = rsqrtf(v * (1.f / 64.f) + e.qk_eps);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            lo[j] = (lo[j] - mean) * rstd * __ldg(w + j) + __ldg(b + j);
+                            hi[j] = (hi[j] - mean) * rstd * __ldg(w + 32 + j) + __ldg(b + 32 + j);
+                        }
+                    }
+                    epi_block_out<MODE>(epi, stage, lane, row0, M, col0, N, lo, 0, 0);
+                    epi_block_out<MODE>(epi, stage, lane, row0, M, col0 + 32, N, hi, 0, 0);
                 }
-                if (r < M) hv_epilogue_row<NC>(epi, r, n0 + c, N, acc);
+            } else {
+#pragma unroll 1
+                for (int c = 0; c < HALF; c += 32) {
+                    const int col0 = n0 + c;
+                    if (col0 >= N) break;  // warp-uniform
+                    float acc[32];
+                    tc::tmem_ld32(taddr + c, acc);
+                    epi_add_bias(epi, col0, N, acc);
+                    if (MODE == HV_EPI_GELU) {
+                        if (e.out_dtype == HV_BF16) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) acc[j] = gelu_tanh_fast(acc[j]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) acc[j] = hv_gelu_tanh(acc[j]);
+                        }
+                    }
+                    epi_block_out<MODE>(epi, stage, lane, row0, M, col0, N, acc, res_off, gate_off);
+                }
             }
             tc::fence_before_sync();
             __syncwarp();
@@ -167,8 +334,11 @@ struct MapKeyHash {
     }
 };
 
+}  // namespace
+
 // K-major bf16 matrix [rows, K] with row stride ld -> 2-D tensor map, box = 64 (K) x box_rows, 128 B swizzle
-int make_tmap(const void* ptr, long long rows, int K, long long ld, int box_rows, CUtensorMap* out) {
+// (shared with attn_tc.cu)
+int hv_make_tmap_bf16(const void* ptr, long long rows, int K, long long ld, int box_rows, CUtensorMap* out) {
     static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
     static std::mutex mu;
     MapKey key{ptr, rows, ld, K, box_rows};
@@ -193,9 +363,11 @@ int make_tmap(const void* ptr, long long rows, int K, long long ld, int box_rows
     return HV_OK;
 }
 
-template <int BN, bool EPI64>
+namespace {
+
+template <int BN, int MODE>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, int64_t M, int N, int K, const HvEpiDev& d, cudaStream_t st) {
-    auto kern = gemm_tc_kernel<BN, EPI64>;
+    auto kern = gemm_tc_kernel<BN, MODE>;
     static bool configured = false;
     if (!configured) {
         HV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN>()));
@@ -223,10 +395,17 @@ extern "C" int hv_linear_bf16(const void* A, int64_t lda, const void* W, int64_t
     if (M == 0) return HV_OK;
     const int BN = N > 128 ? 256 : 128;
     CUtensorMap ta, tb;
-    if ((rc = make_tmap(A, M, K, lda, BM, &ta)) != HV_OK) return rc;
-    if ((rc = make_tmap(W, N, K, ldw, BN, &tb)) != HV_OK) return rc;
+    if ((rc = hv_make_tmap_bf16(A, M, K, lda, BM, &ta)) != HV_OK) return rc;
+    if ((rc = hv_make_tmap_bf16(W, N, K, ldw, BN, &tb)) != HV_OK) return rc;
     cudaStream_t st = hv_stream(stream);
-    const bool e64 = d.e.mode == HV_EPI_QKNORM;
-    if (BN == 256) return e64 ? launch<256, true>(ta, tb, M, N, K, d, st) : launch<256, false>(ta, tb, M, N, K, d, st);
-    return e64 ? launch<128, true>(ta, tb, M, N, K, d, st) : launch<128, false>(ta, tb, M, N, K, d, st);
+    switch (d.e.mode * 2 + (BN == 256)) {
+        case HV_EPI_STORE * 2: return launch<128, HV_EPI_STORE>(ta, tb, M, N, K, d, st);
+        case HV_EPI_STORE * 2 + 1: return launch<256, HV_EPI_STORE>(ta, tb, M, N, K, d, st);
+        case HV_EPI_GELU * 2: return launch<128, HV_EPI_GELU>(ta, tb, M, N, K, d, st);
+        case HV_EPI_GELU * 2 + 1: return launch<256, HV_EPI_GELU>(ta, tb, M, N, K, d, st);
+        case HV_EPI_RESIDUAL * 2: return launch<128, HV_EPI_RESIDUAL>(ta, tb, M, N, K, d, st);
+        case HV_EPI_RESIDUAL * 2 + 1: return launch<256, HV_EPI_RESIDUAL>(ta, tb, M, N, K, d, st);
+        case HV_EPI_QKNORM * 2: return launch<128, HV_EPI_QKNORM>(ta, tb, M, N, K, d, st);
+        default: return launch<256, HV_EPI_QKNORM>(ta, tb, M, N, K, d, st);
+    }
 }

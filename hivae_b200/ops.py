@@ -305,7 +305,7 @@ def seq_map(sdiv, sa, sb, sc):
 def attention(q, k, v, out, seqs, heads, hd, Lq, Lkv, qmap, kvmap, scale, mask=None):
     """q/k/v/out are 2-D (rows, cols) views whose column 0 is head 0; row strides are taken from the views."""
     _lib.require_device()
-    tok = _prof("attention", 4.0 * seqs * heads * Lq * Lkv * hd, q.element_size() * heads * hd * seqs * (2.0 * Lq + 2.0 * Lkv))
+    tok = _prof("attention_L%d" % Lkv, 4.0 * seqs * heads * Lq * Lkv * hd, q.element_size() * heads * hd * seqs * (2.0 * Lq + 2.0 * Lkv))
     _lib.check(_lib.load().hv_attention(_p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0),
                                         _dt(q), seqs, heads, hd, Lq, Lkv, C.byref(qmap), C.byref(kvmap), float(scale),
                                         _p(mask), _stream()))
