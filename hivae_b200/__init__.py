@@ -15,5 +15,6 @@ from .modules import (BasicTransformerBlock, BasicCrossTransformerBlock, AMDTran
 from .transformer import (MotionEncoderLearnTokenTransformer, MotionEncoderLearnTokenOnlyTemporalTransformer,  # noqa: F401
                           AMDDiffusionTransformerModelImgSpatialTempMotion)
 from .model_AMD import AMDModel_New, AMD_N, AMD_models  # noqa: F401
+from . import sharding  # noqa: F401
 
 __version__ = "0.1.0"
