@@ -234,7 +234,12 @@ def run_ours(args):
     if rank == 0:
         clocks.start()
     n0 = ops.launch_count()
+    if args.ncu_range:  # `ncu --profile-from-start off`: the launch list covers exactly the timed steps
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
     ms = timed(step_resident, args.steps)
+    if args.ncu_range:
+        torch.cuda.profiler.stop()
     launches = ops.launch_count() - n0
     clk = clocks.stop() if rank == 0 else None
     step_e2e()
@@ -297,6 +302,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ncu-range", action="store_true", help="cudaProfilerStart/Stop around the timed steps")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

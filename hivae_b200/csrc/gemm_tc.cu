@@ -1,29 +1,40 @@
 // bf16 tensor-core GEMM for sm_100a:  out = epilogue(A[M,K] @ W[N,K]^T), fp32 accumulation.
 //
-//   * operands staged by TMA (cp.async.bulk.tensor, SWIZZLE_128B) into a 4-stage smem ring,
-//   * tcgen05.mma (cta_group::1, 128 x BN x 16) issued by one thread, accumulators in TMEM,
+//   * operands staged by TMA (cp.async.bulk.tensor, SWIZZLE_128B) into a shared-memory ring,
+//   * tcgen05.mma issued by one thread, accumulators in TMEM.  Large problems run as CTA PAIRS
+//     (cta_group::2, one 256 x 256 x 16 MMA over two SMs): each CTA stages 128 rows of A and only
+//     HALF of the B tile, which halves the shared-memory operand traffic per SM and leaves room for
+//     the epilogue's staging traffic; small problems use one CTA per 128 x BN tile (cta_group::1),
 //   * two TMEM accumulator stages so the epilogue of tile i overlaps the main loop of tile i+1,
-//   * persistent CTAs (one per SM) walking tiles N-fastest so the weight matrix stays in L2 and
-//     every activation tile is streamed from HBM once,
-//   * epilogue warps read TMEM with tcgen05.ld and apply the fused epilogue (bias / GELU-tanh /
-//     gated residual scatter / per-head QK LayerNorm) straight from registers.
+//   * persistent CTAs walking tiles N-fastest so the weight matrix stays in L2 and every activation
+//     tile is streamed from HBM once,
+//   * 8 epilogue warps read TMEM with tcgen05.ld, apply bias / GELU-tanh / per-head QK LayerNorm in the
+//     "thread = row" layout, and transpose 32x32 blocks through shared memory so that global accesses
+//     are row-contiguous.  The gated residual epilogue (res += gate * (acc + bias)) never reads the
+//     residual on the SM: the staged fp32 block is added into HBM/L2 by a TMA reduce
+//     (cp.reduce.async.bulk.tensor .add) through a 3-D map (column, row in frame, frame) whose
+//     out-of-range clipping handles the frame boundaries of the (frames, frame_rows, D) buffer.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner,
-// warps 2..5 = epilogue (TMEM lane quarter = warp_idx % 4).
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner,
+// warps 2..9 = epilogue (TMEM lane quarter = warp_idx % 4, column half = (warp_idx - 2) / 4).
 #include <cuda.h>
+#include <stdlib.h>
 #include <mutex>
+#include <string>
 #include <unordered_map>
 #include "epilogue.cuh"
 #include "tc_ptx.cuh"
 
 namespace {
 
-constexpr int BM = 128, BK = 64, STAGES = 4;
+constexpr int BM = 128, BK = 64;                              // rows of A / accumulator lanes per CTA, K per stage
 constexpr int EPI_WARPS = 8, THREADS = 64 + 32 * EPI_WARPS;  // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
 constexpr int STAGING_BYTES = EPI_WARPS * 32 * 32 * 4;       // one 32x32 fp32 transpose tile per epilogue warp
 
-template <int BN> constexpr int stage_bytes() { return (BM + BN) * BK * 2; }
-template <int BN> constexpr int smem_bytes() { return STAGES * stage_bytes<BN>() + STAGING_BYTES + 1024; }
+// CTAS = 1: one CTA per 128 x BN tile.  CTAS = 2: a CTA pair per 256 x BN tile, BN/2 rows of B per CTA.
+template <int CTAS> constexpr int num_stages() { return CTAS == 2 ? 6 : 4; }
+template <int BN, int CTAS> constexpr int stage_bytes() { return (BM + BN / CTAS) * BK * 2; }
+template <int BN, int CTAS> constexpr int smem_bytes() { return num_stages<CTAS>() * stage_bytes<BN, CTAS>() + STAGING_BYTES + 1024; }
 
 __device__ __forceinline__ float gelu_tanh_fast(float x) {
     // tanh.approx (MUFU): 2^-11 relative error, far below the bf16 rounding of the stored value
@@ -42,6 +53,42 @@ __device__ __forceinline__ float4* stage_ptr(float* stage, int r, int c) {
 // Epilogue of one 32-row x 32-column block owned by one warp.  `acc` holds the columns [col0, col0+32) of
 // row (row0 + lane), bias / activation / QK-norm already applied.  The block is transposed through shared
 // memory so that global accesses are row-contiguous (128 B per row for fp32, 64 B for bf16).
+// Gated residual block through a TMA reduce: res[rows, col0:col0+32) += gate * acc.  The 32-row block may
+// straddle frame boundaries of the residual buffer; one reduce per touched frame, rows outside [0, L)
+// are clipped by the tensor map (dims: N columns x L rows x frames).
+__device__ __forceinline__ void epi_block_reduce(const HvEpiDev& d, const CUtensorMap* tmap_r, float* stage, int lane,
+                                                 long long row0, long long r, long long M, int col0, int N,
+                                                 float (&acc)[32], long long gate_off) {
+    const HvEpilogue& e = d.e;
+    if (e.gate && r < M) {
+        const float* g = e.gate + gate_off + col0;
+        if (col0 + 32 <= N) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                const float4 gg = __ldg(reinterpret_cast<const float4*>(g + j));
+                acc[j] *= gg.x; acc[j + 1] *= gg.y; acc[j + 2] *= gg.z; acc[j + 3] *= gg.w;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) if (col0 + j < N) acc[j] *= __ldg(g + j);
+        }
+    }
+    if (lane == 0) tc::bulk_wait_read0();  // the previous reduce has finished reading the staging tile
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+        *stage_ptr(stage, lane, k) = make_float4(acc[4 * k], acc[4 * k + 1], acc[4 * k + 2], acc[4 * k + 3]);
+    tc::fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) {
+        const long long f0 = row0 / e.L;
+        int i = (int)(row0 - f0 * e.L);
+        const long long frames = M / e.L;
+        for (long long f = f0; i > -32 && f < frames; ++f, i -= e.L) tc::tma_reduce_add_3d(tmap_r, stage, col0, i, (int)f);
+        tc::bulk_commit();
+    }
+}
+
 template <int MODE>
 __device__ __forceinline__ void epi_block_out(const HvEpiDev& d, float* stage, int lane, long long row0, long long M,
                                               int col0, int N, const float (&acc)[32], long long res_off, long long gate_off) {
@@ -130,21 +177,28 @@ __device__ __forceinline__ void epi_add_bias(const HvEpiDev& d, int col0, int N,
     }
 }
 
-template <int BN, int MODE>
+template <int BN, int MODE, int CTAS>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-               long long M, int N, int K, const __grid_constant__ HvEpiDev epi) {
+               const __grid_constant__ CUtensorMap tmap_r, long long M, int N, int K, int use_reduce,
+               const __grid_constant__ HvEpiDev epi) {
+    constexpr int STAGES = num_stages<CTAS>();
+    constexpr int STAGE_BYTES = stage_bytes<BN, CTAS>();
+    constexpr int BNL = BN / CTAS;     // rows of the B tile staged by this CTA
+    constexpr int TILE_M = BM * CTAS;  // rows of the output tile of the CTA (pair)
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar[2], tmem_empty_bar[2];
     __shared__ uint32_t tmem_slot;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = CTAS == 2 ? tc::cluster_ctarank() : 0u;  // 0 = leader CTA of the pair
+    const long long unit = blockIdx.x / CTAS, units = gridDim.x / CTAS;
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    auto smem_a = [&](int s) { return smem + s * stage_bytes<BN>(); };
-    auto smem_b = [&](int s) { return smem + s * stage_bytes<BN>() + BM * BK * 2; };
+    auto smem_a = [&](int s) { return smem + s * STAGE_BYTES; };
+    auto smem_b = [&](int s) { return smem + s * STAGE_BYTES + BM * BK * 2; };
 
     const int n_blocks = (N + BN - 1) / BN;
-    const long long m_blocks = (M + BM - 1) / BM;
+    const long long m_blocks = (M + TILE_M - 1) / TILE_M;
     const long long num_tiles = m_blocks * n_blocks;
     const int num_kb = (K + BK - 1) / BK;
     constexpr uint32_t TMEM_COLS = 2 * BN;  // 256 or 512: power of two
@@ -152,40 +206,51 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (threadIdx.x == 0) {
         tc::prefetch_tmap(&tmap_a);
         tc::prefetch_tmap(&tmap_b);
+        if (MODE == HV_EPI_RESIDUAL && use_reduce) tc::prefetch_tmap(&tmap_r);
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
 #pragma unroll
-        for (int a = 0; a < 2; ++a) { tc::mbar_init(&tmem_full_bar[a], 1); tc::mbar_init(&tmem_empty_bar[a], EPI_WARPS); }
+        for (int a = 0; a < 2; ++a) { tc::mbar_init(&tmem_full_bar[a], 1); tc::mbar_init(&tmem_empty_bar[a], EPI_WARPS * CTAS); }
         tc::fence_barrier_init();
     }
-    if (warp == 1) tc::tmem_alloc(&tmem_slot, TMEM_COLS);
+    if (warp == 1) {
+        if (CTAS == 2) tc::tmem_alloc_pair(&tmem_slot, TMEM_COLS); else tc::tmem_alloc(&tmem_slot, TMEM_COLS);
+    }
     tc::fence_before_sync();
-    __syncthreads();
+    if (CTAS == 2) tc::cluster_sync(); else __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem_base = tmem_slot;
 
     if (warp == 0) {
-        // ===================================================== TMA producer
+        // ===================================================== TMA producer (one per CTA)
         if (lane == 0) {
             int s = 0; uint32_t ph = 0;
-            for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m0 = (int)(t / n_blocks) * BM, n0 = (int)(t % n_blocks) * BN;
+            for (long long t = unit; t < num_tiles; t += units) {
+                const int m0 = (int)(t / n_blocks) * TILE_M + (int)rank * BM, n0 = (int)(t % n_blocks) * BN + (int)rank * BNL;
                 for (int kb = 0; kb < num_kb; ++kb) {
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
-                    tc::mbar_expect_tx(&full_bar[s], stage_bytes<BN>());
-                    tc::tma_load_2d(smem_a(s), &tmap_a, &full_bar[s], kb * BK, m0);
-                    tc::tma_load_2d(smem_b(s), &tmap_b, &full_bar[s], kb * BK, n0);
+                    if (CTAS == 2) {
+                        // both CTAs' bytes complete on the leader's barrier, which the leader armed for the pair
+                        const uint32_t bar = tc::mapa(tc::smem_u32(&full_bar[s]), 0);
+                        if (rank == 0) tc::mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+                        tc::tma_load_2d_pair(smem_a(s), &tmap_a, bar, kb * BK, m0);
+                        tc::tma_load_2d_pair(smem_b(s), &tmap_b, bar, kb * BK, n0);
+                    } else {
+                        tc::mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                        tc::tma_load_2d(smem_a(s), &tmap_a, &full_bar[s], kb * BK, m0);
+                        tc::tma_load_2d(smem_b(s), &tmap_b, &full_bar[s], kb * BK, n0);
+                    }
                     if (++s == STAGES) { s = 0; ph ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================================================== MMA issuer
-        if (lane == 0) {
-            constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN);
+        // ===================================================== MMA issuer (leader CTA only)
+        if (lane == 0 && rank == 0) {
+            constexpr uint32_t idesc = tc::make_idesc_bf16(TILE_M, BN);
             int s = 0; uint32_t ph = 0; int a = 0; uint32_t aph = 0;
-            for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                tc::mbar_wait(&tmem_empty_bar[a], aph ^ 1);
+            for (long long t = unit; t < num_tiles; t += units) {
+                if (CTAS == 2) tc::mbar_wait_cluster(&tmem_empty_bar[a], aph ^ 1); else tc::mbar_wait(&tmem_empty_bar[a], aph ^ 1);
                 tc::fence_after_sync();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
                 for (int kb = 0; kb < num_kb; ++kb) {
@@ -194,12 +259,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(smem_a(s)));
                     const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(smem_b(s)));
 #pragma unroll
-                    for (int k = 0; k < BK / 16; ++k)  // +32 B per K=16 step inside the 128 B swizzle row
-                        tc::umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
-                    tc::umma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs retire
+                    for (int k = 0; k < BK / 16; ++k) {  // +32 B per K=16 step inside the 128 B swizzle row
+                        if (CTAS == 2) tc::umma_bf16_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+                        else tc::umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+                    }
+                    // frees the smem stage (in both CTAs) once these MMAs retire
+                    if (CTAS == 2) tc::umma_commit_pair(&empty_bar[s]); else tc::umma_commit(&empty_bar[s]);
                     if (++s == STAGES) { s = 0; ph ^= 1; }
                 }
-                tc::umma_commit(&tmem_full_bar[a]);  // accumulator complete
+                if (CTAS == 2) tc::umma_commit_pair(&tmem_full_bar[a]); else tc::umma_commit(&tmem_full_bar[a]);  // accumulator complete
                 if ((a ^= 1) == 0) aph ^= 1;
             }
         }
@@ -209,11 +277,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         const int q = warp & 3;    // TMEM lane quarter this warp may access (hardware rule: warp id % 4)
         const int half = ew >> 2;  // which half of the tile's columns
         constexpr int HALF = BN / 2;
-        float* stage = reinterpret_cast<float*>(smem + STAGES * stage_bytes<BN>()) + ew * 1024;
+        float* stage = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES) + ew * 1024;
         const HvEpilogue& e = epi.e;
+        const bool reduce = MODE == HV_EPI_RESIDUAL && use_reduce;
         int a = 0; uint32_t aph = 0;
-        for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-            const long long m0 = (t / n_blocks) * BM;
+        for (long long t = unit; t < num_tiles; t += units) {
+            const long long m0 = (t / n_blocks) * TILE_M + (long long)rank * BM;
             const int n0 = (int)(t % n_blocks) * BN + half * HALF;
             const long long row0 = m0 + q * 32, r = row0 + lane;
             long long res_off = 0, gate_off = 0;
@@ -226,7 +295,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     gate_off = (long long)((frame / e.cond_div) * e.cond_mul) * e.gate_ld + (img ? e.gate_col_img : e.gate_col_mot);
                 }
             }
-            if (MODE == HV_EPI_RESIDUAL) {
+            if (MODE == HV_EPI_RESIDUAL && !reduce) {
                 // pull this warp's 32 x HALF residual block into L2 while the tile's MMAs are still running
 #pragma unroll
                 for (int i = 0; i < HALF / 32; ++i) {
@@ -287,20 +356,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             for (int j = 0; j < 32; ++j) acc[j] = hv_gelu_tanh(acc[j]);
                         }
                     }
-                    epi_block_out<MODE>(epi, stage, lane, row0, M, col0, N, acc, res_off, gate_off);
+                    if (reduce) epi_block_reduce(epi, &tmap_r, stage, lane, row0, r, M, col0, N, acc, gate_off);
+                    else epi_block_out<MODE>(epi, stage, lane, row0, M, col0, N, acc, res_off, gate_off);
                 }
             }
             tc::fence_before_sync();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(&tmem_empty_bar[a]);
+            if (lane == 0) {
+                if (CTAS == 2) tc::mbar_arrive_cluster(tc::mapa(tc::smem_u32(&tmem_empty_bar[a]), 0));
+                else tc::mbar_arrive(&tmem_empty_bar[a]);
+            }
             if ((a ^= 1) == 0) aph ^= 1;
         }
+        if (reduce && lane == 0) tc::bulk_wait0();  // every reduce of this warp has landed before the CTA retires
     }
     tc::fence_before_sync();
-    __syncthreads();
+    if (CTAS == 2) tc::cluster_sync(); else __syncthreads();
     if (warp == 1) {
         tc::fence_after_sync();
-        tc::tmem_dealloc(tmem_base, TMEM_COLS);
+        if (CTAS == 2) tc::tmem_dealloc_pair(tmem_base, TMEM_COLS); else tc::tmem_dealloc(tmem_base, TMEM_COLS);
     }
 }
 
@@ -363,22 +437,99 @@ int hv_make_tmap_bf16(const void* ptr, long long rows, int K, long long ld, int 
     return HV_OK;
 }
 
+// fp32 residual rows [row_off, row_off+L) of every frame of a (frames, frame_rows, N) buffer as a 3-D map
+// (N columns, L rows, frames); box = 32 columns x 32 rows x 1 frame, 128 B swizzle (= the staging layout)
+static int make_tmap_residual(float* res, int N, int L, long long frames, long long frame_rows, int row_off, CUtensorMap* out) {
+    struct Key { const void* p; int N, L, off; long long frames, fr; };
+    static std::unordered_map<std::string, CUtensorMap> cache;
+    static std::mutex mu;
+    Key key{res, N, L, row_off, frames, frame_rows};
+    std::string ks(reinterpret_cast<const char*>(&key), sizeof(key));
+    {
+        std::lock_guard<std::mutex> g(mu);
+        auto it = cache.find(ks);
+        if (it != cache.end()) { *out = it->second; return HV_OK; }
+    }
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) { hv_set_error("cuTensorMapEncodeTiled entry point not available (driver too old?)"); return HV_ECUDA; }
+    cuuint64_t gdim[3] = {(cuuint64_t)N, (cuuint64_t)L, (cuuint64_t)frames};
+    cuuint64_t gstride[2] = {(cuuint64_t)N * 4, (cuuint64_t)frame_rows * N * 4};
+    cuuint32_t box[3] = {32, 32, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult rc = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, res + (long long)row_off * N, gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (rc != CUDA_SUCCESS) { hv_set_error("cuTensorMapEncodeTiled (residual) failed with CUresult %d", (int)rc); return HV_ECUDA; }
+    std::lock_guard<std::mutex> g(mu);
+    if (cache.size() > 8192) cache.clear();
+    cache.emplace(ks, *out);
+    return HV_OK;
+}
+
 namespace {
 
+// CTA pairs that can be co-resident (one CTA per SM, clusters of 2 inside a TPC)
 template <int BN, int MODE>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, int64_t M, int N, int K, const HvEpiDev& d, cudaStream_t st) {
-    auto kern = gemm_tc_kernel<BN, MODE>;
+int max_pairs() {
+    static int pairs = -1;
+    if (pairs < 0) {
+        cudaLaunchConfig_t cfg = {};
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.gridDim = dim3(2 * (hv_num_sms() / 2)); cfg.blockDim = dim3(THREADS);
+        cfg.dynamicSmemBytes = smem_bytes<BN, 2>(); cfg.attrs = at; cfg.numAttrs = 1;
+        int n = 0;
+        if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, MODE, 2>, &cfg) != cudaSuccess || n <= 0) {
+            cudaGetLastError();
+            n = hv_num_sms() / 2;
+        }
+        pairs = n < hv_num_sms() / 2 ? n : hv_num_sms() / 2;
+    }
+    return pairs;
+}
+
+template <int BN, int MODE, int CTAS>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, int use_reduce, int64_t M, int N, int K,
+           const HvEpiDev& d, cudaStream_t st) {
+    auto kern = gemm_tc_kernel<BN, MODE, CTAS>;
     static bool configured = false;
     if (!configured) {
-        HV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN>()));
+        HV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, CTAS>()));
         configured = true;
     }
-    const long long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
-    const int sms = hv_num_sms();
-    const int grid = (int)(tiles < sms ? tiles : sms);
-    kern<<<grid, THREADS, smem_bytes<BN>(), st>>>(ta, tb, (long long)M, N, K, d);
+    const long long tiles = ((M + BM * CTAS - 1) / (BM * CTAS)) * ((N + BN - 1) / BN);
+    if constexpr (CTAS == 1) {
+        const int sms = hv_num_sms();
+        const int grid = (int)(tiles < sms ? tiles : sms);
+        kern<<<grid, THREADS, smem_bytes<BN, CTAS>(), st>>>(ta, tb, tr, (long long)M, N, K, use_reduce, d);
+    } else {
+        const int pairs = max_pairs<BN, MODE>();
+        const int units = (int)(tiles < pairs ? tiles : pairs);
+        cudaLaunchConfig_t cfg = {};
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.gridDim = dim3(2 * units); cfg.blockDim = dim3(THREADS);
+        cfg.dynamicSmemBytes = smem_bytes<BN, CTAS>(); cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
+        HV_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tr, (long long)M, N, K, use_reduce, d));
+    }
     HV_LAUNCH_CHECK();
     return HV_OK;
+}
+
+template <int MODE>
+int launch_mode(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, int use_reduce, int64_t M, int N, int K,
+                const HvEpiDev& d, cudaStream_t st, int BN, int ctas) {
+    if (ctas == 2) return launch<256, MODE, 2>(ta, tb, tr, use_reduce, M, N, K, d, st);
+    if (BN == 256) return launch<256, MODE, 1>(ta, tb, tr, use_reduce, M, N, K, d, st);
+    return launch<128, MODE, 1>(ta, tb, tr, use_reduce, M, N, K, d, st);
+}
+
+// HV_GEMM_CTAS=1 forces the single-CTA kernel, HV_GEMM_REDUCE=0 the read-modify-write residual epilogue (A/B testing)
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v && *v ? atoi(v) : dflt;
 }
 
 }  // namespace
@@ -393,19 +544,25 @@ extern "C" int hv_linear_bf16(const void* A, int64_t lda, const void* W, int64_t
     int rc = hv_epilogue_prepare(epi, M, N, d, "hv_linear_bf16");
     if (rc) return rc;
     if (M == 0) return HV_OK;
+    static const int want_ctas = env_int("HV_GEMM_CTAS", 2), want_reduce = env_int("HV_GEMM_REDUCE", 1);
     const int BN = N > 128 ? 256 : 128;
-    CUtensorMap ta, tb;
+    // a CTA pair pays off once there are enough 256 x 256 tiles to occupy the pairs
+    const int ctas = (want_ctas == 2 && N > 128 && M > 256) ? 2 : 1;
+    CUtensorMap ta, tb, tr;
     if ((rc = hv_make_tmap_bf16(A, M, K, lda, BM, &ta)) != HV_OK) return rc;
-    if ((rc = hv_make_tmap_bf16(W, N, K, ldw, BN, &tb)) != HV_OK) return rc;
+    if ((rc = hv_make_tmap_bf16(W, N, K, ldw, BN / ctas, &tb)) != HV_OK) return rc;
+    int use_reduce = 0;
+    if (d.e.mode == HV_EPI_RESIDUAL && want_reduce && d.vec_ok) {
+        if ((rc = make_tmap_residual(d.e.res, N, d.e.L, M / d.e.L, d.e.frame_rows, d.e.row_off, &tr)) != HV_OK) return rc;
+        use_reduce = 1;
+    } else {
+        tr = ta;  // unused
+    }
     cudaStream_t st = hv_stream(stream);
-    switch (d.e.mode * 2 + (BN == 256)) {
-        case HV_EPI_STORE * 2: return launch<128, HV_EPI_STORE>(ta, tb, M, N, K, d, st);
-        case HV_EPI_STORE * 2 + 1: return launch<256, HV_EPI_STORE>(ta, tb, M, N, K, d, st);
-        case HV_EPI_GELU * 2: return launch<128, HV_EPI_GELU>(ta, tb, M, N, K, d, st);
-        case HV_EPI_GELU * 2 + 1: return launch<256, HV_EPI_GELU>(ta, tb, M, N, K, d, st);
-        case HV_EPI_RESIDUAL * 2: return launch<128, HV_EPI_RESIDUAL>(ta, tb, M, N, K, d, st);
-        case HV_EPI_RESIDUAL * 2 + 1: return launch<256, HV_EPI_RESIDUAL>(ta, tb, M, N, K, d, st);
-        case HV_EPI_QKNORM * 2: return launch<128, HV_EPI_QKNORM>(ta, tb, M, N, K, d, st);
-        default: return launch<256, HV_EPI_QKNORM>(ta, tb, M, N, K, d, st);
+    switch (d.e.mode) {
+        case HV_EPI_STORE: return launch_mode<HV_EPI_STORE>(ta, tb, tr, use_reduce, M, N, K, d, st, BN, ctas);
+        case HV_EPI_GELU: return launch_mode<HV_EPI_GELU>(ta, tb, tr, use_reduce, M, N, K, d, st, BN, ctas);
+        case HV_EPI_RESIDUAL: return launch_mode<HV_EPI_RESIDUAL>(ta, tb, tr, use_reduce, M, N, K, d, st, BN, ctas);
+        default: return launch_mode<HV_EPI_QKNORM>(ta, tb, tr, use_reduce, M, N, K, d, st, BN, ctas);
     }
 }

@@ -1,5 +1,6 @@
 // Haar DWT / IDWT (model/wavelet.py) and the 3-D Gaussian frequency split
 // (model/frequency_utils.py) — HBM-bound, 128-bit vectorised kernels.
+#include <type_traits>
 #include "hv_common.cuh"
 
 // ---------------------------------------------------------------------------------------------
@@ -110,11 +111,28 @@ __device__ __forceinline__ void haar_inv(float a, float b, float c, float d, flo
     o11 = hv_rnd<T>(hv_rnd<T>(hv_rnd<T>(x1 + x2) + x3) + x4);  // h[1::2,1::2]
 }
 
-template <typename T>
-__global__ void __launch_bounds__(256) idwt2_haar_vec_kernel(const T* __restrict__ ll, const T* __restrict__ hl,
-                                                             const T* __restrict__ lh, const T* __restrict__ hh,
+// VEC consecutive elements of type T -> floats (16-byte load for 4 x fp32 / 8 x bf16, 8-byte load for 4 x bf16)
+template <typename T, int VEC>
+__device__ __forceinline__ void load_vec(const T* p, float (&v)[VEC]) {
+    if constexpr (sizeof(T) * VEC == 16) {
+        load16<T>(p, v);
+    } else {
+        static_assert(sizeof(T) == 2 && VEC == 4, "load_vec: unsupported combination");
+        uint2 raw = *reinterpret_cast<const uint2*>(p);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+        float2 f0 = __bfloat1622float2(h[0]), f1 = __bfloat1622float2(h[1]);
+        v[0] = f0.x; v[1] = f0.y; v[2] = f1.x; v[3] = f1.y;
+    }
+}
+
+// TL = dtype of LL, TB = dtype of the three detail bands.  The reference concatenates the four bands
+// (torch.cat promotes a mixed fp32/bf16 list to fp32), so the arithmetic type R is bf16 only when both are.
+template <typename TL, typename TB>
+__global__ void __launch_bounds__(256) idwt2_haar_vec_kernel(const TL* __restrict__ ll, const TB* __restrict__ hl,
+                                                             const TB* __restrict__ lh, const TB* __restrict__ hh,
                                                              float* __restrict__ out, long long planes, int h, int w) {
-    constexpr int VEC = Vec16<T>::N;
+    using R = typename std::conditional<sizeof(TL) == 2 && sizeof(TB) == 2, __nv_bfloat16, float>::type;
+    constexpr int VEC = 16 / (sizeof(TL) > sizeof(TB) ? sizeof(TL) : sizeof(TB));
     const int wv = w / VEC;
     const long long total = planes * h * wv;
     for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
@@ -125,10 +143,10 @@ __global__ void __launch_bounds__(256) idwt2_haar_vec_kernel(const T* __restrict
         long long pl = t / h;
         long long o = (pl * h + i) * (long long)w + (long long)cv * VEC;
         float a[VEC], b[VEC], c[VEC], d[VEC];
-        load16<T>(ll + o, a); load16<T>(hl + o, b); load16<T>(lh + o, c); load16<T>(hh + o, d);
+        load_vec<TL, VEC>(ll + o, a); load_vec<TB, VEC>(hl + o, b); load_vec<TB, VEC>(lh + o, c); load_vec<TB, VEC>(hh + o, d);
         float r0[2 * VEC], r1[2 * VEC];
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) haar_inv<T>(a[j], b[j], c[j], d[j], r0[2 * j], r1[2 * j], r0[2 * j + 1], r1[2 * j + 1]);
+        for (int j = 0; j < VEC; ++j) haar_inv<R>(a[j], b[j], c[j], d[j], r0[2 * j], r1[2 * j], r0[2 * j + 1], r1[2 * j + 1]);
         float* p0 = out + (pl * 2 * h + 2 * i) * (long long)(2 * w) + (long long)cv * 2 * VEC;
         float* p1 = p0 + 2 * w;
 #pragma unroll
@@ -139,10 +157,11 @@ __global__ void __launch_bounds__(256) idwt2_haar_vec_kernel(const T* __restrict
     }
 }
 
-template <typename T>
-__global__ void __launch_bounds__(256) idwt2_haar_scalar_kernel(const T* __restrict__ ll, const T* __restrict__ hl,
-                                                                const T* __restrict__ lh, const T* __restrict__ hh,
+template <typename TL, typename TB>
+__global__ void __launch_bounds__(256) idwt2_haar_scalar_kernel(const TL* __restrict__ ll, const TB* __restrict__ hl,
+                                                                const TB* __restrict__ lh, const TB* __restrict__ hh,
                                                                 float* __restrict__ out, long long planes, int h, int w) {
+    using R = typename std::conditional<sizeof(TL) == 2 && sizeof(TB) == 2, __nv_bfloat16, float>::type;
     const long long total = planes * h * w;
     for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
          idx += (long long)gridDim.x * blockDim.x) {
@@ -151,7 +170,7 @@ __global__ void __launch_bounds__(256) idwt2_haar_scalar_kernel(const T* __restr
         int i = (int)(t % h);
         long long pl = t / h;
         float o00, o10, o01, o11;
-        haar_inv<T>(hv_ld(ll + idx), hv_ld(hl + idx), hv_ld(lh + idx), hv_ld(hh + idx), o00, o10, o01, o11);
+        haar_inv<R>(hv_ld(ll + idx), hv_ld(hl + idx), hv_ld(lh + idx), hv_ld(hh + idx), o00, o10, o01, o11);
         float* p0 = out + (pl * 2 * h + 2 * i) * (long long)(2 * w) + 2 * j;
         p0[0] = o00; p0[1] = o01; p0[2 * w] = o10; p0[2 * w + 1] = o11;
     }
@@ -190,30 +209,35 @@ extern "C" int hv_dwt2_haar(const void* x, void* ll, void* hl, void* lh, void* h
     HV_REQUIRE(false, "hv_dwt2_haar: bad dtype %d", dtype);
 }
 
-template <typename T>
+template <typename TL, typename TB>
 static int idwt_launch(const void* ll, const void* hl, const void* lh, const void* hh, float* out,
                        int64_t planes, int h, int w, cudaStream_t st) {
-    constexpr int VEC = Vec16<T>::N;
+    constexpr int VEC = 16 / (sizeof(TL) > sizeof(TB) ? sizeof(TL) : sizeof(TB));
     const bool vec_ok = (w % VEC == 0) && ((reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(ll) |
                         reinterpret_cast<uintptr_t>(hl) | reinterpret_cast<uintptr_t>(lh) | reinterpret_cast<uintptr_t>(hh)) % 16 == 0);
     if (vec_ok) {
         long long total = planes * h * (w / VEC);
-        idwt2_haar_vec_kernel<T><<<grid_for(total, 256), 256, 0, st>>>((const T*)ll, (const T*)hl, (const T*)lh, (const T*)hh, out, planes, h, w);
+        idwt2_haar_vec_kernel<TL, TB><<<grid_for(total, 256), 256, 0, st>>>((const TL*)ll, (const TB*)hl, (const TB*)lh, (const TB*)hh, out, planes, h, w);
     } else {
         long long total = planes * h * w;
-        idwt2_haar_scalar_kernel<T><<<grid_for(total, 256), 256, 0, st>>>((const T*)ll, (const T*)hl, (const T*)lh, (const T*)hh, out, planes, h, w);
+        idwt2_haar_scalar_kernel<TL, TB><<<grid_for(total, 256), 256, 0, st>>>((const TL*)ll, (const TB*)hl, (const TB*)lh, (const TB*)hh, out, planes, h, w);
     }
     HV_LAUNCH_CHECK();
     return HV_OK;
 }
 
+// dtype_in = dtype of all four bands, or (dtype_ll | dtype_bands << 8) for the mixed case that a bf16 pyramid
+// produces from its second inverse level on (LL is the fp32 output of the previous level, wavelet.py:40-41).
 extern "C" int hv_idwt2_haar(const void* ll, const void* hl, const void* lh, const void* hh, float* out,
                              int64_t planes, int h, int w, int dtype_in, void* stream) {
     HV_REQUIRE(planes >= 0 && h >= 0 && w >= 0, "hv_idwt2_haar: negative size");
     if (planes == 0 || h == 0 || w == 0) return HV_OK;
-    if (dtype_in == HV_F32) return idwt_launch<float>(ll, hl, lh, hh, out, planes, h, w, hv_stream(stream));
-    if (dtype_in == HV_BF16) return idwt_launch<__nv_bfloat16>(ll, hl, lh, hh, out, planes, h, w, hv_stream(stream));
-    HV_REQUIRE(false, "hv_idwt2_haar: bad dtype %d", dtype_in);
+    const int dl = dtype_in & 0xff, db = (dtype_in >> 8) ? ((dtype_in >> 8) & 0xff) - 1 : dl;
+    if (dl == HV_F32 && db == HV_F32) return idwt_launch<float, float>(ll, hl, lh, hh, out, planes, h, w, hv_stream(stream));
+    if (dl == HV_BF16 && db == HV_BF16) return idwt_launch<__nv_bfloat16, __nv_bfloat16>(ll, hl, lh, hh, out, planes, h, w, hv_stream(stream));
+    if (dl == HV_F32 && db == HV_BF16) return idwt_launch<float, __nv_bfloat16>(ll, hl, lh, hh, out, planes, h, w, hv_stream(stream));
+    if (dl == HV_BF16 && db == HV_F32) return idwt_launch<__nv_bfloat16, float>(ll, hl, lh, hh, out, planes, h, w, hv_stream(stream));
+    HV_REQUIRE(false, "hv_idwt2_haar: bad dtype code %d", dtype_in);
 }
 
 // ---------------------------------------------------------------------------------------------

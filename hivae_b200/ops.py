@@ -92,10 +92,13 @@ def dwt2_haar(x):
 def idwt2_haar(ll, hl, lh, hh):
     """four (B,C,h,w) sub-bands -> (B,C,2h,2w) fp32 (wavelet.py:31-48)."""
     _chk_cuda(ll, hl, lh, hh)
+    if not (hl.dtype == lh.dtype == hh.dtype) or not (ll.shape == hl.shape == lh.shape == hh.shape):
+        raise ValueError("idwt2_haar: the detail bands must share one dtype and all four bands one shape")
     B, Cc, h, w = ll.shape
     out = torch.empty(B, Cc, 2 * h, 2 * w, dtype=torch.float32, device=ll.device)
-    tok = _prof("idwt2_haar", 0, 4 * ll.numel() * ll.element_size() + out.numel() * 4)
-    _lib.check(_lib.load().hv_idwt2_haar(_p(ll), _p(hl), _p(lh), _p(hh), _p(out), B * Cc, h, w, _dt(ll), _stream()))
+    code = _dt(ll) if ll.dtype == hl.dtype else (_dt(ll) | ((_dt(hl) + 1) << 8))  # mixed: torch.cat promotion
+    tok = _prof("idwt2_haar", 0, ll.numel() * (ll.element_size() + 3 * hl.element_size()) + out.numel() * 4)
+    _lib.check(_lib.load().hv_idwt2_haar(_p(ll), _p(hl), _p(lh), _p(hh), _p(out), B * Cc, h, w, code, _stream()))
     _prof_end(tok)
     return out
 

@@ -46,6 +46,8 @@ def dwt_pyramid(x, levels):
 
 
 def iwt_pyramid(bands, ll):
+    """Multi-level synthesis.  Every level returns fp32 (wavelet.py:40-41), so from the second level on a
+    bf16 pyramid mixes an fp32 LL with bf16 detail bands — promoted to fp32 like the reference's torch.cat."""
     for hl, lh, hh in reversed(bands):
         ll = ops.idwt2_haar(ll.contiguous(), hl, lh, hh)
     return ll

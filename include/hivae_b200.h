@@ -56,7 +56,9 @@ int64_t hv_launch_count(void);
 int hv_dwt2_haar(const void* x, void* ll, void* hl, void* lh, void* hh,
                  int64_t planes, int H, int W, int dtype, void* stream);
 /* model/wavelet.py:31-48 (iwt_init): inverse; the four sub-bands are the four
- * dim-0 quarters of the reference's input.  Output is ALWAYS fp32 (wavelet.py:40-41). */
+ * dim-0 quarters of the reference's input.  Output is ALWAYS fp32 (wavelet.py:40-41).
+ * dtype_in = the dtype of all four bands, or dtype_ll | (dtype_bands + 1) << 8 when LL differs from the
+ * detail bands (second level of a bf16 pyramid: torch.cat promotes the mixed list to fp32). */
 int hv_idwt2_haar(const void* ll, const void* hl, const void* lh, const void* hh, float* out,
                   int64_t planes, int h, int w, int dtype_in, void* stream);
 

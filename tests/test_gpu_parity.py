@@ -107,6 +107,20 @@ def test_dwt_pyramid_full_size_roundtrip(dev, T, H, levels):
             assert rel(b[:2], r) <= TOL_DWT
 
 
+@pytest.mark.parametrize("shape,levels", [((3, 2, 64, 40), 2), ((33, 3, 512, 512), 3), ((2, 1, 24, 8), 3)])
+def test_bf16_pyramid_inverse_mixed_dtypes(dev, shape, levels):
+    """bf16 pyramid: level 1 of the inverse sees four bf16 bands, later levels an fp32 LL (iwt_init always
+    returns fp32) with bf16 detail bands; the reference's torch.cat promotes -> bit-exact vs the oracle."""
+    import hivae_b200 as hv
+    x = torch.randn(*shape, generator=_gen(3)).bfloat16()
+    bands, ll = hv.dwt_pyramid(x.to(dev), levels)
+    ob, oll = O.haar_pyramid(x, levels)
+    assert torch.equal(ll.cpu(), oll)
+    rec = hv.iwt_pyramid(bands, ll)
+    assert rec.dtype == torch.float32
+    assert torch.equal(rec.cpu(), O.haar_pyramid_inverse(ob, oll))
+
+
 # =============================================================================== frequency split
 def test_freq_split_golden(dev, golden):
     import hivae_b200 as hv
@@ -198,27 +212,31 @@ def test_linear_qknorm_epilogue(dev, dtype):
     assert rel(out, ref) <= (1e-5 if dtype == torch.float32 else 8e-3)
 
 
+@pytest.mark.parametrize("geom", [(6, 50, 128, 256, 3, 40, 10, 25),        # one CTA per tile, blocks straddle 2 frames
+                                  (5, 300, 384, 128, 18, 274, 18, 256),    # CTA pairs (M > 256, N > 128), the DiT row layout
+                                  (37, 30, 200, 64, 5, 20, 8, 10),         # L < 32: a 32-row block touches 3 frames; N % 32 != 0
+                                  (3, 128, 1024, 1024, 0, 128, 0, 128)])   # frame == tile
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-def test_linear_gated_residual_epilogue(dev, dtype):
-    """res[f, row_off+i, :] += gate[cond(f), seg(i)] * (A W^T + b) with image / motion gate columns."""
+def test_linear_gated_residual_epilogue(dev, dtype, geom):
+    """res[f, row_off+i, :] += gate[cond(f), seg(i)] * (A W^T + b) with image / motion gate columns
+    (bf16: TMA-reduce epilogue of the tcgen05 GEMM; fp32: the SIMT GEMM's read-modify-write)."""
     from hivae_b200 import ops
     g = _gen(33)
-    frames, FR, D, K = 6, 50, 128, 256
-    row_off, L, img_start, img_len = 3, 40, 10, 25
+    frames, FR, D, K, row_off, L, img_start, img_len = geom
     A = torch.randn(frames * L, K, generator=g)
     W = torch.randn(D, K, generator=g) / math.sqrt(K)
     b = torch.randn(D, generator=g) * 0.1
     res = torch.randn(frames, FR, D, generator=g)
-    table = torch.randn(3, 6 * D, generator=g)  # conditioning row = (f // 2) * 1
+    table = torch.randn((frames + 1) // 2, 6 * D, generator=g)  # conditioning row = (f // 2) * 1
     if dtype == torch.bfloat16:
         A, W = A.bfloat16(), W.bfloat16()
     y = _ref_linear(A.float(), W.float(), b).float().view(frames, L, D)
     ref = res.clone()
-    for f in range(frames):
-        for i in range(L):
-            ai = row_off + i
-            col = 5 * D if img_start <= ai < img_start + img_len else 2 * D
-            ref[f, ai] += table[f // 2, col:col + D] * y[f, i]
+    ai = row_off + torch.arange(L)
+    img = ((ai >= img_start) & (ai < img_start + img_len)).view(1, L, 1)
+    tf = table[torch.arange(frames) // 2]                                    # (frames, 6D)
+    gate = torch.where(img, tf[:, None, 5 * D:6 * D], tf[:, None, 2 * D:3 * D])  # (frames, L, D)
+    ref[:, row_off:row_off + L] += gate * y
     resd = res.to(dev)
     rows = ops.Rows(resd, row_off, L, img_start, img_len)
     ops.linear(A.to(dev), W.to(dev), ops.epi_residual(rows, b.to(dev), ops.Ada(table.to(dev), 2, 1), 2 * D, 5 * D))

@@ -2,9 +2,9 @@
 # launch list of one timed bench step + full captures of the dominant kernels (run under gpurun)
 set -x
 mkdir -p gpurun_out
-CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline"
+CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --ncu-range"
 $CMD > gpurun_out/plain.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -s 16140 -c 5400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1
 echo "launch list exit=$?"
 CMD2="python tools/bench_gemm.py"
 REPS=1 $CMD2 > gpurun_out/plain2.log 2>&1 &&
