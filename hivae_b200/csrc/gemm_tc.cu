@@ -19,6 +19,7 @@
 // warps 2..9 = epilogue (TMEM lane quarter = warp_idx % 4, column half = (warp_idx - 2) / 4).
 #include <cuda.h>
 #include <stdlib.h>
+#include <string.h>
 #include <mutex>
 #include <string>
 #include <unordered_map>
@@ -29,12 +30,20 @@ namespace {
 
 constexpr int BM = 128, BK = 64;                              // rows of A / accumulator lanes per CTA, K per stage
 constexpr int EPI_WARPS = 8, THREADS = 64 + 32 * EPI_WARPS;  // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
-constexpr int STAGING_BYTES = EPI_WARPS * 32 * 32 * 4;       // one 32x32 fp32 transpose tile per epilogue warp
+constexpr int SMEM_LIMIT = 232448 - 512;                     // 227 KB per CTA minus the static barriers
 
+// One 32x32 fp32 transpose tile per epilogue warp; the residual (TMA reduce) epilogue keeps 32 zero rows behind
+// each tile so that a reduce may start at any row of the tile (see epi_block_reduce).
+template <int MODE> constexpr int staging_floats_per_warp() { return MODE == HV_EPI_RESIDUAL ? 64 * 32 : 32 * 32; }
+template <int MODE> constexpr int staging_bytes() { return EPI_WARPS * staging_floats_per_warp<MODE>() * 4; }
 // CTAS = 1: one CTA per 128 x BN tile.  CTAS = 2: a CTA pair per 256 x BN tile, BN/2 rows of B per CTA.
-template <int CTAS> constexpr int num_stages() { return CTAS == 2 ? 6 : 4; }
 template <int BN, int CTAS> constexpr int stage_bytes() { return (BM + BN / CTAS) * BK * 2; }
-template <int BN, int CTAS> constexpr int smem_bytes() { return num_stages<CTAS>() * stage_bytes<BN, CTAS>() + STAGING_BYTES + 1024; }
+template <int BN, int MODE, int CTAS> constexpr int num_stages() {
+    return (SMEM_LIMIT - 1024 - staging_bytes<MODE>()) / stage_bytes<BN, CTAS>() > 8 ? 8 : (SMEM_LIMIT - 1024 - staging_bytes<MODE>()) / stage_bytes<BN, CTAS>();
+}
+template <int BN, int MODE, int CTAS> constexpr int smem_bytes() {
+    return num_stages<BN, MODE, CTAS>() * stage_bytes<BN, CTAS>() + staging_bytes<MODE>() + 1024;
+}
 
 __device__ __forceinline__ float gelu_tanh_fast(float x) {
     // tanh.approx (MUFU): 2^-11 relative error, far below the bf16 rounding of the stored value
@@ -54,8 +63,11 @@ __device__ __forceinline__ float4* stage_ptr(float* stage, int r, int c) {
 // row (row0 + lane), bias / activation / QK-norm already applied.  The block is transposed through shared
 // memory so that global accesses are row-contiguous (128 B per row for fp32, 64 B for bf16).
 // Gated residual block through a TMA reduce: res[rows, col0:col0+32) += gate * acc.  The 32-row block may
-// straddle frame boundaries of the residual buffer; one reduce per touched frame, rows outside [0, L)
-// are clipped by the tensor map (dims: N columns x L rows x frames).
+// straddle one frame boundary of the residual buffer (L >= 32).  Rows of frame f: one reduce at row i0, the
+// rows >= L are clipped by the tensor map (dims: N columns x L rows x frames).  Rows of frame f+1: a second
+// reduce at row 0 whose SOURCE starts s = L - i0 rows into the staging tile (TMA's 128 B swizzle is a function
+// of the absolute shared-memory address, so any row offset is consistent); its last s rows read the zero rows
+// kept behind the tile and add 0.  (Negative start coordinates are not an option: they fault on sm_100.)
 __device__ __forceinline__ void epi_block_reduce(const HvEpiDev& d, const CUtensorMap* tmap_r, float* stage, int lane,
                                                  long long row0, long long r, long long M, int col0, int N,
                                                  float (&acc)[32], long long gate_off) {
@@ -82,9 +94,9 @@ __device__ __forceinline__ void epi_block_reduce(const HvEpiDev& d, const CUtens
     __syncwarp();
     if (lane == 0) {
         const long long f0 = row0 / e.L;
-        int i = (int)(row0 - f0 * e.L);
-        const long long frames = M / e.L;
-        for (long long f = f0; i > -32 && f < frames; ++f, i -= e.L) tc::tma_reduce_add_3d(tmap_r, stage, col0, i, (int)f);
+        const int i0 = (int)(row0 - f0 * e.L), s = e.L - i0;
+        if (row0 < M) tc::tma_reduce_add_3d(tmap_r, stage, col0, i0, (int)f0);
+        if (s < 32 && row0 + s < M) tc::tma_reduce_add_3d(tmap_r, stage + s * 32, col0, 0, (int)(f0 + 1));
         tc::bulk_commit();
     }
 }
@@ -182,7 +194,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_r, long long M, int N, int K, int use_reduce,
                const __grid_constant__ HvEpiDev epi) {
-    constexpr int STAGES = num_stages<CTAS>();
+    constexpr int STAGES = num_stages<BN, MODE, CTAS>();
     constexpr int STAGE_BYTES = stage_bytes<BN, CTAS>();
     constexpr int BNL = BN / CTAS;     // rows of the B tile staged by this CTA
     constexpr int TILE_M = BM * CTAS;  // rows of the output tile of the CTA (pair)
@@ -277,9 +289,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         const int q = warp & 3;    // TMEM lane quarter this warp may access (hardware rule: warp id % 4)
         const int half = ew >> 2;  // which half of the tile's columns
         constexpr int HALF = BN / 2;
-        float* stage = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES) + ew * 1024;
+        float* stage = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES) + ew * staging_floats_per_warp<MODE>();
         const HvEpilogue& e = epi.e;
         const bool reduce = MODE == HV_EPI_RESIDUAL && use_reduce;
+        if (MODE == HV_EPI_RESIDUAL) {  // the zero rows behind the tile
+#pragma unroll
+            for (int k = 0; k < 8; ++k) reinterpret_cast<float4*>(stage + 32 * 32)[k * 32 + lane] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         int a = 0; uint32_t aph = 0;
         for (long long t = unit; t < num_tiles; t += units) {
             const long long m0 = (t / n_blocks) * TILE_M + (long long)rank * BM;
@@ -443,7 +459,9 @@ static int make_tmap_residual(float* res, int N, int L, long long frames, long l
     struct Key { const void* p; int N, L, off; long long frames, fr; };
     static std::unordered_map<std::string, CUtensorMap> cache;
     static std::mutex mu;
-    Key key{res, N, L, row_off, frames, frame_rows};
+    Key key;
+    memset(&key, 0, sizeof(key));  // padding bytes are part of the cache key
+    key.p = res; key.N = N; key.L = L; key.off = row_off; key.frames = frames; key.fr = frame_rows;
     std::string ks(reinterpret_cast<const char*>(&key), sizeof(key));
     {
         std::lock_guard<std::mutex> g(mu);
@@ -478,7 +496,7 @@ int max_pairs() {
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.gridDim = dim3(2 * (hv_num_sms() / 2)); cfg.blockDim = dim3(THREADS);
-        cfg.dynamicSmemBytes = smem_bytes<BN, 2>(); cfg.attrs = at; cfg.numAttrs = 1;
+        cfg.dynamicSmemBytes = smem_bytes<BN, MODE, 2>(); cfg.attrs = at; cfg.numAttrs = 1;
         int n = 0;
         if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<BN, MODE, 2>, &cfg) != cudaSuccess || n <= 0) {
             cudaGetLastError();
@@ -495,14 +513,14 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, 
     auto kern = gemm_tc_kernel<BN, MODE, CTAS>;
     static bool configured = false;
     if (!configured) {
-        HV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, CTAS>()));
+        HV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, MODE, CTAS>()));
         configured = true;
     }
     const long long tiles = ((M + BM * CTAS - 1) / (BM * CTAS)) * ((N + BN - 1) / BN);
     if constexpr (CTAS == 1) {
         const int sms = hv_num_sms();
         const int grid = (int)(tiles < sms ? tiles : sms);
-        kern<<<grid, THREADS, smem_bytes<BN, CTAS>(), st>>>(ta, tb, tr, (long long)M, N, K, use_reduce, d);
+        kern<<<grid, THREADS, smem_bytes<BN, MODE, CTAS>(), st>>>(ta, tb, tr, (long long)M, N, K, use_reduce, d);
     } else {
         const int pairs = max_pairs<BN, MODE>();
         const int units = (int)(tiles < pairs ? tiles : pairs);
@@ -511,7 +529,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, 
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.gridDim = dim3(2 * units); cfg.blockDim = dim3(THREADS);
-        cfg.dynamicSmemBytes = smem_bytes<BN, CTAS>(); cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
+        cfg.dynamicSmemBytes = smem_bytes<BN, MODE, CTAS>(); cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
         HV_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tr, (long long)M, N, K, use_reduce, d));
     }
     HV_LAUNCH_CHECK();
@@ -552,7 +570,7 @@ extern "C" int hv_linear_bf16(const void* A, int64_t lda, const void* W, int64_t
     if ((rc = hv_make_tmap_bf16(A, M, K, lda, BM, &ta)) != HV_OK) return rc;
     if ((rc = hv_make_tmap_bf16(W, N, K, ldw, BN / ctas, &tb)) != HV_OK) return rc;
     int use_reduce = 0;
-    if (d.e.mode == HV_EPI_RESIDUAL && want_reduce && d.vec_ok) {
+    if (d.e.mode == HV_EPI_RESIDUAL && want_reduce && d.vec_ok && d.e.L >= 32) {
         if ((rc = make_tmap_residual(d.e.res, N, d.e.L, M / d.e.L, d.e.frame_rows, d.e.row_off, &tr)) != HV_OK) return rc;
         use_reduce = 1;
     } else {
