@@ -1,22 +1,27 @@
 // tcgen05 / TMEM attention for the spatial sequences of the DiT and the object encoder
-// (head_dim 64, bf16, no mask, 16 <= Lkv <= 320, rows of a sequence contiguous):
+// (head_dim 64, bf16, no mask, 16 <= Lkv <= 288, rows of a sequence contiguous):
 //   softmax(Q K^T * scale) V   per (sequence, head)
 // (F.scaled_dot_product_attention inside diffusers AttnProcessor2_0; call sites
 //  model/modules.py:699-707, 1043-1051 of the reference).
 //
-// The whole key range of a sequence (<= 320 keys) fits in TMEM, so there is no online-softmax
-// rescaling: per 128-query tile
-//   S[128 x KP]  = Q K^T           tcgen05.mma, A = Q tile, B = K (both K-major, SWIZZLE_128B via TMA)
-//   P            = exp2(S*c - max) 8 softmax warps (2 threads per query row, half the keys each),
+// The whole key range of a sequence (<= 288 keys) fits in TMEM, so there is no online-softmax
+// rescaling.  Per 128-query tile T:
+//   S[128 x KP]  = Q K^T           tcgen05.mma, A = Q tile, B = K (both K-major, SWIZZLE_128B via TMA),
+//                                  issued as two key halves H0 / H1 into a ring of THREE half-buffers
+//   P            = exp2(S*c - max) 8 softmax warps: thread (row, h) owns key half h of its query row,
 //                                  bf16 P written to shared memory in the K-major SWIZZLE_128B layout
 //   O[128 x 64]  = P V             tcgen05.mma, A = P (smem), B = V as an MN-major operand (V is stored
 //                                  [key][dim], exactly what TMA delivers; no transpose pass)
 //   out          = O / rowsum      read back with tcgen05.ld, scaled, stored as bf16
-// CTAs are persistent over (sequence, head) pairs; K is reloaded while the previous pair's last
-// tile is still in its softmax / PV phase, V while its epilogue runs.
+// Software pipeline (the point of the three half-buffers): while the softmax warps work on tile T the
+// tensor core already holds S(T+1); the epilogue of tile T-1 runs between the max pass and the exp pass
+// of tile T, when PV(T-1) has long retired.  The softmax warps therefore never wait for an MMA in steady
+// state and the kernel is bound by MUFU.EX2 / issue slots of the exp pass.  Query tiles past the end of
+// the sequence (e.g. rows 18..127 of the third tile of a 274-token sequence) skip both passes.
 //
-// Warp roles (288 threads): warps 0..7 softmax + epilogue (TMEM lane quarter = warp % 4, key half =
-// warp / 4), warp 8 = TMA producer + MMA issuer + TMEM owner (one elected lane).
+// Warp roles (320 threads): warps 0..7 softmax + epilogue (TMEM lane quarter = warp % 4, key half =
+// warp / 4), warp 8 = MMA issuer + TMEM owner, warp 9 = TMA producer (one elected lane each).
+// CTAs are persistent over (sequence, head) pairs; K is double-buffered across pairs.
 #include <cuda.h>
 #include "attn.cuh"
 #include "tc_ptx.cuh"
@@ -25,9 +30,10 @@ int hv_make_tmap_bf16(const void* ptr, long long rows, int K, long long ld, int 
 
 namespace {
 
-constexpr int QT = 128, HD = 64, KMAX = 320, THREADS = 288;
-constexpr int O_COL = 0, S_COL = 64;  // TMEM columns: O accumulator [0,64), S [64, 64+KP)
+constexpr int QT = 128, HD = 64, KMAX = 288, THREADS = 320;
+constexpr int O_COL = 0, S_COL = 64, SBUF = 144;  // TMEM columns: O [0,64), three S half-buffers of 144 columns
 constexpr uint32_t TMEM_COLS = 512;
+constexpr int QBYTES = QT * 128;
 
 struct TcArgs {
     __nv_bfloat16* out;
@@ -37,28 +43,55 @@ struct TcArgs {
     float sl2;               // scale * log2(e)
 };
 
+__device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+// wait for the outstanding tcgen05.ld; the registers are in/out operands so that no use of them can be
+// scheduled above the wait
+__device__ __forceinline__ void tmem_ld16_wait(uint32_t (&r)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]),
+                   "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])
+                 :
+                 : "memory");
+}
+
 __global__ void __launch_bounds__(THREADS, 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                const __grid_constant__ CUtensorMap tv, const TcArgs a) {
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t q_bar[2], k_bar, v_bar, s_full, p_full, o_full;
+    __shared__ __align__(8) uint64_t q_full[2], q_free[2], k_full[2], k_free[2], v_full, v_free, s_full[2][2], p_full, o_full;
     __shared__ uint32_t tmem_slot;
     __shared__ float smax[2][QT], ssum[2][QT];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int KP = a.KP, KP32 = (KP + 31) & ~31;
     const int nq = (a.Lq + QT - 1) / QT;
+    const int nb = KP >> 4, hb = (nb + 1) >> 1, HB = hb * 16;  // key half 0 = [0, HB), half 1 = [HB, KP)
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* Qs = smem;                       // 2 x [128 x 64] bf16
-    uint8_t* Ks = Qs + 2 * QT * 128;          // [KP32 x 64]
-    uint8_t* Vs = Ks + KP32 * 128;            // [KP32 x 64]
+    uint8_t* Ks = Qs + 2 * QBYTES;            // 2 x [KP32 x 64]
+    uint8_t* Vs = Ks + 2 * KP32 * 128;        // [KP32 x 64]
     uint8_t* Ps = Vs + KP32 * 128;            // nchunks x [128 x 64]
+    const long long n_items = a.items > blockIdx.x ? (a.items - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const long long total = n_items * nq;     // query tiles of this CTA
 
     if (threadIdx.x == 0) {
         tc::prefetch_tmap(&tq); tc::prefetch_tmap(&tk); tc::prefetch_tmap(&tv);
-        tc::mbar_init(&q_bar[0], 1); tc::mbar_init(&q_bar[1], 1);
-        tc::mbar_init(&k_bar, 1); tc::mbar_init(&v_bar, 1);
-        tc::mbar_init(&s_full, 1); tc::mbar_init(&p_full, 256); tc::mbar_init(&o_full, 1);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            tc::mbar_init(&q_full[i], 1); tc::mbar_init(&q_free[i], 1);
+            tc::mbar_init(&k_full[i], 1); tc::mbar_init(&k_free[i], 1);
+            tc::mbar_init(&s_full[i][0], 1); tc::mbar_init(&s_full[i][1], 1);
+        }
+        tc::mbar_init(&v_full, 1); tc::mbar_init(&v_free, 1);
+        tc::mbar_init(&p_full, 256); tc::mbar_init(&o_full, 1);
         tc::fence_barrier_init();
     }
     if (warp == 8) tc::tmem_alloc(&tmem_slot, TMEM_COLS);
@@ -67,139 +100,217 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
     tc::fence_after_sync();
     const uint32_t tmem_base = tmem_slot;
 
-    if (warp == 8) {
+    if (warp == 9) {
+        // ===================================================== TMA producer
         if (lane == 0) {
-            // ================================================= TMA producer + MMA issuer
-            auto issue_s = [&](long long T) {
-                tc::fence_after_sync();
-                const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(Qs + (T & 1) * (QT * 128)));
-                for (int n0 = 0; n0 < KP; n0 += 256) {
-                    const int nn = KP - n0 < 256 ? KP - n0 : 256;
-                    const uint32_t idesc = tc::make_idesc_bf16(QT, nn);
-                    const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(Ks + n0 * 128));
+            long long T = 0, it = 0;
+            auto load_q = [&](long long qrow0, int col, int i) {
+                const int b = (int)(T & 1);
+                tc::mbar_wait(&q_free[b], (uint32_t)(((T >> 1) & 1) ^ 1));
+                tc::mbar_expect_tx(&q_full[b], QBYTES);
 #pragma unroll
-                    for (int k = 0; k < HD / 16; ++k)
-                        tc::umma_bf16(tmem_base + S_COL + n0, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, k != 0);
+                for (int j = 0; j < QT / 32; ++j)
+                    tc::tma_load_2d(Qs + b * QBYTES + j * 4096, &tq, &q_full[b], col, (int)(qrow0 + i * QT + j * 32));
+                ++T;
+            };
+            for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
+                const long long seq = w / a.heads;
+                const int col = (int)(w - seq * a.heads) * HD;
+                const long long qrow0 = seq * a.q_sa, kvrow0 = seq * a.kv_sa;
+                const int kb = (int)(it & 1);
+                tc::mbar_wait(&k_free[kb], (uint32_t)(((it >> 1) & 1) ^ 1));
+                tc::mbar_expect_tx(&k_full[kb], KP32 * 128);
+                for (int j = 0; j < KP32 / 32; ++j)
+                    tc::tma_load_2d(Ks + kb * KP32 * 128 + j * 4096, &tk, &k_full[kb], col, (int)(kvrow0 + j * 32));
+                load_q(qrow0, col, 0);
+                if (nq > 1) load_q(qrow0, col, 1);
+                tc::mbar_wait(&v_free, (uint32_t)((it & 1) ^ 1));
+                tc::mbar_expect_tx(&v_full, KP32 * 128);
+                for (int j = 0; j < KP32 / 32; ++j)
+                    tc::tma_load_2d(Vs + j * 4096, &tv, &v_full, col, (int)(kvrow0 + j * 32));
+                for (int i = 2; i < nq; ++i) load_q(qrow0, col, i);
+            }
+        }
+    } else if (warp == 8) {
+        // ===================================================== MMA issuer
+        if (lane == 0 && total > 0) {
+            auto issue_s = [&](long long T, int h) {  // S(T), key half h -> ring buffer (2T + h) % 3
+                const long long it = T / nq;
+                const int ncols = h ? KP - HB : HB;
+                if (ncols > 0) {
+                    const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(Qs + (T & 1) * QBYTES));
+                    const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(Ks + (it & 1) * KP32 * 128 + h * HB * 128));
+                    const uint32_t idesc = tc::make_idesc_bf16(QT, ncols);
+                    const uint32_t d = tmem_base + S_COL + (uint32_t)((2 * T + h) % 3) * SBUF;
+#pragma unroll
+                    for (int k = 0; k < HD / 16; ++k) tc::umma_bf16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, k != 0);
                 }
-                tc::umma_commit(&s_full);
+                tc::umma_commit(&s_full[T & 1][h]);  // one barrier per (tile parity, half): never more than one phase ahead of a waiter
             };
             auto issue_pv = [&]() {
-                tc::fence_after_sync();
                 constexpr uint32_t idesc = tc::make_idesc_bf16_bmn(QT, HD);
                 for (int j = 0; j < KP / 16; ++j) {
-                    const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(Ps + (j >> 2) * (QT * 128))) + (uint64_t)(2 * (j & 3));
+                    const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(Ps + (j >> 2) * QBYTES)) + (uint64_t)(2 * (j & 3));
                     const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(Vs + j * 2048));  // 16 keys x 128 B, MN-major
                     tc::umma_bf16(tmem_base + O_COL, da, db, idesc, j != 0);
                 }
                 tc::umma_commit(&o_full);
             };
-            long long T0 = 0, it = 0;
-            for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it, T0 += nq) {
-                const long long seq = w / a.heads;
-                const int head = (int)(w - seq * a.heads), col = head * HD;
-                const long long qrow0 = seq * a.q_sa, kvrow0 = seq * a.kv_sa;
-                // K (free: every S MMA of the previous pair completed before its p_full)
-                tc::mbar_expect_tx(&k_bar, KP32 * 128);
-                for (int b = 0; b < KP32 / 32; ++b) tc::tma_load_2d(Ks + b * 4096, &tk, &k_bar, col, (int)(kvrow0 + b * 32));
-                for (int i = 0; i < (nq < 2 ? nq : 2); ++i) {
-                    const long long T = T0 + i;
-                    uint8_t* dst = Qs + (T & 1) * (QT * 128);
-                    tc::mbar_expect_tx(&q_bar[T & 1], QT * 128);
-#pragma unroll
-                    for (int b = 0; b < QT / 32; ++b)
-                        tc::tma_load_2d(dst + b * 4096, &tq, &q_bar[T & 1], col, (int)(qrow0 + i * QT + b * 32));
+            auto after_s = [&](long long T) {  // both halves of S(T) issued: its Q buffer and (last tile) its K buffer retire with them
+                tc::umma_commit(&q_free[T & 1]);
+                if (T % nq == nq - 1) tc::umma_commit(&k_free[(T / nq) & 1]);
+            };
+            tc::mbar_wait(&k_full[0], 0);
+            tc::mbar_wait(&q_full[0], 0);
+            tc::fence_after_sync();
+            issue_s(0, 0); issue_s(0, 1); after_s(0);
+            for (long long T = 0; T < total; ++T) {
+                const long long it = T / nq;
+                const int i = (int)(T - it * nq);
+                if (T + 1 < total) {
+                    const long long it1 = (T + 1) / nq;
+                    if (i + 1 == nq) tc::mbar_wait(&k_full[it1 & 1], (uint32_t)((it1 >> 1) & 1));
+                    tc::mbar_wait(&q_full[(T + 1) & 1], (uint32_t)(((T + 1) >> 1) & 1));
+                    tc::fence_after_sync();
+                    issue_s(T + 1, 0);  // ring buffer of S(T-1).H1: its exp pass ended with p_full(T-1)
                 }
-                if (it > 0) tc::mbar_wait(&o_full, (uint32_t)((T0 - 1) & 1));  // V free once the previous PV retired
-                tc::mbar_expect_tx(&v_bar, KP32 * 128);
-                for (int b = 0; b < KP32 / 32; ++b) tc::tma_load_2d(Vs + b * 4096, &tv, &v_bar, col, (int)(kvrow0 + b * 32));
-                tc::mbar_wait(&k_bar, (uint32_t)(it & 1));
-                tc::mbar_wait(&q_bar[T0 & 1], (uint32_t)((T0 >> 1) & 1));
-                issue_s(T0);
-                for (int i = 0; i < nq; ++i) {
-                    const long long T = T0 + i;
-                    tc::mbar_wait(&p_full, (uint32_t)(T & 1));  // P(T) written, S free
-                    if (i == 0) tc::mbar_wait(&v_bar, (uint32_t)(it & 1));
-                    issue_pv();
-                    if (i + 1 < nq) {
-                        tc::mbar_wait(&q_bar[(T + 1) & 1], (uint32_t)(((T + 1) >> 1) & 1));
-                        issue_s(T + 1);
-                    }
-                    if (i + 2 < nq) {  // Q buffer (T & 1) is free: S(T) retired
-                        uint8_t* dst = Qs + (T & 1) * (QT * 128);
-                        tc::mbar_expect_tx(&q_bar[T & 1], QT * 128);
-#pragma unroll
-                        for (int b = 0; b < QT / 32; ++b)
-                            tc::tma_load_2d(dst + b * 4096, &tq, &q_bar[T & 1], col, (int)(qrow0 + (i + 2) * QT + b * 32));
-                    }
-                }
+                tc::mbar_wait(&p_full, (uint32_t)(T & 1));  // P(T) written; O(T-1) read back
+                if (i == 0) tc::mbar_wait(&v_full, (uint32_t)(it & 1));
+                tc::fence_after_sync();
+                issue_pv();
+                if (i == nq - 1) tc::umma_commit(&v_free);
+                if (T + 1 < total) { issue_s(T + 1, 1); after_s(T + 1); }  // ring buffer of S(T).H0
             }
         }
     } else {
         // ===================================================== softmax + epilogue warps
         const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
-        const int nb = KP >> 4, hb = (nb + 1) >> 1;
-        const int c_begin = h ? hb * 16 : 0, c_end = h ? KP : hb * 16;
+        const int c_begin = h ? HB : 0, c_end = h ? KP : HB;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
         uint8_t* prow = Ps + (row >> 3) * 1024 + (row & 7) * 128;  // this row inside every 64-key P chunk
         long long T = 0;
+        // deferred epilogue of the previous tile
+        bool pend = false;
+        __nv_bfloat16* pend_ptr = nullptr;
+        float pend_inv = 0.f;
+        bool pend_store = false, pend_active = false;
+        auto epilogue = [&]() {
+            tc::mbar_wait(&o_full, (uint32_t)((T - 1) & 1));
+            tc::fence_after_sync();
+            if (pend_active) {  // warp-uniform (tcgen05.ld is .sync.aligned); only the store is per-row
+                float o[32];
+                tc::tmem_ld32(t_lane + O_COL + h * 32, o);
+                const float inv = pend_inv;
+                if (pend_store) {
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8)
+                        *reinterpret_cast<uint4*>(pend_ptr + j) =
+                            make_uint4(hv_pack_bf16(o[j] * inv, o[j + 1] * inv), hv_pack_bf16(o[j + 2] * inv, o[j + 3] * inv),
+                                       hv_pack_bf16(o[j + 4] * inv, o[j + 5] * inv), hv_pack_bf16(o[j + 6] * inv, o[j + 7] * inv));
+                }
+            }
+            tc::fence_before_sync();
+        };
         for (long long w = blockIdx.x; w < a.items; w += gridDim.x) {
             const long long seq = w / a.heads;
             const int head = (int)(w - seq * a.heads);
             for (int i = 0; i < nq; ++i, ++T) {
-                tc::mbar_wait(&s_full, (uint32_t)(T & 1));
+                const bool active = i * QT + q * 32 < a.Lq;  // warp-uniform: this warp has query rows in the tile
+                const uint32_t s_addr = t_lane + S_COL + (uint32_t)((2 * T + h) % 3) * SBUF - (uint32_t)c_begin;
+                tc::mbar_wait(&s_full[T & 1][h], (uint32_t)((T >> 1) & 1));
                 tc::fence_after_sync();
                 // ---- pass 1: row maximum over this thread's half of the keys
                 float mx = -INFINITY;
-                for (int c = c_begin; c < c_end; c += 16) {
-                    float v[16];
-                    tc::tmem_ld16(t_lane + S_COL + c, v);
+                if (active && c_begin < c_end) {
+                    uint32_t va[16], vb[16];
+                    int c = c_begin;
+                    tmem_ld16_issue(s_addr + c, va);
+                    while (true) {
+                        tmem_ld16_wait(va);
+                        bool more = c + 16 < c_end;
+                        if (more) tmem_ld16_issue(s_addr + c + 16, vb);
+                        if (c + 16 <= a.Lkv) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) if (c + j < a.Lkv) mx = fmaxf(mx, v[j]);
+                            for (int j = 0; j < 16; ++j) mx = fmaxf(mx, __uint_as_float(va[j]));
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) if (c + j < a.Lkv) mx = fmaxf(mx, __uint_as_float(va[j]));
+                        }
+                        if (!more) break;
+                        c += 16;
+                        tmem_ld16_wait(vb);
+                        more = c + 16 < c_end;
+                        if (more) tmem_ld16_issue(s_addr + c + 16, va);
+                        if (c + 16 <= a.Lkv) {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) mx = fmaxf(mx, __uint_as_float(vb[j]));
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) if (c + j < a.Lkv) mx = fmaxf(mx, __uint_as_float(vb[j]));
+                        }
+                        if (!more) break;
+                        c += 16;
+                    }
                 }
                 smax[h][row] = mx;
                 tc::named_bar_sync(1, 256);
                 mx = fmaxf(mx, smax[h ^ 1][row]);
                 const float msc = mx * a.sl2;
+                // ---- epilogue of the previous tile: PV(T-1) retired while the max pass ran
+                if (pend) epilogue();
                 // ---- pass 2: P = exp2(S*c - max*c) -> bf16 -> shared memory (K-major, 128 B swizzle)
                 float sum = 0.f;
-                for (int c = c_begin; c < c_end; c += 16) {
-                    float v[16];
-                    tc::tmem_ld16(t_lane + S_COL + c, v);
+                if (active && c_begin < c_end) {
+                    uint32_t va[16], vb[16];
+                    auto emit = [&](uint32_t (&r)[16], int c) {
+                        float v[16];
+                        if (c + 16 <= a.Lkv) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        v[j] = (c + j < a.Lkv) ? tc::ex2_approx(fmaf(v[j], a.sl2, -msc)) : 0.f;
-                        sum += v[j];
+                            for (int j = 0; j < 16; ++j) v[j] = tc::ex2_approx(fmaf(__uint_as_float(r[j]), a.sl2, -msc));
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) v[j] = (c + j < a.Lkv) ? tc::ex2_approx(fmaf(__uint_as_float(r[j]), a.sl2, -msc)) : 0.f;
+                        }
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) sum += v[j];
+                        uint8_t* pc = prow + (c >> 6) * QBYTES;
+                        const int jc = (c & 63) >> 3;
+                        *reinterpret_cast<uint4*>(pc + (((jc) ^ (row & 7)) << 4)) =
+                            make_uint4(hv_pack_bf16(v[0], v[1]), hv_pack_bf16(v[2], v[3]), hv_pack_bf16(v[4], v[5]), hv_pack_bf16(v[6], v[7]));
+                        *reinterpret_cast<uint4*>(pc + (((jc + 1) ^ (row & 7)) << 4)) =
+                            make_uint4(hv_pack_bf16(v[8], v[9]), hv_pack_bf16(v[10], v[11]), hv_pack_bf16(v[12], v[13]), hv_pack_bf16(v[14], v[15]));
+                    };
+                    int c = c_begin;
+                    tmem_ld16_issue(s_addr + c, va);
+                    while (true) {
+                        tmem_ld16_wait(va);
+                        bool more = c + 16 < c_end;
+                        if (more) tmem_ld16_issue(s_addr + c + 16, vb);
+                        emit(va, c);
+                        if (!more) break;
+                        c += 16;
+                        tmem_ld16_wait(vb);
+                        more = c + 16 < c_end;
+                        if (more) tmem_ld16_issue(s_addr + c + 16, va);
+                        emit(vb, c);
+                        if (!more) break;
+                        c += 16;
                     }
-                    uint8_t* pc = prow + (c >> 6) * (QT * 128);
-                    const int jc = (c & 63) >> 3;
-                    *reinterpret_cast<uint4*>(pc + (((jc) ^ (row & 7)) << 4)) =
-                        make_uint4(hv_pack_bf16(v[0], v[1]), hv_pack_bf16(v[2], v[3]), hv_pack_bf16(v[4], v[5]), hv_pack_bf16(v[6], v[7]));
-                    *reinterpret_cast<uint4*>(pc + (((jc + 1) ^ (row & 7)) << 4)) =
-                        make_uint4(hv_pack_bf16(v[8], v[9]), hv_pack_bf16(v[10], v[11]), hv_pack_bf16(v[12], v[13]), hv_pack_bf16(v[14], v[15]));
                 }
                 ssum[h][row] = sum;
-                tc::fence_before_sync();
-                tc::fence_proxy_async();
+                tc::fence_before_sync();   // orders this thread's tcgen05.ld of S / O before the MMAs that overwrite them
+                tc::fence_proxy_async();   // P (generic-proxy stores) -> visible to the tensor core
                 tc::mbar_arrive(&p_full);
                 tc::named_bar_sync(1, 256);
-                const float inv = 1.f / (sum + ssum[h ^ 1][row]);
-                // ---- epilogue: O / rowsum -> bf16 (this thread: 32 of the 64 output dims of its row)
-                tc::mbar_wait(&o_full, (uint32_t)(T & 1));
-                tc::fence_after_sync();
-                float o[32];
-                tc::tmem_ld32(t_lane + O_COL + h * 32, o);
-                tc::fence_before_sync();
                 const int qr = i * QT + row;
-                if (qr < a.Lq) {
-                    __nv_bfloat16* op = a.out + (seq * a.q_sa + qr) * a.ldo + head * HD + h * 32;
-#pragma unroll
-                    for (int j = 0; j < 32; j += 8)
-                        *reinterpret_cast<uint4*>(op + j) =
-                            make_uint4(hv_pack_bf16(o[j] * inv, o[j + 1] * inv), hv_pack_bf16(o[j + 2] * inv, o[j + 3] * inv),
-                                       hv_pack_bf16(o[j + 4] * inv, o[j + 5] * inv), hv_pack_bf16(o[j + 6] * inv, o[j + 7] * inv));
-                }
+                pend = true;
+                pend_active = active;
+                pend_store = qr < a.Lq;
+                pend_inv = 1.f / (sum + ssum[h ^ 1][row]);
+                pend_ptr = a.out + (seq * a.q_sa + qr) * a.ldo + head * HD + h * 32;
             }
         }
+        if (pend) epilogue();
     }
     tc::fence_before_sync();
     __syncthreads();
@@ -234,7 +345,7 @@ int hv_attention_tc_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
     t.items = seqs * a.heads;
     t.sl2 = a.scale * 1.4426950408889634f;
     const int KP32 = (t.KP + 31) & ~31, nchunks = (t.KP + 63) >> 6;
-    const int smem = 2 * QT * 128 + 2 * KP32 * 128 + nchunks * QT * 128 + 1024;
+    const int smem = 2 * QBYTES + 3 * KP32 * 128 + nchunks * QBYTES + 1024;
     static int configured = 0;
     if (configured < smem) {
         HV_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -1,18 +1,19 @@
 #!/bin/bash
-# runs the gpu tier in groups, each under its own timeout, so that one hung kernel cannot eat the whole call
+# runs the gpu tier in groups, each under its own timeout, so that one hung kernel cannot eat the whole call;
+# the first group that times out stops the run (a hang would otherwise repeat in every later group)
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/gpu.txt 2>&1
 nproc >> gpurun_out/gpu.txt; lscpu | grep -E "Model name|^CPU\(s\)" >> gpurun_out/gpu.txt
-run() { name=$1; shift; timeout -k 5 "$T" python -m pytest tests/test_gpu_parity.py -q -m gpu -k "$@" > gpurun_out/test_$name.log 2>&1; echo "$name exit=$?" | tee -a gpurun_out/summary.txt; tail -n 3 gpurun_out/test_$name.log; }
+run() { name=$1; shift; timeout -k 5 "$T" python -u -m pytest tests/test_gpu_parity.py -q -m gpu -k "$@" > gpurun_out/test_$name.log 2>&1; rc=$?; echo "$name exit=$rc" | tee -a gpurun_out/summary.txt; tail -n 3 gpurun_out/test_$name.log; if [ $rc == 124 ]; then echo "TIMEOUT in $name: stopping"; exit 124; fi; }
 : > gpurun_out/summary.txt
-T=300 run signal "dwt or freq"
-T=300 run simt "linear_f32 or rope or patch_embed"
-T=300 run attn "attention"
-T=300 run gemm "linear_bf16 or qknorm or gated"
-T=300 run blocks "blocks"
-T=600 run small "small_model"
-T=900 run default "default_model or natively"
+T=120 run signal "dwt or freq or pyramid"
+T=120 run simt "linear_f32 or rope or patch_embed"
+T=120 run attn "attention"
+T=120 run gemm "linear_bf16 or qknorm or gated"
+T=120 run blocks "blocks"
+T=180 run small "small_model"
+T=300 run default "default_model or natively"
 if [ "$1" == "bench" ]; then
-  timeout -k 5 600 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit=$?" | tee -a gpurun_out/summary.txt; tail -n 4 gpurun_out/smoke.log
-  timeout -k 5 900 python bench.py --steps 2 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit=$?" | tee -a gpurun_out/summary.txt; tail -n 5 gpurun_out/bench.err; cat gpurun_out/bench.json
+  timeout -k 5 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit=$?" | tee -a gpurun_out/summary.txt; tail -n 4 gpurun_out/smoke.log
+  timeout -k 5 600 python bench.py --steps 2 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit=$?" | tee -a gpurun_out/summary.txt; tail -n 5 gpurun_out/bench.err; cat gpurun_out/bench.json
 fi
