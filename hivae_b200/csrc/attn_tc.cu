@@ -16,8 +16,13 @@
 // Software pipeline (the point of the three half-buffers): while the softmax warps work on tile T the
 // tensor core already holds S(T+1); the epilogue of tile T-1 runs between the max pass and the exp pass
 // of tile T, when PV(T-1) has long retired.  The softmax warps therefore never wait for an MMA in steady
-// state and the kernel is bound by MUFU.EX2 / issue slots of the exp pass.  Query tiles past the end of
-// the sequence (e.g. rows 18..127 of the third tile of a 274-token sequence) skip both passes.
+// state.  Measured bound (tools/probes, clock64 per phase): TMEM read bandwidth.  tcgen05.ld delivers
+// ~64 B/clk/SM, the two passes (max, exp) each read the 128 x 288 fp32 tile (147 KB) -> ~4600 of the
+// ~7000 clk a tile takes; MUFU.EX2 (2300 clk/tile) and the MMAs (1150 clk/tile) hide under it.  A variant
+// that keeps the scores in registers between the passes (16 softmax warps, 72 scores per thread) read
+// TMEM once but lost more to register spills and barrier cost than it gained (299 vs 188 us at the DiT
+// shape) and was not kept.  Query tiles past the end of the sequence (e.g. rows 18..127 of the third
+// tile of a 274-token sequence) skip both passes.
 //
 // Warp roles (320 threads): warps 0..7 softmax + epilogue (TMEM lane quarter = warp % 4, key half =
 // warp / 4), warp 8 = MMA issuer + TMEM owner, warp 9 = TMA producer (one elected lane each).
@@ -177,9 +182,11 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                 tc::mbar_wait(&p_full, (uint32_t)(T & 1));  // P(T) written; O(T-1) read back
                 if (i == 0) tc::mbar_wait(&v_full, (uint32_t)(it & 1));
                 tc::fence_after_sync();
+                // S(T+1).H1 (ring buffer of S(T).H0) goes ahead of PV(T): the softmax warps need it first, PV(T)
+                // is only read back after their next max pass
+                if (T + 1 < total) { issue_s(T + 1, 1); after_s(T + 1); }
                 issue_pv();
                 if (i == nq - 1) tc::umma_commit(&v_free);
-                if (T + 1 < total) { issue_s(T + 1, 1); after_s(T + 1); }  // ring buffer of S(T).H0
             }
         }
     } else {
