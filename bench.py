@@ -165,7 +165,8 @@ def run_reference(args):
 
 
 def _config(n_gpus):
-    return {"workload": "configs[1]: default Hi-VAE autoencoder (AMD_N 695M, random-init), bf16 inference, "
+    name = "configs[1]" if (SAMPLE_STEPS, CLIPS_PER_GPU) == (20, 8) else "configs[2] sampling sweep"
+    return {"workload": name + ": default Hi-VAE autoencoder (AMD_N 695M, random-init), bf16 inference, "
                         "batch %d synthetic 17-frame 256x256 clips (17x4x32x32 VAE latents) per GPU, encode + %d-step "
                         "rectified-flow decode" % (CLIPS_PER_GPU, SAMPLE_STEPS),
             "clips_per_gpu": CLIPS_PER_GPU, "global_clips": CLIPS_PER_GPU * n_gpus, "sample_steps": SAMPLE_STEPS,
@@ -303,7 +304,15 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ncu-range", action="store_true", help="cudaProfilerStart/Stop around the timed steps")
+    ap.add_argument("--sample-steps", type=int, default=None, help="Euler steps per clip (default 20 = configs[1]; 10/25/50 = configs[2] sweep)")
+    ap.add_argument("--clips-per-gpu", type=int, default=None, help="clips per GPU (default 8 = configs[1]; configs[2] uses 32 / n_gpus)")
     args = ap.parse_args()
+    global SAMPLE_STEPS, CLIPS_PER_GPU, TFLOP_PER_CLIP
+    if args.sample_steps:
+        SAMPLE_STEPS = args.sample_steps
+    if args.clips_per_gpu:
+        CLIPS_PER_GPU = args.clips_per_gpu
+    TFLOP_PER_CLIP = 0.475 + SAMPLE_STEPS * 4.02
     if args.impl == "reference":
         run_reference(args)
     else:

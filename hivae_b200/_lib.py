@@ -37,6 +37,8 @@ SIGNATURES = {
     "hv_check_device": (_i, []),
     "hv_launch_count": (_i64, []),
     "hv_dwt2_haar": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
+    "hv_dwt2_haar_pyramid": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
+    "hv_idwt2_haar_pyramid": (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "hv_idwt2_haar": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "hv_freq_split3d": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "hv_ln_modulate": (_i, [_vp, _i64, _i64, _i, _i, _i, _vp, _vp, _f, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _i, _vp]),

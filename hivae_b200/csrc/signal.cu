@@ -102,6 +102,90 @@ __global__ void __launch_bounds__(256) dwt2_haar_scalar_kernel(const T* __restri
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fused multi-level analysis (the caller-side recursion on LL of frenquence_wavelet.py:86-89): one thread
+// owns a 2^L x 8 input patch, keeps every intermediate LL in registers (rounded to the tensor dtype exactly
+// where the per-level path would store it) and writes the 3 detail bands of every level plus the last LL.
+// x is read once and no intermediate LL ever touches HBM: 1 launch instead of L, (1 + 1) N bytes instead of
+// 2 N (1 + 1/4 + ...).
+struct PyrOut {
+    void* hl[3];
+    void* lh[3];
+    void* hh[3];
+    void* ll;
+};
+
+template <typename T, int N>
+__device__ __forceinline__ void store_n(T* p, const float* v) {  // N in {1, 2, 4} consecutive elements, N*sizeof(T)-aligned
+    if constexpr (sizeof(T) == 4) {
+        if constexpr (N == 4) *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+        else if constexpr (N == 2) *reinterpret_cast<float2*>(p) = make_float2(v[0], v[1]);
+        else *p = v[0];
+    } else {
+        if constexpr (N == 4) *reinterpret_cast<uint2*>(p) = make_uint2(hv_pack_bf16(v[0], v[1]), hv_pack_bf16(v[2], v[3]));
+        else if constexpr (N == 2) *reinterpret_cast<uint32_t*>(p) = hv_pack_bf16(v[0], v[1]);
+        else *p = __float2bfloat16(v[0]);
+    }
+}
+
+// one level on a register patch: in[R][C] -> ll[R/2][C/2]; bands stored at (row0 + i, col0 .. col0 + C/2) of a plane of width w
+template <typename T, int R, int C>
+__device__ __forceinline__ void pyr_level(const float (&in)[R][C], float (&ll)[R / 2][C / 2], T* hl, T* lh, T* hh,
+                                          long long plane_off, int row0, int col0, int w) {
+#pragma unroll
+    for (int i = 0; i < R / 2; ++i) {
+        float bhl[C / 2], blh[C / 2], bhh[C / 2];
+#pragma unroll
+        for (int j = 0; j < C / 2; ++j)
+            haar_fwd<T>(in[2 * i][2 * j], in[2 * i + 1][2 * j], in[2 * i][2 * j + 1], in[2 * i + 1][2 * j + 1], ll[i][j], bhl[j], blh[j], bhh[j]);
+        const long long o = plane_off + (long long)(row0 + i) * w + col0;
+        store_n<T, C / 2>(hl + o, bhl); store_n<T, C / 2>(lh + o, blh); store_n<T, C / 2>(hh + o, bhh);
+    }
+}
+
+template <typename T, int LV>
+__global__ void __launch_bounds__(256) dwt2_haar_pyramid_kernel(const T* __restrict__ x, PyrOut out, long long planes, int H, int W) {
+    constexpr int B = 1 << LV;
+    const int tw = W >> 3, th = H / B;
+    const long long total = planes * th * tw;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const int cx = (int)(idx % tw);
+        const long long t = idx / tw;
+        const int by = (int)(t % th);
+        const long long pl = t / th;
+        float a[B][8];
+        const T* src = x + (pl * H + (long long)by * B) * W + cx * 8;
+#pragma unroll
+        for (int r = 0; r < B; ++r) {
+            if constexpr (sizeof(T) == 4) {
+                float lo[4], hi[4];
+                load16<T>(src + (long long)r * W, lo); load16<T>(src + (long long)r * W + 4, hi);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { a[r][j] = lo[j]; a[r][4 + j] = hi[j]; }
+            } else {
+                load16<T>(src + (long long)r * W, a[r]);
+            }
+        }
+        float l1[B / 2][4];
+        pyr_level<T, B, 8>(a, l1, (T*)out.hl[0], (T*)out.lh[0], (T*)out.hh[0], pl * (H / 2) * (W / 2), by * (B / 2), cx * 4, W / 2);
+        if constexpr (LV == 1) {
+#pragma unroll
+            for (int i = 0; i < B / 2; ++i) store_n<T, 4>((T*)out.ll + pl * (H / 2) * (W / 2) + (long long)(by * (B / 2) + i) * (W / 2) + cx * 4, l1[i]);
+        } else {
+            float l2[B / 4][2];
+            pyr_level<T, B / 2, 4>(l1, l2, (T*)out.hl[1], (T*)out.lh[1], (T*)out.hh[1], pl * (H / 4) * (W / 4), by * (B / 4), cx * 2, W / 4);
+            if constexpr (LV == 2) {
+#pragma unroll
+                for (int i = 0; i < B / 4; ++i) store_n<T, 2>((T*)out.ll + pl * (H / 4) * (W / 4) + (long long)(by * (B / 4) + i) * (W / 4) + cx * 2, l2[i]);
+            } else {
+                float l3[B / 8][1];
+                pyr_level<T, B / 4, 2>(l2, l3, (T*)out.hl[2], (T*)out.lh[2], (T*)out.hh[2], pl * (H / 8) * (W / 8), by * (B / 8), cx, W / 8);
+                store_n<T, 1>((T*)out.ll + pl * (H / 8) * (W / 8) + (long long)by * (W / 8) + cx, l3[0]);
+            }
+        }
+    }
+}
+
 template <typename T>
 __device__ __forceinline__ void haar_inv(float a, float b, float c, float d, float& o00, float& o10, float& o01, float& o11) {
     float x1 = a * 0.5f, x2 = b * 0.5f, x3 = c * 0.5f, x4 = d * 0.5f;
@@ -176,6 +260,80 @@ __global__ void __launch_bounds__(256) idwt2_haar_scalar_kernel(const TL* __rest
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Fused multi-level synthesis: the mirror of dwt2_haar_pyramid_kernel.  One thread rebuilds a 2^L x 8 output
+// patch from 1 x (8 >> L) coarse LL values and the matching detail-band patches of every level; no
+// intermediate image touches HBM.  Rounding follows the per-level path: the coarsest level computes in the
+// band dtype (four same-dtype bands), every later level in fp32 (iwt_init returned fp32, torch.cat promoted).
+template <typename T, int N>
+__device__ __forceinline__ void load_n(const T* p, float* v) {  // N in {1, 2, 4}
+    if constexpr (sizeof(T) == 4) {
+        if constexpr (N == 4) { float4 t = *reinterpret_cast<const float4*>(p); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
+        else if constexpr (N == 2) { float2 t = *reinterpret_cast<const float2*>(p); v[0] = t.x; v[1] = t.y; }
+        else v[0] = *p;
+    } else {
+        if constexpr (N == 4) {
+            uint2 raw = *reinterpret_cast<const uint2*>(p);
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+            float2 f0 = __bfloat1622float2(h[0]), f1 = __bfloat1622float2(h[1]);
+            v[0] = f0.x; v[1] = f0.y; v[2] = f1.x; v[3] = f1.y;
+        } else if constexpr (N == 2) {
+            float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+            v[0] = f.x; v[1] = f.y;
+        } else v[0] = __bfloat162float(*p);
+    }
+}
+
+// cur[R][C] (LL) + bands at (row0 + i, col0 .. col0 + C) of planes of width w  ->  next[2R][2C]
+template <typename TB, typename RT, int R, int C>
+__device__ __forceinline__ void pyr_inv_level(const float (&cur)[R][C], float (&next)[2 * R][2 * C], const TB* hl, const TB* lh,
+                                              const TB* hh, long long plane_off, int row0, int col0, int w) {
+#pragma unroll
+    for (int i = 0; i < R; ++i) {
+        float b[C], c[C], d[C];
+        const long long o = plane_off + (long long)(row0 + i) * w + col0;
+        load_n<TB, C>(hl + o, b); load_n<TB, C>(lh + o, c); load_n<TB, C>(hh + o, d);
+#pragma unroll
+        for (int j = 0; j < C; ++j)
+            haar_inv<RT>(cur[i][j], b[j], c[j], d[j], next[2 * i][2 * j], next[2 * i + 1][2 * j], next[2 * i][2 * j + 1], next[2 * i + 1][2 * j + 1]);
+    }
+}
+
+template <typename T, int LV>
+__global__ void __launch_bounds__(256) idwt2_haar_pyramid_kernel(PyrOut in, float* __restrict__ out, long long planes, int H, int W) {
+    constexpr int B = 1 << LV;  // H, W: full-resolution output size
+    const int tw = W >> 3, th = H / B;
+    const long long total = planes * th * tw;
+    for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
+        const int cx = (int)(idx % tw);
+        const long long t = idx / tw;
+        const int by = (int)(t % th);
+        const long long pl = t / th;
+        float full[B][8];
+        constexpr int CL = 8 >> LV;  // coarse LL values per thread
+        float top[1][CL];
+        load_n<T, CL>((const T*)in.ll + pl * (H >> LV) * (W >> LV) + (long long)by * (W >> LV) + cx * CL, top[0]);
+        if constexpr (LV == 1) {
+            pyr_inv_level<T, T, 1, 4>(top, full, (const T*)in.hl[0], (const T*)in.lh[0], (const T*)in.hh[0], pl * (H / 2) * (W / 2), by, cx * 4, W / 2);
+        } else if constexpr (LV == 2) {
+            float m1[2][4];
+            pyr_inv_level<T, T, 1, 2>(top, m1, (const T*)in.hl[1], (const T*)in.lh[1], (const T*)in.hh[1], pl * (H / 4) * (W / 4), by, cx * 2, W / 4);
+            pyr_inv_level<T, float, 2, 4>(m1, full, (const T*)in.hl[0], (const T*)in.lh[0], (const T*)in.hh[0], pl * (H / 2) * (W / 2), by * 2, cx * 4, W / 2);
+        } else {
+            float m2[2][2], m1[4][4];
+            pyr_inv_level<T, T, 1, 1>(top, m2, (const T*)in.hl[2], (const T*)in.lh[2], (const T*)in.hh[2], pl * (H / 8) * (W / 8), by, cx, W / 8);
+            pyr_inv_level<T, float, 2, 2>(m2, m1, (const T*)in.hl[1], (const T*)in.lh[1], (const T*)in.hh[1], pl * (H / 4) * (W / 4), by * 2, cx * 2, W / 4);
+            pyr_inv_level<T, float, 4, 4>(m1, full, (const T*)in.hl[0], (const T*)in.lh[0], (const T*)in.hh[0], pl * (H / 2) * (W / 2), by * 4, cx * 4, W / 2);
+        }
+        float* dst = out + (pl * H + (long long)by * B) * W + cx * 8;
+#pragma unroll
+        for (int r = 0; r < B; ++r) {
+            *reinterpret_cast<float4*>(dst + (long long)r * W) = make_float4(full[r][0], full[r][1], full[r][2], full[r][3]);
+            *reinterpret_cast<float4*>(dst + (long long)r * W + 4) = make_float4(full[r][4], full[r][5], full[r][6], full[r][7]);
+        }
+    }
+}
+
 static int grid_for(long long total, int block) {
     long long need = (total + block - 1) / block;
     long long cap = (long long)hv_num_sms() * 8;  // 8 resident 256-thread CTAs per SM
@@ -207,6 +365,73 @@ extern "C" int hv_dwt2_haar(const void* x, void* ll, void* hl, void* lh, void* h
     if (dtype == HV_F32) return dwt_launch<float>(x, ll, hl, lh, hh, planes, H, W, hv_stream(stream));
     if (dtype == HV_BF16) return dwt_launch<__nv_bfloat16>(x, ll, hl, lh, hh, planes, H, W, hv_stream(stream));
     HV_REQUIRE(false, "hv_dwt2_haar: bad dtype %d", dtype);
+}
+
+template <typename T>
+static int pyramid_launch(const void* x, const PyrOut& o, int levels, int64_t planes, int H, int W, cudaStream_t st) {
+    const long long total = planes * (H >> levels) * (W >> 3);
+    const int grid = grid_for(total, 256);
+    if (levels == 1) dwt2_haar_pyramid_kernel<T, 1><<<grid, 256, 0, st>>>((const T*)x, o, planes, H, W);
+    else if (levels == 2) dwt2_haar_pyramid_kernel<T, 2><<<grid, 256, 0, st>>>((const T*)x, o, planes, H, W);
+    else dwt2_haar_pyramid_kernel<T, 3><<<grid, 256, 0, st>>>((const T*)x, o, planes, H, W);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+// levels in 1..3; hl/lh/hh: arrays of `levels` device pointers (level k: planes x H/2^(k+1) x W/2^(k+1)); ll: last level.
+// Needs H % 2^levels == 0, W % 8 == 0 and 16-byte aligned x (the caller falls back to per-level hv_dwt2_haar otherwise).
+extern "C" int hv_dwt2_haar_pyramid(const void* x, int levels, void* const* hl, void* const* lh, void* const* hh, void* ll,
+                                    int64_t planes, int H, int W, int dtype, void* stream) {
+    HV_REQUIRE(levels >= 1 && levels <= 3, "hv_dwt2_haar_pyramid: levels must be 1..3 (got %d)", levels);
+    HV_REQUIRE(planes >= 0 && H >= 0 && W >= 0, "hv_dwt2_haar_pyramid: negative size");
+    HV_REQUIRE(H % (1 << levels) == 0 && W % 8 == 0, "hv_dwt2_haar_pyramid: needs H %% 2^levels == 0 and W %% 8 == 0 (got %d x %d)", H, W);
+    HV_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "hv_dwt2_haar_pyramid: x must be 16-byte aligned");
+    HV_REQUIRE(dtype == HV_F32 || dtype == HV_BF16, "hv_dwt2_haar_pyramid: bad dtype %d", dtype);
+    if (planes == 0 || H == 0 || W == 0) return HV_OK;
+    PyrOut o;
+    for (int k = 0; k < 3; ++k) { o.hl[k] = k < levels ? hl[k] : nullptr; o.lh[k] = k < levels ? lh[k] : nullptr; o.hh[k] = k < levels ? hh[k] : nullptr; }
+    o.ll = ll;
+    const int es = dtype == HV_F32 ? 4 : 2;
+    for (int k = 0; k < levels; ++k) {  // store_n alignment: N = 4 >> k elements per store
+        const uintptr_t al = (uintptr_t)((4 >> k) * es - 1);
+        HV_REQUIRE(((reinterpret_cast<uintptr_t>(o.hl[k]) | reinterpret_cast<uintptr_t>(o.lh[k]) | reinterpret_cast<uintptr_t>(o.hh[k])) & al) == 0,
+                   "hv_dwt2_haar_pyramid: level %d bands are misaligned", k);
+    }
+    if (dtype == HV_F32) return pyramid_launch<float>(x, o, levels, planes, H, W, hv_stream(stream));
+    return pyramid_launch<__nv_bfloat16>(x, o, levels, planes, H, W, hv_stream(stream));
+}
+
+// inverse of hv_dwt2_haar_pyramid: H x W is the full-resolution OUTPUT size; out is fp32 (wavelet.py:40-41)
+extern "C" int hv_idwt2_haar_pyramid(const void* ll, int levels, const void* const* hl, const void* const* lh, const void* const* hh,
+                                     float* out, int64_t planes, int H, int W, int dtype, void* stream) {
+    HV_REQUIRE(levels >= 1 && levels <= 3, "hv_idwt2_haar_pyramid: levels must be 1..3 (got %d)", levels);
+    HV_REQUIRE(planes >= 0 && H >= 0 && W >= 0, "hv_idwt2_haar_pyramid: negative size");
+    HV_REQUIRE(H % (1 << levels) == 0 && W % 8 == 0, "hv_idwt2_haar_pyramid: needs H %% 2^levels == 0 and W %% 8 == 0 (got %d x %d)", H, W);
+    HV_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0, "hv_idwt2_haar_pyramid: out must be 16-byte aligned");
+    HV_REQUIRE(dtype == HV_F32 || dtype == HV_BF16, "hv_idwt2_haar_pyramid: bad dtype %d", dtype);
+    if (planes == 0 || H == 0 || W == 0) return HV_OK;
+    PyrOut o;
+    for (int k = 0; k < 3; ++k) {
+        o.hl[k] = k < levels ? const_cast<void*>(hl[k]) : nullptr; o.lh[k] = k < levels ? const_cast<void*>(lh[k]) : nullptr;
+        o.hh[k] = k < levels ? const_cast<void*>(hh[k]) : nullptr;
+    }
+    o.ll = const_cast<void*>(ll);
+    const int es = dtype == HV_F32 ? 4 : 2;
+    for (int k = 0; k < levels; ++k) {
+        const uintptr_t al = (uintptr_t)((4 >> k) * es - 1);
+        HV_REQUIRE(((reinterpret_cast<uintptr_t>(o.hl[k]) | reinterpret_cast<uintptr_t>(o.lh[k]) | reinterpret_cast<uintptr_t>(o.hh[k])) & al) == 0,
+                   "hv_idwt2_haar_pyramid: level %d bands are misaligned", k);
+    }
+    HV_REQUIRE((reinterpret_cast<uintptr_t>(ll) & (uintptr_t)((8 >> levels) * es - 1)) == 0, "hv_idwt2_haar_pyramid: ll is misaligned");
+    const long long total = planes * (H >> levels) * (W >> 3);
+    const int grid = grid_for(total, 256);
+    cudaStream_t st = hv_stream(stream);
+#define IPYR(T, L) idwt2_haar_pyramid_kernel<T, L><<<grid, 256, 0, st>>>(o, out, planes, H, W)
+    if (dtype == HV_F32) { if (levels == 1) IPYR(float, 1); else if (levels == 2) IPYR(float, 2); else IPYR(float, 3); }
+    else { if (levels == 1) IPYR(__nv_bfloat16, 1); else if (levels == 2) IPYR(__nv_bfloat16, 2); else IPYR(__nv_bfloat16, 3); }
+#undef IPYR
+    HV_LAUNCH_CHECK();
+    return HV_OK;
 }
 
 template <typename TL, typename TB>

@@ -103,6 +103,46 @@ def idwt2_haar(ll, hl, lh, hh):
     return out
 
 
+def _ptr_array(ts):
+    return (C.c_void_p * len(ts))(*[t.data_ptr() for t in ts])
+
+
+def pyramid_fusable(shape, levels):
+    """the fused pyramid kernels need 1..3 levels, H divisible by 2^levels and W by 8"""
+    H, W = shape[-2], shape[-1]
+    return 1 <= levels <= 3 and H % (1 << levels) == 0 and W % 8 == 0 and H > 0 and W > 0
+
+
+def dwt2_haar_pyramid(x, levels):
+    """fused `levels`-level analysis in one launch -> ([(HL, LH, HH) per level], LL of the last level)"""
+    _chk_cuda(x)
+    B, Cc, H, W = x.shape
+    mk = lambda k: torch.empty(B, Cc, H >> (k + 1), W >> (k + 1), dtype=x.dtype, device=x.device)
+    hl, lh, hh = [mk(k) for k in range(levels)], [mk(k) for k in range(levels)], [mk(k) for k in range(levels)]
+    ll = mk(levels - 1)
+    # algorithmic bytes of the per-level formulation (SURVEY 8d): read + write N * sum_k 4^-k
+    tok = _prof("dwt2_haar_pyramid", 0, 2 * x.numel() * x.element_size() * sum(4.0 ** -k for k in range(levels)))
+    _lib.check(_lib.load().hv_dwt2_haar_pyramid(_p(x), levels, _ptr_array(hl), _ptr_array(lh), _ptr_array(hh), _p(ll),
+                                                B * Cc, H, W, _dt(x), _stream()))
+    _prof_end(tok)
+    return list(zip(hl, lh, hh)), ll
+
+
+def idwt2_haar_pyramid(bands, ll):
+    """fused synthesis of a same-dtype pyramid (bands[k] = (HL, LH, HH) of level k, finest first) -> fp32 image"""
+    flat = [b for lv in bands for b in lv]
+    _chk_cuda(ll, *flat)
+    levels = len(bands)
+    B, Cc, h, w = ll.shape
+    H, W = h << levels, w << levels
+    out = torch.empty(B, Cc, H, W, dtype=torch.float32, device=ll.device)
+    tok = _prof("idwt2_haar_pyramid", 0, out.numel() * (ll.element_size() + 4) * sum(4.0 ** -k for k in range(levels)))
+    _lib.check(_lib.load().hv_idwt2_haar_pyramid(_p(ll), levels, _ptr_array([b[0] for b in bands]), _ptr_array([b[1] for b in bands]),
+                                                 _ptr_array([b[2] for b in bands]), _p(out), B * Cc, H, W, _dt(ll), _stream()))
+    _prof_end(tok)
+    return out
+
+
 def freq_split3d(x, ct, ch, cw):
     """x (..., T, H, W) fp32 -> (low, high) via the three circulant matrices."""
     _chk_cuda(x, ct, ch, cw)

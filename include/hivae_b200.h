@@ -55,6 +55,18 @@ int64_t hv_launch_count(void);
  * `planes` = B*C images of H x W (both even).  Outputs are planes x H/2 x W/2. */
 int hv_dwt2_haar(const void* x, void* ll, void* hl, void* lh, void* hh,
                  int64_t planes, int H, int W, int dtype, void* stream);
+/* Fused multi-level analysis: `levels` (1..3) applications of dwt_init to the running LL
+ * (the caller-side recursion of model/frenquence_wavelet.py:86-89) in ONE pass over x.
+ * hl/lh/hh: host arrays of `levels` device pointers (level k bands: planes x H/2^(k+1) x W/2^(k+1));
+ * ll: LL of the last level.  Bit-identical to `levels` calls of hv_dwt2_haar in both dtypes.
+ * Needs H % 2^levels == 0, W % 8 == 0, 16-byte aligned x. */
+int hv_dwt2_haar_pyramid(const void* x, int levels, void* const* hl, void* const* lh, void* const* hh, void* ll,
+                         int64_t planes, int H, int W, int dtype, void* stream);
+/* Fused multi-level synthesis, the inverse of hv_dwt2_haar_pyramid: `levels` applications of
+ * iwt_init starting from the coarsest LL.  H x W is the full-resolution OUTPUT size, out is fp32.
+ * Bit-identical to the per-level path (coarsest level in the band dtype, later levels in fp32). */
+int hv_idwt2_haar_pyramid(const void* ll, int levels, const void* const* hl, const void* const* lh, const void* const* hh,
+                          float* out, int64_t planes, int H, int W, int dtype, void* stream);
 /* model/wavelet.py:31-48 (iwt_init): inverse; the four sub-bands are the four
  * dim-0 quarters of the reference's input.  Output is ALWAYS fp32 (wavelet.py:40-41).
  * dtype_in = the dtype of all four bands, or dtype_ll | (dtype_bands + 1) << 8 when LL differs from the

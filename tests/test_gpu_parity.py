@@ -121,6 +121,31 @@ def test_bf16_pyramid_inverse_mixed_dtypes(dev, shape, levels):
     assert torch.equal(rec.cpu(), O.haar_pyramid_inverse(ob, oll))
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("shape,levels", [((2, 3, 16, 24), 1), ((17, 3, 256, 256), 2), ((3, 1, 64, 136), 3), ((2, 2, 20, 12), 2)])
+def test_fused_pyramid_equals_per_level(dev, dtype, shape, levels):
+    """one-launch pyramid kernels (hv_dwt2_haar_pyramid / hv_idwt2_haar_pyramid) are bit-identical to the per-level
+    recursion and to the oracle; the last shape (W % 8 != 0) exercises the per-level fallback of the wrapper"""
+    import hivae_b200 as hv
+    from hivae_b200 import ops
+    x = torch.randn(*shape, generator=_gen(5)).to(dtype)
+    xd = x.to(dev)
+    bands, ll = hv.dwt_pyramid(xd, levels)
+    pb, pll = [], xd
+    for _ in range(levels):
+        pll, a, b, c = ops.dwt2_haar(pll)
+        pb.append((a, b, c))
+    assert torch.equal(ll, pll) and all(torch.equal(u, v) for lu, lv in zip(bands, pb) for u, v in zip(lu, lv))
+    ob, oll = O.haar_pyramid(x, levels)
+    assert torch.equal(ll.cpu(), oll) and all(torch.equal(u.cpu(), v) for lu, lv in zip(bands, ob) for u, v in zip(lu, lv))
+    rec = hv.iwt_pyramid(bands, ll)
+    prec = ll
+    for hl, lh, hh in reversed(bands):
+        prec = ops.idwt2_haar(prec, hl, lh, hh)
+    assert rec.dtype == torch.float32 and torch.equal(rec, prec)
+    assert torch.equal(rec.cpu(), O.haar_pyramid_inverse(ob, oll))
+
+
 # =============================================================================== frequency split
 def test_freq_split_golden(dev, golden):
     import hivae_b200 as hv

@@ -25,18 +25,41 @@ def report(name, ms, nbytes=None, flops=None):
     if nbytes: s += " %8.1f GB/s" % (nbytes / ms / 1e6); res[name] = round(nbytes / ms / 1e6, 1)
     if flops: s += " %8.1f TFLOP/s" % (flops / ms / 1e9); res[name + "/tflops"] = round(flops / ms / 1e9, 1)
     print(s, flush=True)
-# ---- Haar pyramids (fp32 + bf16), 2-3 levels
-for (T, H, L) in ((17, 256, 2), (33, 256, 3), (17, 512, 2), (33, 512, 3)):
+def timeit_rotating(make_fn, nbytes_one, reps=5):
+    """kernel-level time of a short kernel: `copies` independent input sets totalling > 2x L2 are processed back to
+    back inside ONE CUDA graph (no host gaps, every call sees cold data); time per call = graph time / copies."""
+    copies = max(4, int(2 * 126e6 / max(nbytes_one, 1)) + 1)
+    copies = min(copies, 64)
+    fns = [make_fn(i) for i in range(copies)]
+    for f in fns: f()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for f in fns: f()
+    g.replay(); torch.cuda.synchronize()
+    tot = 0.0
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+        tot += e0.elapsed_time(e1)
+    return tot / reps / copies
+# ---- Haar pyramids (fp32 + bf16), 2-3 levels (BASELINE.json configs[3]); algorithmic bytes = SURVEY 8d formula
+for (T, H, L) in ((17, 256, 2), (33, 256, 3), (17, 384, 2), (33, 384, 3), (17, 512, 2), (33, 512, 3)):
     for dt in (torch.float32, torch.bfloat16):
-        x = torch.randn(T, 3, H, H, device=dev).to(dt)
-        es = x.element_size()
-        alg = 2 * x.numel() * es * sum(4.0 ** -k for k in range(L))
-        report("dwt_pyramid %s T=%d %dx%d L=%d" % (str(dt)[6:], T, H, H, L), timeit(lambda: hv.dwt_pyramid(x, L)), alg)
-        bands, ll = hv.dwt_pyramid(x, L)
-        alg_i = x.numel() * sum(4.0 ** -k for k in range(L)) * (es + 4)
-        report("iwt_pyramid %s T=%d %dx%d L=%d" % (str(dt)[6:], T, H, H, L), timeit(lambda: hv.iwt_pyramid(bands, ll)), alg_i)
-    x = torch.randn(T, 3, H, H, device=dev)
-    report("dwt single level fp32 T=%d %dx%d" % (T, H, H), timeit(lambda: hv.dwt_init(x)), 2 * x.numel() * 4)
+        es = 4 if dt == torch.float32 else 2
+        numel = T * 3 * H * H
+        geo = sum(4.0 ** -k for k in range(L))
+        xs = {}
+        def mk_fwd(i):
+            xs[i] = torch.randn(T, 3, H, H, device=dev).to(dt)
+            return lambda: hv.dwt_pyramid(xs[i], L)
+        report("dwt_pyramid %s T=%d %dx%d L=%d" % (str(dt)[6:], T, H, H, L), timeit_rotating(mk_fwd, numel * es), 2 * numel * es * geo)
+        pyr = {}
+        def mk_inv(i):
+            pyr[i] = hv.dwt_pyramid(xs[i % len(xs)], L)
+            return lambda: hv.iwt_pyramid(*pyr[i])
+        report("iwt_pyramid %s T=%d %dx%d L=%d" % (str(dt)[6:], T, H, H, L), timeit_rotating(mk_inv, numel * es), numel * geo * (es + 4))
+        del xs, pyr
 for n in (8, 32):
     x = torch.randn(n, 4, 32, 32, 32, device=dev)
     report("freq_split3d n=%d" % n, timeit(lambda: freq_split_gauss(x, 0.6, 0.6)), 3 * x.numel() * 4)
