@@ -16,5 +16,6 @@ from .transformer import (MotionEncoderLearnTokenTransformer, MotionEncoderLearn
                           AMDDiffusionTransformerModelImgSpatialTempMotion)
 from .model_AMD import AMDModel_New, AMD_N, AMD_models  # noqa: F401
 from . import sharding  # noqa: F401
+from . import optim  # noqa: F401
 
 __version__ = "0.1.0"

@@ -55,6 +55,11 @@ SIGNATURES = {
     "hv_rope": (_i, [_vp, _vp, _i64, _i, _i, _i, _i64, _i, _f, _vp]),
     "hv_linear_f32": (_i, [_vp, _i, _i64, _vp, _i64, _i64, _i, _i, C.POINTER(HvEpilogue), _vp]),
     "hv_linear_bf16": (_i, [_vp, _i64, _vp, _i64, _i64, _i, _i, C.POINTER(HvEpilogue), _vp]),
+    "hv_reduce_workspace_doubles": (_i, []),
+    "hv_mse_loss": (_i, [_vp, _vp, _i64, _vp, _vp, _vp]),
+    "hv_grad_norm_clip_coef": (_i, [_vp, _i64, _f, _f, _vp, _vp, _vp]),
+    "hv_adamw_clip": (_i, [_vp, _vp, _vp, _vp, _i64, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, _i64, _f, _vp, _vp]),
+    "hv_scale_by_device": (_i, [_vp, _i64, _vp, _f, _vp]),
     "hv_attention": (_i, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i, _i64, _i, _i, _i, _i,
                           C.POINTER(HvSeqMap), C.POINTER(HvSeqMap), _f, _vp, _vp]),
 }

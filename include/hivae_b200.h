@@ -204,6 +204,25 @@ int hv_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const v
                  void* out, int64_t ldo, int dtype, int64_t seqs, int heads, int hd, int Lq, int Lkv,
                  const HvSeqMap* qmap, const HvSeqMap* kvmap, float scale, const float* mask, void* stream);
 
+/* ------------------------------------------------------------------ train-step tail (train_amd.py:489-496)
+ * Flat fp32 arenas (parameters, gradients, AdamW moments), no host synchronisation.
+ * workspace: hv_reduce_workspace_doubles() fp64 values of device scratch. */
+int hv_reduce_workspace_doubles(void);
+/* out[0] = mean((pre-gt)^2): model/loss.py:13-14 (F.mse_loss), the diff_loss / rec_loss of model_AMD.py:1997-2000 */
+int hv_mse_loss(const float* pre, const float* gt, int64_t n, double* workspace, float* out, void* stream);
+/* out[0] = ||grad_scale*g||_2, out[1] = min(1, max_norm/(out[0]+1e-6)): torch.nn.utils.clip_grad_norm_
+ * behind accelerator.clip_grad_norm_ (train_amd.py:491-492).  out: 2 floats on the device. */
+int hv_grad_norm_clip_coef(const float* g, int64_t n, float grad_scale, float max_norm, double* workspace,
+                           float* out, void* stream);
+/* fused gradient clip + torch.optim.AdamW step `step` (1-based) (train_amd.py:255,494; defaults
+ * betas (0.9, 0.999), eps 1e-8, weight_decay 0.01), same fp32 operation order as torch's single-tensor path.
+ * g is read as grad_scale * clip_coef[0] * g (clip_coef may be NULL). 28 B/parameter of HBM traffic.
+ * Hyper-parameters are doubles: torch forms 1-beta, 1-lr*wd, lr/bias_correction in Python doubles and rounds once. */
+int hv_adamw_clip(float* p, const float* g, float* m, float* v, int64_t n, double lr, double beta1, double beta2,
+                  double eps, double weight_decay, int64_t step, float grad_scale, const float* clip_coef, void* stream);
+/* x *= coef[0] * extra: materialises the clip in the gradient arena (torch's observable in-place scaling) */
+int hv_scale_by_device(float* x, int64_t n, const float* coef, float extra, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -486,3 +486,60 @@ def test_kernels_ran_natively(dev):
     import hivae_b200 as hv
     hv.dwt_init(torch.randn(1, 1, 4, 4, device=dev))
     assert ops.launch_count() == n0 + 1
+
+
+# =============================================================================== train-step tail (train_amd.py:489-496)
+def _toy_params(seed, device):
+    g = _gen(seed)
+    shapes = [(64, 33), (129,), (7, 5, 3), (1,), (256, 256), (1000,)]  # ragged sizes: padded arena offsets, tails
+    return [torch.nn.Parameter(torch.randn(*s, generator=g).to(device)) for s in shapes]
+
+
+@pytest.mark.parametrize("max_norm", [1.0, 1e9])
+def test_adamw_clip_matches_torch(dev, max_norm):
+    """fused clip + AdamW over a flat arena vs torch.nn.utils.clip_grad_norm_ + torch.optim.AdamW (CPU fp32),
+    4 steps with fresh gradients each step; max_norm=1e9 exercises the coef-clamped-to-1 branch"""
+    from hivae_b200 import optim
+    ref = _toy_params(3, "cpu")
+    ours = [torch.nn.Parameter(p.detach().clone().to(dev)) for p in ref]
+    topt = torch.optim.AdamW(ref, lr=1e-2)  # reference defaults: betas (0.9, 0.999), eps 1e-8, weight_decay 0.01
+    arena = optim.FlatArena(ours)
+    opt = optim.AdamW(arena, lr=1e-2)
+    assert all(p.data_ptr() >= arena.flat.data_ptr() for p in ours)
+    g = _gen(4)
+    for step in range(4):
+        grads = [torch.randn(*p.shape, generator=g) * (3.0 if step % 2 else 0.01) for p in ref]
+        for p, q, gr in zip(ref, ours, grads):
+            p.grad = gr.clone()
+            q.grad.copy_(gr.to(dev))
+        tn = torch.nn.utils.clip_grad_norm_(ref, max_norm)
+        topt.step()
+        norm = optim.clip_grad_norm_(arena, max_norm)
+        opt.step()
+        assert abs(float(norm) - float(tn)) <= 1e-6 * float(tn)
+        for p, q in zip(ref, ours):
+            assert rel(q.data, p.data) <= 2e-6
+    for p, st in zip(ref, arena.offsets):
+        assert rel(opt.exp_avg[st:st + p.numel()].view_as(p), topt.state[p]["exp_avg"]) <= 2e-6
+        assert rel(opt.exp_avg_sq[st:st + p.numel()].view_as(p), topt.state[p]["exp_avg_sq"]) <= 2e-6
+
+
+def test_clip_materialize_and_mse(dev):
+    from hivae_b200 import optim
+    ref = _toy_params(8, "cpu")
+    ours = [torch.nn.Parameter(p.detach().clone().to(dev)) for p in ref]
+    arena = optim.FlatArena(ours)
+    g = _gen(9)
+    for p, q in zip(ref, ours):
+        gr = torch.randn(*p.shape, generator=g)
+        p.grad = gr.clone()
+        q.grad.copy_(gr.to(dev))
+    tn = torch.nn.utils.clip_grad_norm_(ref, 0.5)
+    norm = optim.clip_grad_norm_(arena, 0.5, materialize=True)
+    assert abs(float(norm) - float(tn)) <= 1e-6 * float(tn) and arena.clip is None
+    for p, q in zip(ref, ours):
+        assert rel(q.grad, p.grad) <= 1e-6
+    a, b = torch.randn(8 * 16, 4, 32, 32, generator=g), torch.randn(8 * 16, 4, 32, 32, generator=g)
+    assert abs(float(optim.mse_loss(a.to(dev), b.to(dev))) - float(torch.nn.functional.mse_loss(a, b))) <= 1e-6
+    a, b = torch.randn(1003, generator=g), torch.randn(1003, generator=g)  # ragged tail
+    assert abs(float(optim.mse_loss(a.to(dev), b.to(dev))) - float(torch.nn.functional.mse_loss(a, b))) <= 1e-6

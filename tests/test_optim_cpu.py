@@ -1,0 +1,76 @@
+"""CPU tier of the train-step tail: flat-arena aliasing, bucket layout, and the world_size-2 gloo path of the
+gradient all-reduce (host logic only; the kernels themselves are covered by the gpu tier)."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from hivae_b200 import optim
+
+
+def _params(seed):
+    g = torch.Generator().manual_seed(seed)
+    return [torch.nn.Parameter(torch.randn(*s, generator=g)) for s in [(5, 3), (7,), (2, 2, 2), (1,)]]
+
+
+def test_flat_arena_views_alias_and_keep_values():
+    ps = _params(0)
+    before = [p.detach().clone() for p in ps]
+    arena = optim.FlatArena(ps)
+    assert arena.numel == 16 + 8 + 8 + 4 and all(o % 4 == 0 for o in arena.offsets)  # 16-byte aligned starts
+    for p, b, o in zip(ps, before, arena.offsets):
+        assert torch.equal(p.data, b)
+        assert p.data.data_ptr() == arena.flat.data_ptr() + 4 * o and p.grad.data_ptr() == arena.grad.data_ptr() + 4 * o
+    arena.flat.add_(1.0)
+    assert all(torch.equal(p.data, b + 1.0) for p, b in zip(ps, before))
+    (ps[0].sum() * 2.0 + ps[1].sum()).backward()  # autograd accumulates into the arena views in place
+    assert float(arena.grad[:15].min()) == 2.0 and float(arena.grad[16:23].max()) == 1.0 and float(arena.grad[15]) == 0.0
+    arena.zero_grad()
+    assert float(arena.grad.abs().max()) == 0.0
+
+
+def test_bucket_layout_covers_arena_once():
+    arena = optim.FlatArena([torch.nn.Parameter(torch.zeros(1000)), torch.nn.Parameter(torch.zeros(37))])
+    r = optim.GradAllReducer(arena, bucket_mb=1e-3)  # ~262 elements per bucket
+    assert r.buckets[0][0] == 0 and r.buckets[-1][1] == arena.numel
+    assert all(a[1] == b[0] for a, b in zip(r.buckets, r.buckets[1:])) and len(r.buckets) > 2
+    assert r.all_reduce() == 1.0  # no process group: single replica
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    arena = optim.FlatArena(_params(1))  # same init on every rank (set_seed is rank-independent, train_amd.py:154)
+    for i, p in enumerate(arena.params):
+        p.grad.fill_(float(rank + 1) * (i + 1))
+    scale = optim.GradAllReducer(arena, bucket_mb=4e-5).all_reduce()  # ~10 elements per bucket
+    mean = [float((p.grad * scale).flatten()[0]) for p in arena.params]
+    q.put((rank, scale, mean))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_gradient_all_reduce_mean():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for _rank, scale, mean in res:
+        assert scale == 0.5                      # gloo: SUM, the 1/world is folded into the clip / AdamW kernels
+        assert mean == [1.5, 3.0, 4.5, 6.0]      # mean over ranks of (rank+1)*(i+1)
