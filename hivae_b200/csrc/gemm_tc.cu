@@ -101,6 +101,32 @@ __device__ __forceinline__ void epi_block_reduce(const HvEpiDev& d, const CUtens
     }
 }
 
+// bf16 output block of 32 rows x 64 columns through a TMA store: every thread packs the 64 columns of its row
+// (128 B) into the warp's staging tile in the 128 B swizzle layout (conflict-free 16-byte writes), one lane
+// issues cp.async.bulk.tensor.  No shared-memory read-back and no per-lane global stores; rows >= M and
+// columns >= N are clipped by the tensor map.
+__device__ __forceinline__ void epi_block_tma_store(const CUtensorMap* tmap_c, float* stage, int lane, long long row0,
+                                                    int col0, const float (&lo)[32], const float (&hi)[32]) {
+    if (lane == 0) tc::bulk_wait_read0();  // the previous store has finished reading the staging tile
+    __syncwarp();
+    uint8_t* rowp = reinterpret_cast<uint8_t*>(stage) + lane * 128;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        *reinterpret_cast<uint4*>(rowp + ((k ^ (lane & 7)) << 4)) =
+            make_uint4(hv_pack_bf16(lo[8 * k], lo[8 * k + 1]), hv_pack_bf16(lo[8 * k + 2], lo[8 * k + 3]),
+                       hv_pack_bf16(lo[8 * k + 4], lo[8 * k + 5]), hv_pack_bf16(lo[8 * k + 6], lo[8 * k + 7]));
+        *reinterpret_cast<uint4*>(rowp + (((k + 4) ^ (lane & 7)) << 4)) =
+            make_uint4(hv_pack_bf16(hi[8 * k], hi[8 * k + 1]), hv_pack_bf16(hi[8 * k + 2], hi[8 * k + 3]),
+                       hv_pack_bf16(hi[8 * k + 4], hi[8 * k + 5]), hv_pack_bf16(hi[8 * k + 6], hi[8 * k + 7]));
+    }
+    tc::fence_proxy_async();
+    __syncwarp();
+    if (lane == 0) {
+        tc::tma_store_2d(tmap_c, stage, col0, (int)row0);
+        tc::bulk_commit();
+    }
+}
+
 template <int MODE>
 __device__ __forceinline__ void epi_block_out(const HvEpiDev& d, float* stage, int lane, long long row0, long long M,
                                               int col0, int N, const float (&acc)[32], long long res_off, long long gate_off) {
@@ -218,7 +244,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (threadIdx.x == 0) {
         tc::prefetch_tmap(&tmap_a);
         tc::prefetch_tmap(&tmap_b);
-        if (MODE == HV_EPI_RESIDUAL && use_reduce) tc::prefetch_tmap(&tmap_r);
+        if (use_reduce) tc::prefetch_tmap(&tmap_r);
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
 #pragma unroll
@@ -292,6 +318,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         float* stage = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES) + ew * staging_floats_per_warp<MODE>();
         const HvEpilogue& e = epi.e;
         const bool reduce = MODE == HV_EPI_RESIDUAL && use_reduce;
+        const bool tma_store = MODE != HV_EPI_RESIDUAL && use_reduce;  // tmap_r is then the bf16 OUTPUT map (box 64 x 32)
         if (MODE == HV_EPI_RESIDUAL) {  // the zero rows behind the tile
 #pragma unroll
             for (int k = 0; k < 8; ++k) reinterpret_cast<float4*>(stage + 32 * 32)[k * 32 + lane] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -352,8 +379,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             hi[j] = (hi[j] - mean) * rstd * __ldg(w + 32 + j) + __ldg(b + 32 + j);
                         }
                     }
-                    epi_block_out<MODE>(epi, stage, lane, row0, M, col0, N, lo, 0, 0);
-                    epi_block_out<MODE>(epi, stage, lane, row0, M, col0 + 32, N, hi, 0, 0);
+                    if (tma_store) {
+                        epi_block_tma_store(&tmap_r, stage, lane, row0, col0, lo, hi);
+                    } else {
+                        epi_block_out<MODE>(epi, stage, lane, row0, M, col0, N, lo, 0, 0);
+                        epi_block_out<MODE>(epi, stage, lane, row0, M, col0 + 32, N, hi, 0, 0);
+                    }
+                }
+            } else if (tma_store) {  // STORE / GELU with a bf16 output: 64 columns per TMA store
+#pragma unroll 1
+                for (int c = 0; c < HALF; c += 64) {
+                    const int col0 = n0 + c;
+                    if (col0 >= N) break;  // warp-uniform
+                    float lo[32], hi[32];
+                    tc::tmem_ld32(taddr + c, lo);
+                    tc::tmem_ld32(taddr + c + 32, hi);
+                    epi_add_bias(epi, col0, N, lo);
+                    epi_add_bias(epi, col0 + 32, N, hi);
+                    if (MODE == HV_EPI_GELU) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) { lo[j] = gelu_tanh_fast(lo[j]); hi[j] = gelu_tanh_fast(hi[j]); }
+                    }
+                    epi_block_tma_store(&tmap_r, stage, lane, row0, col0, lo, hi);
                 }
             } else {
 #pragma unroll 1
@@ -384,7 +431,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
             if ((a ^= 1) == 0) aph ^= 1;
         }
-        if (reduce && lane == 0) tc::bulk_wait0();  // every reduce of this warp has landed before the CTA retires
+        if ((reduce || tma_store) && lane == 0) tc::bulk_wait0();  // every bulk store / reduce of this warp has landed before the CTA retires
     }
     tc::fence_before_sync();
     if (CTAS == 2) tc::cluster_sync(); else __syncthreads();
@@ -562,7 +609,8 @@ extern "C" int hv_linear_bf16(const void* A, int64_t lda, const void* W, int64_t
     int rc = hv_epilogue_prepare(epi, M, N, d, "hv_linear_bf16");
     if (rc) return rc;
     if (M == 0) return HV_OK;
-    static const int want_ctas = env_int("HV_GEMM_CTAS", 2), want_reduce = env_int("HV_GEMM_REDUCE", 1);
+    static const int want_ctas = env_int("HV_GEMM_CTAS", 2), want_reduce = env_int("HV_GEMM_REDUCE", 1),
+                     want_tma_store = env_int("HV_GEMM_TMA_STORE", 1);
     const int BN = N > 128 ? 256 : 128;
     // a CTA pair pays off once there are enough 256 x 256 tiles to occupy the pairs
     const int ctas = (want_ctas == 2 && N > 128 && M > 256) ? 2 : 1;
@@ -572,6 +620,10 @@ extern "C" int hv_linear_bf16(const void* A, int64_t lda, const void* W, int64_t
     int use_reduce = 0;
     if (d.e.mode == HV_EPI_RESIDUAL && want_reduce && d.vec_ok && d.e.L >= 32) {
         if ((rc = make_tmap_residual(d.e.res, N, d.e.L, M / d.e.L, d.e.frame_rows, d.e.row_off, &tr)) != HV_OK) return rc;
+        use_reduce = 1;
+    } else if (d.e.mode != HV_EPI_RESIDUAL && want_tma_store && d.vec_ok && d.e.out_dtype == HV_BF16 && BN == 256) {
+        // bf16 outputs leave through TMA stores: 64-column x 32-row boxes of the output matrix (128 B swizzle)
+        if ((rc = hv_make_tmap_bf16(d.e.out, M, N, d.e.ldo, 32, &tr)) != HV_OK) return rc;
         use_reduce = 1;
     } else {
         tr = ta;  // unused
