@@ -67,6 +67,125 @@ __global__ void __launch_bounds__(256) ln_modulate_kernel(
         }
 }
 
+// Two rows per warp, 16 consecutive rows per CTA.  The LayerNorm affine and the adaLN shift / scale of a CTA's rows
+// almost always come from ONE (frame, segment) pair; the CTA then folds them once into A = w (1 + scale),
+// B = b (1 + scale) + shift in shared memory and every row is y = xhat * A + B: 8 KB of parameter reads per CTA
+// instead of 16 KB per row through L1 (x itself is only 4 KB per row).  CTAs that straddle a frame / segment
+// boundary (about 1 in 8) take the unfolded path with the reference's operation order.
+template <int NV, typename OutT>
+__global__ void __launch_bounds__(256, 2) ln_modulate2_kernel(
+    const float* __restrict__ res, long long rows, HvRowMap map, int D,
+    const float* __restrict__ ln_w, const float* __restrict__ ln_b, float eps,
+    const float* __restrict__ ada, long long ada_ld, int shift_col_mot, int scale_col_mot,
+    int shift_col_img, int scale_col_img, int img_start, int img_len, int cond_div, int cond_mul,
+    OutT* __restrict__ out) {
+    __shared__ float4 sA[NV * 32], sB[NV * 32];
+    const int lane = threadIdx.x & 31;
+    const long long rb = blockIdx.x * 16ll;                       // first row of the CTA
+    const long long r0 = rb + 2 * (threadIdx.x >> 5);
+    const bool valid = r0 < rows, two = r0 + 1 < rows;
+    auto params = [&](long long r, const float4*& sh, const float4*& sc) {
+        int f, a;
+        map.res_row(r, f, a);
+        const bool img = (a >= img_start) && (a < img_start + img_len);
+        const float* rowp = ada + (long long)((f / cond_div) * cond_mul) * ada_ld;
+        sh = reinterpret_cast<const float4*>(rowp + (img ? shift_col_img : shift_col_mot));
+        sc = reinterpret_cast<const float4*>(rowp + (img ? scale_col_img : scale_col_mot));
+    };
+    const float4* wp = reinterpret_cast<const float4*>(ln_w);
+    const float4* bp = reinterpret_cast<const float4*>(ln_b);
+    // ---- CTA-uniform: do all rows of this CTA share one parameter set?
+    bool folded = true;  // plain LayerNorm: A = w, B = b
+    const float4 *shf = nullptr, *scf = nullptr;
+    if (ada != nullptr) {
+        const long long rl = rb + 15 < rows ? rb + 15 : rows - 1;
+        const float4 *shl, *scl;
+        params(rb, shf, scf);
+        params(rl, shl, scl);
+        folded = shf == shl && scf == scl;
+    }
+    {
+        if (folded) {
+            for (int c4 = threadIdx.x; c4 < NV * 32; c4 += 256) {
+                const float4 w = wp ? __ldg(wp + c4) : make_float4(1.f, 1.f, 1.f, 1.f);
+                const float4 b = bp ? __ldg(bp + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 s = scf ? __ldg(scf + c4) : make_float4(0.f, 0.f, 0.f, 0.f), t = shf ? __ldg(shf + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+                sA[c4] = make_float4(w.x * (1.f + s.x), w.y * (1.f + s.y), w.z * (1.f + s.z), w.w * (1.f + s.w));
+                sB[c4] = make_float4(fmaf(b.x, 1.f + s.x, t.x), fmaf(b.y, 1.f + s.y, t.y), fmaf(b.z, 1.f + s.z, t.z), fmaf(b.w, 1.f + s.w, t.w));
+            }
+        }
+    }
+    float4 u[NV], v[NV];
+    if (valid) {
+        int f, a;
+        const float4* x0 = reinterpret_cast<const float4*>(res + map.res_row(r0, f, a) * D);
+        const float4* x1 = two ? reinterpret_cast<const float4*>(res + map.res_row(r0 + 1, f, a) * D) : x0;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) { u[j] = x0[j * 32 + lane]; v[j] = x1[j * 32 + lane]; }
+    } else {
+#pragma unroll
+        for (int j = 0; j < NV; ++j) u[j] = v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const float inv_d = 1.0f / (float)D;
+    float su = 0.f, sv = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) { su += (u[j].x + u[j].y) + (u[j].z + u[j].w); sv += (v[j].x + v[j].y) + (v[j].z + v[j].w); }
+    const float mu = hv_warp_sum(su) * inv_d, mv = hv_warp_sum(sv) * inv_d;
+    float qu = 0.f, qv = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        float a = u[j].x - mu, b = u[j].y - mu, c = u[j].z - mu, d = u[j].w - mu;
+        qu += (a * a + b * b) + (c * c + d * d);
+        a = v[j].x - mv; b = v[j].y - mv; c = v[j].z - mv; d = v[j].w - mv;
+        qv += (a * a + b * b) + (c * c + d * d);
+    }
+    const float ru = rsqrtf(hv_warp_sum(qu) * inv_d + eps), rv = rsqrtf(hv_warp_sum(qv) * inv_d + eps);
+    __syncthreads();  // sA / sB complete (every thread of the CTA reaches this point)
+    if (!valid) return;
+    auto emit = [&](OutT* o, int c4, float4 y) {
+        if constexpr (sizeof(OutT) == 4) reinterpret_cast<float4*>(o)[c4] = y;
+        else reinterpret_cast<uint2*>(o)[c4] = make_uint2(hv_pack_bf16(y.x, y.y), hv_pack_bf16(y.z, y.w));
+    };
+    if (folded) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            const int c4 = j * 32 + lane;
+            const float4 A = sA[c4], B = sB[c4];
+            float4 y, z;
+            y.x = fmaf((u[j].x - mu) * ru, A.x, B.x); y.y = fmaf((u[j].y - mu) * ru, A.y, B.y);
+            y.z = fmaf((u[j].z - mu) * ru, A.z, B.z); y.w = fmaf((u[j].w - mu) * ru, A.w, B.w);
+            z.x = fmaf((v[j].x - mv) * rv, A.x, B.x); z.y = fmaf((v[j].y - mv) * rv, A.y, B.y);
+            z.z = fmaf((v[j].z - mv) * rv, A.z, B.z); z.w = fmaf((v[j].w - mv) * rv, A.w, B.w);
+            emit(out + r0 * D, c4, y);
+            if (two) emit(out + (r0 + 1) * D, c4, z);
+        }
+        return;
+    }
+    const float4 *sh0 = nullptr, *sc0 = nullptr, *sh1 = nullptr, *sc1 = nullptr;
+    if (ada != nullptr) {
+        params(r0, sh0, sc0);
+        params(two ? r0 + 1 : r0, sh1, sc1);
+    }
+    const bool same = sh0 == sh1 && sc0 == sc1;  // warp-uniform
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        const int c4 = j * 32 + lane;
+        float4 y, z;
+        y.x = (u[j].x - mu) * ru; y.y = (u[j].y - mu) * ru; y.z = (u[j].z - mu) * ru; y.w = (u[j].w - mu) * ru;
+        z.x = (v[j].x - mv) * rv; z.y = (v[j].y - mv) * rv; z.z = (v[j].z - mv) * rv; z.w = (v[j].w - mv) * rv;
+        if (wp) { const float4 w = __ldg(wp + c4); y.x *= w.x; y.y *= w.y; y.z *= w.z; y.w *= w.w; z.x *= w.x; z.y *= w.y; z.z *= w.z; z.w *= w.w; }
+        if (bp) { const float4 b = __ldg(bp + c4); y.x += b.x; y.y += b.y; y.z += b.z; y.w += b.w; z.x += b.x; z.y += b.y; z.z += b.z; z.w += b.w; }
+        if (sh0) {
+            float4 s = __ldg(sc0 + c4), t = __ldg(sh0 + c4);
+            y.x = y.x * (1.f + s.x) + t.x; y.y = y.y * (1.f + s.y) + t.y; y.z = y.z * (1.f + s.z) + t.z; y.w = y.w * (1.f + s.w) + t.w;
+            if (!same) { s = __ldg(sc1 + c4); t = __ldg(sh1 + c4); }
+            z.x = z.x * (1.f + s.x) + t.x; z.y = z.y * (1.f + s.y) + t.y; z.z = z.z * (1.f + s.z) + t.z; z.w = z.w * (1.f + s.w) + t.w;
+        }
+        emit(out + r0 * D, c4, y);
+        if (two) emit(out + (r0 + 1) * D, c4, z);
+    }
+}
+
 extern "C" int hv_ln_modulate(const float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D,
                               const float* ln_w, const float* ln_b, float eps,
                               const float* ada, int64_t ada_ld, int shift_col_mot, int scale_col_mot,
@@ -84,8 +203,17 @@ extern "C" int hv_ln_modulate(const float* res, int64_t frames, int64_t frame_ro
     if (rows == 0) return HV_OK;
     HvRowMap map{L, (long long)frame_rows, row_off};
     const int nv = D / 128;
-    dim3 grid((unsigned)((rows + 7) / 8)), block(256);
     cudaStream_t st = hv_stream(stream);
+#define LN_ARGS res, rows, map, D, ln_w, ln_b, eps, ada, ada_ld, shift_col_mot, scale_col_mot, shift_col_img, scale_col_img, \
+                img_start, img_len, cond_div, cond_mul
+    if (nv == 8 || nv == 4) {  // D = 1024 / 512 (the DiT and the encoders): two rows per warp
+        dim3 grid((unsigned)((rows + 15) / 16)), block(256);
+        if (out_dtype == HV_F32) { if (nv == 8) ln_modulate2_kernel<8, float><<<grid, block, 0, st>>>(LN_ARGS, (float*)out); else ln_modulate2_kernel<4, float><<<grid, block, 0, st>>>(LN_ARGS, (float*)out); }
+        else { if (nv == 8) ln_modulate2_kernel<8, __nv_bfloat16><<<grid, block, 0, st>>>(LN_ARGS, (__nv_bfloat16*)out); else ln_modulate2_kernel<4, __nv_bfloat16><<<grid, block, 0, st>>>(LN_ARGS, (__nv_bfloat16*)out); }
+        HV_LAUNCH_CHECK();
+        return HV_OK;
+    }
+    dim3 grid((unsigned)((rows + 7) / 8)), block(256);
 #define LN_LAUNCH(MAXNV, T)                                                                                   \
     ln_modulate_kernel<MAXNV, T><<<grid, block, 0, st>>>(res, rows, map, D, ln_w, ln_b, eps, ada, ada_ld,     \
         shift_col_mot, scale_col_mot, shift_col_img, scale_col_img, img_start, img_len, cond_div, cond_mul, (T*)out)
