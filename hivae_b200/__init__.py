@@ -13,7 +13,7 @@ from .rectified_flow import RectifiedFlow  # noqa: F401
 from .modules import (BasicTransformerBlock, BasicCrossTransformerBlock, AMDTransformerBlock, BasicDiTBlock,  # noqa: F401
                       PatchEmbed, AMDLayerNormZero, AMDLayerNormZero_OneVariable, AdaLayerNorm)
 from .transformer import (MotionEncoderLearnTokenTransformer, MotionEncoderLearnTokenOnlyTemporalTransformer,  # noqa: F401
-                          AMDDiffusionTransformerModelImgSpatialTempMotion)
+                          AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion)
 from .model_AMD import AMDModel_New, AMD_N, AMD_models  # noqa: F401
 from . import sharding  # noqa: F401
 from . import optim  # noqa: F401

@@ -15,4 +15,7 @@ DEFAULT = dict(
 SMALL = dict(DEFAULT, object_enc_num_layers=2, camera_enc_num_layers=2, enc_nhead=2,
              diffusion_attn_num_heads=4, diffusion_num_layers=2)
 
-CONFIGS = {"default": DEFAULT, "small": SMALL}
+# diffusion_model_type='default' (AMDDiffusionTransformerModelTempMotion): object stream only
+SMALL_OBJECT_ONLY = dict(SMALL, use_camera=False, diffusion_model_type="default")
+
+CONFIGS = {"default": DEFAULT, "small": SMALL, "small_object_only": SMALL_OBJECT_ONLY}

@@ -29,6 +29,37 @@ __global__ void __launch_bounds__(256) patch_embed_kernel(
         xs[idx] = v;
     }
     __syncthreads();
+    if (K == 32 || K == 16) {
+        // the DiT (K = 8 ch x 2 x 2) and encoder (K = 4 ch x 2 x 2) patch sizes: the thread keeps its weight row in
+        // registers and streams the tokens with 16-byte broadcast reads (4x fewer shared-memory instructions)
+        for (int d = threadIdx.x; d < D; d += blockDim.x) {
+            float4 wk[8];
+            const float4* wr4 = reinterpret_cast<const float4*>(w + (long long)d * K);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) wk[k] = (4 * k < K) ? __ldg(wr4 + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float b = bias ? bias[d] : 0.f;
+#pragma unroll 4
+            for (int t = 0; t < TOK; ++t) {
+                const long long tok = tok0 + t;
+                if (tok >= ntok) break;
+                const float4* x4 = reinterpret_cast<const float4*>(xs + t * K);
+                float acc = 0.f;
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (4 * k < K) {
+                        const float4 xv = x4[k];
+                        acc = fmaf(wk[k].x, xv.x, acc); acc = fmaf(wk[k].y, xv.y, acc); acc = fmaf(wk[k].z, xv.z, acc); acc = fmaf(wk[k].w, xv.w, acc);
+                    }
+                const long long f = tok / S;
+                const int s = (int)(tok - f * S);
+                float v = acc + b;
+                if (pos) v += pos[(long long)s * D + d];
+                if (tpos) v += tpos[(long long)(f % Tmod) * D + d];
+                hv_st(out + (f * frame_rows + row_off + s) * D + d, v);
+            }
+        }
+        return;
+    }
     for (int d = threadIdx.x; d < D; d += blockDim.x) {
         float acc[TOK];
 #pragma unroll

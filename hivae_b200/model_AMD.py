@@ -17,8 +17,8 @@ from torch import nn
 from . import engine, ops
 from .frequency_utils import freq_split_gauss
 from .rectified_flow import RectifiedFlow
-from .transformer import (AMDDiffusionTransformerModelImgSpatialTempMotion, MotionEncoderLearnTokenOnlyTemporalTransformer,
-                          MotionEncoderLearnTokenTransformer)
+from .transformer import (AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion,
+                          MotionEncoderLearnTokenOnlyTemporalTransformer, MotionEncoderLearnTokenTransformer)
 
 
 def l2(pre, gt):
@@ -76,8 +76,12 @@ class AMDModel_New(_ConfigModel):
                  motion_patch_size=1, motion_drop_ratio=0.0, extract_motion_with_motion_transformer=False, **kwargs):
         super().__init__()
         self._register(locals())
-        if diffusion_model_type != "spatial":
-            raise NotImplementedError("hivae_b200 implements diffusion_model_type='spatial' (the shipped AMD_N recipe)")
+        if diffusion_model_type not in ("spatial", "default"):
+            raise IndexError(diffusion_model_type)  # model_AMD.py:1841-1842
+        if diffusion_model_type == "default" and (use_camera or not use_object):
+            # the reference's 'default' denoiser takes no camera stream (its forward has no such argument,
+            # transformer.py:1631-1640) and dereferences the object tokens unconditionally (1656)
+            raise NotImplementedError("diffusion_model_type='default' needs use_camera=False, use_object=True")
         if use_grey or need_motion_transformer or use_regularizers:
             raise NotImplementedError("use_grey / need_motion_transformer / use_regularizers are outside the hot path")
         self.num_step = scheduler_num_step
@@ -108,7 +112,8 @@ class AMDModel_New(_ConfigModel):
                 nn.Conv2d(in_channels=4, out_channels=16, kernel_size=3, stride=2, padding=1),
                 nn.Conv2d(in_channels=16, out_channels=4, kernel_size=3, stride=1, padding=1),
                 nn.MaxPool2d(kernel_size=2, stride=2, padding=0))
-        self.diffusion_transformer = AMDDiffusionTransformerModelImgSpatialTempMotion(
+        dit_cls = AMDDiffusionTransformerModelImgSpatialTempMotion if diffusion_model_type == "spatial" else AMDDiffusionTransformerModelTempMotion
+        self.diffusion_transformer = dit_cls(
             num_attention_heads=diffusion_attn_num_heads, attention_head_dim=diffusion_attn_head_dim,
             out_channels=diffusion_out_channels, num_layers=diffusion_num_layers, use_camera=use_camera,
             use_object=use_object, image_width=image_width, image_height=image_height, image_patch_size=image_patch_size,
@@ -185,8 +190,8 @@ class AMDModel_New(_ConfigModel):
         zi, zj = ref_img.flatten(0, 1).float().contiguous(), video.flatten(0, 1).float().contiguous()
         if time_step is None:
             time_step = self.prepare_timestep(batch_size=zj.shape[0], device=device)
-        # 'spatial' mode redraws one step per clip (model_AMD.py:1962-1964)
-        time_step = self.prepare_timestep(batch_size=n, device=device).repeat_interleave(t)
+        if self.diffusion_model_type != "default":  # 'spatial' mode redraws one step per clip (model_AMD.py:1962-1964)
+            time_step = self.prepare_timestep(batch_size=n, device=device).repeat_interleave(t)
         zt, vel = self.scheduler.get_train_tuple(z1=zj, time_step=time_step)
         zt = zt.contiguous()
         pre = self._dit(zi, zt, time_step.float(), cam, osrc, otgt)

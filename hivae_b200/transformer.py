@@ -231,6 +231,7 @@ class AMDDiffusionTransformerModelImgSpatialTempMotion(_HvModule):
     (image + object tokens), a camera joint block (image + camera tokens) and a temporal block."""
 
     _supports_gradient_checkpointing = True
+    _has_temporal_blocks = True
 
     def __init__(self, num_attention_heads=20, attention_head_dim=64, out_channels: Optional[int] = 4, num_layers=12,
                  use_camera=False, use_object=False, image_width=32, image_height=32, image_patch_size=2,
@@ -266,7 +267,8 @@ class AMDDiffusionTransformerModelImgSpatialTempMotion(_HvModule):
             self.target_token = nn.Parameter(torch.zeros(1, 1, hidden_dim), requires_grad=True)
             self.object_motion_patch_embed = nn.Linear(object_motion_in_channels, hidden_dim)
             self.object_transformer_blocks = nn.ModuleList([AMDTransformerBlock(**blk) for _ in range(num_layers)])
-        self.spatial_blocks = nn.ModuleList([BasicDiTBlock(**blk) for _ in range(num_layers)])
+        if self._has_temporal_blocks:
+            self.spatial_blocks = nn.ModuleList([BasicDiTBlock(**blk) for _ in range(num_layers)])
         self.norm_final = nn.LayerNorm(hidden_dim, norm_eps, norm_elementwise_affine)
         self.norm_out = AdaLayerNorm(embedding_dim=time_embed_dim, output_dim=2 * hidden_dim,
                                      norm_elementwise_affine=norm_elementwise_affine, norm_eps=norm_eps, chunk_dim=1)
@@ -276,10 +278,10 @@ class AMDDiffusionTransformerModelImgSpatialTempMotion(_HvModule):
     def _prepare(self, ctx):
         P = _Prepared()
         P.ctx = ctx
-        n = len(self.spatial_blocks)
+        n = len(self.spatial_blocks) if self._has_temporal_blocks else len(self.object_transformer_blocks)
         P.obj = [engine.prepare_block(ctx, b, "joint") for b in self.object_transformer_blocks] if self.use_object else [None] * n
         P.cam = [engine.prepare_block(ctx, b, "joint") for b in self.camera_transformer_blocks] if self.use_camera else [None] * n
-        P.sp = [engine.prepare_block(ctx, b, "dit") for b in self.spatial_blocks]
+        P.sp = [engine.prepare_block(ctx, b, "dit") for b in self.spatial_blocks] if self._has_temporal_blocks else [None] * n
         order = [bp for trio in zip(P.obj, P.cam, P.sp) for bp in trio if bp is not None]
         P.ada = AdaPack(ctx, order, extra=[(self.norm_out.linear.weight, self.norm_out.linear.bias)])
         P.pw, P.pb = self._patch_params(ctx, self.image_patch_embed)
@@ -361,7 +363,8 @@ class AMDDiffusionTransformerModelImgSpatialTempMotion(_HvModule):
                 engine.run_block(ctx, bo, obj_rows, g_obj, ada_f)
             if Lc:
                 engine.run_block(ctx, bc, cam_rows, g_cam, ada_f)
-            engine.run_block(ctx, bs, img_rows, g_tmp, ada_s)
+            if bs is not None:
+                engine.run_block(ctx, bs, img_rows, g_tmp, ada_s)
         off = P.ada.extra_off[0]
         ops.final_head(img_rows, P.nfw, P.nfb, P.now, P.nob, self.norm_final.eps, ada_f, off, off + D,
                        P.hw, P.hb, self.out_channels, p, Wi // p, pre, zt, dt)
@@ -380,3 +383,23 @@ class AMDDiffusionTransformerModelImgSpatialTempMotion(_HvModule):
         pre = torch.empty(N, self.out_channels, Hi, Wi, dtype=torch.float32, device=x.device)
         self.run(M, x, None, timestep, pre=pre)
         return pre.to(image_hidden_states.dtype)
+
+
+class AMDDiffusionTransformerModelTempMotion(AMDDiffusionTransformerModelImgSpatialTempMotion):
+    """The diffusion_model_type='default' denoiser of AMDModel_New (transformer.py:1483-1743): object joint blocks
+    only (image + object-motion tokens, per-frame timestep embedding), no camera stream and no temporal blocks.
+    Same parameter names as the reference, so its checkpoints load unchanged."""
+
+    _has_temporal_blocks = False
+
+    def __init__(self, num_attention_heads=20, attention_head_dim=64, out_channels: Optional[int] = 4, num_layers=12,
+                 use_camera=False, use_object=False, **kwargs):
+        # the reference class builds the object stream only (use_camera is accepted and ignored, 1612-1630)
+        super().__init__(num_attention_heads=num_attention_heads, attention_head_dim=attention_head_dim,
+                         out_channels=out_channels, num_layers=num_layers, use_camera=False, use_object=use_object, **kwargs)
+
+    @torch.no_grad()
+    def forward(self, image_hidden_states, timestep, timestep_cond=None, object_motion_source_hidden_states=None,
+                object_motion_target_hidden_states=None, return_dict=True):
+        return super().forward(image_hidden_states, timestep, timestep_cond, None, object_motion_source_hidden_states,
+                               object_motion_target_hidden_states, return_dict)

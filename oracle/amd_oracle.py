@@ -284,14 +284,17 @@ def dit_forward(sd, p, image, timestep, cam, osrc, otgt, heads, T, patch=2, moti
     tpos = torch.from_numpy(sincos_1d(D, np.arange(T))).float().to(dev)
     img = (img + pos[None]).view(n, T, S, D) + tpos[None, :, None]
     img = img.view(N, S, D)
-    for i in range(_count_layers(sd, p + ".spatial_blocks")):
+    has_temporal = _count_layers(sd, p + ".spatial_blocks") > 0  # absent in ...TempMotion (transformer.py:1483-1743)
+    n_layers = max(_count_layers(sd, p + ".spatial_blocks"), _count_layers(sd, p + ".object_transformer_blocks"))
+    for i in range(n_layers):
         if osrc is not None:
             omo, img = joint_block(sd, p + ".object_transformer_blocks.%d" % i, omo, img, emb, heads)
         if cam is not None:
             cmo, img = joint_block(sd, p + ".camera_transformer_blocks.%d" % i, cmo, img, emb, heads)
-        x = img.view(n, T, S, D).permute(0, 2, 1, 3).reshape(n * S, T, D)
-        x = dit_block(sd, p + ".spatial_blocks.%d" % i, x, emb_s, heads)
-        img = x.view(n, S, T, D).permute(0, 2, 1, 3).reshape(N, S, D)
+        if has_temporal:
+            x = img.view(n, T, S, D).permute(0, 2, 1, 3).reshape(n * S, T, D)
+            x = dit_block(sd, p + ".spatial_blocks.%d" % i, x, emb_s, heads)
+            img = x.view(n, S, T, D).permute(0, 2, 1, 3).reshape(N, S, D)
     img = _ln(sd, p + ".norm_final", img)
     shift, scale = _lin(sd, p + ".norm_out.linear", F.silu(emb)).chunk(2, dim=1)
     img = _ln(sd, p + ".norm_out.norm", img) * (1 + scale)[:, None] + shift[:, None]
@@ -317,10 +320,12 @@ class AMDOracle:
         rv = torch.cat([ref_img, video], 1)
         lpf = gaussian_lpf([2 * t, h, w], d_lo, d_lo).to(video.device)
         lo, _ = freq_split3d(rv.permute(0, 2, 1, 3, 4), lpf)
-        lf = lo.permute(0, 2, 1, 3, 4)[:, t:]
-        lf = camera_down(self.sd, "camera_down", lf.flatten(0, 1))
-        lf = lf.view(n, t, *lf.shape[1:])
-        cam = camera_encoder(self.sd, "camera_motion_encoder", lf, self.eh, self.T, self.patch, self.nno)
+        cam = None
+        if "camera_motion_encoder.motion_token" in self.sd:  # use_camera
+            lf = lo.permute(0, 2, 1, 3, 4)[:, t:]
+            lf = camera_down(self.sd, "camera_down", lf.flatten(0, 1))
+            lf = lf.view(n, t, *lf.shape[1:])
+            cam = camera_encoder(self.sd, "camera_motion_encoder", lf, self.eh, self.T, self.patch, self.nno)
         obj = object_encoder(self.sd, "object_motion_encoder", rv, self.eh, self.patch, self.nno)
         return cam, obj[:, :t].flatten(0, 1), obj[:, t:].flatten(0, 1)
 

@@ -12,6 +12,8 @@ T=120 run attn "attention"
 T=120 run gemm "linear_bf16 or qknorm or gated"
 T=120 run blocks "blocks"
 T=180 run small "small_model"
+T=180 run variant "object_only"
+T=120 run optim "adamw or clip"
 T=300 run default "default_model or natively"
 if [ "$1" == "bench" ]; then
   timeout -k 5 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit=$?" | tee -a gpurun_out/summary.txt; tail -n 4 gpurun_out/smoke.log

@@ -1,0 +1,54 @@
+"""Golden fixture for the sibling denoiser: AMDModel_New(diffusion_model_type='default', use_camera=False) =
+AMDDiffusionTransformerModelTempMotion (transformer.py:1483-1743), from the UNMODIFIED reference via oracle/shim.
+Run in the build container only:  python tests/golden/make_golden_variants.py"""
+import os
+import sys
+
+import torch
+from safetensors.torch import save_file
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from make_golden import OUT, build_ref_model, check  # noqa: E402
+from oracle import amd_oracle as O  # noqa: E402
+from oracle import ref_loader  # noqa: E402
+from hivae_b200 import configs, synth  # noqa: E402
+
+torch.set_grad_enabled(False)
+
+
+def main():
+    ref = ref_loader.load()
+    cfg = configs.SMALL_OBJECT_ONLY
+    m, sd = build_ref_model(ref, cfg, seed=0)
+    assert type(m.diffusion_transformer).__name__ == "AMDDiffusionTransformerModelTempMotion"
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(1, seed=1))
+    z0 = torch.randn(16, 4, 32, 32, generator=torch.Generator().manual_seed(2))
+    orc = O.AMDOracle(sd, cfg["enc_nhead"], cfg["diffusion_attn_num_heads"], 16, 2, cfg["motion_token_num"])
+    orig = m.scheduler.get_train_tuple
+    m.scheduler.get_train_tuple = lambda z0_=None, z1=None, time_step=None: orig(z0=z0, z1=z1, time_step=time_step)
+    meta = m.sample(video, ref_img, sample_step=3, return_meta_info=True)
+    trace = []
+    _, ozt, _ = orc.sample(video, ref_img, sample_step=3, z0=z0, trace=trace)
+    for i, (a, b) in enumerate(zip(trace, meta["pre_cache"])):
+        check("object-only sample pre[%d]" % i, a, b)
+    check("object-only sample zt", ozt, meta["sample"])
+    # training forward: 'default' keeps the per-FRAME timesteps it is given (no per-clip redraw, model_AMD.py:1962)
+    ts = torch.arange(16).float() * 60.0 + 13.0
+    m.prepare_timestep = lambda batch_size, device, time_step=None: ts.to(device)
+    pre, vel, ld = m(video, ref_img)
+    opre, ovel, old = orc.forward(video, ref_img, ts, z0)
+    check("object-only forward pre", opre, pre), check("object-only forward loss", old["loss"], ld["loss"])
+    save_file({k: v.contiguous() for k, v in {
+        "z0": z0, "ts": ts, **{"pre_%d" % i: p for i, p in enumerate(meta["pre_cache"])}, "zt": meta["sample"].contiguous(),
+        "fwd_pre": pre, "fwd_loss": torch.stack([ld["loss"], ld["diff_loss"], ld["rec_loss"]])}.items()},
+        os.path.join(OUT, "small_object_only.safetensors"))
+    with open(os.path.join(OUT, "state_dict_keys_small_object_only.json"), "w") as f:
+        import json
+        json.dump({k: list(v.shape) for k, v in m.state_dict().items()}, f, indent=0)
+    print("written", os.path.join(OUT, "small_object_only.safetensors"))
+
+
+if __name__ == "__main__":
+    main()

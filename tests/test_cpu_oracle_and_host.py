@@ -119,6 +119,20 @@ def test_state_dict_keys_match_reference():
     assert abs(sum(int(np.prod(s)) for s in mine.values()) - 695.00e6) < 0.01e6
 
 
+def test_state_dict_keys_object_only_variant():
+    """diffusion_model_type='default' (AMDDiffusionTransformerModelTempMotion, transformer.py:1483-1743):
+    same keys/shapes as the unmodified reference; unknown types raise like the reference's list lookup."""
+    import hivae_b200 as hv
+    with open(os.path.join(ROOT, "tests", "golden", "state_dict_keys_small_object_only.json")) as f:
+        ref = json.load(f)
+    m = hv.AMDModel_New(**configs.SMALL_OBJECT_ONLY)
+    assert type(m.diffusion_transformer).__name__ == "AMDDiffusionTransformerModelTempMotion"
+    assert {k: list(v.shape) for k, v in m.state_dict().items()} == ref
+    assert not any(".spatial_blocks." in k or ".camera_transformer_blocks." in k for k in ref)
+    with pytest.raises(IndexError):
+        hv.AMDModel_New(**dict(configs.SMALL, diffusion_model_type="nope"))
+
+
 def test_sincos_tables_match_oracle():
     from hivae_b200 import embeddings as E
     assert np.array_equal(E.sincos_2d(256, 16, 16), O.sincos_2d(256, 16, 16))

@@ -448,6 +448,28 @@ def test_small_model_batch_independence(dev):
         assert rel(zti, zt[i:i + 1]) <= 1e-5
 
 
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_object_only_variant_golden(dev, golden, dtype, tol):
+    """diffusion_model_type='default', use_camera=False -> AMDDiffusionTransformerModelTempMotion
+    (transformer.py:1483-1743; object joint blocks only, per-frame timesteps kept): sample + training forward
+    against the unmodified reference's outputs (tests/golden/make_golden_variants.py)."""
+    import hivae_b200 as hv
+    g = golden("small_object_only")
+    m = hv.AMDModel_New(**configs.SMALL_OBJECT_ONLY)
+    m.load_state_dict(synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 0))
+    m.to(dev).set_compute_dtype(dtype)
+    video, ref_img = (t.to(dev) for t in synth.split_clip(synth.synth_clip_latents(1, seed=1)))
+    _fix_noise(m, g["z0"])
+    meta = m.sample(video, ref_img, sample_step=3, return_meta_info=True)
+    for i, p in enumerate(meta["pre_cache"]):
+        assert rel(p, g["pre_%d" % i]) <= tol, i
+    assert rel(meta["sample"], g["zt"]) <= tol
+    m.prepare_timestep = lambda batch_size, device, time_step=None: g["ts"].to(device)
+    pre, vel, ld = m(video, ref_img)
+    assert rel(pre, g["fwd_pre"]) <= tol
+    assert abs(float(ld["loss"]) - float(g["fwd_loss"][0])) <= (1e-4 if dtype == torch.float32 else 2e-2) * float(g["fwd_loss"][0])
+
+
 def _default(dev, dtype):
     import hivae_b200 as hv
     m = hv.AMDModel_New(**configs.DEFAULT)

@@ -25,7 +25,8 @@ def test_flat_arena_views_alias_and_keep_values():
         assert p.data.data_ptr() == arena.flat.data_ptr() + 4 * o and p.grad.data_ptr() == arena.grad.data_ptr() + 4 * o
     arena.flat.add_(1.0)
     assert all(torch.equal(p.data, b + 1.0) for p, b in zip(ps, before))
-    (ps[0].sum() * 2.0 + ps[1].sum()).backward()  # autograd accumulates into the arena views in place
+    with torch.enable_grad():  # other test modules switch grad mode off process-wide
+        (ps[0].sum() * 2.0 + ps[1].sum()).backward()  # autograd accumulates into the arena views in place
     assert float(arena.grad[:15].min()) == 2.0 and float(arena.grad[16:23].max()) == 1.0 and float(arena.grad[15]) == 0.0
     arena.zero_grad()
     assert float(arena.grad.abs().max()) == 0.0
