@@ -11,8 +11,9 @@ from .wavelet import DWT, IWT, dwt_init, iwt_init, dwt_pyramid, iwt_pyramid  # n
 from .frequency_utils import gaussian_low_pass_filter, freq_3d_filter  # noqa: F401
 from .rectified_flow import RectifiedFlow  # noqa: F401
 from .modules import (BasicTransformerBlock, BasicCrossTransformerBlock, AMDTransformerBlock, BasicDiTBlock,  # noqa: F401
-                      PatchEmbed, AMDLayerNormZero, AMDLayerNormZero_OneVariable, AdaLayerNorm)
+                      PatchEmbed, AMDLayerNormZero, AMDLayerNormZero_OneVariable, AdaLayerNorm, AMDTransformerMotionBlock)
 from .transformer import (MotionEncoderLearnTokenTransformer, MotionEncoderLearnTokenOnlyTemporalTransformer,  # noqa: F401
+                          MotionEncoderLearnTokenTemporalTransformer,
                           AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion)
 from .model_AMD import AMDModel_New, AMD_N, AMD_models  # noqa: F401
 from . import sharding  # noqa: F401

@@ -162,6 +162,21 @@ class BasicTransformerBlock(_Block):
         return res.to(hidden_states.dtype)
 
 
+class AMDTransformerMotionBlock(BasicTransformerBlock):
+    """modules.py:1190-1285 with time_embed_dim=None (the only runnable form: `if temb:` on a tensor raises in the
+    reference): plain pre-LN self-attention + feed-forward block."""
+
+    def __init__(self, dim, num_attention_heads, attention_head_dim, time_embed_dim=None, **kw):
+        if time_embed_dim:
+            raise NotImplementedError("AMDTransformerMotionBlock with time_embed_dim is not runnable in the reference (modules.py:1250)")
+        super().__init__(dim, num_attention_heads, attention_head_dim, **kw)
+
+    @torch.no_grad()
+    def forward(self, hidden_states, temb=None):
+        assert temb is None
+        return super().forward(hidden_states)
+
+
 class BasicCrossTransformerBlock(_Block):
     """modules.py:745-840: queries from hidden_states, K/V from the (un-normalised) encoder_hidden_state."""
     KIND = "cross"

@@ -12,7 +12,7 @@ from torch import nn
 from . import embeddings as E
 from . import engine, ops
 from .engine import AdaPack, Ctx
-from .modules import (AdaLayerNorm, AMDTransformerBlock, BasicCrossTransformerBlock, BasicDiTBlock,
+from .modules import (AdaLayerNorm, AMDTransformerBlock, AMDTransformerMotionBlock, BasicCrossTransformerBlock, BasicDiTBlock,
                       BasicTransformerBlock, PatchEmbed)
 from .ops import Ada, Rows
 
@@ -130,6 +130,91 @@ class MotionEncoderLearnTokenTransformer(_HvModule):
         mrows = Rows(res, 0, Lm)
         y = ops.ln_modulate(mrows, P.nfw, P.nfb, self.norm_final.eps, ctx.buf("enc_fin", (frames * Lm, D), torch.float32))
         m = engine.small_linear(ctx, y, P.ow, P.ob, "enc_out").view(N, T, Lm, -1).clone()
+        return _final_norm_out(self.need_norm_out, m)
+
+
+# ================================================================================================
+class MotionEncoderLearnTokenTemporalTransformer(_HvModule):
+    """Spatial + per-token temporal motion encoder (transformer.py:195-367; AMDModel's encoder when
+    use_motiontemporal): every layer = BasicTransformerBlock over each frame's [motion tokens || patch tokens],
+    then AMDTransformerMotionBlock over time for each motion token of the SECOND HALF of the flat (n t) frame
+    batch (the reference's `chunk(2, dim=0)`, transformer.py:340 — the target frames when n == 1).  Both run in
+    place on one fp32 residual buffer; the '(n t) l d -> (n l) t d' regrouping is a strided attention geometry."""
+
+    def __init__(self, img_height=32, img_width=32, img_inchannel=4, img_patch_size=2, motion_token_num=12,
+                 motion_channel=128, need_norm_out=True, video_frames=16, num_attention_heads=12, attention_head_dim=64,
+                 num_layers=8, freq_shift=0, dropout=0.0, attention_bias=True, activation_fn="gelu-approximate",
+                 norm_elementwise_affine=True, norm_eps=1e-5, spatial_interpolation_scale=1.0,
+                 temporal_interpolation_scale=1.0):
+        super().__init__()
+        hidden_dim = num_attention_heads * attention_head_dim
+        iph, ipw = img_height // img_patch_size, img_width // img_patch_size
+        self.img_token_len, self.video_frames = iph * ipw, video_frames
+        self.motion_token = nn.Parameter(torch.randn(1, motion_token_num, motion_channel) * 0.02)
+        self.motion_embed = nn.Linear(motion_channel, hidden_dim)
+        self.patch_embed = PatchEmbed(img_patch_size, img_inchannel, hidden_dim)
+        self.embedding_dropout = nn.Dropout(dropout)
+        self.register_buffer("pos_embedding", E.table(E.sincos_2d(hidden_dim, iph, ipw)), persistent=False)
+        self.register_buffer("motion_temporal_embedding",
+                             E.table(E.sincos_1d(hidden_dim, np.arange(video_frames * motion_token_num))), persistent=False)
+        kw = dict(dim=hidden_dim, num_attention_heads=num_attention_heads, attention_head_dim=attention_head_dim,
+                  dropout=dropout, activation_fn=activation_fn, attention_bias=attention_bias,
+                  norm_elementwise_affine=norm_elementwise_affine, norm_eps=norm_eps)
+        self.transformer_blocks = nn.ModuleList([BasicTransformerBlock(**kw) for _ in range(num_layers)])
+        self.motion_blocks = nn.ModuleList([AMDTransformerMotionBlock(**kw) for _ in range(num_layers)])
+        self.norm_final = nn.LayerNorm(hidden_dim, eps=norm_eps, elementwise_affine=norm_elementwise_affine)
+        self.proj_out = nn.Linear(hidden_dim, motion_channel)
+        self.need_norm_out = need_norm_out
+        if need_norm_out:
+            self.norm_out = nn.LayerNorm(motion_channel, eps=norm_eps, elementwise_affine=False)
+        self.gradient_checkpointing = False
+
+    def _prepare(self, ctx):
+        P = MotionEncoderLearnTokenTransformer._prepare(self, ctx)
+        P.mblocks = [engine.prepare_block(ctx, b, "basic") for b in self.motion_blocks]
+        P.tpos = ctx.f32(self.motion_temporal_embedding[0])
+        P.tabs = {}
+        return P
+
+    @staticmethod
+    def _token_table(P, ctx, T):
+        """initial motion tokens of one clip (T, Lm, D): embed(motion_token) for the first T/2 frames,
+        + temporal sincos at position (f - T/2)*Lm + l for the others (transformer.py:305-313); cached per T"""
+        if T not in P.tabs:
+            Lm, D, half = P.tok.shape[0], P.ew.shape[0], T // 2
+            tok = engine.small_linear(ctx, P.tok, P.ew, P.eb, "tenc_tok")
+            tab = torch.empty(T, Lm, D, dtype=torch.float32, device=ctx.device)
+            ops.rows_scatter(tok, 0, 1, None, Rows(tab[:half], 0, Lm))
+            for f in range(half):
+                ops.rows_scatter(tok, 0, 1, P.tpos[f * Lm:(f + 1) * Lm].contiguous(), Rows(tab[half + f:half + f + 1], 0, Lm))
+            P.tabs[T] = tab
+        return P.tabs[T]
+
+    @torch.no_grad()
+    def forward(self, img_hidden_states, mask_ratio=None):
+        if mask_ratio is not None:
+            raise NotImplementedError("random token masking (train-time augmentation, transformer.py:369-397) is out of scope")
+        N, T, C, H, W = img_hidden_states.shape
+        P = self._prepared(img_hidden_states.device)
+        ctx = P.ctx
+        D, p = P.ew.shape[0], self.patch_embed.patch_size
+        Lm, S = P.tok.shape[0], self.img_token_len
+        assert S == (H // p) * (W // p), "img_token_len should be equal!"
+        assert T % 2 == 0 and (T // 2) * Lm <= P.tpos.shape[0]
+        frames, FR, half = N * T, Lm + S, T // 2
+        x = img_hidden_states.reshape(frames, C, H, W).float().contiguous()
+        res = ctx.buf("tenc_res", (frames, FR, D), torch.float32)
+        tab = self._token_table(P, ctx, T)
+        for n in range(N):
+            ops.rows_scatter(tab.view(T * Lm, D), Lm, 1, None, Rows(res[n * T:(n + 1) * T], 0, Lm))
+        ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, None, res, FR, Lm, D)
+        rows, geom = Rows(res, 0, FR), engine.dense_geom(frames, FR)
+        trows, tgeom = Rows(res[frames // 2:], 0, Lm), engine.strided_geom(N, Lm, half)  # '(n t) l d -> (n l) t d'
+        for bp, mp in zip(P.blocks, P.mblocks):
+            engine.run_block(ctx, bp, rows, geom)
+            engine.run_block(ctx, mp, trows, tgeom)
+        y = ops.ln_modulate(Rows(res, 0, Lm), P.nfw, P.nfb, self.norm_final.eps, ctx.buf("tenc_fin", (frames * Lm, D), torch.float32))
+        m = engine.small_linear(ctx, y, P.ow, P.ob, "tenc_out").view(N, T, Lm, -1).clone()
         return _final_norm_out(self.need_norm_out, m)
 
 

@@ -232,6 +232,33 @@ def object_encoder(sd, p, x, heads, patch=2, need_norm_out=False):
     return m.view(N, T, *m.shape[1:])
 
 
+def temporal_motion_encoder(sd, p, x, heads, video_frames, patch=2, need_norm_out=True):
+    """MotionEncoderLearnTokenTemporalTransformer.forward (transformer.py:298-367), mask_ratio=None.  Keeps the
+    reference's two different splits: frames of each clip at 305 (dim=1), the flat (n t) batch at 340 (dim=0)."""
+    N, T, C, H, W = x.shape
+    D = sd[p + ".motion_embed.weight"].shape[0]
+    tok = _lin(sd, p + ".motion_embed", sd[p + ".motion_token"])  # (1, l, D)
+    l, half = tok.shape[1], T // 2
+    tem = torch.from_numpy(sincos_1d(D, np.arange(video_frames * l))).float().to(x.device)
+    mt = tok[None].repeat(N, T, 1, 1).clone()
+    mt[:, half:] += tem[:half * l].view(1, half, l, D)
+    mt = mt.reshape(N * T, l, D)
+    img = patch_embed(sd, p + ".patch_embed", x.reshape(N * T, C, H, W), patch)
+    pos = torch.from_numpy(sincos_2d(D, H // patch, W // patch)).float().to(x.device)
+    h = torch.cat([mt, img + pos[None]], 1)
+    for i in range(_count_layers(sd, p + ".transformer_blocks")):
+        h = basic_block(sd, p + ".transformer_blocks.%d" % i, h, heads)
+        src, tgt = h[:, :l].chunk(2, dim=0)
+        tgt = tgt.reshape(N, half, l, D).permute(0, 2, 1, 3).reshape(N * l, half, D)
+        tgt = basic_block(sd, p + ".motion_blocks.%d" % i, tgt, heads)  # AMDTransformerMotionBlock, temb=None (modules.py:1246-1285)
+        tgt = tgt.view(N, l, half, D).permute(0, 2, 1, 3).reshape(N * half, l, D)
+        h = torch.cat([torch.cat([src, tgt], 0), h[:, l:]], 1)
+    m = _lin(sd, p + ".proj_out", _ln(sd, p + ".norm_final", h[:, :l]))
+    if need_norm_out:
+        m = F.layer_norm(m, (m.shape[-1],))
+    return m.view(N, T, *m.shape[1:])
+
+
 def camera_encoder(sd, p, x, heads, video_frames, patch=2, need_norm_out=False):
     """MotionEncoderLearnTokenOnlyTemporalTransformer.forward (transformer.py:495-556)."""
     N, T, C, H, W = x.shape

@@ -48,6 +48,30 @@ def main():
         import json
         json.dump({k: list(v.shape) for k, v in m.state_dict().items()}, f, indent=0)
     print("written", os.path.join(OUT, "small_object_only.safetensors"))
+    temporal_encoder(ref)
+
+
+TENC = dict(img_height=32, img_width=32, img_inchannel=4, img_patch_size=2, motion_token_num=4, motion_channel=16,
+            need_norm_out=True, video_frames=4, num_attention_heads=2, attention_head_dim=64, num_layers=2)
+
+
+def temporal_encoder(ref):
+    """a16: MotionEncoderLearnTokenTemporalTransformer (transformer.py:195-367), n = 1 (target = frames T/2..T-1)
+    and n = 2 (where the reference's dim-0 chunk regroups the second CLIP instead)."""
+    torch.manual_seed(0)
+    m = ref.transformer.MotionEncoderLearnTokenTemporalTransformer(**TENC).eval()
+    sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 3)
+    m.load_state_dict(sd)
+    out = {}
+    for n in (1, 2):
+        x = torch.randn(n, 8, 4, 32, 32, generator=torch.Generator().manual_seed(10 + n))
+        y = m(x)
+        check("temporal encoder n=%d" % n, O.temporal_motion_encoder({"e." + k: v for k, v in sd.items()}, "e", x, 2, 4), y)
+        out["x%d" % n], out["y%d" % n] = x, y.contiguous()
+    save_file(out, os.path.join(OUT, "temporal_encoder.safetensors"))
+    with open(os.path.join(OUT, "state_dict_keys_temporal_encoder.json"), "w") as f:
+        import json
+        json.dump({k: list(v.shape) for k, v in m.state_dict().items()}, f, indent=0)
 
 
 if __name__ == "__main__":

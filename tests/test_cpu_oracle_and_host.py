@@ -105,6 +105,10 @@ def test_oracle_rope_attention(golden):
     assert rel(O.rope_attention(*args, mask=torch.tril(torch.ones(24, 24)), start_pos=3), g["ropeattn_rope_mask"]) < 1e-5
 
 
+TENC = dict(img_height=32, img_width=32, img_inchannel=4, img_patch_size=2, motion_token_num=4, motion_channel=16,
+            need_norm_out=True, video_frames=4, num_attention_heads=2, attention_head_dim=64, num_layers=2)  # = make_golden_variants.TENC
+
+
 # ------------------------------------------------------------------ host logic (no GPU)
 def test_state_dict_keys_match_reference():
     """drop-in contract: a reference model.safetensors must load unchanged."""
@@ -131,6 +135,18 @@ def test_state_dict_keys_object_only_variant():
     assert not any(".spatial_blocks." in k or ".camera_transformer_blocks." in k for k in ref)
     with pytest.raises(IndexError):
         hv.AMDModel_New(**dict(configs.SMALL, diffusion_model_type="nope"))
+
+
+def test_state_dict_keys_temporal_encoder():
+    """a16 MotionEncoderLearnTokenTemporalTransformer (transformer.py:195-296): keys/shapes of the unmodified reference."""
+    import hivae_b200 as hv
+    with open(os.path.join(ROOT, "tests", "golden", "state_dict_keys_temporal_encoder.json")) as f:
+        ref = json.load(f)
+    m = hv.MotionEncoderLearnTokenTemporalTransformer(**TENC)
+    assert {k: list(v.shape) for k, v in m.state_dict().items()} == ref
+    assert m.motion_temporal_embedding.shape == (1, 16, 128)
+    with pytest.raises(NotImplementedError):
+        hv.AMDTransformerMotionBlock(128, 2, 64, time_embed_dim=32)
 
 
 def test_sincos_tables_match_oracle():

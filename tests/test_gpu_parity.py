@@ -470,6 +470,24 @@ def test_object_only_variant_golden(dev, golden, dtype, tol):
     assert abs(float(ld["loss"]) - float(g["fwd_loss"][0])) <= (1e-4 if dtype == torch.float32 else 2e-2) * float(g["fwd_loss"][0])
 
 
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_temporal_motion_encoder_golden(dev, golden, dtype, tol):
+    """MotionEncoderLearnTokenTemporalTransformer (transformer.py:195-367) vs the unmodified
+    reference, n = 1 and n = 2 (the reference regroups the second half of the flat (n t) batch, 340)."""
+    import hivae_b200 as hv
+    from test_cpu_oracle_and_host import TENC
+    g = golden("temporal_encoder")
+    m = hv.MotionEncoderLearnTokenTemporalTransformer(**TENC)
+    m.load_state_dict(synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 3))
+    m.to(dev)
+    for sub in m.modules():
+        sub.hv_compute_dtype = dtype
+    for n in (1, 2):
+        y = m(g["x%d" % n].to(dev))
+        assert y.shape == (n, 8, 4, 16)
+        assert rel(y, g["y%d" % n]) <= tol, n
+
+
 def _default(dev, dtype):
     import hivae_b200 as hv
     m = hv.AMDModel_New(**configs.DEFAULT)
