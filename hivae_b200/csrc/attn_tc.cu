@@ -21,8 +21,9 @@
 // ~7000 clk a tile takes; MUFU.EX2 (2300 clk/tile) and the MMAs (1150 clk/tile) hide under it.  A variant
 // that keeps the scores in registers between the passes (16 softmax warps, 72 scores per thread) read
 // TMEM once but lost more to register spills and barrier cost than it gained (299 vs 188 us at the DiT
-// shape) and was not kept.  Query tiles past the end of the sequence (e.g. rows 18..127 of the third
-// tile of a 274-token sequence) skip both passes.
+// shape) and was not kept.  Tail tiles (<= 32 query rows left, e.g. the third tile of a 274-token sequence):
+// the producer replicates the 32-row Q box into all four lane quarters, so every softmax warp can reach the
+// rows and the keys are split eight ways instead of two (a third of a full tile's softmax time).
 //
 // Warp roles (320 threads): warps 0..7 softmax + epilogue (TMEM lane quarter = warp % 4, key half =
 // warp / 4), warp 8 = MMA issuer + TMEM owner, warp 9 = TMA producer (one elected lane each).
@@ -114,8 +115,9 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                 tc::mbar_wait(&q_free[b], (uint32_t)(((T >> 1) & 1) ^ 1));
                 tc::mbar_expect_tx(&q_full[b], QBYTES);
 #pragma unroll
+                const bool tail = a.Lq - i * QT <= 32;  // tail tile: the same 32-row box goes to all four lane quarters
                 for (int j = 0; j < QT / 32; ++j)
-                    tc::tma_load_2d(Qs + b * QBYTES + j * 4096, &tq, &q_full[b], col, (int)(qrow0 + i * QT + j * 32));
+                    tc::tma_load_2d(Qs + b * QBYTES + j * 4096, &tq, &q_full[b], col, (int)(qrow0 + i * QT + (tail ? 0 : j * 32)));
                 ++T;
             };
             for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
@@ -194,7 +196,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
         const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
         const int c_begin = h ? HB : 0, c_end = h ? KP : HB;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
-        uint8_t* prow = Ps + (row >> 3) * 1024 + (row & 7) * 128;  // this row inside every 64-key P chunk
+        uint8_t* prow_full = Ps + (row >> 3) * 1024 + (row & 7) * 128;  // this row inside every 64-key P chunk
+        uint8_t* prow_tail = Ps + (lane >> 3) * 1024 + (lane & 7) * 128;  // tail tiles: row = lane in every quarter
         long long T = 0;
         // deferred epilogue of the previous tile
         bool pend = false;
@@ -223,12 +226,27 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
             const int head = (int)(w - seq * a.heads);
             for (int i = 0; i < nq; ++i, ++T) {
                 const bool active = i * QT + q * 32 < a.Lq;  // warp-uniform: this warp has query rows in the tile
+                // tail tile (<= 32 query rows left): the producer replicated the rows into all four lane quarters, so
+                // the eight softmax warps split the KEYS eight ways (16-key chunks k = q, q+4, ... of key half h)
+                // instead of six of them idling for a whole tile
+                const bool tail = a.Lq - i * QT <= 32;
+                const int nch = (c_end - c_begin) >> 4;
+                uint8_t* prow = tail ? prow_tail : prow_full;
                 const uint32_t s_addr = t_lane + S_COL + (uint32_t)((2 * T + h) % 3) * SBUF - (uint32_t)c_begin;
                 tc::mbar_wait(&s_full[T & 1][h], (uint32_t)((T >> 1) & 1));
                 tc::fence_after_sync();
                 // ---- pass 1: row maximum over this thread's half of the keys
                 float mx = -INFINITY;
-                if (active && c_begin < c_end) {
+                if (tail) {
+                    uint32_t va[16];
+                    for (int k = q; k < nch; k += 4) {
+                        const int c = c_begin + (k << 4);
+                        tmem_ld16_issue(s_addr + c, va);
+                        tmem_ld16_wait(va);
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) if (c + j < a.Lkv) mx = fmaxf(mx, __uint_as_float(va[j]));
+                    }
+                } else if (active && c_begin < c_end) {
                     uint32_t va[16], vb[16];
                     int c = c_begin;
                     tmem_ld16_issue(s_addr + c, va);
@@ -261,15 +279,18 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                 }
                 smax[h][row] = mx;
                 tc::named_bar_sync(1, 256);
-                mx = fmaxf(mx, smax[h ^ 1][row]);
+                if (tail) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) mx = fmaxf(mx, fmaxf(smax[0][j * 32 + lane], smax[1][j * 32 + lane]));
+                } else {
+                    mx = fmaxf(mx, smax[h ^ 1][row]);
+                }
                 const float msc = mx * a.sl2;
                 // ---- epilogue of the previous tile: PV(T-1) retired while the max pass ran
                 if (pend) epilogue();
                 // ---- pass 2: P = exp2(S*c - max*c) -> bf16 -> shared memory (K-major, 128 B swizzle)
                 float sum = 0.f;
-                if (active && c_begin < c_end) {
-                    uint32_t va[16], vb[16];
-                    auto emit = [&](uint32_t (&r)[16], int c) {
+                auto emit = [&](uint32_t (&r)[16], int c) {
                         float v[16];
                         if (c + 16 <= a.Lkv) {
 #pragma unroll
@@ -286,7 +307,17 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                             make_uint4(hv_pack_bf16(v[0], v[1]), hv_pack_bf16(v[2], v[3]), hv_pack_bf16(v[4], v[5]), hv_pack_bf16(v[6], v[7]));
                         *reinterpret_cast<uint4*>(pc + (((jc + 1) ^ (row & 7)) << 4)) =
                             make_uint4(hv_pack_bf16(v[8], v[9]), hv_pack_bf16(v[10], v[11]), hv_pack_bf16(v[12], v[13]), hv_pack_bf16(v[14], v[15]));
-                    };
+                };
+                if (tail) {
+                    uint32_t va[16];
+                    for (int k = q; k < nch; k += 4) {
+                        const int c = c_begin + (k << 4);
+                        tmem_ld16_issue(s_addr + c, va);
+                        tmem_ld16_wait(va);
+                        emit(va, c);
+                    }
+                } else if (active && c_begin < c_end) {
+                    uint32_t va[16], vb[16];
                     int c = c_begin;
                     tmem_ld16_issue(s_addr + c, va);
                     while (true) {
@@ -313,7 +344,14 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                 pend = true;
                 pend_active = active;
                 pend_store = qr < a.Lq;
-                pend_inv = 1.f / (sum + ssum[h ^ 1][row]);
+                if (tail) {
+                    sum = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) sum += ssum[0][j * 32 + lane] + ssum[1][j * 32 + lane];
+                } else {
+                    sum += ssum[h ^ 1][row];
+                }
+                pend_inv = 1.f / sum;
                 pend_ptr = a.out + (seq * a.q_sa + qr) * a.ldo + head * HD + h * 32;
             }
         }

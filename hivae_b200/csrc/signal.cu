@@ -525,6 +525,75 @@ __global__ void __launch_bounds__(256) freq_split3d_kernel(const float* __restri
     }
 }
 
+// Slab variant for axis lengths <= 32 (every shape on the path): a volume is split into T/TC slabs of TC
+// consecutive frames, one CTA per slab, so that 32 volumes already give 128 CTAs and several CTAs fit on an SM
+// (46 KB instead of 152 KB of shared memory).  The T axis goes FIRST, straight from global memory: thread (h, w)
+// reads its T-long column (coalesced across w), keeps it in registers and produces only the slab's TC output
+// frames — a CTA reads the whole volume (L2 hits after the first slab) but never needs another CTA's data.
+// The H and W passes then run inside the slab in shared memory as above.  Four accumulators per output break
+// the 32-long dependent FMA chain.
+__device__ __forceinline__ float circ_dot32(const float* __restrict__ crow, const float (&xr)[32]) {
+    const float4* row = reinterpret_cast<const float4*>(crow);
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+    for (int k4 = 0; k4 < 8; ++k4) {
+        const float4 c = row[k4];  // broadcast read, zero-padded beyond the axis length
+        a0 = fmaf(c.x, xr[4 * k4], a0); a1 = fmaf(c.y, xr[4 * k4 + 1], a1);
+        a2 = fmaf(c.z, xr[4 * k4 + 2], a2); a3 = fmaf(c.w, xr[4 * k4 + 3], a3);
+    }
+    return (a0 + a1) + (a2 + a3);
+}
+
+__device__ __forceinline__ void circ_line32(float* line, int stride, int N, const float* __restrict__ C) {
+    float xr[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) xr[k] = (k < N) ? line[k * stride] : 0.0f;
+    for (int i = 0; i < N; ++i) line[i * stride] = circ_dot32(C + i * 32, xr);
+}
+
+__global__ void __launch_bounds__(256, 3) freq_split3d_slab_kernel(const float* __restrict__ x, const float* __restrict__ ct,
+                                                                const float* __restrict__ ch, const float* __restrict__ cw,
+                                                                float* __restrict__ lo, float* __restrict__ hi,
+                                                                int T, int H, int W, int TC) {
+    extern __shared__ __align__(16) float smem[];
+    float* sct = smem;                 // TC rows x 32 (rows t0 .. t0+TC-1 of the T circulant)
+    float* sch = sct + 32 * 32;
+    float* scw = sch + 32 * 32;
+    float* slab = scw + 32 * 32;       // TC*H rows, pitch W+1
+    const int P = W + 1, HW = H * W;
+    const int slabs = T / TC;
+    const long long v = blockIdx.x / slabs;
+    const int t0 = (int)(blockIdx.x - v * slabs) * TC;
+    const float* xv = x + v * (long long)T * HW;
+    for (int i = threadIdx.x; i < 3 * 32 * 32; i += blockDim.x) smem[i] = 0.0f;
+    __syncthreads();
+    for (int i = threadIdx.x; i < TC * T; i += blockDim.x) sct[(i / T) * 32 + i % T] = ct[(t0 + i / T) * T + i % T];
+    for (int i = threadIdx.x; i < H * H; i += blockDim.x) sch[(i / H) * 32 + i % H] = ch[i];
+    for (int i = threadIdx.x; i < W * W; i += blockDim.x) scw[(i / W) * 32 + i % W] = cw[i];
+    __syncthreads();
+    // T axis from global memory: column (h, w), element stride H*W
+    for (int col = threadIdx.x; col < HW; col += blockDim.x) {
+        float xr[32];
+#pragma unroll
+        for (int k = 0; k < 32; ++k) xr[k] = (k < T) ? __ldg(xv + (long long)k * HW + col) : 0.0f;
+        float* dst = slab + (col / W) * P + col % W;
+        for (int tt = 0; tt < TC; ++tt) dst[tt * H * P] = circ_dot32(sct + tt * 32, xr);
+    }
+    __syncthreads();
+    // H axis: line = (tt, w), stride P
+    for (int l = threadIdx.x; l < TC * W; l += blockDim.x) circ_line32(slab + (l / W) * H * P + l % W, P, H, sch);
+    __syncthreads();
+    // W axis: line = (tt, h), stride 1, consecutive threads a pitch apart (conflict-free)
+    for (int l = threadIdx.x; l < TC * H; l += blockDim.x) circ_line32(slab + l * P, 1, W, scw);
+    __syncthreads();
+    const long long off = v * (long long)T * HW + (long long)t0 * HW;
+    for (int i = threadIdx.x; i < TC * HW; i += blockDim.x) {
+        const float l = slab[(i / W) * P + i % W];
+        lo[off + i] = l;
+        hi[off + i] = __ldg(x + off + i) - l;
+    }
+}
+
 extern "C" int hv_freq_split3d(const float* x, const float* ct, const float* ch, const float* cw,
                                float* lo, float* hi, int64_t vols, int T, int H, int W, void* stream) {
     HV_REQUIRE(vols >= 0 && T > 0 && H > 0 && W > 0, "hv_freq_split3d: bad sizes");
@@ -536,6 +605,15 @@ extern "C" int hv_freq_split3d(const float* x, const float* ct, const float* ch,
     size_t smem = (size_t)(3 * MAXN * MAXN + (size_t)T * H * (W + 1)) * sizeof(float);
     HV_REQUIRE(smem <= 227 * 1024, "hv_freq_split3d: volume %dx%dx%d needs %zu B of shared memory (> 227 KB)", T, H, W, smem);
     cudaStream_t st = hv_stream(stream);
+    if (MAXN == 32) {
+        int TC = T;  // frames per slab: at least 4, at most 8 slabs' worth of parallelism per volume
+        for (int d = 8; d >= 2; d >>= 1) if (T % d == 0 && T / d >= 4) { TC = T / d; break; }
+        const size_t sm = (size_t)(3 * 32 * 32 + (size_t)TC * H * (W + 1)) * sizeof(float);
+        HV_CUDA(cudaFuncSetAttribute(freq_split3d_slab_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        freq_split3d_slab_kernel<<<(unsigned)(vols * (T / TC)), 256, sm, st>>>(x, ct, ch, cw, lo, hi, T, H, W, TC);
+        HV_LAUNCH_CHECK();
+        return HV_OK;
+    }
     if (MAXN == 32) {
         HV_CUDA(cudaFuncSetAttribute(freq_split3d_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         freq_split3d_kernel<32><<<(unsigned)vols, 256, smem, st>>>(x, ct, ch, cw, lo, hi, T, H, W);

@@ -214,16 +214,27 @@ class AMDModel_New(_ConfigModel):
             raise ValueError("decode() needs start_step (the reference raises a TypeError here, model_AMD.py:2476)")
         n, t = video.shape[:2]
         zi, zj = ref_img.flatten(0, 1).float().contiguous(), video.flatten(0, 1).float().contiguous()
-        time_step = torch.ones((zj.shape[0],), device=video.device) * start_step
+        zi, zt, zj, meta = self._euler(zi, zj, camera_target_motion if self.use_camera else None,
+                                       object_source_motion if self.use_object else None,
+                                       object_target_motion if self.use_object else None,
+                                       start_step, sample_step, return_meta_info)
+        shp = (n, t) + tuple(zi.shape[1:])
+        zi, zt, zj = zi.view(shp), zt.view(shp), zj.view(shp)
+        if return_meta_info:
+            return dict(meta, zi=zi, zj=zj, sample=zt)
+        return zi, zt, zj
+
+    def _euler(self, zi, zj, cam, osrc, otgt, start_step, sample_step, return_meta_info):
+        """noise zj to start_step, then the Euler loop shared by decode / sample_cross / sample_with_refimg_motion
+        (model_AMD.py:2124-2160, 2326-2356, 2745-2768); flat (n*t, c, h, w) tensors in and out"""
+        time_step = torch.ones((zj.shape[0],), device=zj.device) * start_step
         zt, _vel = self.scheduler.get_train_tuple(z1=zj, time_step=time_step)
         zt = zt.contiguous().clone()
         step_seq = np.linspace(0, start_step, num=sample_step + 1, endpoint=True, dtype=int)
         step_seq = list(reversed(step_seq[1:]))
         dt = 1.0 / sample_step
         dit = self.diffusion_transformer
-        M = dit.set_motion(zi.shape[0], zi.device, camera_target_motion if self.use_camera else None,
-                           object_source_motion if self.use_object else None,
-                           object_target_motion if self.use_object else None)
+        M = dit.set_motion(zi.shape[0], zi.device, cam, osrc, otgt)
         pre_cache, sample_cache = [], []
         ts = torch.empty(zt.shape[0], dtype=torch.float32, device=zt.device)
         for i in step_seq:
@@ -233,12 +244,54 @@ class AMDModel_New(_ConfigModel):
             if return_meta_info:
                 pre_cache.append(pre)
                 sample_cache.append(zt.clone())
+        return zi, zt, zj, {"pre_cache": pre_cache, "sample_cache": sample_cache, "step_seq": step_seq}
+
+    @torch.no_grad()
+    def sample_cross(self, video_1, video_2, ref_img, video_grey_1=None, video_grey_2=None, ref_img_grey=None, sample_step=50,
+                     object_mask_ratio=None, camera_mask_ratio=None, start_step=None, return_meta_info=False):
+        """model_AMD.py:2198-2377: camera motion from video_1 (low band, cut-off 0.5 over ITS t-frame volume, 2219-2221),
+        noised ground truth and reference image from video_2.  The reference also encodes video_2's object motion
+        (2256-2260) but does not hand it to the denoiser (2349-2351); that unused encoder pass is not run here."""
+        n, t, c, h, w = video_1.shape
+        if start_step is None:
+            start_step = self.scheduler.num_step
+        assert start_step <= self.scheduler.num_step, "start_step cant be larger than scheduler.num_step"
+        if not (self.use_filter and self.use_camera) or self.diffusion_model_type != "spatial":
+            raise NotImplementedError("sample_cross needs use_filter, use_camera and the 'spatial' denoiser "
+                                      "(the reference's other branches read undefined names, model_AMD.py:2264-2272)")
+        lo, _hi = freq_split_gauss(video_1.float().permute(0, 2, 1, 3, 4).contiguous(), 0.5, 0.5)
+        lf_video = lo.permute(0, 2, 1, 3, 4).contiguous()
+        if self.use_camera_down:
+            lf = self._camera_down(lf_video.view(n * t, c, h, w))
+            lf_video = lf.view(n, t, *lf.shape[1:])
+        cam = self.camera_motion_encoder(lf_video, camera_mask_ratio)
+        zi, zj = ref_img.flatten(0, 1).float().contiguous(), video_2.flatten(0, 1).float().contiguous()
+        zi, zt, zj, meta = self._euler(zi, zj, cam, None, None, start_step, sample_step, return_meta_info)
         shp = (n, t) + tuple(zi.shape[1:])
         zi, zt, zj = zi.view(shp), zt.view(shp), zj.view(shp)
         if return_meta_info:
-            return {"zi": zi, "zj": zj, "sample": zt, "pre_cache": pre_cache, "sample_cache": sample_cache,
-                    "step_seq": step_seq}
+            return dict(meta, zi=zi, zj=zj, sample=zt)
         return zi, zt, zj
+
+    @torch.no_grad()
+    def sample_with_refimg_motion(self, ref_img, camera_target_motion=None, object_target_motion=None, sample_step=10,
+                                  return_meta_info=False, ref_img_grey=None):
+        """model_AMD.py:2701-2785: generate from given target motions; the object SOURCE motion comes from the high
+        band (cut-off 0.6 over the t-frame volume) of `ref_img_grey`.  Returns (zi, zt, zj) with zj left flat
+        (n*t, c, h, w) as the reference does (2774-2775 rearrange only zi and zt)."""
+        if return_meta_info:
+            raise NameError("name 'target_motion' is not defined (the reference's meta-info branch, model_AMD.py:2782)")
+        n, t, c, h, w = ref_img.shape
+        start_step = self.scheduler.num_step
+        _lo, hi = freq_split_gauss(ref_img_grey.float().permute(0, 2, 1, 3, 4).contiguous(), 0.6, 0.6)
+        hf_refimg = hi.permute(0, 2, 1, 3, 4).contiguous()
+        osrc = self.object_motion_encoder(hf_refimg).flatten(0, 1).contiguous()
+        assert osrc.shape == object_target_motion.shape, \
+            f"object_source_motion.shape {osrc.shape} != object_target_motion.shape {object_target_motion.shape}"
+        zi = ref_img.flatten(0, 1).float().contiguous()
+        zi, zt, zj, _meta = self._euler(zi, zi, camera_target_motion, osrc, object_target_motion, start_step, sample_step, False)
+        shp = (n, t) + tuple(zi.shape[1:])
+        return zi.view(shp), zt.view(shp), zj
 
     @torch.no_grad()
     def sample(self, video, ref_img, video_grey=None, ref_img_grey=None, sample_step=50, object_mask_ratio=None,

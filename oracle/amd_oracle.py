@@ -379,6 +379,25 @@ class AMDOracle:
         cam, osrc, otgt = self.encode(video, ref_img)
         return self.decode(video, ref_img, cam, osrc, otgt, start_step, sample_step, z0, trace)
 
+    def sample_cross(self, video_1, video_2, ref_img, sample_step=50, start_step=None, z0=None, trace=None):
+        """model_AMD.py:2198-2377 (use_filter, use_camera, use_grey=False): camera motion from the low band of
+        video_1 (cut-off 0.5 over its own t-frame volume, 2219-2221); the denoiser gets NO object motion (2349-2351)."""
+        n, t, c, h, w = video_1.shape
+        start_step = self.num_step if start_step is None else start_step
+        lo, _ = freq_split3d(video_1.permute(0, 2, 1, 3, 4), gaussian_lpf([t, h, w], 0.5, 0.5).to(video_1.device))
+        lf = camera_down(self.sd, "camera_down", lo.permute(0, 2, 1, 3, 4).flatten(0, 1))
+        cam = camera_encoder(self.sd, "camera_motion_encoder", lf.view(n, t, *lf.shape[1:]), self.eh, self.T, self.patch, self.nno)
+        return self.decode(video_2, ref_img, cam, None, None, start_step, sample_step, z0, trace)
+
+    def sample_with_refimg_motion(self, ref_img, cam, otgt, ref_img_grey, sample_step=10, z0=None):
+        """model_AMD.py:2701-2785: object source motion from the HIGH band (cut-off 0.6, t-frame volume) of
+        ref_img_grey; zj = zi; zj is returned flat (2774-2775)."""
+        n, t, c, h, w = ref_img.shape
+        _, hi = freq_split3d(ref_img_grey.permute(0, 2, 1, 3, 4), gaussian_lpf([t, h, w], 0.6, 0.6).to(ref_img.device))
+        osrc = object_encoder(self.sd, "object_motion_encoder", hi.permute(0, 2, 1, 3, 4), self.eh, self.patch, self.nno).flatten(0, 1)
+        zi, zt, zj = self.decode(ref_img, ref_img, cam, osrc, otgt, self.num_step, sample_step, z0)
+        return zi, zt, zj.flatten(0, 1)
+
     def forward(self, video, ref_img, time_step, z0=None):
         """Training forward (model_AMD.py:1844-2017) with an explicit per-frame time_step
         (b,) and noise z0; returns (pre, vel, loss dict)."""

@@ -49,6 +49,30 @@ def main():
         json.dump({k: list(v.shape) for k, v in m.state_dict().items()}, f, indent=0)
     print("written", os.path.join(OUT, "small_object_only.safetensors"))
     temporal_encoder(ref)
+    cross_and_refimg(ref)
+
+
+def cross_and_refimg(ref):
+    """a18: AMDModel_New.sample_cross (model_AMD.py:2198-2377) and .sample_with_refimg_motion (2701-2785), small config"""
+    cfg = configs.SMALL
+    m, sd = build_ref_model(ref, cfg, seed=0)
+    orc = O.AMDOracle(sd, cfg["enc_nhead"], cfg["diffusion_attn_num_heads"], 16, 2, cfg["motion_token_num"])
+    v1, ref_img = synth.split_clip(synth.synth_clip_latents(1, seed=1))
+    v2, _ = synth.split_clip(synth.synth_clip_latents(1, seed=4))
+    z0 = torch.randn(16, 4, 32, 32, generator=torch.Generator().manual_seed(2))
+    orig = m.scheduler.get_train_tuple
+    m.scheduler.get_train_tuple = lambda z0_=None, z1=None, time_step=None: orig(z0=z0, z1=z1, time_step=time_step)
+    zi, zt, zj = m.sample_cross(v1, v2, ref_img, sample_step=3)
+    ozi, ozt, ozj = orc.sample_cross(v1, v2, ref_img, sample_step=3, z0=z0)
+    check("sample_cross zt", ozt, zt), check("sample_cross zj", ozj, zj)
+    cam, osrc, otgt = m.encode(v2, ref_img)
+    grey = ref_img * 0.5 + v2 * 0.25  # any (n, t, c, h, w) tensor serves as the "grey" reference clip
+    ri, rt, rj = m.sample_with_refimg_motion(ref_img, cam, otgt, sample_step=3, ref_img_grey=grey)
+    oi, ot, oj = orc.sample_with_refimg_motion(ref_img, cam, otgt, grey, sample_step=3, z0=z0)
+    check("refimg_motion zt", ot, rt)
+    assert rj.shape == oj.shape == (16, 4, 32, 32)
+    save_file({k: v.contiguous() for k, v in dict(z0=z0, cross_zt=zt, cam=cam, otgt=otgt, grey=grey, refimg_zt=rt).items()},
+              os.path.join(OUT, "small_cross_refimg.safetensors"))
 
 
 TENC = dict(img_height=32, img_width=32, img_inchannel=4, img_patch_size=2, motion_token_num=4, motion_channel=16,

@@ -488,6 +488,25 @@ def test_temporal_motion_encoder_golden(dev, golden, dtype, tol):
         assert rel(y, g["y%d" % n]) <= tol, n
 
 
+def test_small_model_sample_cross_and_refimg_motion(dev, golden):
+    """a18: AMDModel_New.sample_cross (model_AMD.py:2198-2377; camera motion of video_1, no object motion in the
+    denoiser) and .sample_with_refimg_motion (2701-2785; object source motion from the high band of the grey
+    reference) against the unmodified reference, fp32."""
+    g = golden("small_cross_refimg")
+    m, _ = _small(dev)
+    v1, ref_img = (t.to(dev) for t in synth.split_clip(synth.synth_clip_latents(1, seed=1)))
+    v2 = synth.split_clip(synth.synth_clip_latents(1, seed=4))[0].to(dev)
+    _fix_noise(m, g["z0"])
+    zi, zt, zj = m.sample_cross(v1, v2, ref_img, sample_step=3)
+    assert rel(zt, g["cross_zt"]) <= TOL_F32 and torch.equal(zj, v2) and torch.equal(zi, ref_img)
+    ri, rt, rj = m.sample_with_refimg_motion(ref_img, g["cam"].to(dev), g["otgt"].to(dev), sample_step=3,
+                                             ref_img_grey=g["grey"].to(dev))
+    assert rel(rt, g["refimg_zt"]) <= TOL_F32
+    assert rj.shape == (16, 4, 32, 32) and ri.shape == rt.shape == (1, 16, 4, 32, 32)  # zj stays flat (2774-2775)
+    with pytest.raises(NameError):
+        m.sample_with_refimg_motion(ref_img, g["cam"].to(dev), g["otgt"].to(dev), return_meta_info=True, ref_img_grey=ref_img)
+
+
 def _default(dev, dtype):
     import hivae_b200 as hv
     m = hv.AMDModel_New(**configs.DEFAULT)
