@@ -269,6 +269,12 @@ def run_ours(args):
                     "peak_source": pk["src"] + " sustained bf16 (kernel timed inside a long step)",
                     "launches": g["launches"], "avg_launch_ms": round(g["ms"] / g["launches"], 4),
                     "share_of_step": round(g["ms"] / tot, 4), "traffic": None}
+            try:  # DRAM bytes of one launch from the committed ncu --set full capture (not measurable live)
+                with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")) as f:
+                    t = json.load(f)["gemm_tc_kernel"]
+                roof.update(traffic=t["dram_bytes_per_launch"], traffic_launch=t["launch"], traffic_algorithmic=t["algorithmic_bytes"])
+            except (OSError, KeyError, ValueError):
+                pass
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
