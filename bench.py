@@ -188,6 +188,7 @@ def run_ours(args):
     dist = None
     if world > 1:
         import torch.distributed as dist
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keeps NCCL's version banner off stdout (one JSON line)
         dist.init_process_group("nccl", device_id=dev)
     torch.set_grad_enabled(False)
 

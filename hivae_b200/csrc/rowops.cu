@@ -67,64 +67,79 @@ __global__ void __launch_bounds__(256) ln_modulate_kernel(
         }
 }
 
-// Two rows per warp, 16 consecutive rows per CTA.  The LayerNorm affine and the adaLN shift / scale of a CTA's rows
-// almost always come from ONE (frame, segment) pair; the CTA then folds them once into A = w (1 + scale),
-// B = b (1 + scale) + shift in shared memory and every row is y = xhat * A + B: 8 KB of parameter reads per CTA
-// instead of 16 KB per row through L1 (x itself is only 4 KB per row).  CTAs that straddle a frame / segment
-// boundary (about 1 in 8) take the unfolded path with the reference's operation order.
+// Two rows per warp, up to 16 consecutive rows per CTA.  With adaLN the CTAs are aligned to (frame, segment):
+// a frame's row range splits into [motion | image | motion] segments (any of them may be empty) and a CTA never
+// crosses a segment, so its rows share ONE conditioning set.  The CTA folds the LayerNorm affine and the adaLN
+// shift / scale once into A = w (1 + scale), B = b (1 + scale) + shift in shared memory and every row is
+// y = xhat * A + B: 16 KB of parameter reads per CTA instead of per row (x itself is only 4 KB per row).
+// Without adaLN the rows are simply taken 16 at a time (A = w, B = b).
+// The row loads are issued first so that their DRAM round trip overlaps the parameter fold.
+struct LnSeg {
+    int ga, gb, gc;  // CTAs per frame for the three segments (0 when ada == nullptr: flat mapping)
+    int a, b, c;     // segment lengths: rows [row_off, img_start), [img_start, img_start+img_len), rest
+};
+
 template <int NV, typename OutT>
 __global__ void __launch_bounds__(256, 2) ln_modulate2_kernel(
     const float* __restrict__ res, long long rows, HvRowMap map, int D,
     const float* __restrict__ ln_w, const float* __restrict__ ln_b, float eps,
     const float* __restrict__ ada, long long ada_ld, int shift_col_mot, int scale_col_mot,
     int shift_col_img, int scale_col_img, int img_start, int img_len, int cond_div, int cond_mul,
-    OutT* __restrict__ out) {
+    LnSeg sg, OutT* __restrict__ out) {
     __shared__ float4 sA[NV * 32], sB[NV * 32];
-    const int lane = threadIdx.x & 31;
-    const long long rb = blockIdx.x * 16ll;                       // first row of the CTA
-    const long long r0 = rb + 2 * (threadIdx.x >> 5);
-    const bool valid = r0 < rows, two = r0 + 1 < rows;
-    auto params = [&](long long r, const float4*& sh, const float4*& sc) {
-        int f, a;
-        map.res_row(r, f, a);
-        const bool img = (a >= img_start) && (a < img_start + img_len);
-        const float* rowp = ada + (long long)((f / cond_div) * cond_mul) * ada_ld;
-        sh = reinterpret_cast<const float4*>(rowp + (img ? shift_col_img : shift_col_mot));
-        sc = reinterpret_cast<const float4*>(rowp + (img ? scale_col_img : scale_col_mot));
-    };
-    const float4* wp = reinterpret_cast<const float4*>(ln_w);
-    const float4* bp = reinterpret_cast<const float4*>(ln_b);
-    // ---- CTA-uniform: do all rows of this CTA share one parameter set?
-    bool folded = true;  // plain LayerNorm: A = w, B = b
-    const float4 *shf = nullptr, *scf = nullptr;
+    const int lane = threadIdx.x & 31, k0 = 2 * (threadIdx.x >> 5);
+    // ---- which rows does this CTA own?  (dense output row, residual-buffer row, count)
+    long long rd, rr;   // first dense row / first residual row of the CTA
+    int cnt;            // rows of the CTA (<= 16)
+    bool img = false;
+    int frame = 0;
     if (ada != nullptr) {
-        const long long rl = rb + 15 < rows ? rb + 15 : rows - 1;
-        const float4 *shl, *scl;
-        params(rb, shf, scf);
-        params(rl, shl, scl);
-        folded = shf == shl && scf == scl;
+        const int G = sg.ga + sg.gb + sg.gc;
+        frame = blockIdx.x / G;
+        int g = blockIdx.x - frame * G, abs0, len;
+        if (g < sg.ga) { abs0 = map.row_off; len = sg.a; }
+        else if (g < sg.ga + sg.gb) { g -= sg.ga; abs0 = img_start; len = sg.b; img = true; }
+        else { g -= sg.ga + sg.gb; abs0 = img_start + img_len; len = sg.c; }
+        const int i0 = g * 16;
+        cnt = len - i0 < 16 ? len - i0 : 16;
+        rr = (long long)frame * map.frame_rows + abs0 + i0;
+        rd = (long long)frame * map.L + (abs0 - map.row_off) + i0;
+    } else {
+        rd = blockIdx.x * 16ll;
+        cnt = rows - rd < 16 ? (int)(rows - rd) : 16;
+        int f, a;
+        rr = map.res_row(rd, f, a);
+        if (a + cnt > map.row_off + map.L) rr = -1;  // the 16 rows cross a frame of a non-dense range: per-row mapping below
     }
-    {
-        if (folded) {
-            for (int c4 = threadIdx.x; c4 < NV * 32; c4 += 256) {
-                const float4 w = wp ? __ldg(wp + c4) : make_float4(1.f, 1.f, 1.f, 1.f);
-                const float4 b = bp ? __ldg(bp + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
-                const float4 s = scf ? __ldg(scf + c4) : make_float4(0.f, 0.f, 0.f, 0.f), t = shf ? __ldg(shf + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
-                sA[c4] = make_float4(w.x * (1.f + s.x), w.y * (1.f + s.y), w.z * (1.f + s.z), w.w * (1.f + s.w));
-                sB[c4] = make_float4(fmaf(b.x, 1.f + s.x, t.x), fmaf(b.y, 1.f + s.y, t.y), fmaf(b.z, 1.f + s.z, t.z), fmaf(b.w, 1.f + s.w, t.w));
-            }
-        }
-    }
+    const bool valid = k0 < cnt, two = k0 + 1 < cnt;
     float4 u[NV], v[NV];
     if (valid) {
-        int f, a;
-        const float4* x0 = reinterpret_cast<const float4*>(res + map.res_row(r0, f, a) * D);
-        const float4* x1 = two ? reinterpret_cast<const float4*>(res + map.res_row(r0 + 1, f, a) * D) : x0;
+        long long ra = rr + k0, rb2 = rr + k0 + 1;
+        if (rr < 0) { int f, a; ra = map.res_row(rd + k0, f, a); rb2 = two ? map.res_row(rd + k0 + 1, f, a) : ra; }
+        const float4* x0 = reinterpret_cast<const float4*>(res + ra * D);
+        const float4* x1 = two ? reinterpret_cast<const float4*>(res + rb2 * D) : x0;
 #pragma unroll
         for (int j = 0; j < NV; ++j) { u[j] = x0[j * 32 + lane]; v[j] = x1[j * 32 + lane]; }
     } else {
 #pragma unroll
         for (int j = 0; j < NV; ++j) u[j] = v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    {
+        const float4* wp = reinterpret_cast<const float4*>(ln_w);
+        const float4* bp = reinterpret_cast<const float4*>(ln_b);
+        const float4 *shf = nullptr, *scf = nullptr;
+        if (ada != nullptr) {
+            const float* rowp = ada + (long long)((frame / cond_div) * cond_mul) * ada_ld;
+            shf = reinterpret_cast<const float4*>(rowp + (img ? shift_col_img : shift_col_mot));
+            scf = reinterpret_cast<const float4*>(rowp + (img ? scale_col_img : scale_col_mot));
+        }
+        for (int c4 = threadIdx.x; c4 < NV * 32; c4 += 256) {
+            const float4 w = wp ? __ldg(wp + c4) : make_float4(1.f, 1.f, 1.f, 1.f);
+            const float4 b = bp ? __ldg(bp + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 s = scf ? __ldg(scf + c4) : make_float4(0.f, 0.f, 0.f, 0.f), t = shf ? __ldg(shf + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            sA[c4] = make_float4(w.x * (1.f + s.x), w.y * (1.f + s.y), w.z * (1.f + s.z), w.w * (1.f + s.w));
+            sB[c4] = make_float4(fmaf(b.x, 1.f + s.x, t.x), fmaf(b.y, 1.f + s.y, t.y), fmaf(b.z, 1.f + s.z, t.z), fmaf(b.w, 1.f + s.w, t.w));
+        }
     }
     const float inv_d = 1.0f / (float)D;
     float su = 0.f, sv = 0.f;
@@ -146,43 +161,18 @@ __global__ void __launch_bounds__(256, 2) ln_modulate2_kernel(
         if constexpr (sizeof(OutT) == 4) reinterpret_cast<float4*>(o)[c4] = y;
         else reinterpret_cast<uint2*>(o)[c4] = make_uint2(hv_pack_bf16(y.x, y.y), hv_pack_bf16(y.z, y.w));
     };
-    if (folded) {
-#pragma unroll
-        for (int j = 0; j < NV; ++j) {
-            const int c4 = j * 32 + lane;
-            const float4 A = sA[c4], B = sB[c4];
-            float4 y, z;
-            y.x = fmaf((u[j].x - mu) * ru, A.x, B.x); y.y = fmaf((u[j].y - mu) * ru, A.y, B.y);
-            y.z = fmaf((u[j].z - mu) * ru, A.z, B.z); y.w = fmaf((u[j].w - mu) * ru, A.w, B.w);
-            z.x = fmaf((v[j].x - mv) * rv, A.x, B.x); z.y = fmaf((v[j].y - mv) * rv, A.y, B.y);
-            z.z = fmaf((v[j].z - mv) * rv, A.z, B.z); z.w = fmaf((v[j].w - mv) * rv, A.w, B.w);
-            emit(out + r0 * D, c4, y);
-            if (two) emit(out + (r0 + 1) * D, c4, z);
-        }
-        return;
-    }
-    const float4 *sh0 = nullptr, *sc0 = nullptr, *sh1 = nullptr, *sc1 = nullptr;
-    if (ada != nullptr) {
-        params(r0, sh0, sc0);
-        params(two ? r0 + 1 : r0, sh1, sc1);
-    }
-    const bool same = sh0 == sh1 && sc0 == sc1;  // warp-uniform
+    OutT* o0 = out + (rd + k0) * D;
 #pragma unroll
     for (int j = 0; j < NV; ++j) {
         const int c4 = j * 32 + lane;
+        const float4 A = sA[c4], B = sB[c4];
         float4 y, z;
-        y.x = (u[j].x - mu) * ru; y.y = (u[j].y - mu) * ru; y.z = (u[j].z - mu) * ru; y.w = (u[j].w - mu) * ru;
-        z.x = (v[j].x - mv) * rv; z.y = (v[j].y - mv) * rv; z.z = (v[j].z - mv) * rv; z.w = (v[j].w - mv) * rv;
-        if (wp) { const float4 w = __ldg(wp + c4); y.x *= w.x; y.y *= w.y; y.z *= w.z; y.w *= w.w; z.x *= w.x; z.y *= w.y; z.z *= w.z; z.w *= w.w; }
-        if (bp) { const float4 b = __ldg(bp + c4); y.x += b.x; y.y += b.y; y.z += b.z; y.w += b.w; z.x += b.x; z.y += b.y; z.z += b.z; z.w += b.w; }
-        if (sh0) {
-            float4 s = __ldg(sc0 + c4), t = __ldg(sh0 + c4);
-            y.x = y.x * (1.f + s.x) + t.x; y.y = y.y * (1.f + s.y) + t.y; y.z = y.z * (1.f + s.z) + t.z; y.w = y.w * (1.f + s.w) + t.w;
-            if (!same) { s = __ldg(sc1 + c4); t = __ldg(sh1 + c4); }
-            z.x = z.x * (1.f + s.x) + t.x; z.y = z.y * (1.f + s.y) + t.y; z.z = z.z * (1.f + s.z) + t.z; z.w = z.w * (1.f + s.w) + t.w;
-        }
-        emit(out + r0 * D, c4, y);
-        if (two) emit(out + (r0 + 1) * D, c4, z);
+        y.x = fmaf((u[j].x - mu) * ru, A.x, B.x); y.y = fmaf((u[j].y - mu) * ru, A.y, B.y);
+        y.z = fmaf((u[j].z - mu) * ru, A.z, B.z); y.w = fmaf((u[j].w - mu) * ru, A.w, B.w);
+        z.x = fmaf((v[j].x - mv) * rv, A.x, B.x); z.y = fmaf((v[j].y - mv) * rv, A.y, B.y);
+        z.z = fmaf((v[j].z - mv) * rv, A.z, B.z); z.w = fmaf((v[j].w - mv) * rv, A.w, B.w);
+        emit(o0, c4, y);
+        if (two) emit(o0 + D, c4, z);
     }
 }
 
@@ -205,9 +195,20 @@ extern "C" int hv_ln_modulate(const float* res, int64_t frames, int64_t frame_ro
     const int nv = D / 128;
     cudaStream_t st = hv_stream(stream);
 #define LN_ARGS res, rows, map, D, ln_w, ln_b, eps, ada, ada_ld, shift_col_mot, scale_col_mot, shift_col_img, scale_col_img, \
-                img_start, img_len, cond_div, cond_mul
+                img_start, img_len, cond_div, cond_mul, sg
     if (nv == 8 || nv == 4) {  // D = 1024 / 512 (the DiT and the encoders): two rows per warp
-        dim3 grid((unsigned)((rows + 15) / 16)), block(256);
+        LnSeg sg{0, 0, 0, 0, 0, 0};
+        long long ctas = (rows + 15) / 16;
+        if (ada) {  // segment-aligned CTAs: [row_off, img_start) | [img_start, img_start + img_len) | rest, clipped to the range
+            const int lo = row_off, hi = row_off + L;
+            const int is = img_start < lo ? lo : (img_start > hi ? hi : img_start);
+            const int ie = img_start + img_len < is ? is : (img_start + img_len > hi ? hi : img_start + img_len);
+            sg.a = is - lo; sg.b = ie - is; sg.c = hi - ie;
+            sg.ga = (sg.a + 15) / 16; sg.gb = (sg.b + 15) / 16; sg.gc = (sg.c + 15) / 16;
+            ctas = (long long)frames * (sg.ga + sg.gb + sg.gc);
+            img_start = is; img_len = sg.b;  // the kernel derives the segment starts from these
+        }
+        dim3 grid((unsigned)ctas), block(256);
         if (out_dtype == HV_F32) { if (nv == 8) ln_modulate2_kernel<8, float><<<grid, block, 0, st>>>(LN_ARGS, (float*)out); else ln_modulate2_kernel<4, float><<<grid, block, 0, st>>>(LN_ARGS, (float*)out); }
         else { if (nv == 8) ln_modulate2_kernel<8, __nv_bfloat16><<<grid, block, 0, st>>>(LN_ARGS, (__nv_bfloat16*)out); else ln_modulate2_kernel<4, __nv_bfloat16><<<grid, block, 0, st>>>(LN_ARGS, (__nv_bfloat16*)out); }
         HV_LAUNCH_CHECK();

@@ -17,6 +17,7 @@ rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1
 dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0)))
 torch.cuda.set_device(dev)
 if world > 1:
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     dist.init_process_group("nccl", device_id=dev)
 N = int(float(os.environ.get("NPARAM", 695e6)))
 p = torch.nn.Parameter(torch.randn(N, device=dev) * 0.02)
