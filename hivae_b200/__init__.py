@@ -14,7 +14,8 @@ from .modules import (BasicTransformerBlock, BasicCrossTransformerBlock, AMDTran
                       PatchEmbed, AMDLayerNormZero, AMDLayerNormZero_OneVariable, AdaLayerNorm, AMDTransformerMotionBlock)
 from .transformer import (MotionEncoderLearnTokenTransformer, MotionEncoderLearnTokenOnlyTemporalTransformer,  # noqa: F401
                           MotionEncoderLearnTokenTemporalTransformer,
-                          AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion)
+                          AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion,
+                          AMDDiffusionTransformerModelImgSpatial)
 from .model_AMD import AMDModel_New, AMD_N, AMD_models  # noqa: F401
 from . import sharding  # noqa: F401
 from . import optim  # noqa: F401

@@ -488,3 +488,151 @@ class AMDDiffusionTransformerModelTempMotion(AMDDiffusionTransformerModelImgSpat
                 object_motion_target_hidden_states=None, return_dict=True):
         return super().forward(image_hidden_states, timestep, timestep_cond, None, object_motion_source_hidden_states,
                                object_motion_target_hidden_states, return_dict)
+
+
+# ================================================================================================
+class AMDDiffusionTransformerModelImgSpatial(_HvModule):
+    """The single-motion-stream sibling of the default denoiser (transformer.py:2044-2356; AMDModel's
+    diffusion_model_type='spatial'): ONE `motion_patch_embed` and ONE stack of joint `transformer_blocks`, each
+    followed by a temporal `spatial_blocks[i]`.
+
+    motion_type='plus'     : the motion stream is [source_token | object source | target_token | object target].
+    motion_type='decouple' : the stream starts as the camera tokens ([source_token | camera source | target_token |
+                             camera target], or [target_token | camera target] without a camera source); when object
+                             motions are given, layers 0-5 run on the camera stream, then the camera rows are
+                             REPLACED by the object tokens (the evolved source/target tokens stay) and layers >= 6
+                             run on that stream (2259-2322).  The reference forms the object TARGET rows from the
+                             object SOURCE embedding (2262-2263); that is reproduced.
+    All streams live in one fp32 frames buffer (rows [0, 2L+2) motion, then the image rows), so the swap is two
+    small row scatters and no block ever concatenates anything."""
+
+    def __init__(self, num_attention_heads=20, attention_head_dim=64, out_channels: Optional[int] = 4, num_layers=12,
+                 motion_type="plus", image_width=32, image_height=32, image_patch_size=2,
+                 image_in_channels: Optional[int] = 4, motion_token_num=12, motion_in_channels: Optional[int] = 128,
+                 motion_target_num_frame=16, flip_sin_to_cos=True, freq_shift=0, time_embed_dim=512, dropout=0.0,
+                 attention_bias=True, temporal_compression_ratio=4, activation_fn="gelu-approximate",
+                 timestep_activation_fn="silu", norm_elementwise_affine=True, norm_eps=1e-5,
+                 spatial_interpolation_scale=1.0, temporal_interpolation_scale=1.0):
+        super().__init__()
+        hidden_dim = num_attention_heads * attention_head_dim
+        iph, ipw = image_height // image_patch_size, image_width // image_patch_size
+        self.image_patch_size, self.out_channels = image_patch_size, out_channels
+        self.target_frame, self.motion_type = motion_target_num_frame, motion_type
+        self.image_patch_embed = PatchEmbed(patch_size=image_patch_size, in_channels=image_in_channels,
+                                            embed_dim=hidden_dim, bias=True)
+        self.motion_patch_embed = nn.Linear(motion_in_channels, hidden_dim)
+        self.embedding_dropout = nn.Dropout(dropout)
+        self.register_buffer("pos_embedding", E.table(E.sincos_2d(hidden_dim, iph, ipw)), persistent=False)
+        self.register_buffer("motion_pos_embedding", E.table(E.sincos_1d(hidden_dim, np.arange(2 + 2 * motion_token_num))),
+                             persistent=False)
+        self.register_buffer("img_temporal_embedding", E.table(E.sincos_1d(hidden_dim, np.arange(self.target_frame))),
+                             persistent=False)
+        self.source_token = nn.Parameter(torch.zeros(1, 1, hidden_dim), requires_grad=True)
+        self.target_token = nn.Parameter(torch.zeros(1, 1, hidden_dim), requires_grad=True)
+        self.time_proj = Timesteps(hidden_dim, flip_sin_to_cos, freq_shift)
+        self.time_embedding = TimestepEmbedding(hidden_dim, time_embed_dim, timestep_activation_fn)
+        blk = dict(dim=hidden_dim, num_attention_heads=num_attention_heads, attention_head_dim=attention_head_dim,
+                   time_embed_dim=time_embed_dim, dropout=dropout, activation_fn=activation_fn,
+                   attention_bias=attention_bias, norm_elementwise_affine=norm_elementwise_affine, norm_eps=norm_eps)
+        self.transformer_blocks = nn.ModuleList([AMDTransformerBlock(**blk) for _ in range(num_layers)])
+        self.spatial_blocks = nn.ModuleList([BasicDiTBlock(**blk) for _ in range(num_layers)])
+        self.norm_final = nn.LayerNorm(hidden_dim, norm_eps, norm_elementwise_affine)
+        self.norm_out = AdaLayerNorm(embedding_dim=time_embed_dim, output_dim=2 * hidden_dim,
+                                     norm_elementwise_affine=norm_elementwise_affine, norm_eps=norm_eps, chunk_dim=1)
+        self.proj_out = nn.Linear(hidden_dim, image_patch_size * image_patch_size * out_channels)
+        self.gradient_checkpointing = False
+
+    def _prepare(self, ctx):
+        P = _Prepared()
+        P.ctx = ctx
+        P.joint = [engine.prepare_block(ctx, b, "joint") for b in self.transformer_blocks]
+        P.sp = [engine.prepare_block(ctx, b, "dit") for b in self.spatial_blocks]
+        order = [bp for pair in zip(P.joint, P.sp) for bp in pair]
+        P.ada = AdaPack(ctx, order, extra=[(self.norm_out.linear.weight, self.norm_out.linear.bias)])
+        P.pw, P.pb = self._patch_params(ctx, self.image_patch_embed)
+        P.pos, P.tpos = ctx.f32(self.pos_embedding[0]), ctx.f32(self.img_temporal_embedding[0])
+        P.mpos = ctx.f32(self.motion_pos_embedding[0])
+        te = self.time_embedding
+        P.tw1, P.tb1 = ctx.weight(te.linear_1.weight), ctx.f32(te.linear_1.bias)
+        P.tw2, P.tb2 = ctx.weight(te.linear_2.weight), ctx.f32(te.linear_2.bias)
+        P.mw, P.mb = ctx.f32(self.motion_patch_embed.weight), ctx.f32(self.motion_patch_embed.bias)
+        P.stok, P.ttok = ctx.f32(self.source_token[0]), ctx.f32(self.target_token[0])
+        P.nfw, P.nfb = ctx.f32(self.norm_final.weight), ctx.f32(self.norm_final.bias)
+        P.now, P.nob = ctx.f32(self.norm_out.norm.weight), ctx.f32(self.norm_out.norm.bias)
+        P.hw, P.hb = ctx.f32(self.proj_out.weight), ctx.f32(self.proj_out.bias)
+        return P
+
+    @torch.no_grad()
+    def forward(self, camera_motion_target_hidden_states, image_hidden_states, timestep, timestep_cond=None,
+                camera_motion_source_hidden_states=None, object_motion_source_hidden_states=None,
+                object_motion_target_hidden_states=None, return_dict=True):
+        N, Ci, Hi, Wi = image_hidden_states.shape
+        _, L, Cm = camera_motion_target_hidden_states.shape
+        P = self._prepared(image_hidden_states.device)
+        ctx = P.ctx
+        T, p = self.target_frame, self.image_patch_size
+        n, D, S = N // T, P.hw.shape[1], (Hi // p) * (Wi // p)
+        LM = 2 * L + 2
+        FR = LM + S
+        res = ctx.buf("dits_res", (N, FR, D), torch.float32)
+        emb_m = lambda x, name: engine.small_linear(ctx, x.reshape(N * L, Cm).float().contiguous(), P.mw, P.mb, name)
+        obj = object_motion_source_hidden_states is not None
+        cam_src = camera_motion_source_hidden_states is not None
+
+        def put_tokens(src_rows, tgt_rows, pos_src, pos_tgt):
+            """rows 1..L <- src_rows + pos_src, rows L+2.. <- tgt_rows + pos_tgt  (either may be None)"""
+            if src_rows is not None:
+                ops.rows_scatter(src_rows, L, 1, pos_src, Rows(res, 1, L))
+            if tgt_rows is not None:
+                ops.rows_scatter(tgt_rows, L, 1, pos_tgt, Rows(res, L + 2, L))
+
+        if self.motion_type == "plus":
+            put_tokens(emb_m(object_motion_source_hidden_states, "dits_s"), emb_m(object_motion_target_hidden_states, "dits_t"),
+                       P.mpos[1:1 + L], P.mpos[L + 2:LM])
+            ops.rows_scatter(P.stok, 0, 0, P.mpos[0:1], Rows(res, 0, 1))
+            ops.rows_scatter(P.ttok, 0, 0, P.mpos[L + 1:L + 2], Rows(res, L + 1, 1))
+            phases = [(0, 0, len(P.joint))]                              # (first motion row, first layer, last layer)
+        elif self.motion_type == "decouple":
+            ct = emb_m(camera_motion_target_hidden_states, "dits_ct")
+            if cam_src:
+                put_tokens(emb_m(camera_motion_source_hidden_states, "dits_cs"), ct, P.mpos[1:1 + L], P.mpos[L + 2:LM])
+                ops.rows_scatter(P.stok, 0, 0, P.mpos[0:1], Rows(res, 0, 1))
+                ops.rows_scatter(P.ttok, 0, 0, P.mpos[L + 1:L + 2], Rows(res, L + 1, 1))
+                off = 0
+            else:  # [target_token | camera target] + pos[:L+1], kept right-aligned next to the image rows
+                put_tokens(None, ct, None, P.mpos[1:1 + L])
+                ops.rows_scatter(P.ttok, 0, 0, P.mpos[0:1], Rows(res, L + 1, 1))
+                off = L + 1
+            phases = [(off, 0, 6), (0, 6, len(P.joint))] if obj else [(off, 0, len(P.joint))]
+        else:
+            raise UnboundLocalError("motion_hidden_states")  # the reference leaves it undefined for other motion types
+        x = image_hidden_states.float().contiguous()
+        ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, P.tpos, res, FR, LM, D)
+        if not torch.is_tensor(timestep):
+            timestep = torch.full((N,), float(timestep), device=x.device)
+        ts = timestep.to(device=x.device, dtype=torch.float32).contiguous()
+        te = ops.timestep_embed(ts, D, ctx.buf("dits_te", (N, D)))
+        h = engine.small_linear(ctx, te, P.tw1, P.tb1, "dits_te_h")
+        emb = engine.small_linear(ctx, ops.silu(h, ctx.buf("dits_te_hs", h.shape)), P.tw2, P.tb2, "dits_emb")
+        table = P.ada.table(ctx, emb, "dits_ada")
+        ada_f, ada_s = Ada(table, 1, 1), Ada(table, T, T)
+        img_rows, g_tmp = Rows(res, LM, S, img_start=LM, img_len=S), engine.strided_geom(n, S, T)
+        for k, (off, l0, l1) in enumerate(phases):
+            if k == 1:  # camera rows -> object tokens; row 0 only when there was no camera source (fresh source_token, no pos)
+                so = emb_m(object_motion_source_hidden_states, "dits_os")
+                src_pos = ctx.buf("dits_osp", (N * L, D), torch.float32)
+                tmp = Rows(src_pos.view(N, L, D), 0, L)
+                ops.rows_scatter(so, L, 1, P.mpos[1:1 + L], tmp)                 # object source + pos[1:L+1]
+                put_tokens(src_pos, src_pos, None, P.mpos[L + 2:LM])            # target rows = SOURCE + pos[L+2:] (2262-2263)
+                if not cam_src:
+                    ops.rows_scatter(P.stok, 0, 0, None, Rows(res, 0, 1))
+            rows = Rows(res, off, LM - off + S, img_start=LM, img_len=S)
+            geom = engine.dense_geom(N, LM - off + S)
+            for i in range(l0, min(l1, len(P.joint))):
+                engine.run_block(ctx, P.joint[i], rows, geom, ada_f)
+                engine.run_block(ctx, P.sp[i], img_rows, g_tmp, ada_s)
+        pre = torch.empty(N, self.out_channels, Hi, Wi, dtype=torch.float32, device=x.device)
+        o = P.ada.extra_off[0]
+        ops.final_head(img_rows, P.nfw, P.nfb, P.now, P.nob, self.norm_final.eps, ada_f, o, o + D,
+                       P.hw, P.hb, self.out_channels, p, Wi // p, pre, None, 0.0)
+        return pre.to(image_hidden_states.dtype)

@@ -331,6 +331,65 @@ def dit_forward(sd, p, image, timestep, cam, osrc, otgt, heads, T, patch=2, moti
     return out.reshape(N, C, Hi, Wi)
 
 
+def dit_imgspatial_forward(sd, p, cam_tgt, image, timestep, heads, T, patch=2, motion_token_num=12, motion_type="plus",
+                           cam_src=None, osrc=None, otgt=None):
+    """AMDDiffusionTransformerModelImgSpatial.forward (transformer.py:2186-2356): one motion stream; 'decouple'
+    with object motions swaps the camera rows for object tokens after layer 5 (2259-2322) and forms the object
+    target rows from the object SOURCE embedding (2262-2263)."""
+    N, Ci, Hi, Wi = image.shape
+    L = cam_tgt.shape[1]
+    n, dev = N // T, image.device
+    D = sd[p + ".image_patch_embed.proj.weight"].shape[0]
+    S = (Hi // patch) * (Wi // patch)
+    img = patch_embed(sd, p + ".image_patch_embed", image, patch)
+    emb = _lin(sd, p + ".time_embedding.linear_2", F.silu(_lin(sd, p + ".time_embedding.linear_1", timestep_embedding(timestep, D))))
+    emb_s = emb.view(n, T, -1)[:, :1].repeat(1, S, 1).flatten(0, 1)
+    mpos = torch.from_numpy(sincos_1d(D, np.arange(2 + 2 * motion_token_num))).float().to(dev)
+    stok, ttok = sd[p + ".source_token"].repeat(N, 1, 1), sd[p + ".target_token"].repeat(N, 1, 1)
+    me = lambda x: _lin(sd, p + ".motion_patch_embed", x)
+    if motion_type == "plus":
+        mo = torch.cat([stok, me(osrc), ttok, me(otgt)], 1) + mpos[None, :2 * L + 2]
+    else:
+        if cam_src is not None:
+            mo = torch.cat([stok, me(cam_src), ttok, me(cam_tgt)], 1) + mpos[None, :2 * L + 2]
+        else:
+            mo = torch.cat([ttok, me(cam_tgt)], 1) + mpos[None, :L + 1]
+        if osrc is not None:
+            o_s = me(osrc) + mpos[None, 1:L + 1]
+            o_t = o_s + mpos[None, L + 2:2 * L + 2]
+    pos = torch.from_numpy(sincos_2d(D, Hi // patch, Wi // patch)).float().to(dev)
+    tpos = torch.from_numpy(sincos_1d(D, np.arange(T))).float().to(dev)
+    img = ((img + pos[None]).view(n, T, S, D) + tpos[None, :, None]).view(N, S, D)
+    nl = _count_layers(sd, p + ".spatial_blocks")
+
+    def layer(i, mo, img):
+        mo, img = joint_block(sd, p + ".transformer_blocks.%d" % i, mo, img, emb, heads)
+        x = img.view(n, T, S, D).permute(0, 2, 1, 3).reshape(n * S, T, D)
+        x = dit_block(sd, p + ".spatial_blocks.%d" % i, x, emb_s, heads)
+        return mo, x.view(n, S, T, D).permute(0, 2, 1, 3).reshape(N, S, D)
+
+    if motion_type == "decouple" and osrc is not None:
+        for i in range(min(6, nl)):
+            mo, img = layer(i, mo, img)
+        if cam_src is not None:
+            s_tok, t_tok = mo[:, :1], mo[:, 1 + L:2 + L]
+        else:
+            s_tok, t_tok = stok, mo[:, :1]
+        mo = torch.cat([s_tok, o_s, t_tok, o_t], 1)
+        for i in range(6, nl):
+            mo, img = layer(i, mo, img)
+    else:
+        for i in range(nl):
+            mo, img = layer(i, mo, img)
+    img = _ln(sd, p + ".norm_final", img)
+    shift, scale = _lin(sd, p + ".norm_out.linear", F.silu(emb)).chunk(2, dim=1)
+    img = _ln(sd, p + ".norm_out.norm", img) * (1 + scale)[:, None] + shift[:, None]
+    out = _lin(sd, p + ".proj_out", img)
+    C = out.shape[-1] // (patch * patch)
+    out = out.reshape(N, Hi // patch, Wi // patch, C, patch, patch).permute(0, 3, 1, 4, 2, 5)
+    return out.reshape(N, C, Hi, Wi)
+
+
 # ----------------------------------------------------------------------------- model
 class AMDOracle:
     """AMDModel_New (model_AMD.py:1663-2838) for use_filter / use_camera_down /

@@ -50,6 +50,38 @@ def main():
     print("written", os.path.join(OUT, "small_object_only.safetensors"))
     temporal_encoder(ref)
     cross_and_refimg(ref)
+    imgspatial_dit(ref)
+
+
+DITS = dict(num_attention_heads=2, attention_head_dim=64, out_channels=4, num_layers=8, image_width=32, image_height=32,
+            image_patch_size=2, image_in_channels=8, motion_token_num=4, motion_in_channels=16, motion_target_num_frame=4)
+
+
+def imgspatial_dit(ref):
+    """a17 sibling AMDDiffusionTransformerModelImgSpatial (transformer.py:2044-2356): 'plus', and 'decouple' with and
+    without a camera source (8 layers so that the swap after layer 5 is exercised)."""
+    g = torch.Generator().manual_seed(21)
+    N, L = 8, 4  # two clips of four frames
+    image, ts = torch.randn(N, 8, 32, 32, generator=g), torch.tensor([900.0] * 4 + [350.0] * 4)
+    ct, cs, os_, ot = (torch.randn(N, L, 16, generator=g) for _ in range(4))
+    out = dict(image=image, ts=ts, ct=ct, cs=cs, os=os_, ot=ot)
+    for mt in ("plus", "decouple"):
+        torch.manual_seed(0)
+        m = ref.transformer.AMDDiffusionTransformerModelImgSpatial(motion_type=mt, **DITS).eval()
+        sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 5)
+        m.load_state_dict(sd)
+        osd = {"d." + k: v for k, v in sd.items()}
+        cases = {"plus": [("obj", None, os_, ot)], "decouple": [("cam", None, None, None), ("cam_obj", None, os_, ot), ("camsrc_obj", cs, os_, ot)]}[mt]
+        for name, c_src, o_s, o_t in cases:
+            y = m(ct, image, ts, camera_motion_source_hidden_states=c_src, object_motion_source_hidden_states=o_s,
+                  object_motion_target_hidden_states=o_t)
+            yo = O.dit_imgspatial_forward(osd, "d", ct, image, ts, 2, 4, 2, 4, mt, c_src, o_s, o_t)
+            check("ImgSpatial %s/%s" % (mt, name), yo, y)
+            out["y_%s_%s" % (mt, name)] = y.contiguous()
+    save_file(out, os.path.join(OUT, "imgspatial_dit.safetensors"))
+    with open(os.path.join(OUT, "state_dict_keys_imgspatial_dit.json"), "w") as f:
+        import json
+        json.dump({k: list(v.shape) for k, v in m.state_dict().items()}, f, indent=0)
 
 
 def cross_and_refimg(ref):

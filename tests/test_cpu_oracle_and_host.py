@@ -149,6 +149,19 @@ def test_state_dict_keys_temporal_encoder():
         hv.AMDTransformerMotionBlock(128, 2, 64, time_embed_dim=32)
 
 
+DITS = dict(num_attention_heads=2, attention_head_dim=64, out_channels=4, num_layers=8, image_width=32, image_height=32,
+            image_patch_size=2, image_in_channels=8, motion_token_num=4, motion_in_channels=16, motion_target_num_frame=4)  # = make_golden_variants.DITS
+
+
+def test_state_dict_keys_imgspatial_dit():
+    """a17 sibling AMDDiffusionTransformerModelImgSpatial (transformer.py:2044-2184): keys/shapes of the unmodified reference."""
+    import hivae_b200 as hv
+    with open(os.path.join(ROOT, "tests", "golden", "state_dict_keys_imgspatial_dit.json")) as f:
+        ref = json.load(f)
+    m = hv.AMDDiffusionTransformerModelImgSpatial(motion_type="decouple", **DITS)
+    assert {k: list(v.shape) for k, v in m.state_dict().items()} == ref
+
+
 def test_sincos_tables_match_oracle():
     from hivae_b200 import embeddings as E
     assert np.array_equal(E.sincos_2d(256, 16, 16), O.sincos_2d(256, 16, 16))

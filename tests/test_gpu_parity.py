@@ -507,6 +507,29 @@ def test_small_model_sample_cross_and_refimg_motion(dev, golden):
         m.sample_with_refimg_motion(ref_img, g["cam"].to(dev), g["otgt"].to(dev), return_meta_info=True, ref_img_grey=ref_img)
 
 
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_imgspatial_dit_golden(dev, golden, dtype, tol):
+    """a17 sibling AMDDiffusionTransformerModelImgSpatial (transformer.py:2044-2356) vs the unmodified reference:
+    'plus', 'decouple' camera-only, and 'decouple' with object motions (camera rows swapped for object tokens after
+    layer 5) with and without a camera source."""
+    import hivae_b200 as hv
+    from test_cpu_oracle_and_host import DITS
+    g = golden("imgspatial_dit")
+    t = lambda k: g[k].to(dev)
+    for mt, cases in (("plus", [("obj", None, "os", "ot")]),
+                      ("decouple", [("cam", None, None, None), ("cam_obj", None, "os", "ot"), ("camsrc_obj", "cs", "os", "ot")])):
+        m = hv.AMDDiffusionTransformerModelImgSpatial(motion_type=mt, **DITS)
+        m.load_state_dict(synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 5))
+        m.to(dev)
+        for sub in m.modules():
+            sub.hv_compute_dtype = dtype
+        for name, cs, os_, ot in cases:
+            y = m(t("ct"), t("image"), t("ts"), camera_motion_source_hidden_states=t(cs) if cs else None,
+                  object_motion_source_hidden_states=t(os_) if os_ else None,
+                  object_motion_target_hidden_states=t(ot) if ot else None)
+            assert rel(y, g["y_%s_%s" % (mt, name)]) <= tol, (mt, name)
+
+
 def _default(dev, dtype):
     import hivae_b200 as hv
     m = hv.AMDModel_New(**configs.DEFAULT)
