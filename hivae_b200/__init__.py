@@ -15,7 +15,7 @@ from .modules import (BasicTransformerBlock, BasicCrossTransformerBlock, AMDTran
 from .transformer import (MotionEncoderLearnTokenTransformer, MotionEncoderLearnTokenOnlyTemporalTransformer,  # noqa: F401
                           MotionEncoderLearnTokenTemporalTransformer,
                           AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion,
-                          AMDDiffusionTransformerModelImgSpatial)
+                          AMDDiffusionTransformerModelImgSpatial, AMDDiffusionTransformerModel)
 from .model_AMD import AMDModel_New, AMD_N, AMD_models  # noqa: F401
 from . import sharding  # noqa: F401
 from . import optim  # noqa: F401

@@ -506,6 +506,11 @@ class AMDDiffusionTransformerModelImgSpatial(_HvModule):
     All streams live in one fp32 frames buffer (rows [0, 2L+2) motion, then the image rows), so the swap is two
     small row scatters and no block ever concatenates anything."""
 
+    _has_temporal_blocks = True   # spatial_blocks[i] (attention over time) after every joint block
+    _camera_layers_end = 6        # 'decouple' with object motions: camera stream for layers [0, 6) ...
+    _object_layers_start = 6      # ... object stream for layers [6, n)
+    _plus_adds_camera = False     # 'plus' embeds the object tokens only (2231-2239)
+
     def __init__(self, num_attention_heads=20, attention_head_dim=64, out_channels: Optional[int] = 4, num_layers=12,
                  motion_type="plus", image_width=32, image_height=32, image_patch_size=2,
                  image_in_channels: Optional[int] = 4, motion_token_num=12, motion_in_channels: Optional[int] = 128,
@@ -525,8 +530,9 @@ class AMDDiffusionTransformerModelImgSpatial(_HvModule):
         self.register_buffer("pos_embedding", E.table(E.sincos_2d(hidden_dim, iph, ipw)), persistent=False)
         self.register_buffer("motion_pos_embedding", E.table(E.sincos_1d(hidden_dim, np.arange(2 + 2 * motion_token_num))),
                              persistent=False)
-        self.register_buffer("img_temporal_embedding", E.table(E.sincos_1d(hidden_dim, np.arange(self.target_frame))),
-                             persistent=False)
+        if self._has_temporal_blocks:
+            self.register_buffer("img_temporal_embedding", E.table(E.sincos_1d(hidden_dim, np.arange(self.target_frame))),
+                                 persistent=False)
         self.source_token = nn.Parameter(torch.zeros(1, 1, hidden_dim), requires_grad=True)
         self.target_token = nn.Parameter(torch.zeros(1, 1, hidden_dim), requires_grad=True)
         self.time_proj = Timesteps(hidden_dim, flip_sin_to_cos, freq_shift)
@@ -535,7 +541,8 @@ class AMDDiffusionTransformerModelImgSpatial(_HvModule):
                    time_embed_dim=time_embed_dim, dropout=dropout, activation_fn=activation_fn,
                    attention_bias=attention_bias, norm_elementwise_affine=norm_elementwise_affine, norm_eps=norm_eps)
         self.transformer_blocks = nn.ModuleList([AMDTransformerBlock(**blk) for _ in range(num_layers)])
-        self.spatial_blocks = nn.ModuleList([BasicDiTBlock(**blk) for _ in range(num_layers)])
+        if self._has_temporal_blocks:
+            self.spatial_blocks = nn.ModuleList([BasicDiTBlock(**blk) for _ in range(num_layers)])
         self.norm_final = nn.LayerNorm(hidden_dim, norm_eps, norm_elementwise_affine)
         self.norm_out = AdaLayerNorm(embedding_dim=time_embed_dim, output_dim=2 * hidden_dim,
                                      norm_elementwise_affine=norm_elementwise_affine, norm_eps=norm_eps, chunk_dim=1)
@@ -546,11 +553,12 @@ class AMDDiffusionTransformerModelImgSpatial(_HvModule):
         P = _Prepared()
         P.ctx = ctx
         P.joint = [engine.prepare_block(ctx, b, "joint") for b in self.transformer_blocks]
-        P.sp = [engine.prepare_block(ctx, b, "dit") for b in self.spatial_blocks]
-        order = [bp for pair in zip(P.joint, P.sp) for bp in pair]
+        P.sp = [engine.prepare_block(ctx, b, "dit") for b in self.spatial_blocks] if self._has_temporal_blocks else [None] * len(P.joint)
+        order = [bp for pair in zip(P.joint, P.sp) for bp in pair if bp is not None]
         P.ada = AdaPack(ctx, order, extra=[(self.norm_out.linear.weight, self.norm_out.linear.bias)])
         P.pw, P.pb = self._patch_params(ctx, self.image_patch_embed)
-        P.pos, P.tpos = ctx.f32(self.pos_embedding[0]), ctx.f32(self.img_temporal_embedding[0])
+        P.pos = ctx.f32(self.pos_embedding[0])
+        P.tpos = ctx.f32(self.img_temporal_embedding[0]) if self._has_temporal_blocks else None
         P.mpos = ctx.f32(self.motion_pos_embedding[0])
         te = self.time_embedding
         P.tw1, P.tb1 = ctx.weight(te.linear_1.weight), ctx.f32(te.linear_1.bias)
@@ -570,7 +578,7 @@ class AMDDiffusionTransformerModelImgSpatial(_HvModule):
         _, L, Cm = camera_motion_target_hidden_states.shape
         P = self._prepared(image_hidden_states.device)
         ctx = P.ctx
-        T, p = self.target_frame, self.image_patch_size
+        T, p = (self.target_frame if self._has_temporal_blocks else 1), self.image_patch_size
         n, D, S = N // T, P.hw.shape[1], (Hi // p) * (Wi // p)
         LM = 2 * L + 2
         FR = LM + S
@@ -587,8 +595,10 @@ class AMDDiffusionTransformerModelImgSpatial(_HvModule):
                 ops.rows_scatter(tgt_rows, L, 1, pos_tgt, Rows(res, L + 2, L))
 
         if self.motion_type == "plus":
-            put_tokens(emb_m(object_motion_source_hidden_states, "dits_s"), emb_m(object_motion_target_hidden_states, "dits_t"),
-                       P.mpos[1:1 + L], P.mpos[L + 2:LM])
+            ms, mt = object_motion_source_hidden_states, object_motion_target_hidden_states
+            if self._plus_adds_camera:  # embed(camera + object) (transformer.py:1171-1175)
+                ms, mt = camera_motion_source_hidden_states + ms, camera_motion_target_hidden_states + mt
+            put_tokens(emb_m(ms, "dits_s"), emb_m(mt, "dits_t"), P.mpos[1:1 + L], P.mpos[L + 2:LM])
             ops.rows_scatter(P.stok, 0, 0, P.mpos[0:1], Rows(res, 0, 1))
             ops.rows_scatter(P.ttok, 0, 0, P.mpos[L + 1:L + 2], Rows(res, L + 1, 1))
             phases = [(0, 0, len(P.joint))]                              # (first motion row, first layer, last layer)
@@ -603,7 +613,8 @@ class AMDDiffusionTransformerModelImgSpatial(_HvModule):
                 put_tokens(None, ct, None, P.mpos[1:1 + L])
                 ops.rows_scatter(P.ttok, 0, 0, P.mpos[0:1], Rows(res, L + 1, 1))
                 off = L + 1
-            phases = [(off, 0, 6), (0, 6, len(P.joint))] if obj else [(off, 0, len(P.joint))]
+            phases = ([(off, 0, self._camera_layers_end), (0, self._object_layers_start, len(P.joint))] if obj
+                      else [(off, 0, len(P.joint))])
         else:
             raise UnboundLocalError("motion_hidden_states")  # the reference leaves it undefined for other motion types
         x = image_hidden_states.float().contiguous()
@@ -630,9 +641,32 @@ class AMDDiffusionTransformerModelImgSpatial(_HvModule):
             geom = engine.dense_geom(N, LM - off + S)
             for i in range(l0, min(l1, len(P.joint))):
                 engine.run_block(ctx, P.joint[i], rows, geom, ada_f)
-                engine.run_block(ctx, P.sp[i], img_rows, g_tmp, ada_s)
+                if P.sp[i] is not None:
+                    engine.run_block(ctx, P.sp[i], img_rows, g_tmp, ada_s)
         pre = torch.empty(N, self.out_channels, Hi, Wi, dtype=torch.float32, device=x.device)
         o = P.ada.extra_off[0]
         ops.final_head(img_rows, P.nfw, P.nfb, P.now, P.nob, self.norm_final.eps, ada_f, o, o + D,
                        P.hw, P.hb, self.out_channels, p, Wi // p, pre, None, 0.0)
         return pre.to(image_hidden_states.dtype)
+
+
+class AMDDiffusionTransformerModel(AMDDiffusionTransformerModelImgSpatial):
+    """The oldest single-stream denoiser (transformer.py:1010-1259; AMDModel's diffusion_model_type='default'): joint
+    blocks only (no temporal blocks, no temporal position table).  'plus' embeds camera + object tokens;
+    'decouple' with object motions runs layers [0, 8) on the camera stream and layers [6, n) on the object
+    stream — layers 6 and 7 run in BOTH passes (1211, 1231), which is reproduced."""
+
+    _has_temporal_blocks = False
+    _camera_layers_end = 8
+    _object_layers_start = 6
+    _plus_adds_camera = True
+
+    def __init__(self, num_attention_heads=20, attention_head_dim=64, out_channels: Optional[int] = 4, num_layers=12,
+                 motion_type="plus", image_width=32, image_height=32, image_patch_size=2,
+                 image_in_channels: Optional[int] = 4, motion_token_num=12, motion_in_channels: Optional[int] = 128, **kw):
+        kw.pop("motion_target_num_frame", None)
+        super().__init__(num_attention_heads=num_attention_heads, attention_head_dim=attention_head_dim,
+                         out_channels=out_channels, num_layers=num_layers, motion_type=motion_type, image_width=image_width,
+                         image_height=image_height, image_patch_size=image_patch_size, image_in_channels=image_in_channels,
+                         motion_token_num=motion_token_num, motion_in_channels=motion_in_channels,
+                         motion_target_num_frame=1, **kw)

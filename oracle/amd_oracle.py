@@ -332,12 +332,15 @@ def dit_forward(sd, p, image, timestep, cam, osrc, otgt, heads, T, patch=2, moti
 
 
 def dit_imgspatial_forward(sd, p, cam_tgt, image, timestep, heads, T, patch=2, motion_token_num=12, motion_type="plus",
-                           cam_src=None, osrc=None, otgt=None):
+                           cam_src=None, osrc=None, otgt=None, legacy=False):
     """AMDDiffusionTransformerModelImgSpatial.forward (transformer.py:2186-2356): one motion stream; 'decouple'
     with object motions swaps the camera rows for object tokens after layer 5 (2259-2322) and forms the object
-    target rows from the object SOURCE embedding (2262-2263)."""
+    target rows from the object SOURCE embedding (2262-2263).
+    legacy=True: AMDDiffusionTransformerModel.forward (transformer.py:1130-1259) — no temporal blocks / table,
+    'plus' embeds camera + object, camera stream for layers [0, 8), object stream for layers [6, n)."""
     N, Ci, Hi, Wi = image.shape
     L = cam_tgt.shape[1]
+    T = 1 if legacy else T
     n, dev = N // T, image.device
     D = sd[p + ".image_patch_embed.proj.weight"].shape[0]
     S = (Hi // patch) * (Wi // patch)
@@ -348,7 +351,8 @@ def dit_imgspatial_forward(sd, p, cam_tgt, image, timestep, heads, T, patch=2, m
     stok, ttok = sd[p + ".source_token"].repeat(N, 1, 1), sd[p + ".target_token"].repeat(N, 1, 1)
     me = lambda x: _lin(sd, p + ".motion_patch_embed", x)
     if motion_type == "plus":
-        mo = torch.cat([stok, me(osrc), ttok, me(otgt)], 1) + mpos[None, :2 * L + 2]
+        ms, mt = (cam_src + osrc, cam_tgt + otgt) if legacy else (osrc, otgt)
+        mo = torch.cat([stok, me(ms), ttok, me(mt)], 1) + mpos[None, :2 * L + 2]
     else:
         if cam_src is not None:
             mo = torch.cat([stok, me(cam_src), ttok, me(cam_tgt)], 1) + mpos[None, :2 * L + 2]
@@ -358,25 +362,30 @@ def dit_imgspatial_forward(sd, p, cam_tgt, image, timestep, heads, T, patch=2, m
             o_s = me(osrc) + mpos[None, 1:L + 1]
             o_t = o_s + mpos[None, L + 2:2 * L + 2]
     pos = torch.from_numpy(sincos_2d(D, Hi // patch, Wi // patch)).float().to(dev)
-    tpos = torch.from_numpy(sincos_1d(D, np.arange(T))).float().to(dev)
-    img = ((img + pos[None]).view(n, T, S, D) + tpos[None, :, None]).view(N, S, D)
-    nl = _count_layers(sd, p + ".spatial_blocks")
+    img = img + pos[None]
+    if not legacy:
+        tpos = torch.from_numpy(sincos_1d(D, np.arange(T))).float().to(dev)
+        img = (img.view(n, T, S, D) + tpos[None, :, None]).view(N, S, D)
+    nl = _count_layers(sd, p + ".transformer_blocks")
+    cam_end, obj_start = (8, 6) if legacy else (6, 6)
 
     def layer(i, mo, img):
         mo, img = joint_block(sd, p + ".transformer_blocks.%d" % i, mo, img, emb, heads)
+        if legacy:
+            return mo, img
         x = img.view(n, T, S, D).permute(0, 2, 1, 3).reshape(n * S, T, D)
         x = dit_block(sd, p + ".spatial_blocks.%d" % i, x, emb_s, heads)
         return mo, x.view(n, S, T, D).permute(0, 2, 1, 3).reshape(N, S, D)
 
     if motion_type == "decouple" and osrc is not None:
-        for i in range(min(6, nl)):
+        for i in range(min(cam_end, nl)):
             mo, img = layer(i, mo, img)
         if cam_src is not None:
             s_tok, t_tok = mo[:, :1], mo[:, 1 + L:2 + L]
         else:
             s_tok, t_tok = stok, mo[:, :1]
         mo = torch.cat([s_tok, o_s, t_tok, o_t], 1)
-        for i in range(6, nl):
+        for i in range(obj_start, nl):
             mo, img = layer(i, mo, img)
     else:
         for i in range(nl):

@@ -78,6 +78,26 @@ def imgspatial_dit(ref):
             yo = O.dit_imgspatial_forward(osd, "d", ct, image, ts, 2, 4, 2, 4, mt, c_src, o_s, o_t)
             check("ImgSpatial %s/%s" % (mt, name), yo, y)
             out["y_%s_%s" % (mt, name)] = y.contiguous()
+    # the oldest sibling, AMDDiffusionTransformerModel (transformer.py:1010-1259): 9 layers so that layers 6, 7 run in
+    # both passes and layer 8 only in the object pass
+    kw = {k: v for k, v in DITS.items() if k != "motion_target_num_frame"}
+    kw["num_layers"] = 9
+    for mt in ("plus", "decouple"):
+        torch.manual_seed(0)
+        m2 = ref.transformer.AMDDiffusionTransformerModel(motion_type=mt, **kw).eval()
+        sd = synth.synth_state_dict(((k, v.shape) for k, v in m2.state_dict().items()), 6)
+        m2.load_state_dict(sd)
+        osd = {"d." + k: v for k, v in sd.items()}
+        cases = {"plus": [("camsrc_obj", cs, os_, ot)], "decouple": [("cam_obj", None, os_, ot), ("camsrc_obj", cs, os_, ot)]}[mt]
+        for name, c_src, o_s, o_t in cases:
+            y = m2(ct, image, ts, camera_motion_source_hidden_states=c_src, object_motion_source_hidden_states=o_s,
+                   object_motion_target_hidden_states=o_t)
+            yo = O.dit_imgspatial_forward(osd, "d", ct, image, ts, 2, 4, 2, 4, mt, c_src, o_s, o_t, legacy=True)
+            check("legacy DiT %s/%s" % (mt, name), yo, y)
+            out["legacy_%s_%s" % (mt, name)] = y.contiguous()
+    with open(os.path.join(OUT, "state_dict_keys_legacy_dit.json"), "w") as f:
+        import json
+        json.dump({k: list(v.shape) for k, v in m2.state_dict().items()}, f, indent=0)
     save_file(out, os.path.join(OUT, "imgspatial_dit.safetensors"))
     with open(os.path.join(OUT, "state_dict_keys_imgspatial_dit.json"), "w") as f:
         import json

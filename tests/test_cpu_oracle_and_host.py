@@ -160,6 +160,12 @@ def test_state_dict_keys_imgspatial_dit():
         ref = json.load(f)
     m = hv.AMDDiffusionTransformerModelImgSpatial(motion_type="decouple", **DITS)
     assert {k: list(v.shape) for k, v in m.state_dict().items()} == ref
+    # the oldest sibling AMDDiffusionTransformerModel (transformer.py:1010-1128): no temporal blocks
+    with open(os.path.join(ROOT, "tests", "golden", "state_dict_keys_legacy_dit.json")) as f:
+        ref = json.load(f)
+    kw = dict({k: v for k, v in DITS.items() if k != "motion_target_num_frame"}, num_layers=9)
+    m = hv.AMDDiffusionTransformerModel(motion_type="plus", **kw)
+    assert {k: list(v.shape) for k, v in m.state_dict().items()} == ref
 
 
 def test_sincos_tables_match_oracle():

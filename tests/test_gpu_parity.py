@@ -528,6 +528,18 @@ def test_imgspatial_dit_golden(dev, golden, dtype, tol):
                   object_motion_source_hidden_states=t(os_) if os_ else None,
                   object_motion_target_hidden_states=t(ot) if ot else None)
             assert rel(y, g["y_%s_%s" % (mt, name)]) <= tol, (mt, name)
+    # AMDDiffusionTransformerModel (transformer.py:1010-1259): joint blocks only, layers 6-7 run in both passes of 'decouple'
+    kw = dict({k: v for k, v in DITS.items() if k != "motion_target_num_frame"}, num_layers=9)
+    for mt, cases in (("plus", [("camsrc_obj", "cs", "os", "ot")]), ("decouple", [("cam_obj", None, "os", "ot"), ("camsrc_obj", "cs", "os", "ot")])):
+        m = hv.AMDDiffusionTransformerModel(motion_type=mt, **kw)
+        m.load_state_dict(synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 6))
+        m.to(dev)
+        for sub in m.modules():
+            sub.hv_compute_dtype = dtype
+        for name, cs, os_, ot in cases:
+            y = m(t("ct"), t("image"), t("ts"), camera_motion_source_hidden_states=t(cs) if cs else None,
+                  object_motion_source_hidden_states=t(os_), object_motion_target_hidden_states=t(ot))
+            assert rel(y, g["legacy_%s_%s" % (mt, name)]) <= tol, ("legacy", mt, name)
 
 
 def _default(dev, dtype):
