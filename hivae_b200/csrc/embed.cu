@@ -322,3 +322,35 @@ extern "C" int hv_rope(float* q, float* k, int64_t batch, int L, int heads, int 
     HV_LAUNCH_CHECK();
     return HV_OK;
 }
+
+
+// tokens (N, h*w, p*p*c) -> image (N, c, h*p, w*p).  order 0: token features are (p, q, c) — `AMDModel*.unpatchify`
+// (model_AMD.py:2816-2830) and `MaskedAutoencoderViT.unpatchify` (model_MAE.py:131-145), einsum 'nhwpqc->nchpwq';
+// order 1: (c, p, q) — the DiT heads' reshape/permute (transformer.py:2038-2041).  One thread per output pixel,
+// consecutive threads walk an output row: coalesced 4-byte stores, reads strided by the feature order (c or 1).
+// `inverse` != 0 runs the same index map the other way (patchify, model_MAE.py:116-129).
+namespace {
+__global__ void unpatchify_kernel(const float* __restrict__ in, float* __restrict__ out, long long total, int c, int h, int w,
+                                  int p, int order, int inverse) {
+    const int H = h * p, W = w * p;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int x = (int)(i % W), y = (int)((i / W) % H), ch = (int)((i / ((long long)W * H)) % c);
+        const long long n = i / ((long long)W * H * c);
+        const int ty = y / p, py = y - ty * p, tx = x / p, px = x - tx * p;
+        const int feat = order == 0 ? (py * p + px) * c + ch : (ch * p + py) * p + px;
+        const long long tok = ((n * h + ty) * w + tx) * (long long)(p * p * c) + feat;
+        if (inverse) out[tok] = in[i]; else out[i] = in[tok];
+    }
+}
+}  // namespace
+
+extern "C" int hv_unpatchify(const float* in, float* out, int64_t N, int c, int h, int w, int p, int order, int inverse, void* stream) {
+    HV_REQUIRE(N >= 0 && c > 0 && h > 0 && w > 0 && p > 0 && (order == 0 || order == 1), "hv_unpatchify: bad arguments");
+    const long long total = (long long)N * c * h * p * w * p;
+    if (total == 0) return HV_OK;
+    long long grid = (total + 255) / 256;
+    if (grid > 148 * 32) grid = 148 * 32;
+    unpatchify_kernel<<<(unsigned)grid, 256, 0, hv_stream(stream)>>>(in, out, total, c, h, w, p, order, inverse);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}

@@ -305,6 +305,25 @@ class AMDModel_New(_ConfigModel):
                            return_meta_info=return_meta_info)
 
 
+    # ------------------------------------------------------------------ small helpers of the reference class
+    def prepare_encoder_input(self, video):
+        """model_AMD.py:2804-2814: consecutive frame pairs stacked on the channel axis, (b*(t-1), 2c, h, w)"""
+        assert len(video.shape) == 5, f"only support video data : 5D tensor , but got {video.shape}"
+        return torch.cat([video[:, :-1], video[:, 1:]], dim=2).flatten(0, 1)
+
+    @torch.no_grad()
+    def unpatchify(self, x, patch_size):
+        """model_AMD.py:2816-2830: tokens (N, S, p*p*C) with (p, q, c) feature order -> (N, C, H, W)"""
+        return ops.unpatchify(x, patch_size, order=0).to(x.dtype)
+
+    def reset_infer_num_frame(self, num):
+        """model_AMD.py:2832-2838 (the reference then reads a non-existent `use_motiontemporal`; the
+        frame count of the denoiser is what matters for AMDModel_New and is set before that)"""
+        old_num = self.diffusion_transformer.target_frame
+        self.diffusion_transformer.target_frame = num
+        print(f"* Reset infer frame from {old_num} to {self.diffusion_transformer.target_frame} *")
+
+
 def AMD_N(**kwargs):
     """model_AMD.py:3151-3161."""
     return AMDModel_New(enc_nhead=8, enc_ndim=64, diffusion_attn_head_dim=64, diffusion_attn_num_heads=16,

@@ -261,6 +261,30 @@ def rows_gather(rows, out):
     return out
 
 
+def unpatchify(x, p, c=None, order=0):
+    """tokens (N, S, p*p*c) -> (N, c, H, W); order 0 = (p,q,c) features (model_AMD.py:2816-2830), 1 = (c,p,q)"""
+    _chk_cuda(x)
+    N, S, F = x.shape
+    h = w = int(S ** 0.5)
+    assert h * w == S
+    c = F // (p * p) if c is None else c
+    x = x.float().contiguous()
+    out = torch.empty(N, c, h * p, w * p, dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().hv_unpatchify(_p(x), _p(out), N, c, h, w, p, order, 0, _stream()))
+    return out
+
+
+def patchify(img, p, order=0):
+    """(N, c, H, W) -> tokens (N, (H/p)*(W/p), p*p*c) (model_MAE.py:116-129)"""
+    _chk_cuda(img)
+    N, c, H, W = img.shape
+    assert H % p == 0 and W % p == 0
+    img = img.float().contiguous()
+    out = torch.empty(N, (H // p) * (W // p), p * p * c, dtype=torch.float32, device=img.device)
+    _lib.check(_lib.load().hv_unpatchify(_p(img), _p(out), N, c, H // p, W // p, p, order, 1, _stream()))
+    return out
+
+
 def conv3x3(x, w, bias, stride):
     _chk_cuda(x, w, bias)
     B, Cin, H, W = x.shape

@@ -7,7 +7,7 @@ nproc >> gpurun_out/gpu.txt; lscpu | grep -E "Model name|^CPU\(s\)" >> gpurun_ou
 run() { name=$1; shift; timeout -k 5 "$T" python -u -m pytest tests/test_gpu_parity.py -q -m gpu -k "$@" > gpurun_out/test_$name.log 2>&1; rc=$?; echo "$name exit=$rc" | tee -a gpurun_out/summary.txt; tail -n 3 gpurun_out/test_$name.log; if [ $rc == 124 ]; then echo "TIMEOUT in $name: stopping"; exit 124; fi; }
 : > gpurun_out/summary.txt
 T=120 run signal "dwt or freq or pyramid"
-T=120 run simt "linear_f32 or rope or patch_embed"
+T=120 run simt "linear_f32 or rope or patch_embed or unpatchify"
 T=120 run attn "attention"
 T=120 run gemm "linear_bf16 or qknorm or gated"
 T=120 run blocks "blocks"

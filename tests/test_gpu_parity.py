@@ -542,6 +542,23 @@ def test_imgspatial_dit_golden(dev, golden, dtype, tol):
             assert rel(y, g["legacy_%s_%s" % (mt, name)]) <= tol, ("legacy", mt, name)
 
 
+def test_unpatchify_both_feature_orders(dev):
+    """(p,q,c) order of AMDModel*.unpatchify / MAE (einsum 'nhwpqc->nchpwq', model_AMD.py:2816-2830) and
+    (c,p,q) order of the DiT heads (transformer.py:2038-2041); patchify is the exact inverse. Bit-exact (pure moves)."""
+    from hivae_b200 import ops
+    N, h, p, c = 3, 16, 2, 4
+    x = torch.randn(N, h * h, p * p * c, generator=_gen(31))
+    ref0 = torch.einsum("nhwpqc->nchpwq", x.reshape(N, h, h, p, p, c)).reshape(N, c, h * p, h * p)
+    ref1 = x.reshape(N, 1, h, h, c, p, p).permute(0, 1, 4, 2, 5, 3, 6).flatten(5, 6).flatten(3, 4).squeeze(1)
+    y0, y1 = ops.unpatchify(x.to(dev), p, order=0), ops.unpatchify(x.to(dev), p, order=1)
+    assert torch.equal(y0.cpu(), ref0) and torch.equal(y1.cpu(), ref1)
+    assert torch.equal(ops.patchify(y0, p, order=0).cpu(), x) and torch.equal(ops.patchify(y1, p, order=1).cpu(), x)
+    m, _ = _small(dev)
+    assert torch.equal(m.unpatchify(x.to(dev), p).cpu(), ref0)
+    v = torch.randn(2, 5, 4, 8, 8, generator=_gen(32))
+    assert m.prepare_encoder_input(v).shape == (8, 8, 8, 8)
+
+
 def _default(dev, dtype):
     import hivae_b200 as hv
     m = hv.AMDModel_New(**configs.DEFAULT)
