@@ -21,7 +21,12 @@
 // ~7000 clk a tile takes; MUFU.EX2 (2300 clk/tile) and the MMAs (1150 clk/tile) hide under it.  A variant
 // that keeps the scores in registers between the passes (16 softmax warps, 72 scores per thread) read
 // TMEM once but lost more to register spills and barrier cost than it gained (299 vs 188 us at the DiT
-// shape) and was not kept.  Tail tiles (<= 32 query rows left, e.g. the third tile of a 274-token sequence):
+// shape) and was not kept.  Neither was a later one-pass variant with EIGHT softmax warps that holds all 144 scores
+// of a thread in registers (three warpgroups, setmaxnreg 216 / 56 so that nothing spills): 189 us against 169 us
+// for this two-pass kernel on the same box, i.e. halving the TMEM reads does not pay — the per-tile time
+// (~7000 clk) is dominated by dependent-latency chains of the two softmax warps per SM sub-partition, which is
+// what the next redesign has to attack (more independent rows in flight per warp, not fewer TMEM reads).
+// Tail tiles (<= 32 query rows left, e.g. the third tile of a 274-token sequence):
 // the producer replicates the 32-row Q box into all four lane quarters, so every softmax warp can reach the
 // rows and the keys are split eight ways instead of two (a third of a full tile's softmax time).
 //
