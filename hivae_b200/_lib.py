@@ -50,6 +50,7 @@ SIGNATURES = {
     "hv_axpy": (_i, [_f, _vp, _vp, _i64, _vp]),
     "hv_rows_scatter": (_i, [_vp, _i64, _i64, _vp, _vp, _i64, _i64, _i, _i, _i, _vp]),
     "hv_rows_gather": (_i, [_vp, _i64, _i64, _i, _i, _i, _vp, _vp]),
+    "hv_attn_prof_read": (_i, [_vp]),
     "hv_unpatchify": (_i, [_vp, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp]),
     "hv_conv3x3": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp]),
     "hv_maxpool2": (_i, [_vp, _vp, _i64, _i, _i, _vp]),

@@ -26,6 +26,10 @@
 // for this two-pass kernel on the same box, i.e. halving the TMEM reads does not pay — the per-tile time
 // (~7000 clk) is dominated by dependent-latency chains of the two softmax warps per SM sub-partition, which is
 // what the next redesign has to attack (more independent rows in flight per warp, not fewer TMEM reads).
+// Measured phase split (HV_ATTN_PROF=1, tools/attn_phases.py, L = 274, cycles per tile averaged over full and tail
+// tiles): wait S 215-307, max pass ~1600, max exchange 600-750, O epilogue ~1250 (includes the o_full wait), exp pass
+// 3230-3390, publish P + sums ~480; total ~7550.  The MUFU floor of the exp pass is 2304 clk per full tile, the
+// max pass moves 147 KB of TMEM at ~92 B/clk/SM (8 warps x one 2 KB tcgen05.ld in flight / ~170 clk).
 // Tail tiles (<= 32 query rows left, e.g. the third tile of a 274-token sequence):
 // the producer replicates the 32-row Q box into all four lane quarters, so every softmax warp can reach the
 // rows and the keys are split eight ways instead of two (a third of a full tile's softmax time).
@@ -34,6 +38,7 @@
 // warp / 4), warp 8 = MMA issuer + TMEM owner, warp 9 = TMA producer (one elected lane each).
 // CTAs are persistent over (sequence, head) pairs; K is double-buffered across pairs.
 #include <cuda.h>
+#include <cstdlib>
 #include "attn.cuh"
 #include "tc_ptx.cuh"
 
@@ -52,6 +57,7 @@ struct TcArgs {
     int heads, Lq, Lkv, KP;  // KP = Lkv rounded up to 16
     long long items;         // seqs * heads
     float sl2;               // scale * log2(e)
+    unsigned long long* dbg; // phase cycle counters (HV_ATTN_PROF=1, tools/attn_phases.py) or nullptr
 };
 
 __device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
@@ -73,6 +79,7 @@ __device__ __forceinline__ void tmem_ld16_wait(uint32_t (&r)[16]) {
                  : "memory");
 }
 
+template <bool PROF>  // PROF: phase cycle counters (a separate instantiation, the production kernel carries none of it)
 __global__ void __launch_bounds__(THREADS, 1)
 attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                const __grid_constant__ CUtensorMap tv, const TcArgs a) {
@@ -119,8 +126,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                 const int b = (int)(T & 1);
                 tc::mbar_wait(&q_free[b], (uint32_t)(((T >> 1) & 1) ^ 1));
                 tc::mbar_expect_tx(&q_full[b], QBYTES);
-#pragma unroll
                 const bool tail = a.Lq - i * QT <= 32;  // tail tile: the same 32-row box goes to all four lane quarters
+#pragma unroll
                 for (int j = 0; j < QT / 32; ++j)
                     tc::tma_load_2d(Qs + b * QBYTES + j * 4096, &tq, &q_full[b], col, (int)(qrow0 + i * QT + (tail ? 0 : j * 32)));
                 ++T;
@@ -238,8 +245,15 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                 const int nch = (c_end - c_begin) >> 4;
                 uint8_t* prow = tail ? prow_tail : prow_full;
                 const uint32_t s_addr = t_lane + S_COL + (uint32_t)((2 * T + h) % 3) * SBUF - (uint32_t)c_begin;
+                const bool prof = PROF && a.dbg != nullptr && lane == 0 && q == 0;
+                long long tk0 = 0, tk1 = 0;
+                auto tick = [&](int phase) {  // cycles since the previous tick -> counter `phase` of (CTA, key half)
+                    if (PROF && prof) { tk1 = clock64(); if (phase >= 0) a.dbg[(blockIdx.x * 2 + h) * 8 + phase] += (unsigned long long)(tk1 - tk0); tk0 = tk1; }
+                };
+                tick(-1);
                 tc::mbar_wait(&s_full[T & 1][h], (uint32_t)((T >> 1) & 1));
                 tc::fence_after_sync();
+                tick(0);
                 // ---- pass 1: row maximum over this thread's half of the keys
                 float mx = -INFINITY;
                 if (tail) {
@@ -253,6 +267,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                     }
                 } else if (active && c_begin < c_end) {
                     uint32_t va[16], vb[16];
+                    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
                     int c = c_begin;
                     tmem_ld16_issue(s_addr + c, va);
                     while (true) {
@@ -261,7 +276,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                         if (more) tmem_ld16_issue(s_addr + c + 16, vb);
                         if (c + 16 <= a.Lkv) {
 #pragma unroll
-                            for (int j = 0; j < 16; ++j) mx = fmaxf(mx, __uint_as_float(va[j]));
+                            for (int j = 0; j < 4; ++j)  // four independent chains instead of one 16-long dependent one
+                                mx4[j] = fmaxf(fmaxf(mx4[j], __uint_as_float(va[j])), fmaxf(fmaxf(__uint_as_float(va[j + 4]), __uint_as_float(va[j + 8])), __uint_as_float(va[j + 12])));
                         } else {
 #pragma unroll
                             for (int j = 0; j < 16; ++j) if (c + j < a.Lkv) mx = fmaxf(mx, __uint_as_float(va[j]));
@@ -273,7 +289,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                         if (more) tmem_ld16_issue(s_addr + c + 16, va);
                         if (c + 16 <= a.Lkv) {
 #pragma unroll
-                            for (int j = 0; j < 16; ++j) mx = fmaxf(mx, __uint_as_float(vb[j]));
+                            for (int j = 0; j < 4; ++j)  // four independent chains instead of one 16-long dependent one
+                                mx4[j] = fmaxf(fmaxf(mx4[j], __uint_as_float(vb[j])), fmaxf(fmaxf(__uint_as_float(vb[j + 4]), __uint_as_float(vb[j + 8])), __uint_as_float(vb[j + 12])));
                         } else {
 #pragma unroll
                             for (int j = 0; j < 16; ++j) if (c + j < a.Lkv) mx = fmaxf(mx, __uint_as_float(vb[j]));
@@ -281,8 +298,10 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                         if (!more) break;
                         c += 16;
                     }
+                    mx = fmaxf(fmaxf(mx, mx4[0]), fmaxf(fmaxf(mx4[1], mx4[2]), mx4[3]));
                 }
                 smax[h][row] = mx;
+                tick(1);
                 tc::named_bar_sync(1, 256);
                 if (tail) {
 #pragma unroll
@@ -291,10 +310,14 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                     mx = fmaxf(mx, smax[h ^ 1][row]);
                 }
                 const float msc = mx * a.sl2;
-                // ---- epilogue of the previous tile: PV(T-1) retired while the max pass ran
+                tick(2);
+                // ---- epilogue of the previous tile.  Its wait on o_full is ALSO what protects the single P buffer in shared
+                // memory: PV(T-1) must have finished reading P(T-1) before the exp pass below overwrites it, so this
+                // cannot move behind the exp pass (tried: 166 us instead of 170, but P(T) then races with PV(T-1)).
                 if (pend) epilogue();
+                tick(3);
                 // ---- pass 2: P = exp2(S*c - max*c) -> bf16 -> shared memory (K-major, 128 B swizzle)
-                float sum = 0.f;
+                float sum4[4] = {0.f, 0.f, 0.f, 0.f};
                 auto emit = [&](uint32_t (&r)[16], int c) {
                         float v[16];
                         if (c + 16 <= a.Lkv) {
@@ -305,7 +328,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                             for (int j = 0; j < 16; ++j) v[j] = (c + j < a.Lkv) ? tc::ex2_approx(fmaf(__uint_as_float(r[j]), a.sl2, -msc)) : 0.f;
                         }
 #pragma unroll
-                        for (int j = 0; j < 16; ++j) sum += v[j];
+                        for (int j = 0; j < 4; ++j) sum4[j] += (v[j] + v[j + 4]) + (v[j + 8] + v[j + 12]);
                         uint8_t* pc = prow + (c >> 6) * QBYTES;
                         const int jc = (c & 63) >> 3;
                         *reinterpret_cast<uint4*>(pc + (((jc) ^ (row & 7)) << 4)) =
@@ -340,11 +363,15 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                         c += 16;
                     }
                 }
+                float sum = (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
                 ssum[h][row] = sum;
+                tick(4);
                 tc::fence_before_sync();   // orders this thread's tcgen05.ld of S / O before the MMAs that overwrite them
                 tc::fence_proxy_async();   // P (generic-proxy stores) -> visible to the tensor core
                 tc::mbar_arrive(&p_full);
                 tc::named_bar_sync(1, 256);
+                tick(5);
+                if (PROF && prof) a.dbg[(blockIdx.x * 2 + h) * 8 + (tail ? 7 : 6)] += 1;
                 const int qr = i * QT + row;
                 pend = true;
                 pend_active = active;
@@ -372,6 +399,24 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
 
 }  // namespace
 
+// HV_ATTN_PROF=1: per-(CTA, key half) cycle counters of the softmax phases, 8 x u64 each:
+// 0 wait S, 1 max pass, 2 max exchange, 3 O epilogue, 4 exp pass, 5 publish P + sum exchange, 6 full tiles, 7 tail tiles
+static unsigned long long* g_prof = nullptr;
+static unsigned long long* hv_attn_prof_buffer() {
+    static const bool on = [] { const char* e = getenv("HV_ATTN_PROF"); return e && atoi(e) != 0; }();
+    if (on && !g_prof && cudaMalloc(&g_prof, 148 * 2 * 8 * sizeof(unsigned long long)) == cudaSuccess)
+        cudaMemset(g_prof, 0, 148 * 2 * 8 * sizeof(unsigned long long));
+    return on ? g_prof : nullptr;
+}
+// copies the counters to `host` (148 * 16 u64) and clears them; returns 0 when profiling is off
+extern "C" int hv_attn_prof_read(unsigned long long* host) {
+    if (!g_prof) return 0;
+    cudaDeviceSynchronize();
+    cudaMemcpy(host, g_prof, 148 * 2 * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    cudaMemset(g_prof, 0, 148 * 2 * 8 * sizeof(unsigned long long));
+    return 1;
+}
+
 // returns 1 if the shape is handled here (and launched), 0 if the caller should use another kernel, < 0 on error
 int hv_attention_tc_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
     const HvSeqMap &qm = a.qmap, &km = a.kvmap;
@@ -394,16 +439,19 @@ int hv_attention_tc_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
     t.heads = a.heads; t.Lq = a.Lq; t.Lkv = a.Lkv; t.KP = (a.Lkv + 15) & ~15;
     t.items = seqs * a.heads;
     t.sl2 = a.scale * 1.4426950408889634f;
+    t.dbg = hv_attn_prof_buffer();
     const int KP32 = (t.KP + 31) & ~31, nchunks = (t.KP + 63) >> 6;
     const int smem = 2 * QBYTES + 3 * KP32 * 128 + nchunks * QBYTES + 1024;
     static int configured = 0;
     if (configured < smem) {
-        HV_CUDA(cudaFuncSetAttribute(attn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        HV_CUDA(cudaFuncSetAttribute(attn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        HV_CUDA(cudaFuncSetAttribute(attn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = smem;
     }
     const int sms = hv_num_sms();
     const int grid = (int)(t.items < sms ? t.items : sms);
-    attn_tc_kernel<<<grid, THREADS, smem, st>>>(tq, tk, tv, t);
+    if (t.dbg) attn_tc_kernel<true><<<grid, THREADS, smem, st>>>(tq, tk, tv, t);
+    else attn_tc_kernel<false><<<grid, THREADS, smem, st>>>(tq, tk, tv, t);
     HV_LAUNCH_CHECK();
     return 1;
 }

@@ -134,6 +134,11 @@ int hv_axpy(float a, const float* x, float* y, int64_t n, void* stream);
 int hv_rows_scatter(const float* src, int64_t src_stride_f, int64_t src_stride_i, const float* add,
                     float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D, void* stream);
 /* dense fp32 out[(f*L+i), :] = res[f*frame_rows + row_off + i, :] */
+/* Diagnostics: with HV_ATTN_PROF=1 in the environment the tcgen05 attention kernel accumulates per-phase cycle
+ * counters (148 CTAs x 2 key halves x 8 u64: wait S, max pass, max exchange, O epilogue, exp pass, publish P, full
+ * tiles, tail tiles); this copies them to `host` and clears them.  Returns 0 when profiling is off. */
+int hv_attn_prof_read(unsigned long long* host);
+
 /* tokens (N, h*w, p*p*c) <-> image (N, c, h*p, w*p).  order 0 = (p,q,c) features: AMDModel*.unpatchify
  * (model_AMD.py:2816-2830), MaskedAutoencoderViT.patchify/unpatchify (model_MAE.py:116-145); order 1 = (c,p,q): the DiT
  * heads (transformer.py:2038-2041).  inverse != 0: image -> tokens (patchify). */
