@@ -16,7 +16,7 @@ from .transformer import (MotionEncoderLearnTokenTransformer, MotionEncoderLearn
                           MotionEncoderLearnTokenTemporalTransformer,
                           AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion,
                           AMDDiffusionTransformerModelImgSpatial, AMDDiffusionTransformerModel)
-from .model_AMD import AMDModel_New, AMD_N, AMD_models  # noqa: F401
+from .model_AMD import AMDModel, AMDModel_New, AMD_N, AMD_models  # noqa: F401
 from . import sharding  # noqa: F401
 from . import optim  # noqa: F401
 

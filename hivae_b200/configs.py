@@ -19,3 +19,14 @@ SMALL = dict(DEFAULT, object_enc_num_layers=2, camera_enc_num_layers=2, enc_nhea
 SMALL_OBJECT_ONLY = dict(SMALL, use_camera=False, diffusion_model_type="default")
 
 CONFIGS = {"default": DEFAULT, "small": SMALL, "small_object_only": SMALL_OBJECT_ONLY}
+
+
+# the older AMDModel (model_AMD.py:33-594), two runnable small configurations
+AMDMODEL_TEMPORAL = dict(video_frames=4, use_filter=True, use_grey=True, use_motiontemporal=True, use_mask=True, motion_type="decouple",
+                         object_motion_token_num=4, object_motion_token_channel=16, object_enc_num_layers=2, enc_nhead=2, enc_ndim=64,
+                         camera_motion_token_num=4, camera_motion_token_channel=8, camera_enc_num_layers=2, motion_token_num=4,
+                         motion_token_channel=16, diffusion_model_type="spatial", diffusion_attn_num_heads=2, diffusion_num_layers=7)
+AMDMODEL_LEGACY = dict(video_frames=4, use_filter=True, use_grey=True, use_motiontemporal=False, use_camera_down=True, motion_type="plus",
+                       object_motion_token_num=4, object_motion_token_channel=16, object_enc_num_layers=2, enc_nhead=2, enc_ndim=64,
+                       camera_motion_token_num=4, camera_motion_token_channel=16, camera_enc_num_layers=2, motion_token_num=4,
+                       motion_token_channel=16, diffusion_model_type="default", diffusion_attn_num_heads=2, diffusion_num_layers=3)

@@ -17,12 +17,17 @@ from torch import nn
 from . import engine, ops
 from .frequency_utils import freq_split_gauss
 from .rectified_flow import RectifiedFlow
-from .transformer import (AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion,
-                          MotionEncoderLearnTokenOnlyTemporalTransformer, MotionEncoderLearnTokenTransformer)
+from .transformer import (AMDDiffusionTransformerModel, AMDDiffusionTransformerModelImgSpatial,
+                          AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion,
+                          MotionEncoderLearnTokenOnlyTemporalTransformer, MotionEncoderLearnTokenTemporalTransformer,
+                          MotionEncoderLearnTokenTransformer)
 
 
 def l2(pre, gt):
-    """model/loss.py:13-14."""
+    """model/loss.py:13-14 (sm_100a reduction kernel on the device, torch on CPU tensors)."""
+    if pre.is_cuda:
+        from . import optim
+        return optim.mse_loss(pre, gt)
     return torch.nn.functional.mse_loss(pre, gt)
 
 
@@ -322,6 +327,168 @@ class AMDModel_New(_ConfigModel):
         old_num = self.diffusion_transformer.target_frame
         self.diffusion_transformer.target_frame = num
         print(f"* Reset infer frame from {old_num} to {self.diffusion_transformer.target_frame} *")
+
+
+class AMDModel(_ConfigModel):
+    """The older two-encoder model (model_AMD.py:33-594): object motion from the HIGH band and camera motion from the
+    LOW band of the grey clip, both over all 2t frames, one single-stream denoiser ('default' ->
+    AMDDiffusionTransformerModel, 'spatial' -> AMDDiffusionTransformerModelImgSpatial).  Built for the runnable
+    configurations: use_regularizers=False, need_motion_transformer=False; use_filter needs use_grey (the reference reads
+    an undefined name otherwise, 291 / 462) and use_camera_down needs use_filter (314 / 472)."""
+    _supports_gradient_checkpointing = True
+
+    def __init__(self, image_inchannel=4, image_height=32, image_width=32, video_frames=16, scheduler_num_step=1000,
+                 use_filter=False, filter_num=0.4, high_filter_num=0.6, use_grey=False, use_camera_down=False,
+                 use_regularizers=False, use_motiontemporal=True, klloss_weight=0.005, use_mask=False, motion_type="plus",
+                 object_motion_token_num=12, object_motion_token_channel=128, object_enc_num_layers=8, enc_nhead=8,
+                 enc_ndim=64, enc_dropout=0.0, motion_need_norm_out=False, camera_motion_token_num=12,
+                 camera_motion_token_channel=128, camera_enc_num_layers=8, motion_token_num=12, motion_token_channel=128,
+                 need_motion_transformer=False, motion_transformer_attn_head_dim=64, motion_transformer_attn_num_heads=16,
+                 motion_transformer_num_layers=4, diffusion_model_type="default", diffusion_attn_head_dim=64,
+                 diffusion_attn_num_heads=16, diffusion_out_channels=4, diffusion_num_layers=16, image_patch_size=2,
+                 motion_patch_size=1, motion_drop_ratio=0.0, extract_motion_with_motion_transformer=False, **kwargs):
+        super().__init__()
+        self._register(locals())
+        if use_regularizers or need_motion_transformer:
+            raise NotImplementedError("use_regularizers / need_motion_transformer are out of scope (false in every shipped script)")
+        self.num_step = scheduler_num_step
+        self.scheduler = RectifiedFlow(num_steps=scheduler_num_step)
+        self.need_motion_transformer, self.extract_motion_with_motion_transformer = need_motion_transformer, extract_motion_with_motion_transformer
+        self.diffusion_model_type, self.target_frame, self.use_motiontemporal = diffusion_model_type, video_frames, use_motiontemporal
+        self.camera_motion_token_channel, self.object_motion_token_channel = camera_motion_token_channel, object_motion_token_channel
+        self.motion_token_channel, self.filter_num, self.high_filter_num = motion_token_channel, filter_num, high_filter_num
+        self.use_filter, self.use_grey, self.use_camera_down, self.use_mask = use_filter, use_grey, use_camera_down, use_mask
+        self.use_regularizers, self.klloss_weight = use_regularizers, klloss_weight
+        if camera_motion_token_channel != motion_token_channel:
+            self.camera_motion_map = nn.Linear(camera_motion_token_channel, motion_token_channel)
+        if object_motion_token_channel != motion_token_channel:
+            self.object_motion_map = nn.Linear(object_motion_token_channel, motion_token_channel)
+        enc = dict(img_inchannel=image_inchannel, img_patch_size=image_patch_size, need_norm_out=motion_need_norm_out,
+                   num_attention_heads=enc_nhead, attention_head_dim=enc_ndim, dropout=enc_dropout, attention_bias=True)
+        obj = dict(img_height=image_height, img_width=image_width, motion_token_num=object_motion_token_num,
+                   motion_channel=object_motion_token_channel, num_layers=object_enc_num_layers)
+        cam = dict(motion_token_num=camera_motion_token_num, motion_channel=camera_motion_token_channel, num_layers=camera_enc_num_layers)
+        if use_motiontemporal:
+            self.object_motion_encoder = MotionEncoderLearnTokenTemporalTransformer(video_frames=video_frames, **obj, **enc)
+            self.camera_motion_encoder = MotionEncoderLearnTokenTemporalTransformer(img_height=image_height, img_width=image_width,
+                                                                                    video_frames=video_frames, **cam, **enc)
+        else:
+            self.object_motion_encoder = MotionEncoderLearnTokenTransformer(**obj, **enc)
+            self.camera_motion_encoder = MotionEncoderLearnTokenTransformer(img_height=image_height // 4, img_width=image_width // 4,
+                                                                            **cam, **enc)  # sized for the camera_down output (186-187)
+        if use_camera_down:
+            self.camera_down = nn.Sequential(nn.Conv2d(4, 16, kernel_size=3, stride=2, padding=1),
+                                             nn.Conv2d(16, 4, kernel_size=3, stride=1, padding=1), nn.MaxPool2d(2, 2, 0))
+        dit = dict(num_attention_heads=diffusion_attn_num_heads, attention_head_dim=diffusion_attn_head_dim,
+                   out_channels=diffusion_out_channels, num_layers=diffusion_num_layers, motion_type=motion_type,
+                   image_width=image_width, image_height=image_height, image_patch_size=image_patch_size,
+                   image_in_channels=image_inchannel * 2, motion_token_num=motion_token_num, motion_in_channels=motion_token_channel)
+        if diffusion_model_type == "default":
+            self.diffusion_transformer = AMDDiffusionTransformerModel(**dit)
+        elif diffusion_model_type == "spatial":
+            self.diffusion_transformer = AMDDiffusionTransformerModelImgSpatial(motion_target_num_frame=video_frames, **dit)
+        elif diffusion_model_type == "dual":
+            raise NotImplementedError("AMDDiffusionTransformerModelDualStream is not runnable in the reference (modules.py:1250)")
+        else:
+            raise IndexError
+
+    set_compute_dtype = AMDModel_New.set_compute_dtype
+    prepare_timestep = AMDModel_New.prepare_timestep
+    _camera_down = AMDModel_New._camera_down
+
+    def _motions(self, video, ref_img, video_grey, ref_img_grey, camera_mask, mask_ratio):
+        """shared front half of forward / sample (model_AMD.py:272-343, 441-500) -> four (n*t, l, d) motion tensors"""
+        n, t, c, h, w = video.shape
+        rv = torch.cat([ref_img, video], dim=1).float().contiguous()
+        if self.use_filter:
+            if not self.use_grey:
+                raise NameError("name 'refimg_and_video_grey' is not defined")  # model_AMD.py:291, 462
+            grey = torch.cat([ref_img_grey, video_grey], dim=1).float().permute(0, 2, 1, 3, 4).contiguous()
+            lo, _ = freq_split_gauss(grey, self.filter_num, self.filter_num)
+            _, hi = freq_split_gauss(grey, self.high_filter_num, self.high_filter_num)
+            lf, hf = lo.permute(0, 2, 1, 3, 4).contiguous(), hi.permute(0, 2, 1, 3, 4).contiguous()
+            if self.use_mask and camera_mask is not None:
+                lf = (lf * camera_mask).contiguous()
+            if self.use_camera_down:
+                y = self._camera_down(lf.view(n * 2 * t, c, h, w))
+                lf = y.view(n, 2 * t, *y.shape[1:])
+            obj, cam = self.object_motion_encoder(hf, mask_ratio), self.camera_motion_encoder(lf, mask_ratio)
+        else:
+            if self.use_camera_down:
+                raise UnboundLocalError("LF_refimg_and_video")  # model_AMD.py:314, 472
+            obj, cam = self.object_motion_encoder(rv, mask_ratio), self.camera_motion_encoder(rv, mask_ratio)
+        osrc, otgt = obj[:, :t].flatten(0, 1).contiguous(), obj[:, t:].flatten(0, 1).contiguous()
+        csrc, ctgt = cam[:, :t].flatten(0, 1).contiguous(), cam[:, t:].flatten(0, 1).contiguous()
+        assert osrc.shape == otgt.shape and csrc.shape == ctgt.shape
+        lin = lambda m, x: torch.nn.functional.linear(x, m.weight, m.bias) if not x.is_cuda else _device_linear(m, x)
+        if self.camera_motion_token_channel != self.motion_token_channel:
+            csrc, ctgt = lin(self.camera_motion_map, csrc), lin(self.camera_motion_map, ctgt)
+        if self.object_motion_token_channel != self.motion_token_channel:
+            osrc, otgt = lin(self.object_motion_map, osrc), lin(self.object_motion_map, otgt)
+        return cam, obj, csrc, ctgt, osrc, otgt
+
+    def _dit(self, zi, zt, time_step, m):
+        _, _, csrc, ctgt, osrc, otgt = m
+        return self.diffusion_transformer(ctgt, (zi, zt), time_step, camera_motion_source_hidden_states=csrc,
+                                          object_motion_source_hidden_states=osrc, object_motion_target_hidden_states=otgt)
+
+    @torch.no_grad()
+    def forward(self, video, ref_img, video_grey=None, ref_img_grey=None, camera_mask=None, time_step=None,
+                return_meta_info=False, mask_ratio=None):
+        """model_AMD.py:258-423 (inference kernels; no autograd yet) -> (pre, vel, {'loss','diff_loss','rec_loss'})"""
+        n, t, c, h, w = video.shape
+        assert video.shape == ref_img.shape, f"video.shape:{video.shape}should be equal to ref_img.shape:{ref_img.shape}"
+        if mask_ratio is not None:
+            raise NotImplementedError("random token masking is out of scope")
+        m = self._motions(video, ref_img, video_grey, ref_img_grey, camera_mask, None)
+        zi, zj = ref_img.flatten(0, 1).float().contiguous(), video.flatten(0, 1).float().contiguous()
+        if time_step is None:
+            time_step = self.prepare_timestep(batch_size=zj.shape[0], device=video.device)
+        if self.diffusion_model_type != "default":  # one step per clip, redrawn even when a time_step was given (370-372)
+            time_step = self.prepare_timestep(batch_size=n, device=video.device).repeat_interleave(t)
+        zt, vel = self.scheduler.get_train_tuple(z1=zj, time_step=time_step)
+        zt = zt.contiguous()
+        pre = self._dit(zi, zt, time_step.float(), m)
+        diff_loss = l2(pre, vel)
+        rec_loss = l2(self.scheduler.get_target_with_zt_vel(zt, pre, time_step), zj)
+        if return_meta_info:
+            return {"camera_motion": m[0], "object_motion": m[1], "zi": zi, "zj": zj, "zt": zt, "pre": pre, "time_step": time_step}
+        return pre, vel, {"loss": diff_loss, "diff_loss": diff_loss, "rec_loss": rec_loss}
+
+    @torch.no_grad()
+    def sample(self, video, ref_img, video_grey=None, ref_img_grey=None, camera_mask=None, sample_step=50, mask_ratio=None,
+               start_step=None, return_meta_info=False):
+        """model_AMD.py:426-594 -> (zi, zt, zj), each (n, t, c, h, w).  (The reference's camera_mask is not applied in
+        sample either, 441-478; its meta-info branch reads an undefined `target_motion`, 590.)"""
+        if return_meta_info:
+            raise NameError("name 'target_motion' is not defined")
+        n, t = video.shape[:2]
+        if start_step is None:
+            start_step = self.scheduler.num_step
+        assert start_step <= self.scheduler.num_step, "start_step cant be larger than scheduler.num_step"
+        if mask_ratio is not None:
+            raise NotImplementedError("random token masking is out of scope")
+        m = self._motions(video, ref_img, video_grey, ref_img_grey, None, None)
+        zi, zj = ref_img.flatten(0, 1).float().contiguous(), video.flatten(0, 1).float().contiguous()
+        zt, _ = self.scheduler.get_train_tuple(z1=zj, time_step=torch.ones((zj.shape[0],), device=zj.device) * start_step)
+        zt = zt.contiguous().clone()
+        step_seq = list(reversed(np.linspace(0, start_step, num=sample_step + 1, endpoint=True, dtype=int)[1:]))
+        dt = 1.0 / sample_step
+        ts = torch.empty(zt.shape[0], dtype=torch.float32, device=zt.device)
+        for i in step_seq:
+            ts.fill_(float(i))
+            ops.axpy(dt, self._dit(zi, zt, ts, m).contiguous(), zt)  # zt += dt * pre
+        shp = (n, t) + tuple(zi.shape[1:])
+        return zi.view(shp), zt.view(shp), zj.view(shp)
+
+
+def _device_linear(m, x):
+    """tiny motion-map Linear (model_AMD.py:124-127) on the SIMT GEMM"""
+    from .engine import Ctx, small_linear
+    ctx = Ctx(x.device, torch.float32)
+    y = small_linear(ctx, x.reshape(-1, x.shape[-1]).float().contiguous(), m.weight.detach().float().contiguous(),
+                     m.bias.detach().float().contiguous(), "motion_map")
+    return y.view(*x.shape[:-1], -1).clone()
 
 
 def AMD_N(**kwargs):

@@ -574,6 +574,9 @@ class AMDDiffusionTransformerModelImgSpatial(_HvModule):
     def forward(self, camera_motion_target_hidden_states, image_hidden_states, timestep, timestep_cond=None,
                 camera_motion_source_hidden_states=None, object_motion_source_hidden_states=None,
                 object_motion_target_hidden_states=None, return_dict=True):
+        image2 = None
+        if isinstance(image_hidden_states, (tuple, list)):  # (zi, zt): the channel concat of model_AMD.py:380 is folded into the patch embed
+            image_hidden_states, image2 = image_hidden_states
         N, Ci, Hi, Wi = image_hidden_states.shape
         _, L, Cm = camera_motion_target_hidden_states.shape
         P = self._prepared(image_hidden_states.device)
@@ -618,7 +621,7 @@ class AMDDiffusionTransformerModelImgSpatial(_HvModule):
         else:
             raise UnboundLocalError("motion_hidden_states")  # the reference leaves it undefined for other motion types
         x = image_hidden_states.float().contiguous()
-        ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, P.tpos, res, FR, LM, D)
+        ops.patch_embed(x, image2.float().contiguous() if image2 is not None else None, p, P.pw, P.pb, P.pos, P.tpos, res, FR, LM, D)
         if not torch.is_tensor(timestep):
             timestep = torch.full((N,), float(timestep), device=x.device)
         ts = timestep.to(device=x.device, dtype=torch.float32).contiguous()

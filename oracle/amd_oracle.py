@@ -479,6 +479,68 @@ class AMDOracle:
         return pre, vel, {"loss": diff, "diff_loss": diff, "rec_loss": rec}
 
 
+class AMDModelOracle:
+    """AMDModel (model_AMD.py:33-594) for use_filter + use_grey (or neither), use_regularizers=False,
+    need_motion_transformer=False: motions() = 272-343 / 441-500, forward = 258-423, sample = 426-594."""
+
+    def __init__(self, sd, cfg):
+        self.sd, self.c = {k: v.float() for k, v in sd.items()}, cfg
+        self.T, self.num_step = cfg["video_frames"], cfg.get("scheduler_num_step", 1000)
+
+    def _enc(self, p, x):
+        c = self.c
+        if c.get("use_motiontemporal", True):
+            return temporal_motion_encoder(self.sd, p, x, c["enc_nhead"], self.T, c.get("image_patch_size", 2), c.get("motion_need_norm_out", False))
+        return object_encoder(self.sd, p, x, c["enc_nhead"], c.get("image_patch_size", 2), c.get("motion_need_norm_out", False))
+
+    def motions(self, video, ref_img, video_grey=None, ref_img_grey=None, camera_mask=None):
+        c = self.c
+        n, t, ch, h, w = video.shape
+        rv = torch.cat([ref_img, video], 1)
+        if c.get("use_filter", False):
+            grey = torch.cat([ref_img_grey, video_grey], 1).permute(0, 2, 1, 3, 4)
+            lo, _ = freq_split3d(grey, gaussian_lpf([2 * t, h, w], c.get("filter_num", 0.4), c.get("filter_num", 0.4)))
+            _, hi = freq_split3d(grey, gaussian_lpf([2 * t, h, w], c.get("high_filter_num", 0.6), c.get("high_filter_num", 0.6)))
+            lf, hf = lo.permute(0, 2, 1, 3, 4), hi.permute(0, 2, 1, 3, 4)
+            if camera_mask is not None:
+                lf = lf * camera_mask
+            if c.get("use_camera_down", False):
+                y = camera_down(self.sd, "camera_down", lf.flatten(0, 1))
+                lf = y.view(n, 2 * t, *y.shape[1:])
+            obj, cam = self._enc("object_motion_encoder", hf), self._enc("camera_motion_encoder", lf)
+        else:
+            obj, cam = self._enc("object_motion_encoder", rv), self._enc("camera_motion_encoder", rv)
+        osrc, otgt, csrc, ctgt = obj[:, :t].flatten(0, 1), obj[:, t:].flatten(0, 1), cam[:, :t].flatten(0, 1), cam[:, t:].flatten(0, 1)
+        if "camera_motion_map.weight" in self.sd:
+            csrc, ctgt = _lin(self.sd, "camera_motion_map", csrc), _lin(self.sd, "camera_motion_map", ctgt)
+        if "object_motion_map.weight" in self.sd:
+            osrc, otgt = _lin(self.sd, "object_motion_map", osrc), _lin(self.sd, "object_motion_map", otgt)
+        return csrc, ctgt, osrc, otgt
+
+    def dit(self, zi, zt, step, m):
+        c = self.c
+        csrc, ctgt, osrc, otgt = m
+        return dit_imgspatial_forward(self.sd, "diffusion_transformer", ctgt, torch.cat([zi, zt], 1), step, c["diffusion_attn_num_heads"],
+                                      self.T, c.get("image_patch_size", 2), c.get("motion_token_num", 12), c.get("motion_type", "plus"),
+                                      csrc, osrc, otgt, legacy=c.get("diffusion_model_type", "default") == "default")
+
+    def forward(self, video, ref_img, time_step, z0, video_grey=None, ref_img_grey=None, camera_mask=None):
+        m = self.motions(video, ref_img, video_grey, ref_img_grey, camera_mask)
+        zi, zj = ref_img.flatten(0, 1), video.flatten(0, 1)
+        zt, vel = rf_train_tuple(zj, time_step, z0, self.num_step)
+        pre = self.dit(zi, zt, time_step, m)
+        return pre, vel, {"loss": F.mse_loss(pre, vel), "rec_loss": F.mse_loss(rf_target(zt, pre, time_step, self.num_step), zj)}
+
+    def sample(self, video, ref_img, sample_step, z0, video_grey=None, ref_img_grey=None, start_step=None):
+        start_step = self.num_step if start_step is None else start_step
+        m = self.motions(video, ref_img, video_grey, ref_img_grey)
+        zi, zj = ref_img.flatten(0, 1), video.flatten(0, 1)
+        zt, _ = rf_train_tuple(zj, torch.ones(zj.shape[0]) * start_step, z0, self.num_step)
+        for i in sample_steps(start_step, sample_step):
+            zt = zt + self.dit(zi, zt, torch.ones(zt.shape[0]) * i, m) / sample_step
+        return zt.view(video.shape)
+
+
 def psnr(a, b):
     """model/metric.py:8-10: 20*log10(1/sqrt(mse))."""
     return float(20 * torch.log10(1.0 / torch.sqrt(F.mse_loss(a, b))))

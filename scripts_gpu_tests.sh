@@ -12,7 +12,7 @@ T=120 run attn "attention"
 T=120 run gemm "linear_bf16 or qknorm or gated"
 T=120 run blocks "blocks"
 T=180 run small "small_model"
-T=180 run variant "object_only or temporal_motion_encoder or imgspatial or sample_cross"
+T=180 run variant "object_only or temporal_motion_encoder or imgspatial or sample_cross or amdmodel"
 T=120 run optim "adamw or clip"
 T=300 run default "default_model or natively"
 if [ "$1" == "bench" ]; then

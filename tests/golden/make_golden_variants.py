@@ -51,6 +51,41 @@ def main():
     temporal_encoder(ref)
     cross_and_refimg(ref)
     imgspatial_dit(ref)
+    amd_model(ref)
+
+
+def amd_model(ref):
+    """a18 sibling AMDModel (model_AMD.py:33-594): forward + sample for two runnable configurations"""
+    out = {}
+    gen = torch.Generator().manual_seed(41)
+    n, t = 2, 4
+    video, ref_img, vg, rg = (torch.randn(n, t, 4, 32, 32, generator=gen) * 0.7 for _ in range(4))
+    mask = (torch.rand(n, 2 * t, 4, 32, 32, generator=gen) > 0.3).float()
+    z0 = torch.randn(n * t, 4, 32, 32, generator=gen)
+    out.update(video=video, ref_img=ref_img, vg=vg, rg=rg, mask=mask, z0=z0)
+    for name, cfg in (("temporal", configs.AMDMODEL_TEMPORAL), ("legacy", configs.AMDMODEL_LEGACY)):
+        torch.manual_seed(0)
+        m = ref.model_AMD.AMDModel(**cfg).eval()
+        sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 7)
+        m.load_state_dict(sd)
+        orc = O.AMDModelOracle(sd, cfg)
+        orig = m.scheduler.get_train_tuple
+        m.scheduler.get_train_tuple = lambda z0_=None, z1=None, time_step=None: orig(z0=z0, z1=z1, time_step=time_step)
+        ts_clip = torch.tensor([700.0, 250.0])
+        ts = ts_clip.repeat_interleave(t) if cfg["diffusion_model_type"] != "default" else torch.arange(n * t).float() * 100 + 50
+        m.prepare_timestep = (lambda batch_size, device, time_step=None: ts_clip) if cfg["diffusion_model_type"] != "default" \
+            else (lambda batch_size, device, time_step=None: ts)
+        cm = mask if cfg.get("use_mask") else None
+        pre, vel, ld = m(video, ref_img, video_grey=vg, ref_img_grey=rg, camera_mask=cm)
+        opre, ovel, old = orc.forward(video, ref_img, ts, z0, vg, rg, cm)
+        check("AMDModel %s forward pre" % name, opre, pre), check("AMDModel %s loss" % name, old["loss"], ld["loss"])
+        zi, zt, zj = m.sample(video, ref_img, video_grey=vg, ref_img_grey=rg, sample_step=2)
+        check("AMDModel %s sample zt" % name, orc.sample(video, ref_img, 2, z0, vg, rg), zt)
+        out.update({name + "_ts": ts, name + "_pre": pre.contiguous(), name + "_loss": torch.stack([ld["loss"], ld["rec_loss"]]), name + "_zt": zt.contiguous()})
+        with open(os.path.join(OUT, "state_dict_keys_amdmodel_%s.json" % name), "w") as f:
+            import json
+            json.dump({k: list(v.shape) for k, v in m.state_dict().items()}, f, indent=0)
+    save_file(out, os.path.join(OUT, "amd_model.safetensors"))
 
 
 DITS = dict(num_attention_heads=2, attention_head_dim=64, out_channels=4, num_layers=8, image_width=32, image_height=32,

@@ -168,6 +168,21 @@ def test_state_dict_keys_imgspatial_dit():
     assert {k: list(v.shape) for k, v in m.state_dict().items()} == ref
 
 
+def test_state_dict_keys_amdmodel():
+    """a18 sibling AMDModel (model_AMD.py:33-256): keys/shapes of the unmodified reference for two runnable configurations;
+    the branches the reference cannot run raise the same kind of error."""
+    import hivae_b200 as hv
+    for name, cfg in (("temporal", configs.AMDMODEL_TEMPORAL), ("legacy", configs.AMDMODEL_LEGACY)):
+        with open(os.path.join(ROOT, "tests", "golden", "state_dict_keys_amdmodel_%s.json" % name)) as f:
+            ref = json.load(f)
+        m = hv.AMDModel(**cfg)
+        assert {k: list(v.shape) for k, v in m.state_dict().items()} == ref, name
+    with pytest.raises(IndexError):
+        hv.AMDModel(**dict(configs.AMDMODEL_LEGACY, diffusion_model_type="nope"))
+    with pytest.raises(NotImplementedError):
+        hv.AMDModel(**dict(configs.AMDMODEL_LEGACY, diffusion_model_type="dual"))
+
+
 def test_sincos_tables_match_oracle():
     from hivae_b200 import embeddings as E
     assert np.array_equal(E.sincos_2d(256, 16, 16), O.sincos_2d(256, 16, 16))

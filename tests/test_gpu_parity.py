@@ -559,6 +559,32 @@ def test_unpatchify_both_feature_orders(dev):
     assert m.prepare_encoder_input(v).shape == (8, 8, 8, 8)
 
 
+@pytest.mark.parametrize("name", ["temporal", "legacy"])
+def test_amdmodel_golden(dev, golden, name):
+    """a18 sibling AMDModel (model_AMD.py:33-594) vs the unmodified reference, fp32: training forward (per-clip
+    timesteps for 'spatial', per-frame for 'default'; camera mask on the low band) and a 2-step sample.
+    'temporal' = temporal motion encoders + ImgSpatial 'decouple' (7 layers: swap after layer 5);
+    'legacy' = per-frame encoders + camera_down + AMDDiffusionTransformerModel 'plus'."""
+    import hivae_b200 as hv
+    g = golden("amd_model")
+    cfg = configs.AMDMODEL_TEMPORAL if name == "temporal" else configs.AMDMODEL_LEGACY
+    m = hv.AMDModel(**cfg)
+    m.load_state_dict(synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 7))
+    m.to(dev)
+    t = lambda k: g[k].to(dev)
+    _fix_noise(m, g["z0"])
+    ts = g[name + "_ts"]
+    per_clip = cfg["diffusion_model_type"] != "default"
+    m.prepare_timestep = (lambda batch_size, device, time_step=None: ts[::4].to(device)) if per_clip else \
+        (lambda batch_size, device, time_step=None: ts.to(device))
+    pre, vel, ld = m(t("video"), t("ref_img"), video_grey=t("vg"), ref_img_grey=t("rg"), camera_mask=t("mask") if cfg.get("use_mask") else None)
+    assert rel(pre, g[name + "_pre"]) <= TOL_F32
+    assert abs(float(ld["loss"]) - float(g[name + "_loss"][0])) <= 1e-4 * float(g[name + "_loss"][0])
+    assert abs(float(ld["rec_loss"]) - float(g[name + "_loss"][1])) <= 1e-4 * float(g[name + "_loss"][1])
+    zi, zt, zj = m.sample(t("video"), t("ref_img"), video_grey=t("vg"), ref_img_grey=t("rg"), sample_step=2)
+    assert rel(zt, g[name + "_zt"]) <= TOL_F32 and torch.equal(zj, t("video"))
+
+
 def _default(dev, dtype):
     import hivae_b200 as hv
     m = hv.AMDModel_New(**configs.DEFAULT)
