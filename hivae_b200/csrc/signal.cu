@@ -594,6 +594,71 @@ __global__ void __launch_bounds__(256, 3) freq_split3d_slab_kernel(const float* 
     }
 }
 
+// 32 x 32 x 32 volumes (the 2t = 32 frame clip of the default model): the three matrices are circulant
+// (C[i][k] = c[(k - i) mod 32], a circular convolution), so a thread keeps the 32 taps AND its 32-long line in
+// registers and every output is 32 FMAs with compile-time register indices — no shared-memory coefficient reads
+// at all (the generic kernel issues one LDS.128 per four FMAs, which is what bounds it).
+__device__ __forceinline__ void circ32_line(float* line, int stride, const float (&c)[32]) {
+    float xr[32];
+#pragma unroll
+    for (int k = 0; k < 32; ++k) xr[k] = line[k * stride];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+        for (int k = 0; k < 32; k += 4) {
+            a0 = fmaf(c[(k - i) & 31], xr[k], a0); a1 = fmaf(c[(k + 1 - i) & 31], xr[k + 1], a1);
+            a2 = fmaf(c[(k + 2 - i) & 31], xr[k + 2], a2); a3 = fmaf(c[(k + 3 - i) & 31], xr[k + 3], a3);
+        }
+        line[i * stride] = (a0 + a1) + (a2 + a3);
+    }
+}
+
+__global__ void __launch_bounds__(256, 2) freq_split3d_slab32_kernel(const float* __restrict__ x, const float* __restrict__ ct,
+                                                                     const float* __restrict__ ch, const float* __restrict__ cw,
+                                                                     float* __restrict__ lo, float* __restrict__ hi) {
+    constexpr int N = 32, TC = 8, P = N + 1, HW = N * N;
+    __shared__ float slab[TC * N * P];
+    const long long v = blockIdx.x >> 2;
+    const int t0 = (int)(blockIdx.x & 3) * TC;
+    const float* xv = x + v * (long long)N * HW;
+    float c[32];
+    // T axis from global memory; the column is loaded rotated by t0 so that the tap indices stay compile-time constants
+#pragma unroll
+    for (int k = 0; k < 32; ++k) c[k] = __ldg(ct + k);
+    for (int col = threadIdx.x; col < HW; col += 256) {
+        float xr[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) xr[j] = __ldg(xv + (long long)((j + t0) & 31) * HW + col);
+        float* dst = slab + (col >> 5) * P + (col & 31);
+#pragma unroll
+        for (int tt = 0; tt < TC; ++tt) {
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+                a0 = fmaf(c[(j - tt) & 31], xr[j], a0); a1 = fmaf(c[(j + 1 - tt) & 31], xr[j + 1], a1);
+                a2 = fmaf(c[(j + 2 - tt) & 31], xr[j + 2], a2); a3 = fmaf(c[(j + 3 - tt) & 31], xr[j + 3], a3);
+            }
+            dst[tt * N * P] = (a0 + a1) + (a2 + a3);
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 32; ++k) c[k] = __ldg(ch + k);
+    circ32_line(slab + (threadIdx.x >> 5) * N * P + (threadIdx.x & 31), P, c);   // H axis: line (tt, w), 256 lines
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 32; ++k) c[k] = __ldg(cw + k);
+    circ32_line(slab + threadIdx.x * P, 1, c);                                    // W axis: line (tt, h)
+    __syncthreads();
+    const long long off = v * (long long)N * HW + (long long)t0 * HW;
+    for (int i = threadIdx.x; i < TC * HW; i += 256) {
+        const float l = slab[(i >> 5) * P + (i & 31)];
+        lo[off + i] = l;
+        hi[off + i] = __ldg(x + off + i) - l;
+    }
+}
+
 extern "C" int hv_freq_split3d(const float* x, const float* ct, const float* ch, const float* cw,
                                float* lo, float* hi, int64_t vols, int T, int H, int W, void* stream) {
     HV_REQUIRE(vols >= 0 && T > 0 && H > 0 && W > 0, "hv_freq_split3d: bad sizes");
@@ -605,6 +670,11 @@ extern "C" int hv_freq_split3d(const float* x, const float* ct, const float* ch,
     size_t smem = (size_t)(3 * MAXN * MAXN + (size_t)T * H * (W + 1)) * sizeof(float);
     HV_REQUIRE(smem <= 227 * 1024, "hv_freq_split3d: volume %dx%dx%d needs %zu B of shared memory (> 227 KB)", T, H, W, smem);
     cudaStream_t st = hv_stream(stream);
+    if (T == 32 && H == 32 && W == 32) {  // circulant taps in registers (row 0 of each matrix)
+        freq_split3d_slab32_kernel<<<(unsigned)(vols * 4), 256, 0, st>>>(x, ct, ch, cw, lo, hi);
+        HV_LAUNCH_CHECK();
+        return HV_OK;
+    }
     if (MAXN == 32) {
         int TC = T;  // frames per slab: at least 4, at most 8 slabs' worth of parallelism per volume
         for (int d = 8; d >= 2; d >>= 1) if (T % d == 0 && T / d >= 4) { TC = T / d; break; }
