@@ -11,7 +11,8 @@ from .wavelet import DWT, IWT, dwt_init, iwt_init, dwt_pyramid, iwt_pyramid  # n
 from .frequency_utils import gaussian_low_pass_filter, freq_3d_filter  # noqa: F401
 from .rectified_flow import RectifiedFlow  # noqa: F401
 from .modules import (BasicTransformerBlock, BasicCrossTransformerBlock, AMDTransformerBlock, BasicDiTBlock,  # noqa: F401
-                      PatchEmbed, AMDLayerNormZero, AMDLayerNormZero_OneVariable, AdaLayerNorm, AMDTransformerMotionBlock)
+                      PatchEmbed, AMDLayerNormZero, AMDLayerNormZero_OneVariable, AMDLayerNormZero2Condition, AdaLayerNorm,
+                      AMDTransformerMotionBlock)
 from .transformer import (MotionEncoderLearnTokenTransformer, MotionEncoderLearnTokenOnlyTemporalTransformer,  # noqa: F401
                           MotionEncoderLearnTokenTemporalTransformer,
                           AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion,

@@ -60,11 +60,39 @@ class _AdaNorm(nn.Module):
         self.norm = nn.LayerNorm(embedding_dim, eps=eps, elementwise_affine=elementwise_affine)
 
 
+    @torch.no_grad()
+    def _modulate(self, streams, temb):
+        """standalone forward of the adaLN-Zero family: table = Linear(SiLU(temb)) by one small GEMM, then one
+        LayerNorm + modulate kernel per stream; returns ([modulated streams], [gates (B, 1, D)]).  (Inside the blocks
+        the table of ALL norms of a step comes from a single GEMM instead, engine.AdaPack.)"""
+        ctx = Ctx(temb.device, torch.float32)
+        D = self.embed_dim
+        t32 = temb.float().contiguous()
+        table = engine.small_linear(ctx, ops.silu(t32, torch.empty_like(t32)), ctx.f32(self.linear.weight),
+                                    ctx.f32(self.linear.bias), "ada_standalone").clone()
+        ada, outs, gates = Ada(table, 1, 1), [], []
+        nw = ctx.f32(self.norm.weight) if self.norm.weight is not None else None
+        nb = ctx.f32(self.norm.bias) if self.norm.bias is not None else None
+        for i, x in enumerate(streams):
+            res = x.float().contiguous()
+            B, L, _ = res.shape
+            y = torch.empty(B * L, D, dtype=torch.float32, device=res.device)
+            o = 3 * i * D  # chunk order per stream: shift, scale, gate
+            ops.ln_modulate(Rows(res, 0, L), nw, nb, self.norm.eps, y, ada, shift_mot=o, scale_mot=o + D, shift_img=o, scale_img=o + D)
+            outs.append(y.view(B, L, D).to(x.dtype))
+            gates.append(table[:, o + 2 * D:o + 3 * D][:, None, :].to(x.dtype))
+        return outs, gates
+
+
 class AMDLayerNormZero(_AdaNorm):
     """modules.py:881-904 (6 chunks: shift, scale, gate, enc_shift, enc_scale, enc_gate)."""
 
     def __init__(self, conditioning_dim, embedding_dim, elementwise_affine=True, eps=1e-5, bias=True):
         super().__init__(conditioning_dim, embedding_dim, 6, elementwise_affine, eps, bias)
+
+    def forward(self, hidden_states, encoder_hidden_states, temb):
+        (h, e), (g, eg) = self._modulate([hidden_states, encoder_hidden_states], temb)
+        return h, e, g, eg
 
 
 class AMDLayerNormZero_OneVariable(_AdaNorm):
@@ -72,6 +100,21 @@ class AMDLayerNormZero_OneVariable(_AdaNorm):
 
     def __init__(self, conditioning_dim, embedding_dim, elementwise_affine=True, eps=1e-5, bias=True):
         super().__init__(conditioning_dim, embedding_dim, 3, elementwise_affine, eps, bias)
+
+    def forward(self, hidden_states, temb):
+        (h,), (g,) = self._modulate([hidden_states], temb)
+        return h, g
+
+
+class AMDLayerNormZero2Condition(_AdaNorm):
+    """modules.py:930-956 (9 chunks: hidden, condition 1, condition 2, each shift, scale, gate)."""
+
+    def __init__(self, conditioning_dim, embedding_dim, elementwise_affine=True, eps=1e-5, bias=True):
+        super().__init__(conditioning_dim, embedding_dim, 9, elementwise_affine, eps, bias)
+
+    def forward(self, hidden_states, condition_states1, condition_states2, temb):
+        (h, c1, c2), (g, g1, g2) = self._modulate([hidden_states, condition_states1, condition_states2], temb)
+        return h, c1, c2, g, g1, g2
 
 
 class AdaLayerNorm(nn.Module):
@@ -87,6 +130,22 @@ class AdaLayerNorm(nn.Module):
         self.silu = nn.SiLU()
         self.linear = nn.Linear(embedding_dim, output_dim)
         self.norm = nn.LayerNorm(output_dim // 2, norm_eps, norm_elementwise_affine)
+
+    @torch.no_grad()
+    def forward(self, x, timestep=None, temb=None):
+        """x (B, L, D), temb (B, E): norm(x) * (1 + scale) + shift with the (shift, scale) chunk order of chunk_dim=1"""
+        ctx = Ctx(x.device, torch.float32)
+        D = self.norm.normalized_shape[0]
+        t32 = temb.float().contiguous()
+        table = engine.small_linear(ctx, ops.silu(t32, torch.empty_like(t32)), ctx.f32(self.linear.weight),
+                                    ctx.f32(self.linear.bias), "adaln_standalone")
+        res = x.float().contiguous()
+        B, L, _ = res.shape
+        y = torch.empty(B * L, D, dtype=torch.float32, device=res.device)
+        nw = ctx.f32(self.norm.weight) if self.norm.weight is not None else None
+        nb = ctx.f32(self.norm.bias) if self.norm.bias is not None else None
+        ops.ln_modulate(Rows(res, 0, L), nw, nb, self.norm.eps, y, Ada(table, 1, 1), shift_mot=0, scale_mot=D, shift_img=0, scale_img=D)
+        return y.view(B, L, D).to(x.dtype)
 
 
 class PatchEmbed(nn.Module):

@@ -10,7 +10,7 @@ T=120 run signal "dwt or freq or pyramid"
 T=120 run simt "linear_f32 or rope or patch_embed or unpatchify"
 T=120 run attn "attention"
 T=120 run gemm "linear_bf16 or qknorm or gated"
-T=120 run blocks "blocks"
+T=120 run blocks "blocks or adaln"
 T=180 run small "small_model"
 T=180 run variant "object_only or temporal_motion_encoder or imgspatial or sample_cross or amdmodel"
 T=120 run optim "adamw or clip"

@@ -585,6 +585,39 @@ def test_amdmodel_golden(dev, golden, name):
     assert rel(zt, g[name + "_zt"]) <= TOL_F32 and torch.equal(zj, t("video"))
 
 
+def test_adaln_modules_standalone(dev):
+    """AMDLayerNormZero / _OneVariable / 2Condition (modules.py:881-956) and AdaLayerNorm(chunk_dim=1)
+    (958-1013) as stand-alone modules against the reference formulas, fp32 1e-5."""
+    import torch.nn.functional as F
+    import hivae_b200 as hv
+    g = _gen(51)
+    B, L, L2, D, E = 5, 33, 7, 256, 64
+    x, c1, c2 = (torch.randn(B, n, D, generator=g) for n in (L, L2, 3))
+    temb = torch.randn(B, E, generator=g)
+
+    def ref(m, streams):
+        ch = F.linear(F.silu(temb), m.linear.weight, m.linear.bias).chunk(3 * len(streams), dim=1)
+        outs = [F.layer_norm(s, (D,), m.norm.weight, m.norm.bias, m.norm.eps) * (1 + ch[3 * i + 1])[:, None] + ch[3 * i][:, None]
+                for i, s in enumerate(streams)]
+        return outs, [ch[3 * i + 2][:, None] for i in range(len(streams))]
+
+    for cls, streams in ((hv.AMDLayerNormZero_OneVariable, [x]), (hv.AMDLayerNormZero, [x, c1]), (hv.AMDLayerNormZero2Condition, [x, c1, c2])):
+        torch.manual_seed(3)
+        m = cls(E, D)
+        with torch.no_grad():
+            m.norm.weight.normal_(1.0, 0.2), m.norm.bias.normal_(0.0, 0.2)
+        eo, eg = ref(m, streams)
+        got = m.to(dev)(*[s.to(dev) for s in streams], temb.to(dev))
+        n = len(streams)
+        for i in range(n):
+            assert rel(got[i], eo[i].detach()) <= 1e-5 and rel(got[n + i], eg[i].detach()) <= 1e-5, (cls.__name__, i)
+    torch.manual_seed(4)
+    m = hv.AdaLayerNorm(embedding_dim=E, output_dim=2 * D, norm_elementwise_affine=True, chunk_dim=1)
+    shift, scale = F.linear(F.silu(temb), m.linear.weight, m.linear.bias).chunk(2, dim=1)
+    exp = F.layer_norm(x, (D,), m.norm.weight, m.norm.bias, m.norm.eps) * (1 + scale)[:, None] + shift[:, None]
+    assert rel(m.to(dev)(x.to(dev), temb=temb.to(dev)), exp.detach()) <= 1e-5
+
+
 def _default(dev, dtype):
     import hivae_b200 as hv
     m = hv.AMDModel_New(**configs.DEFAULT)
