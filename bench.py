@@ -188,8 +188,19 @@ def run_ours(args):
     dist = None
     if world > 1:
         import torch.distributed as dist
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keeps NCCL's version banner off stdout (one JSON line)
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner with printf on stdout when the communicator is created; stdout must carry
+        # exactly one JSON line, so fd 1 points at stderr until the first collective has gone through
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            dist.all_reduce(torch.zeros(1, device=dev))
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved, 1)
+            os.close(saved)
     torch.set_grad_enabled(False)
 
     m = hv.AMDModel_New(**configs.DEFAULT)
