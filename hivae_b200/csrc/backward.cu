@@ -1,0 +1,225 @@
+// Building blocks of the backward pass of the blocks (`accelerator.backward(loss)` at
+// train_amd.py:489 reaches, through autograd, the backward of nn.Linear / LayerNorm / GELU(tanh) of
+// model/modules.py:651-1188).  The gradient GEMMs reuse the tcgen05 kernel of gemm_tc.cu (C = A W^T):
+//   dX[M,K] = dY[M,N]  W[N,K]      -> A = dY,   W := W^T  (K x N, from hv_transpose2d)
+//   dW[N,K] = dY^T[N,M] X[M,K]     -> A = dY^T, W := X^T  (both from hv_transpose2d), fp32 output
+//   db[N]   = column sums of dY    -> hv_colsum
+// Everything here is HBM-bound streaming work: 128-byte coalesced rows, fp32 accumulation, deterministic two-stage
+// reductions (fixed grid, fixed order).
+#include "hv_common.cuh"
+
+namespace {
+
+template <typename T> __device__ __forceinline__ float ldf(const T* p, long long i);
+template <> __device__ __forceinline__ float ldf<float>(const float* p, long long i) { return p[i]; }
+template <> __device__ __forceinline__ float ldf<__nv_bfloat16>(const __nv_bfloat16* p, long long i) { return __bfloat162float(p[i]); }
+template <typename T> __device__ __forceinline__ void stf(T* p, long long i, float v);
+template <> __device__ __forceinline__ void stf<float>(float* p, long long i, float v) { p[i] = v; }
+template <> __device__ __forceinline__ void stf<__nv_bfloat16>(__nv_bfloat16* p, long long i, float v) { p[i] = __float2bfloat16_rn(v); }
+
+// ---------------------------------------------------------------- out[c][r] = in[r][c]
+// 64 x 64 tiles through shared memory (pitch 65): reads and writes are both row-contiguous.
+template <typename T>
+__global__ void __launch_bounds__(256) transpose_kernel(const T* __restrict__ in, T* __restrict__ out, long long rows, long long cols,
+                                                        long long ld_in, long long ld_out) {
+    __shared__ T tile[64][65];
+    const long long r0 = blockIdx.y * 64ll, c0 = blockIdx.x * 64ll;
+    const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;  // 64 x 4
+    for (int i = ty; i < 64; i += 4)
+        if (r0 + i < rows && c0 + tx < cols) tile[i][tx] = in[(r0 + i) * ld_in + c0 + tx];
+    __syncthreads();
+    for (int i = ty; i < 64; i += 4)
+        if (c0 + i < cols && r0 + tx < rows) out[(c0 + i) * ld_out + r0 + tx] = tile[tx][i];
+}
+
+// ---------------------------------------------------------------- column sums, stage 1: partial[s][n] over a row slice
+template <typename T>
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const T* __restrict__ x, long long M, int N, long long ld,
+                                                             float* __restrict__ partial) {
+    __shared__ float sh[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int n = blockIdx.x * 32 + tx;
+    float acc = 0.f;
+    if (n < N)
+        for (long long m = blockIdx.y * 8ll + ty; m < M; m += (long long)gridDim.y * 8) acc += ldf<T>(x, m * ld + n);
+    sh[ty][tx] = acc;
+    __syncthreads();
+    if (ty == 0 && n < N) {
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s += sh[i][tx];
+        partial[(long long)blockIdx.y * N + n] = s;
+    }
+}
+__global__ void colsum_final_kernel(const float* __restrict__ partial, int S, int N, float* __restrict__ out) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    float s = 0.f;
+    for (int i = 0; i < S; ++i) s += partial[(long long)i * N + n];
+    out[n] = s;
+}
+
+// ---------------------------------------------------------------- dx = dy * d/dx gelu_tanh(x)
+__device__ __forceinline__ float gelu_tanh_grad(float x) {
+    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+    const float x2 = x * x, u = k0 * (x + k1 * x2 * x), t = tanhf(u);
+    return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * k0 * (1.0f + 3.0f * k1 * x2);
+}
+template <typename TI, typename TO>
+__global__ void gelu_bwd_kernel(const TI* __restrict__ pre, const TI* __restrict__ dy, TO* __restrict__ dx, long long n) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        stf<TO>(dx, i, ldf<TI>(dy, i) * gelu_tanh_grad(ldf<TI>(pre, i)));
+}
+
+// ---------------------------------------------------------------- LayerNorm backward (rows of D <= 2048, D % 128 == 0)
+// y = xhat * w + b, xhat = (x - mean) * rstd.  One warp per row, the row in registers:
+//   g = dy * w;  dx = rstd * (g - mean(g) - xhat * mean(g * xhat))      (written or accumulated into dx)
+//   dw += dy * xhat, db += dy   -> per-CTA partial sums in shared memory -> partial[cta][2][D] -> hv_colsum-style final
+template <int NV, typename TDY>
+__global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x, const TDY* __restrict__ dy, const float* __restrict__ w,
+                                                     float eps, long long rows, int D, float* __restrict__ dx, int accumulate,
+                                                     float* __restrict__ partial) {
+    extern __shared__ float sh[];  // [2][D] dw / db partials of the CTA
+    for (int i = threadIdx.x; i < 2 * D; i += 256) sh[i] = 0.f;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float inv_d = 1.0f / (float)D;
+    float dwa[NV * 4], dba[NV * 4];
+#pragma unroll
+    for (int j = 0; j < NV * 4; ++j) dwa[j] = dba[j] = 0.f;
+    for (long long r = blockIdx.x * 8ll + warp; r < rows; r += (long long)gridDim.x * 8) {
+        float xv[NV * 4], gv[NV * 4];
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            const float4 v = reinterpret_cast<const float4*>(x + r * D)[j * 32 + lane];
+            xv[4 * j] = v.x; xv[4 * j + 1] = v.y; xv[4 * j + 2] = v.z; xv[4 * j + 3] = v.w;
+            s += (v.x + v.y) + (v.z + v.w);
+        }
+        const float mean = hv_warp_sum(s) * inv_d;
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV * 4; ++j) { xv[j] -= mean; q += xv[j] * xv[j]; }
+        const float rstd = rsqrtf(hv_warp_sum(q) * inv_d + eps);
+        float c1 = 0.f, c2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int col = (j * 32 + lane) * 4 + e;
+                const float d = ldf<TDY>(dy, r * D + col);
+                const float xh = xv[4 * j + e] * rstd;
+                const float g = d * (w ? w[col] : 1.0f);
+                xv[4 * j + e] = xh; gv[4 * j + e] = g;
+                c1 += g; c2 += g * xh;
+                dwa[4 * j + e] += d * xh; dba[4 * j + e] += d;
+            }
+        }
+        c1 = hv_warp_sum(c1) * inv_d; c2 = hv_warp_sum(c2) * inv_d;
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            float4 o;
+            o.x = rstd * (gv[4 * j] - c1 - xv[4 * j] * c2); o.y = rstd * (gv[4 * j + 1] - c1 - xv[4 * j + 1] * c2);
+            o.z = rstd * (gv[4 * j + 2] - c1 - xv[4 * j + 2] * c2); o.w = rstd * (gv[4 * j + 3] - c1 - xv[4 * j + 3] * c2);
+            float4* dst = reinterpret_cast<float4*>(dx + r * D) + j * 32 + lane;
+            if (accumulate) { const float4 p = *dst; o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w; }
+            *dst = o;
+        }
+    }
+    // warps of the CTA add their register partials one after the other (deterministic order)
+    for (int wv = 0; wv < 8; ++wv) {
+        if (warp == wv) {
+#pragma unroll
+            for (int j = 0; j < NV; ++j)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const int col = (j * 32 + lane) * 4 + e;
+                    sh[col] += dwa[4 * j + e]; sh[D + col] += dba[4 * j + e];
+                }
+        }
+        __syncthreads();
+    }
+    for (int i = threadIdx.x; i < 2 * D; i += 256) partial[(long long)blockIdx.x * 2 * D + i] = sh[i];
+}
+
+}  // namespace
+
+extern "C" int hv_transpose2d(const void* in, void* out, int64_t rows, int64_t cols, int64_t ld_in, int64_t ld_out, int dtype, void* stream) {
+    HV_REQUIRE(rows >= 0 && cols >= 0 && ld_in >= cols && ld_out >= rows && (dtype == HV_F32 || dtype == HV_BF16), "hv_transpose2d: bad arguments");
+    if (rows == 0 || cols == 0) return HV_OK;
+    dim3 grid((unsigned)((cols + 63) / 64), (unsigned)((rows + 63) / 64));
+    if (dtype == HV_F32) transpose_kernel<float><<<grid, 256, 0, hv_stream(stream)>>>((const float*)in, (float*)out, rows, cols, ld_in, ld_out);
+    else transpose_kernel<__nv_bfloat16><<<grid, 256, 0, hv_stream(stream)>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+// number of row slices (= rows of fp32 workspace of width N) the column-sum entry points use
+extern "C" int hv_colsum_slices() { return hv_num_sms() * 2; }
+
+// out[n] = sum_m x[m][n]  (bias gradient of nn.Linear); workspace: hv_colsum_slices() * N floats
+extern "C" int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype, float* workspace, float* out, void* stream) {
+    HV_REQUIRE(M >= 0 && N > 0 && ld >= N && workspace && out && (dtype == HV_F32 || dtype == HV_BF16), "hv_colsum: bad arguments");
+    int S = hv_colsum_slices();
+    const long long strips = (N + 31) / 32;
+    long long sy = (long long)S / strips;  // keep the grid near 2 CTAs per SM overall
+    if (sy < 1) sy = 1;
+    if (sy > (M + 7) / 8) sy = (M + 7) / 8 > 0 ? (M + 7) / 8 : 1;
+    S = (int)sy;
+    dim3 grid((unsigned)strips, (unsigned)S);
+    cudaStream_t st = hv_stream(stream);
+    if (dtype == HV_F32) colsum_partial_kernel<float><<<grid, 256, 0, st>>>((const float*)x, M, N, ld, workspace);
+    else colsum_partial_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, M, N, ld, workspace);
+    HV_LAUNCH_CHECK();
+    colsum_final_kernel<<<(N + 255) / 256, 256, 0, st>>>(workspace, S, N, out);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+// dx = dy * gelu_tanh'(pre)   (FeedForward's GELU(approximate="tanh"), modules.py:712-719 through diffusers)
+extern "C" int hv_gelu_tanh_bwd(const void* pre, const void* dy, void* dx, int64_t n, int dtype_in, int dtype_out, void* stream) {
+    HV_REQUIRE(n >= 0 && pre && dy && dx, "hv_gelu_tanh_bwd: bad arguments");
+    if (n == 0) return HV_OK;
+    long long grid = (n + 255) / 256;
+    if (grid > (long long)hv_num_sms() * 16) grid = (long long)hv_num_sms() * 16;
+    cudaStream_t st = hv_stream(stream);
+    if (dtype_in == HV_BF16 && dtype_out == HV_BF16) gelu_bwd_kernel<__nv_bfloat16, __nv_bfloat16><<<(unsigned)grid, 256, 0, st>>>((const __nv_bfloat16*)pre, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, n);
+    else if (dtype_in == HV_F32 && dtype_out == HV_F32) gelu_bwd_kernel<float, float><<<(unsigned)grid, 256, 0, st>>>((const float*)pre, (const float*)dy, (float*)dx, n);
+    else if (dtype_in == HV_BF16 && dtype_out == HV_F32) gelu_bwd_kernel<__nv_bfloat16, float><<<(unsigned)grid, 256, 0, st>>>((const __nv_bfloat16*)pre, (const __nv_bfloat16*)dy, (float*)dx, n);
+    else HV_REQUIRE(false, "hv_gelu_tanh_bwd: unsupported dtype combination %d -> %d", dtype_in, dtype_out);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+// number of CTAs (= rows of the [cta][2][D] fp32 workspace) hv_layernorm_bwd uses
+extern "C" int hv_layernorm_bwd_ctas() { return hv_num_sms() * 2; }
+
+// LayerNorm backward over dense fp32 rows: dx (written, or accumulated when accumulate != 0), dw, db.
+// workspace: hv_layernorm_bwd_ctas() * 2 * D floats.  dw / db may be NULL (elementwise_affine=False).
+extern "C" int hv_layernorm_bwd(const float* x, const void* dy, int dy_dtype, const float* w, float eps, int64_t rows, int D,
+                                float* dx, int accumulate, float* workspace, float* dw, float* db, void* stream) {
+    HV_REQUIRE(rows >= 0 && D > 0 && D % 128 == 0 && D <= 1024, "hv_layernorm_bwd: D=%d must be a multiple of 128 and <= 1024", D);
+    HV_REQUIRE(x && dy && dx && workspace, "hv_layernorm_bwd: null argument");
+    if (rows == 0) return HV_OK;
+    int ctas = hv_layernorm_bwd_ctas();
+    if (ctas > (rows + 7) / 8) ctas = (int)((rows + 7) / 8);
+    cudaStream_t st = hv_stream(stream);
+    const size_t smem = (size_t)2 * D * sizeof(float);
+#define LNB(NV, T) ln_bwd_kernel<NV, T><<<ctas, 256, smem, st>>>(x, (const T*)dy, w, eps, rows, D, dx, accumulate, workspace)
+#define LNB_T(NV) do { if (dy_dtype == HV_F32) LNB(NV, float); else LNB(NV, __nv_bfloat16); } while (0)
+    switch (D / 128) {
+        case 1: LNB_T(1); break; case 2: LNB_T(2); break; case 3: LNB_T(3); break; case 4: LNB_T(4); break;
+        case 5: LNB_T(5); break; case 6: LNB_T(6); break; case 7: LNB_T(7); break; default: LNB_T(8); break;
+    }
+#undef LNB_T
+#undef LNB
+    HV_LAUNCH_CHECK();
+    if (dw || db) {  // [ctas][2*D] -> column sums; dw = first D columns, db = last D
+        float* fin = workspace + (size_t)hv_layernorm_bwd_ctas() * 2 * D;  // 2*D floats behind the partials
+        colsum_final_kernel<<<(2 * D + 255) / 256, 256, 0, st>>>(workspace, ctas, 2 * D, fin);
+        HV_LAUNCH_CHECK();
+        if (dw) HV_CUDA(cudaMemcpyAsync(dw, fin, (size_t)D * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        if (db) HV_CUDA(cudaMemcpyAsync(db, fin + D, (size_t)D * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    }
+    return HV_OK;
+}

@@ -134,6 +134,22 @@ int hv_axpy(float a, const float* x, float* y, int64_t n, void* stream);
 int hv_rows_scatter(const float* src, int64_t src_stride_f, int64_t src_stride_i, const float* add,
                     float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D, void* stream);
 /* dense fp32 out[(f*L+i), :] = res[f*frame_rows + row_off + i, :] */
+/* ---- building blocks of the backward pass (autograd of nn.Linear / LayerNorm / GELU under `accelerator.backward`,
+ * train_amd.py:489; forward definitions model/modules.py:651-1188).  The gradient GEMMs themselves go through
+ * hv_linear_bf16 with transposed operands:  dX = dY W  (A = dY, W := W^T),  dW = dY^T X  (A = dY^T, W := X^T). */
+/* out[c][r] = in[r][c]; dtype HV_F32 / HV_BF16; ld in elements */
+int hv_transpose2d(const void* in, void* out, int64_t rows, int64_t cols, int64_t ld_in, int64_t ld_out, int dtype, void* stream);
+/* bias gradient: out[n] = sum_m x[m][n]; workspace = hv_colsum_slices() * N floats */
+int hv_colsum_slices(void);
+int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype, float* workspace, float* out, void* stream);
+/* dx = dy * d/dx gelu_tanh(pre)  (diffusers GELU(approximate="tanh") inside FeedForward, modules.py:712-719) */
+int hv_gelu_tanh_bwd(const void* pre, const void* dy, void* dx, int64_t n, int dtype_in, int dtype_out, void* stream);
+/* nn.LayerNorm backward over dense fp32 rows (D % 128 == 0, D <= 1024): dx written (or accumulated), dw / db optional.
+ * workspace = (hv_layernorm_bwd_ctas() + 1) * 2 * D floats */
+int hv_layernorm_bwd_ctas(void);
+int hv_layernorm_bwd(const float* x, const void* dy, int dy_dtype, const float* w, float eps, int64_t rows, int D,
+                     float* dx, int accumulate, float* workspace, float* dw, float* db, void* stream);
+
 /* Diagnostics: with HV_ATTN_PROF=1 in the environment the tcgen05 attention kernel accumulates per-phase cycle
  * counters (148 CTAs x 2 key halves x 8 u64: wait S, max pass, max exchange, O epilogue, exp pass, publish P, full
  * tiles, tail tiles); this copies them to `host` and clears them.  Returns 0 when profiling is off. */

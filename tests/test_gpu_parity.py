@@ -713,3 +713,61 @@ def test_clip_materialize_and_mse(dev):
     assert abs(float(optim.mse_loss(a.to(dev), b.to(dev))) - float(torch.nn.functional.mse_loss(a, b))) <= 1e-6
     a, b = torch.randn(1003, generator=g), torch.randn(1003, generator=g)  # ragged tail
     assert abs(float(optim.mse_loss(a.to(dev), b.to(dev))) - float(torch.nn.functional.mse_loss(a, b))) <= 1e-6
+
+
+# =============================================================================== backward building blocks
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,dtype", [((1000, 520), torch.bfloat16), ((77, 129), torch.float32), ((4096, 1024), torch.bfloat16)])
+def test_transpose_and_colsum(dev, shape, dtype):
+    from hivae_b200 import backward as B
+    x = torch.randn(*shape, generator=_gen(61)).to(dtype)
+    assert torch.equal(B.transpose2d(x.to(dev)).cpu(), x.t().contiguous())       # pure data movement: bit-exact
+    wide = torch.randn(shape[0], shape[1] + 8, generator=_gen(62)).to(dtype).to(dev)
+    assert torch.equal(B.transpose2d(wide[:, 3:3 + shape[1]]).cpu(), wide[:, 3:3 + shape[1]].t().contiguous().cpu())  # strided view
+    assert rel(B.colsum(x.to(dev)), x.double().sum(0).float()) <= 1e-5
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N,K", [(1024, 512, 256), (4096, 1024, 1024), (2304, 3072, 1024)])
+def test_linear_backward_vs_autograd(dev, M, N, K):
+    """dX, dW, db of y = x W^T + b on the tcgen05 GEMM against torch autograd (fp64 on the same bf16-rounded operands);
+    bf16 tolerance 2e-2 for the bf16 dX, 1e-3 for the fp32 dW / db"""
+    from hivae_b200 import backward as B
+    g = _gen(63)
+    x = (torch.randn(M, K, generator=g) * 0.5).to(torch.bfloat16)
+    w = (torch.randn(N, K, generator=g) * 0.05).to(torch.bfloat16)
+    dy = (torch.randn(M, N, generator=g) * 0.1).to(torch.bfloat16)
+    with torch.enable_grad():
+        xr, wr, br = x.double().requires_grad_(), w.double().requires_grad_(), torch.zeros(N, dtype=torch.float64, requires_grad=True)
+        (torch.nn.functional.linear(xr, wr, br) * dy.double()).sum().backward()
+    dx, dw, db = B.linear_backward(dy.to(dev), x.to(dev), w.to(dev))
+    assert dx.dtype == torch.bfloat16 and dw.dtype == torch.float32
+    assert rel(dx, xr.grad.float()) <= TOL_BF16
+    assert rel(dw, wr.grad.float()) <= 1e-3 and rel(db, br.grad.float()) <= 1e-3
+    dx32, _, _ = B.linear_backward(dy.to(dev), x.to(dev), w.to(dev), dx_dtype=torch.float32)
+    assert rel(dx32, xr.grad.float()) <= 1e-3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gelu_and_layernorm_backward_vs_autograd(dev, dtype):
+    from hivae_b200 import backward as B
+    g = _gen(64)
+    pre = (torch.randn(333, 1024, generator=g) * 2).to(dtype)
+    dy = torch.randn(333, 1024, generator=g).to(dtype)
+    with torch.enable_grad():
+        p = pre.double().requires_grad_()
+        (torch.nn.functional.gelu(p, approximate="tanh") * dy.double()).sum().backward()
+    assert rel(B.gelu_tanh_backward(pre.to(dev), dy.to(dev)), p.grad.float()) <= (1e-5 if dtype == torch.float32 else 1e-2)
+    for D, rows in ((1024, 1000), (512, 77), (128, 9)):
+        x = torch.randn(rows, D, generator=g) * 1.5 + 0.3
+        w, b = torch.randn(D, generator=g) * 0.3 + 1.0, torch.randn(D, generator=g) * 0.1
+        d = torch.randn(rows, D, generator=g).to(dtype)
+        with torch.enable_grad():
+            xr, wr, br = x.double().requires_grad_(), w.double().requires_grad_(), b.double().requires_grad_()
+            (torch.nn.functional.layer_norm(xr, (D,), wr, br, 1e-5) * d.double()).sum().backward()
+        dx, dw, db = B.layernorm_backward(x.to(dev), d.to(dev), w.to(dev), 1e-5)
+        assert rel(dx, xr.grad.float()) <= 1e-5 and rel(dw, wr.grad.float()) <= 1e-5 and rel(db, br.grad.float()) <= 1e-5, (D, rows)
+        base = torch.randn(rows, D, generator=g)
+        acc, _, _ = B.layernorm_backward(x.to(dev), d.to(dev), w.to(dev), 1e-5, dx=base.clone().to(dev), accumulate=True)
+        assert rel(acc, base + xr.grad.float()) <= 1e-5
