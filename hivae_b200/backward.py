@@ -34,7 +34,7 @@ def colsum(x):
     return out
 
 
-def linear_backward(dy, x, w, need_dx=True, dx_dtype=torch.bfloat16):
+def linear_backward(dy, x, w, need_dx=True, dx_dtype=torch.bfloat16, w_t=None):
     """Gradients of y = x @ w.T + b for bf16 operands (fp32 accumulation on the tensor cores):
     dy (M, N), x (M, K), w (N, K)  ->  dx (M, K) in `dx_dtype`, dw (N, K) fp32, db (N,) fp32.
     dX = dY W and dW = dY^T X both run on the tcgen05 GEMM (C = A B^T) with transposed bf16 operand copies."""
@@ -47,7 +47,7 @@ def linear_backward(dy, x, w, need_dx=True, dx_dtype=torch.bfloat16):
     dx = None
     if need_dx:
         dx = torch.empty(M, K, dtype=dx_dtype, device=dy.device)
-        ops.linear(dy, transpose2d(w), ops.epi_store(dx))              # (M, N) x (K, N)^T
+        ops.linear(dy, w_t if w_t is not None else transpose2d(w), ops.epi_store(dx))  # (M, N) x (K, N)^T; W^T is reusable for a whole step
     dw = torch.empty(N, K, dtype=torch.float32, device=dy.device)
     ops.linear(transpose2d(dy), transpose2d(x), ops.epi_store(dw))     # (N, M) x (K, M)^T
     return dx, dw, colsum(dy)

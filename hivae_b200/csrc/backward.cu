@@ -19,6 +19,26 @@ template <> __device__ __forceinline__ void stf<__nv_bfloat16>(__nv_bfloat16* p,
 
 // ---------------------------------------------------------------- out[c][r] = in[r][c]
 // 64 x 64 tiles through shared memory (pitch 65): reads and writes are both row-contiguous.
+// bf16 fast path (even sizes / strides): 4-byte accesses on both sides — a warp reads 128 B of an input row and writes
+// 128 B of an output row per instruction; the tile is stored transposed ([col][row], pitch 66) so that the write side
+// reads row pairs as one word.
+__global__ void __launch_bounds__(256) transpose_bf16x2_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                                               long long rows, long long cols, long long ld_in, long long ld_out) {
+    __shared__ __align__(4) __nv_bfloat16 tile[64][66];
+    const long long r0 = blockIdx.y * 64ll, c0 = blockIdx.x * 64ll;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    for (int i = ty; i < 64; i += 8) {
+        if (r0 + i < rows && c0 + 2 * tx < cols) {  // cols even: the pair is inside
+            const __nv_bfloat162 v = *reinterpret_cast<const __nv_bfloat162*>(in + (r0 + i) * ld_in + c0 + 2 * tx);
+            tile[2 * tx][i] = v.x; tile[2 * tx + 1][i] = v.y;
+        }
+    }
+    __syncthreads();
+    for (int j = ty; j < 64; j += 8)
+        if (c0 + j < cols && r0 + 2 * tx < rows)
+            *reinterpret_cast<__nv_bfloat162*>(out + (c0 + j) * ld_out + r0 + 2 * tx) = *reinterpret_cast<const __nv_bfloat162*>(&tile[j][2 * tx]);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) transpose_kernel(const T* __restrict__ in, T* __restrict__ out, long long rows, long long cols,
                                                         long long ld_in, long long ld_out) {
@@ -51,6 +71,27 @@ __global__ void __launch_bounds__(256) colsum_partial_kernel(const T* __restrict
         partial[(long long)blockIdx.y * N + n] = s;
     }
 }
+// bf16, two columns per thread (a warp reads 128 B of a row); N and ld even
+__global__ void __launch_bounds__(256) colsum_partial_bf16x2_kernel(const __nv_bfloat16* __restrict__ x, long long M, int N, long long ld,
+                                                                    float* __restrict__ partial) {
+    __shared__ float sh[8][65];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int n = blockIdx.x * 64 + 2 * tx;
+    float a0 = 0.f, a1 = 0.f;
+    if (n < N)
+        for (long long m = blockIdx.y * 8ll + ty; m < M; m += (long long)gridDim.y * 8) {
+            const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(x + m * ld + n));
+            a0 += v.x; a1 += v.y;
+        }
+    sh[ty][2 * tx] = a0; sh[ty][2 * tx + 1] = a1;
+    __syncthreads();
+    if (ty < 2 && n < N) {
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s += sh[i][2 * tx + ty];
+        partial[(long long)blockIdx.y * N + n + ty] = s;
+    }
+}
 __global__ void colsum_final_kernel(const float* __restrict__ partial, int S, int N, float* __restrict__ out) {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
@@ -69,6 +110,22 @@ template <typename TI, typename TO>
 __global__ void gelu_bwd_kernel(const TI* __restrict__ pre, const TI* __restrict__ dy, TO* __restrict__ dx, long long n) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         stf<TO>(dx, i, ldf<TI>(dy, i) * gelu_tanh_grad(ldf<TI>(pre, i)));
+}
+
+// bf16 -> bf16, 8 elements (16 bytes) per thread
+__global__ void gelu_bwd_bf16x8_kernel(const uint4* __restrict__ pre, const uint4* __restrict__ dy, uint4* __restrict__ dx, long long n8) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+        const uint4 p = pre[i], d = dy[i];
+        const uint32_t pw[4] = {p.x, p.y, p.z, p.w}, dw[4] = {d.x, d.y, d.z, d.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float p0 = __uint_as_float(pw[k] << 16), p1 = __uint_as_float(pw[k] & 0xffff0000u);
+            const float d0 = __uint_as_float(dw[k] << 16), d1 = __uint_as_float(dw[k] & 0xffff0000u);
+            o[k] = hv_pack_bf16(d0 * gelu_tanh_grad(p0), d1 * gelu_tanh_grad(p1));
+        }
+        dx[i] = make_uint4(o[0], o[1], o[2], o[3]);
+    }
 }
 
 // ---------------------------------------------------------------- LayerNorm backward (rows of D <= 2048, D % 128 == 0)
@@ -149,6 +206,8 @@ extern "C" int hv_transpose2d(const void* in, void* out, int64_t rows, int64_t c
     if (rows == 0 || cols == 0) return HV_OK;
     dim3 grid((unsigned)((cols + 63) / 64), (unsigned)((rows + 63) / 64));
     if (dtype == HV_F32) transpose_kernel<float><<<grid, 256, 0, hv_stream(stream)>>>((const float*)in, (float*)out, rows, cols, ld_in, ld_out);
+    else if (((rows | cols | ld_in | ld_out) & 1) == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 3) == 0)
+        transpose_bf16x2_kernel<<<grid, 256, 0, hv_stream(stream)>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out);
     else transpose_kernel<__nv_bfloat16><<<grid, 256, 0, hv_stream(stream)>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out);
     HV_LAUNCH_CHECK();
     return HV_OK;
@@ -161,7 +220,8 @@ extern "C" int hv_colsum_slices() { return hv_num_sms() * 2; }
 extern "C" int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype, float* workspace, float* out, void* stream) {
     HV_REQUIRE(M >= 0 && N > 0 && ld >= N && workspace && out && (dtype == HV_F32 || dtype == HV_BF16), "hv_colsum: bad arguments");
     int S = hv_colsum_slices();
-    const long long strips = (N + 31) / 32;
+    const bool x2 = dtype == HV_BF16 && (N % 2 == 0) && (ld % 2 == 0) && (reinterpret_cast<uintptr_t>(x) & 3) == 0;
+    const long long strips = x2 ? (N + 63) / 64 : (N + 31) / 32;
     long long sy = (long long)S / strips;  // keep the grid near 2 CTAs per SM overall
     if (sy < 1) sy = 1;
     if (sy > (M + 7) / 8) sy = (M + 7) / 8 > 0 ? (M + 7) / 8 : 1;
@@ -169,6 +229,7 @@ extern "C" int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype,
     dim3 grid((unsigned)strips, (unsigned)S);
     cudaStream_t st = hv_stream(stream);
     if (dtype == HV_F32) colsum_partial_kernel<float><<<grid, 256, 0, st>>>((const float*)x, M, N, ld, workspace);
+    else if (x2) colsum_partial_bf16x2_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, M, N, ld, workspace);
     else colsum_partial_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, M, N, ld, workspace);
     HV_LAUNCH_CHECK();
     colsum_final_kernel<<<(N + 255) / 256, 256, 0, st>>>(workspace, S, N, out);
@@ -183,7 +244,12 @@ extern "C" int hv_gelu_tanh_bwd(const void* pre, const void* dy, void* dx, int64
     long long grid = (n + 255) / 256;
     if (grid > (long long)hv_num_sms() * 16) grid = (long long)hv_num_sms() * 16;
     cudaStream_t st = hv_stream(stream);
-    if (dtype_in == HV_BF16 && dtype_out == HV_BF16) gelu_bwd_kernel<__nv_bfloat16, __nv_bfloat16><<<(unsigned)grid, 256, 0, st>>>((const __nv_bfloat16*)pre, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, n);
+    const bool vec = (n % 8 == 0) && ((reinterpret_cast<uintptr_t>(pre) | reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(dx)) & 15) == 0;
+    if (dtype_in == HV_BF16 && dtype_out == HV_BF16 && vec) {
+        long long g8 = (n / 8 + 255) / 256;
+        if (g8 > (long long)hv_num_sms() * 16) g8 = (long long)hv_num_sms() * 16;
+        gelu_bwd_bf16x8_kernel<<<(unsigned)g8, 256, 0, st>>>((const uint4*)pre, (const uint4*)dy, (uint4*)dx, n / 8);
+    } else if (dtype_in == HV_BF16 && dtype_out == HV_BF16) gelu_bwd_kernel<__nv_bfloat16, __nv_bfloat16><<<(unsigned)grid, 256, 0, st>>>((const __nv_bfloat16*)pre, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, n);
     else if (dtype_in == HV_F32 && dtype_out == HV_F32) gelu_bwd_kernel<float, float><<<(unsigned)grid, 256, 0, st>>>((const float*)pre, (const float*)dy, (float*)dx, n);
     else if (dtype_in == HV_BF16 && dtype_out == HV_F32) gelu_bwd_kernel<__nv_bfloat16, float><<<(unsigned)grid, 256, 0, st>>>((const __nv_bfloat16*)pre, (const __nv_bfloat16*)dy, (float*)dx, n);
     else HV_REQUIRE(false, "hv_gelu_tanh_bwd: unsupported dtype combination %d -> %d", dtype_in, dtype_out);
