@@ -161,12 +161,23 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
         float c1 = 0.f, c2 = 0.f;
 #pragma unroll
         for (int j = 0; j < NV; ++j) {
+            // four consecutive columns per lane: one 16-byte (fp32) or 8-byte (bf16) load of dy, one 16-byte load of w
+            float dv[4];
+            if constexpr (sizeof(TDY) == 4) {
+                const float4 t = reinterpret_cast<const float4*>(dy + r * D)[j * 32 + lane];
+                dv[0] = t.x; dv[1] = t.y; dv[2] = t.z; dv[3] = t.w;
+            } else {
+                const uint2 t = reinterpret_cast<const uint2*>(dy + r * D)[j * 32 + lane];
+                dv[0] = __uint_as_float(t.x << 16); dv[1] = __uint_as_float(t.x & 0xffff0000u);
+                dv[2] = __uint_as_float(t.y << 16); dv[3] = __uint_as_float(t.y & 0xffff0000u);
+            }
+            const float4 wv4 = w ? __ldg(reinterpret_cast<const float4*>(w) + j * 32 + lane) : make_float4(1.f, 1.f, 1.f, 1.f);
+            const float wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                const int col = (j * 32 + lane) * 4 + e;
-                const float d = ldf<TDY>(dy, r * D + col);
+                const float d = dv[e];
                 const float xh = xv[4 * j + e] * rstd;
-                const float g = d * (w ? w[col] : 1.0f);
+                const float g = d * wv[e];
                 xv[4 * j + e] = xh; gv[4 * j + e] = g;
                 c1 += g; c2 += g * xh;
                 dwa[4 * j + e] += d * xh; dba[4 * j + e] += d;
