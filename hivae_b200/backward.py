@@ -77,3 +77,35 @@ def layernorm_backward(x, dy, weight, eps, dx=None, accumulate=False, affine_gra
     _lib.check(lib.hv_layernorm_bwd(_p(x), _p(dy), _dt(dy), _p(weight), float(eps), rows, D, _p(dx), int(bool(accumulate)),
                                     _p(ws), _p(dw), _p(db), _stream()))
     return dx, dw, db
+
+
+def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, scale):
+    """Gradients of ops.attention (head_dim 64, no mask): q / k / v / out / dout are 2-D (rows, heads*64) views in one
+    dtype (bf16 or fp32) with unit column stride -> (dq, dk, dv) of the same dtype, dense (rows, heads*64)."""
+    _lib.require_device()
+    for t in (q, k, v, out, dout):
+        assert t.is_cuda and t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype
+    dq = torch.zeros(q.shape[0], heads * 64, dtype=q.dtype, device=q.device)
+    dk = torch.zeros(k.shape[0], heads * 64, dtype=q.dtype, device=q.device)
+    dv = torch.zeros(v.shape[0], heads * 64, dtype=q.dtype, device=q.device)
+    stats = torch.empty(seqs * heads * Lq * 2, dtype=torch.float32, device=q.device)
+    _lib.check(_lib.load().hv_attention_bwd(
+        _p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0), _p(dout), dout.stride(0),
+        _p(dq), dq.stride(0), _p(dk), dk.stride(0), _p(dv), dv.stride(0), _dt(q), seqs, heads, 64, Lq, Lkv,
+        C.byref(qmap), C.byref(kvmap), float(scale), _p(stats), _stream()))
+    return dq, dk, dv
+
+
+def headnorm64_backward(x, dy, weight, heads, eps=1e-6):
+    """backward of the per-head LayerNorm(64) of q / k (QK-norm): x (pre-norm), dy are (tokens, heads*64) views (bf16 or
+    fp32, unit column stride) -> (dx dense, dw (64,), db (64,))"""
+    _lib.require_device()
+    assert x.is_cuda and x.dim() == 2 and x.shape == dy.shape and x.shape[1] == heads * 64 and x.dtype == dy.dtype
+    assert x.stride(1) == 1 and dy.stride(1) == 1
+    lib = _lib.load()
+    dx = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+    ws = torch.empty((lib.hv_layernorm_bwd_ctas() + 1) * 128, dtype=torch.float32, device=x.device)
+    dw, db = (torch.empty(64, dtype=torch.float32, device=x.device) for _ in range(2))
+    _lib.check(lib.hv_headnorm64_bwd(_p(x), x.stride(0), _p(dy), dy.stride(0), _p(weight), float(eps), x.shape[0], heads,
+                                     _p(dx), dx.stride(0), _dt(x), _p(ws), _p(dw), _p(db), _stream()))
+    return dx, dw, db

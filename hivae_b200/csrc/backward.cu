@@ -210,7 +210,68 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
     for (int i = threadIdx.x; i < 2 * D; i += 256) partial[(long long)blockIdx.x * 2 * D + i] = sh[i];
 }
 
+// ---------------------------------------------------------------- per-head LayerNorm(64) backward (QK-norm)
+// q (or k) = LayerNorm_64(q_raw) * w + b per (token, head) — diffusers Attention(qk_norm="layer_norm"), eps 1e-6
+// (modules.py:699-707).  Row r = (token, head) lives at x + token*ld + head*64; one warp per row, two columns per lane.
+template <typename T>
+__global__ void __launch_bounds__(256) headnorm_bwd_kernel(const T* __restrict__ x, long long ldx, const T* __restrict__ dy, long long lddy,
+                                                           const float* __restrict__ w, float eps, long long tokens, int heads,
+                                                           T* __restrict__ dx, long long lddx, float* __restrict__ partial) {
+    __shared__ float sh[8][128];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float w0 = w ? w[2 * lane] : 1.f, w1 = w ? w[2 * lane + 1] : 1.f;
+    float dw0 = 0.f, dw1 = 0.f, db0 = 0.f, db1 = 0.f;
+    const long long rows = tokens * heads;
+    for (long long r = blockIdx.x * 8ll + warp; r < rows; r += (long long)gridDim.x * 8) {
+        const long long t = r / heads;
+        const int c = (int)(r - t * heads) * 64 + 2 * lane;
+        float x0 = ldf<T>(x, t * ldx + c), x1 = ldf<T>(x, t * ldx + c + 1);
+        const float d0 = ldf<T>(dy, t * lddy + c), d1 = ldf<T>(dy, t * lddy + c + 1);
+        const float mean = hv_warp_sum(x0 + x1) * (1.f / 64.f);
+        x0 -= mean; x1 -= mean;
+        const float rstd = rsqrtf(hv_warp_sum(x0 * x0 + x1 * x1) * (1.f / 64.f) + eps);
+        x0 *= rstd; x1 *= rstd;
+        const float g0 = d0 * w0, g1 = d1 * w1;
+        const float c1 = hv_warp_sum(g0 + g1) * (1.f / 64.f), c2 = hv_warp_sum(g0 * x0 + g1 * x1) * (1.f / 64.f);
+        stf<T>(dx, t * lddx + c, rstd * (g0 - c1 - x0 * c2));
+        stf<T>(dx, t * lddx + c + 1, rstd * (g1 - c1 - x1 * c2));
+        dw0 += d0 * x0; dw1 += d1 * x1; db0 += d0; db1 += d1;
+    }
+    sh[warp][2 * lane] = dw0; sh[warp][2 * lane + 1] = dw1; sh[warp][64 + 2 * lane] = db0; sh[warp][64 + 2 * lane + 1] = db1;
+    __syncthreads();
+    if (threadIdx.x < 128) {
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s += sh[i][threadIdx.x];
+        partial[(long long)blockIdx.x * 128 + threadIdx.x] = s;
+    }
+}
+
 }  // namespace
+
+// backward of the per-head LayerNorm(64) of q / k (QK-norm): x, dy, dx are (tokens, heads*64) views with their own leading
+// dimensions and one dtype; dw, db (64 each, fp32) are summed over tokens AND heads (the affine is shared by all heads).
+// workspace = (hv_layernorm_bwd_ctas() + 1) * 128 floats.
+extern "C" int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int64_t lddy, const float* w, float eps, int64_t tokens,
+                                 int heads, void* dx, int64_t lddx, int dtype, float* workspace, float* dw, float* db, void* stream) {
+    HV_REQUIRE(tokens >= 0 && heads > 0 && x && dy && dx && workspace && (dtype == HV_F32 || dtype == HV_BF16), "hv_headnorm64_bwd: bad arguments");
+    if (tokens == 0) return HV_OK;
+    int ctas = hv_layernorm_bwd_ctas();
+    const long long rows = tokens * heads;
+    if (ctas > (rows + 7) / 8) ctas = (int)((rows + 7) / 8);
+    cudaStream_t st = hv_stream(stream);
+    if (dtype == HV_F32) headnorm_bwd_kernel<float><<<ctas, 256, 0, st>>>((const float*)x, ldx, (const float*)dy, lddy, w, eps, tokens, heads, (float*)dx, lddx, workspace);
+    else headnorm_bwd_kernel<__nv_bfloat16><<<ctas, 256, 0, st>>>((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy, w, eps, tokens, heads, (__nv_bfloat16*)dx, lddx, workspace);
+    HV_LAUNCH_CHECK();
+    if (dw || db) {
+        float* fin = workspace + (size_t)hv_layernorm_bwd_ctas() * 128;
+        colsum_final_kernel<<<1, 128, 0, st>>>(workspace, ctas, 128, fin);
+        HV_LAUNCH_CHECK();
+        if (dw) HV_CUDA(cudaMemcpyAsync(dw, fin, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+        if (db) HV_CUDA(cudaMemcpyAsync(db, fin + 64, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    }
+    return HV_OK;
+}
 
 extern "C" int hv_transpose2d(const void* in, void* out, int64_t rows, int64_t cols, int64_t ld_in, int64_t ld_out, int dtype, void* stream) {
     HV_REQUIRE(rows >= 0 && cols >= 0 && ld_in >= cols && ld_out >= rows && (dtype == HV_F32 || dtype == HV_BF16), "hv_transpose2d: bad arguments");

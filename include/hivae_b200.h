@@ -150,6 +150,12 @@ int hv_layernorm_bwd_ctas(void);
 int hv_layernorm_bwd(const float* x, const void* dy, int dy_dtype, const float* w, float eps, int64_t rows, int D,
                      float* dx, int accumulate, float* workspace, float* dw, float* db, void* stream);
 
+/* backward of the per-head LayerNorm(64) applied to q / k (diffusers Attention(qk_norm="layer_norm"), eps 1e-6,
+ * modules.py:699-707): x, dy, dx are (tokens, heads*64) views, one dtype; dw / db (64 floats) are summed over tokens and
+ * heads.  workspace = (hv_layernorm_bwd_ctas() + 1) * 128 floats */
+int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int64_t lddy, const float* w, float eps, int64_t tokens,
+                      int heads, void* dx, int64_t lddx, int dtype, float* workspace, float* dw, float* db, void* stream);
+
 /* Diagnostics: with HV_ATTN_PROF=1 in the environment the tcgen05 attention kernel accumulates per-phase cycle
  * counters (148 CTAs x 2 key halves x 8 u64: wait S, max pass, max exchange, O epilogue, exp pass, publish P, full
  * tiles, tail tiles); this copies them to `host` and clears them.  Returns 0 when profiling is off. */
@@ -229,6 +235,16 @@ typedef struct HvSeqMap { int sdiv; int64_t sa, sb, sc; } HvSeqMap;
 int hv_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                  void* out, int64_t ldo, int dtype, int64_t seqs, int heads, int hd, int Lq, int Lkv,
                  const HvSeqMap* qmap, const HvSeqMap* kvmap, float scale, const float* mask, void* stream);
+
+/* Attention backward (first, SIMT fp32-math version): gradients of out = softmax(q k^T * scale) v for head_dim 64, no
+ * mask — autograd of F.scaled_dot_product_attention at model/modules.py:699-707, 1043-1051.  Same matrix / sequence-map
+ * conventions as hv_attention; `stats` = seqs * heads * Lq * 2 floats of workspace (lse, delta per query row). */
+int hv_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                     const void* out, int64_t ldo, const void* dout, int64_t lddo,
+                     void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, int dtype,
+                     int64_t seqs, int heads, int hd, int Lq, int Lkv, const HvSeqMap* qmap, const HvSeqMap* kvmap,
+                     float scale, float* stats, void* stream);
+
 
 /* ------------------------------------------------------------------ train-step tail (train_amd.py:489-496)
  * Flat fp32 arenas (parameters, gradients, AdamW moments), no host synchronisation.

@@ -771,3 +771,48 @@ def test_gelu_and_layernorm_backward_vs_autograd(dev, dtype):
         base = torch.randn(rows, D, generator=g)
         acc, _, _ = B.layernorm_backward(x.to(dev), d.to(dev), w.to(dev), 1e-5, dx=base.clone().to(dev), accumulate=True)
         assert rel(acc, base + xr.grad.float()) <= 1e-5
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-4), (torch.bfloat16, TOL_BF16)])
+@pytest.mark.parametrize("B,H,Lq,Lkv", [(3, 2, 274, 274), (2, 4, 100, 49), (5, 2, 16, 16), (2, 8, 264, 264)])
+def test_attention_backward_vs_autograd(dev, dtype, tol, B, H, Lq, Lkv):
+    """dq, dk, dv of the dense attention against torch autograd of the reference formula (fp64 on the same rounded inputs)"""
+    from hivae_b200 import backward as Bk, engine, ops
+    g = _gen(71)
+    D = H * 64
+    q = (torch.randn(B * Lq, D, generator=g) * 0.8).to(dtype)
+    k = (torch.randn(B * Lkv, D, generator=g) * 0.8).to(dtype)
+    v = torch.randn(B * Lkv, D, generator=g).to(dtype)
+    do = torch.randn(B * Lq, D, generator=g).to(dtype)
+    with torch.enable_grad():
+        qr, kr, vr = (t.double().requires_grad_() for t in (q, k, v))
+        hq = qr.view(B, Lq, H, 64).transpose(1, 2)
+        hk, hv_ = kr.view(B, Lkv, H, 64).transpose(1, 2), vr.view(B, Lkv, H, 64).transpose(1, 2)
+        o = (torch.softmax(hq @ hk.transpose(-1, -2) * 0.125, -1) @ hv_).transpose(1, 2).reshape(B * Lq, D)
+        (o * do.double()).sum().backward()
+    qm, km = ops.seq_map(1, Lq, 0, 1), ops.seq_map(1, Lkv, 0, 1)
+    out = o.detach().to(dtype).to(dev)   # the forward output the backward receives
+    dq, dk, dv = Bk.attention_backward(q.to(dev), k.to(dev), v.to(dev), out, do.to(dev), B, H, Lq, Lkv, qm, km, 0.125)
+    assert rel(dq, qr.grad.float()) <= tol and rel(dk, kr.grad.float()) <= tol and rel(dv, vr.grad.float()) <= tol
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, TOL_BF16)])
+def test_headnorm64_backward_vs_autograd(dev, dtype, tol):
+    """QK-norm backward: per-head LayerNorm(64, eps 1e-6) with one affine shared by all heads, on a column slice of a wider
+    matrix (q inside qkv), against torch autograd in fp64"""
+    from hivae_b200 import backward as Bk
+    g = _gen(81)
+    T_, H = 517, 4
+    qkv = (torch.randn(T_, 3 * H * 64, generator=g) * 1.3 + 0.2).to(dtype)
+    dy = torch.randn(T_, H * 64, generator=g).to(dtype)
+    w, b = torch.randn(64, generator=g) * 0.3 + 1.0, torch.randn(64, generator=g) * 0.1
+    with torch.enable_grad():
+        xr = qkv[:, H * 64:2 * H * 64].double().requires_grad_()
+        wr, br = w.double().requires_grad_(), b.double().requires_grad_()
+        y = torch.nn.functional.layer_norm(xr.view(T_, H, 64), (64,), wr, br, 1e-6).reshape(T_, H * 64)
+        (y * dy.double()).sum().backward()
+    dx, dw, db = Bk.headnorm64_backward(qkv.to(dev)[:, H * 64:2 * H * 64], dy.to(dev), w.to(dev), H)
+    assert rel(dx, xr.grad.float()) <= tol
+    assert rel(dw, wr.grad.float()) <= (1e-5 if dtype == torch.float32 else 1e-2) and rel(db, br.grad.float()) <= 1e-5
