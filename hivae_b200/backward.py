@@ -1,7 +1,8 @@
 """Building blocks of the backward pass of the blocks (`accelerator.backward(loss)`, train_amd.py:489)
 on the sm_100a kernels of csrc/backward.cu and the tcgen05 GEMM: gradients of nn.Linear, nn.LayerNorm and the
-tanh-GELU of FeedForward.  These are the operator-level pieces; the autograd wiring of whole blocks (attention
-backward, adaLN / gated-residual backward, torch.autograd.Function wrappers) is the next round's work.
+tanh-GELU of FeedForward, the dense attention and the QK-norm, and on top of them the whole-block backward of
+BasicTransformerBlock (the motion encoders' block) behind a torch.autograd.Function.  The adaLN /
+gated-residual blocks of the denoiser are the next step.
 
 No CPU fallback: every function raises without the CUDA library."""
 import ctypes as C
@@ -109,3 +110,125 @@ def headnorm64_backward(x, dy, weight, heads, eps=1e-6):
     _lib.check(lib.hv_headnorm64_bwd(_p(x), x.stride(0), _p(dy), dy.stride(0), _p(weight), float(eps), x.shape[0], heads,
                                      _p(dx), dx.stride(0), _dt(x), _p(ws), _p(dw), _p(db), _stream()))
     return dx, dw, db
+
+
+# ------------------------------------------------------------------------------------------------
+# Whole-block backward: BasicTransformerBlock (modules.py:721-743, the object motion encoder's block, a10 / a14) and
+# BasicCrossTransformerBlock (modules.py:817-840, the camera motion encoder's block, a15).
+# bf16 compute mode = the reference's `--mp bf16` autocast semantics (train_amd.py:160-165): bf16 GEMM / attention
+# operands, fp32 accumulation, fp32 residual stream, fp32 LayerNorm statistics, fp32 parameter gradients.
+
+def block_forward_train(ctx, bp, x, enc=None):
+    """x (B, L, D) [, enc (B, Lk, cross_dim) for the cross block] -> (out (B, L, D) fp32, saved activations).
+    Same kernels as engine.run_block; the q/k/v and the first feed-forward GEMM run a second time with the plain store
+    epilogue because the backward needs the pre-norm q / k and the pre-GELU activations (first version: a dual-output
+    epilogue removes the extra GEMMs)."""
+    from . import engine
+    assert bp.kind in ("basic", "cross") and (enc is not None) == (bp.kind == "cross")
+    assert ctx.dtype == torch.bfloat16, "the block backward is built for the bf16 compute mode"
+    B, L, D = x.shape
+    M, bf, dev = B * L, torch.bfloat16, x.device
+    new = lambda *shape: torch.empty(*shape, dtype=bf, device=dev)
+    x0 = x.detach().float().contiguous()
+    res = x0.clone()
+    rows = ops.Rows(res, 0, L)
+    scale = 1.0 / (D // bp.heads) ** 0.5
+    xn1 = ops.ln_modulate(rows, bp.n1w, bp.n1b, bp.eps, new(M, D))
+    s = dict(x0=x0, xn1=xn1, scale=scale)
+    if bp.kind == "cross":
+        Lk = enc.shape[1]
+        geom = engine.AttnGeom(B, L, Lk, ops.seq_map(1, L, 0, 1), ops.seq_map(1, Lk, 0, 1))
+        enc32 = enc.detach().reshape(B * Lk, -1).float().contiguous()
+        enc16 = ops.convert(enc32, new(*enc32.shape))
+        q_pre, q, kv_pre, kv = new(M, D), new(M, D), new(B * Lk, 2 * D), new(B * Lk, 2 * D)
+        ops.linear(xn1, bp.wq, ops.epi_store(q_pre, bp.bq))
+        ops.linear(xn1, bp.wq, ops.epi_qknorm(q, bp.bq, bp.qn_w, bp.qn_b, None, None, D, 0))
+        ops.linear(enc16, bp.wkv, ops.epi_store(kv_pre, bp.bkv))
+        ops.linear(enc16, bp.wkv, ops.epi_qknorm(kv, bp.bkv, None, None, bp.kn_w, bp.kn_b, 0, D))
+        s.update(enc16=enc16, q=q, k=kv[:, :D], v=kv[:, D:], q_pre=q_pre, k_pre=kv_pre[:, :D])
+    else:
+        geom = engine.dense_geom(B, L)
+        qkv_pre, qkv = new(M, 3 * D), new(M, 3 * D)
+        ops.linear(xn1, bp.wqkv, ops.epi_store(qkv_pre, bp.bqkv))
+        ops.linear(xn1, bp.wqkv, ops.epi_qknorm(qkv, bp.bqkv, bp.qn_w, bp.qn_b, bp.kn_w, bp.kn_b, D, D))
+        s.update(q=qkv[:, :D], k=qkv[:, D:2 * D], v=qkv[:, 2 * D:], q_pre=qkv_pre[:, :D], k_pre=qkv_pre[:, D:2 * D])
+    att = new(M, D)
+    ops.attention(s["q"], s["k"], s["v"], att, geom.seqs, bp.heads, D // bp.heads, geom.Lq, geom.Lkv, geom.qmap, geom.kvmap, scale)
+    ops.linear(att, bp.wo, ops.epi_residual(rows, bp.bo))
+    x1 = res.clone()
+    xn2 = ops.ln_modulate(rows, bp.n2w, bp.n2b, bp.eps, new(M, D))
+    F = bp.w1.shape[0]
+    hpre, h = new(M, F), new(M, F)
+    ops.linear(xn2, bp.w1, ops.epi_store(hpre, bp.b1))
+    ops.linear(xn2, bp.w1, ops.epi_store(h, bp.b1, gelu=True))
+    ops.linear(h, bp.w2, ops.epi_residual(rows, bp.b2))
+    s.update(att=att, x1=x1, xn2=xn2, hpre=hpre, h=h, geom=geom)
+    return res, s
+
+
+def block_backward(bp, saved, dy):
+    """dy (B, L, D) = d loss / d out  ->  (dx (B, L, D) fp32, d enc (B*Lk, cross_dim) fp32 or None,
+    {reference parameter name: fp32 gradient}).
+    Chain: W2 -> GELU -> W1 -> LayerNorm2 (+ residual) -> Wo -> attention -> QK-norm -> Wq/Wk/Wv -> LayerNorm1 (+ residual)."""
+    s = saved
+    B, L, D = dy.shape
+    M, bf, dev = B * L, torch.bfloat16, dy.device
+    g = {}
+    d2 = dy.detach().reshape(M, D).float().contiguous()
+    dx = d2.clone()                                                 # running residual-stream gradient
+    d16 = ops.convert(d2, torch.empty(M, D, dtype=bf, device=dev))
+    dh, g["ff.net.2.weight"], g["ff.net.2.bias"] = linear_backward(d16, s["h"], bp.w2)
+    dhpre = gelu_tanh_backward(s["hpre"], dh)
+    dxn2, g["ff.net.0.proj.weight"], g["ff.net.0.proj.bias"] = linear_backward(dhpre, s["xn2"], bp.w1)
+    _, g["norm2.weight"], g["norm2.bias"] = layernorm_backward(s["x1"].view(M, D), dxn2, bp.n2w, bp.eps, dx=dx, accumulate=True)
+    ops.convert(dx, d16)
+    datt, g["attn1.to_out.0.weight"], g["attn1.to_out.0.bias"] = linear_backward(d16, s["att"], bp.wo)
+    geom = s["geom"]
+    dq, dk, dv = attention_backward(s["q"], s["k"], s["v"], s["att"], datt, geom.seqs, bp.heads, geom.Lq, geom.Lkv,
+                                    geom.qmap, geom.kvmap, s["scale"])
+    dqp, g["attn1.norm_q.weight"], g["attn1.norm_q.bias"] = headnorm64_backward(s["q_pre"], dq, bp.qn_w, bp.heads)
+    dkp, g["attn1.norm_k.weight"], g["attn1.norm_k.bias"] = headnorm64_backward(s["k_pre"], dk, bp.kn_w, bp.heads)
+    denc = None
+    if bp.kind == "cross":
+        dxn1, g["attn1.to_q.weight"], g["attn1.to_q.bias"] = linear_backward(dqp, s["xn1"], bp.wq)
+        denc, dwkv, dbkv = linear_backward(torch.cat([dkp, dv], dim=1), s["enc16"], bp.wkv, dx_dtype=torch.float32)
+        for i, n in enumerate(("to_k", "to_v")):
+            g["attn1.%s.weight" % n], g["attn1.%s.bias" % n] = dwkv[i * D:(i + 1) * D], dbkv[i * D:(i + 1) * D]
+    else:
+        dxn1, dwqkv, dbqkv = linear_backward(torch.cat([dqp, dkp, dv], dim=1), s["xn1"], bp.wqkv)
+        for i, n in enumerate(("to_q", "to_k", "to_v")):
+            g["attn1.%s.weight" % n], g["attn1.%s.bias" % n] = dwqkv[i * D:(i + 1) * D], dbqkv[i * D:(i + 1) * D]
+    _, g["norm1.weight"], g["norm1.bias"] = layernorm_backward(s["x0"].view(M, D), dxn1, bp.n1w, bp.eps, dx=dx, accumulate=True)
+    return dx.view(B, L, D), denc, g
+
+
+class BlockFn(torch.autograd.Function):
+    """autograd wrapper: forward(blk, x, enc | None, *blk.parameters()) -> out; backward returns dx, d enc and
+    every parameter gradient from the sm_100a kernels.  `blk` is a hivae_b200.modules.BasicTransformerBlock or
+    BasicCrossTransformerBlock."""
+
+    @staticmethod
+    def forward(fctx, blk, x, enc, *params):
+        ctx, bp, _ = blk._prepared(x)
+        out, saved = block_forward_train(ctx, bp, x, enc)
+        fctx.bp, fctx.saved, fctx.names = bp, saved, [n for n, _ in blk.named_parameters()]
+        fctx.x_dtype, fctx.enc_meta = x.dtype, (None if enc is None else (enc.shape, enc.dtype))
+        return out.to(x.dtype)
+
+    @staticmethod
+    def backward(fctx, dy):
+        dx, denc, g = block_backward(fctx.bp, fctx.saved, dy)
+        fctx.saved = None
+        if denc is not None:
+            denc = denc.view(fctx.enc_meta[0]).to(fctx.enc_meta[1])
+        return (None, dx.to(fctx.x_dtype), denc) + tuple(g[n] for n in fctx.names)
+
+
+def basic_block_apply(blk, x):
+    """differentiable BasicTransformerBlock.forward: gradients flow to x and to blk's parameters"""
+    return BlockFn.apply(blk, x, None, *blk.parameters())
+
+
+def cross_block_apply(blk, x, encoder_hidden_state):
+    """differentiable BasicCrossTransformerBlock.forward: gradients flow to x, encoder_hidden_state and the parameters"""
+    return BlockFn.apply(blk, x, encoder_hidden_state, *blk.parameters())

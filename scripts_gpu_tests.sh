@@ -14,7 +14,7 @@ T=120 run blocks "blocks or adaln"
 T=180 run small "small_model"
 T=180 run variant "object_only or temporal_motion_encoder or imgspatial or sample_cross or amdmodel"
 T=120 run optim "adamw or clip"
-T=180 run backward "transpose or linear_backward or gelu_and_layernorm or attention_backward or headnorm64"
+T=180 run backward "transpose or linear_backward or gelu_and_layernorm or attention_backward or headnorm64 or block_backward"
 T=300 run default "default_model or natively"
 if [ "$1" == "bench" ]; then
   timeout -k 5 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit=$?" | tee -a gpurun_out/summary.txt; tail -n 4 gpurun_out/smoke.log

@@ -816,3 +816,74 @@ def test_headnorm64_backward_vs_autograd(dev, dtype, tol):
     dx, dw, db = Bk.headnorm64_backward(qkv.to(dev)[:, H * 64:2 * H * 64], dy.to(dev), w.to(dev), H)
     assert rel(dx, xr.grad.float()) <= tol
     assert rel(dw, wr.grad.float()) <= (1e-5 if dtype == torch.float32 else 1e-2) and rel(db, br.grad.float()) <= 1e-5
+
+
+def _ref_block(x, P, heads, enc=None):
+    """modules.py:721-743 (basic) / 817-840 (cross: K/V from the un-normalised encoder_hidden_state) with the diffusers
+    Attention / FeedForward of modules.py:699-719 written out (fp64 autograd reference)"""
+    Fn = torch.nn.functional
+    B, L, D = x.shape
+    split = lambda t: t.view(B, -1, heads, 64).transpose(1, 2)
+    xn = Fn.layer_norm(x, (D,), P["norm1.weight"], P["norm1.bias"], 1e-5)
+    src = xn if enc is None else enc
+    q = Fn.layer_norm(split(Fn.linear(xn, P["attn1.to_q.weight"], P["attn1.to_q.bias"])), (64,), P["attn1.norm_q.weight"], P["attn1.norm_q.bias"], 1e-6)
+    k = Fn.layer_norm(split(Fn.linear(src, P["attn1.to_k.weight"], P["attn1.to_k.bias"])), (64,), P["attn1.norm_k.weight"], P["attn1.norm_k.bias"], 1e-6)
+    v = split(Fn.linear(src, P["attn1.to_v.weight"], P["attn1.to_v.bias"]))
+    o = (torch.softmax(q @ k.transpose(-1, -2) * 0.125, -1) @ v).transpose(1, 2).reshape(B, L, D)
+    x = x + Fn.linear(o, P["attn1.to_out.0.weight"], P["attn1.to_out.0.bias"])
+    xn = Fn.layer_norm(x, (D,), P["norm2.weight"], P["norm2.bias"], 1e-5)
+    return x + Fn.linear(Fn.gelu(Fn.linear(xn, P["ff.net.0.proj.weight"], P["ff.net.0.proj.bias"]), approximate="tanh"),
+                         P["ff.net.2.weight"], P["ff.net.2.bias"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,L,Lk,D,cross,heads", [(4, 264, 0, 512, 0, 8), (3, 40, 0, 128, 0, 2), (6, 16, 16, 512, 512, 8), (3, 40, 24, 128, 64, 2)])
+def test_block_backward_vs_autograd(dev, B, L, Lk, D, cross, heads):
+    """whole-block backward of BasicTransformerBlock (object motion encoder) and BasicCrossTransformerBlock (camera motion
+    encoder; Lk > 0) through the autograd.Function wrapper: output, dx, d encoder_hidden_state and every parameter
+    gradient against torch autograd of the reference formula in fp64 on the same bf16-rounded GEMM weights;
+    bf16 tolerance 2e-2 (max-abs relative)"""
+    from hivae_b200 import backward as Bk
+    from hivae_b200.modules import BasicTransformerBlock, BasicCrossTransformerBlock
+    g = _gen(91)
+    blk = BasicCrossTransformerBlock(D, cross, heads, 64, attention_bias=True) if Lk else BasicTransformerBlock(D, heads, 64, attention_bias=True)
+    with torch.no_grad():
+        for n, p in blk.named_parameters():
+            if p.dim() == 2:
+                p.copy_((torch.randn(p.shape, generator=g) / p.shape[1] ** 0.5).to(torch.bfloat16).float())
+            elif "norm" in n and n.endswith("weight"):
+                p.copy_(1.0 + 0.2 * torch.randn(p.shape, generator=g))
+            else:
+                p.copy_(0.1 * torch.randn(p.shape, generator=g))
+    x = torch.randn(B, L, D, generator=g)
+    dy = torch.randn(B, L, D, generator=g)
+    enc = torch.randn(B, Lk, cross, generator=g) if Lk else None
+    with torch.enable_grad():
+        P = {n: p.detach().double().requires_grad_() for n, p in blk.named_parameters()}
+        xr = x.double().requires_grad_()
+        er = enc.double().requires_grad_() if Lk else None
+        yr = _ref_block(xr, P, heads, er)
+        (yr * dy.double()).sum().backward()
+    blk.to(dev)
+    blk.hv_compute_dtype = torch.bfloat16
+    with torch.enable_grad():
+        xg = x.to(dev).requires_grad_()
+        eg = enc.to(dev).requires_grad_() if Lk else None
+        y = Bk.cross_block_apply(blk, xg, eg) if Lk else Bk.basic_block_apply(blk, xg)
+        (y * dy.to(dev)).sum().backward()
+    assert rel(y, yr.detach().float()) <= TOL_BF16
+    y_inf = blk(x.to(dev), enc.to(dev)) if Lk else blk(x.to(dev))
+    assert rel(y_inf, y) <= 1e-6          # the training forward is the inference forward
+    errs = {"dx": rel(xg.grad, xr.grad.float())}
+    if Lk:
+        errs["denc"] = rel(eg.grad, er.grad.float())
+    for n, p in blk.named_parameters():
+        assert p.grad is not None and p.grad.shape == p.shape, n
+        errs[n] = rel(p.grad, P[n].grad.float())
+    # softmax is invariant to a per-query shift of the scores, so sum_j dk_j = 0 in every (sequence, head): d norm_k.bias is
+    # identically zero and d to_k.bias is a cancellation residue; both are judged on the scale of their q-side counterparts
+    for kn, qn in (("attn1.norm_k.bias", "attn1.norm_q.bias"), ("attn1.to_k.bias", "attn1.to_q.bias")):
+        pk = dict(blk.named_parameters())[kn]
+        errs[kn] = float((pk.grad.cpu() - P[kn].grad.float()).abs().max() / P[qn].grad.float().abs().max())
+    print({k: "%.1e" % v for k, v in errs.items()})
+    assert max(errs.values()) <= TOL_BF16, errs
