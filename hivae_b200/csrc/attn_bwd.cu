@@ -1,4 +1,4 @@
-// Attention backward, first (SIMT fp32-math) version: gradients of softmax(Q K^T * scale) V per (sequence, head)
+// Attention backward: gradients of softmax(Q K^T * scale) V per (sequence, head)
 // for head_dim 64, no mask — the autograd of F.scaled_dot_product_attention inside diffusers AttnProcessor2_0 at the
 // call sites model/modules.py:699-707, 1043-1051.  Two kernels, each recomputing the
 // probabilities it needs (flash-attention style, nothing of size Lq x Lkv ever goes to HBM):
@@ -9,8 +9,8 @@
 //               Per key: p, ds as above (from lse / delta), dV = p^T dO, dK = ds^T Q.
 // Lanes own keys (or queries) for the 64-long dot products — rows are padded to 65 floats, so lanes reading different
 // rows at the same column hit different banks — and then own columns for the rank-1 accumulations.
-// This is the correctness baseline of the backward path (about 450 FMA per (query, key) pair on the FMA pipes); the
-// tcgen05 version is next round's work.
+// The SIMT fp32-math kernels below serve fp32 tensors (1e-4-level parity) and odd alignments (about 450 FMA per
+// (query, key) pair on the FMA pipes); bf16 tensors take the warp-level tensor-core kernels further down.
 #include "attn.cuh"
 
 namespace {
@@ -172,6 +172,277 @@ __global__ void __launch_bounds__(256) attn_bwd_dkv_kernel(const BwdArgs a) {
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// bf16 tensor-core version (warp-level mma.sync.m16n8k16, fp32 accumulation), same two-kernel structure and the same
+// (lse, delta) hand-over.  A CTA is four warps; each warp owns 16 query rows (dq kernel) or 16 keys (dkv kernel), holds
+// their Q / dO (K / V) rows as A fragments in registers and walks the other dimension in chunks of 32, whose rows sit
+// in shared memory as bf16 with a pitch of 72 elements (fragment loads and ldmatrix rows hit 32 distinct banks):
+//   dq : S = Q K^T and dP = dO V^T (B fragments = plain 32-bit loads of K / V rows), P = exp(S scale - lse),
+//        dS = P (dP - delta) scale re-packed from the accumulator layout into A fragments, dQ += dS K with the B
+//        fragments of K taken through ldmatrix.trans.  lse comes from a first pass of S with an online max / sum.
+//   dkv: S^T = K Q^T, dP^T = V dO^T, P^T / dS^T as above (lse / delta indexed by column), dV += P^T dO, dK += dS^T Q.
+// Padded rows are zero in shared memory; padded keys are masked, padded queries carry lse = +inf (p = 0).
+constexpr int MP = 72;
+
+__device__ __forceinline__ void mma16816(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3, const void* p) {
+    const uint32_t addr = (uint32_t)__cvta_generic_to_shared(p);
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];\n"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
+    return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u));
+}
+
+// rows [0, L) x 64 columns of one head -> shared memory [Lp][MP] bf16, rows [L, Lp) zero
+__device__ __forceinline__ void stage_head(__nv_bfloat16* dst, const __nv_bfloat16* src, long long ld, const HvSeqMap& m,
+                                           long long seq, int L, int Lp, int col0, int vec) {
+    if (vec) {
+        for (int i = threadIdx.x; i < Lp * 8; i += blockDim.x) {
+            const int r = i >> 3, c = (i & 7) * 8;
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if (r < L) v = *reinterpret_cast<const uint4*>(src + seq_row(m, seq, r) * ld + col0 + c);
+            *reinterpret_cast<uint4*>(dst + r * MP + c) = v;
+        }
+    } else {
+        for (int i = threadIdx.x; i < Lp * 32; i += blockDim.x) {
+            const int r = i >> 5, c = (i & 31) * 2;
+            uint32_t v = 0u;
+            if (r < L) v = *reinterpret_cast<const uint32_t*>(src + seq_row(m, seq, r) * ld + col0 + c);
+            *reinterpret_cast<uint32_t*>(dst + r * MP + c) = v;
+        }
+    }
+}
+
+// A fragments (four 16-wide k tiles) of rows r0 .. r0+15 of one head, straight from global memory; rows >= L are zero
+__device__ __forceinline__ void load_a_frags(uint32_t (&f)[4][4], const __nv_bfloat16* src, long long ld, const HvSeqMap& m,
+                                             long long seq, int r0, int L, int col0, int g, int tig) {
+    const __nv_bfloat16* p0 = (r0 + g < L) ? src + seq_row(m, seq, r0 + g) * ld + col0 + 2 * tig : nullptr;
+    const __nv_bfloat16* p1 = (r0 + g + 8 < L) ? src + seq_row(m, seq, r0 + g + 8) * ld + col0 + 2 * tig : nullptr;
+#pragma unroll
+    for (int kt = 0; kt < 4; ++kt) {
+        f[kt][0] = p0 ? *reinterpret_cast<const uint32_t*>(p0 + kt * 16) : 0u;
+        f[kt][1] = p1 ? *reinterpret_cast<const uint32_t*>(p1 + kt * 16) : 0u;
+        f[kt][2] = p0 ? *reinterpret_cast<const uint32_t*>(p0 + kt * 16 + 8) : 0u;
+        f[kt][3] = p1 ? *reinterpret_cast<const uint32_t*>(p1 + kt * 16 + 8) : 0u;
+    }
+}
+
+// acc[nt] (16 x 8, nt < 4) += A(16 x 64) . rows (base + nt*8 + g) of a [.][MP] shared array, i.e. A X^T for 32 rows of X
+__device__ __forceinline__ void mma_rows32(float (&acc)[4][4], const uint32_t (&af)[4][4], const __nv_bfloat16* X, int base, int g, int tig) {
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+        const __nv_bfloat16* xr = X + (base + nt * 8 + g) * MP + 2 * tig;
+#pragma unroll
+        for (int kt = 0; kt < 4; ++kt)
+            mma16816(acc[nt], af[kt], *reinterpret_cast<const uint32_t*>(xr + kt * 16), *reinterpret_cast<const uint32_t*>(xr + kt * 16 + 8));
+    }
+}
+
+// acc (16 x 64 as eight 8-wide column tiles) += A(16 x 32, two k tiles of fragments) . X[base .. base+32)[0..64)
+__device__ __forceinline__ void mma_cols64(float (&acc)[8][4], const uint32_t (&af)[2][4], const __nv_bfloat16* X, int base, int lane) {
+#pragma unroll
+    for (int kt = 0; kt < 2; ++kt) {
+        const __nv_bfloat16* xr = X + (base + kt * 16 + (lane & 15)) * MP + (lane >> 4) * 8;
+#pragma unroll
+        for (int nc = 0; nc < 8; nc += 2) {
+            uint32_t b0, b1, b2, b3;
+            ldsm_x4_trans(b0, b1, b2, b3, xr + nc * 8);
+            mma16816(acc[nc], af[kt], b0, b1);
+            mma16816(acc[nc + 1], af[kt], b2, b3);
+        }
+    }
+}
+
+// accumulator tiles of a 16 x 32 block -> A fragments of its two 16-wide k tiles
+__device__ __forceinline__ void acc_to_a(uint32_t (&af)[2][4], const float (&x)[4][4]) {
+#pragma unroll
+    for (int kt = 0; kt < 2; ++kt) {
+        af[kt][0] = pack_bf16(x[2 * kt][0], x[2 * kt][1]);
+        af[kt][1] = pack_bf16(x[2 * kt][2], x[2 * kt][3]);
+        af[kt][2] = pack_bf16(x[2 * kt + 1][0], x[2 * kt + 1][1]);
+        af[kt][3] = pack_bf16(x[2 * kt + 1][2], x[2 * kt + 1][3]);
+    }
+}
+
+__device__ __forceinline__ void store_rows(__nv_bfloat16* dst, long long ld, const HvSeqMap& m, long long seq, int r0, int L,
+                                           int col0, int g, int tig, const float (&acc)[8][4]) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int r = r0 + g + 8 * h;
+        if (r >= L) continue;
+        __nv_bfloat16* p = dst + seq_row(m, seq, r) * ld + col0 + 2 * tig;
+#pragma unroll
+        for (int nc = 0; nc < 8; ++nc) *reinterpret_cast<uint32_t*>(p + nc * 8) = pack_bf16(acc[nc][2 * h], acc[nc][2 * h + 1]);
+    }
+}
+
+__global__ void __launch_bounds__(128, 2) attn_bwd_dq_mma_kernel(const BwdArgs a, int Lp, int vec) {
+    extern __shared__ __align__(16) unsigned char smraw[];
+    __nv_bfloat16* Ks = reinterpret_cast<__nv_bfloat16*>(smraw);
+    __nv_bfloat16* Vs = Ks + Lp * MP;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tig = lane & 3;
+    const long long seq = blockIdx.z;
+    const int head = blockIdx.y, col0 = head * HDB;
+    stage_head(Ks, (const __nv_bfloat16*)a.k, a.ldk, a.kvmap, seq, a.Lkv, Lp, col0, vec);
+    stage_head(Vs, (const __nv_bfloat16*)a.v, a.ldv, a.kvmap, seq, a.Lkv, Lp, col0, vec);
+    __syncthreads();
+    const int r0 = blockIdx.x * 64 + warp * 16;
+    if (r0 >= a.Lq) return;  // warp-uniform, no block-wide barrier below
+    uint32_t qa[4][4], da[4][4];
+    load_a_frags(qa, (const __nv_bfloat16*)a.q, a.ldq, a.qmap, seq, r0, a.Lq, col0, g, tig);
+    load_a_frags(da, (const __nv_bfloat16*)a.dout, a.lddo, a.qmap, seq, r0, a.Lq, col0, g, tig);
+    float del[2] = {0.f, 0.f};
+    {
+        uint32_t oa[4][4];
+        load_a_frags(oa, (const __nv_bfloat16*)a.o, a.ldo, a.qmap, seq, r0, a.Lq, col0, g, tig);
+#pragma unroll
+        for (int kt = 0; kt < 4; ++kt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float2 d = unpack_bf16(da[kt][e]), o = unpack_bf16(oa[kt][e]);
+                del[e & 1] += d.x * o.x + d.y * o.y;
+            }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            del[h] += __shfl_xor_sync(0xffffffffu, del[h], 1);
+            del[h] += __shfl_xor_sync(0xffffffffu, del[h], 2);
+        }
+    }
+    // pass 1: log-sum-exp of the scaled scores (online max / sum over this thread's columns, then across the quad)
+    float mx[2] = {-INFINITY, -INFINITY}, sm[2] = {0.f, 0.f};
+    for (int jc = 0; jc < Lp; jc += 32) {
+        float s[4][4] = {};
+        mma_rows32(s, qa, Ks, jc, g, tig);
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (jc + nt * 8 + 2 * tig + (e & 1) >= a.Lkv) continue;
+                const float v = s[nt][e] * a.scale;
+                const int h = e >> 1;
+                if (v > mx[h]) { sm[h] = sm[h] * __expf(mx[h] - v) + 1.f; mx[h] = v; }
+                else sm[h] += __expf(v - mx[h]);
+            }
+    }
+    float lse[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        float M = fmaxf(mx[h], __shfl_xor_sync(0xffffffffu, mx[h], 1));
+        M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, 2));
+        float L = sm[h] * __expf(mx[h] - M);
+        L += __shfl_xor_sync(0xffffffffu, L, 1);
+        L += __shfl_xor_sync(0xffffffffu, L, 2);
+        lse[h] = M + __logf(L);
+        const int i = r0 + g + 8 * h;
+        if (tig == 0 && i < a.Lq) {
+            float* st = a.stats + ((seq * a.heads + head) * a.Lq + i) * 2;
+            st[0] = lse[h]; st[1] = del[h];
+        }
+    }
+    // pass 2
+    float dq[8][4] = {};
+    for (int jc = 0; jc < Lp; jc += 32) {
+        float s[4][4] = {}, dp[4][4] = {};
+        mma_rows32(s, qa, Ks, jc, g, tig);
+        mma_rows32(dp, da, Vs, jc, g, tig);
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int h = e >> 1;
+                const float p = (jc + nt * 8 + 2 * tig + (e & 1) < a.Lkv) ? __expf(s[nt][e] * a.scale - lse[h]) : 0.f;
+                s[nt][e] = p * (dp[nt][e] - del[h]) * a.scale;
+            }
+        uint32_t dsa[2][4];
+        acc_to_a(dsa, s);
+        mma_cols64(dq, dsa, Ks, jc, lane);
+    }
+    store_rows((__nv_bfloat16*)a.dq, a.lddq, a.qmap, seq, r0, a.Lq, col0, g, tig, dq);
+}
+
+__global__ void __launch_bounds__(128, 2) attn_bwd_dkv_mma_kernel(const BwdArgs a, int Lp, int vec) {
+    extern __shared__ __align__(16) unsigned char smraw[];
+    __nv_bfloat16* Qs = reinterpret_cast<__nv_bfloat16*>(smraw);
+    __nv_bfloat16* Ds = Qs + Lp * MP;
+    float* slse = reinterpret_cast<float*>(Ds + Lp * MP);
+    float* sdel = slse + Lp;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, tig = lane & 3;
+    const long long seq = blockIdx.z;
+    const int head = blockIdx.y, col0 = head * HDB;
+    stage_head(Qs, (const __nv_bfloat16*)a.q, a.ldq, a.qmap, seq, a.Lq, Lp, col0, vec);
+    stage_head(Ds, (const __nv_bfloat16*)a.dout, a.lddo, a.qmap, seq, a.Lq, Lp, col0, vec);
+    const float* st = a.stats + (seq * a.heads + head) * a.Lq * 2;
+    for (int i = threadIdx.x; i < Lp; i += blockDim.x) {
+        slse[i] = i < a.Lq ? st[2 * i] : INFINITY;
+        sdel[i] = i < a.Lq ? st[2 * i + 1] : 0.f;
+    }
+    __syncthreads();
+    const int j0 = blockIdx.x * 64 + warp * 16;
+    if (j0 >= a.Lkv) return;  // warp-uniform, no block-wide barrier below
+    uint32_t ka[4][4], va[4][4];
+    load_a_frags(ka, (const __nv_bfloat16*)a.k, a.ldk, a.kvmap, seq, j0, a.Lkv, col0, g, tig);
+    load_a_frags(va, (const __nv_bfloat16*)a.v, a.ldv, a.kvmap, seq, j0, a.Lkv, col0, g, tig);
+    float dk[8][4] = {}, dv[8][4] = {};
+    for (int ic = 0; ic < Lp; ic += 32) {
+        float s[4][4] = {}, dp[4][4] = {};
+        mma_rows32(s, ka, Qs, ic, g, tig);
+        mma_rows32(dp, va, Ds, ic, g, tig);
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) {
+            const int i = ic + nt * 8 + 2 * tig;
+            const float l0 = slse[i], l1 = slse[i + 1], d0 = sdel[i], d1 = sdel[i + 1];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float p = __expf(s[nt][e] * a.scale - ((e & 1) ? l1 : l0));
+                dp[nt][e] = p * (dp[nt][e] - ((e & 1) ? d1 : d0)) * a.scale;
+                s[nt][e] = p;
+            }
+        }
+        uint32_t pa[2][4], dsa[2][4];
+        acc_to_a(pa, s);
+        acc_to_a(dsa, dp);
+        mma_cols64(dv, pa, Ds, ic, lane);
+        mma_cols64(dk, dsa, Qs, ic, lane);
+    }
+    store_rows((__nv_bfloat16*)a.dv, a.lddv, a.kvmap, seq, j0, a.Lkv, col0, g, tig, dv);
+    store_rows((__nv_bfloat16*)a.dk, a.lddk, a.kvmap, seq, j0, a.Lkv, col0, g, tig, dk);
+}
+
+inline bool al(const void* p, long long ld, int bytes) {
+    return (reinterpret_cast<uintptr_t>(p) % bytes) == 0 && (ld * 2) % bytes == 0;
+}
+
+// returns HV_OK after launching, or 1 when the shapes / alignments need the SIMT kernels
+int launch_bwd_mma(const BwdArgs& a, int64_t seqs, cudaStream_t st) {
+    static const bool off = [] { const char* e = getenv("HV_ATTN_BWD_SIMT"); return e && *e == '1'; }();
+    if (off) return 1;
+    const bool ok4 = al(a.q, a.ldq, 4) && al(a.k, a.ldk, 4) && al(a.v, a.ldv, 4) && al(a.o, a.ldo, 4) && al(a.dout, a.lddo, 4) &&
+                     al(a.dq, a.lddq, 4) && al(a.dk, a.lddk, 4) && al(a.dv, a.lddv, 4);
+    const int Lpk = (a.Lkv + 31) / 32 * 32, Lpq = (a.Lq + 31) / 32 * 32;
+    const size_t sm1 = (size_t)2 * Lpk * MP * 2, sm2 = (size_t)2 * Lpq * MP * 2 + (size_t)2 * Lpq * 4;
+    if (!ok4 || sm1 > 227 * 1024 || sm2 > 227 * 1024) return 1;
+    const int vec1 = al(a.k, a.ldk, 16) && al(a.v, a.ldv, 16), vec2 = al(a.q, a.ldq, 16) && al(a.dout, a.lddo, 16);
+    HV_CUDA(cudaFuncSetAttribute(attn_bwd_dq_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm1));
+    HV_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+    dim3 g1((a.Lq + 63) / 64, a.heads, (unsigned)seqs);
+    attn_bwd_dq_mma_kernel<<<g1, 128, sm1, st>>>(a, Lpk, vec1);
+    HV_LAUNCH_CHECK();
+    dim3 g2((a.Lkv + 63) / 64, a.heads, (unsigned)seqs);
+    attn_bwd_dkv_mma_kernel<<<g2, 128, sm2, st>>>(a, Lpq, vec2);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
 template <typename T>
 int launch_bwd(const BwdArgs& a, int64_t seqs, cudaStream_t st) {
     const size_t sm1 = (size_t)(2 * a.Lkv * PITCH + 16 * HDB + 8 * a.Lkv) * sizeof(float);
@@ -203,5 +474,7 @@ extern "C" int hv_attention_bwd(const void* q, int64_t ldq, const void* k, int64
     HV_REQUIRE(dtype == HV_F32 || dtype == HV_BF16, "hv_attention_bwd: bad dtype");
     if (seqs == 0) return HV_OK;
     BwdArgs a{q, k, v, out, dout, dq, dk, dv, ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv, heads, Lq, Lkv, *qmap, *kvmap, scale, stats};
-    return dtype == HV_F32 ? launch_bwd<float>(a, seqs, hv_stream(stream)) : launch_bwd<__nv_bfloat16>(a, seqs, hv_stream(stream));
+    if (dtype == HV_F32) return launch_bwd<float>(a, seqs, hv_stream(stream));
+    const int rc = launch_bwd_mma(a, seqs, hv_stream(stream));  // bf16: tensor-core kernels unless shape / alignment forbid
+    return rc == 1 ? launch_bwd<__nv_bfloat16>(a, seqs, hv_stream(stream)) : rc;
 }
