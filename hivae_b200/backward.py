@@ -86,9 +86,9 @@ def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, sc
     _lib.require_device()
     for t in (q, k, v, out, dout):
         assert t.is_cuda and t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype
-    dq = torch.zeros(q.shape[0], heads * 64, dtype=q.dtype, device=q.device)
-    dk = torch.zeros(k.shape[0], heads * 64, dtype=q.dtype, device=q.device)
-    dv = torch.zeros(v.shape[0], heads * 64, dtype=q.dtype, device=q.device)
+    dq = torch.empty(q.shape[0], heads * 64, dtype=q.dtype, device=q.device)
+    dk = torch.empty(k.shape[0], heads * 64, dtype=q.dtype, device=q.device)
+    dv = torch.empty(v.shape[0], heads * 64, dtype=q.dtype, device=q.device)
     stats = torch.empty(seqs * heads * Lq * 2, dtype=torch.float32, device=q.device)
     _lib.check(_lib.load().hv_attention_bwd(
         _p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0), _p(dout), dout.stride(0),

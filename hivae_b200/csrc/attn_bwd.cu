@@ -203,15 +203,21 @@ __device__ __forceinline__ float2 unpack_bf16(uint32_t u) {
     return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u));
 }
 
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" :: "n"(N) : "memory"); }
+
 // rows [0, L) x 64 columns of one head -> shared memory [Lp][MP] bf16, rows [L, Lp) zero
 __device__ __forceinline__ void stage_head(__nv_bfloat16* dst, const __nv_bfloat16* src, long long ld, const HvSeqMap& m,
                                            long long seq, int L, int Lp, int col0, int vec) {
-    if (vec) {
+    if (vec) {  // 16-byte cp.async: every copy of the head is in flight at once (the caller commits / waits)
         for (int i = threadIdx.x; i < Lp * 8; i += blockDim.x) {
             const int r = i >> 3, c = (i & 7) * 8;
-            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-            if (r < L) v = *reinterpret_cast<const uint4*>(src + seq_row(m, seq, r) * ld + col0 + c);
-            *reinterpret_cast<uint4*>(dst + r * MP + c) = v;
+            if (r < L) {
+                const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst + r * MP + c);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" :: "r"(d), "l"(src + seq_row(m, seq, r) * ld + col0 + c) : "memory");
+            } else {
+                *reinterpret_cast<uint4*>(dst + r * MP + c) = make_uint4(0u, 0u, 0u, 0u);
+            }
         }
     } else {
         for (int i = threadIdx.x; i < Lp * 32; i += blockDim.x) {
@@ -237,14 +243,25 @@ __device__ __forceinline__ void load_a_frags(uint32_t (&f)[4][4], const __nv_bfl
     }
 }
 
-// acc[nt] (16 x 8, nt < 4) += A(16 x 64) . rows (base + nt*8 + g) of a [.][MP] shared array, i.e. A X^T for 32 rows of X
-__device__ __forceinline__ void mma_rows32(float (&acc)[4][4], const uint32_t (&af)[4][4], const __nv_bfloat16* X, int base, int g, int tig) {
+__device__ __forceinline__ void ldsm_x4(uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3, const void* p) {
+    const uint32_t addr = (uint32_t)__cvta_generic_to_shared(p);
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+
+// acc[nt] (16 x 8, nt < 4) += A(16 x 64) . rows (base + nt*8 + g) of a [.][MP] shared array, i.e. A X^T for 32 rows of X.
+// One ldmatrix.x4 fetches the B fragments of two k tiles: lane l addresses row (l & 7), columns 8 (l >> 3) of the 8 x 32 block.
+__device__ __forceinline__ void mma_rows32(float (&acc)[4][4], const uint32_t (&af)[4][4], const __nv_bfloat16* X, int base, int lane) {
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt) {
-        const __nv_bfloat16* xr = X + (base + nt * 8 + g) * MP + 2 * tig;
+        const __nv_bfloat16* xr = X + (base + nt * 8 + (lane & 7)) * MP + (lane >> 3) * 8;
 #pragma unroll
-        for (int kt = 0; kt < 4; ++kt)
-            mma16816(acc[nt], af[kt], *reinterpret_cast<const uint32_t*>(xr + kt * 16), *reinterpret_cast<const uint32_t*>(xr + kt * 16 + 8));
+        for (int kt = 0; kt < 4; kt += 2) {
+            uint32_t b0, b1, b2, b3;
+            ldsm_x4(b0, b1, b2, b3, xr + kt * 16);
+            mma16816(acc[nt], af[kt], b0, b1);
+            mma16816(acc[nt], af[kt + 1], b2, b3);
+        }
     }
 }
 
@@ -294,10 +311,10 @@ __global__ void __launch_bounds__(128, 2) attn_bwd_dq_mma_kernel(const BwdArgs a
     const long long seq = blockIdx.z;
     const int head = blockIdx.y, col0 = head * HDB;
     stage_head(Ks, (const __nv_bfloat16*)a.k, a.ldk, a.kvmap, seq, a.Lkv, Lp, col0, vec);
+    cp_async_commit();
     stage_head(Vs, (const __nv_bfloat16*)a.v, a.ldv, a.kvmap, seq, a.Lkv, Lp, col0, vec);
-    __syncthreads();
+    cp_async_commit();
     const int r0 = blockIdx.x * 64 + warp * 16;
-    if (r0 >= a.Lq) return;  // warp-uniform, no block-wide barrier below
     uint32_t qa[4][4], da[4][4];
     load_a_frags(qa, (const __nv_bfloat16*)a.q, a.ldq, a.qmap, seq, r0, a.Lq, col0, g, tig);
     load_a_frags(da, (const __nv_bfloat16*)a.dout, a.lddo, a.qmap, seq, r0, a.Lq, col0, g, tig);
@@ -318,11 +335,14 @@ __global__ void __launch_bounds__(128, 2) attn_bwd_dq_mma_kernel(const BwdArgs a
             del[h] += __shfl_xor_sync(0xffffffffu, del[h], 2);
         }
     }
+    cp_async_wait<1>();  // K has landed (V still in flight: pass 1 does not read it)
+    __syncthreads();
     // pass 1: log-sum-exp of the scaled scores (online max / sum over this thread's columns, then across the quad)
+    const bool active = r0 < a.Lq;  // warp-uniform; idle warps of the last tile only keep the barriers
     float mx[2] = {-INFINITY, -INFINITY}, sm[2] = {0.f, 0.f};
-    for (int jc = 0; jc < Lp; jc += 32) {
+    for (int jc = 0; active && jc < Lp; jc += 32) {
         float s[4][4] = {};
-        mma_rows32(s, qa, Ks, jc, g, tig);
+        mma_rows32(s, qa, Ks, jc, lane);
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
@@ -349,12 +369,15 @@ __global__ void __launch_bounds__(128, 2) attn_bwd_dq_mma_kernel(const BwdArgs a
             st[0] = lse[h]; st[1] = del[h];
         }
     }
+    cp_async_wait<0>();
+    __syncthreads();
+    if (!active) return;
     // pass 2
     float dq[8][4] = {};
     for (int jc = 0; jc < Lp; jc += 32) {
         float s[4][4] = {}, dp[4][4] = {};
-        mma_rows32(s, qa, Ks, jc, g, tig);
-        mma_rows32(dp, da, Vs, jc, g, tig);
+        mma_rows32(s, qa, Ks, jc, lane);
+        mma_rows32(dp, da, Vs, jc, lane);
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
@@ -386,17 +409,19 @@ __global__ void __launch_bounds__(128, 2) attn_bwd_dkv_mma_kernel(const BwdArgs 
         slse[i] = i < a.Lq ? st[2 * i] : INFINITY;
         sdel[i] = i < a.Lq ? st[2 * i + 1] : 0.f;
     }
-    __syncthreads();
+    cp_async_commit();
     const int j0 = blockIdx.x * 64 + warp * 16;
-    if (j0 >= a.Lkv) return;  // warp-uniform, no block-wide barrier below
     uint32_t ka[4][4], va[4][4];
     load_a_frags(ka, (const __nv_bfloat16*)a.k, a.ldk, a.kvmap, seq, j0, a.Lkv, col0, g, tig);
     load_a_frags(va, (const __nv_bfloat16*)a.v, a.ldv, a.kvmap, seq, j0, a.Lkv, col0, g, tig);
+    cp_async_wait<0>();
+    __syncthreads();
+    if (j0 >= a.Lkv) return;  // warp-uniform, no block-wide barrier below
     float dk[8][4] = {}, dv[8][4] = {};
     for (int ic = 0; ic < Lp; ic += 32) {
         float s[4][4] = {}, dp[4][4] = {};
-        mma_rows32(s, ka, Qs, ic, g, tig);
-        mma_rows32(dp, va, Ds, ic, g, tig);
+        mma_rows32(s, ka, Qs, ic, lane);
+        mma_rows32(dp, va, Ds, ic, lane);
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) {
             const int i = ic + nt * 8 + 2 * tig;

@@ -236,7 +236,7 @@ int hv_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const v
                  void* out, int64_t ldo, int dtype, int64_t seqs, int heads, int hd, int Lq, int Lkv,
                  const HvSeqMap* qmap, const HvSeqMap* kvmap, float scale, const float* mask, void* stream);
 
-/* Attention backward (first, SIMT fp32-math version): gradients of out = softmax(q k^T * scale) v for head_dim 64, no
+/* Attention backward (bf16: warp-level tensor-core kernels, fp32 accumulation; fp32: SIMT kernels): gradients of out = softmax(q k^T * scale) v for head_dim 64, no
  * mask — autograd of F.scaled_dot_product_attention at model/modules.py:699-707, 1043-1051.  Same matrix / sequence-map
  * conventions as hv_attention; `stats` = seqs * heads * Lq * 2 floats of workspace (lse, delta per query row). */
 int hv_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,

@@ -1,5 +1,5 @@
 """One or two launches of a chosen kernel at the DiT's shapes, for `ncu -k regex:<kernel> --set full` captures.
-usage: python tools/prof_targets.py attn|ln|small|gemm_out|gemm_ff1|gemm_qkv|dwt"""
+usage: python tools/prof_targets.py attn|ln|small|gemm_out|gemm_ff1|gemm_qkv|dwt|attn_bwd"""
 import sys, os, math
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -54,5 +54,14 @@ elif what == "dwt":
     for _ in range(reps):
         bands, ll = hv.dwt_pyramid(x, 3)
         hv.iwt_pyramid(bands, ll)
+elif what == "attn_bwd":
+    from hivae_b200 import backward as Bk
+    frames, L, D, H = 128, 264, 512, 8  # object motion encoder, 4 clips
+    M = frames * L
+    qkv = torch.randn(M, 3 * D, device=dev).bfloat16()
+    o, do = torch.randn(M, D, device=dev).bfloat16(), torch.randn(M, D, device=dev).bfloat16()
+    g = engine.dense_geom(frames, L)
+    for _ in range(reps):
+        Bk.attention_backward(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], o, do, g.seqs, H, L, L, g.qmap, g.kvmap, 0.125)
 torch.cuda.synchronize()
 print("done", what)
