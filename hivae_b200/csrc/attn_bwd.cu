@@ -252,16 +252,16 @@ __device__ __forceinline__ void ldsm_x4(uint32_t& r0, uint32_t& r1, uint32_t& r2
 // acc[nt] (16 x 8, nt < 4) += A(16 x 64) . rows (base + nt*8 + g) of a [.][MP] shared array, i.e. A X^T for 32 rows of X.
 // One ldmatrix.x4 fetches the B fragments of two k tiles: lane l addresses row (l & 7), columns 8 (l >> 3) of the 8 x 32 block.
 __device__ __forceinline__ void mma_rows32(float (&acc)[4][4], const uint32_t (&af)[4][4], const __nv_bfloat16* X, int base, int lane) {
+    const __nv_bfloat16* xr = X + (base + (lane & 7)) * MP + (lane >> 3) * 8;
 #pragma unroll
-    for (int nt = 0; nt < 4; ++nt) {
-        const __nv_bfloat16* xr = X + (base + nt * 8 + (lane & 7)) * MP + (lane >> 3) * 8;
+    for (int kt = 0; kt < 4; kt += 2) {
+        uint32_t b[4][4];
 #pragma unroll
-        for (int kt = 0; kt < 4; kt += 2) {
-            uint32_t b0, b1, b2, b3;
-            ldsm_x4(b0, b1, b2, b3, xr + kt * 16);
-            mma16816(acc[nt], af[kt], b0, b1);
-            mma16816(acc[nt], af[kt + 1], b2, b3);
-        }
+        for (int nt = 0; nt < 4; ++nt) ldsm_x4(b[nt][0], b[nt][1], b[nt][2], b[nt][3], xr + nt * 8 * MP + kt * 16);
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) mma16816(acc[nt], af[kt], b[nt][0], b[nt][1]);       // four independent accumulators
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) mma16816(acc[nt], af[kt + 1], b[nt][2], b[nt][3]);   // back to back
     }
 }
 
@@ -339,20 +339,26 @@ __global__ void __launch_bounds__(128, 2) attn_bwd_dq_mma_kernel(const BwdArgs a
     __syncthreads();
     // pass 1: log-sum-exp of the scaled scores (online max / sum over this thread's columns, then across the quad)
     const bool active = r0 < a.Lq;  // warp-uniform; idle warps of the last tile only keep the barriers
-    float mx[2] = {-INFINITY, -INFINITY}, sm[2] = {0.f, 0.f};
+    float mx[2] = {-1e30f, -1e30f}, sm[2] = {0.f, 0.f};
     for (int jc = 0; active && jc < Lp; jc += 32) {
         float s[4][4] = {};
         mma_rows32(s, qa, Ks, jc, lane);
+        // branch-free online update: chunk maximum first, then one rescale of the running sum per row half
+        float cm[2] = {mx[0], mx[1]};
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
-                if (jc + nt * 8 + 2 * tig + (e & 1) >= a.Lkv) continue;
-                const float v = s[nt][e] * a.scale;
-                const int h = e >> 1;
-                if (v > mx[h]) { sm[h] = sm[h] * __expf(mx[h] - v) + 1.f; mx[h] = v; }
-                else sm[h] += __expf(v - mx[h]);
+                const bool valid = jc + nt * 8 + 2 * tig + (e & 1) < a.Lkv;
+                s[nt][e] = valid ? s[nt][e] * a.scale : -1e30f;
+                cm[e >> 1] = fmaxf(cm[e >> 1], s[nt][e]);
             }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) { sm[h] *= __expf(mx[h] - cm[h]); mx[h] = cm[h]; }
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) sm[e >> 1] += s[nt][e] > -1e29f ? __expf(s[nt][e] - mx[e >> 1]) : 0.f;
     }
     float lse[2];
 #pragma unroll
