@@ -887,3 +887,25 @@ def test_block_backward_vs_autograd(dev, B, L, Lk, D, cross, heads):
         errs[kn] = float((pk.grad.cpu() - P[kn].grad.float()).abs().max() / P[qn].grad.float().abs().max())
     print({k: "%.1e" % v for k, v in errs.items()})
     assert max(errs.values()) <= TOL_BF16, errs
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-4), (torch.bfloat16, TOL_BF16)])
+def test_attention_backward_strided_geometry(dev, dtype, tol):
+    """the temporal regrouping '(n t) s d -> (n s) t d' of transformer.py:2022 as a sequence map (no data movement):
+    sequence (o, s) owns the rows (o*T + t)*inner + s; gradients against fp64 autograd of the regrouped formula"""
+    from hivae_b200 import backward as Bk, engine
+    g = _gen(73)
+    outer, inner, T_, H = 2, 5, 16, 2
+    D, rows = H * 64, 2 * 16 * 5
+    q, k, v, do = ((torch.randn(rows, D, generator=g) * 0.8).to(dtype) for _ in range(4))
+    with torch.enable_grad():
+        qr, kr, vr = (t.double().requires_grad_() for t in (q, k, v))
+        grp = lambda t: t.view(outer, T_, inner, H, 64).permute(0, 2, 3, 1, 4)          # (o, s, h, t, 64)
+        o = torch.softmax(grp(qr) @ grp(kr).transpose(-1, -2) * 0.125, -1) @ grp(vr)
+        o = o.permute(0, 3, 1, 2, 4).reshape(rows, D)
+        (o * do.double()).sum().backward()
+    geom = engine.strided_geom(outer, inner, T_)
+    dq, dk, dv = Bk.attention_backward(q.to(dev), k.to(dev), v.to(dev), o.detach().to(dtype).to(dev), do.to(dev),
+                                       geom.seqs, H, T_, T_, geom.qmap, geom.kvmap, 0.125)
+    assert rel(dq, qr.grad.float()) <= tol and rel(dk, kr.grad.float()) <= tol and rel(dv, vr.grad.float()) <= tol
