@@ -92,6 +92,53 @@ __global__ void __launch_bounds__(256) colsum_partial_bf16x2_kernel(const __nv_b
         partial[(long long)blockIdx.y * N + n + ty] = s;
     }
 }
+// bf16, eight columns per thread (16-byte loads, a warp reads 512 B of a row), four rows in flight per thread;
+// N, ld multiples of 8 and a 16-byte aligned base
+__global__ void __launch_bounds__(256) colsum_partial_bf16x8_kernel(const __nv_bfloat16* __restrict__ x, long long M, int N, long long ld,
+                                                                    float* __restrict__ partial) {
+    __shared__ float sh[8][256 + 8];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int n = blockIdx.x * 256 + 8 * tx;
+    float acc[8] = {};
+    if (n < N) {
+        const long long step = (long long)gridDim.y * 8;
+        long long m = blockIdx.y * 8ll + ty;
+        const __nv_bfloat16* p = x + n;
+        for (; m + 3 * step < M; m += 4 * step) {
+            uint4 v[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(p + (m + u * step) * ld));
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[j]));
+                    acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+                }
+            }
+        }
+        for (; m < M; m += step) {
+            const uint4 v = __ldg(reinterpret_cast<const uint4*>(p + m * ld));
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&w[j]));
+                acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sh[ty][8 * tx + j] = acc[j];
+    __syncthreads();
+    const int c = threadIdx.x, nn = blockIdx.x * 256 + c;
+    if (nn < N) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += sh[i][c];
+        partial[(long long)blockIdx.y * N + nn] = t;
+    }
+}
 __global__ void colsum_final_kernel(const float* __restrict__ partial, int S, int N, float* __restrict__ out) {
     const int n = blockIdx.x * blockDim.x + threadIdx.x;
     if (n >= N) return;
@@ -247,6 +294,80 @@ __global__ void __launch_bounds__(256) headnorm_bwd_kernel(const T* __restrict__
     }
 }
 
+// bf16 with 16-byte alignment: eight lanes per row (one 16-byte load of x and of dy per lane), four rows per warp, so the
+// four row reductions cost three shuffles each for four rows at once
+__global__ void __launch_bounds__(256) headnorm_bwd_bf16x8_kernel(const __nv_bfloat16* __restrict__ x, long long ldx,
+                                                                  const __nv_bfloat16* __restrict__ dy, long long lddy,
+                                                                  const float* __restrict__ w, float eps, long long tokens, int heads,
+                                                                  __nv_bfloat16* __restrict__ dx, long long lddx, float* __restrict__ partial) {
+    __shared__ float sh[8][128];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7, rg = lane >> 3;
+    float wv[8], dwa[8] = {}, dba[8] = {};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) wv[j] = w ? w[8 * sub + j] : 1.f;
+    const long long rows = tokens * heads;
+    auto red8 = [](float v) {
+        v += __shfl_xor_sync(0xffffffffu, v, 1); v += __shfl_xor_sync(0xffffffffu, v, 2); v += __shfl_xor_sync(0xffffffffu, v, 4);
+        return v;
+    };
+    for (long long r0 = (blockIdx.x * 8ll + warp) * 4; r0 < rows; r0 += (long long)gridDim.x * 32) {
+        const long long r = r0 + rg;
+        const bool valid = r < rows;
+        const long long t = valid ? r / heads : 0;
+        const int c = valid ? (int)(r - t * heads) * 64 + 8 * sub : 0;
+        float xv[8] = {}, dv[8] = {};
+        if (valid) {
+            const uint4 a = *reinterpret_cast<const uint4*>(x + t * ldx + c), b = *reinterpret_cast<const uint4*>(dy + t * lddy + c);
+            const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 fa = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&aw[j]));
+                const float2 fb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&bw[j]));
+                xv[2 * j] = fa.x; xv[2 * j + 1] = fa.y; dv[2 * j] = fb.x; dv[2 * j + 1] = fb.y;
+            }
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += xv[j];
+        const float mean = red8(s) * (1.f / 64.f);
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { xv[j] -= mean; q += xv[j] * xv[j]; }
+        const float rstd = rsqrtf(red8(q) * (1.f / 64.f) + eps);
+        float g[8], s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { xv[j] *= rstd; g[j] = dv[j] * wv[j]; s1 += g[j]; s2 += g[j] * xv[j]; }
+        const float c1 = red8(s1) * (1.f / 64.f), c2 = red8(s2) * (1.f / 64.f);
+        if (valid) {
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const __nv_bfloat162 v = __floats2bfloat162_rn(rstd * (g[2 * j] - c1 - xv[2 * j] * c2), rstd * (g[2 * j + 1] - c1 - xv[2 * j + 1] * c2));
+                o[j] = *reinterpret_cast<const uint32_t*>(&v);
+            }
+            *reinterpret_cast<uint4*>(dx + t * lddx + c) = make_uint4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { dwa[j] += dv[j] * xv[j]; dba[j] += dv[j]; }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        dwa[j] += __shfl_xor_sync(0xffffffffu, dwa[j], 8); dwa[j] += __shfl_xor_sync(0xffffffffu, dwa[j], 16);
+        dba[j] += __shfl_xor_sync(0xffffffffu, dba[j], 8); dba[j] += __shfl_xor_sync(0xffffffffu, dba[j], 16);
+    }
+    if (rg == 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { sh[warp][8 * sub + j] = dwa[j]; sh[warp][64 + 8 * sub + j] = dba[j]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 128) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += sh[i][threadIdx.x];
+        partial[(long long)blockIdx.x * 128 + threadIdx.x] = t;
+    }
+}
+
 }  // namespace
 
 // backward of the per-head LayerNorm(64) of q / k (QK-norm): x, dy, dx are (tokens, heads*64) views with their own leading
@@ -258,9 +379,13 @@ extern "C" int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int
     if (tokens == 0) return HV_OK;
     int ctas = hv_layernorm_bwd_ctas();
     const long long rows = tokens * heads;
-    if (ctas > (rows + 7) / 8) ctas = (int)((rows + 7) / 8);
+    auto al16 = [](const void* p, int64_t ld) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && ld % 8 == 0; };
+    const bool x8 = dtype == HV_BF16 && al16(x, ldx) && al16(dy, lddy) && al16(dx, lddx);
+    const long long per_cta = x8 ? 32 : 8;
+    if (ctas > (rows + per_cta - 1) / per_cta) ctas = (int)((rows + per_cta - 1) / per_cta);
     cudaStream_t st = hv_stream(stream);
-    if (dtype == HV_F32) headnorm_bwd_kernel<float><<<ctas, 256, 0, st>>>((const float*)x, ldx, (const float*)dy, lddy, w, eps, tokens, heads, (float*)dx, lddx, workspace);
+    if (x8) headnorm_bwd_bf16x8_kernel<<<ctas, 256, 0, st>>>((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy, w, eps, tokens, heads, (__nv_bfloat16*)dx, lddx, workspace);
+    else if (dtype == HV_F32) headnorm_bwd_kernel<float><<<ctas, 256, 0, st>>>((const float*)x, ldx, (const float*)dy, lddy, w, eps, tokens, heads, (float*)dx, lddx, workspace);
     else headnorm_bwd_kernel<__nv_bfloat16><<<ctas, 256, 0, st>>>((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy, w, eps, tokens, heads, (__nv_bfloat16*)dx, lddx, workspace);
     HV_LAUNCH_CHECK();
     if (dw || db) {
@@ -293,7 +418,8 @@ extern "C" int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype,
     HV_REQUIRE(M >= 0 && N > 0 && ld >= N && workspace && out && (dtype == HV_F32 || dtype == HV_BF16), "hv_colsum: bad arguments");
     int S = hv_colsum_slices();
     const bool x2 = dtype == HV_BF16 && (N % 2 == 0) && (ld % 2 == 0) && (reinterpret_cast<uintptr_t>(x) & 3) == 0;
-    const long long strips = x2 ? (N + 63) / 64 : (N + 31) / 32;
+    const bool x8 = dtype == HV_BF16 && (N % 8 == 0) && (ld % 8 == 0) && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && M >= 2048;
+    const long long strips = x8 ? (N + 255) / 256 : x2 ? (N + 63) / 64 : (N + 31) / 32;
     long long sy = (long long)S / strips;  // keep the grid near 2 CTAs per SM overall
     if (sy < 1) sy = 1;
     if (sy > (M + 7) / 8) sy = (M + 7) / 8 > 0 ? (M + 7) / 8 : 1;
@@ -301,6 +427,7 @@ extern "C" int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype,
     dim3 grid((unsigned)strips, (unsigned)S);
     cudaStream_t st = hv_stream(stream);
     if (dtype == HV_F32) colsum_partial_kernel<float><<<grid, 256, 0, st>>>((const float*)x, M, N, ld, workspace);
+    else if (x8) colsum_partial_bf16x8_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, M, N, ld, workspace);
     else if (x2) colsum_partial_bf16x2_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, M, N, ld, workspace);
     else colsum_partial_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, M, N, ld, workspace);
     HV_LAUNCH_CHECK();

@@ -265,6 +265,13 @@ def test_no_cpu_fallback():
         hv.dwt_init(torch.randn(1, 1, 4, 4))
     with pytest.raises(RuntimeError):
         hv.BasicTransformerBlock(128, 2, 64, attention_bias=True)(torch.randn(1, 4, 128))
+    from hivae_b200 import backward as Bk
+    blk = hv.BasicTransformerBlock(128, 2, 64, attention_bias=True)
+    blk.hv_compute_dtype = torch.bfloat16
+    with pytest.raises(RuntimeError):   # the differentiable block has no torch / CPU path either
+        Bk.basic_block_apply(blk, torch.randn(1, 8, 128, requires_grad=True))
+    with pytest.raises(RuntimeError):
+        Bk.transpose2d(torch.randn(4, 4))
 
 
 def test_product_does_not_import_oracle():
