@@ -775,7 +775,7 @@ def test_gelu_and_layernorm_backward_vs_autograd(dev, dtype):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-4), (torch.bfloat16, TOL_BF16)])
-@pytest.mark.parametrize("B,H,Lq,Lkv", [(3, 2, 274, 274), (2, 4, 100, 49), (5, 2, 16, 16), (2, 8, 264, 264)])
+@pytest.mark.parametrize("B,H,Lq,Lkv", [(3, 2, 274, 274), (2, 4, 100, 49), (5, 2, 16, 16), (2, 8, 264, 264), (2, 1, 1, 1), (1, 2, 7, 600), (1, 2, 650, 33)])
 def test_attention_backward_vs_autograd(dev, dtype, tol, B, H, Lq, Lkv):
     """dq, dk, dv of the dense attention against torch autograd of the reference formula (fp64 on the same rounded inputs)"""
     from hivae_b200 import backward as Bk, engine, ops
