@@ -6,11 +6,15 @@ gated-residual blocks of the denoiser are the next step.
 
 No CPU fallback: every function raises without the CUDA library."""
 import ctypes as C
+import os
 
 import torch
 
 from . import _lib, ops
 from .ops import _chk_cuda, _dt, _p, _stream
+
+
+_SPLITK = os.environ.get("HV_WGRAD_SPLITK", "1") != "0"
 
 
 def transpose2d(x, out=None):
@@ -49,8 +53,19 @@ def linear_backward(dy, x, w, need_dx=True, dx_dtype=torch.bfloat16, w_t=None):
     if need_dx:
         dx = torch.empty(M, K, dtype=dx_dtype, device=dy.device)
         ops.linear(dy, w_t if w_t is not None else transpose2d(w), ops.epi_store(dx))  # (M, N) x (K, N)^T; W^T is reusable for a whole step
-    dw = torch.empty(N, K, dtype=torch.float32, device=dy.device)
-    ops.linear(transpose2d(dy), transpose2d(x), ops.epi_store(dw))     # (N, M) x (K, M)^T
+    # dW = dY^T X: (N, M) x (K, M)^T.  The output has only ceil(N/256) * ceil(K/256) tiles while the contraction runs over
+    # all M tokens, so the tokens are split over `ks` work items per tile that reduce-add into a zeroed dW (fp32 partials
+    # are added in arrival order; HV_WGRAD_SPLITK=0 restores the single-pass, bit-reproducible form)
+    tiles = -(-N // 256) * -(-K // 256)
+    ks = max(1, min(16, 74 // tiles, M // 512)) if _SPLITK and N >= 32 and K % 4 == 0 else 1
+    if ks > 1:
+        dw = torch.zeros(N, K, dtype=torch.float32, device=dy.device)
+        e = ops.epi_residual(ops.Rows(dw.view(1, N, K), 0, N))
+        e.k_split = ks
+        ops.linear(transpose2d(dy), transpose2d(x), e)
+    else:
+        dw = torch.empty(N, K, dtype=torch.float32, device=dy.device)
+        ops.linear(transpose2d(dy), transpose2d(x), ops.epi_store(dw))
     return dx, dw, colsum(dy)
 
 

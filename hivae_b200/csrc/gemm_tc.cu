@@ -239,6 +239,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const long long m_blocks = (M + TILE_M - 1) / TILE_M;
     const long long num_tiles = m_blocks * n_blocks;
     const int num_kb = (K + BK - 1) / BK;
+    // split-K (reduce-add residual epilogue only; the host guarantees every split is non-empty): work item t is split
+    // t / num_tiles of tile t % num_tiles and accumulates k blocks [ks * kb_per, min(num_kb, (ks + 1) * kb_per))
+    const int ksplit = (MODE == HV_EPI_RESIDUAL && epi.e.k_split > 1) ? epi.e.k_split : 1;
+    const int kb_per = (num_kb + ksplit - 1) / ksplit;
+    const long long num_items = num_tiles * ksplit;
     constexpr uint32_t TMEM_COLS = 2 * BN;  // 256 or 512: power of two
 
     if (threadIdx.x == 0) {
@@ -263,9 +268,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         // ===================================================== TMA producer (one per CTA)
         if (lane == 0) {
             int s = 0; uint32_t ph = 0;
-            for (long long t = unit; t < num_tiles; t += units) {
+            for (long long it = unit; it < num_items; it += units) {
+                const long long t = it % num_tiles;
+                const int kb0 = (int)(it / num_tiles) * kb_per, kb1 = kb0 + kb_per < num_kb ? kb0 + kb_per : num_kb;
                 const int m0 = (int)(t / n_blocks) * TILE_M + (int)rank * BM, n0 = (int)(t % n_blocks) * BN + (int)rank * BNL;
-                for (int kb = 0; kb < num_kb; ++kb) {
+                for (int kb = kb0; kb < kb1; ++kb) {
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
                     if (CTAS == 2) {
                         // both CTAs' bytes complete on the leader's barrier, which the leader armed for the pair
@@ -287,19 +294,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         if (lane == 0 && rank == 0) {
             constexpr uint32_t idesc = tc::make_idesc_bf16(TILE_M, BN);
             int s = 0; uint32_t ph = 0; int a = 0; uint32_t aph = 0;
-            for (long long t = unit; t < num_tiles; t += units) {
+            for (long long it = unit; it < num_items; it += units) {
+                const int kb0 = (int)(it / num_tiles) * kb_per, kb1 = kb0 + kb_per < num_kb ? kb0 + kb_per : num_kb;
                 if (CTAS == 2) tc::mbar_wait_cluster(&tmem_empty_bar[a], aph ^ 1); else tc::mbar_wait(&tmem_empty_bar[a], aph ^ 1);
                 tc::fence_after_sync();
                 const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
-                for (int kb = 0; kb < num_kb; ++kb) {
+                for (int kb = kb0; kb < kb1; ++kb) {
                     tc::mbar_wait(&full_bar[s], ph);
                     tc::fence_after_sync();
                     const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(smem_a(s)));
                     const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(smem_b(s)));
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) {  // +32 B per K=16 step inside the 128 B swizzle row
-                        if (CTAS == 2) tc::umma_bf16_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
-                        else tc::umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (kb | k) != 0);
+                        if (CTAS == 2) tc::umma_bf16_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, ((kb - kb0) | k) != 0);
+                        else tc::umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, ((kb - kb0) | k) != 0);
                     }
                     // frees the smem stage (in both CTAs) once these MMAs retire
                     if (CTAS == 2) tc::umma_commit_pair(&empty_bar[s]); else tc::umma_commit(&empty_bar[s]);
@@ -324,7 +332,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             for (int k = 0; k < 8; ++k) reinterpret_cast<float4*>(stage + 32 * 32)[k * 32 + lane] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         int a = 0; uint32_t aph = 0;
-        for (long long t = unit; t < num_tiles; t += units) {
+        for (long long it = unit; it < num_items; it += units) {
+            const long long t = it % num_tiles;
             const long long m0 = (t / n_blocks) * TILE_M + (long long)rank * BM;
             const int n0 = (int)(t % n_blocks) * BN + half * HALF;
             const long long row0 = m0 + q * 32, r = row0 + lane;
@@ -563,7 +572,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, 
         HV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, MODE, CTAS>()));
         configured = true;
     }
-    const long long tiles = ((M + BM * CTAS - 1) / (BM * CTAS)) * ((N + BN - 1) / BN);
+    const long long tiles = ((M + BM * CTAS - 1) / (BM * CTAS)) * ((N + BN - 1) / BN) * (d.e.k_split > 1 ? d.e.k_split : 1);
     if constexpr (CTAS == 1) {
         const int sms = hv_num_sms();
         const int grid = (int)(tiles < sms ? tiles : sms);
@@ -627,6 +636,16 @@ extern "C" int hv_linear_bf16(const void* A, int64_t lda, const void* W, int64_t
         use_reduce = 1;
     } else {
         tr = ta;  // unused
+    }
+    // split-K needs the atomic TMA reduce-add epilogue and nothing that must be applied exactly once
+    if (d.e.k_split > 1) {
+        HV_REQUIRE(d.e.mode == HV_EPI_RESIDUAL && !d.e.bias && !d.e.gate, "hv_linear_bf16: k_split needs a plain residual epilogue (no bias, no gate)");
+        const int num_kb = (K + 63) / 64;
+        int S = (use_reduce && d.e.k_split <= num_kb) ? d.e.k_split : (use_reduce ? num_kb : 1);
+        const int per = (num_kb + S - 1) / S;
+        d.e.k_split = (num_kb + per - 1) / per;  // every split owns at least one k block
+    } else {
+        d.e.k_split = 1;
     }
     cudaStream_t st = hv_stream(stream);
     switch (d.e.mode) {

@@ -207,6 +207,10 @@ typedef struct HvEpilogue {
     const float *qn_w, *qn_b, *kn_w, *kn_b;
     int q_cols, k_cols;
     float qk_eps;
+    /* HV_EPI_RESIDUAL on the tcgen05 path only: split the K dimension over k_split work items per output tile, each
+     * reduce-adding its partial product into res (weight gradients: few output tiles, very long K).  0 / 1 = off.
+     * Needs bias == gate == NULL; fp32 partials are added in arrival order. */
+    int k_split;
 } HvEpilogue;
 
 #define HV_EPI_STORE 0
