@@ -39,6 +39,43 @@ __global__ void __launch_bounds__(256) transpose_bf16x2_kernel(const __nv_bfloat
             *reinterpret_cast<__nv_bfloat162*>(out + (c0 + j) * ld_out + r0 + 2 * tx) = *reinterpret_cast<const __nv_bfloat162*>(&tile[j][2 * tx]);
 }
 
+// bf16 with sizes / strides that are multiples of 8 and 16-byte aligned bases: 16-byte global accesses on both sides.
+// Load: lane = (row, 16-byte chunk) so that 8 lanes cover 128 B of an input row; the eight values are scattered into the
+// transposed tile [col][row] (pitch 66: 2-way conflicts on these 2-byte stores).  Store: lane = (column, 8-row chunk),
+// four conflict-free word reads of the transposed tile make one 16-byte store; 8 lanes cover 128 B of an output row.
+__global__ void __launch_bounds__(256) transpose_bf16x8_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                                               long long rows, long long cols, long long ld_in, long long ld_out) {
+    __shared__ __align__(4) __nv_bfloat16 tile[64][66];
+    const long long r0 = blockIdx.y * 64ll, c0 = blockIdx.x * 64ll;
+    const int ch = threadIdx.x & 7, rr = threadIdx.x >> 3;  // 8 chunks x 32 rows
+    uint4 v[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const long long r = r0 + rr + 32 * h, c = c0 + 8 * ch;
+        v[h] = (r < rows && c < cols) ? __ldg(reinterpret_cast<const uint4*>(in + r * ld_in + c)) : make_uint4(0u, 0u, 0u, 0u);
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const uint32_t w[4] = {v[h].x, v[h].y, v[h].z, v[h].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat162 p = *reinterpret_cast<const __nv_bfloat162*>(&w[j]);
+            tile[8 * ch + 2 * j][rr + 32 * h] = p.x;
+            tile[8 * ch + 2 * j + 1][rr + 32 * h] = p.y;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int cc = rr + 32 * h;  // tile column = output row
+        const long long c = c0 + cc, r = r0 + 8 * ch;
+        if (c < cols && r < rows) {
+            const uint32_t* src = reinterpret_cast<const uint32_t*>(&tile[cc][8 * ch]);
+            *reinterpret_cast<uint4*>(out + c * ld_out + r) = make_uint4(src[0], src[1], src[2], src[3]);
+        }
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) transpose_kernel(const T* __restrict__ in, T* __restrict__ out, long long rows, long long cols,
                                                         long long ld_in, long long ld_out) {
@@ -403,6 +440,8 @@ extern "C" int hv_transpose2d(const void* in, void* out, int64_t rows, int64_t c
     if (rows == 0 || cols == 0) return HV_OK;
     dim3 grid((unsigned)((cols + 63) / 64), (unsigned)((rows + 63) / 64));
     if (dtype == HV_F32) transpose_kernel<float><<<grid, 256, 0, hv_stream(stream)>>>((const float*)in, (float*)out, rows, cols, ld_in, ld_out);
+    else if (((rows | cols | ld_in | ld_out) & 7) == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0)
+        transpose_bf16x8_kernel<<<grid, 256, 0, hv_stream(stream)>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out);
     else if (((rows | cols | ld_in | ld_out) & 1) == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 3) == 0)
         transpose_bf16x2_kernel<<<grid, 256, 0, hv_stream(stream)>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out);
     else transpose_kernel<__nv_bfloat16><<<grid, 256, 0, hv_stream(stream)>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out);
