@@ -249,20 +249,54 @@ __device__ __forceinline__ void ldsm_x4(uint32_t& r0, uint32_t& r1, uint32_t& r2
                  : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
 }
 
-// acc[nt] (16 x 8, nt < 4) += A(16 x 64) . rows (base + nt*8 + g) of a [.][MP] shared array, i.e. A X^T for 32 rows of X.
-// One ldmatrix.x4 fetches the B fragments of two k tiles: lane l addresses row (l & 7), columns 8 (l >> 3) of the 8 x 32 block.
-__device__ __forceinline__ void mma_rows32(float (&acc)[4][4], const uint32_t (&af)[4][4], const __nv_bfloat16* X, int base, int lane) {
-    const __nv_bfloat16* xr = X + (base + (lane & 7)) * MP + (lane >> 3) * 8;
+// B fragments of 32 rows of a [.][MP] shared array: one ldmatrix.x4 fetches two k tiles of an 8-row block; lane l addresses
+// row (l & 7), columns 8 (l >> 3) of the 8 x 32 block.
+// two independent products over the same 32 rows (S = A1 X1^T and dP = A2 X2^T) with their MMAs interleaved, so that
+// consecutive tensor instructions never touch the same accumulator (dependent MMAs are eight instructions apart)
+__device__ __forceinline__ void mma_rows32x2(float (&acc1)[4][4], const uint32_t (&af1)[4][4], const __nv_bfloat16* X1,
+                                             float (&acc2)[4][4], const uint32_t (&af2)[4][4], const __nv_bfloat16* X2, int base, int lane) {
+    const int off = (base + (lane & 7)) * MP + (lane >> 3) * 8;
 #pragma unroll
     for (int kt = 0; kt < 4; kt += 2) {
-        uint32_t b[4][4];
+        uint32_t b1[4][4], b2[4][4];
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) ldsm_x4(b[nt][0], b[nt][1], b[nt][2], b[nt][3], xr + nt * 8 * MP + kt * 16);
+        for (int nt = 0; nt < 4; ++nt) {
+            ldsm_x4(b1[nt][0], b1[nt][1], b1[nt][2], b1[nt][3], X1 + off + nt * 8 * MP + kt * 16);
+            ldsm_x4(b2[nt][0], b2[nt][1], b2[nt][2], b2[nt][3], X2 + off + nt * 8 * MP + kt * 16);
+        }
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) mma16816(acc[nt], af[kt], b[nt][0], b[nt][1]);       // four independent accumulators
+        for (int nt = 0; nt < 4; ++nt) mma16816(acc1[nt], af1[kt], b1[nt][0], b1[nt][1]);
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt) mma16816(acc[nt], af[kt + 1], b[nt][2], b[nt][3]);   // back to back
+        for (int nt = 0; nt < 4; ++nt) mma16816(acc2[nt], af2[kt], b2[nt][0], b2[nt][1]);
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) mma16816(acc1[nt], af1[kt + 1], b1[nt][2], b1[nt][3]);
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt) mma16816(acc2[nt], af2[kt + 1], b2[nt][2], b2[nt][3]);
     }
+}
+
+// one product with the K dimension split over two accumulator sets (same reason), summed at the end
+__device__ __forceinline__ void mma_rows32_split(float (&acc)[4][4], const uint32_t (&af)[4][4], const __nv_bfloat16* X, int base, int lane) {
+    const int off = (base + (lane & 7)) * MP + (lane >> 3) * 8;
+    float hi[4][4] = {};
+    uint32_t b1[4][4], b2[4][4];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+        ldsm_x4(b1[nt][0], b1[nt][1], b1[nt][2], b1[nt][3], X + off + nt * 8 * MP);
+        ldsm_x4(b2[nt][0], b2[nt][1], b2[nt][2], b2[nt][3], X + off + nt * 8 * MP + 32);
+    }
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) mma16816(acc[nt], af[0], b1[nt][0], b1[nt][1]);
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) mma16816(hi[nt], af[2], b2[nt][0], b2[nt][1]);
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) mma16816(acc[nt], af[1], b1[nt][2], b1[nt][3]);
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) mma16816(hi[nt], af[3], b2[nt][2], b2[nt][3]);
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) acc[nt][e] += hi[nt][e];
 }
 
 // acc (16 x 64 as eight 8-wide column tiles) += A(16 x 32, two k tiles of fragments) . X[base .. base+32)[0..64)
@@ -342,7 +376,7 @@ __global__ void __launch_bounds__(128, 2) attn_bwd_dq_mma_kernel(const BwdArgs a
     float mx[2] = {-1e30f, -1e30f}, sm[2] = {0.f, 0.f};
     for (int jc = 0; active && jc < Lp; jc += 32) {
         float s[4][4] = {};
-        mma_rows32(s, qa, Ks, jc, lane);
+        mma_rows32_split(s, qa, Ks, jc, lane);
         // branch-free online update: chunk maximum first, then one rescale of the running sum per row half
         float cm[2] = {mx[0], mx[1]};
 #pragma unroll
@@ -382,8 +416,7 @@ __global__ void __launch_bounds__(128, 2) attn_bwd_dq_mma_kernel(const BwdArgs a
     float dq[8][4] = {};
     for (int jc = 0; jc < Lp; jc += 32) {
         float s[4][4] = {}, dp[4][4] = {};
-        mma_rows32(s, qa, Ks, jc, lane);
-        mma_rows32(dp, da, Vs, jc, lane);
+        mma_rows32x2(s, qa, Ks, dp, da, Vs, jc, lane);
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
@@ -426,8 +459,7 @@ __global__ void __launch_bounds__(128, 2) attn_bwd_dkv_mma_kernel(const BwdArgs 
     float dk[8][4] = {}, dv[8][4] = {};
     for (int ic = 0; ic < Lp; ic += 32) {
         float s[4][4] = {}, dp[4][4] = {};
-        mma_rows32(s, ka, Qs, ic, lane);
-        mma_rows32(dp, va, Ds, ic, lane);
+        mma_rows32x2(s, ka, Qs, dp, va, Ds, ic, lane);
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt) {
             const int i = ic + nt * 8 + 2 * tig;
