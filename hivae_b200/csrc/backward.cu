@@ -7,6 +7,7 @@
 // Everything here is HBM-bound streaming work: 128-byte coalesced rows, fp32 accumulation, deterministic two-stage
 // reductions (fixed grid, fixed order).
 #include "hv_common.cuh"
+#include <type_traits>
 
 namespace {
 
@@ -184,6 +185,17 @@ __global__ void colsum_final_kernel(const float* __restrict__ partial, int S, in
     out[n] = s;
 }
 
+// same reduction, the first `split` sums going to out_a and the rest to out_b (dw / db of a norm; either may be NULL)
+__global__ void colsum_final2_kernel(const float* __restrict__ partial, int S, int N, int split, float* __restrict__ out_a,
+                                     float* __restrict__ out_b) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    float s = 0.f;
+    for (int i = 0; i < S; ++i) s += partial[(long long)i * N + n];
+    if (n < split) { if (out_a) out_a[n] = s; }
+    else if (out_b) out_b[n - split] = s;
+}
+
 // ---------------------------------------------------------------- dx = dy * d/dx gelu_tanh(x)
 __device__ __forceinline__ float gelu_tanh_grad(float x) {
     const float k0 = 0.7978845608028654f, k1 = 0.044715f;
@@ -217,20 +229,30 @@ __global__ void gelu_bwd_bf16x8_kernel(const uint4* __restrict__ pre, const uint
 //   g = dy * w;  dx = rstd * (g - mean(g) - xhat * mean(g * xhat))      (written or accumulated into dx)
 //   dw += dy * xhat, db += dy   -> per-CTA partial sums in shared memory -> partial[cta][2][D] -> hv_colsum-style final
 template <int NV, typename TDY>
-__global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x, const TDY* __restrict__ dy, const float* __restrict__ w,
+__global__ void __launch_bounds__(256, 2) ln_bwd_kernel(const float* __restrict__ x, const TDY* __restrict__ dy, const float* __restrict__ w,
                                                      float eps, long long rows, int D, float* __restrict__ dx, int accumulate,
                                                      float* __restrict__ partial) {
-    extern __shared__ float sh[];  // [2][D] dw / db partials of the CTA
-    for (int i = threadIdx.x; i < 2 * D; i += 256) sh[i] = 0.f;
+    extern __shared__ __align__(16) float sh[];  // [8 warps][2][D] dw / db partials: each lane owns its columns of its warp's rows,
+                                                 // which keeps 2 x NV x 4 accumulators out of the register file (2 CTAs per SM)
+    for (int i = threadIdx.x; i < 16 * D; i += 256) sh[i] = 0.f;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float inv_d = 1.0f / (float)D;
-    float dwa[NV * 4], dba[NV * 4];
-#pragma unroll
-    for (int j = 0; j < NV * 4; ++j) dwa[j] = dba[j] = 0.f;
+    float4* const accw = reinterpret_cast<float4*>(sh + (size_t)warp * 2 * D) + lane;
+    float4* const accb = reinterpret_cast<float4*>(sh + (size_t)warp * 2 * D + D) + lane;
     for (long long r = blockIdx.x * 8ll + warp; r < rows; r += (long long)gridDim.x * 8) {
         float xv[NV * 4], gv[NV * 4];
         float s = 0.f;
+        // every global read of the row is issued before the first reduction: dy stays raw in registers, the dx row that an
+        // accumulating call reads back at the end is pulled into L2 now
+        using DyVec = typename std::conditional<sizeof(TDY) == 4, float4, uint2>::type;
+        DyVec dyraw[NV];
+#pragma unroll
+        for (int j = 0; j < NV; ++j) dyraw[j] = reinterpret_cast<const DyVec*>(dy + r * D)[j * 32 + lane];
+        if (accumulate) {
+#pragma unroll
+            for (int j = 0; j < NV; ++j) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const float4*>(dx + r * D) + j * 32 + lane));
+        }
 #pragma unroll
         for (int j = 0; j < NV; ++j) {
             const float4 v = reinterpret_cast<const float4*>(x + r * D)[j * 32 + lane];
@@ -248,15 +270,16 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
             // four consecutive columns per lane: one 16-byte (fp32) or 8-byte (bf16) load of dy, one 16-byte load of w
             float dv[4];
             if constexpr (sizeof(TDY) == 4) {
-                const float4 t = reinterpret_cast<const float4*>(dy + r * D)[j * 32 + lane];
+                const float4 t = *reinterpret_cast<const float4*>(&dyraw[j]);
                 dv[0] = t.x; dv[1] = t.y; dv[2] = t.z; dv[3] = t.w;
             } else {
-                const uint2 t = reinterpret_cast<const uint2*>(dy + r * D)[j * 32 + lane];
+                const uint2 t = *reinterpret_cast<const uint2*>(&dyraw[j]);
                 dv[0] = __uint_as_float(t.x << 16); dv[1] = __uint_as_float(t.x & 0xffff0000u);
                 dv[2] = __uint_as_float(t.y << 16); dv[3] = __uint_as_float(t.y & 0xffff0000u);
             }
             const float4 wv4 = w ? __ldg(reinterpret_cast<const float4*>(w) + j * 32 + lane) : make_float4(1.f, 1.f, 1.f, 1.f);
             const float wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
+            float dwv[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
                 const float d = dv[e];
@@ -264,8 +287,12 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
                 const float g = d * wv[e];
                 xv[4 * j + e] = xh; gv[4 * j + e] = g;
                 c1 += g; c2 += g * xh;
-                dwa[4 * j + e] += d * xh; dba[4 * j + e] += d;
+                dwv[e] = d * xh;
             }
+            float4 aw = accw[j * 32], ab = accb[j * 32];
+            aw.x += dwv[0]; aw.y += dwv[1]; aw.z += dwv[2]; aw.w += dwv[3];
+            ab.x += dv[0]; ab.y += dv[1]; ab.z += dv[2]; ab.w += dv[3];
+            accw[j * 32] = aw; accb[j * 32] = ab;
         }
         c1 = hv_warp_sum(c1) * inv_d; c2 = hv_warp_sum(c2) * inv_d;
 #pragma unroll
@@ -278,20 +305,14 @@ __global__ void __launch_bounds__(256) ln_bwd_kernel(const float* __restrict__ x
             *dst = o;
         }
     }
-    // warps of the CTA add their register partials one after the other (deterministic order)
-    for (int wv = 0; wv < 8; ++wv) {
-        if (warp == wv) {
+    // the eight warps' partials are added in a fixed order (deterministic)
+    __syncthreads();
+    for (int i = threadIdx.x; i < 2 * D; i += 256) {
+        float t = 0.f;
 #pragma unroll
-            for (int j = 0; j < NV; ++j)
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int col = (j * 32 + lane) * 4 + e;
-                    sh[col] += dwa[4 * j + e]; sh[D + col] += dba[4 * j + e];
-                }
-        }
-        __syncthreads();
+        for (int wv = 0; wv < 8; ++wv) t += sh[(size_t)wv * 2 * D + i];
+        partial[(long long)blockIdx.x * 2 * D + i] = t;
     }
-    for (int i = threadIdx.x; i < 2 * D; i += 256) partial[(long long)blockIdx.x * 2 * D + i] = sh[i];
 }
 
 // ---------------------------------------------------------------- per-head LayerNorm(64) backward (QK-norm)
@@ -426,11 +447,8 @@ extern "C" int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int
     else headnorm_bwd_kernel<__nv_bfloat16><<<ctas, 256, 0, st>>>((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy, w, eps, tokens, heads, (__nv_bfloat16*)dx, lddx, workspace);
     HV_LAUNCH_CHECK();
     if (dw || db) {
-        float* fin = workspace + (size_t)hv_layernorm_bwd_ctas() * 128;
-        colsum_final_kernel<<<1, 128, 0, st>>>(workspace, ctas, 128, fin);
+        colsum_final2_kernel<<<1, 128, 0, st>>>(workspace, ctas, 128, 64, dw, db);
         HV_LAUNCH_CHECK();
-        if (dw) HV_CUDA(cudaMemcpyAsync(dw, fin, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
-        if (db) HV_CUDA(cudaMemcpyAsync(db, fin + 64, 64 * sizeof(float), cudaMemcpyDeviceToDevice, st));
     }
     return HV_OK;
 }
@@ -508,8 +526,9 @@ extern "C" int hv_layernorm_bwd(const float* x, const void* dy, int dy_dtype, co
     int ctas = hv_layernorm_bwd_ctas();
     if (ctas > (rows + 7) / 8) ctas = (int)((rows + 7) / 8);
     cudaStream_t st = hv_stream(stream);
-    const size_t smem = (size_t)2 * D * sizeof(float);
-#define LNB(NV, T) ln_bwd_kernel<NV, T><<<ctas, 256, smem, st>>>(x, (const T*)dy, w, eps, rows, D, dx, accumulate, workspace)
+    const size_t smem = (size_t)16 * D * sizeof(float);
+#define LNB(NV, T) do { HV_CUDA(cudaFuncSetAttribute(ln_bwd_kernel<NV, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+                        ln_bwd_kernel<NV, T><<<ctas, 256, smem, st>>>(x, (const T*)dy, w, eps, rows, D, dx, accumulate, workspace); } while (0)
 #define LNB_T(NV) do { if (dy_dtype == HV_F32) LNB(NV, float); else LNB(NV, __nv_bfloat16); } while (0)
     switch (D / 128) {
         case 1: LNB_T(1); break; case 2: LNB_T(2); break; case 3: LNB_T(3); break; case 4: LNB_T(4); break;
@@ -519,11 +538,8 @@ extern "C" int hv_layernorm_bwd(const float* x, const void* dy, int dy_dtype, co
 #undef LNB
     HV_LAUNCH_CHECK();
     if (dw || db) {  // [ctas][2*D] -> column sums; dw = first D columns, db = last D
-        float* fin = workspace + (size_t)hv_layernorm_bwd_ctas() * 2 * D;  // 2*D floats behind the partials
-        colsum_final_kernel<<<(2 * D + 255) / 256, 256, 0, st>>>(workspace, ctas, 2 * D, fin);
+        colsum_final2_kernel<<<(2 * D + 255) / 256, 256, 0, st>>>(workspace, ctas, 2 * D, D, dw, db);
         HV_LAUNCH_CHECK();
-        if (dw) HV_CUDA(cudaMemcpyAsync(dw, fin, (size_t)D * sizeof(float), cudaMemcpyDeviceToDevice, st));
-        if (db) HV_CUDA(cudaMemcpyAsync(db, fin + D, (size_t)D * sizeof(float), cudaMemcpyDeviceToDevice, st));
     }
     return HV_OK;
 }
