@@ -54,6 +54,7 @@ SIGNATURES = {
     "hv_headnorm64_bwd": (_i, [_vp, _i64, _vp, _i64, _vp, _f, _i64, _i, _vp, _i64, _i, _vp, _vp, _vp, _vp]),
     "hv_attention_bwd": (_i, [_vp, _i64] * 8 + [_i, _i64, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp]),
     "hv_transpose2d": (_i, [_vp, _vp, _i64, _i64, _i64, _i64, _i, _vp]),
+    "hv_transpose2d_colsum": (_i, [_vp, _vp, _i64, _i64, _i64, _i64, _i, _vp, _vp, _vp]),
     "hv_colsum_slices": (_i, []),
     "hv_colsum": (_i, [_vp, _i64, _i, _i64, _i, _vp, _vp, _vp]),
     "hv_gelu_tanh_bwd": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),

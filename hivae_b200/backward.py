@@ -27,6 +27,21 @@ def transpose2d(x, out=None):
     return out
 
 
+def transpose2d_colsum(x):
+    """(x^T, column sums of x) in one pass over x when the fused kernel applies (bf16, sizes / strides multiples of 8,
+    16-byte aligned), otherwise the two separate kernels"""
+    _lib.require_device()
+    assert x.dim() == 2 and x.is_cuda and x.stride(1) == 1
+    R, Cc = x.shape
+    if x.dtype != torch.bfloat16 or (R | Cc | x.stride(0)) & 7 or x.data_ptr() & 15 or R == 0:
+        return transpose2d(x), colsum(x)
+    out = torch.empty(Cc, R, dtype=x.dtype, device=x.device)
+    ws = torch.empty(-(-R // 64) * Cc, dtype=torch.float32, device=x.device)
+    cs = torch.empty(Cc, dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().hv_transpose2d_colsum(_p(x), _p(out), R, Cc, x.stride(0), out.stride(0), _dt(x), _p(ws), _p(cs), _stream()))
+    return out, cs
+
+
 def colsum(x):
     """sum over rows of a (M, N) matrix -> fp32 (N,)  (bias gradient)"""
     _lib.require_device()
@@ -56,17 +71,18 @@ def linear_backward(dy, x, w, need_dx=True, dx_dtype=torch.bfloat16, w_t=None):
     # dW = dY^T X: (N, M) x (K, M)^T.  The output has only ceil(N/256) * ceil(K/256) tiles while the contraction runs over
     # all M tokens, so the tokens are split over `ks` work items per tile that reduce-add into a zeroed dW (fp32 partials
     # are added in arrival order; HV_WGRAD_SPLITK=0 restores the single-pass, bit-reproducible form)
+    dy_t, db = transpose2d_colsum(dy)
     tiles = -(-N // 256) * -(-K // 256)
     ks = max(1, min(16, 74 // tiles, M // 512)) if _SPLITK and N >= 32 and K % 4 == 0 else 1
     if ks > 1:
         dw = torch.zeros(N, K, dtype=torch.float32, device=dy.device)
         e = ops.epi_residual(ops.Rows(dw.view(1, N, K), 0, N))
         e.k_split = ks
-        ops.linear(transpose2d(dy), transpose2d(x), e)
+        ops.linear(dy_t, transpose2d(x), e)
     else:
         dw = torch.empty(N, K, dtype=torch.float32, device=dy.device)
-        ops.linear(transpose2d(dy), transpose2d(x), ops.epi_store(dw))
-    return dx, dw, colsum(dy)
+        ops.linear(dy_t, transpose2d(x), ops.epi_store(dw))
+    return dx, dw, db
 
 
 def gelu_tanh_backward(pre, dy, out_dtype=None):

@@ -44,8 +44,12 @@ __global__ void __launch_bounds__(256) transpose_bf16x2_kernel(const __nv_bfloat
 // Load: lane = (row, 16-byte chunk) so that 8 lanes cover 128 B of an input row; the eight values are scattered into the
 // transposed tile [col][row] (pitch 66: 2-way conflicts on these 2-byte stores).  Store: lane = (column, 8-row chunk),
 // four conflict-free word reads of the transposed tile make one 16-byte store; 8 lanes cover 128 B of an output row.
+// COLSUM: the eight values a lane is about to store are eight rows of one input column, so the column sum over the tile's
+// 64 rows is one 8-lane reduction away; it goes to partial[row tile][column] (summed by colsum_final_kernel).
+template <bool COLSUM>
 __global__ void __launch_bounds__(256) transpose_bf16x8_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
-                                                               long long rows, long long cols, long long ld_in, long long ld_out) {
+                                                               long long rows, long long cols, long long ld_in, long long ld_out,
+                                                               float* __restrict__ partial) {
     __shared__ __align__(4) __nv_bfloat16 tile[64][66];
     const long long r0 = blockIdx.y * 64ll, c0 = blockIdx.x * 64ll;
     const int ch = threadIdx.x & 7, rr = threadIdx.x >> 3;  // 8 chunks x 32 rows
@@ -70,9 +74,20 @@ __global__ void __launch_bounds__(256) transpose_bf16x8_kernel(const __nv_bfloat
     for (int h = 0; h < 2; ++h) {
         const int cc = rr + 32 * h;  // tile column = output row
         const long long c = c0 + cc, r = r0 + 8 * ch;
-        if (c < cols && r < rows) {
-            const uint32_t* src = reinterpret_cast<const uint32_t*>(&tile[cc][8 * ch]);
-            *reinterpret_cast<uint4*>(out + c * ld_out + r) = make_uint4(src[0], src[1], src[2], src[3]);
+        const uint32_t* src = reinterpret_cast<const uint32_t*>(&tile[cc][8 * ch]);
+        const bool inside = c < cols && r < rows;
+        if (inside) *reinterpret_cast<uint4*>(out + c * ld_out + r) = make_uint4(src[0], src[1], src[2], src[3]);
+        if (COLSUM) {
+            float t = 0.f;
+            if (inside) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&src[k]));
+                    t += f.x + f.y;
+                }
+            }
+            t += __shfl_xor_sync(0xffffffffu, t, 1); t += __shfl_xor_sync(0xffffffffu, t, 2); t += __shfl_xor_sync(0xffffffffu, t, 4);
+            if (ch == 0 && c < cols) partial[(long long)blockIdx.y * cols + c] = t;
         }
     }
 }
@@ -183,6 +198,23 @@ __global__ void colsum_final_kernel(const float* __restrict__ partial, int S, in
     float s = 0.f;
     for (int i = 0; i < S; ++i) s += partial[(long long)i * N + n];
     out[n] = s;
+}
+
+// the same reduction for many slices (S in the hundreds): 32 columns x 8 row groups per CTA, fixed summation order
+__global__ void __launch_bounds__(256) colsum_final_wide_kernel(const float* __restrict__ partial, int S, int N, float* __restrict__ out) {
+    __shared__ float sh[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5, n = blockIdx.x * 32 + tx;
+    float a = 0.f;
+    if (n < N)
+        for (int i = ty; i < S; i += 8) a += partial[(long long)i * N + n];
+    sh[ty][tx] = a;
+    __syncthreads();
+    if (ty == 0 && n < N) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += sh[i][tx];
+        out[n] = t;
+    }
 }
 
 // same reduction, the first `split` sums going to out_a and the rest to out_b (dw / db of a norm; either may be NULL)
@@ -459,10 +491,28 @@ extern "C" int hv_transpose2d(const void* in, void* out, int64_t rows, int64_t c
     dim3 grid((unsigned)((cols + 63) / 64), (unsigned)((rows + 63) / 64));
     if (dtype == HV_F32) transpose_kernel<float><<<grid, 256, 0, hv_stream(stream)>>>((const float*)in, (float*)out, rows, cols, ld_in, ld_out);
     else if (((rows | cols | ld_in | ld_out) & 7) == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0)
-        transpose_bf16x8_kernel<<<grid, 256, 0, hv_stream(stream)>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out);
+        transpose_bf16x8_kernel<false><<<grid, 256, 0, hv_stream(stream)>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out, nullptr);
     else if (((rows | cols | ld_in | ld_out) & 1) == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 3) == 0)
         transpose_bf16x2_kernel<<<grid, 256, 0, hv_stream(stream)>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out);
     else transpose_kernel<__nv_bfloat16><<<grid, 256, 0, hv_stream(stream)>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+// out = in^T and colsum[c] = sum_r in[r][c] in one pass over `in` (dY^T and the bias gradient of linear_backward).
+// bf16 only, rows / cols / strides multiples of 8, 16-byte aligned bases (HV_EINVAL otherwise: the caller then uses
+// hv_transpose2d + hv_colsum).  workspace: ceil(rows / 64) * cols floats.
+extern "C" int hv_transpose2d_colsum(const void* in, void* out, int64_t rows, int64_t cols, int64_t ld_in, int64_t ld_out, int dtype,
+                                     float* workspace, float* colsum, void* stream) {
+    HV_REQUIRE(rows > 0 && cols > 0 && ld_in >= cols && ld_out >= rows && dtype == HV_BF16 && workspace && colsum, "hv_transpose2d_colsum: bad arguments");
+    HV_REQUIRE(((rows | cols | ld_in | ld_out) & 7) == 0 && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0,
+               "hv_transpose2d_colsum: sizes / strides must be multiples of 8 and the bases 16-byte aligned");
+    HV_REQUIRE(cols < (1ll << 31) && (rows + 63) / 64 < 65536, "hv_transpose2d_colsum: too large");
+    dim3 grid((unsigned)((cols + 63) / 64), (unsigned)((rows + 63) / 64));
+    cudaStream_t st = hv_stream(stream);
+    transpose_bf16x8_kernel<true><<<grid, 256, 0, st>>>((const __nv_bfloat16*)in, (__nv_bfloat16*)out, rows, cols, ld_in, ld_out, workspace);
+    HV_LAUNCH_CHECK();
+    colsum_final_wide_kernel<<<(unsigned)((cols + 31) / 32), 256, 0, st>>>(workspace, (int)grid.y, (int)cols, colsum);
     HV_LAUNCH_CHECK();
     return HV_OK;
 }

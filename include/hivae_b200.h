@@ -139,6 +139,10 @@ int hv_rows_scatter(const float* src, int64_t src_stride_f, int64_t src_stride_i
  * hv_linear_bf16 with transposed operands:  dX = dY W  (A = dY, W := W^T),  dW = dY^T X  (A = dY^T, W := X^T). */
 /* out[c][r] = in[r][c]; dtype HV_F32 / HV_BF16; ld in elements */
 int hv_transpose2d(const void* in, void* out, int64_t rows, int64_t cols, int64_t ld_in, int64_t ld_out, int dtype, void* stream);
+/* out = in^T and colsum[c] = sum_r in[r][c] in one pass (dY^T + bias gradient of nn.Linear's backward); bf16, sizes and
+ * strides multiples of 8, 16-byte aligned bases; workspace = ceil(rows / 64) * cols floats */
+int hv_transpose2d_colsum(const void* in, void* out, int64_t rows, int64_t cols, int64_t ld_in, int64_t ld_out, int dtype,
+                          float* workspace, float* colsum, void* stream);
 /* bias gradient: out[n] = sum_m x[m][n]; workspace = hv_colsum_slices() * N floats */
 int hv_colsum_slices(void);
 int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype, float* workspace, float* out, void* stream);

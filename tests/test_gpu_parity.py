@@ -725,6 +725,8 @@ def test_transpose_and_colsum(dev, shape, dtype):
     wide = torch.randn(shape[0], shape[1] + 8, generator=_gen(62)).to(dtype).to(dev)
     assert torch.equal(B.transpose2d(wide[:, 3:3 + shape[1]]).cpu(), wide[:, 3:3 + shape[1]].t().contiguous().cpu())  # strided view
     assert rel(B.colsum(x.to(dev)), x.double().sum(0).float()) <= 1e-5
+    xt, cs = B.transpose2d_colsum(x.to(dev))       # fused kernel for aligned bf16, the two separate kernels otherwise
+    assert torch.equal(xt.cpu(), x.t().contiguous()) and rel(cs, x.double().sum(0).float()) <= 1e-5
 
 
 @pytest.mark.gpu
