@@ -217,15 +217,23 @@ __global__ void __launch_bounds__(256) colsum_final_wide_kernel(const float* __r
     }
 }
 
-// same reduction, the first `split` sums going to out_a and the rest to out_b (dw / db of a norm; either may be NULL)
-__global__ void colsum_final2_kernel(const float* __restrict__ partial, int S, int N, int split, float* __restrict__ out_a,
-                                     float* __restrict__ out_b) {
-    const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= N) return;
-    float s = 0.f;
-    for (int i = 0; i < S; ++i) s += partial[(long long)i * N + n];
-    if (n < split) { if (out_a) out_a[n] = s; }
-    else if (out_b) out_b[n - split] = s;
+// same wide reduction, the first `split` sums going to out_a and the rest to out_b (dw / db of a norm; either may be NULL)
+__global__ void __launch_bounds__(256) colsum_final2_kernel(const float* __restrict__ partial, int S, int N, int split,
+                                                            float* __restrict__ out_a, float* __restrict__ out_b) {
+    __shared__ float sh[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5, n = blockIdx.x * 32 + tx;
+    float a = 0.f;
+    if (n < N)
+        for (int i = ty; i < S; i += 8) a += partial[(long long)i * N + n];
+    sh[ty][tx] = a;
+    __syncthreads();
+    if (ty == 0 && n < N) {
+        float t = 0.f;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) t += sh[i][tx];
+        if (n < split) { if (out_a) out_a[n] = t; }
+        else if (out_b) out_b[n - split] = t;
+    }
 }
 
 // ---------------------------------------------------------------- dx = dy * d/dx gelu_tanh(x)
@@ -479,7 +487,7 @@ extern "C" int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int
     else headnorm_bwd_kernel<__nv_bfloat16><<<ctas, 256, 0, st>>>((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy, w, eps, tokens, heads, (__nv_bfloat16*)dx, lddx, workspace);
     HV_LAUNCH_CHECK();
     if (dw || db) {
-        colsum_final2_kernel<<<1, 128, 0, st>>>(workspace, ctas, 128, 64, dw, db);
+        colsum_final2_kernel<<<4, 256, 0, st>>>(workspace, ctas, 128, 64, dw, db);
         HV_LAUNCH_CHECK();
     }
     return HV_OK;
@@ -588,7 +596,7 @@ extern "C" int hv_layernorm_bwd(const float* x, const void* dy, int dy_dtype, co
 #undef LNB
     HV_LAUNCH_CHECK();
     if (dw || db) {  // [ctas][2*D] -> column sums; dw = first D columns, db = last D
-        colsum_final2_kernel<<<(2 * D + 255) / 256, 256, 0, st>>>(workspace, ctas, 2 * D, D, dw, db);
+        colsum_final2_kernel<<<(2 * D + 31) / 32, 256, 0, st>>>(workspace, ctas, 2 * D, D, dw, db);
         HV_LAUNCH_CHECK();
     }
     return HV_OK;
