@@ -111,15 +111,16 @@ def layernorm_backward(x, dy, weight, eps, dx=None, accumulate=False, affine_gra
     return dx, dw, db
 
 
-def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, scale):
+def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, scale, dq=None, dk=None, dv=None):
     """Gradients of ops.attention (head_dim 64, no mask): q / k / v / out / dout are 2-D (rows, heads*64) views in one
     dtype (bf16 or fp32) with unit column stride -> (dq, dk, dv) of the same dtype, dense (rows, heads*64)."""
     _lib.require_device()
     for t in (q, k, v, out, dout):
         assert t.is_cuda and t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype
-    dq = torch.empty(q.shape[0], heads * 64, dtype=q.dtype, device=q.device)
-    dk = torch.empty(k.shape[0], heads * 64, dtype=q.dtype, device=q.device)
-    dv = torch.empty(v.shape[0], heads * 64, dtype=q.dtype, device=q.device)
+    new = lambda t, ref: torch.empty(ref.shape[0], heads * 64, dtype=q.dtype, device=q.device) if t is None else t
+    dq, dk, dv = new(dq, q), new(dk, k), new(dv, v)   # callers may pass column slices of a wider gradient matrix
+    for t in (dq, dk, dv):
+        assert t.is_cuda and t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype and t.shape[1] == heads * 64
     stats = torch.empty(seqs * heads * Lq * 2, dtype=torch.float32, device=q.device)
     _lib.check(_lib.load().hv_attention_bwd(
         _p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0), _p(dout), dout.stride(0),
@@ -128,14 +129,15 @@ def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, sc
     return dq, dk, dv
 
 
-def headnorm64_backward(x, dy, weight, heads, eps=1e-6):
+def headnorm64_backward(x, dy, weight, heads, eps=1e-6, out=None):
     """backward of the per-head LayerNorm(64) of q / k (QK-norm): x (pre-norm), dy are (tokens, heads*64) views (bf16 or
     fp32, unit column stride) -> (dx dense, dw (64,), db (64,))"""
     _lib.require_device()
     assert x.is_cuda and x.dim() == 2 and x.shape == dy.shape and x.shape[1] == heads * 64 and x.dtype == dy.dtype
     assert x.stride(1) == 1 and dy.stride(1) == 1
     lib = _lib.load()
-    dx = torch.empty(x.shape, dtype=x.dtype, device=x.device)
+    dx = torch.empty(x.shape, dtype=x.dtype, device=x.device) if out is None else out   # `out`: e.g. the q columns of d(qkv)
+    assert dx.shape == x.shape and dx.dtype == x.dtype and dx.stride(1) == 1
     ws = torch.empty((lib.hv_layernorm_bwd_ctas() + 1) * 128, dtype=torch.float32, device=x.device)
     dw, db = (torch.empty(64, dtype=torch.float32, device=x.device) for _ in range(2))
     _lib.check(lib.hv_headnorm64_bwd(_p(x), x.stride(0), _p(dy), dy.stride(0), _p(weight), float(eps), x.shape[0], heads,
@@ -215,18 +217,24 @@ def block_backward(bp, saved, dy):
     ops.convert(dx, d16)
     datt, g["attn1.to_out.0.weight"], g["attn1.to_out.0.bias"] = linear_backward(d16, s["att"], bp.wo)
     geom = s["geom"]
-    dq, dk, dv = attention_backward(s["q"], s["k"], s["v"], s["att"], datt, geom.seqs, bp.heads, geom.Lq, geom.Lkv,
-                                    geom.qmap, geom.kvmap, s["scale"])
-    dqp, g["attn1.norm_q.weight"], g["attn1.norm_q.bias"] = headnorm64_backward(s["q_pre"], dq, bp.qn_w, bp.heads)
-    dkp, g["attn1.norm_k.weight"], g["attn1.norm_k.bias"] = headnorm64_backward(s["k_pre"], dk, bp.kn_w, bp.heads)
+    # d(q_pre) | d(k_pre) | dv are written straight into the column slices of the gradient of the fused projection output
+    cross = bp.kind == "cross"
+    Mk = s["k"].shape[0]
+    dproj = torch.empty(Mk, 2 * D if cross else 3 * D, dtype=bf, device=dev)
+    dqp = torch.empty(M, D, dtype=bf, device=dev) if cross else dproj[:, :D]
+    dkp, dvv = (dproj[:, :D], dproj[:, D:]) if cross else (dproj[:, D:2 * D], dproj[:, 2 * D:])
+    dq, dk, _ = attention_backward(s["q"], s["k"], s["v"], s["att"], datt, geom.seqs, bp.heads, geom.Lq, geom.Lkv,
+                                   geom.qmap, geom.kvmap, s["scale"], dv=dvv)
+    _, g["attn1.norm_q.weight"], g["attn1.norm_q.bias"] = headnorm64_backward(s["q_pre"], dq, bp.qn_w, bp.heads, out=dqp)
+    _, g["attn1.norm_k.weight"], g["attn1.norm_k.bias"] = headnorm64_backward(s["k_pre"], dk, bp.kn_w, bp.heads, out=dkp)
     denc = None
-    if bp.kind == "cross":
+    if cross:
         dxn1, g["attn1.to_q.weight"], g["attn1.to_q.bias"] = linear_backward(dqp, s["xn1"], bp.wq)
-        denc, dwkv, dbkv = linear_backward(torch.cat([dkp, dv], dim=1), s["enc16"], bp.wkv, dx_dtype=torch.float32)
+        denc, dwkv, dbkv = linear_backward(dproj, s["enc16"], bp.wkv, dx_dtype=torch.float32)
         for i, n in enumerate(("to_k", "to_v")):
             g["attn1.%s.weight" % n], g["attn1.%s.bias" % n] = dwkv[i * D:(i + 1) * D], dbkv[i * D:(i + 1) * D]
     else:
-        dxn1, dwqkv, dbqkv = linear_backward(torch.cat([dqp, dkp, dv], dim=1), s["xn1"], bp.wqkv)
+        dxn1, dwqkv, dbqkv = linear_backward(dproj, s["xn1"], bp.wqkv)
         for i, n in enumerate(("to_q", "to_k", "to_v")):
             g["attn1.%s.weight" % n], g["attn1.%s.bias" % n] = dwqkv[i * D:(i + 1) * D], dbqkv[i * D:(i + 1) * D]
     _, g["norm1.weight"], g["norm1.bias"] = layernorm_backward(s["x0"].view(M, D), dxn1, bp.n1w, bp.eps, dx=dx, accumulate=True)
