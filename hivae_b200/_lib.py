@@ -71,6 +71,17 @@ SIGNATURES = {
     "hv_grad_norm_clip_coef": (_i, [_vp, _i64, _f, _f, _vp, _vp, _vp]),
     "hv_adamw_clip": (_i, [_vp, _vp, _vp, _vp, _i64, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, _i64, _f, _vp, _vp]),
     "hv_scale_by_device": (_i, [_vp, _i64, _vp, _f, _vp]),
+    "hv_train_chunk_rows": (_i, []),
+    "hv_gate_bwd": (_i, [_vp, _i64, _i64, _i, _i, _i, _vp, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i64, _vp]),
+    "hv_ln_modulate_bwd": (_i, [_vp, _vp, _i, _vp, _vp, _f, _vp, _i64, _i64, _i, _i, _i, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _i,
+                                _vp, _vp, _vp, _vp, _i64, _vp]),
+    "hv_gate_residual": (_i, [_vp, _i64, _i64, _i, _i, _i, _vp, _i, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp]),
+    "hv_silu_bwd": (_i, [_vp, _vp, _i, _vp, _i, _i64, _vp]),
+    "hv_mse_bwd": (_i, [_vp, _vp, _i64, _vp, _vp, _vp]),
+    "hv_rows_reduce": (_i, [_vp, _i, _i64, _i64, _i64, _i64, _i64, _i64, _i64, _vp, _i, _vp]),
+    "hv_rows_index": (_i, [_vp, _vp, _vp, _i64, _i, _i, _i, _i64, _i64, _i, _vp]),
+    "hv_conv3x3_bwd": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp]),
+    "hv_maxpool2_bwd": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
     "hv_attention": (_i, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i, _i64, _i, _i, _i, _i,
                           C.POINTER(HvSeqMap), C.POINTER(HvSeqMap), _f, _vp, _vp]),
 }

@@ -146,6 +146,184 @@ def headnorm64_backward(x, dy, weight, heads, eps=1e-6, out=None):
 
 
 # ------------------------------------------------------------------------------------------------
+# kernels of csrc/train_ops.cu: backward of the adaLN-Zero blocks and of the small layers around them
+
+def _ws_floats(frames, L, D, per=1, groups=0):
+    return (frames * (L // _lib.load().hv_train_chunk_rows() + 3) * per + groups * 2) * D
+
+
+def gate_bwd(drows, y, ada, gate_mot, gate_img, dY, dtable=None):
+    """dY (dense M x D, fp32 / bf16) = gate * dres rows; dtable[cond row, gate column] += sum_rows dres * y.
+    ada None: plain residual branch -> dY = the gradient rows, gathered and converted."""
+    _chk_cuda(drows.res, y, dY)
+    t = ada.table if ada is not None else None
+    ws = torch.empty(_ws_floats(drows.frames, drows.L, drows.D), dtype=torch.float32, device=dY.device) if t is not None else None
+    _lib.check(_lib.load().hv_gate_bwd(
+        _p(drows.res), drows.frames, drows.frame_rows, drows.row_off, drows.L, drows.D, _p(y), _p(t),
+        t.shape[1] if t is not None else 0, gate_mot, gate_img, drows.img_start, drows.img_len,
+        ada.cond_div if ada else 1, ada.cond_mul if ada else 1, _p(dY), _dt(dY), _p(dtable), _p(ws), ws.numel() if ws is not None else 0,
+        _stream()))
+    return dY
+
+
+def ln_modulate_bwd(x, dy, ln_w, ln_b, eps, drows, ada=None, dtable=None, dw=None, db=None, shift_mot=0, scale_mot=0, shift_img=0,
+                    scale_img=0):
+    """backward of ops.ln_modulate: x (M, D) fp32 = the saved input rows, dy (M, D) fp32 / bf16; the input gradient is
+    accumulated into `drows`, dshift / dscale into dtable, dw / db (fp32, D) are accumulated"""
+    _chk_cuda(x, dy, ln_w, ln_b, drows.res, dtable, dw, db)
+    assert x.dtype == torch.float32 and x.shape == dy.shape and x.shape[1] == drows.D and x.shape[0] == drows.M
+    t = ada.table if ada is not None else None
+    cond_div = ada.cond_div if ada is not None else 8
+    groups = -(-drows.frames // cond_div)
+    ws = torch.empty(_ws_floats(drows.frames, drows.L, drows.D, 2, groups), dtype=torch.float32, device=x.device)
+    _lib.check(_lib.load().hv_ln_modulate_bwd(
+        _p(x), _p(dy), _dt(dy), _p(ln_w), _p(ln_b), float(eps), _p(drows.res), drows.frames, drows.frame_rows, drows.row_off,
+        drows.L, drows.D, _p(t), t.shape[1] if t is not None else 0, shift_mot, scale_mot, shift_img, scale_img,
+        drows.img_start, drows.img_len, cond_div, ada.cond_mul if ada else 1, _p(dtable), _p(dw), _p(db), _p(ws), ws.numel(),
+        _stream()))
+
+
+def gate_residual(rows, y, ada=None, gate_mot=0, gate_img=0):
+    """res rows += gate * y (training forward: the branch output y is kept for the gate gradient)"""
+    _chk_cuda(rows.res, y)
+    t = ada.table if ada is not None else None
+    _lib.check(_lib.load().hv_gate_residual(
+        _p(rows.res), rows.frames, rows.frame_rows, rows.row_off, rows.L, rows.D, _p(y), _dt(y), _p(t),
+        t.shape[1] if t is not None else 0, gate_mot, gate_img, rows.img_start, rows.img_len,
+        ada.cond_div if ada else 1, ada.cond_mul if ada else 1, _stream()))
+
+
+def silu_backward(x, dy, out):
+    _chk_cuda(x, dy, out)
+    assert x.dtype == torch.float32 and x.shape == dy.shape == out.shape
+    _lib.check(_lib.load().hv_silu_bwd(_p(x), _p(dy), _dt(dy), _p(out), _dt(out), x.numel(), _stream()))
+    return out
+
+
+def mse_backward(pre, gt, gout=None):
+    """d mse_loss(pre, gt) / d pre * gout (gout: 0-dim / 1-element fp32 device tensor or None)"""
+    _chk_cuda(pre, gt, gout)
+    assert pre.dtype == gt.dtype == torch.float32 and pre.shape == gt.shape
+    out = torch.empty_like(pre)
+    _lib.check(_lib.load().hv_mse_bwd(_p(pre), _p(gt), pre.numel(), _p(gout), _p(out), _stream()))
+    return out
+
+
+def rows_reduce(src, D, n_out, base, stride_out, A, stride_a, B=1, stride_b=0, out=None, accumulate=False):
+    """out[o] (+)= sum_{a, b} src row (base + o*stride_out + a*stride_a + b*stride_b); rows of D floats"""
+    _chk_cuda(src, out)
+    out = torch.empty(n_out, D, dtype=torch.float32, device=src.device) if out is None else out
+    _lib.check(_lib.load().hv_rows_reduce(_p(src), D, n_out, base, stride_out, A, stride_a, B, stride_b, _p(out), int(accumulate), _stream()))
+    return out
+
+
+def rows_index(src, out, idx, frames, S, keep, D, in_frame_rows, out_frame_rows, scatter=False):
+    """src / out may be row-range views of a frames buffer (their frame strides are passed explicitly)"""
+    _chk_cuda(idx)
+    for t in (src, out):
+        assert t.is_cuda and t.dtype == torch.float32 and t.stride(-1) == 1 and (t.dim() < 2 or t.stride(-2) == D)
+    assert idx.dtype == torch.int32
+    _lib.check(_lib.load().hv_rows_index(_p(src), _p(out), _p(idx), frames, S, keep, D, in_frame_rows, out_frame_rows, int(scatter), _stream()))
+    return out
+
+
+def conv3x3_backward(x, w, dy, stride, dw=None, db=None, need_dx=True):
+    _chk_cuda(x, w, dy, dw, db)
+    B_, Cin, H, W = x.shape
+    dx = torch.empty_like(x) if need_dx else None
+    _lib.check(_lib.load().hv_conv3x3_bwd(_p(x), _p(w), _p(dy), _p(dx), _p(dw), _p(db), B_, Cin, w.shape[0], H, W, stride, _stream()))
+    return dx
+
+
+def maxpool2_backward(x, dy):
+    _chk_cuda(x, dy)
+    B_, Cc, H, W = x.shape
+    dx = torch.empty_like(x)
+    _lib.check(_lib.load().hv_maxpool2_bwd(_p(x), _p(dy), _p(dx), B_ * Cc, H, W, _stream()))
+    return dx
+
+
+def weight_t(ctx, w):
+    """W^T of a prepared (packed) weight of `ctx`, cached in the context (same lifetime as the weights it was derived
+    from) and recomputed in place when the context's weights were refreshed"""
+    from . import engine
+    cache = ctx.__dict__.setdefault("_wt", {})
+    key = (w.data_ptr(), tuple(w.shape), w.dtype)
+    ent = cache.get(key)
+    gen = (engine.WEIGHT_EPOCH[0], ctx.generation)
+    if ent is None or ent[0] != gen:
+        t = ent[1] if ent is not None else torch.empty(w.shape[1], w.shape[0], dtype=w.dtype, device=w.device)
+        transpose2d(w, out=t)
+        cache[key] = ent = (gen, t)
+    return ent[1]
+
+
+def linear_grads(ctx, dy, x, w, dw=None, db=None, need_dx=True, dx_accum=None, tag="lg", splitk=None):
+    """Gradients of y = x @ w.T + b in the compute dtype of `w` (bf16 -> tcgen05 GEMM, fp32 -> SIMT GEMM, the parity mode):
+    dy (M, N), x (M, K), w (N, K).  dw: an fp32 (N, K) tensor or a list of row blocks of it (the parameters behind a fused
+    weight) and db likewise are ACCUMULATED into (autograd semantics; they may be views of the gradient arena).
+    Returns dx (M, K) in the compute dtype, or None; dx_accum: an fp32 (M, K) buffer to add dx into instead.
+    A token count that is not a multiple of 8 is handled by zero-padding the contraction dimension of the weight-gradient
+    GEMM's transposed operands."""
+    cd = w.dtype
+    M, N = dy.shape
+    K = x.shape[1]
+    assert x.shape[0] == M and tuple(w.shape) == (N, K), (dy.shape, x.shape, w.shape)
+    if dy.dtype != cd:
+        dy = ops.convert(dy.contiguous(), ctx.buf(tag + "_dyc", (M, N), cd))
+    if x.dtype != cd:
+        x = ops.convert(x.contiguous(), ctx.buf(tag + "_xc", (M, K), cd))
+    dx = None
+    if need_dx:
+        wt = weight_t(ctx, w)
+        if dx_accum is not None:
+            assert dx_accum.dtype == torch.float32 and tuple(dx_accum.shape) == (M, K) and dx_accum.is_contiguous()
+            e = ops.epi_residual(ops.Rows(dx_accum.view(1, M, K), 0, M))
+            if cd == torch.bfloat16 and N >= 16384:  # few output tiles, very long contraction (the packed adaLN Linear)
+                e.k_split = min(64, N // 4096)
+            ops.linear(dy, wt, e)
+        else:
+            dx = ctx.buf(tag + "_dx", (M, K), cd)
+            ops.linear(dy, wt, ops.epi_store(dx))
+    if dw is None and db is None:
+        return dx
+    Mp = -(-M // 8) * 8 if cd == torch.bfloat16 else M
+    dyT = ctx.buf(tag + "_dyT", (N, Mp), cd)
+    if Mp != M:
+        dyT[:, M:].zero_()
+    fused = cd == torch.bfloat16 and not ((M | N | dy.stride(0)) & 7) and not (dy.data_ptr() & 15) and db is not None
+    if fused:
+        ws = ctx.buf(tag + "_csw", (-(-M // 64) * N,), torch.float32)
+        cs = ctx.buf(tag + "_cs", (N,), torch.float32)
+        _lib.check(_lib.load().hv_transpose2d_colsum(_p(dy), _p(dyT), M, N, dy.stride(0), Mp, _dt(dy), _p(ws), _p(cs), _stream()))
+    else:
+        transpose2d(dy, out=dyT)
+        cs = colsum(dy) if db is not None else None
+    if db is not None:
+        dbs, o = (db if isinstance(db, (list, tuple)) else [db]), 0
+        for t in dbs:
+            ops.axpy(1.0, cs[o:o + t.numel()], t.view(-1))
+            o += t.numel()
+    if dw is not None:
+        xT = ctx.buf(tag + "_xT", (K, Mp), cd)
+        if Mp != M:
+            xT[:, M:].zero_()
+        transpose2d(x, out=xT)
+        dws, o = (dw if isinstance(dw, (list, tuple)) else [dw]), 0
+        for t in dws:
+            n = t.shape[0]
+            t2 = t.view(n, K)
+            assert t2.dtype == torch.float32 and t2.is_contiguous()
+            e = ops.epi_residual(ops.Rows(t2.view(1, n, K), 0, n))
+            if cd == torch.bfloat16:
+                tiles = -(-n // 256) * -(-K // 256)
+                e.k_split = splitk if splitk is not None else max(1, min(16, 74 // tiles, Mp // 512))
+            ops.linear(dyT[o:o + n], xT, e)
+            o += n
+    return dx
+
+
+# ------------------------------------------------------------------------------------------------
 # Whole-block backward: BasicTransformerBlock (modules.py:721-743, the object motion encoder's block, a10 / a14) and
 # BasicCrossTransformerBlock (modules.py:817-840, the camera motion encoder's block, a15).
 # bf16 compute mode = the reference's `--mp bf16` autocast semantics (train_amd.py:160-165): bf16 GEMM / attention

@@ -26,33 +26,86 @@ def compute_dtype_for(module):
     return torch.float32
 
 
+# Bumped whenever parameters are updated behind torch's back (optim.AdamW.step writes the flat arena through raw
+# pointers, which never touches `p._version`): prepared weight copies older than this are refreshed in place.
+WEIGHT_EPOCH = [0]
+
+
+def bump_weight_epoch():
+    WEIGHT_EPOCH[0] += 1
+
+
+def params_key(module):
+    """identity of a module's parameter storage: changes when parameters are re-homed (FlatArena, .to(device))"""
+    return hash(tuple(p.data_ptr() for p in module.parameters()))
+
+
+def params_version(module):
+    return (WEIGHT_EPOCH[0], sum(p._version for p in module.parameters()))
+
+
 class Ctx:
     """Device, compute dtype and a name-keyed workspace (stable addresses -> TMA descriptor cache
-    hits, CUDA-graph friendly)."""
+    hits, CUDA-graph friendly).  Every packed / down-cast weight copy is recorded as a binding
+    (destination rows <- source parameters) so that `refresh()` re-derives it in place after an optimizer step."""
 
     def __init__(self, device, dtype):
         assert dtype in (torch.float32, torch.bfloat16)
         self.device, self.dtype = torch.device(device), dtype
         self._ws = {}
+        self.bindings = []
+        self.version = None
+        self.generation = 0
 
-    def buf(self, name, shape, dtype=None):
+    def _bind(self, dst, srcs):
+        self.bindings.append((dst, list(srcs)))
+        return dst
+
+    def refresh(self):
+        """re-copy every derived weight from its (updated) source parameters; addresses stay the same"""
+        self.generation += 1
+        for dst, srcs in self.bindings:
+            off = 0
+            for p in srcs:
+                n = p.shape[0]
+                src = p.detach()
+                if src.device != self.device or src.dtype != torch.float32 or not src.is_contiguous():
+                    src = src.to(self.device, torch.float32).contiguous()
+                ops.convert(src, dst[off:off + n])
+                off += n
+
+    def pack(self, params, gemm=True):
+        """the parameters concatenated along dim 0: a GEMM weight (bf16 when the tcgen05 path applies) or an fp32
+        vector / matrix; recorded for refresh()"""
+        cat = torch.cat([self.f32(p, bind=False) for p in params], 0).contiguous() if len(params) > 1 else self.f32(params[0], bind=False)
+        if gemm:
+            N, K = cat.shape
+            if self.dtype == torch.bfloat16 and K >= 64 and K % 8 == 0 and N >= 64:
+                return self._bind(cat.to(torch.bfloat16), params)
+        if len(params) == 1 and cat.data_ptr() == params[0].data_ptr():
+            return cat  # live alias of the parameter storage
+        return self._bind(cat.clone() if cat.data_ptr() == params[0].data_ptr() else cat, params)
+
+    def buf(self, name, shape, dtype=None, zero=False):
+        """zero=True: zero-filled at creation (for buffers whose padding is never written afterwards)"""
         dtype = dtype or self.dtype
         key = (name, tuple(int(s) for s in shape), dtype)
         t = self._ws.get(key)
         if t is None:
-            t = self._ws[key] = torch.empty(key[1], dtype=dtype, device=self.device)
+            t = self._ws[key] = (torch.zeros if zero else torch.empty)(key[1], dtype=dtype, device=self.device)
         return t
 
-    def f32(self, t):
-        return None if t is None else t.detach().to(self.device, torch.float32).contiguous()
+    def f32(self, t, bind=True):
+        if t is None:
+            return None
+        out = t.detach().to(self.device, torch.float32).contiguous()
+        if bind and out.data_ptr() != t.data_ptr():
+            self._bind(out, [t])
+        return out
 
     def weight(self, w):
         """GEMM weight (N,K): bf16 copy for the tcgen05 path when it applies, fp32 otherwise."""
-        w = self.f32(w)
-        N, K = w.shape
-        if self.dtype == torch.bfloat16 and K >= 64 and K % 8 == 0 and N >= 64:
-            return w.to(torch.bfloat16)
-        return w
+        return self.pack([w])
 
     def act(self, x, name):
         """activation matrix in the dtype the GEMM with weight dtype == self.dtype expects"""
@@ -105,7 +158,7 @@ class BlockP:
 def _cat_bias(ctx, *bs):
     if any(b is None for b in bs):
         return None
-    return torch.cat([ctx.f32(b) for b in bs]).contiguous()
+    return ctx.pack(list(bs), gemm=False)
 
 
 def prepare_block(ctx, blk, kind):
@@ -127,10 +180,10 @@ def prepare_block(ctx, blk, kind):
     )
     if kind == "cross":
         bp.wq, bp.bq = ctx.weight(at.to_q.weight), ctx.f32(at.to_q.bias)
-        bp.wkv = ctx.weight(torch.cat([at.to_k.weight.detach(), at.to_v.weight.detach()], 0))
+        bp.wkv = ctx.pack([at.to_k.weight, at.to_v.weight])
         bp.bkv = _cat_bias(ctx, at.to_k.bias, at.to_v.bias)
     else:
-        bp.wqkv = ctx.weight(torch.cat([at.to_q.weight.detach(), at.to_k.weight.detach(), at.to_v.weight.detach()], 0))
+        bp.wqkv = ctx.pack([at.to_q.weight, at.to_k.weight, at.to_v.weight])
         bp.bqkv = _cat_bias(ctx, at.to_q.bias, at.to_k.bias, at.to_v.bias)
     if ada:
         bp.ada_src = [(blk.norm1.linear.weight, blk.norm1.linear.bias), (blk.norm2.linear.weight, blk.norm2.linear.bias)]
@@ -149,17 +202,17 @@ class AdaPack:
             (w1, b1), (w2, b2) = bp.ada_src
             bp.ada_off1, off = off, off + w1.shape[0]
             bp.ada_off2, off = off, off + w2.shape[0]
-            ws += [w1.detach(), w2.detach()]
-            bs += [b1.detach(), b2.detach()]
+            ws += [w1, w2]
+            bs += [b1, b2]
         self.extra_off = []
         for w, b in extra:
             self.extra_off.append(off)
             off += w.shape[0]
-            ws.append(w.detach())
-            bs.append(b.detach())
+            ws.append(w)
+            bs.append(b)
         self.N = off
-        self.w = ctx.weight(torch.cat(ws, 0))
-        self.b = torch.cat([ctx.f32(b) for b in bs]).contiguous()
+        self.w = ctx.pack(ws)
+        self.b = ctx.pack(bs, gemm=False)
 
     def table(self, ctx, temb, name="ada"):
         """temb (rows, E) fp32 -> (rows, N) fp32"""

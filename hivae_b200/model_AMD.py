@@ -184,14 +184,26 @@ class AMDModel_New(_ConfigModel):
         return pre
 
     # ------------------------------------------------------------------ public API
-    @torch.no_grad()
     def forward(self, video, ref_img, video_grey=None, ref_img_grey=None, time_step=None, return_meta_info=False,
                 camera_mask_ratio=None, object_mask_ratio=None):
-        """Training-step forward (model_AMD.py:1844-2017), inference kernels only (no autograd yet):
-        returns (pre, vel, {'loss','diff_loss','rec_loss'})."""
+        """Training-step forward (model_AMD.py:1844-2017): returns (pre, vel, {'loss','diff_loss','rec_loss'}).
+        With autograd enabled and trainable parameters the result is differentiable (`loss.backward()` runs the
+        hand-chained backward of hivae_b200.train on the sm_100a kernels); under torch.no_grad() it is the plain forward.
+        Random draws are the reference's torch calls in the reference's order (mask ratios, masking noise, time steps,
+        rectified-flow noise), so a seeded run sees the same random numbers."""
         n, t, c, h, w = video.shape
         device = video.device
-        cam, osrc, otgt = self._encode(video, ref_img, 0.6, camera_mask_ratio, object_mask_ratio)
+        assert video.shape == ref_img.shape, f"video.shape:{video.shape}should be equal to ref_img.shape:{ref_img.shape}"
+        if camera_mask_ratio is not None:
+            camera_mask_ratio = (0.6 + 0.4 * torch.rand(1)).item() * camera_mask_ratio   # model_AMD.py:1857-1858
+        if object_mask_ratio is not None:
+            object_mask_ratio = (0.5 * torch.rand(1)).item() * object_mask_ratio           # model_AMD.py:1861-1862
+        grad = torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters())
+        if not grad:
+            with torch.no_grad():
+                cam, osrc, otgt = self._encode(video, ref_img, 0.6, camera_mask_ratio, object_mask_ratio)
+        else:
+            cam_idx, obj_idx = self._mask_indices(n, t, device, camera_mask_ratio, object_mask_ratio)
         zi, zj = ref_img.flatten(0, 1).float().contiguous(), video.flatten(0, 1).float().contiguous()
         if time_step is None:
             time_step = self.prepare_timestep(batch_size=zj.shape[0], device=device)
@@ -199,12 +211,31 @@ class AMDModel_New(_ConfigModel):
             time_step = self.prepare_timestep(batch_size=n, device=device).repeat_interleave(t)
         zt, vel = self.scheduler.get_train_tuple(z1=zj, time_step=time_step)
         zt = zt.contiguous()
-        pre = self._dit(zi, zt, time_step.float(), cam, osrc, otgt)
-        diff_loss = l2(pre, vel)
-        rec_loss = l2(self.scheduler.get_target_with_zt_vel(zt, pre, time_step), zj)
+        if grad:
+            from . import train
+            pre = train.forward_with_grad(self, video, ref_img, time_step.float(), zt, cam_idx, obj_idx)
+            diff_loss = train.mse(pre, vel)
+        else:
+            with torch.no_grad():
+                pre = self._dit(zi, zt, time_step.float(), cam, osrc, otgt)
+                diff_loss = l2(pre, vel)
+        with torch.no_grad():
+            rec_loss = l2(self.scheduler.get_target_with_zt_vel(zt, pre.detach(), time_step), zj)
         if return_meta_info:
             return {"zi": zi, "zj": zj, "zt": zt, "pre": pre, "time_step": time_step}
         return pre, vel, {"loss": diff_loss, "diff_loss": diff_loss, "rec_loss": rec_loss}
+
+    def _mask_indices(self, n, t, device, camera_mask_ratio, object_mask_ratio):
+        """kept-token indices of the two encoders' random_masking, drawn in the reference's order (camera encoder first,
+        model_AMD.py:1920-1926) with the reference's calls (torch.rand on the device, argsort)"""
+        from .transformer import _mask_idx as mask_indices
+        from .transformer import mask_noise
+        cam_idx = obj_idx = None
+        if camera_mask_ratio is not None and self.use_camera:
+            cam_idx = mask_indices(mask_noise(n, self.camera_motion_encoder.img_token_len, device), camera_mask_ratio)
+        if object_mask_ratio is not None and self.use_object and self.use_filter:
+            obj_idx = mask_indices(mask_noise(n * 2 * t, self.object_motion_encoder.img_token_len, device), object_mask_ratio)
+        return cam_idx, obj_idx
 
     @torch.no_grad()
     def encode(self, video, ref_img, video_grey=None, ref_img_grey=None, camera_mask_ratio=None, object_mask_ratio=None):

@@ -185,12 +185,16 @@ class _Block(nn.Module):
 
     def _prepared(self, x):
         dtype = engine.compute_dtype_for(self)
-        key = (x.device, dtype, sum(p._version for p in self.parameters()))
+        key = (x.device, dtype, engine.params_key(self))
         if getattr(self, "_hv_key", None) != key:
             self._hv_ctx = Ctx(x.device, dtype)
             self._hv_bp = engine.prepare_block(self._hv_ctx, self, self.KIND)
             self._hv_ada = engine.AdaPack(self._hv_ctx, [self._hv_bp]) if self._hv_bp.ada_src else None
             self._hv_key = key
+            self._hv_ctx.version = engine.params_version(self)
+        elif self._hv_ctx.version != engine.params_version(self):  # parameters updated in place: refresh the packed copies
+            self._hv_ctx.refresh()
+            self._hv_ctx.version = engine.params_version(self)
         return self._hv_ctx, self._hv_bp, self._hv_ada
 
     @staticmethod

@@ -61,8 +61,26 @@ class FlatArena:
         return self._ws
 
     def zero_grad(self):
+        self.sync_grads(copy_stray=False)
         self.grad.zero_()
         self.clip = None
+
+    def sync_grads(self, copy_stray=True):
+        """`p.grad` is a view of the gradient arena only while nobody rebinds it: `module.zero_grad()` (set_to_none=True by
+        default in torch 2.x) or `p.grad = ...` leave the arena stale and the step would silently see zeros.  Every
+        parameter is checked; a stray gradient is copied into its arena slice (or treated as zero when it is None, as
+        torch's optimizers skip such parameters... which here means a zero update direction) and `p.grad` re-bound."""
+        for p, o in zip(self.params, self.offsets):
+            view = self.grad[o:o + p.numel()].view_as(p)
+            g = p.grad
+            if g is not None and g.data_ptr() == view.data_ptr():
+                continue
+            if copy_stray:
+                if g is None:
+                    view.zero_()
+                else:
+                    view.copy_(g)
+            p.grad = view
 
 
 def mse_loss(pre, gt, out=None):
@@ -82,6 +100,7 @@ def clip_grad_norm_(arena, max_norm, grad_scale=1.0, materialize=False):
     tensor).  The scaling itself is deferred into the next AdamW.step() (no extra pass over the gradients);
     materialize=True also scales arena.grad in place, which is what torch makes observable."""
     _lib.require_device()
+    arena.sync_grads()
     arena.clip = torch.empty(2, dtype=torch.float32, device=arena.grad.device)
     _lib.check(_lib.load().hv_grad_norm_clip_coef(_p(arena.grad), arena.numel, float(grad_scale), float(max_norm),
                                                   _p(arena.workspace()), _p(arena.clip), _stream(arena.grad)))
@@ -108,6 +127,8 @@ class AdamW:
     def step(self, grad_scale=1.0):
         _lib.require_device()
         a = self.arena
+        if a.clip is None:
+            a.sync_grads()  # clip_grad_norm_ already did otherwise
         self.step_count += 1
         g = self.param_groups[0]
         clip = C.c_void_p(a.clip.data_ptr() + 4) if a.clip is not None else None
@@ -115,8 +136,13 @@ class AdamW:
                                              float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
                                              float(g["weight_decay"]), self.step_count, float(grad_scale), clip, _stream(a.flat)))
         a.clip = None
+        # the arena was written through raw pointers (no p._version bump): prepared bf16 / packed weight copies are stale
+        from . import engine
+        engine.bump_weight_epoch()
 
     def zero_grad(self, set_to_none=False):
+        """gradients stay views of the arena (set_to_none is accepted for API compatibility and ignored: a None gradient
+        would detach the parameter from the flat arena)"""
         self.arena.zero_grad()
 
     def state_dict(self):
@@ -135,9 +161,67 @@ class GradAllReducer:
         self.dist, self.arena, self.group = dist, arena, group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         n = max(1, int(bucket_mb * (1 << 20) // 4))
+        self._bucket_elems = n
+        self._issued, self._works = [], []
         self.buckets = [(s, min(s + n, arena.numel)) for s in range(0, arena.numel, n)]
         self.stream = torch.cuda.Stream(arena.grad.device) if arena.grad.is_cuda else None
         self.backend = dist.get_backend(group) if dist.is_initialized() else None
+
+    # ---- overlap with the backward pass: the backward reports finished parameters, a bucket is issued on the side stream
+    # as soon as the last of its parameters is final (DDP's bucketed all-reduce, train_amd.py:489 through accelerate)
+    def begin(self, name_to_param):
+        """arm the per-bucket counters for one backward pass; name_to_param: {parameter name: parameter}"""
+        a = self.arena
+        off = {id(p): o for p, o in zip(a.params, a.offsets)}
+        self._bucket_of, self._pending, self._works = {}, [0] * len(self.buckets), []
+        for name, p in name_to_param.items():
+            o = off.get(id(p))
+            if o is None:
+                continue
+            b0, b1 = o // self._bucket_elems, (o + max(p.numel(), 1) - 1) // self._bucket_elems
+            self._bucket_of[name] = range(b0, b1 + 1)
+            for b in range(b0, b1 + 1):
+                self._pending[b] += 1
+        self._issued = [False] * len(self.buckets)
+
+    def done(self, names):
+        """parameters whose gradient is final; issues every bucket that became complete"""
+        if self.world == 1:
+            return
+        for name in names:
+            for b in self._bucket_of.pop(name, ()):
+                self._pending[b] -= 1
+                if self._pending[b] == 0 and not self._issued[b]:
+                    self._issue(b)
+
+    def _issue(self, b):
+        self._issued[b] = True
+        s, e = self.buckets[b]
+        avg = self.backend == "nccl"
+        op = self.dist.ReduceOp.AVG if avg else self.dist.ReduceOp.SUM
+        if self.stream is not None:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.arena.grad.device))
+            self.stream.wait_event(ev)
+            with torch.cuda.stream(self.stream):
+                self._works.append(self.dist.all_reduce(self.arena.grad[s:e], op=op, group=self.group, async_op=True))
+        else:
+            self.dist.all_reduce(self.arena.grad[s:e], op=op, group=self.group)
+
+    def finish(self):
+        """issue what is left, wait for every bucket; returns the grad_scale for clip / AdamW (1.0 when NCCL averaged)"""
+        if self.world == 1:
+            return 1.0
+        for b in range(len(self.buckets)):
+            if not self._issued[b]:
+                self._issue(b)
+        if self.stream is not None:
+            with torch.cuda.stream(self.stream):
+                for w in self._works:
+                    w.wait()
+            torch.cuda.current_stream(self.arena.grad.device).wait_stream(self.stream)
+        self._works = []
+        return 1.0 if self.backend == "nccl" else 1.0 / self.world
 
     def all_reduce(self):
         """returns the grad_scale the following clip_grad_norm_ / AdamW.step must apply (1.0 when NCCL averaged)"""
@@ -156,3 +240,83 @@ class GradAllReducer:
             for s, e in self.buckets:
                 self.dist.all_reduce(self.arena.grad[s:e], op=op, group=self.group)
         return 1.0 if avg else 1.0 / self.world
+
+
+def backward_order(model):
+    """parameters in the order their gradients become final in hivae_b200.train's backward (denoiser head, denoiser
+    layers last to first, denoiser embeddings + adaLN Linears, object encoder, camera encoder, camera_down), so that the
+    flat arena fills front to back and buckets complete contiguously"""
+    named = dict(model.named_parameters())
+    order, seen = [], set()
+
+    def take(pred):
+        for k in named:
+            if k not in seen and pred(k):
+                seen.add(k)
+                order.append(k)
+
+    dt = "diffusion_transformer."
+    take(lambda k: k.startswith(dt) and any(k.startswith(dt + h) for h in ("proj_out.", "norm_out.norm.", "norm_final.")))
+    nl = 0
+    for k in named:
+        if k.startswith(dt) and "_blocks." in k:
+            nl = max(nl, int(k.split("_blocks.")[1].split(".")[0]) + 1)
+    for i in reversed(range(nl)):
+        for fam in ("spatial_blocks", "camera_transformer_blocks", "object_transformer_blocks"):
+            take(lambda k, fam=fam, i=i: k.startswith("%s%s.%d." % (dt, fam, i)) and ".linear." not in k)
+    take(lambda k: k.startswith(dt))
+    take(lambda k: k.startswith("object_motion_encoder."))
+    take(lambda k: k.startswith("camera_motion_encoder."))
+    take(lambda k: True)
+    return [(k, named[k]) for k in order]
+
+
+class TrainStep:
+    """One optimisation step of train_amd.py:459-496 without an autograd graph:
+        forward (activations kept) -> loss -> hand-chained backward writing into the flat gradient arena, gradient buckets
+        all-reduced on a side stream as they complete -> clip_grad_norm_(max_grad_norm) -> AdamW -> zero_grad.
+    `model` is a hivae_b200.AMDModel_New on the device; parameters with requires_grad=False stay frozen
+    (`--frozen_name`, train_amd.py:226-233)."""
+
+    def __init__(self, model, lr=1e-4, max_grad_norm=1.0, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, bucket_mb=128,
+                 group=None, distributed=None):
+        import torch.distributed as dist
+        self.model = model
+        named = [(k, p) for k, p in backward_order(model) if p.requires_grad]
+        self.names = [k for k, _ in named]
+        self.arena = FlatArena([p for _, p in named])
+        self.opt = AdamW(self.arena, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
+        self.max_grad_norm = max_grad_norm
+        self.sink = {k: p.grad for k, p in named}
+        self.params = dict(named)
+        use_dist = dist.is_initialized() if distributed is None else distributed
+        self.reducer = GradAllReducer(self.arena, bucket_mb=bucket_mb, group=group) if use_dist else None
+        self.last = {}
+
+    def step(self, video, ref_img, time_step=None, noise=None):
+        """returns {'loss', 'diff_loss', 'rec_loss', 'grad_norm'} as 0-dim device tensors (no host synchronisation)"""
+        from . import train
+        from .backward import mse_backward
+        m = self.model
+        n, t = video.shape[:2]
+        dev = video.device
+        zj = video.flatten(0, 1).float().contiguous()
+        if time_step is None:  # the reference's draws, in its order (model_AMD.py:1961-1965)
+            time_step = m.prepare_timestep(batch_size=zj.shape[0], device=dev)
+            if m.diffusion_model_type != "default":
+                time_step = m.prepare_timestep(batch_size=n, device=dev).repeat_interleave(t)
+        zt, vel = m.scheduler.get_train_tuple(z0=noise, z1=zj, time_step=time_step)
+        self.arena.zero_grad()
+        run = train.TrainRun(m)
+        pre = run.forward(video, ref_img, time_step.float(), zt.contiguous(), self.sink)
+        vel = vel.contiguous()
+        loss = mse_loss(pre, vel)
+        rec = mse_loss(m.scheduler.get_target_with_zt_vel(zt, pre, time_step), zj)
+        if self.reducer is not None:
+            self.reducer.begin(self.params)
+        run.backward(mse_backward(pre, vel), self.reducer.done if self.reducer is not None else None)
+        scale = self.reducer.finish() if self.reducer is not None else 1.0
+        norm = clip_grad_norm_(self.arena, self.max_grad_norm, grad_scale=scale)
+        self.opt.step(grad_scale=scale)
+        self.last = {"loss": loss, "diff_loss": loss, "rec_loss": rec, "grad_norm": norm}
+        return self.last

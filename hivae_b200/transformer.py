@@ -40,7 +40,10 @@ class TimestepEmbedding(nn.Module):
 
 
 class _Prepared:
-    pass
+    def weights_changed(self):
+        """drop everything that was derived from the weights by kernels (token tables)"""
+        if hasattr(self, "tabs"):
+            self.tabs.clear()
 
 
 class _HvModule(nn.Module):
@@ -48,15 +51,32 @@ class _HvModule(nn.Module):
 
     def _prepared(self, device):
         dtype = engine.compute_dtype_for(self)
-        key = (torch.device(device), dtype, sum(p._version for p in self.parameters()))
+        key = (torch.device(device), dtype, engine.params_key(self))
         if getattr(self, "_hv_key", None) != key:
             self._hv_P = self._prepare(Ctx(device, dtype))
             self._hv_key = key
+            self._hv_P.ctx.version = engine.params_version(self)
+        elif self._hv_P.ctx.version != engine.params_version(self):  # parameters updated in place: refresh the packed copies
+            self._hv_P.ctx.refresh()
+            self._hv_P.weights_changed()
+            self._hv_P.ctx.version = engine.params_version(self)
         return self._hv_P
 
     def _patch_params(self, ctx, pe):
         w = ctx.f32(pe.proj.weight)
         return w.reshape(w.shape[0], -1).contiguous(), ctx.f32(pe.proj.bias)
+
+
+def mask_noise(N, L, device):
+    """the noise of random_masking (transformer.py:173, 567): the reference's own call, so a seeded run draws the same
+    numbers; tests replace this hook to inject the noise of a CPU run of the reference"""
+    return torch.rand(N, L, device=device)
+
+
+def _mask_idx(noise, mask_ratio):
+    """transformer.py:170-181: ids_keep = argsort(noise)[:, :int(L (1 - mask_ratio))]"""
+    keep = int(noise.shape[1] * (1 - mask_ratio))
+    return torch.argsort(noise, dim=1)[:, :keep].to(torch.int32).contiguous()
 
 
 def _final_norm_out(need_norm_out, m):
@@ -110,20 +130,27 @@ class MotionEncoderLearnTokenTransformer(_HvModule):
 
     @torch.no_grad()
     def forward(self, img_hidden_states, mask_ratio=None):
-        if mask_ratio is not None:
-            raise NotImplementedError("random token masking (train-time augmentation, transformer.py:164-192) is out of scope")
         N, T, C, H, W = img_hidden_states.shape
         P = self._prepared(img_hidden_states.device)
         ctx = P.ctx
         D, p = P.ew.shape[0], self.patch_embed.patch_size
         Lm, S = P.tok.shape[0], self.img_token_len
         assert S == (H // p) * (W // p), "img_token_len should be equal!"
-        frames, FR = N * T, Lm + S
+        # random_masking (transformer.py:164-192): every frame keeps the int(S (1 - ratio)) tokens with the smallest noise
+        idx = _mask_idx(mask_noise(N * T, S, img_hidden_states.device), mask_ratio) if mask_ratio is not None else None
+        keep = S if idx is None else idx.shape[1]
+        frames, FR = N * T, Lm + keep
         x = img_hidden_states.reshape(frames, C, H, W).float().contiguous()
         res = ctx.buf("enc_res", (frames, FR, D), torch.float32)
         tok = engine.small_linear(ctx, P.tok, P.ew, P.eb, "enc_tok")          # (Lm, D), same for every frame
         ops.rows_scatter(tok, 0, 1, None, Rows(res, 0, Lm))
-        ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, None, res, FR, Lm, D)
+        if idx is None:
+            ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, None, res, FR, Lm, D)
+        else:
+            from .backward import rows_index
+            full = ctx.buf("enc_full", (frames, S, D), torch.float32)
+            ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, None, full, S, 0, D)
+            rows_index(full, res[:, Lm:], idx, frames, S, keep, D, S, FR)
         rows, geom = Rows(res, 0, FR), engine.dense_geom(frames, FR)
         for bp in P.blocks:
             engine.run_block(ctx, bp, rows, geom)
@@ -269,7 +296,7 @@ class MotionEncoderLearnTokenOnlyTemporalTransformer(_HvModule):
     @staticmethod
     def _token_table(P, ctx, T, S, D):
         """weights-only table of the initial query tokens of one clip, cached per T"""
-        if T not in P.tabs:
+        if (T, S) not in P.tabs:
             t0 = P.tok.shape[0]
             rep = T // t0
             tok = engine.small_linear(ctx, P.tok, P.ew, P.eb, "cam_tok")  # (t0, D)
@@ -278,24 +305,33 @@ class MotionEncoderLearnTokenOnlyTemporalTransformer(_HvModule):
                 ops.rows_scatter(tok[f:f + 1], 0, 0, P.tpos[f * rep:(f + 1) * rep].contiguous(), Rows(tt, f * rep, rep))
             tab = torch.empty(1, T * S, D, dtype=torch.float32, device=ctx.device)
             ops.rows_scatter(tt.view(T, D), 1, 0, None, Rows(tab.view(T, S, D), 0, S))  # broadcast over s
-            P.tabs[T] = tab
-        return P.tabs[T]
+            P.tabs[(T, S)] = tab
+        return P.tabs[(T, S)]
 
     @torch.no_grad()
     def forward(self, img_hidden_states, mask_ratio=None):
-        if mask_ratio is not None:
-            raise NotImplementedError("random token masking (transformer.py:558-586) is out of scope")
         N, T, C, H, W = img_hidden_states.shape
         P = self._prepared(img_hidden_states.device)
         ctx = P.ctx
         D, p = P.ew.shape[0], self.patch_embed.patch_size
-        S, t0 = self.img_token_len, P.tok.shape[0]
-        assert S == (H // p) * (W // p), "img_token_len should be equal!"
+        S0, t0 = self.img_token_len, P.tok.shape[0]
+        assert S0 == (H // p) * (W // p), "img_token_len should be equal!"
         assert T <= self.video_frames and T % t0 == 0
         x = img_hidden_states.reshape(N * T, C, H, W).float().contiguous()
+        # random_masking (transformer.py:558-586): a clip keeps the same int(S (1 - ratio)) spatial locations in every frame
+        idx = _mask_idx(mask_noise(N, S0, img_hidden_states.device), mask_ratio) if mask_ratio is not None else None
+        S = S0 if idx is None else idx.shape[1]
         # image K/V tokens, dense rows ordered (n, t, s), + 2-D sincos + temporal sincos  (506-514)
         img = ctx.buf("cam_img", (N * T * S, D))
-        ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, P.tpos[:T].contiguous(), img.view(N * T, S, D), S, 0, D)
+        if idx is None:
+            ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, P.tpos[:T].contiguous(), img.view(N * T, S, D), S, 0, D)
+        else:
+            from .backward import rows_index
+            full = ctx.buf("cam_full", (N * T, S0, D), torch.float32)
+            ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, P.tpos[:T].contiguous(), full, S0, 0, D)
+            kept = rows_index(full, ctx.buf("cam_kept", (N * T, S, D), torch.float32), idx.repeat_interleave(T, 0).contiguous(),
+                              N * T, S0, S, D, S0, S)
+            ops.convert(kept, img.view(N * T, S, D))
         # motion queries: token (t) = embed(motion_token)[t // (T/t0)] + temporal[t], identical for all (n, s)  (521-531)
         res = ctx.buf("cam_res", (N * T, S, D), torch.float32)                            # rows ordered (n, t, s)
         block = Rows(res.view(N, T * S, D), 0, T * S)

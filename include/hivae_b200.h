@@ -160,6 +160,51 @@ int hv_layernorm_bwd(const float* x, const void* dy, int dy_dtype, const float* 
 int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int64_t lddy, const float* w, float eps, int64_t tokens,
                       int heads, void* dx, int64_t lddx, int dtype, float* workspace, float* dw, float* db, void* stream);
 
+/* ---- backward of the adaLN-Zero blocks (AMDTransformerBlock / BasicDiTBlock, model/modules.py:1065-1109, 1160-1188) and of
+ * the small layers around them; csrc/train_ops.cu.  Same row addressing as the forward ("frames" above).  Every reduction
+ * is two-stage in a fixed order (bit-reproducible).  hv_train_chunk_rows() = rows per CTA chunk: a frame's range is cut into
+ * G <= L / chunk + 3 chunks, which sizes the workspaces below. */
+int hv_train_chunk_rows(void);
+/* gate backward of `hidden = hidden + gate * branch` (modules.py:1094-1107): dY[dense row] = gate * dres[row] in `dtype`
+ * (fp32 / bf16), dtable[cond row, gate column of the segment] += sum_rows dres * y (y = the saved branch output, dense,
+ * `dtype`).  gate == NULL: plain residual branch, dY = dres rows (gather + convert), y / dtable / workspace unused.
+ * workspace >= frames * G * D floats. */
+int hv_gate_bwd(const float* dres, int64_t frames, int64_t frame_rows, int row_off, int L, int D, const void* y,
+                const float* gate, int64_t gate_ld, int gate_col_mot, int gate_col_img, int img_start, int img_len,
+                int cond_div, int cond_mul, void* dY, int dtype, float* dtable, float* workspace, int64_t ws_floats,
+                void* stream);
+/* backward of hv_ln_modulate: x = the saved fp32 input rows (dense, frames*L x D), dy dense (fp32 / bf16).  The input
+ * gradient is ACCUMULATED into dres rows [row_off, row_off+L) of every frame; dtable (same layout as `ada`) accumulates
+ * dshift / dscale per conditioning row and segment; dw / db (D floats, may be NULL) are accumulated (+=).
+ * ada == NULL: plain nn.LayerNorm backward.  workspace >= (frames * G + groups) * 2 * D floats, groups = ceil(frames /
+ * cond_div) (cond_div = 8 when ada == NULL). */
+int hv_ln_modulate_bwd(const float* x, const void* dy, int dy_dtype, const float* ln_w, const float* ln_b, float eps,
+                       float* dres, int64_t frames, int64_t frame_rows, int row_off, int L, int D, const float* ada,
+                       int64_t ada_ld, int shift_col_mot, int scale_col_mot, int shift_col_img, int scale_col_img,
+                       int img_start, int img_len, int cond_div, int cond_mul, float* dtable, float* dw, float* db,
+                       float* workspace, int64_t ws_floats, void* stream);
+/* training forward of the gated residual when the branch output must be kept: res[row] += gate * y[dense row]
+ * (gate == NULL: plain add); the inference path fuses this into the GEMM epilogue instead */
+int hv_gate_residual(float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D, const void* y, int dtype,
+                     const float* gate, int64_t gate_ld, int gate_col_mot, int gate_col_img, int img_start, int img_len,
+                     int cond_div, int cond_mul, void* stream);
+/* dx = dy * silu'(x) (x fp32): TimestepEmbedding / adaLN activations (transformer.py:1940-1941, modules.py:894) */
+int hv_silu_bwd(const float* x, const void* dy, int dy_dtype, void* dx, int dx_dtype, int64_t n, void* stream);
+/* dpre = gout[0] * 2/n * (pre - gt): backward of hv_mse_loss (gout: device scalar or NULL = 1) */
+int hv_mse_bwd(const float* pre, const float* gt, int64_t n, const float* gout, float* dpre, void* stream);
+/* out[o][:] (+)= sum_{a<A} sum_{b<B} src[base + o*stride_out + a*stride_a + b*stride_b][:]  (rows of D floats, fixed order):
+ * gradients of broadcast token rows (motion_token, source_token / target_token, transformer.py:122-123, 1971-1979) */
+int hv_rows_reduce(const float* src, int D, int64_t n_out, int64_t base, int64_t stride_out, int64_t A, int64_t stride_a,
+                   int64_t B, int64_t stride_b, float* out, int accumulate, void* stream);
+/* random_masking's gather (transformer.py:181-183, 575-577): out[f, j, :] = in[f, idx[f*keep + j], :] (frame strides in
+ * rows); scatter != 0 is its backward out[f, idx[..], :] = in[f, j, :] into a pre-zeroed buffer */
+int hv_rows_index(const float* in, float* out, const int* idx, int64_t frames, int S, int keep, int D, int64_t in_frame_rows,
+                  int64_t out_frame_rows, int scatter, void* stream);
+/* camera_down backward (model/model_AMD.py:1788-1793): dx written (may be NULL), dw / db accumulated (may be NULL) */
+int hv_conv3x3_bwd(const float* x, const float* w, const float* dy, float* dx, float* dw, float* db, int64_t B, int Cin,
+                   int Cout, int H, int W, int stride, void* stream);
+int hv_maxpool2_bwd(const float* x, const float* dy, float* dx, int64_t planes, int H, int W, void* stream);
+
 /* Diagnostics: with HV_ATTN_PROF=1 in the environment the tcgen05 attention kernel accumulates per-phase cycle
  * counters (148 CTAs x 2 key halves x 8 u64: wait S, max pass, max exchange, O epilogue, exp pass, publish P, full
  * tiles, tail tiles); this copies them to `host` and clears them.  Returns 0 when profiling is off. */

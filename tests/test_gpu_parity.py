@@ -649,6 +649,35 @@ def test_default_model_golden(dev, golden, dtype, tol):
     assert rel(pre, g["dit_pre_600"]) <= tol
 
 
+def rms_rel(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return float((a - b).norm() / (b.norm() + 1e-30))
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_default_model_sample20_golden(dev, golden, dtype, tol):
+    """THE HEADLINE COMPUTATION end to end (BASELINE.json config 2, the one bench.py times): the default 695 M model,
+    encode + 20 Euler steps (20 x 36 blocks), against the UNMODIFIED reference run on CPU
+    (tests/golden/make_golden_train.py sample20; model_AMD.py:2020-2195).  Final latents and four intermediate
+    predictions: max-abs error over max-abs of the reference <= 1e-4 (fp32 mode) / 2e-2 (bf16 mode), PSNR(zt, zj) within
+    0.05 dB; the RMS-relative error is printed beside each figure."""
+    g = golden("default_sample20")
+    m = _default(dev, dtype)
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(1, seed=1))
+    _fix_noise(m, g["z0"])
+    meta = m.sample(video.to(dev), ref_img.to(dev), sample_step=20, return_meta_info=True)
+    assert len(meta["pre_cache"]) == 20
+    for i in (0, 6, 13, 19):
+        e, r = rel(meta["pre_cache"][i], g["pre_%d" % i]), rms_rel(meta["pre_cache"][i], g["pre_%d" % i])
+        print("\n  %s step %2d pre: max-abs rel %.2e  rms rel %.2e" % (dtype, i, e, r))
+        assert e <= tol, (i, e)
+    e, r = rel(meta["sample"], g["zt"]), rms_rel(meta["sample"], g["zt"])
+    zj = meta["zj"].cpu()
+    dpsnr = abs(O.psnr(meta["sample"].cpu(), zj) - float(g["psnr"]))
+    print("  %s final zt: max-abs rel %.2e  rms rel %.2e  |dPSNR| %.4f dB" % (dtype, e, r, dpsnr))
+    assert e <= tol and dpsnr <= 0.05
+
+
 def test_kernels_ran_natively(dev):
     """the product path launched our kernels (no silent eager fallback)"""
     from hivae_b200 import ops

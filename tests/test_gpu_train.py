@@ -1,0 +1,265 @@
+"""GPU tier (-m gpu): the training path (BASELINE config 5) against
+  * tests/golden/train_step_small.safetensors — one step of train_amd.py:459-496 run by the UNMODIFIED reference on CPU
+    (loss, global gradient norm, the norm of every parameter gradient, 31 named gradients in full, their AdamW deltas),
+  * the oracle restatement under torch autograd (checked against the reference's autograd when the fixture was made),
+  * tests/golden/small_masked.safetensors — random_masking with the reference's noise.
+
+Tolerances: fp32 mode 1e-4, bf16 mode 2e-2 — max-abs error over max-abs of the reference tensor, floored at 1e-5 of the
+global gradient norm for gradients that are mathematically zero (norm_k.bias: softmax is invariant to a constant added to
+every key), with the RMS-relative figure printed beside it.
+"""
+import json
+import os
+
+import pytest
+import torch
+
+from oracle import amd_oracle as O
+from hivae_b200 import configs, synth
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TOL = {torch.float32: 1e-4, torch.bfloat16: 2e-2}
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available(), "the gpu tier needs a CUDA device"
+    from hivae_b200 import _lib
+    _lib.require_device()
+    return torch.device("cuda:0")
+
+
+def _small(dev, dtype, cfg=None):
+    import hivae_b200 as hv
+    m = hv.AMDModel_New(**(cfg or configs.SMALL))
+    sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 0)
+    m.load_state_dict(sd)
+    return m.to(dev).set_compute_dtype(dtype), sd
+
+
+def _fix(m, z0, steps, n):
+    ts = steps.repeat_interleave(16)
+    orig = m.scheduler.get_train_tuple
+    m.scheduler.get_train_tuple = lambda z0_=None, z1=None, time_step=None, **kw: orig(z0=z0.to(z1.device), z1=z1, time_step=time_step)
+    m.prepare_timestep = lambda batch_size, device, time_step=None: (steps if batch_size == n else ts).to(device)
+
+
+def _err(a, b, floor=0.0):
+    a, b = a.detach().float().cpu().reshape(-1), b.detach().float().cpu().reshape(-1)
+    mx = float((a - b).abs().max() / max(float(b.abs().max()), floor, 1e-30))
+    rms = float((a - b).norm() / max(float(b.norm()), floor, 1e-30))
+    return mx, rms
+
+
+def _report(rows, tol, what):
+    rows.sort(key=lambda r: -r[1])
+    print("\n%s: worst of %d tensors (max-abs rel, rms rel)" % (what, len(rows)))
+    for name, mx, rms in rows[:8]:
+        print("  %-72s %.2e %.2e" % (name, mx, rms))
+    bad = [r for r in rows if not r[1] <= tol]
+    assert not bad, "%s: %d tensors above %.0e, worst %s" % (what, len(bad), tol, bad[0])
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_train_step_golden(dev, golden, dtype):
+    """loss.backward() through the differentiable AMDModel_New.forward == the reference's autograd (SURVEY 8c golden #6)"""
+    g = golden("train_step_small")
+    names = json.load(open(os.path.join(GOLDEN, "train_step_small_names.json")))
+    tol = TOL[dtype]
+    m, _ = _small(dev, dtype)
+    assert sorted(k for k, _ in m.named_parameters()) == sorted(names)  # registration order differs, the key set is the contract
+    n = g["steps"].numel()
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(n, seed=1))
+    _fix(m, g["z0"], g["steps"], n)
+    with torch.enable_grad():
+        pre, vel, ld = m(video.to(dev), ref_img.to(dev))
+        assert pre.requires_grad and ld["loss"].requires_grad
+        ld["loss"].backward()
+    assert _err(pre, g["pre"])[0] <= tol and _err(vel, g["vel"])[0] <= 1e-6
+    assert abs(float(ld["loss"]) - float(g["loss"][0])) <= tol * float(g["loss"][0])
+    assert abs(float(ld["rec_loss"]) - float(g["loss"][2])) <= tol * float(g["loss"][2])
+    gn = float(g["grad_norm"])
+    grads = {k: p.grad for k, p in m.named_parameters()}
+    assert all(v is not None for v in grads.values())
+    total = torch.sqrt(sum((v.double() ** 2).sum() for v in grads.values()))
+    print("\nloss %.6f (ref %.6f)  grad-norm %.6f (ref %.6f)" % (float(ld["loss"]), float(g["loss"][0]), float(total), gn))
+    assert abs(float(total) - gn) <= tol * gn
+    # the norm of EVERY parameter gradient, then 31 gradients element by element
+    rows = []
+    for k, ref in zip(names, g["grad_norms_all"]):
+        rows.append((k, abs(float(grads[k].norm()) - float(ref)) / max(float(ref), 1e-3 * gn), 0.0))
+    _report(rows, tol, "per-parameter gradient norms (%s)" % dtype)
+    rows = [(k[5:],) + _err(grads[k[5:]], v, 1e-5 * gn) for k, v in g.items() if k.startswith("grad.")]
+    _report(rows, tol, "named gradients (%s)" % dtype)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_fused_train_step_golden(dev, golden, dtype):
+    """optim.TrainStep (forward -> backward into the flat arena -> clip -> AdamW) == the reference's step: the parameter
+    deltas after one step, and a second step still sees the updated weights (prepared copies are refreshed)"""
+    from hivae_b200 import optim
+    g = golden("train_step_small")
+    tol = TOL[dtype]
+    m, sd = _small(dev, dtype)
+    n = g["steps"].numel()
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(n, seed=1))
+    video, ref_img = video.to(dev), ref_img.to(dev)
+    ts = g["steps"].repeat_interleave(16).to(dev)
+    step = optim.TrainStep(m, lr=1e-4, max_grad_norm=1.0, distributed=False)
+    out = step.step(video, ref_img, time_step=ts, noise=g["z0"].to(dev))
+    gn = float(g["grad_norm"])
+    assert abs(float(out["loss"]) - float(g["loss"][0])) <= tol * float(g["loss"][0])
+    assert abs(float(out["grad_norm"]) - gn) <= tol * gn
+    # AdamW's first step is -lr * g / (|g| + eps) - lr * wd * p: its direction is ill-conditioned where |g| ~ eps, so the
+    # deltas are compared element by element where the reference gradient is at least 5 % of the tensor's largest, and in
+    # the rms sense over all elements in fp32
+    cur = dict(m.named_parameters())
+    rows = []
+    for k, v in g.items():
+        if k.startswith("delta."):
+            name = k[6:]
+            d = cur[name].detach().cpu() - sd[name]
+            gr = g["grad." + name]
+            mask = gr.abs() > 0.05 * gr.abs().max()
+            mx = float((d - v)[mask].abs().max() / v[mask].abs().max())
+            rows.append((name, mx, _err(d, v)[1]))
+    _report(list(rows), 1e-3, "AdamW parameter deltas where |g| > 5 %% of max (%s)" % dtype)
+    if dtype == torch.float32:
+        _report([(k, rms, rms) for k, mx, rms in rows], 2e-3, "AdamW parameter deltas, rms over all elements (fp32)")
+    # second step: it must see the UPDATED weights (stale prepared copies would reproduce the first loss exactly), and the
+    # inference forward on the weights after two steps must agree with the oracle evaluated on those weights
+    out2 = step.step(video, ref_img, time_step=ts, noise=g["z0"].to(dev))
+    assert float(out2["loss"]) != float(out["loss"])
+    sd2 = {k: v.detach().cpu().clone() for k, v in m.state_dict().items()}
+    orc = O.AMDOracle(sd2, configs.SMALL["enc_nhead"], configs.SMALL["diffusion_attn_num_heads"], 16, 2, configs.SMALL["motion_token_num"])
+    _fix(m, g["z0"], g["steps"], n)
+    with torch.no_grad():
+        pre, vel, ld = m(video, ref_img)
+        opre, ovel, old = orc.forward(video.cpu(), ref_img.cpu(), ts.cpu(), g["z0"])
+    assert _err(pre, opre)[0] <= tol, "forward after two optimizer steps runs on stale prepared weights"
+
+
+def test_train_vs_oracle_autograd_other_batch(dev):
+    """a different batch / steps / noise than the fixture, fp32 mode, checked against the oracle's autograd on the host"""
+    m, sd = _small(dev, torch.float32)
+    n = 1
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(n, seed=5))
+    z0 = torch.randn(16, 4, 32, 32, generator=torch.Generator().manual_seed(9))
+    steps = torch.tensor([250.0])
+    _fix(m, z0, steps, n)
+    with torch.enable_grad():
+        pre, vel, ld = m(video.to(dev), ref_img.to(dev))
+        ld["loss"].backward()
+        sdg = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+        orc = O.AMDOracle(sdg, configs.SMALL["enc_nhead"], configs.SMALL["diffusion_attn_num_heads"], 16, 2, configs.SMALL["motion_token_num"])
+        opre, ovel, old = orc.forward(video, ref_img, steps.repeat_interleave(16), z0)
+        old["loss"].backward()
+    gn = float(torch.sqrt(sum((v.grad.double() ** 2).sum() for v in sdg.values())))
+    rows = [(k,) + _err(p.grad, sdg[k].grad, 1e-5 * gn) for k, p in m.named_parameters()]
+    _report(rows, 1e-4, "all gradients vs oracle autograd (fp32)")
+
+
+def test_frozen_camera_encoder(dev, golden):
+    """--frozen_name camera_motion_encoder (scripts/amd_new.sh:66): frozen parameters get no gradient, camera_down behind
+    the frozen encoder still does, and every other gradient is unchanged"""
+    g = golden("train_step_small")
+    m, _ = _small(dev, torch.float32)
+    for k, p in m.named_parameters():
+        if "camera_motion_encoder" in k:
+            p.requires_grad_(False)
+    n = g["steps"].numel()
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(n, seed=1))
+    _fix(m, g["z0"], g["steps"], n)
+    with torch.enable_grad():
+        pre, vel, ld = m(video.to(dev), ref_img.to(dev))
+        ld["loss"].backward()
+    gn = float(g["grad_norm"])
+    for k, p in m.named_parameters():
+        if "camera_motion_encoder" in k:
+            assert p.grad is None
+        elif "grad." + k in g:
+            assert _err(p.grad, g["grad." + k], 1e-5 * gn)[0] <= 1e-4, k
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_random_masking_golden(dev, golden, dtype, monkeypatch):
+    """camera_mask_ratio / object_mask_ratio (train_amd.py:459, transformer.py:164-192, 558-586) with the reference's noise:
+    forward() in both modes (no_grad and differentiable) and encode()"""
+    from hivae_b200 import transformer as T
+    g = golden("small_masked")
+    tol = TOL[dtype]
+    m, _ = _small(dev, dtype)
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(2, seed=1))
+    video, ref_img = video.to(dev), ref_img.to(dev)
+    _fix(m, g["z0"], g["steps"], 2)
+
+    def feed(*noises):
+        it = iter(noises)
+        monkeypatch.setattr(T, "mask_noise", lambda N, L, device: next(it).to(device))
+
+    feed(g["enc_cam_noise"], g["enc_obj_noise"])
+    cam, osrc, otgt = m.encode(video, ref_img, camera_mask_ratio=0.5, object_mask_ratio=0.8)
+    assert cam.shape == g["enc_camera"].shape
+    assert _err(cam, g["enc_camera"])[0] <= tol and _err(osrc, g["enc_obj_src"])[0] <= tol and _err(otgt, g["enc_obj_tgt"])[0] <= tol
+    for grad_mode in (False, True):
+        feed(g["cam_noise"], g["obj_noise"])
+        torch.manual_seed(1234)  # the two ratio draws of forward() come from the CPU generator
+        with torch.set_grad_enabled(grad_mode):
+            pre, vel, ld = m(video, ref_img, camera_mask_ratio=0.5, object_mask_ratio=0.8)
+            assert pre.requires_grad == grad_mode
+            if grad_mode:
+                ld["loss"].backward()
+                assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in m.parameters())
+        assert _err(pre, g["pre"])[0] <= tol, grad_mode
+        assert abs(float(ld["loss"]) - float(g["loss"][0])) <= tol * float(g["loss"][0])
+
+
+def test_linear_grads_odd_token_count(dev):
+    """a token count that is not a multiple of 8: the contraction dimension of the weight-gradient GEMM is
+    zero-padded; bf16 operands, fp64 reference"""
+    from hivae_b200 import backward as B
+    from hivae_b200.engine import Ctx
+    ctx = Ctx(dev, torch.bfloat16)
+    gen = torch.Generator().manual_seed(3)
+    for M, N, K in ((274, 256, 128), (3 * 18 + 1, 192, 64)):
+        x = torch.randn(M, K, generator=gen).to(dev).bfloat16()
+        w = (torch.randn(N, K, generator=gen) / K ** 0.5).to(dev).bfloat16()
+        dy = torch.randn(M, N, generator=gen).to(dev).bfloat16()
+        dw = torch.zeros(N, K, device=dev)
+        db = torch.zeros(N, device=dev)
+        dx = B.linear_grads(ctx, dy, x, w, dw, db)
+        xd, wd, dyd = x.double(), w.double(), dy.double()
+        assert _err(dx, dyd @ wd)[0] <= 1e-2 and _err(dw, dyd.t() @ xd)[0] <= 1e-2 and _err(db, dyd.sum(0))[0] <= 1e-2
+        B.linear_grads(ctx, dy, x, w, dw, db)  # accumulates
+        assert _err(dw, 2 * (dyd.t() @ xd))[0] <= 1e-2
+
+
+def test_block_forward_after_adamw_step_uses_new_weights(dev):
+    """FlatArena + AdamW update the parameters through raw pointers; the prepared bf16 / packed copies of
+    a block must follow"""
+    import hivae_b200 as hv
+    from hivae_b200 import optim
+    torch.manual_seed(0)
+    blk = hv.modules.BasicTransformerBlock(128, 2, 64, attention_bias=True).to(dev)
+    blk.hv_compute_dtype = torch.bfloat16
+    x = torch.randn(2, 24, 128, device=dev)
+    y0 = blk(x).clone()
+    opt = optim.AdamW(blk.parameters(), lr=1e-1)
+    y1 = blk(x).clone()           # the arena re-homed every parameter
+    assert torch.equal(y0, y1)
+    opt.arena.grad.normal_()
+    optim.clip_grad_norm_(opt.arena, 1.0)
+    opt.step()
+    y2 = blk(x)
+    sd = {"b." + k: v.detach().cpu() for k, v in blk.state_dict().items()}
+    ref = O.basic_block(sd, "b", x.cpu(), 2)
+    assert _err(y2, ref)[0] <= 3e-2 and _err(y2, y0)[0] > 5e-2
+    # a gradient re-bound behind the arena's back is picked up
+    p = next(blk.parameters())
+    before = p.detach().clone()
+    blk.zero_grad(set_to_none=True)
+    for q in blk.parameters():
+        q.grad = torch.ones_like(q)
+    opt.step()
+    assert not torch.equal(before, p.detach())
