@@ -156,7 +156,9 @@ def run_reference(args):
         "impl": "reference", "metric": "clips_per_sec_encode_decode_17x256x256", "value": value, "unit": "clips/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": 1e3 * wall / steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": _config(args.gpus),
+        "config": dict(_config(args.gpus), reference_arm="CPU arm: 1 clip per step, encode + 1 Euler step timed, x%d extrapolated "
+                       "(identical work per Euler step); uses no GPU and does not grow with --gpus" % SAMPLE_STEPS),
+        "gpus_used": 0,
         "cpu_baseline": {"value": value, "unit": "clips/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -175,6 +177,116 @@ def _config(n_gpus):
 
 
 # ------------------------------------------------------------------------------------------------
+def _secondary(torch, dev, share):
+    """The two secondary figures BASELINE.json's metric names.
+    attn_tensor_pct: in-step TFLOP/s of the spatial attention launches (algorithmic 4 S^2 64 per (sequence, head)) over the
+    measured sustained bf16 peak.  dwt_hbm_pct: the fused Haar pyramid kernels on configs[3] sizes, timed HBM-clean: one
+    CUDA graph walks over >= 5 GB of distinct inputs + outputs (40x the 126 MB L2), so no launch can be served from L2.
+    `gbs` = the bytes the fused kernel has to move (every input element read once, every output element written once:
+    2 N sizeof for the analysis, N (sizeof + 4) for the synthesis) / time — the HBM roofline of the operation;
+    `gbs_per_level_formula` = SURVEY 8d's per-level count (read N + write N on every level, sum_k 4^-k more), which
+    a fused pyramid beats by construction and is therefore NOT compared with the HBM peak.  A `gbs` above 1.2x the
+    measured HBM copy peak would be rejected as cache-served."""
+    from hivae_b200 import ops
+    pk = _peaks()
+    sec = {"peaks": {"hbm_gbs": pk["hbm"], "bf16_tflops_sustained": pk["tf_sustained"], "source": pk["src"]}}
+    att = {k: v for k, v in share.items() if k.startswith("attention_L") and v["tflops"] > 0 and int(k.split("L")[1]) >= 64}
+    if att:
+        ms = sum(v["ms"] for v in att.values())
+        tf = sum(v["tflops"] * v["ms"] for v in att.values()) / ms
+        sec["attn_tensor_pct"] = round(100.0 * tf / pk["tf_sustained"], 2)
+        sec["attn_tflops_in_step"] = round(tf, 1)
+        sec["attn_share_of_step"] = round(sum(v["share"] for v in att.values()), 4)
+    cases = {}
+    for name, T, H, L, dt, inverse in (("fwd_f32_33x3x512x512_L3", 33, 512, 3, torch.float32, False),
+                                       ("inv_f32_33x3x512x512_L3", 33, 512, 3, torch.float32, True),
+                                       ("fwd_bf16_33x3x512x512_L3", 33, 512, 3, torch.bfloat16, False),
+                                       ("fwd_f32_17x3x256x256_L2", 17, 256, 2, torch.float32, False)):
+        es = 4 if dt == torch.float32 else 2
+        numel = T * 3 * H * H
+        geo = sum(4.0 ** -k for k in range(L))
+        alg = numel * geo * (es + 4) if inverse else 2 * numel * es * geo
+        per_inst = numel * es * 2 if not inverse else numel * (es + 4)   # bytes the fused kernel moves
+        n_inst = max(4, min(512, int(5.0e9 / per_inst) + 1))
+        xs = [torch.randn(T, 3, H, H, device=dev).to(dt) for _ in range(n_inst)]
+        if inverse:
+            pyr = [ops.dwt2_haar_pyramid(x, L) for x in xs]
+            del xs
+            keep = []
+            run = lambda: keep.append([ops.idwt2_haar_pyramid(*p) for p in pyr])
+        else:
+            keep = []
+            run = lambda: keep.append([ops.dwt2_haar_pyramid(x, L) for x in xs])
+        run(); keep.clear()            # warms the allocator: the graph's outputs are then distinct live blocks
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            run()
+        g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(3):
+            g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        gbs = per_inst * n_inst * 3 / (e0.elapsed_time(e1) * 1e6)
+        cases[name] = {"gbs": round(gbs, 1), "pct": round(100.0 * gbs / pk["hbm"], 2), "instances": n_inst,
+                       "gbs_per_level_formula": round(alg * n_inst * 3 / (e0.elapsed_time(e1) * 1e6), 1),
+                       "rejected": bool(gbs > 1.2 * pk["hbm"])}
+        del g, keep
+        torch.cuda.empty_cache()
+    sec["dwt"] = cases
+    head = cases["fwd_f32_33x3x512x512_L3"]
+    sec["dwt_hbm_pct"] = None if head["rejected"] else head["pct"]
+    return sec
+
+
+TRAIN_CLIPS_PER_GPU = 4        # scripts/amd_new.sh:40 (--batch_size 4), BASELINE.json configs[4]
+TRAIN_TFLOP_PER_CLIP = 13.5    # SURVEY.md 8d: 3 x (one DiT forward + the encoders)
+
+
+def _train_leg(torch, dist, dev, m, rank, world, timed, steps=3, warmup=2):
+    """BASELINE.json configs[4]: one train step of train_amd.py:459-496 on the default model (bf16 compute, fp32 master
+    weights and AdamW moments, random init, synthetic latents, 4 clips per GPU): forward with kept activations ->
+    hand-chained backward into the flat gradient arena, gradient buckets all-reduced over NCCL as they complete ->
+    clip_grad_norm_(1.0) -> AdamW.  Also timed: the same step without the collective (difference = exposed all-reduce)
+    and the all-reduce of the whole arena alone."""
+    from hivae_b200 import optim, synth
+    step = optim.TrainStep(m, lr=1e-4, max_grad_norm=1.0, distributed=world > 1)
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(TRAIN_CLIPS_PER_GPU, seed=101 + rank).to(dev))
+    torch.manual_seed(1234)  # every rank draws the same time steps / noise stream, like the reference's set_seed (train_amd.py:154)
+    fn = lambda: step.step(video, ref_img)
+    for _ in range(warmup):
+        out = fn()
+    ms = timed(fn, steps) / steps
+    rec = {"workload": "configs[4]: train step, default model 695M, bf16 compute / fp32 master + AdamW, %d clips per GPU, "
+                       "synthetic latents, random init" % TRAIN_CLIPS_PER_GPU,
+           "ms_per_step": round(ms, 2), "clips_per_s": round(TRAIN_CLIPS_PER_GPU * world / ms * 1e3, 3),
+           "tflops_per_gpu": round(TRAIN_TFLOP_PER_CLIP * TRAIN_CLIPS_PER_GPU / ms * 1e3, 1),
+           "frac_of_sustained_peak": round(TRAIN_TFLOP_PER_CLIP * TRAIN_CLIPS_PER_GPU / ms * 1e3 / _peaks()["tf_sustained"], 4),
+           "loss": round(float(out["loss"]), 5), "grad_norm": round(float(out["grad_norm"]), 4),
+           "grad_bytes": step.arena.numel * 4, "allreduce_ms": None, "allreduce_exposed_ms": None,
+           "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2)}
+    if world > 1:
+        red = step.reducer
+        step.reducer = None
+        ms_local = timed(fn, steps) / steps           # same step, gradients left un-reduced
+        step.reducer = red
+
+        def only_allreduce():
+            red.begin({})
+            red.finish()
+        only_allreduce()
+        ms_ar = timed(only_allreduce, steps) / steps
+        busbw = 2.0 * (world - 1) / world * step.arena.numel * 4 / (ms_ar * 1e6)
+        rec.update(allreduce_ms=round(ms_ar, 3), allreduce_exposed_ms=round(max(ms - ms_local, 0.0), 3),
+                   ms_per_step_without_collective=round(ms_local, 2), allreduce_busbw_gbs=round(busbw, 1),
+                   buckets=len(red.buckets))
+    return rec if rank == 0 else None
+
+
+# ------------------------------------------------------------------------------------------------
 def run_ours(args):
     import torch
     import hivae_b200 as hv
@@ -183,6 +295,10 @@ def run_ours(args):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus != world:
+        raise SystemExit("bench.py --gpus %d needs %d ranks: launch it as `python -m torch.distributed.run --nnodes=1 --nproc-per-node %d "
+                         "--master-addr 127.0.0.1 --master-port P bench.py --gpus %d ...` (WORLD_SIZE is %d)"
+                         % (args.gpus, args.gpus, args.gpus, args.gpus, world))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     dist = None
@@ -288,6 +404,11 @@ def run_ours(args):
             except (OSError, KeyError, ValueError):
                 pass
 
+    secondary = None
+    if rank == 0 and not args.no_secondary:
+        secondary = _secondary(torch, dev, share)
+    train = None if args.no_train else _train_leg(torch, dist, dev, m, rank, world, timed)
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
@@ -306,7 +427,8 @@ def run_ours(args):
             "tflops_per_gpu": round(TFLOP_PER_CLIP * CLIPS_PER_GPU * args.steps / (ms / 1e3) , 1),
             "e2e": {"value": clips / (ms_e2e / 1e3), "unit": "clips/s",
                     "h2d_bytes_per_step": z_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4},
-            "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu, "kernels": share,
+            "gpu_launches": int(launches), "clocks": clk, "roofline": roof, "cpu_baseline": cpu, "secondary": secondary,
+            "train": train, "kernels": share,
         }
         print(json.dumps(line), flush=True)
     if dist is not None:
@@ -321,6 +443,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the train-step sub-record (BASELINE configs[4])")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the attention tensor-pipe %% / DWT HBM %% legs")
     ap.add_argument("--ncu-range", action="store_true", help="cudaProfilerStart/Stop around the timed steps")
     ap.add_argument("--sample-steps", type=int, default=None, help="Euler steps per clip (default 20 = configs[1]; 10/25/50 = configs[2] sweep)")
     ap.add_argument("--clips-per-gpu", type=int, default=None, help="clips per GPU (default 8 = configs[1]; configs[2] uses 32 / n_gpus)")

@@ -17,6 +17,21 @@ from .ops import _chk_cuda, _dt, _p, _stream
 _SPLITK = os.environ.get("HV_WGRAD_SPLITK", "1") != "0"
 
 
+def _timed(name):
+    """records the wrapped call in ops.PROFILE (per-launch CUDA events) when the bench's profile leg is on"""
+    def deco(fn):
+        def wrapper(*a, **k):
+            tok = ops._prof(name)
+            try:
+                return fn(*a, **k)
+            finally:
+                ops._prof_end(tok)
+        wrapper.__name__, wrapper.__doc__ = fn.__name__, fn.__doc__
+        return wrapper
+    return deco
+
+
+@_timed("transpose")
 def transpose2d(x, out=None):
     """(R, C) -> (C, R), bf16 or fp32; x may be a row-strided view with unit column stride"""
     _lib.require_device()
@@ -27,6 +42,7 @@ def transpose2d(x, out=None):
     return out
 
 
+@_timed("transpose_colsum")
 def transpose2d_colsum(x):
     """(x^T, column sums of x) in one pass over x when the fused kernel applies (bf16, sizes / strides multiples of 8,
     16-byte aligned), otherwise the two separate kernels"""
@@ -42,6 +58,7 @@ def transpose2d_colsum(x):
     return out, cs
 
 
+@_timed("colsum")
 def colsum(x):
     """sum over rows of a (M, N) matrix -> fp32 (N,)  (bias gradient)"""
     _lib.require_device()
@@ -85,6 +102,7 @@ def linear_backward(dy, x, w, need_dx=True, dx_dtype=torch.bfloat16, w_t=None):
     return dx, dw, db
 
 
+@_timed("gelu_bwd")
 def gelu_tanh_backward(pre, dy, out_dtype=None):
     """dx = dy * gelu_tanh'(pre); pre / dy bf16 or fp32 (same dtype), dx in out_dtype (default: same)"""
     _chk_cuda(pre, dy)
@@ -94,6 +112,7 @@ def gelu_tanh_backward(pre, dy, out_dtype=None):
     return dx
 
 
+@_timed("ln_bwd")
 def layernorm_backward(x, dy, weight, eps, dx=None, accumulate=False, affine_grads=True):
     """nn.LayerNorm backward over the last dimension: x fp32 (..., D), dy fp32 / bf16 -> (dx fp32, dw, db).
     dx may be an existing fp32 buffer to write or accumulate into (the residual-stream gradient)."""
@@ -111,6 +130,7 @@ def layernorm_backward(x, dy, weight, eps, dx=None, accumulate=False, affine_gra
     return dx, dw, db
 
 
+@_timed("attention_bwd")
 def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, scale, dq=None, dk=None, dv=None):
     """Gradients of ops.attention (head_dim 64, no mask): q / k / v / out / dout are 2-D (rows, heads*64) views in one
     dtype (bf16 or fp32) with unit column stride -> (dq, dk, dv) of the same dtype, dense (rows, heads*64)."""
@@ -129,6 +149,7 @@ def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, sc
     return dq, dk, dv
 
 
+@_timed("headnorm_bwd")
 def headnorm64_backward(x, dy, weight, heads, eps=1e-6, out=None):
     """backward of the per-head LayerNorm(64) of q / k (QK-norm): x (pre-norm), dy are (tokens, heads*64) views (bf16 or
     fp32, unit column stride) -> (dx dense, dw (64,), db (64,))"""
@@ -152,6 +173,7 @@ def _ws_floats(frames, L, D, per=1, groups=0):
     return (frames * (L // _lib.load().hv_train_chunk_rows() + 3) * per + groups * 2) * D
 
 
+@_timed("gate_bwd")
 def gate_bwd(drows, y, ada, gate_mot, gate_img, dY, dtable=None):
     """dY (dense M x D, fp32 / bf16) = gate * dres rows; dtable[cond row, gate column] += sum_rows dres * y.
     ada None: plain residual branch -> dY = the gradient rows, gathered and converted."""
@@ -166,6 +188,7 @@ def gate_bwd(drows, y, ada, gate_mot, gate_img, dY, dtable=None):
     return dY
 
 
+@_timed("ln_modulate_bwd")
 def ln_modulate_bwd(x, dy, ln_w, ln_b, eps, drows, ada=None, dtable=None, dw=None, db=None, shift_mot=0, scale_mot=0, shift_img=0,
                     scale_img=0):
     """backward of ops.ln_modulate: x (M, D) fp32 = the saved input rows, dy (M, D) fp32 / bf16; the input gradient is
@@ -183,6 +206,7 @@ def ln_modulate_bwd(x, dy, ln_w, ln_b, eps, drows, ada=None, dtable=None, dw=Non
         _stream()))
 
 
+@_timed("gate_residual")
 def gate_residual(rows, y, ada=None, gate_mot=0, gate_img=0):
     """res rows += gate * y (training forward: the branch output y is kept for the gate gradient)"""
     _chk_cuda(rows.res, y)

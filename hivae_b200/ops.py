@@ -238,7 +238,9 @@ def silu(x, out):
 
 def convert(x, out):
     _chk_cuda(x, out)
+    tok = _prof("convert", 0, x.numel() * (x.element_size() + out.element_size()))
     _lib.check(_lib.load().hv_convert(_p(x), _dt(x), _p(out), _dt(out), x.numel(), _stream()))
+    _prof_end(tok)
     return out
 
 
@@ -256,8 +258,10 @@ def rows_scatter(src, stride_f, stride_i, add, rows):
 
 def rows_gather(rows, out):
     _chk_cuda(rows.res, out)
+    tok = _prof("rows_gather", 0, rows.M * rows.D * 8)
     _lib.check(_lib.load().hv_rows_gather(_p(rows.res), rows.frames, rows.frame_rows, rows.row_off, rows.L, rows.D, _p(out),
                                           _stream()))
+    _prof_end(tok)
     return out
 
 

@@ -111,9 +111,11 @@ def test_fused_train_step_golden(dev, golden, dtype):
     gn = float(g["grad_norm"])
     assert abs(float(out["loss"]) - float(g["loss"][0])) <= tol * float(g["loss"][0])
     assert abs(float(out["grad_norm"]) - gn) <= tol * gn
-    # AdamW's first step is -lr * g / (|g| + eps) - lr * wd * p: its direction is ill-conditioned where |g| ~ eps, so the
-    # deltas are compared element by element where the reference gradient is at least 5 % of the tensor's largest, and in
-    # the rms sense over all elements in fp32
+    # AdamW's first step is -lr * g / (|g| + eps) - lr * wd * p.  Where |g| ~ eps = 1e-8 (clipped gradients of the small
+    # layers) the step is proportional to g, so it inherits the gradient tolerance (1e-4 / 2e-2); where |g| >> eps it is
+    # -lr * sign(g).  Its direction is ill-conditioned for near-zero elements, so the deltas are compared element by element
+    # where the reference gradient is at least 5 % of the tensor's largest; one ulp of the parameter is allowed on top
+    # (the delta is a difference of two fp32 parameters).  fp32 also checks the rms over all elements.
     cur = dict(m.named_parameters())
     rows = []
     for k, v in g.items():
@@ -122,9 +124,10 @@ def test_fused_train_step_golden(dev, golden, dtype):
             d = cur[name].detach().cpu() - sd[name]
             gr = g["grad." + name]
             mask = gr.abs() > 0.05 * gr.abs().max()
-            mx = float((d - v)[mask].abs().max() / v[mask].abs().max())
+            ulp = 1.2e-7 * float(sd[name].abs().max())
+            mx = max(0.0, float((d - v)[mask].abs().max()) - ulp) / float(v[mask].abs().max())
             rows.append((name, mx, _err(d, v)[1]))
-    _report(list(rows), 1e-3, "AdamW parameter deltas where |g| > 5 %% of max (%s)" % dtype)
+    _report(list(rows), 2e-4 if dtype == torch.float32 else 2e-2, "AdamW parameter deltas where |g| > 5 %% of max (%s)" % dtype)
     if dtype == torch.float32:
         _report([(k, rms, rms) for k, mx, rms in rows], 2e-3, "AdamW parameter deltas, rms over all elements (fp32)")
     # second step: it must see the UPDATED weights (stale prepared copies would reproduce the first loss exactly), and the
