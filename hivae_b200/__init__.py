@@ -20,5 +20,8 @@ from .transformer import (MotionEncoderLearnTokenTransformer, MotionEncoderLearn
 from .model_AMD import AMDModel, AMDModel_New, AMD_N, AMD_models  # noqa: F401
 from . import sharding  # noqa: F401
 from . import optim  # noqa: F401
+from . import utils  # noqa: F401
+from .utils import find_latest_checkpoint, model_load_pretrain, frozen_model  # noqa: F401
+from .pipeline import AMDPipeLine_single  # noqa: F401
 
 __version__ = "0.1.0"

@@ -22,7 +22,7 @@ class HvEpilogue(C.Structure):
         ("gate", _vp), ("gate_ld", _i64), ("gate_col_mot", _i), ("gate_col_img", _i),
         ("img_start", _i), ("img_len", _i), ("cond_div", _i), ("cond_mul", _i),
         ("qn_w", _vp), ("qn_b", _vp), ("kn_w", _vp), ("kn_b", _vp),
-        ("q_cols", _i), ("k_cols", _i), ("qk_eps", _f), ("k_split", _i),
+        ("q_cols", _i), ("k_cols", _i), ("qk_eps", _f), ("k_split", _i), ("out2", _vp), ("ldo2", _i64),
     ]
 
 

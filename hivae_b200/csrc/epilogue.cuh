@@ -5,7 +5,8 @@
 
 struct HvEpiDev {
     HvEpilogue e;
-    int vec_ok;  // out / res / bias / gate bases and strides allow 16-byte accesses
+    int vec_ok;   // out / res / bias / gate bases and strides allow 16-byte accesses
+    int vec_ok2;  // the same for the optional second output
 };
 
 // host-side validation + alignment analysis
@@ -33,13 +34,23 @@ static inline int hv_epilogue_prepare(const HvEpilogue* epi, int64_t M, int N, H
         }
     }
     d.vec_ok = ok ? 1 : 0;
+    d.vec_ok2 = 0;
+    if (e.out2) {
+        HV_REQUIRE(e.mode == HV_EPI_GELU || e.mode == HV_EPI_QKNORM, "%s: a second output needs the GELU or QKNORM epilogue", who);
+        HV_REQUIRE(e.ldo2 >= N, "%s: bad second output", who);
+        const int per16 = e.out_dtype == HV_F32 ? 4 : 8;
+        d.vec_ok2 = (ok && al16(e.out2) && e.ldo2 % per16 == 0) ? 1 : 0;
+    }
     return HV_OK;
 }
 
 template <int NC>
-__device__ __forceinline__ void hv_epi_store_dense(const HvEpilogue& e, int vec_ok, long long r, int col0, int N, const float (&v)[NC]) {
+__device__ __forceinline__ void hv_epi_store_dense(const HvEpilogue& e, int vec_ok, long long r, int col0, int N, const float (&v)[NC],
+                                                   void* out_ptr = nullptr, long long out_ld = 0) {
+    void* const base = out_ptr ? out_ptr : e.out;
+    const long long ld = out_ptr ? out_ld : e.ldo;
     if (e.out_dtype == HV_F32) {
-        float* o = reinterpret_cast<float*>(e.out) + r * e.ldo + col0;
+        float* o = reinterpret_cast<float*>(base) + r * ld + col0;
         if (vec_ok && col0 + NC <= N) {
 #pragma unroll
             for (int j = 0; j < NC; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
@@ -48,7 +59,7 @@ __device__ __forceinline__ void hv_epi_store_dense(const HvEpilogue& e, int vec_
             for (int j = 0; j < NC; ++j) if (col0 + j < N) o[j] = v[j];
         }
     } else {
-        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(e.out) + r * e.ldo + col0;
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(base) + r * ld + col0;
         if (vec_ok && (NC % 8 == 0) && col0 + NC <= N) {
 #pragma unroll
             for (int j = 0; j < NC; j += 8)
@@ -82,6 +93,7 @@ __device__ __forceinline__ void hv_epilogue_row(const HvEpiDev& d, long long r, 
             for (int j = 0; j < NC; ++j) if (col0 + j < N) acc[j] += e.bias[col0 + j];
         }
     }
+    if (e.out2 && e.mode != HV_EPI_RESIDUAL) hv_epi_store_dense<NC>(e, d.vec_ok2, r, col0, N, acc, e.out2, e.ldo2);
     if (e.mode == HV_EPI_STORE) {
         hv_epi_store_dense<NC>(e, d.vec_ok, r, col0, N, acc);
     } else if (e.mode == HV_EPI_GELU) {

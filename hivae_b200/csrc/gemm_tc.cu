@@ -34,7 +34,10 @@ constexpr int SMEM_LIMIT = 232448 - 512;                     // 227 KB per CTA m
 
 // One 32x32 fp32 transpose tile per epilogue warp; the residual (TMA reduce) epilogue keeps 32 zero rows behind
 // each tile so that a reduce may start at any row of the tile (see epi_block_reduce).
-template <int MODE> constexpr int staging_floats_per_warp() { return MODE == HV_EPI_RESIDUAL ? 64 * 32 : 32 * 32; }
+// MODE_DUAL: internal flag on top of HV_EPI_GELU / HV_EPI_QKNORM — two bf16 outputs (pre-activation + activation) leave
+// through two alternating staging tiles per warp, so a tile is only rewritten when the store issued two back has been read
+constexpr int MODE_DUAL = 8;
+template <int MODE> constexpr int staging_floats_per_warp() { return (MODE & ~MODE_DUAL) == HV_EPI_RESIDUAL ? 64 * 32 : ((MODE & MODE_DUAL) ? 2 * 32 * 32 : 32 * 32); }
 template <int MODE> constexpr int staging_bytes() { return EPI_WARPS * staging_floats_per_warp<MODE>() * 4; }
 // CTAS = 1: one CTA per 128 x BN tile.  CTAS = 2: a CTA pair per 256 x BN tile, BN/2 rows of B per CTA.
 template <int BN, int CTAS> constexpr int stage_bytes() { return (BM + BN / CTAS) * BK * 2; }
@@ -105,9 +108,12 @@ __device__ __forceinline__ void epi_block_reduce(const HvEpiDev& d, const CUtens
 // (128 B) into the warp's staging tile in the 128 B swizzle layout (conflict-free 16-byte writes), one lane
 // issues cp.async.bulk.tensor.  No shared-memory read-back and no per-lane global stores; rows >= M and
 // columns >= N are clipped by the tensor map.
+template <int PENDING = 0>
 __device__ __forceinline__ void epi_block_tma_store(const CUtensorMap* tmap_c, float* stage, int lane, long long row0,
                                                     int col0, const float (&lo)[32], const float (&hi)[32]) {
-    if (lane == 0) tc::bulk_wait_read0();  // the previous store has finished reading the staging tile
+    if (lane == 0) {  // the previous store from THIS staging tile has finished reading it
+        if (PENDING == 0) tc::bulk_wait_read0(); else tc::bulk_wait_read1();
+    }
     __syncwarp();
     uint8_t* rowp = reinterpret_cast<uint8_t*>(stage) + lane * 128;
 #pragma unroll
@@ -215,12 +221,14 @@ __device__ __forceinline__ void epi_add_bias(const HvEpiDev& d, int col0, int N,
     }
 }
 
-template <int BN, int MODE, int CTAS>
+template <int BN, int MODEX, int CTAS>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-               const __grid_constant__ CUtensorMap tmap_r, long long M, int N, int K, int use_reduce,
-               const __grid_constant__ HvEpiDev epi) {
-    constexpr int STAGES = num_stages<BN, MODE, CTAS>();
+               const __grid_constant__ CUtensorMap tmap_r, const __grid_constant__ CUtensorMap tmap_r2, long long M, int N, int K,
+               int use_reduce, const __grid_constant__ HvEpiDev epi) {
+    constexpr int MODE = MODEX & ~MODE_DUAL;
+    constexpr bool DUAL = (MODEX & MODE_DUAL) != 0;  // second (pre-activation) output through tmap_r2; TMA-store path only
+    constexpr int STAGES = num_stages<BN, MODEX, CTAS>();
     constexpr int STAGE_BYTES = stage_bytes<BN, CTAS>();
     constexpr int BNL = BN / CTAS;     // rows of the B tile staged by this CTA
     constexpr int TILE_M = BM * CTAS;  // rows of the output tile of the CTA (pair)
@@ -250,6 +258,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         tc::prefetch_tmap(&tmap_a);
         tc::prefetch_tmap(&tmap_b);
         if (use_reduce) tc::prefetch_tmap(&tmap_r);
+        if (DUAL) tc::prefetch_tmap(&tmap_r2);
 #pragma unroll
         for (int s = 0; s < STAGES; ++s) { tc::mbar_init(&full_bar[s], 1); tc::mbar_init(&empty_bar[s], 1); }
 #pragma unroll
@@ -323,7 +332,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         const int q = warp & 3;    // TMEM lane quarter this warp may access (hardware rule: warp id % 4)
         const int half = ew >> 2;  // which half of the tile's columns
         constexpr int HALF = BN / 2;
-        float* stage = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES) + ew * staging_floats_per_warp<MODE>();
+        float* stage = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES) + ew * staging_floats_per_warp<MODEX>();
         const HvEpilogue& e = epi.e;
         const bool reduce = MODE == HV_EPI_RESIDUAL && use_reduce;
         const bool tma_store = MODE != HV_EPI_RESIDUAL && use_reduce;  // tmap_r is then the bf16 OUTPUT map (box 64 x 32)
@@ -370,6 +379,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     tc::tmem_ld32(taddr + c + 32, hi);
                     epi_add_bias(epi, col0, N, lo);
                     epi_add_bias(epi, col0 + 32, N, hi);
+                    if (DUAL) epi_block_tma_store<1>(&tmap_r2, stage + 32 * 32, lane, row0, col0, lo, hi);  // pre-norm q / k (and v)
                     const float *w = nullptr, *b = nullptr;
                     if (col0 < e.q_cols) { w = e.qn_w; b = e.qn_b; }
                     else if (col0 < e.q_cols + e.k_cols) { w = e.kn_w; b = e.kn_b; }
@@ -389,7 +399,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         }
                     }
                     if (tma_store) {
-                        epi_block_tma_store(&tmap_r, stage, lane, row0, col0, lo, hi);
+                        epi_block_tma_store<DUAL ? 1 : 0>(&tmap_r, stage, lane, row0, col0, lo, hi);
                     } else {
                         epi_block_out<MODE>(epi, stage, lane, row0, M, col0, N, lo, 0, 0);
                         epi_block_out<MODE>(epi, stage, lane, row0, M, col0 + 32, N, hi, 0, 0);
@@ -405,11 +415,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     tc::tmem_ld32(taddr + c + 32, hi);
                     epi_add_bias(epi, col0, N, lo);
                     epi_add_bias(epi, col0 + 32, N, hi);
+                    if (DUAL) epi_block_tma_store<1>(&tmap_r2, stage + 32 * 32, lane, row0, col0, lo, hi);  // pre-GELU activations
                     if (MODE == HV_EPI_GELU) {
 #pragma unroll
                         for (int j = 0; j < 32; ++j) { lo[j] = gelu_tanh_fast(lo[j]); hi[j] = gelu_tanh_fast(hi[j]); }
                     }
-                    epi_block_tma_store(&tmap_r, stage, lane, row0, col0, lo, hi);
+                    epi_block_tma_store<DUAL ? 1 : 0>(&tmap_r, stage, lane, row0, col0, lo, hi);
                 }
             } else {
 #pragma unroll 1
@@ -564,8 +575,8 @@ int max_pairs() {
 }
 
 template <int BN, int MODE, int CTAS>
-int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, int use_reduce, int64_t M, int N, int K,
-           const HvEpiDev& d, cudaStream_t st) {
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, const CUtensorMap& tr2, int use_reduce, int64_t M, int N,
+           int K, const HvEpiDev& d, cudaStream_t st) {
     auto kern = gemm_tc_kernel<BN, MODE, CTAS>;
     static bool configured = false;
     if (!configured) {
@@ -576,7 +587,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, 
     if constexpr (CTAS == 1) {
         const int sms = hv_num_sms();
         const int grid = (int)(tiles < sms ? tiles : sms);
-        kern<<<grid, THREADS, smem_bytes<BN, MODE, CTAS>(), st>>>(ta, tb, tr, (long long)M, N, K, use_reduce, d);
+        kern<<<grid, THREADS, smem_bytes<BN, MODE, CTAS>(), st>>>(ta, tb, tr, tr2, (long long)M, N, K, use_reduce, d);
     } else {
         const int pairs = max_pairs<BN, MODE>();
         const int units = (int)(tiles < pairs ? tiles : pairs);
@@ -586,18 +597,19 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, 
         at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.gridDim = dim3(2 * units); cfg.blockDim = dim3(THREADS);
         cfg.dynamicSmemBytes = smem_bytes<BN, MODE, CTAS>(); cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
-        HV_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tr, (long long)M, N, K, use_reduce, d));
+        HV_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tr, tr2, (long long)M, N, K, use_reduce, d));
     }
     HV_LAUNCH_CHECK();
     return HV_OK;
 }
 
 template <int MODE>
-int launch_mode(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, int use_reduce, int64_t M, int N, int K,
-                const HvEpiDev& d, cudaStream_t st, int BN, int ctas) {
-    if (ctas == 2) return launch<256, MODE, 2>(ta, tb, tr, use_reduce, M, N, K, d, st);
-    if (BN == 256) return launch<256, MODE, 1>(ta, tb, tr, use_reduce, M, N, K, d, st);
-    return launch<128, MODE, 1>(ta, tb, tr, use_reduce, M, N, K, d, st);
+int launch_mode(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, const CUtensorMap& tr2, int use_reduce, int64_t M,
+                int N, int K, const HvEpiDev& d, cudaStream_t st, int BN, int ctas) {
+    if (ctas == 2) return launch<256, MODE, 2>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st);
+    if (BN == 256) return launch<256, MODE, 1>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st);
+    if constexpr ((MODE & MODE_DUAL) != 0) { hv_set_error("hv_linear_bf16: dual output needs BN = 256"); return HV_EINVAL; }
+    else return launch<128, MODE, 1>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st);
 }
 
 // HV_GEMM_CTAS=1 forces the single-CTA kernel, HV_GEMM_REDUCE=0 the read-modify-write residual epilogue (A/B testing)
@@ -648,10 +660,25 @@ extern "C" int hv_linear_bf16(const void* A, int64_t lda, const void* W, int64_t
         d.e.k_split = 1;
     }
     cudaStream_t st = hv_stream(stream);
+    if (d.e.out2) {
+        // second (pre-activation) output: fused into the TMA-store epilogue when that path applies, otherwise an extra
+        // plain-store launch of the same GEMM
+        const bool tma2 = use_reduce && d.e.mode != HV_EPI_RESIDUAL && d.vec_ok2;
+        if (tma2) {
+            CUtensorMap tr2;
+            if ((rc = hv_make_tmap_bf16(d.e.out2, M, N, d.e.ldo2, 32, &tr2)) != HV_OK) return rc;
+            if (d.e.mode == HV_EPI_GELU) return launch_mode<HV_EPI_GELU | MODE_DUAL>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st, BN, ctas);
+            return launch_mode<HV_EPI_QKNORM | MODE_DUAL>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st, BN, ctas);
+        }
+        HvEpilogue pre = *epi;
+        pre.mode = HV_EPI_STORE; pre.out = epi->out2; pre.ldo = epi->ldo2; pre.out2 = nullptr;
+        if ((rc = hv_linear_bf16(A, lda, W, ldw, M, N, K, &pre, stream)) != HV_OK) return rc;
+        d.e.out2 = nullptr;
+    }
     switch (d.e.mode) {
-        case HV_EPI_STORE: return launch_mode<HV_EPI_STORE>(ta, tb, tr, use_reduce, M, N, K, d, st, BN, ctas);
-        case HV_EPI_GELU: return launch_mode<HV_EPI_GELU>(ta, tb, tr, use_reduce, M, N, K, d, st, BN, ctas);
-        case HV_EPI_RESIDUAL: return launch_mode<HV_EPI_RESIDUAL>(ta, tb, tr, use_reduce, M, N, K, d, st, BN, ctas);
-        default: return launch_mode<HV_EPI_QKNORM>(ta, tb, tr, use_reduce, M, N, K, d, st, BN, ctas);
+        case HV_EPI_STORE: return launch_mode<HV_EPI_STORE>(ta, tb, tr, tr, use_reduce, M, N, K, d, st, BN, ctas);
+        case HV_EPI_GELU: return launch_mode<HV_EPI_GELU>(ta, tb, tr, tr, use_reduce, M, N, K, d, st, BN, ctas);
+        case HV_EPI_RESIDUAL: return launch_mode<HV_EPI_RESIDUAL>(ta, tb, tr, tr, use_reduce, M, N, K, d, st, BN, ctas);
+        default: return launch_mode<HV_EPI_QKNORM>(ta, tb, tr, tr, use_reduce, M, N, K, d, st, BN, ctas);
     }
 }

@@ -313,15 +313,20 @@ def rope_(q, k, batch, L, heads, head_dim, start_pos=0, base=10000.0):
 
 
 # ------------------------------------------------------------------ GEMM
-def epi_store(out, bias=None, gelu=False):
+def epi_store(out, bias=None, gelu=False, pre=None):
+    """pre: optional second output (GELU only) that receives acc + bias BEFORE the activation (training forward)"""
     e = HvEpilogue()
     e.mode = EPI_GELU if gelu else EPI_STORE
     e.out_dtype, e.out, e.ldo, e.bias = _dt(out), out.data_ptr(), out.stride(0), (bias.data_ptr() if bias is not None else None)
+    if pre is not None:
+        assert pre.dtype == out.dtype and pre.shape == out.shape and pre.stride(1) == 1
+        e.out2, e.ldo2 = pre.data_ptr(), pre.stride(0)
     return e
 
 
-def epi_qknorm(out, bias, qn_w, qn_b, kn_w, kn_b, q_cols, k_cols, eps=1e-6):
-    e = epi_store(out, bias)
+def epi_qknorm(out, bias, qn_w, qn_b, kn_w, kn_b, q_cols, k_cols, eps=1e-6, pre=None):
+    """pre: optional second output receiving the projections BEFORE the per-head LayerNorm (training forward)"""
+    e = epi_store(out, bias, pre=pre)
     e.mode = EPI_QKNORM
     e.qn_w = qn_w.data_ptr() if qn_w is not None else None
     e.qn_b = qn_b.data_ptr() if qn_b is not None else None

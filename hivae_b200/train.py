@@ -91,17 +91,15 @@ def block_train(tape, ctx, bp, rows, drows, geom, sink, pfx, tag, ada=None, dada
     if bp.kind == "cross":
         Mk = kv.shape[0]
         q_pre, q = sv("q_pre", (M, D)), sv("q", (M, D))
-        ops.linear(xn1, bp.wq, ops.epi_store(q_pre, bp.bq))
-        ops.linear(xn1, bp.wq, ops.epi_qknorm(q, bp.bq, bp.qn_w, bp.qn_b, None, None, D, 0))
+        ops.linear(xn1, bp.wq, ops.epi_qknorm(q, bp.bq, bp.qn_w, bp.qn_b, None, None, D, 0, pre=q_pre))
         kv_pre, kvn = sv("kv_pre", (Mk, 2 * D)), sv("kv", (Mk, 2 * D))
-        ops.linear(kv, bp.wkv, ops.epi_store(kv_pre, bp.bkv))
-        ops.linear(kv, bp.wkv, ops.epi_qknorm(kvn, bp.bkv, None, None, bp.kn_w, bp.kn_b, 0, D))
+        ops.linear(kv, bp.wkv, ops.epi_qknorm(kvn, bp.bkv, None, None, bp.kn_w, bp.kn_b, 0, D, pre=kv_pre))
         qv, kk, vv, k_pre = q, kvn[:, :D], kvn[:, D:], kv_pre[:, :D]
     else:
         Mk = M
         qkv_pre, qkv = sv("qkv_pre", (M, 3 * D)), sv("qkv", (M, 3 * D))
-        ops.linear(xn1, bp.wqkv, ops.epi_store(qkv_pre, bp.bqkv))
-        ops.linear(xn1, bp.wqkv, ops.epi_qknorm(qkv, bp.bqkv, bp.qn_w, bp.qn_b, bp.kn_w, bp.kn_b, D, D))
+        # ONE GEMM, two outputs: the normalised q / k (and v) for the attention, the pre-norm projections for the backward
+        ops.linear(xn1, bp.wqkv, ops.epi_qknorm(qkv, bp.bqkv, bp.qn_w, bp.qn_b, bp.kn_w, bp.kn_b, D, D, pre=qkv_pre))
         qv, kk, vv = qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:]
         q_pre, k_pre = qkv_pre[:, :D], qkv_pre[:, D:2 * D]
     att = sv("att", (M, D))
@@ -116,8 +114,7 @@ def block_train(tape, ctx, bp, rows, drows, geom, sink, pfx, tag, ada=None, dada
     x1 = ops.rows_gather(rows, sv("x1", (M, D), torch.float32))
     xn2 = ops.ln_modulate(rows, bp.n2w, bp.n2b, bp.eps, sv("xn2", (M, D)), ada, **c2)
     hpre, h = sv("hpre", (M, F)), sv("h", (M, F))
-    ops.linear(xn2, bp.w1, ops.epi_store(hpre, bp.b1))
-    ops.linear(xn2, bp.w1, ops.epi_store(h, bp.b1, gelu=True))
+    ops.linear(xn2, bp.w1, ops.epi_store(h, bp.b1, gelu=True, pre=hpre))   # GELU output + pre-GELU activations
     if gated:
         y2 = sv("y2", (M, D))
         ops.linear(h, bp.w2, ops.epi_store(y2, bp.b2))

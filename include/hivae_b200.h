@@ -260,6 +260,11 @@ typedef struct HvEpilogue {
      * reduce-adding its partial product into res (weight gradients: few output tiles, very long K).  0 / 1 = off.
      * Needs bias == gate == NULL; fp32 partials are added in arrival order. */
     int k_split;
+    /* modes GELU / QKNORM, optional second output (training forward): the pre-activation matrix acc + bias (before the GELU /
+     * before the per-head LayerNorm) in the same dtype as `out`, row stride ldo2; NULL = off.  One GEMM then yields both the
+     * activations the next layer consumes and what the backward needs (GELU', QK-norm backward). */
+    void* out2;
+    int64_t ldo2;
 } HvEpilogue;
 
 #define HV_EPI_STORE 0

@@ -280,3 +280,51 @@ def test_product_does_not_import_oracle():
             if f.endswith((".py", ".cu", ".cuh")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle|import_module\(.oracle", src, flags=re.M), f
+
+
+# ------------------------------------------------------------------ checkpoint compatibility
+def test_reference_format_checkpoint_loads(tmp_path):
+    """`checkpoint-<step>/model.safetensors` written by safetensors.torch.save_model — from the UNMODIFIED reference module
+    when /root/reference is present (build container), otherwise from a module with the same key contract — loads with
+    safetensors.torch.load_model into hivae_b200.AMDModel_New (amd_inference.py:99-109), and find_latest_checkpoint /
+    model_load_pretrain (model/utils.py:178-185, 217-237) behave like the reference's."""
+    import hivae_b200 as hv
+    from safetensors.torch import load_model, save_model
+    from oracle import ref_loader
+    cfg = configs.SMALL
+    if ref_loader.available():
+        ref = ref_loader.load()
+        torch.manual_seed(3)
+        src = ref.model_AMD.AMDModel_New(**cfg)
+    else:
+        torch.manual_seed(3)
+        src = hv.AMDModel_New(**cfg)
+    with torch.no_grad():
+        for p in src.parameters():
+            p.add_(0.01 * torch.randn_like(p))
+    for step in (500, 12000, 3000):
+        os.makedirs(tmp_path / ("checkpoint-%d" % step))
+    (tmp_path / "checkpoint-best").mkdir()
+    path = hv.find_latest_checkpoint(str(tmp_path))
+    assert path == str(tmp_path / "checkpoint-12000" / "model.safetensors")
+    save_model(src, path)
+    m = hv.AMDModel_New(**cfg)
+    missing, unexpected = load_model(m, path)
+    assert not missing and not unexpected
+    want = src.state_dict()
+    for k, v in m.state_dict().items():
+        assert torch.equal(v, want[k]), k
+    # filtered load: everything but the denoiser (the reference's keyword filter), strict=False
+    m2 = hv.AMDModel_New(**cfg)
+    before = {k: v.clone() for k, v in m2.state_dict().items()}
+    hv.model_load_pretrain(m2, path, not_load_keyword="diffusion_transformer")
+    for k, v in m2.state_dict().items():
+        assert torch.equal(v, before[k] if "diffusion_transformer" in k else want[k]), k
+    with pytest.raises(ValueError):
+        hv.find_latest_checkpoint(str(tmp_path / "checkpoint-best"))
+    # config round trip next to the weights (train_amd.py:175, amd_inference.py:99-107)
+    m.save_config(str(tmp_path))
+    m3 = hv.AMDModel_New.from_config(hv.AMDModel_New.load_config(str(tmp_path)))
+    assert sorted(m3.state_dict()) == sorted(want)
+    hv.frozen_model(m3, "camera_motion_encoder")
+    assert all(p.requires_grad != ("camera_motion_encoder" in k) for k, p in m3.named_parameters())
