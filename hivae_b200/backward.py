@@ -311,17 +311,27 @@ def linear_grads(ctx, dy, x, w, dw=None, db=None, need_dx=True, dx_accum=None, t
             ops.linear(dy, wt, ops.epi_store(dx))
     if dw is None and db is None:
         return dx
-    Mp = -(-M // 8) * 8 if cd == torch.bfloat16 else M
-    dyT = ctx.buf(tag + "_dyT", (N, Mp), cd)
+    # weight-gradient operands: the compute dtype of the layer — except for the small fp32 layers (patch embeds, heads) inside
+    # a bf16 context with many tokens, whose dW = dY^T X contracts over ALL tokens with a handful of output tiles: there the
+    # operands are rounded to bf16 and the contraction runs on the tensor cores (the reference's autocast runs these layers in
+    # bf16 as well)
+    wd = torch.bfloat16 if (cd == torch.float32 and ctx.dtype == torch.bfloat16 and M >= 2048 and dw is not None) else cd
+    if wd != cd:
+        dy_w = ops.convert(dy.contiguous(), ctx.buf(tag + "_dy16", (M, N), wd))
+        x_w = ops.convert(x.contiguous(), ctx.buf(tag + "_x16", (M, K), wd))
+    else:
+        dy_w, x_w = dy, x
+    Mp = -(-M // 8) * 8 if wd == torch.bfloat16 else M
+    dyT = ctx.buf(tag + "_dyT", (N, Mp), wd)
     if Mp != M:
         dyT[:, M:].zero_()
-    fused = cd == torch.bfloat16 and not ((M | N | dy.stride(0)) & 7) and not (dy.data_ptr() & 15) and db is not None
+    fused = wd == torch.bfloat16 and not ((M | N | dy_w.stride(0)) & 7) and not (dy_w.data_ptr() & 15) and db is not None and wd == cd
     if fused:
         ws = ctx.buf(tag + "_csw", (-(-M // 64) * N,), torch.float32)
         cs = ctx.buf(tag + "_cs", (N,), torch.float32)
-        _lib.check(_lib.load().hv_transpose2d_colsum(_p(dy), _p(dyT), M, N, dy.stride(0), Mp, _dt(dy), _p(ws), _p(cs), _stream()))
+        _lib.check(_lib.load().hv_transpose2d_colsum(_p(dy_w), _p(dyT), M, N, dy_w.stride(0), Mp, _dt(dy_w), _p(ws), _p(cs), _stream()))
     else:
-        transpose2d(dy, out=dyT)
+        transpose2d(dy_w, out=dyT)
         cs = colsum(dy) if db is not None else None
     if db is not None:
         dbs, o = (db if isinstance(db, (list, tuple)) else [db]), 0
@@ -329,17 +339,17 @@ def linear_grads(ctx, dy, x, w, dw=None, db=None, need_dx=True, dx_accum=None, t
             ops.axpy(1.0, cs[o:o + t.numel()], t.view(-1))
             o += t.numel()
     if dw is not None:
-        xT = ctx.buf(tag + "_xT", (K, Mp), cd)
+        xT = ctx.buf(tag + "_xT", (K, Mp), wd)
         if Mp != M:
             xT[:, M:].zero_()
-        transpose2d(x, out=xT)
+        transpose2d(x_w, out=xT)
         dws, o = (dw if isinstance(dw, (list, tuple)) else [dw]), 0
         for t in dws:
             n = t.shape[0]
             t2 = t.view(n, K)
             assert t2.dtype == torch.float32 and t2.is_contiguous()
             e = ops.epi_residual(ops.Rows(t2.view(1, n, K), 0, n))
-            if cd == torch.bfloat16:
+            if wd == torch.bfloat16:
                 tiles = -(-n // 256) * -(-K // 256)
                 e.k_split = splitk if splitk is not None else max(1, min(16, 74 // tiles, Mp // 512))
             ops.linear(dyT[o:o + n], xT, e)

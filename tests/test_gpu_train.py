@@ -266,3 +266,46 @@ def test_block_forward_after_adamw_step_uses_new_weights(dev):
         q.grad = torch.ones_like(q)
     opt.step()
     assert not torch.equal(before, p.detach())
+
+
+def test_dual_output_epilogue_matches_two_launches(dev):
+    """the training forward's dual-output GEMM epilogue (pre-activation + activation from ONE tcgen05 GEMM) is bit-identical
+    to the two separate launches it replaces; bf16 TMA-store path, the fallback shapes and the fp32 SIMT path"""
+    from hivae_b200 import ops
+    gen = torch.Generator().manual_seed(5)
+    for dtype, M, D in ((torch.bfloat16, 1000, 256), (torch.bfloat16, 300, 128), (torch.float32, 130, 128)):
+        x = torch.randn(M, D, generator=gen).to(dev).to(dtype)
+        w = (torch.randn(3 * D, D, generator=gen) / D ** 0.5).to(dev).to(dtype)
+        b = torch.randn(3 * D, generator=gen).to(dev)
+        nw, nb = (1 + 0.1 * torch.randn(64, generator=gen)).to(dev), (0.1 * torch.randn(64, generator=gen)).to(dev)
+        new = lambda: torch.empty(M, 3 * D, dtype=dtype, device=dev)
+        a1, p1, a2, p2 = new(), new(), new(), new()
+        ops.linear(x, w, ops.epi_qknorm(a1, b, nw, nb, nw, nb, D, D, pre=p1))
+        ops.linear(x, w, ops.epi_qknorm(a2, b, nw, nb, nw, nb, D, D))
+        ops.linear(x, w, ops.epi_store(p2, b))
+        assert torch.equal(a1, a2) and torch.equal(p1, p2), ("qknorm", dtype, M)
+        ops.linear(x, w, ops.epi_store(a1, b, gelu=True, pre=p1))
+        ops.linear(x, w, ops.epi_store(a2, b, gelu=True))
+        assert torch.equal(a1, a2) and torch.equal(p1, p2), ("gelu", dtype, M)
+
+
+def test_pipeline_windowed_sample(dev):
+    """AMDPipeLine_single on VAE latents (model/pipeline.py:647-751): one window, and a 33-frame latent sequence cut into two
+    windows reconstructed in one batched sample call == the oracle's sample of each window"""
+    import hivae_b200 as hv
+    m, sd = _small(dev, torch.float32)
+    pipe = hv.AMDPipeLine_single(None, m, window=16, device=dev)
+    z = synth.synth_clip_latents(1, frames=33, seed=4)[0]
+    z0 = torch.randn(32, 4, 32, 32, generator=torch.Generator().manual_seed(6))
+    orig = m.scheduler.get_train_tuple
+    m.scheduler.get_train_tuple = lambda z0_=None, z1=None, time_step=None: orig(z0=z0[:z1.shape[0]].to(z1.device), z1=z1, time_step=time_step)
+    out = pipe.sample_long(z, video_sample_step=3)
+    assert out.shape == (1, 33, 4, 32, 32) and torch.equal(out[0, 0].cpu(), z[0])
+    orc = O.AMDOracle(sd, configs.SMALL["enc_nhead"], configs.SMALL["diffusion_attn_num_heads"], 16, 2, configs.SMALL["motion_token_num"])
+    for k in range(2):
+        video = z[1 + 16 * k:17 + 16 * k].unsqueeze(0)
+        ref = z[16 * k:16 * k + 1].unsqueeze(0).repeat(1, 16, 1, 1, 1)
+        _, ozt, _ = orc.sample(video, ref, sample_step=3, z0=z0[16 * k:16 * k + 16])
+        assert _err(out[0, 1 + 16 * k:17 + 16 * k], ozt.reshape(16, 4, 32, 32))[0] <= 1e-4, k
+    one = pipe.sample_latents(z[:17], video_sample_step=3)
+    assert _err(one[0, 1:], out[0, 1:17])[0] <= 1e-5
