@@ -293,8 +293,9 @@ class TrainStep:
         self.reducer = GradAllReducer(self.arena, bucket_mb=bucket_mb, group=group) if use_dist else None
         self.last = {}
 
-    def step(self, video, ref_img, time_step=None, noise=None):
-        """returns {'loss', 'diff_loss', 'rec_loss', 'grad_norm'} as 0-dim device tensors (no host synchronisation)"""
+    def forward_backward(self, video, ref_img, time_step=None, noise=None):
+        """forward + backward + gradient all-reduce; leaves the (averaged, unclipped) gradients in the arena and returns
+        (loss, rec_loss, grad_scale) — grad_scale is what clip / AdamW still have to apply (1.0 unless gloo summed)"""
         from . import train
         from .backward import mse_backward
         m = self.model
@@ -316,6 +317,11 @@ class TrainStep:
             self.reducer.begin(self.params)
         run.backward(mse_backward(pre, vel), self.reducer.done if self.reducer is not None else None)
         scale = self.reducer.finish() if self.reducer is not None else 1.0
+        return loss, rec, scale
+
+    def step(self, video, ref_img, time_step=None, noise=None):
+        """returns {'loss', 'diff_loss', 'rec_loss', 'grad_norm'} as 0-dim device tensors (no host synchronisation)"""
+        loss, rec, scale = self.forward_backward(video, ref_img, time_step, noise)
         norm = clip_grad_norm_(self.arena, self.max_grad_norm, grad_scale=scale)
         self.opt.step(grad_scale=scale)
         self.last = {"loss": loss, "diff_loss": loss, "rec_loss": rec, "grad_norm": norm}

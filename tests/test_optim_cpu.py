@@ -75,3 +75,55 @@ def test_gloo_world2_gradient_all_reduce_mean():
     for _rank, scale, mean in res:
         assert scale == 0.5                      # gloo: SUM, the 1/world is folded into the clip / AdamW kernels
         assert mean == [1.5, 3.0, 4.5, 6.0]      # mean over ranks of (rank+1)*(i+1)
+
+
+def _worker_overlap(rank, world, port, q):
+    """the backward reports finished parameters out of arena order; buckets go out as soon as their last parameter is done"""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    ps = _params(1)
+    names = {"p%d" % i: p for i, p in enumerate(ps)}
+    arena = optim.FlatArena(ps)
+    red = optim.GradAllReducer(arena, bucket_mb=4e-5)  # ~10 elements per bucket: parameters straddle buckets
+    issued_after = []
+    red.begin(names)
+    for name in ("p3", "p1", "p0", "p2"):        # completion order != arena order
+        i = int(name[1])
+        names[name].grad.fill_(float(rank + 1) * (i + 1))
+        red.done([name])
+        issued_after.append(sum(red._issued))
+    scale = red.finish()
+    mean = [float((p.grad * scale).flatten()[0]) for p in arena.params]
+    q.put((rank, scale, mean, issued_after, len(red.buckets), all(red._issued)))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gloo_world2_bucketed_all_reduce_overlapped_with_backward():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_overlap, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for _rank, scale, mean, issued_after, nb, all_issued in res:
+        assert scale == 0.5 and mean == [1.5, 3.0, 4.5, 6.0] and all_issued
+        assert issued_after == sorted(issued_after) and issued_after[-1] == nb   # every bucket exactly once, none before its parameters
+        assert issued_after[0] < nb                                              # ... and not all at the end
+
+
+def test_backward_order_covers_every_parameter_once():
+    import hivae_b200 as hv
+    from hivae_b200 import configs
+    m = hv.AMDModel_New(**configs.SMALL)
+    order = optim.backward_order(m)
+    assert sorted(k for k, _ in order) == sorted(k for k, _ in m.named_parameters())
+    names = [k for k, _ in order]
+    # the denoiser head completes first, layer i + 1 before layer i, the encoders after the denoiser
+    assert names[0].startswith("diffusion_transformer.") and ("proj_out" in names[0] or "norm_" in names[0])
+    assert names.index("diffusion_transformer.spatial_blocks.1.ff.net.2.weight") < names.index("diffusion_transformer.spatial_blocks.0.ff.net.2.weight")
+    assert max(i for i, k in enumerate(names) if k.startswith("diffusion_transformer.")) < min(i for i, k in enumerate(names) if "motion_encoder." in k)
