@@ -279,10 +279,19 @@ def _train_leg(torch, dist, dev, m, rank, world, timed, steps=3, warmup=2):
             red.finish()
         only_allreduce()
         ms_ar = timed(only_allreduce, steps) / steps
+        modes = {}
+        for name, frac in (("fine_grained_ddp_style", 0.0), ("all_at_the_end", 1.0)):
+            red.issue_after = frac
+            fn()
+            modes[name] = round(timed(fn, steps) / steps - ms_local, 3)
+        red.issue_after = 0.9
         busbw = 2.0 * (world - 1) / world * step.arena.numel * 4 / (ms_ar * 1e6)
         rec.update(allreduce_ms=round(ms_ar, 3), allreduce_exposed_ms=round(max(ms - ms_local, 0.0), 3),
                    ms_per_step_without_collective=round(ms_local, 2), allreduce_busbw_gbs=round(busbw, 1),
-                   buckets=len(red.buckets))
+                   buckets=len(red.buckets),
+                   schedule="coarse: the denoiser's buckets (first 90 %) go out when its backward is done and overlap the "
+                            "encoders' backward, the rest at the end",
+                   allreduce_exposed_ms_other_schedules=modes)
     return rec if rank == 0 else None
 
 

@@ -524,6 +524,16 @@ int launch_bwd(const BwdArgs& a, int64_t seqs, cudaStream_t st) {
 
 }  // namespace
 
+int hv_attention_bwd_tc_bf16(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
+                             const void* o, long long ldo, const void* dout, long long lddo, void* dq, long long lddq,
+                             void* dk, long long lddk, void* dv, long long lddv, long long seqs, int heads, int Lq, int Lkv,
+                             const HvSeqMap& qm, const HvSeqMap& km, float scale, float* stats, cudaStream_t st);  // attn_bwd_tc.cu
+
+int hv_attention_small_bwd_bf16(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
+                                const void* o, long long ldo, const void* dout, long long lddo, void* dq, long long lddq,
+                                void* dk, long long lddk, void* dv, long long lddv, long long seqs, int heads, int Lq, int Lkv,
+                                const HvSeqMap& qm, const HvSeqMap& km, float scale, cudaStream_t st);  // attn_small_bwd.cu
+
 // Gradients of out = softmax(q k^T * scale) v for head_dim 64 (no mask).  All matrices are (rows, heads*64) with their own
 // leading dimension, one dtype (HV_F32 / HV_BF16); `stats` = seqs * heads * Lq * 2 floats of workspace.
 extern "C" int hv_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
@@ -538,6 +548,14 @@ extern "C" int hv_attention_bwd(const void* q, int64_t ldq, const void* k, int64
     if (seqs == 0) return HV_OK;
     BwdArgs a{q, k, v, out, dout, dq, dk, dv, ldq, ldk, ldv, ldo, lddo, lddq, lddk, lddv, heads, Lq, Lkv, *qmap, *kvmap, scale, stats};
     if (dtype == HV_F32) return launch_bwd<float>(a, seqs, hv_stream(stream));
-    const int rc = launch_bwd_mma(a, seqs, hv_stream(stream));  // bf16: tensor-core kernels unless shape / alignment forbid
+    // bf16: tcgen05 / TMEM kernels (attn_bwd_tc.cu) for dense sequences of 16..288 tokens, then the warp-level tensor-core
+    // kernels, then SIMT
+    const int rs = hv_attention_small_bwd_bf16(q, ldq, k, ldk, v, ldv, out, ldo, dout, lddo, dq, lddq, dk, lddk, dv, lddv, seqs, heads, Lq, Lkv,
+                                               *qmap, *kvmap, scale, hv_stream(stream));  // L <= 16: one warp per (sequence, head)
+    if (rs != 0) return rs < 0 ? rs : HV_OK;
+    const int rt = hv_attention_bwd_tc_bf16(q, ldq, k, ldk, v, ldv, out, ldo, dout, lddo, dq, lddq, dk, lddk, dv, lddv, seqs, heads, Lq, Lkv,
+                                            *qmap, *kvmap, scale, stats, hv_stream(stream));
+    if (rt != 0) return rt < 0 ? rt : HV_OK;
+    const int rc = launch_bwd_mma(a, seqs, hv_stream(stream));  // shape / alignment outside the tcgen05 kernels
     return rc == 1 ? launch_bwd<__nv_bfloat16>(a, seqs, hv_stream(stream)) : rc;
 }

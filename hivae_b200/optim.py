@@ -156,9 +156,15 @@ class GradAllReducer:
     whatever still runs on the compute stream; NCCL's AVG does the 1/world (gloo: SUM, 1/world folded into
     the clip / AdamW kernels through `grad_scale`)."""
 
-    def __init__(self, arena, bucket_mb=256, group=None):
+    def __init__(self, arena, bucket_mb=256, group=None, issue_after=0.0):
+        """issue_after: fraction of the buckets that must be complete before the first one is issued during the backward
+        (0 = every bucket as soon as it completes, DDP style; 1 = all at the end).  The compute kernels of this package are
+        persistent, one CTA (pair) per SM: an NCCL kernel that holds SMs while they run delays whole waves of tiles, so
+        on B200 a coarse schedule — everything of the denoiser (93 % of the bytes) once its backward is done, overlapped with
+        the encoders' backward — exposes less than the fine-grained one (measured: profiles/r02_*_bench_n2.json)."""
         import torch.distributed as dist
         self.dist, self.arena, self.group = dist, arena, group
+        self.issue_after = issue_after
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         n = max(1, int(bucket_mb * (1 << 20) // 4))
         self._bucket_elems = n
@@ -191,8 +197,11 @@ class GradAllReducer:
         for name in names:
             for b in self._bucket_of.pop(name, ()):
                 self._pending[b] -= 1
-                if self._pending[b] == 0 and not self._issued[b]:
-                    self._issue(b)
+        ready = [b for b in range(len(self.buckets)) if self._pending[b] == 0 and not self._issued[b]]
+        done = sum(1 for b in range(len(self.buckets)) if self._pending[b] == 0)
+        if ready and done >= self.issue_after * len(self.buckets):
+            for b in ready:
+                self._issue(b)
 
     def _issue(self, b):
         self._issued[b] = True
@@ -279,7 +288,7 @@ class TrainStep:
     (`--frozen_name`, train_amd.py:226-233)."""
 
     def __init__(self, model, lr=1e-4, max_grad_norm=1.0, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, bucket_mb=128,
-                 group=None, distributed=None):
+                 group=None, distributed=None, issue_after=0.9):
         import torch.distributed as dist
         self.model = model
         named = [(k, p) for k, p in backward_order(model) if p.requires_grad]
@@ -290,7 +299,7 @@ class TrainStep:
         self.sink = {k: p.grad for k, p in named}
         self.params = dict(named)
         use_dist = dist.is_initialized() if distributed is None else distributed
-        self.reducer = GradAllReducer(self.arena, bucket_mb=bucket_mb, group=group) if use_dist else None
+        self.reducer = GradAllReducer(self.arena, bucket_mb=bucket_mb, group=group, issue_after=issue_after) if use_dist else None
         self.last = {}
 
     def forward_backward(self, video, ref_img, time_step=None, noise=None):

@@ -84,7 +84,7 @@ def _worker_overlap(rank, world, port, q):
     ps = _params(1)
     names = {"p%d" % i: p for i, p in enumerate(ps)}
     arena = optim.FlatArena(ps)
-    red = optim.GradAllReducer(arena, bucket_mb=4e-5)  # ~10 elements per bucket: parameters straddle buckets
+    red = optim.GradAllReducer(arena, bucket_mb=4e-5, issue_after=0.0)  # ~10 elements per bucket: parameters straddle buckets
     issued_after = []
     red.begin(names)
     for name in ("p3", "p1", "p0", "p2"):        # completion order != arena order
