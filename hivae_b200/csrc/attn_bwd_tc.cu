@@ -10,15 +10,21 @@
 //       key half)) take the row max, then P~ = exp2(S c - max c) which they KEEP IN REGISTERS as packed bf16 (72 registers) —
 //       so that dP = dO V^T can overwrite the very same TMEM columns; dS~ = P~ (dP - D) -> bf16 -> shared memory (K-major,
 //       128 B swizzle) -> dQ~ = dS~ K with K as an MN-major operand (no transpose) -> dQ = dQ~ * scale / rowsum.
-//       Also writes (log2-sum-exp, D) per query row for the second kernel.
+//       Also writes the log2-sum-exp per query row for the second kernel.  D comes from a small streaming pre-kernel
+//       (one coalesced pass over O and dO; the row-scattered loads it replaces cost 4300 of 17000 cycles per tile).
+//       Software pipeline: when dS~(T) is staged the MMA warp issues S(T+1) BEFORE dQ(T), and the compute warps read dQ(T)
+//       back only after their pass 2 of tile T+1, so they never wait for the (slow, N = 64) dQ product.
 //   dkv kernel, one 128-KEY tile at a time:  S^T = K_t Q^T (keys on the TMEM lanes, <= 288 query columns),
 //       P^T = exp2(S^T c - lse_q) exact (lse from the dq kernel), kept in registers AND staged to shared memory,
 //       dV_t = P^T dO (dO MN-major);  dP^T = V_t dO^T overwrites S^T;  dS^T = P^T (dP^T - D_q) scale -> the same staging
-//       buffer once the dV MMA has retired -> dK_t = dS^T Q (Q MN-major).
+//       buffer once the dV MMA has retired (dS^T is formed in place in the P^T registers while that MMA runs) ->
+//       dK_t = dS^T Q (Q MN-major).  Same pipeline: S^T(t+1) is issued before dK_t, the accumulators of tile t are read
+//       back after pass 2 of tile t+1.
 // No atomics anywhere: every output element is produced by exactly one CTA (bit-reproducible).
 //
-// Warp roles (320 threads): warps 0..7 compute (TMEM lane quarter = warp % 4, column half = warp / 4), warp 8 = MMA issuer +
-// TMEM owner, warp 9 = TMA producer.  CTAs are persistent over (sequence, head) pairs.
+// Warp roles (384 threads): warps 0..7 compute (TMEM lane quarter = warp % 4, column half = warp / 4), warp 8 = MMA issuer +
+// TMEM owner, warp 9 = TMA producer, warps 10-11 idle (they complete the third warpgroup: setmaxnreg moves registers from
+// it to the compute warpgroups, 216 per compute thread — P lives in 72 of them).  CTAs are persistent over (sequence, head) pairs.
 #include <cuda.h>
 #include <cstdlib>
 #include "attn.cuh"
@@ -28,7 +34,7 @@ int hv_make_tmap_bf16(const void* ptr, long long rows, int K, long long ld, int 
 
 namespace {
 
-constexpr int QT = 128, HD = 64, LMAX = 288, THREADS = 320;
+constexpr int QT = 128, HD = 64, LMAX = 288, THREADS = 384;  // 12 warps = 3 warpgroups (setmaxnreg works per warpgroup)
 constexpr int ACC_COL = 0, S_COL = 128;  // TMEM: accumulators (dQ | dV, dK) in [0, 128), S / dP in [128, 416)
 constexpr uint32_t TMEM_COLS = 512;
 constexpr int TBYTES = QT * 128;         // one 128-row x 64-column bf16 tile
@@ -46,6 +52,58 @@ struct BwdTc {
 
 // cycles since the previous tick of (warp 0, lane 0) -> counter `phase` of this CTA (only when profiling is on)
 #define BWD_TICK(phase) do { if (prof) { const long long t_ = clock64(); a.dbg[(KERNEL_ID * 148 + (blockIdx.x % 148)) * 16 + (phase)] += (unsigned long long)(t_ - tk0); tk0 = t_; } } while (0)
+
+__device__ __forceinline__ void regs_compute() { asm volatile("setmaxnreg.inc.sync.aligned.u32 216;"); }
+__device__ __forceinline__ void regs_service() { asm volatile("setmaxnreg.dec.sync.aligned.u32 56;"); }
+
+__device__ __forceinline__ void ld32_issue(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+// issues the tcgen05.ld of columns [c, c + 32) (or [c, c + 16) when only 16 are left) and waits for it
+__device__ __forceinline__ void ld_cols(uint32_t taddr, bool full32, uint32_t (&r)[32]) {
+    if (full32) {
+        ld32_issue(taddr, r);
+    } else {
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+            : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+              "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+            : "r"(taddr)
+            : "memory");
+    }
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void ld16_issue(uint32_t taddr, uint32_t (&r)[16]);
+__device__ __forceinline__ void ld16_wait(uint32_t (&r)[16]);
+// Walks this thread's TMEM columns [c_begin, c_end) in 16-column chunks; the load of chunk k + 1 is in flight while f(k, c,
+// values) works on chunk k.  TMEM -> register bandwidth is 64 B/clk/SM (one pass over a 128 x 288 fp32 tile = 2300 clk), so a
+// pass is as fast as the hardware allows only when its arithmetic hides under the loads; the 32 extra live registers are
+// what setmaxnreg pays for.  Fully unrolled: k is a compile-time constant inside f (register arrays are indexed statically).
+template <typename F>
+__device__ __forceinline__ void for_chunks(uint32_t s_addr, int c_begin, int c_end, F&& f) {
+    uint32_t buf[2][16];
+    ld16_issue(s_addr + c_begin, buf[0]);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+        const int c = c_begin + 16 * k;
+        if (c < c_end) {  // warp-uniform
+            ld16_wait(buf[k & 1]);
+            if (c + 16 < c_end) ld16_issue(s_addr + c + 16, buf[(k + 1) & 1]);
+            f(k, c, buf[k & 1]);
+        }
+    }
+}
 
 __device__ __forceinline__ void ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
     asm volatile(
@@ -74,6 +132,12 @@ __device__ __forceinline__ void stage16(uint8_t* base, int row, int c, const flo
     *reinterpret_cast<uint4*>(pc + (((jc + 1) ^ (row & 7)) << 4)) =
         make_uint4(hv_pack_bf16(v[8], v[9]), hv_pack_bf16(v[10], v[11]), hv_pack_bf16(v[12], v[13]), hv_pack_bf16(v[14], v[15]));
 }
+__device__ __forceinline__ void stage16_packed(uint8_t* base, int row, int c, const uint4 lo, const uint4 hi) {  // 2 x 8 bf16
+    uint8_t* pc = base + (c >> 6) * TBYTES + (row >> 3) * 1024 + (row & 7) * 128;
+    const int jc = (c & 63) >> 3;
+    *reinterpret_cast<uint4*>(pc + ((jc ^ (row & 7)) << 4)) = lo;
+    *reinterpret_cast<uint4*>(pc + (((jc + 1) ^ (row & 7)) << 4)) = hi;
+}
 __device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
 
@@ -101,9 +165,29 @@ __device__ __forceinline__ void issue_pv_like(uint32_t d_tmem, const uint8_t* a_
     }
 }
 
-// ------------------------------------------------------------------------------------------------ dQ (+ stats)
-// PIPE: keep the next 16-column TMEM load in flight while the current one is processed (32 more live registers)
-template <bool PIPE>
+// ------------------------------------------------------------------------------------------------ D = rowsum(dO o O)
+// one thread per (sequence, query row, head), heads fastest: adjacent threads read adjacent 128-byte head slices
+__global__ void __launch_bounds__(256) attn_bwd_delta_kernel(const __nv_bfloat16* __restrict__ o, long long ldo,
+                                                             const __nv_bfloat16* __restrict__ dout, long long lddo, float* __restrict__ stats,
+                                                             long long seqs, int heads, int Lq, long long q_sa) {
+    const long long idx = blockIdx.x * 256ll + threadIdx.x;
+    if (idx >= seqs * Lq * heads) return;
+    const int head = (int)(idx % heads);
+    const long long t = idx / heads, seq = t / Lq;
+    const int row = (int)(t - seq * Lq);
+    const uint4* po = reinterpret_cast<const uint4*>(o + (seq * q_sa + row) * ldo + head * HD);
+    const uint4* pd = reinterpret_cast<const uint4*>(dout + (seq * q_sa + row) * lddo + head * HD);
+    float d = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const uint4 x = __ldg(po + j), y = __ldg(pd + j);
+        d += bf_lo(x.x) * bf_lo(y.x) + bf_hi(x.x) * bf_hi(y.x) + bf_lo(x.y) * bf_lo(y.y) + bf_hi(x.y) * bf_hi(y.y)
+           + bf_lo(x.z) * bf_lo(y.z) + bf_hi(x.z) * bf_hi(y.z) + bf_lo(x.w) * bf_lo(y.w) + bf_hi(x.w) * bf_hi(y.w);
+    }
+    stats[(((seq * heads + head) * Lq) + row) * 2 + 1] = d;
+}
+
+// ------------------------------------------------------------------------------------------------ dQ (+ log-sum-exp)
 __global__ void __launch_bounds__(THREADS, 1)
 attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                       const __grid_constant__ CUtensorMap tv, const __grid_constant__ CUtensorMap tdo, const BwdTc a) {
@@ -136,8 +220,11 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
     tc::fence_after_sync();
     const uint32_t tmem_base = tmem_slot;
 
-    if (warp == 9) {
+    if (warp >= 10) {
+        regs_service();  // idle members of the service warpgroup
+    } else if (warp == 9) {
         // ===================================================== TMA producer
+        regs_service();
         if (lane == 0) {
             long long T = 0, it = 0;
             for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
@@ -162,25 +249,32 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
         }
     } else if (warp == 8) {
         // ===================================================== MMA issuer
+        regs_service();
         if (lane == 0) {
             long long T = 0, it = 0;
+            bool ahead = false;  // S of the current tile was already issued (before the previous tile's dQ)
+            auto issue_s = [&](long long Tn) {
+                tc::mbar_wait(&q_full, (uint32_t)(Tn & 1));
+                tc::fence_after_sync();
+                issue_s_like(tmem_base + S_COL, Qs, Ks, KP, HB);           // S = Q K^T
+                tc::umma_commit(&s_full);
+                tc::umma_commit(&q_free);
+            };
             for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
                 tc::mbar_wait(&kv_full, (uint32_t)(it & 1));
                 for (int i = 0; i < nq; ++i, ++T) {
                     const uint32_t ph = (uint32_t)(T & 1);
-                    tc::mbar_wait(&q_full, ph);
-                    tc::fence_after_sync();
-                    issue_s_like(tmem_base + S_COL, Qs, Ks, KP, HB);       // S = Q K^T  (the previous tile's dP was consumed: ds_full below)
-                    tc::umma_commit(&s_full);
-                    tc::umma_commit(&q_free);
+                    if (!ahead) issue_s(T);
                     tc::mbar_wait(&do_full, ph);
                     tc::mbar_wait(&s_free, ph);                            // P~ is in registers, S may be overwritten
                     tc::fence_after_sync();
                     issue_s_like(tmem_base + S_COL, dOs, Vs, KP, HB);      // dP = dO V^T
                     tc::umma_commit(&dp_full);
                     tc::umma_commit(&do_free);
-                    tc::mbar_wait(&ds_full, ph);                           // dS~ staged; the previous tile's dQ was read back
+                    tc::mbar_wait(&ds_full, ph);                           // dS~ staged, dP consumed; the previous dQ was read back
                     tc::fence_after_sync();
+                    ahead = i + 1 < nq;
+                    if (ahead) issue_s(T + 1);                             // next tile of the same item first: the compute warps need it first
                     issue_pv_like(tmem_base + ACC_COL, dSs, Ks, KP);       // dQ~ = dS~ K
                     tc::umma_commit(&dq_full);
                     if (i == nq - 1) tc::umma_commit(&kv_free);
@@ -189,11 +283,30 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
         }
     } else {
         // ===================================================== compute warps
+        regs_compute();
         const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
         const int c_begin = h ? HB : 0, c_end = h ? KP : HB;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
         const uint32_t s_addr = t_lane + S_COL;
         long long T = 0;
+        // deferred read-back of the previous tile's dQ
+        bool pend = false, pend_valid = false;
+        float pend_f = 0.f;
+        __nv_bfloat16* pend_dst = nullptr;
+        auto epilogue = [&]() {
+            tc::mbar_wait(&dq_full, (uint32_t)((T - 1) & 1));
+            tc::fence_after_sync();
+            float o[32];
+            tc::tmem_ld32(t_lane + ACC_COL + h * 32, o);
+            if (pend_valid) {
+                const float f = pend_f;
+#pragma unroll
+                for (int j = 0; j < 32; j += 8)
+                    *reinterpret_cast<uint4*>(pend_dst + j) = make_uint4(hv_pack_bf16(o[j] * f, o[j + 1] * f), hv_pack_bf16(o[j + 2] * f, o[j + 3] * f),
+                                                                         hv_pack_bf16(o[j + 4] * f, o[j + 5] * f), hv_pack_bf16(o[j + 6] * f, o[j + 7] * f));
+            }
+            tc::fence_before_sync();
+        };
         for (long long w = blockIdx.x; w < a.items; w += gridDim.x) {
             const long long seq = w / a.heads;
             const int head = (int)(w - seq * a.heads);
@@ -204,48 +317,25 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                 constexpr int KERNEL_ID = 0;
                 const bool prof = a.dbg != nullptr && threadIdx.x == 0;
                 long long tk0 = prof ? clock64() : 0;
-                // D = sum_d dO O of this thread's query row (both key halves compute it: 2 x 128 B per row)
-                float Dr = 0.f;
-                if (valid) {
-                    const uint4* po = reinterpret_cast<const uint4*>(a.o + (seq * a.q_sa + qr) * a.ldo + head * HD);
-                    const uint4* pd = reinterpret_cast<const uint4*>(a.dout + (seq * a.q_sa + qr) * a.lddo + head * HD);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const uint4 x = __ldg(po + j), y = __ldg(pd + j);
-                        Dr += bf_lo(x.x) * bf_lo(y.x) + bf_hi(x.x) * bf_hi(y.x) + bf_lo(x.y) * bf_lo(y.y) + bf_hi(x.y) * bf_hi(y.y)
-                            + bf_lo(x.z) * bf_lo(y.z) + bf_hi(x.z) * bf_hi(y.z) + bf_lo(x.w) * bf_lo(y.w) + bf_hi(x.w) * bf_hi(y.w);
-                    }
-                }
-                BWD_TICK(0);   // D loads
+                float* const st = a.stats + (w * a.Lq + (valid ? qr : 0)) * 2;
+                const float Dr = valid ? __ldg(st + 1) : 0.f;  // from attn_bwd_delta_kernel
                 tc::mbar_wait(&s_full, ph);
                 tc::fence_after_sync();
                 BWD_TICK(1);   // wait S
                 // ---- pass 1: row maximum over this thread's key half
                 float mx = -INFINITY;
-                {
-                    uint32_t buf[2][16];
-                    if (PIPE) ld16_issue(s_addr + c_begin, buf[0]);
+                for_chunks(s_addr, c_begin, c_end, [&](int, int c, const uint32_t (&va)[16]) {
+                    if (c + 16 <= a.Lkv) {
+                        float m4[4];
 #pragma unroll
-                    for (int k = 0; k < 9; ++k) {
-                        const int c = c_begin + 16 * k;
-                        if (c < c_end) {  // warp-uniform; the next chunk is in flight while this one is reduced
-                            if (!PIPE) ld16_issue(s_addr + c, buf[k & 1]);
-                            ld16_wait(buf[k & 1]);
-                            if (PIPE && c + 16 < c_end) ld16_issue(s_addr + c + 16, buf[(k + 1) & 1]);
-                            const uint32_t (&va)[16] = buf[k & 1];
-                            if (c + 16 <= a.Lkv) {
-                                float m4[4];
+                        for (int j = 0; j < 4; ++j)
+                            m4[j] = fmaxf(fmaxf(__uint_as_float(va[j]), __uint_as_float(va[j + 4])), fmaxf(__uint_as_float(va[j + 8]), __uint_as_float(va[j + 12])));
+                        mx = fmaxf(mx, fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])));
+                    } else {
 #pragma unroll
-                                for (int j = 0; j < 4; ++j)
-                                    m4[j] = fmaxf(fmaxf(__uint_as_float(va[j]), __uint_as_float(va[j + 4])), fmaxf(__uint_as_float(va[j + 8]), __uint_as_float(va[j + 12])));
-                                mx = fmaxf(mx, fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])));
-                            } else {
-#pragma unroll
-                                for (int j = 0; j < 16; ++j) if (c + j < a.Lkv) mx = fmaxf(mx, __uint_as_float(va[j]));
-                            }
-                        }
+                        for (int j = 0; j < 16; ++j) if (c + j < a.Lkv) mx = fmaxf(mx, __uint_as_float(va[j]));
                     }
-                }
+                });
                 smax[h][row] = mx;
                 BWD_TICK(2);   // pass 1
                 tc::named_bar_sync(1, 256);
@@ -255,29 +345,16 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                 // ---- pass 2: P~ = exp2(S c - max c) -> registers (packed bf16), row sum
                 uint32_t preg[72];
                 float sum = 0.f;
-                {
-                    uint32_t buf[2][16];
-                    if (PIPE) ld16_issue(s_addr + c_begin, buf[0]);
+                for_chunks(s_addr, c_begin, c_end, [&](int k, int c, const uint32_t (&va)[16]) {
+                    float p[16];
 #pragma unroll
-                    for (int k = 0; k < 9; ++k) {
-                        const int c = c_begin + 16 * k;
-                        if (c < c_end) {  // warp-uniform
-                            if (!PIPE) ld16_issue(s_addr + c, buf[k & 1]);
-                            ld16_wait(buf[k & 1]);
-                            if (PIPE && c + 16 < c_end) ld16_issue(s_addr + c + 16, buf[(k + 1) & 1]);
-                            const uint32_t (&va)[16] = buf[k & 1];
-                            float p[16];
+                    for (int j = 0; j < 16; ++j)
+                        p[j] = (c + j < a.Lkv) ? tc::ex2_approx(fmaf(__uint_as_float(va[j]), a.sl2, -msc)) : 0.f;
 #pragma unroll
-                            for (int j = 0; j < 16; ++j)
-                                p[j] = (c + j < a.Lkv) ? tc::ex2_approx(fmaf(__uint_as_float(va[j]), a.sl2, -msc)) : 0.f;
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                preg[8 * k + j] = hv_pack_bf16(p[2 * j], p[2 * j + 1]);
-                                sum += bf_lo(preg[8 * k + j]) + bf_hi(preg[8 * k + j]);  // the sum of what the MMAs will see
-                            }
-                        }
-                    }
-                }
+                    for (int j = 0; j < 8; ++j) preg[8 * k + j] = hv_pack_bf16(p[2 * j], p[2 * j + 1]);
+                    sum += ((p[0] + p[1]) + (p[2] + p[3])) + ((p[4] + p[5]) + (p[6] + p[7]))
+                         + ((p[8] + p[9]) + (p[10] + p[11])) + ((p[12] + p[13]) + (p[14] + p[15]));
+                });
                 BWD_TICK(4);   // pass 2
                 tc::fence_before_sync();
                 __syncwarp();
@@ -285,62 +362,37 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                 ssum[h][row] = sum;
                 tc::named_bar_sync(1, 256);
                 const float l = sum + ssum[h ^ 1][row];
-                if (h == 0 && valid) {
-                    float2* st = reinterpret_cast<float2*>(a.stats) + (w * a.Lq + qr);
-                    *st = make_float2(msc + __log2f(l), Dr);
-                }
-                // ---- pass 3: dS~ = P~ (dP - D) -> bf16 -> shared memory
+                if (h == 0 && valid) st[0] = msc + __log2f(l);
                 BWD_TICK(5);   // sum exchange + stats
+                // ---- the previous tile's dQ (its MMA was issued behind this tile's S and is long done)
+                if (pend) epilogue();
+                BWD_TICK(9);   // epilogue (deferred)
+                // ---- pass 3: dS~ = P~ (dP - D) -> bf16 -> shared memory
                 tc::mbar_wait(&dp_full, ph);
                 tc::fence_after_sync();
                 BWD_TICK(6);   // wait dP
-                {
-                    uint32_t buf[2][16];
-                    if (PIPE) ld16_issue(s_addr + c_begin, buf[0]);
+                for_chunks(s_addr, c_begin, c_end, [&](int k, int c, const uint32_t (&va)[16]) {
+                    float ds[16];
 #pragma unroll
-                    for (int k = 0; k < 9; ++k) {
-                        const int c = c_begin + 16 * k;
-                        if (c < c_end) {
-                            if (!PIPE) ld16_issue(s_addr + c, buf[k & 1]);
-                            ld16_wait(buf[k & 1]);
-                            if (PIPE && c + 16 < c_end) ld16_issue(s_addr + c + 16, buf[(k + 1) & 1]);
-                            const uint32_t (&va)[16] = buf[k & 1];
-                            float ds[16];
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                ds[2 * j] = bf_lo(preg[8 * k + j]) * (__uint_as_float(va[2 * j]) - Dr);
-                                ds[2 * j + 1] = bf_hi(preg[8 * k + j]) * (__uint_as_float(va[2 * j + 1]) - Dr);
-                            }
-                            stage16(dSs, row, c, ds);
-                        }
+                    for (int j = 0; j < 8; ++j) {
+                        ds[2 * j] = bf_lo(preg[8 * k + j]) * (__uint_as_float(va[2 * j]) - Dr);
+                        ds[2 * j + 1] = bf_hi(preg[8 * k + j]) * (__uint_as_float(va[2 * j + 1]) - Dr);
                     }
-                }
+                    stage16(dSs, row, c, ds);
+                });
                 tc::fence_before_sync();
                 tc::fence_proxy_async();
                 __syncwarp();
                 BWD_TICK(7);   // pass 3
                 if (lane == 0) tc::mbar_arrive(&ds_full);
-                // ---- dQ = dQ~ * scale / rowsum
-                tc::mbar_wait(&dq_full, ph);
-                tc::fence_after_sync();
-                BWD_TICK(8);   // wait dQ
-                {
-                    float o[32];
-                    tc::tmem_ld32(t_lane + ACC_COL + h * 32, o);
-                    if (valid) {
-                        const float f = a.scale / l;
-                        __nv_bfloat16* dst = a.dq + (seq * a.q_sa + qr) * a.lddq + head * HD + h * 32;
-#pragma unroll
-                        for (int j = 0; j < 32; j += 8)
-                            *reinterpret_cast<uint4*>(dst + j) = make_uint4(hv_pack_bf16(o[j] * f, o[j + 1] * f), hv_pack_bf16(o[j + 2] * f, o[j + 3] * f),
-                                                                            hv_pack_bf16(o[j + 4] * f, o[j + 5] * f), hv_pack_bf16(o[j + 6] * f, o[j + 7] * f));
-                    }
-                }
-                tc::fence_before_sync();
-                BWD_TICK(9);   // epilogue
+                pend = true;
+                pend_valid = valid;
+                pend_f = a.scale / l;
+                pend_dst = a.dq + (seq * a.q_sa + qr) * a.lddq + head * HD + h * 32;
                 if (prof) a.dbg[(KERNEL_ID * 148 + (blockIdx.x % 148)) * 16 + 15] += 1;
             }
         }
+        if (pend) epilogue();
     }
     tc::fence_before_sync();
     __syncthreads();
@@ -351,14 +403,13 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
 }
 
 // ------------------------------------------------------------------------------------------------ dK, dV
-template <bool PIPE>
 __global__ void __launch_bounds__(THREADS, 1)
 attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                        const __grid_constant__ CUtensorMap tv, const __grid_constant__ CUtensorMap tdo, const BwdTc a) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t qdo_full, qdo_free, kt_full, kt_free, st_full, p_full, dpt_full, dv_done, ds_full, acc_full;
     __shared__ uint32_t tmem_slot;
-    __shared__ float sLse[LMAX], sD[LMAX];
+    __shared__ __align__(16) float sLse[LMAX], sD[LMAX];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int QP = a.QP, QP32 = (QP + 31) & ~31;
@@ -384,8 +435,11 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_cons
     tc::fence_after_sync();
     const uint32_t tmem_base = tmem_slot;
 
-    if (warp == 9) {
+    if (warp >= 10) {
+        regs_service();  // idle members of the service warpgroup
+    } else if (warp == 9) {
         // ===================================================== TMA producer
+        regs_service();
         if (lane == 0) {
             long long T = 0, it = 0;
             for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
@@ -410,25 +464,32 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_cons
         }
     } else if (warp == 8) {
         // ===================================================== MMA issuer
+        regs_service();
         if (lane == 0) {
             long long T = 0, it = 0;
+            bool ahead = false;
+            auto issue_st = [&](long long Tn) {
+                tc::mbar_wait(&kt_full, (uint32_t)(Tn & 1));
+                tc::fence_after_sync();
+                issue_s_like(tmem_base + S_COL, Kt, Qs, QP, HB);            // S^T = K_t Q^T
+                tc::umma_commit(&st_full);
+            };
             for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
                 tc::mbar_wait(&qdo_full, (uint32_t)(it & 1));
                 for (int t = 0; t < nk; ++t, ++T) {
                     const uint32_t ph = (uint32_t)(T & 1);
-                    tc::mbar_wait(&kt_full, ph);
-                    tc::fence_after_sync();
-                    issue_s_like(tmem_base + S_COL, Kt, Qs, QP, HB);        // S^T = K_t Q^T
-                    tc::umma_commit(&st_full);
+                    if (!ahead) issue_st(T);
                     tc::mbar_wait(&p_full, ph);                             // P^T in registers + staged; accumulators of the previous tile read back
                     tc::fence_after_sync();
                     issue_s_like(tmem_base + S_COL, Vt, dOs, QP, HB);       // dP^T = V_t dO^T over the S^T columns
                     tc::umma_commit(&dpt_full);
-                    tc::umma_commit(&kt_free);
+                    tc::umma_commit(&kt_free);                              // K_t / V_t retire: the producer prefetches the next key tile
                     issue_pv_like(tmem_base + ACC_COL, Ps, dOs, QP);        // dV_t = P^T dO
                     tc::umma_commit(&dv_done);
-                    tc::mbar_wait(&ds_full, ph);                            // dS^T staged (after dv_done)
+                    tc::mbar_wait(&ds_full, ph);                            // dS^T staged (after dv_done), dP^T consumed
                     tc::fence_after_sync();
+                    ahead = t + 1 < nk;
+                    if (ahead) issue_st(T + 1);
                     issue_pv_like(tmem_base + ACC_COL + HD, Ps, Qs, QP);    // dK_t = dS^T Q
                     tc::umma_commit(&acc_full);
                     if (t == nk - 1) tc::umma_commit(&qdo_free);
@@ -437,16 +498,36 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_cons
         }
     } else {
         // ===================================================== compute warps: thread = (key row, query half)
+        regs_compute();
         const int q = warp & 3, h = warp >> 2, row = q * 32 + lane;
         const int c_begin = h ? HB : 0, c_end = h ? QP : HB;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16);
         const uint32_t s_addr = t_lane + S_COL;
         long long T = 0;
+        bool pend = false, pend_valid = false;
+        __nv_bfloat16 *pend_v = nullptr, *pend_k = nullptr;
+        auto epilogue = [&]() {
+            tc::mbar_wait(&acc_full, (uint32_t)((T - 1) & 1));
+            tc::fence_after_sync();
+            float ov[32], ok[32];
+            tc::tmem_ld32(t_lane + ACC_COL + h * 32, ov);
+            tc::tmem_ld32(t_lane + ACC_COL + HD + h * 32, ok);
+            if (pend_valid) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 8) {
+                    *reinterpret_cast<uint4*>(pend_v + j) = make_uint4(hv_pack_bf16(ov[j], ov[j + 1]), hv_pack_bf16(ov[j + 2], ov[j + 3]),
+                                                                       hv_pack_bf16(ov[j + 4], ov[j + 5]), hv_pack_bf16(ov[j + 6], ov[j + 7]));
+                    *reinterpret_cast<uint4*>(pend_k + j) = make_uint4(hv_pack_bf16(ok[j], ok[j + 1]), hv_pack_bf16(ok[j + 2], ok[j + 3]),
+                                                                       hv_pack_bf16(ok[j + 4], ok[j + 5]), hv_pack_bf16(ok[j + 6], ok[j + 7]));
+                }
+            }
+            tc::fence_before_sync();
+        };
         for (long long w = blockIdx.x; w < a.items; w += gridDim.x) {
             const long long seq = w / a.heads;
             const int head = (int)(w - seq * a.heads);
-            // per-query statistics of the dq kernel -> shared memory (the previous item's readers are past their last use:
-            // every thread went through the acc_full wait of its last tile after reading them)
+            // per-query statistics -> shared memory (the previous item's readers are past their last use: every thread has
+            // arrived on ds_full of its last tile after reading them)
             tc::named_bar_sync(1, 256);
             for (int i = threadIdx.x; i < QP; i += 256) {
                 const float2 s = i < a.Lq ? reinterpret_cast<const float2*>(a.stats)[w * a.Lq + i] : make_float2(0.f, 0.f);
@@ -465,88 +546,78 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_cons
                 BWD_TICK(1);   // wait S^T
                 // ---- P^T = exp2(S^T c - lse_q) -> registers (packed bf16) and the staging buffer
                 uint32_t preg[72];
-                {
-                    uint32_t buf[2][16];
-                    if (PIPE) ld16_issue(s_addr + c_begin, buf[0]);
+                for_chunks(s_addr, c_begin, c_end, [&](int k, int c, const uint32_t (&va)[16]) {
+                    float ls[16];
 #pragma unroll
-                    for (int k = 0; k < 9; ++k) {
-                        const int c = c_begin + 16 * k;
-                        if (c < c_end) {  // warp-uniform
-                            if (!PIPE) ld16_issue(s_addr + c, buf[k & 1]);
-                            ld16_wait(buf[k & 1]);
-                            if (PIPE && c + 16 < c_end) ld16_issue(s_addr + c + 16, buf[(k + 1) & 1]);
-                            const uint32_t (&va)[16] = buf[k & 1];
-                            float p[16];
-#pragma unroll
-                            for (int j = 0; j < 16; ++j)
-                                p[j] = (c + j < a.Lq) ? tc::ex2_approx(fmaf(__uint_as_float(va[j]), a.sl2, -sLse[c + j])) : 0.f;
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) preg[8 * k + j] = hv_pack_bf16(p[2 * j], p[2 * j + 1]);
-                            stage16(Ps, row, c, p);
-                        }
+                    for (int j = 0; j < 4; ++j) {  // broadcast reads
+                        const float4 v4 = *reinterpret_cast<const float4*>(sLse + c + 4 * j);
+                        ls[4 * j] = v4.x; ls[4 * j + 1] = v4.y; ls[4 * j + 2] = v4.z; ls[4 * j + 3] = v4.w;
                     }
+                    float p[16];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        p[j] = (c + j < a.Lq) ? tc::ex2_approx(fmaf(__uint_as_float(va[j]), a.sl2, -ls[j])) : 0.f;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) preg[8 * k + j] = hv_pack_bf16(p[2 * j], p[2 * j + 1]);
+                });
+                BWD_TICK(4);   // pass 2 (registers)
+                // ---- the previous tile's dV / dK leave TMEM, and its dK MMA has finished READING the staging buffer, before this
+                // tile's P^T goes there and this tile's dV MMA (issued on p_full) overwrites the accumulators
+                if (pend) epilogue();
+                BWD_TICK(9);   // epilogue (deferred)
+#pragma unroll
+                for (int k = 0; k < 9; ++k) {
+                    const int c = c_begin + 16 * k;
+                    if (c < c_end)
+                        stage16_packed(Ps, row, c, make_uint4(preg[8 * k], preg[8 * k + 1], preg[8 * k + 2], preg[8 * k + 3]),
+                                       make_uint4(preg[8 * k + 4], preg[8 * k + 5], preg[8 * k + 6], preg[8 * k + 7]));
                 }
-                BWD_TICK(4);   // pass 2
+                BWD_TICK(3);   // stage P^T
                 tc::fence_before_sync();
                 tc::fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&p_full);
-                // ---- dS^T = P^T (dP^T - D_q) scale -> the same staging buffer, once the dV MMA has read P^T
+                // ---- dS^T = P^T (dP^T - D_q) scale, formed in place in the P^T registers while the dV MMA reads the staging buffer
                 tc::mbar_wait(&dpt_full, ph);
-                tc::mbar_wait(&dv_done, ph);
                 tc::fence_after_sync();
-                BWD_TICK(6);   // wait dP^T + dV
-                {
-                    uint32_t buf[2][16];
-                    if (PIPE) ld16_issue(s_addr + c_begin, buf[0]);
+                BWD_TICK(6);   // wait dP^T
+                for_chunks(s_addr, c_begin, c_end, [&](int k, int c, const uint32_t (&va)[16]) {
+                    float dd[16];
 #pragma unroll
-                    for (int k = 0; k < 9; ++k) {
-                        const int c = c_begin + 16 * k;
-                        if (c < c_end) {
-                            if (!PIPE) ld16_issue(s_addr + c, buf[k & 1]);
-                            ld16_wait(buf[k & 1]);
-                            if (PIPE && c + 16 < c_end) ld16_issue(s_addr + c + 16, buf[(k + 1) & 1]);
-                            const uint32_t (&va)[16] = buf[k & 1];
-                            float ds[16];
-#pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                ds[2 * j] = bf_lo(preg[8 * k + j]) * (__uint_as_float(va[2 * j]) - sD[c + 2 * j]) * a.scale;
-                                ds[2 * j + 1] = bf_hi(preg[8 * k + j]) * (__uint_as_float(va[2 * j + 1]) - sD[c + 2 * j + 1]) * a.scale;
-                            }
-                            stage16(Ps, row, c, ds);
-                        }
+                    for (int j = 0; j < 4; ++j) {
+                        const float4 v4 = *reinterpret_cast<const float4*>(sD + c + 4 * j);
+                        dd[4 * j] = v4.x; dd[4 * j + 1] = v4.y; dd[4 * j + 2] = v4.z; dd[4 * j + 3] = v4.w;
                     }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float d0 = bf_lo(preg[8 * k + j]) * (__uint_as_float(va[2 * j]) - dd[2 * j]) * a.scale;
+                        const float d1 = bf_hi(preg[8 * k + j]) * (__uint_as_float(va[2 * j + 1]) - dd[2 * j + 1]) * a.scale;
+                        preg[8 * k + j] = hv_pack_bf16(d0, d1);
+                    }
+                });
+                BWD_TICK(7);   // pass 3 (registers)
+                tc::mbar_wait(&dv_done, ph);   // the dV MMA has read P^T: the staging buffer may take dS^T
+                BWD_TICK(8);   // wait dV
+#pragma unroll
+                for (int k = 0; k < 9; ++k) {
+                    const int c = c_begin + 16 * k;
+                    if (c < c_end)
+                        stage16_packed(Ps, row, c, make_uint4(preg[8 * k], preg[8 * k + 1], preg[8 * k + 2], preg[8 * k + 3]),
+                                       make_uint4(preg[8 * k + 4], preg[8 * k + 5], preg[8 * k + 6], preg[8 * k + 7]));
                 }
                 tc::fence_before_sync();
                 tc::fence_proxy_async();
                 __syncwarp();
-                BWD_TICK(7);   // pass 3
                 if (lane == 0) tc::mbar_arrive(&ds_full);
-                // ---- dV_t, dK_t -> global
-                tc::mbar_wait(&acc_full, ph);
-                tc::fence_after_sync();
-                BWD_TICK(8);   // wait dK
-                {
-                    float ov[32], ok[32];
-                    tc::tmem_ld32(t_lane + ACC_COL + h * 32, ov);
-                    tc::tmem_ld32(t_lane + ACC_COL + HD + h * 32, ok);
-                    if (valid) {
-                        __nv_bfloat16* pv = a.dv + (seq * a.kv_sa + kr) * a.lddv + head * HD + h * 32;
-                        __nv_bfloat16* pk = a.dk + (seq * a.kv_sa + kr) * a.lddk + head * HD + h * 32;
-#pragma unroll
-                        for (int j = 0; j < 32; j += 8) {
-                            *reinterpret_cast<uint4*>(pv + j) = make_uint4(hv_pack_bf16(ov[j], ov[j + 1]), hv_pack_bf16(ov[j + 2], ov[j + 3]),
-                                                                           hv_pack_bf16(ov[j + 4], ov[j + 5]), hv_pack_bf16(ov[j + 6], ov[j + 7]));
-                            *reinterpret_cast<uint4*>(pk + j) = make_uint4(hv_pack_bf16(ok[j], ok[j + 1]), hv_pack_bf16(ok[j + 2], ok[j + 3]),
-                                                                           hv_pack_bf16(ok[j + 4], ok[j + 5]), hv_pack_bf16(ok[j + 6], ok[j + 7]));
-                        }
-                    }
-                }
-                tc::fence_before_sync();
-                BWD_TICK(9);   // epilogue
+                BWD_TICK(5);   // stage dS^T
+                pend = true;
+                pend_valid = valid;
+                pend_v = a.dv + (seq * a.kv_sa + kr) * a.lddv + head * HD + h * 32;
+                pend_k = a.dk + (seq * a.kv_sa + kr) * a.lddk + head * HD + h * 32;
                 if (prof) a.dbg[(KERNEL_ID * 148 + (blockIdx.x % 148)) * 16 + 15] += 1;
             }
         }
+        if (pend) epilogue();
     }
     tc::fence_before_sync();
     __syncthreads();
@@ -610,25 +681,17 @@ int hv_attention_bwd_tc_bf16(const void* q, long long ldq, const void* k, long l
     const int KP32 = (a.KP + 31) & ~31, QP32 = (a.QP + 31) & ~31;
     const int smem_dq = 2 * TBYTES + 2 * KP32 * 128 + ((a.KP + 63) >> 6) * TBYTES + 1024;
     const int smem_dkv = 2 * QP32 * 128 + 2 * TBYTES + ((a.QP + 63) >> 6) * TBYTES + 1024;
-    static const int pipe = [] { const char* e = getenv("HV_ATTN_BWD_PIPE"); return e ? atoi(e) : 0; }();
     static int conf_dq = 0, conf_dkv = 0;
-    if (conf_dq < smem_dq) {
-        HV_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq));
-        HV_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq));
-        conf_dq = smem_dq;
-    }
-    if (conf_dkv < smem_dkv) {
-        HV_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dkv));
-        HV_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dkv));
-        conf_dkv = smem_dkv;
-    }
+    if (conf_dq < smem_dq) { HV_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq)); conf_dq = smem_dq; }
+    if (conf_dkv < smem_dkv) { HV_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dkv)); conf_dkv = smem_dkv; }
     const int sms = hv_num_sms();
     const int grid = (int)(a.items < sms ? a.items : sms);
-    if (pipe & 1) attn_bwd_dq_tc_kernel<true><<<grid, THREADS, smem_dq, st>>>(tq, tk, tv, tdo, a);
-    else attn_bwd_dq_tc_kernel<false><<<grid, THREADS, smem_dq, st>>>(tq, tk, tv, tdo, a);
+    const long long nd = seqs * Lq * heads;
+    attn_bwd_delta_kernel<<<(unsigned)((nd + 255) / 256), 256, 0, st>>>(a.o, ldo, a.dout, lddo, stats, seqs, heads, Lq, qm.sa);
     HV_LAUNCH_CHECK();
-    if (pipe & 2) attn_bwd_dkv_tc_kernel<true><<<grid, THREADS, smem_dkv, st>>>(tq, tk, tv, tdo, a);
-    else attn_bwd_dkv_tc_kernel<false><<<grid, THREADS, smem_dkv, st>>>(tq, tk, tv, tdo, a);
+    attn_bwd_dq_tc_kernel<<<grid, THREADS, smem_dq, st>>>(tq, tk, tv, tdo, a);
+    HV_LAUNCH_CHECK();
+    attn_bwd_dkv_tc_kernel<<<grid, THREADS, smem_dkv, st>>>(tq, tk, tv, tdo, a);
     HV_LAUNCH_CHECK();
     return 1;
 }

@@ -5,8 +5,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from hivae_b200 import _lib, engine, backward as B
 dev = torch.device("cuda:0")
-names = {0: ["D loads", "wait S", "pass 1 (max)", "max exchange", "pass 2 (exp -> regs)", "sum exchange + stats", "wait dP", "pass 3 (dS -> smem)", "wait dQ", "epilogue"],
-         1: ["-", "wait S^T", "-", "-", "pass 2 (exp -> regs + smem)", "-", "wait dP^T + dV", "pass 3 (dS^T -> smem)", "wait dK", "epilogue"]}
+names = {0: ["-", "wait S", "pass 1 (max)", "max exchange", "pass 2 (exp -> regs)", "sum exchange + stats", "wait dP", "pass 3 (dS -> smem)", "-", "deferred dQ read-back"],
+         1: ["-", "wait S^T", "-", "stage P^T", "pass 2 (exp -> regs)", "stage dS^T", "wait dP^T", "pass 3 (dS^T in regs)", "wait dV", "deferred dV / dK read-back"]}
 for frames, L in ((64, 274), (128, 264)):
     H, D = 16, 1024
     qkv = torch.randn(frames * L, 3 * D, device=dev).bfloat16()
