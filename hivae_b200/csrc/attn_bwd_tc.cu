@@ -124,19 +124,22 @@ __device__ __forceinline__ void ld16_wait(uint32_t (&r)[16]) {
 
 // 16 consecutive K-dimension elements (columns c .. c+15 of `row`) of a bf16 A operand staged as 64-column chunks of
 // [128 rows x 128 B] in the K-major SWIZZLE_128B layout
+// explicit st.shared (the staging pointers are carved out of the dynamic shared-memory block at run time; without the
+// state space the compiler emits generic ST.E)
+__device__ __forceinline__ void sts128(uint32_t saddr, const uint4 v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 __device__ __forceinline__ void stage16(uint8_t* base, int row, int c, const float (&v)[16]) {
-    uint8_t* pc = base + (c >> 6) * TBYTES + (row >> 3) * 1024 + (row & 7) * 128;
+    const uint32_t pc = tc::smem_u32(base) + (c >> 6) * TBYTES + (row >> 3) * 1024 + (row & 7) * 128;
     const int jc = (c & 63) >> 3;
-    *reinterpret_cast<uint4*>(pc + ((jc ^ (row & 7)) << 4)) =
-        make_uint4(hv_pack_bf16(v[0], v[1]), hv_pack_bf16(v[2], v[3]), hv_pack_bf16(v[4], v[5]), hv_pack_bf16(v[6], v[7]));
-    *reinterpret_cast<uint4*>(pc + (((jc + 1) ^ (row & 7)) << 4)) =
-        make_uint4(hv_pack_bf16(v[8], v[9]), hv_pack_bf16(v[10], v[11]), hv_pack_bf16(v[12], v[13]), hv_pack_bf16(v[14], v[15]));
+    sts128(pc + ((jc ^ (row & 7)) << 4), make_uint4(hv_pack_bf16(v[0], v[1]), hv_pack_bf16(v[2], v[3]), hv_pack_bf16(v[4], v[5]), hv_pack_bf16(v[6], v[7])));
+    sts128(pc + (((jc + 1) ^ (row & 7)) << 4), make_uint4(hv_pack_bf16(v[8], v[9]), hv_pack_bf16(v[10], v[11]), hv_pack_bf16(v[12], v[13]), hv_pack_bf16(v[14], v[15])));
 }
 __device__ __forceinline__ void stage16_packed(uint8_t* base, int row, int c, const uint4 lo, const uint4 hi) {  // 2 x 8 bf16
-    uint8_t* pc = base + (c >> 6) * TBYTES + (row >> 3) * 1024 + (row & 7) * 128;
+    const uint32_t pc = tc::smem_u32(base) + (c >> 6) * TBYTES + (row >> 3) * 1024 + (row & 7) * 128;
     const int jc = (c & 63) >> 3;
-    *reinterpret_cast<uint4*>(pc + ((jc ^ (row & 7)) << 4)) = lo;
-    *reinterpret_cast<uint4*>(pc + (((jc + 1) ^ (row & 7)) << 4)) = hi;
+    sts128(pc + ((jc ^ (row & 7)) << 4), lo);
+    sts128(pc + (((jc + 1) ^ (row & 7)) << 4), hi);
 }
 __device__ __forceinline__ float bf_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf_hi(uint32_t w) { return __uint_as_float(w & 0xffff0000u); }
