@@ -16,8 +16,8 @@ from .modules import (BasicTransformerBlock, BasicCrossTransformerBlock, AMDTran
 from .transformer import (MotionEncoderLearnTokenTransformer, MotionEncoderLearnTokenOnlyTemporalTransformer,  # noqa: F401
                           MotionEncoderLearnTokenTemporalTransformer,
                           AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion,
-                          AMDDiffusionTransformerModelImgSpatial, AMDDiffusionTransformerModel)
-from .model_AMD import AMDModel, AMDModel_New, AMD_N, AMD_models  # noqa: F401
+                          AMDDiffusionTransformerModelImgSpatial, AMDDiffusionTransformerModel, AMDReconstructTransformerModel)
+from .model_AMD import AMDModel, AMDModel_Camera, AMDModel_New, AMDModel_Rec, AMD_N, AMD_models  # noqa: F401
 from . import sharding  # noqa: F401
 from . import optim  # noqa: F401
 from . import utils  # noqa: F401

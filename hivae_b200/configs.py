@@ -30,3 +30,12 @@ AMDMODEL_LEGACY = dict(video_frames=4, use_filter=True, use_grey=True, use_motio
                        object_motion_token_num=4, object_motion_token_channel=16, object_enc_num_layers=2, enc_nhead=2, enc_ndim=64,
                        camera_motion_token_num=4, camera_motion_token_channel=16, camera_enc_num_layers=2, motion_token_num=4,
                        motion_token_channel=16, diffusion_model_type="default", diffusion_attn_num_heads=2, diffusion_num_layers=3)
+
+# AMDModel_Camera (model_AMD.py:894-1661), runnable configuration: camera stream only
+AMDMODEL_CAMERA = dict(video_frames=4, use_filter=True, filter_num=0.4, use_grey=True, use_mask=True, use_motiontemporal=False,
+                       motion_type="decouple", camera_motion_token_num=4, camera_motion_token_channel=16, camera_enc_num_layers=2,
+                       enc_nhead=2, enc_ndim=64, motion_token_num=4, motion_token_channel=16, diffusion_model_type="spatial",
+                       diffusion_attn_num_heads=2, diffusion_num_layers=3)
+# AMDModel_Rec (model_AMD.py:2840-3125): the non-diffusion reconstruction model
+AMDMODEL_REC = dict(video_frames=4, motion_token_num=4, motion_token_channel=128, enc_num_layers=2, enc_nhead=2, enc_ndim=64,
+                    motion_need_norm_out=True, diffusion_attn_num_heads=2, diffusion_num_layers=2)

@@ -17,7 +17,7 @@ from torch import nn
 from . import engine, ops
 from .frequency_utils import freq_split_gauss
 from .rectified_flow import RectifiedFlow
-from .transformer import (AMDDiffusionTransformerModel, AMDDiffusionTransformerModelImgSpatial,
+from .transformer import (AMDDiffusionTransformerModel, AMDDiffusionTransformerModelImgSpatial, AMDReconstructTransformerModel,
                           AMDDiffusionTransformerModelImgSpatialTempMotion, AMDDiffusionTransformerModelTempMotion,
                           MotionEncoderLearnTokenOnlyTemporalTransformer, MotionEncoderLearnTokenTemporalTransformer,
                           MotionEncoderLearnTokenTransformer)
@@ -470,8 +470,8 @@ class AMDModel(_ConfigModel):
         n, t, c, h, w = video.shape
         assert video.shape == ref_img.shape, f"video.shape:{video.shape}should be equal to ref_img.shape:{ref_img.shape}"
         if mask_ratio is not None:
-            raise NotImplementedError("random token masking is out of scope")
-        m = self._motions(video, ref_img, video_grey, ref_img_grey, camera_mask, None)
+            mask_ratio = torch.rand(1).item() * mask_ratio      # model_AMD.py:271-272
+        m = self._motions(video, ref_img, video_grey, ref_img_grey, camera_mask, mask_ratio)
         zi, zj = ref_img.flatten(0, 1).float().contiguous(), video.flatten(0, 1).float().contiguous()
         if time_step is None:
             time_step = self.prepare_timestep(batch_size=zj.shape[0], device=video.device)
@@ -497,9 +497,7 @@ class AMDModel(_ConfigModel):
         if start_step is None:
             start_step = self.scheduler.num_step
         assert start_step <= self.scheduler.num_step, "start_step cant be larger than scheduler.num_step"
-        if mask_ratio is not None:
-            raise NotImplementedError("random token masking is out of scope")
-        m = self._motions(video, ref_img, video_grey, ref_img_grey, None, None)
+        m = self._motions(video, ref_img, video_grey, ref_img_grey, None, mask_ratio)  # the ratio is used as given (436-438)
         zi, zj = ref_img.flatten(0, 1).float().contiguous(), video.flatten(0, 1).float().contiguous()
         zt, _ = self.scheduler.get_train_tuple(z1=zj, time_step=torch.ones((zj.shape[0],), device=zj.device) * start_step)
         zt = zt.contiguous().clone()
@@ -511,6 +509,186 @@ class AMDModel(_ConfigModel):
             ops.axpy(dt, self._dit(zi, zt, ts, m).contiguous(), zt)  # zt += dt * pre
         shp = (n, t) + tuple(zi.shape[1:])
         return zi.view(shp), zt.view(shp), zj.view(shp)
+
+
+class AMDModel_Camera(_ConfigModel):
+    """The camera-only model (model_AMD.py:894-1661): ONE motion encoder over the LOW band of [ref | video] (the grey clip when
+    use_grey), camera source / target tokens only, a single-stream denoiser; the target of the flow is the low band itself and
+    the reference image is `ref_img_grey` (1192-1193).  Built for the runnable configuration: use_filter (the reference reads
+    undefined names without it, 1136-1141), use_motiontemporal=False (the temporal branch encodes t frames and then splits
+    them into [:t] / [t:], 1147-1163), no camera_down (the encoder is sized for the full image, 960-972), motion_type
+    'decouple' ('plus' adds object tokens that this model never passes)."""
+    _supports_gradient_checkpointing = True
+
+    def __init__(self, image_inchannel=4, image_height=32, image_width=32, video_frames=16, scheduler_num_step=1000,
+                 use_filter=False, filter_num=0.4, use_grey=False, use_camera_down=False, use_regularizers=False,
+                 use_motiontemporal=True, klloss_weight=0.005, use_mask=True, motion_type="plus", object_motion_token_num=12,
+                 object_motion_token_channel=128, object_enc_num_layers=8, enc_nhead=8, enc_ndim=64, enc_dropout=0.0,
+                 motion_need_norm_out=False, camera_motion_token_num=12, camera_motion_token_channel=128, camera_enc_num_layers=8,
+                 motion_token_num=12, motion_token_channel=128, need_motion_transformer=False, motion_transformer_attn_head_dim=64,
+                 motion_transformer_attn_num_heads=16, motion_transformer_num_layers=4, diffusion_model_type="default",
+                 diffusion_attn_head_dim=64, diffusion_attn_num_heads=16, diffusion_out_channels=4, diffusion_num_layers=16,
+                 image_patch_size=2, motion_patch_size=1, motion_drop_ratio=0.0, extract_motion_with_motion_transformer=False, **kwargs):
+        super().__init__()
+        self._register(locals())
+        if use_regularizers or need_motion_transformer:
+            raise NotImplementedError("use_regularizers / need_motion_transformer are out of scope (false in every shipped script)")
+        if use_motiontemporal or use_camera_down or not use_filter or motion_type != "decouple":
+            raise NotImplementedError("AMDModel_Camera is runnable in the reference only with use_filter=True, use_motiontemporal=False, "
+                                      "use_camera_down=False, motion_type='decouple' (model_AMD.py:960-972, 1136-1163)")
+        self.num_step = scheduler_num_step
+        self.scheduler = RectifiedFlow(num_steps=scheduler_num_step)
+        self.diffusion_model_type, self.target_frame = diffusion_model_type, video_frames
+        self.camera_motion_token_channel, self.motion_token_channel = camera_motion_token_channel, motion_token_channel
+        self.filter_num, self.use_filter, self.use_grey, self.use_mask = filter_num, use_filter, use_grey, use_mask
+        if camera_motion_token_channel != motion_token_channel:
+            self.camera_motion_map = nn.Linear(camera_motion_token_channel, motion_token_channel)
+        self.camera_motion_encoder = MotionEncoderLearnTokenTransformer(
+            img_height=image_height, img_width=image_width, img_inchannel=image_inchannel, img_patch_size=image_patch_size,
+            motion_token_num=camera_motion_token_num, motion_channel=camera_motion_token_channel, need_norm_out=motion_need_norm_out,
+            num_attention_heads=enc_nhead, attention_head_dim=enc_ndim, num_layers=camera_enc_num_layers, dropout=enc_dropout,
+            attention_bias=True)
+        dit = dict(num_attention_heads=diffusion_attn_num_heads, attention_head_dim=diffusion_attn_head_dim,
+                   out_channels=diffusion_out_channels, num_layers=diffusion_num_layers, motion_type=motion_type,
+                   image_width=image_width, image_height=image_height, image_patch_size=image_patch_size,
+                   image_in_channels=image_inchannel * 2, motion_token_num=motion_token_num, motion_in_channels=motion_token_channel)
+        if diffusion_model_type == "default":
+            self.diffusion_transformer = AMDDiffusionTransformerModel(**dit)
+        elif diffusion_model_type == "spatial":
+            self.diffusion_transformer = AMDDiffusionTransformerModelImgSpatial(motion_target_num_frame=video_frames, **dit)
+        else:
+            raise IndexError
+
+    set_compute_dtype = AMDModel_New.set_compute_dtype
+    prepare_timestep = AMDModel_New.prepare_timestep
+
+    def _motions(self, video, ref_img, video_grey, ref_img_grey, camera_mask, mask_ratio):
+        n, t, c, h, w = video.shape
+        src = torch.cat([ref_img_grey, video_grey], dim=1) if self.use_grey else torch.cat([ref_img, video], dim=1)
+        lo, _ = freq_split_gauss(src.float().permute(0, 2, 1, 3, 4).contiguous(), self.filter_num, self.filter_num)
+        lf = lo.permute(0, 2, 1, 3, 4).contiguous()
+        gt = lf[:, t:].contiguous()
+        if self.use_mask:
+            lf = (lf * camera_mask).contiguous()
+        cam = self.camera_motion_encoder(lf, mask_ratio)
+        csrc, ctgt = cam[:, :t].flatten(0, 1).contiguous(), cam[:, t:].flatten(0, 1).contiguous()
+        assert csrc.shape == ctgt.shape
+        if self.camera_motion_token_channel != self.motion_token_channel:
+            csrc, ctgt = _device_linear(self.camera_motion_map, csrc), _device_linear(self.camera_motion_map, ctgt)
+        return cam, csrc, ctgt, gt.flatten(0, 1).contiguous()
+
+    def _dit(self, zi, zt, time_step, csrc, ctgt):
+        return self.diffusion_transformer(ctgt, (zi, zt), time_step, camera_motion_source_hidden_states=csrc)
+
+    @torch.no_grad()
+    def forward(self, video, ref_img, video_grey=None, ref_img_grey=None, camera_mask=None, time_step=None,
+                return_meta_info=False, mask_ratio=None):
+        """model_AMD.py:1086-1224 -> (pre, vel, {'loss','diff_loss','rec_loss'})"""
+        n, t, c, h, w = video.shape
+        assert video.shape == ref_img.shape, f"video.shape:{video.shape}should be equal to ref_img.shape:{ref_img.shape}"
+        if mask_ratio is not None:
+            mask_ratio = torch.rand(1).item() * mask_ratio
+        cam, csrc, ctgt, zj = self._motions(video, ref_img, video_grey, ref_img_grey, camera_mask, mask_ratio)
+        zi = ref_img_grey.flatten(0, 1).float().contiguous()
+        if time_step is None:
+            time_step = self.prepare_timestep(batch_size=zj.shape[0], device=video.device)
+        if self.diffusion_model_type != "default":
+            time_step = self.prepare_timestep(batch_size=n, device=video.device).repeat_interleave(t)
+        zt, vel = self.scheduler.get_train_tuple(z1=zj, time_step=time_step)
+        zt = zt.contiguous()
+        pre = self._dit(zi, zt, time_step.float(), csrc, ctgt)
+        diff_loss = l2(pre, vel)
+        rec_loss = l2(self.scheduler.get_target_with_zt_vel(zt, pre, time_step), zj)
+        if return_meta_info:
+            return {"camera_motion": cam, "zi": zi, "zj": zj, "zt": zt, "pre": pre, "time_step": time_step}
+        return pre, vel, {"loss": diff_loss, "diff_loss": diff_loss, "rec_loss": rec_loss}
+
+    @torch.no_grad()
+    def sample(self, video, ref_img, video_grey=None, ref_img_grey=None, camera_mask=None, sample_step=50, mask_ratio=None,
+               start_step=None, return_meta_info=False):
+        """model_AMD.py:1226-1365 -> (zi, zt, zj), each (n, t, c, h, w); zj is the low band the flow reconstructs"""
+        n, t = video.shape[:2]
+        if start_step is None:
+            start_step = self.scheduler.num_step
+        assert start_step <= self.scheduler.num_step, "start_step cant be larger than scheduler.num_step"
+        _cam, csrc, ctgt, zj = self._motions(video, ref_img, video_grey, ref_img_grey, camera_mask, mask_ratio)
+        zi = ref_img_grey.flatten(0, 1).float().contiguous()
+        zt, _ = self.scheduler.get_train_tuple(z1=zj, time_step=torch.ones((zj.shape[0],), device=zj.device) * start_step)
+        zt = zt.contiguous().clone()
+        step_seq = list(reversed(np.linspace(0, start_step, num=sample_step + 1, endpoint=True, dtype=int)[1:]))
+        dt = 1.0 / sample_step
+        ts = torch.empty(zt.shape[0], dtype=torch.float32, device=zt.device)
+        pre_cache, sample_cache = [], []
+        for i in step_seq:
+            ts.fill_(float(i))
+            pre = self._dit(zi, zt, ts, csrc, ctgt).contiguous()
+            ops.axpy(dt, pre, zt)
+            if return_meta_info:
+                pre_cache.append(pre)
+                sample_cache.append(zt.clone())
+        shp = (n, t) + tuple(zi.shape[1:])
+        zi, zt, zj = zi.view(shp), zt.view(shp), zj.view(shp)
+        if return_meta_info:
+            return {"zi": zi, "zj": zj, "sample": zt, "pre_cache": pre_cache, "sample_cache": sample_cache, "step_seq": step_seq, "motion": ctgt}
+        return zi, zt, zj
+
+
+class AMDModel_Rec(_ConfigModel):
+    """The reconstruction model (model_AMD.py:2840-3125): object + camera motion from two MotionEncoderLearnTokenTransformer
+    over [ref | video], added; one pass of AMDReconstructTransformerModel on [zi | learnable zt_token]; loss = l2(pre, video).
+    `sample` is not runnable in the reference (it reads a non-existent `self.motion_encoder`, 3020) and raises the same
+    AttributeError here."""
+    _supports_gradient_checkpointing = True
+
+    def __init__(self, image_inchannel=4, image_height=32, image_width=32, video_frames=16, scheduler_num_step=1000,
+                 motion_token_num=12, motion_token_channel=128, enc_num_layers=8, enc_nhead=8, enc_ndim=64, enc_dropout=0.0,
+                 motion_need_norm_out=True, need_motion_transformer=False, motion_transformer_attn_head_dim=64,
+                 motion_transformer_attn_num_heads=16, motion_transformer_num_layers=4, diffusion_attn_head_dim=64,
+                 diffusion_attn_num_heads=16, diffusion_out_channels=4, diffusion_num_layers=16, image_patch_size=2,
+                 motion_patch_size=1, motion_drop_ratio=0.0, **kwargs):
+        super().__init__()
+        self._register(locals())
+        if need_motion_transformer:
+            raise NotImplementedError("need_motion_transformer is out of scope (false in every shipped script)")
+        self.num_step = scheduler_num_step
+        self.scheduler = RectifiedFlow(num_steps=scheduler_num_step)
+        self.need_motion_transformer = need_motion_transformer
+        self.zt_token = nn.Parameter(torch.randn(1, image_inchannel, image_height, image_width) * 0.02)
+        enc = dict(img_height=image_height, img_width=image_width, img_inchannel=image_inchannel, img_patch_size=image_patch_size,
+                   motion_token_num=motion_token_num, motion_channel=motion_token_channel, need_norm_out=motion_need_norm_out,
+                   num_attention_heads=enc_nhead, attention_head_dim=enc_ndim, num_layers=enc_num_layers, dropout=enc_dropout,
+                   attention_bias=True)
+        self.object_motion_encoder = MotionEncoderLearnTokenTransformer(**enc)
+        self.camera_motion_encoder = MotionEncoderLearnTokenTransformer(**enc)
+        self.transformer = AMDReconstructTransformerModel(
+            num_attention_heads=diffusion_attn_num_heads, attention_head_dim=diffusion_attn_head_dim, out_channels=diffusion_out_channels,
+            num_layers=diffusion_num_layers, image_width=image_width, image_height=image_height, image_patch_size=image_patch_size,
+            image_in_channels=image_inchannel * 2, motion_token_num=motion_token_num, motion_in_channels=motion_token_channel)
+
+    set_compute_dtype = AMDModel_New.set_compute_dtype
+
+    @torch.no_grad()
+    def forward(self, video, ref_img, time_step=None, return_meta_info=False):
+        """model_AMD.py:2940-3007 -> (pre, zj, {'loss', 'rec_loss'})"""
+        n, t, c, h, w = video.shape
+        assert video.shape == ref_img.shape, f"video.shape:{video.shape}should be equal to ref_img.shape:{ref_img.shape}"
+        rv = torch.cat([ref_img, video], dim=1).float().contiguous()
+        obj = self.object_motion_encoder(rv)
+        osrc, otgt = obj[:, :t].flatten(0, 1), obj[:, t:].flatten(0, 1)
+        assert osrc.shape == otgt.shape
+        cam = self.camera_motion_encoder(rv)
+        csrc, ctgt = cam[:, :t].flatten(0, 1), cam[:, t:].flatten(0, 1)
+        assert csrc.shape == ctgt.shape
+        zi, zj = ref_img.flatten(0, 1).float().contiguous(), video.flatten(0, 1).float().contiguous()
+        zt = self.zt_token.detach().float().repeat(zj.shape[0], 1, 1, 1).contiguous()
+        pre = self.transformer((osrc + csrc).contiguous(), (otgt + ctgt).contiguous(), (zi, zt))
+        rec_loss = l2(pre, zj)
+        if return_meta_info:
+            return {"camera_motion": cam, "object_motion": obj, "zi": zi, "zj": zj, "zt": zt, "pre": pre, "time_step": time_step}
+        return pre, zj, {"loss": rec_loss, "rec_loss": rec_loss}
+
+    def sample(self, video, ref_img, sample_step=50, start_step=None, return_meta_info=False):
+        raise AttributeError("'AMDModel_Rec' object has no attribute 'motion_encoder'")  # model_AMD.py:3020
 
 
 def _device_linear(m, x):
@@ -528,4 +706,35 @@ def AMD_N(**kwargs):
                         diffusion_out_channels=4, diffusion_num_layers=12, **kwargs)
 
 
-AMD_models = {"AMD_N": AMD_N}
+def AMD_S(**kwargs):
+    """model_AMD.py:3127-3137."""
+    return AMDModel(enc_nhead=8, enc_ndim=64, diffusion_attn_head_dim=64, diffusion_attn_num_heads=16, diffusion_out_channels=4,
+                    diffusion_num_layers=12, **kwargs)
+
+
+def AMD_S_Camera(**kwargs):
+    """model_AMD.py:3139-3149."""
+    return AMDModel_Camera(enc_nhead=8, enc_ndim=64, diffusion_attn_head_dim=64, diffusion_attn_num_heads=16, diffusion_out_channels=4,
+                           diffusion_num_layers=12, **kwargs)
+
+
+def AMD_L(**kwargs):
+    """model_AMD.py:3163-3173.  96-wide attention heads: outside the 64-wide kernels of this package (raises NotImplementedError)."""
+    return AMDModel(enc_num_layers=8, enc_nhead=16, enc_ndim=64, diffusion_attn_head_dim=96, diffusion_attn_num_heads=16,
+                    diffusion_out_channels=4, diffusion_num_layers=16, **kwargs)
+
+
+def AMD_S_Rec(**kwargs):
+    """model_AMD.py:3176-3186."""
+    return AMDModel_Rec(enc_num_layers=8, enc_nhead=8, enc_ndim=64, diffusion_attn_head_dim=64, diffusion_attn_num_heads=16,
+                        diffusion_out_channels=4, diffusion_num_layers=12, **kwargs)
+
+
+def AMD_S_RecSplit(**kwargs):
+    """model_AMD.py:3189-3200 (`is_split` is swallowed by AMDModel_Rec's **kwargs in the reference too)."""
+    return AMDModel_Rec(enc_num_layers=8, enc_nhead=8, enc_ndim=64, diffusion_attn_head_dim=64, diffusion_attn_num_heads=16,
+                        diffusion_out_channels=4, diffusion_num_layers=12, is_split=True, **kwargs)
+
+
+AMD_models = {"AMD_S": AMD_S, "AMD_S_Camera": AMD_S_Camera, "AMD_N": AMD_N, "AMD_L": AMD_L, "AMD_S_Rec": AMD_S_Rec,
+              "AMD_S_RecSplit": AMD_S_RecSplit}

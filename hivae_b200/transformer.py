@@ -80,8 +80,15 @@ def _mask_idx(noise, mask_ratio):
 
 
 def _final_norm_out(need_norm_out, m):
-    if need_norm_out:  # rarely-used option (motion_need_norm_out=False in every shipped script)
-        m = torch.nn.functional.layer_norm(m, (m.shape[-1],))
+    """norm_out = LayerNorm(motion_channel, elementwise_affine=False) of the encoders (transformer.py:107-108, 157-158)"""
+    if need_norm_out:  # motion_need_norm_out=False in every shipped AMD_N script; AMDModel_Rec's default
+        c = m.shape[-1]
+        if m.is_cuda and c % 128 == 0:
+            rows = m.reshape(1, -1, c).float().contiguous()
+            out = torch.empty(rows.shape[1], c, dtype=torch.float32, device=m.device)
+            ops.ln_modulate(Rows(rows, 0, rows.shape[1]), None, None, 1e-5, out)
+            return out.view(m.shape).to(m.dtype)
+        m = torch.nn.functional.layer_norm(m, (c,))  # narrow token channels (16): a few hundred values
     return m
 
 
@@ -219,8 +226,6 @@ class MotionEncoderLearnTokenTemporalTransformer(_HvModule):
 
     @torch.no_grad()
     def forward(self, img_hidden_states, mask_ratio=None):
-        if mask_ratio is not None:
-            raise NotImplementedError("random token masking (train-time augmentation, transformer.py:369-397) is out of scope")
         N, T, C, H, W = img_hidden_states.shape
         P = self._prepared(img_hidden_states.device)
         ctx = P.ctx
@@ -228,13 +233,22 @@ class MotionEncoderLearnTokenTemporalTransformer(_HvModule):
         Lm, S = P.tok.shape[0], self.img_token_len
         assert S == (H // p) * (W // p), "img_token_len should be equal!"
         assert T % 2 == 0 and (T // 2) * Lm <= P.tpos.shape[0]
-        frames, FR, half = N * T, Lm + S, T // 2
+        # random_masking (transformer.py:369-397): every frame keeps the int(S (1 - ratio)) image tokens with the smallest noise
+        idx = _mask_idx(mask_noise(N * T, S, img_hidden_states.device), mask_ratio) if mask_ratio is not None else None
+        keep = S if idx is None else idx.shape[1]
+        frames, FR, half = N * T, Lm + keep, T // 2
         x = img_hidden_states.reshape(frames, C, H, W).float().contiguous()
         res = ctx.buf("tenc_res", (frames, FR, D), torch.float32)
         tab = self._token_table(P, ctx, T)
         for n in range(N):
             ops.rows_scatter(tab.view(T * Lm, D), Lm, 1, None, Rows(res[n * T:(n + 1) * T], 0, Lm))
-        ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, None, res, FR, Lm, D)
+        if idx is None:
+            ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, None, res, FR, Lm, D)
+        else:
+            from .backward import rows_index
+            full = ctx.buf("tenc_full", (frames, S, D), torch.float32)
+            ops.patch_embed(x, None, p, P.pw, P.pb, P.pos, None, full, S, 0, D)
+            rows_index(full, res[:, Lm:], idx, frames, S, keep, D, S, FR)
         rows, geom = Rows(res, 0, FR), engine.dense_geom(frames, FR)
         trows, tgeom = Rows(res[frames // 2:], 0, Lm), engine.strided_geom(N, Lm, half)  # '(n t) l d -> (n l) t d'
         for bp, mp in zip(P.blocks, P.mblocks):
@@ -709,3 +723,74 @@ class AMDDiffusionTransformerModel(AMDDiffusionTransformerModelImgSpatial):
                          image_height=image_height, image_patch_size=image_patch_size, image_in_channels=image_in_channels,
                          motion_token_num=motion_token_num, motion_in_channels=motion_in_channels,
                          motion_target_num_frame=1, **kw)
+
+
+# ================================================================================================
+class AMDReconstructTransformerModel(_HvModule):
+    """The reconstruction (non-diffusion) transformer of AMDModel_Rec (transformer.py:703-854): plain pre-LN blocks over
+    [image tokens | source_token, source motion, target_token, target motion], norm_final + proj_out on the image rows,
+    (c, p, q) unpatchify.  No timestep, no adaLN."""
+
+    def __init__(self, num_attention_heads=20, attention_head_dim=64, out_channels: Optional[int] = 4, num_layers=12, image_width=32,
+                 image_height=32, image_patch_size=2, image_in_channels: Optional[int] = 4, motion_token_num=12,
+                 motion_in_channels: Optional[int] = 128, flip_sin_to_cos=True, freq_shift=0, time_embed_dim=512, dropout=0.0,
+                 attention_bias=True, temporal_compression_ratio=4, activation_fn="gelu-approximate", timestep_activation_fn="silu",
+                 norm_elementwise_affine=True, norm_eps=1e-5, spatial_interpolation_scale=1.0, temporal_interpolation_scale=1.0):
+        super().__init__()
+        hidden_dim = num_attention_heads * attention_head_dim
+        iph, ipw = image_height // image_patch_size, image_width // image_patch_size
+        self.image_patch_size, self.out_channels = image_patch_size, out_channels
+        self.image_patch_embed = PatchEmbed(patch_size=image_patch_size, in_channels=image_in_channels, embed_dim=hidden_dim, bias=True)
+        self.motion_patch_embed = nn.Linear(motion_in_channels, hidden_dim)
+        self.embedding_dropout = nn.Dropout(dropout)
+        self.register_buffer("pos_embedding", E.table(E.sincos_2d(hidden_dim, iph, ipw)), persistent=False)
+        self.register_buffer("motion_pos_embedding", E.table(E.sincos_1d(hidden_dim, np.arange(2 + 2 * motion_token_num))), persistent=False)
+        self.source_token = nn.Parameter(torch.zeros(1, 1, hidden_dim), requires_grad=True)
+        self.target_token = nn.Parameter(torch.zeros(1, 1, hidden_dim), requires_grad=True)
+        self.transformer_blocks = nn.ModuleList([
+            BasicTransformerBlock(dim=hidden_dim, num_attention_heads=num_attention_heads, attention_head_dim=attention_head_dim,
+                                  dropout=dropout, activation_fn=activation_fn, attention_bias=attention_bias,
+                                  norm_elementwise_affine=norm_elementwise_affine, norm_eps=norm_eps) for _ in range(num_layers)])
+        self.norm_final = nn.LayerNorm(hidden_dim, norm_eps, norm_elementwise_affine)
+        self.proj_out = nn.Linear(hidden_dim, image_patch_size * image_patch_size * out_channels)
+        self.gradient_checkpointing = False
+
+    def _prepare(self, ctx):
+        P = _Prepared()
+        P.ctx = ctx
+        P.blocks = [engine.prepare_block(ctx, b, "basic") for b in self.transformer_blocks]
+        P.pw, P.pb = self._patch_params(ctx, self.image_patch_embed)
+        P.pos, P.mpos = ctx.f32(self.pos_embedding[0]), ctx.f32(self.motion_pos_embedding[0])
+        P.mw, P.mb = ctx.f32(self.motion_patch_embed.weight), ctx.f32(self.motion_patch_embed.bias)
+        P.stok, P.ttok = ctx.f32(self.source_token[0]), ctx.f32(self.target_token[0])
+        P.nfw, P.nfb = ctx.f32(self.norm_final.weight), ctx.f32(self.norm_final.bias)
+        P.hw, P.hb = ctx.f32(self.proj_out.weight), ctx.f32(self.proj_out.bias)
+        return P
+
+    @torch.no_grad()
+    def forward(self, motion_source_hidden_states, motion_target_hidden_states, image_hidden_states):
+        image2 = None
+        if isinstance(image_hidden_states, (tuple, list)):  # (zi, zt): the channel concat is folded into the patch embed
+            image_hidden_states, image2 = image_hidden_states
+        N, Ci, Hi, Wi = image_hidden_states.shape
+        _, L, Cm = motion_source_hidden_states.shape
+        P = self._prepared(image_hidden_states.device)
+        ctx = P.ctx
+        p = self.image_patch_size
+        D, S, LM = P.hw.shape[1], (Hi // p) * (Wi // p), 2 * L + 2
+        assert LM <= P.mpos.shape[0]
+        FR = S + LM
+        res = ctx.buf("rec_res", (N, FR, D), torch.float32)  # rows [0, S) image, then the motion stream (transformer.py:838)
+        x = image_hidden_states.float().contiguous()
+        ops.patch_embed(x, image2.float().contiguous() if image2 is not None else None, p, P.pw, P.pb, P.pos, None, res, FR, 0, D)
+        emb = lambda t, name: engine.small_linear(ctx, t.reshape(N * L, Cm).float().contiguous(), P.mw, P.mb, name)
+        ops.rows_scatter(P.stok, 0, 0, P.mpos[0:1], Rows(res, S, 1))
+        ops.rows_scatter(emb(motion_source_hidden_states, "rec_s"), L, 1, P.mpos[1:1 + L], Rows(res, S + 1, L))
+        ops.rows_scatter(P.ttok, 0, 0, P.mpos[L + 1:L + 2], Rows(res, S + L + 1, 1))
+        ops.rows_scatter(emb(motion_target_hidden_states, "rec_t"), L, 1, P.mpos[L + 2:LM], Rows(res, S + L + 2, L))
+        rows, geom = Rows(res, 0, FR), engine.dense_geom(N, FR)
+        for bp in P.blocks:
+            engine.run_block(ctx, bp, rows, geom)
+        y = ops.ln_modulate(Rows(res, 0, S), P.nfw, P.nfb, self.norm_final.eps, ctx.buf("rec_fin", (N * S, D), torch.float32))
+        tok = engine.small_linear(ctx, y, P.hw, P.hb, "rec_tok")
+        return ops.unpatchify(tok.view(N, S, -1), p, self.out_channels, order=1).to(image_hidden_states.dtype)

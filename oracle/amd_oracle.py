@@ -216,14 +216,22 @@ def _count_layers(sd, prefix):
 
 
 # ----------------------------------------------------------------------------- encoders / DiT
-def object_encoder(sd, p, x, heads, patch=2, need_norm_out=False):
-    """MotionEncoderLearnTokenTransformer.forward (transformer.py:116-162), mask_ratio=None."""
+def mask_keep(noise, mask_ratio):
+    """random_masking (transformer.py:164-192, 369-397, 558-586): indices of the int(L (1 - ratio)) smallest noise values"""
+    return torch.argsort(noise, dim=1)[:, :int(noise.shape[1] * (1 - mask_ratio))]
+
+
+def object_encoder(sd, p, x, heads, patch=2, need_norm_out=False, keep=None):
+    """MotionEncoderLearnTokenTransformer.forward (transformer.py:116-162); keep (N*T, len_keep) = kept image tokens per frame."""
     N, T, C, H, W = x.shape
     D = sd[p + ".motion_embed.weight"].shape[0]
     mt = _lin(sd, p + ".motion_embed", sd[p + ".motion_token"]).repeat(N * T, 1, 1)
     img = patch_embed(sd, p + ".patch_embed", x.reshape(N * T, C, H, W), patch)
     pos = torch.from_numpy(sincos_2d(D, H // patch, W // patch)).float().to(x.device)
-    h = torch.cat([mt, img + pos[None]], 1)
+    img = img + pos[None]
+    if keep is not None:
+        img = torch.gather(img, 1, keep.to(x.device)[..., None].expand(-1, -1, D))
+    h = torch.cat([mt, img], 1)
     for i in range(_count_layers(sd, p + ".transformer_blocks")):
         h = basic_block(sd, p + ".transformer_blocks.%d" % i, h, heads)
     m = _lin(sd, p + ".proj_out", _ln(sd, p + ".norm_final", h[:, :mt.shape[1]]))
@@ -232,8 +240,8 @@ def object_encoder(sd, p, x, heads, patch=2, need_norm_out=False):
     return m.view(N, T, *m.shape[1:])
 
 
-def temporal_motion_encoder(sd, p, x, heads, video_frames, patch=2, need_norm_out=True):
-    """MotionEncoderLearnTokenTemporalTransformer.forward (transformer.py:298-367), mask_ratio=None.  Keeps the
+def temporal_motion_encoder(sd, p, x, heads, video_frames, patch=2, need_norm_out=True, keep=None):
+    """MotionEncoderLearnTokenTemporalTransformer.forward (transformer.py:298-367); keep (N*T, len_keep) as above.  Keeps the
     reference's two different splits: frames of each clip at 305 (dim=1), the flat (n t) batch at 340 (dim=0)."""
     N, T, C, H, W = x.shape
     D = sd[p + ".motion_embed.weight"].shape[0]
@@ -245,7 +253,10 @@ def temporal_motion_encoder(sd, p, x, heads, video_frames, patch=2, need_norm_ou
     mt = mt.reshape(N * T, l, D)
     img = patch_embed(sd, p + ".patch_embed", x.reshape(N * T, C, H, W), patch)
     pos = torch.from_numpy(sincos_2d(D, H // patch, W // patch)).float().to(x.device)
-    h = torch.cat([mt, img + pos[None]], 1)
+    img = img + pos[None]
+    if keep is not None:
+        img = torch.gather(img, 1, keep.to(x.device)[..., None].expand(-1, -1, D))
+    h = torch.cat([mt, img], 1)
     for i in range(_count_layers(sd, p + ".transformer_blocks")):
         h = basic_block(sd, p + ".transformer_blocks.%d" % i, h, heads)
         src, tgt = h[:, :l].chunk(2, dim=0)
@@ -259,8 +270,9 @@ def temporal_motion_encoder(sd, p, x, heads, video_frames, patch=2, need_norm_ou
     return m.view(N, T, *m.shape[1:])
 
 
-def camera_encoder(sd, p, x, heads, video_frames, patch=2, need_norm_out=False):
-    """MotionEncoderLearnTokenOnlyTemporalTransformer.forward (transformer.py:495-556)."""
+def camera_encoder(sd, p, x, heads, video_frames, patch=2, need_norm_out=False, keep=None):
+    """MotionEncoderLearnTokenOnlyTemporalTransformer.forward (transformer.py:495-556); keep (N, len_keep) = the spatial
+    locations a clip keeps in every frame (558-586)."""
     N, T, C, H, W = x.shape
     D = sd[p + ".motion_embed.weight"].shape[0]
     S = (H // patch) * (W // patch)
@@ -268,6 +280,9 @@ def camera_encoder(sd, p, x, heads, video_frames, patch=2, need_norm_out=False):
     pos = torch.from_numpy(sincos_2d(D, H // patch, W // patch)).float().to(x.device)
     tem = torch.from_numpy(sincos_1d(D, np.arange(video_frames))).float().to(x.device)
     img = (img + pos[None]).view(N, T, S, D) + tem[None, :T, None]
+    if keep is not None:
+        S = keep.shape[1]
+        img = torch.gather(img, 2, keep.to(x.device)[:, None, :, None].expand(-1, T, -1, D))
     img = img.permute(0, 2, 1, 3).reshape(N * S, T, D)  # (n s) t c
     tok = _lin(sd, p + ".motion_embed", sd[p + ".motion_token"])[0]  # (t0, D)
     if tok.shape[0] != T:
@@ -410,7 +425,7 @@ class AMDOracle:
         self.eh, self.dh, self.T, self.patch = enc_nhead, dit_nhead, video_frames, patch
         self.mtn, self.num_step, self.nno = motion_token_num, num_step, need_norm_out
 
-    def encode(self, video, ref_img, d_lo=0.6):
+    def encode(self, video, ref_img, d_lo=0.6, cam_keep=None, obj_keep=None):
         n, t, c, h, w = video.shape
         rv = torch.cat([ref_img, video], 1)
         lpf = gaussian_lpf([2 * t, h, w], d_lo, d_lo).to(video.device)
@@ -420,8 +435,8 @@ class AMDOracle:
             lf = lo.permute(0, 2, 1, 3, 4)[:, t:]
             lf = camera_down(self.sd, "camera_down", lf.flatten(0, 1))
             lf = lf.view(n, t, *lf.shape[1:])
-            cam = camera_encoder(self.sd, "camera_motion_encoder", lf, self.eh, self.T, self.patch, self.nno)
-        obj = object_encoder(self.sd, "object_motion_encoder", rv, self.eh, self.patch, self.nno)
+            cam = camera_encoder(self.sd, "camera_motion_encoder", lf, self.eh, self.T, self.patch, self.nno, cam_keep)
+        obj = object_encoder(self.sd, "object_motion_encoder", rv, self.eh, self.patch, self.nno, obj_keep)
         return cam, obj[:, :t].flatten(0, 1), obj[:, t:].flatten(0, 1)
 
     def dit(self, zi, zt, step, cam, osrc, otgt):
@@ -539,6 +554,97 @@ class AMDModelOracle:
         for i in sample_steps(start_step, sample_step):
             zt = zt + self.dit(zi, zt, torch.ones(zt.shape[0]) * i, m) / sample_step
         return zt.view(video.shape)
+
+
+class AMDModelCameraOracle:
+    """AMDModel_Camera (model_AMD.py:894-1661) in its runnable configuration: use_filter, use_motiontemporal=False (the
+    temporal branch splits a t-frame motion into [:t] / [t:] and asserts, 1147-1163), no camera_down (the encoder is sized
+    for the full image, 960-972), motion_type 'decouple' (camera tokens only).  zi = ref_img_grey, target = low band."""
+
+    def __init__(self, sd, cfg):
+        self.sd, self.c = {k: v.float() for k, v in sd.items()}, cfg
+        self.T, self.num_step = cfg["video_frames"], cfg.get("scheduler_num_step", 1000)
+
+    def motions(self, video, ref_img, video_grey, ref_img_grey, camera_mask):
+        c = self.c
+        n, t, ch, h, w = video.shape
+        src = torch.cat([ref_img_grey, video_grey], 1) if c.get("use_grey", False) else torch.cat([ref_img, video], 1)
+        lo, _ = freq_split3d(src.permute(0, 2, 1, 3, 4), gaussian_lpf([2 * t, h, w], c.get("filter_num", 0.4), c.get("filter_num", 0.4)))
+        lf = lo.permute(0, 2, 1, 3, 4)
+        gt = lf[:, t:]
+        if c.get("use_mask", True):
+            lf = lf * camera_mask
+        cam = object_encoder(self.sd, "camera_motion_encoder", lf, c["enc_nhead"], c.get("image_patch_size", 2), c.get("motion_need_norm_out", False))
+        csrc, ctgt = cam[:, :t].flatten(0, 1), cam[:, t:].flatten(0, 1)
+        if "camera_motion_map.weight" in self.sd:
+            csrc, ctgt = _lin(self.sd, "camera_motion_map", csrc), _lin(self.sd, "camera_motion_map", ctgt)
+        return csrc, ctgt, gt.flatten(0, 1)
+
+    def dit(self, zi, zt, step, csrc, ctgt):
+        c = self.c
+        return dit_imgspatial_forward(self.sd, "diffusion_transformer", ctgt, torch.cat([zi, zt], 1), step, c["diffusion_attn_num_heads"],
+                                      self.T, c.get("image_patch_size", 2), c.get("motion_token_num", 12), c.get("motion_type", "plus"),
+                                      csrc, None, None, legacy=c.get("diffusion_model_type", "default") == "default")
+
+    def forward(self, video, ref_img, time_step, z0, video_grey, ref_img_grey, camera_mask):
+        csrc, ctgt, zj = self.motions(video, ref_img, video_grey, ref_img_grey, camera_mask)
+        zi = ref_img_grey.flatten(0, 1)
+        zt, vel = rf_train_tuple(zj, time_step, z0, self.num_step)
+        pre = self.dit(zi, zt, time_step, csrc, ctgt)
+        return pre, vel, {"loss": F.mse_loss(pre, vel), "rec_loss": F.mse_loss(rf_target(zt, pre, time_step, self.num_step), zj)}
+
+    def sample(self, video, ref_img, sample_step, z0, video_grey, ref_img_grey, camera_mask, start_step=None):
+        start_step = self.num_step if start_step is None else start_step
+        csrc, ctgt, zj = self.motions(video, ref_img, video_grey, ref_img_grey, camera_mask)
+        zi = ref_img_grey.flatten(0, 1)
+        zt, _ = rf_train_tuple(zj, torch.ones(zj.shape[0]) * start_step, z0, self.num_step)
+        for i in sample_steps(start_step, sample_step):
+            zt = zt + self.dit(zi, zt, torch.ones(zt.shape[0]) * i, csrc, ctgt) / sample_step
+        return zt.view(video.shape), zj.view(video.shape)
+
+
+def rec_transformer_forward(sd, p, src, tgt, image, heads, patch=2):
+    """AMDReconstructTransformerModel.forward (transformer.py:805-854): BasicTransformerBlocks over [image | source_token,
+    source, target_token, target], norm_final + proj_out on the image rows, (c, p, q) unpatchify."""
+    N, _, Hi, Wi = image.shape
+    L = src.shape[1]
+    D = sd[p + ".motion_patch_embed.weight"].shape[0]
+    ms, mt = _lin(sd, p + ".motion_patch_embed", src), _lin(sd, p + ".motion_patch_embed", tgt)
+    img = patch_embed(sd, p + ".image_patch_embed", image, patch)
+    mo = torch.cat([sd[p + ".source_token"].repeat(N, 1, 1), ms, sd[p + ".target_token"].repeat(N, 1, 1), mt], 1)
+    # the table is sized by the denoiser's motion_token_num (2 + 2 * num rows); the forward only reads the first 2 L + 2
+    mo = mo + torch.from_numpy(sincos_1d(D, np.arange(2 * L + 2))).float().to(image.device)[None]
+    img = img + torch.from_numpy(sincos_2d(D, Hi // patch, Wi // patch)).float().to(image.device)[None]
+    h = torch.cat([img, mo], 1)
+    for i in range(_count_layers(sd, p + ".transformer_blocks")):
+        h = basic_block(sd, p + ".transformer_blocks.%d" % i, h, heads)
+    S = img.shape[1]
+    y = _lin(sd, p + ".proj_out", _ln(sd, p + ".norm_final", h[:, :S]))
+    C = y.shape[-1] // (patch * patch)
+    y = y.reshape(N, 1, Hi // patch, Wi // patch, C, patch, patch)
+    return y.permute(0, 1, 4, 2, 5, 3, 6).flatten(5, 6).flatten(3, 4).squeeze(1)
+
+
+class AMDModelRecOracle:
+    """AMDModel_Rec.forward (model_AMD.py:2940-3007): two MotionEncoderLearnTokenTransformer over [ref | video], motions added,
+    one pass of the reconstruction transformer on [zi | zt_token]; loss = l2(pre, zj)."""
+
+    def __init__(self, sd, cfg):
+        self.sd, self.c = {k: v.float() for k, v in sd.items()}, cfg
+
+    def forward(self, video, ref_img):
+        c = self.c
+        n, t = video.shape[:2]
+        rv = torch.cat([ref_img, video], 1)
+        nno = c.get("motion_need_norm_out", True)
+        obj = object_encoder(self.sd, "object_motion_encoder", rv, c["enc_nhead"], c.get("image_patch_size", 2), nno)
+        cam = object_encoder(self.sd, "camera_motion_encoder", rv, c["enc_nhead"], c.get("image_patch_size", 2), nno)
+        src = obj[:, :t].flatten(0, 1) + cam[:, :t].flatten(0, 1)
+        tgt = obj[:, t:].flatten(0, 1) + cam[:, t:].flatten(0, 1)
+        zi, zj = ref_img.flatten(0, 1), video.flatten(0, 1)
+        zt = self.sd["zt_token"].repeat(zj.shape[0], 1, 1, 1)
+        pre = rec_transformer_forward(self.sd, "transformer", src, tgt, torch.cat([zi, zt], 1), c["diffusion_attn_num_heads"], c.get("image_patch_size", 2))
+        return pre, zj, {"loss": F.mse_loss(pre, zj), "rec_loss": F.mse_loss(pre, zj)}
 
 
 def psnr(a, b):

@@ -185,5 +185,58 @@ def temporal_encoder(ref):
         json.dump({k: list(v.shape) for k, v in m.state_dict().items()}, f, indent=0)
 
 
+def camera_and_rec_models(ref):
+    """f3: AMDModel_Camera (model_AMD.py:894-1661) and AMDModel_Rec (2840-3125) in their runnable configurations"""
+    import json
+    g = torch.Generator().manual_seed(21)
+    # ---- AMDModel_Camera, both denoisers
+    out = {}
+    n, t = 1, 4
+    video, ref_img = torch.randn(n, t, 4, 32, 32, generator=g) * 0.7, torch.randn(n, t, 4, 32, 32, generator=g) * 0.7
+    vg, rg = torch.randn(n, t, 4, 32, 32, generator=g) * 0.7, torch.randn(n, t, 4, 32, 32, generator=g) * 0.7
+    mask = (torch.rand(n, 2 * t, 1, 32, 32, generator=g) > 0.3).float()
+    z0 = torch.randn(n * t, 4, 32, 32, generator=g)
+    ts = torch.tensor([411.0]).repeat_interleave(t)
+    out.update(video=video, ref_img=ref_img, video_grey=vg, ref_img_grey=rg, camera_mask=mask, z0=z0)
+    for dmt in ("spatial", "default"):
+        cfg = dict(configs.AMDMODEL_CAMERA, diffusion_model_type=dmt)
+        torch.manual_seed(0)
+        m = ref.model_AMD.AMDModel_Camera(**cfg).eval()
+        sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 8)
+        m.load_state_dict(sd)
+        orig = m.scheduler.get_train_tuple
+        m.scheduler.get_train_tuple = lambda z0_=None, z1=None, time_step=None, orig=orig: orig(z0=z0, z1=z1, time_step=time_step)
+        m.prepare_timestep = lambda batch_size, device, time_step=None: (torch.tensor([411.0]) if batch_size == n else ts).to(device)
+        pre, vel, ld = m(video, ref_img, video_grey=vg, ref_img_grey=rg, camera_mask=mask)
+        orc = O.AMDModelCameraOracle(sd, cfg)
+        opre, ovel, old = orc.forward(video, ref_img, ts, z0, vg, rg, mask)
+        check("AMDModel_Camera %s forward pre" % dmt, opre, pre), check("AMDModel_Camera %s loss" % dmt, old["loss"], ld["loss"])
+        zi, zt, zj = m.sample(video, ref_img, video_grey=vg, ref_img_grey=rg, camera_mask=mask, sample_step=3)
+        ozt, ozj = orc.sample(video, ref_img, 3, z0, vg, rg, mask)
+        check("AMDModel_Camera %s sample zt" % dmt, ozt, zt), check("AMDModel_Camera %s zj" % dmt, ozj, zj)
+        out.update({"%s_pre" % dmt: pre, "%s_loss" % dmt: torch.stack([ld["loss"], ld["rec_loss"]]), "%s_zt" % dmt: zt.contiguous(),
+                    "%s_zj" % dmt: zj.contiguous()})
+        with open(os.path.join(OUT, "state_dict_keys_amdmodel_camera_%s.json" % dmt), "w") as f:
+            json.dump({k: list(v.shape) for k, v in m.state_dict().items()}, f, indent=0)
+    save_file({k: v.contiguous() for k, v in out.items()}, os.path.join(OUT, "amd_model_camera.safetensors"))
+    # ---- AMDModel_Rec
+    cfg = configs.AMDMODEL_REC
+    torch.manual_seed(0)
+    m = ref.model_AMD.AMDModel_Rec(**cfg).eval()
+    sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 9)
+    m.load_state_dict(sd)
+    pre, zj, ld = m(video, ref_img)
+    opre, ozj, old = O.AMDModelRecOracle(sd, cfg).forward(video, ref_img)
+    check("AMDModel_Rec forward pre", opre, pre), check("AMDModel_Rec loss", old["loss"], ld["loss"])
+    save_file({k: v.contiguous() for k, v in dict(video=video, ref_img=ref_img, pre=pre, loss=ld["loss"].reshape(1)).items()},
+              os.path.join(OUT, "amd_model_rec.safetensors"))
+    with open(os.path.join(OUT, "state_dict_keys_amdmodel_rec.json"), "w") as f:
+        json.dump({k: list(v.shape) for k, v in m.state_dict().items()}, f, indent=0)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "camera_rec":
+        torch.set_grad_enabled(False)
+        camera_and_rec_models(ref_loader.load())
+    else:
+        main()

@@ -328,3 +328,53 @@ def test_reference_format_checkpoint_loads(tmp_path):
     assert sorted(m3.state_dict()) == sorted(want)
     hv.frozen_model(m3, "camera_motion_encoder")
     assert all(p.requires_grad != ("camera_motion_encoder" in k) for k, p in m3.named_parameters())
+
+
+def test_state_dict_keys_and_oracle_camera_rec_models(golden):
+    """f3: AMDModel_Camera / AMDModel_Rec (model_AMD.py:894-1661, 2840-3125): state-dict keys/shapes of the unmodified
+    reference, every AMD_models factory name of the reference exists, and the oracle restatements reproduce the committed
+    fixtures (forward / 3-step sample of AMDModel_Camera with both denoisers, forward of AMDModel_Rec)."""
+    import hivae_b200 as hv
+    assert sorted(hv.AMD_models) == sorted(["AMD_S", "AMD_S_Camera", "AMD_N", "AMD_L", "AMD_S_Rec", "AMD_S_RecSplit"])  # model_AMD.py:3203-3210
+    g = golden("amd_model_camera")
+    ts = torch.tensor([411.0]).repeat_interleave(4)
+    for dmt in ("spatial", "default"):
+        cfg = dict(configs.AMDMODEL_CAMERA, diffusion_model_type=dmt)
+        with open(os.path.join(ROOT, "tests", "golden", "state_dict_keys_amdmodel_camera_%s.json" % dmt)) as f:
+            ref = json.load(f)
+        m = hv.AMDModel_Camera(**cfg)
+        assert {k: list(v.shape) for k, v in m.state_dict().items()} == ref, dmt
+        sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 8)
+        orc = O.AMDModelCameraOracle(sd, cfg)
+        pre, vel, ld = orc.forward(g["video"], g["ref_img"], ts, g["z0"], g["video_grey"], g["ref_img_grey"], g["camera_mask"])
+        assert float((pre - g[dmt + "_pre"]).abs().max() / g[dmt + "_pre"].abs().max()) < 2e-5
+        zt, zj = orc.sample(g["video"], g["ref_img"], 3, g["z0"], g["video_grey"], g["ref_img_grey"], g["camera_mask"])
+        assert float((zt - g[dmt + "_zt"]).abs().max() / g[dmt + "_zt"].abs().max()) < 2e-5
+    with pytest.raises(NotImplementedError):
+        hv.AMDModel_Camera(**dict(configs.AMDMODEL_CAMERA, use_motiontemporal=True))  # not runnable upstream either
+    gr = golden("amd_model_rec")
+    with open(os.path.join(ROOT, "tests", "golden", "state_dict_keys_amdmodel_rec.json")) as f:
+        ref = json.load(f)
+    m = hv.AMDModel_Rec(**configs.AMDMODEL_REC)
+    assert {k: list(v.shape) for k, v in m.state_dict().items()} == ref
+    sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 9)
+    pre, zj, ld = O.AMDModelRecOracle(sd, configs.AMDMODEL_REC).forward(gr["video"], gr["ref_img"])
+    assert float((pre - gr["pre"]).abs().max() / gr["pre"].abs().max()) < 2e-5
+    with pytest.raises(AttributeError):
+        m.sample(gr["video"], gr["ref_img"])
+
+
+def test_oracle_random_masking_matches_reference_fixture(golden):
+    """random_masking (transformer.py:164-192, 558-586) in the oracle: with the reference's noise tensors the masked encode
+    of the small model reproduces what the unmodified reference returned (tests/golden/small_masked.safetensors)"""
+    g = golden("small_masked")
+    cfg = configs.SMALL
+    import hivae_b200 as hv
+    m = hv.AMDModel_New(**cfg)
+    sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 0)
+    orc = O.AMDOracle(sd, cfg["enc_nhead"], cfg["diffusion_attn_num_heads"], 16, 2, cfg["motion_token_num"])
+    video, ref_img = synth.split_clip(synth.synth_clip_latents(2, seed=1))
+    cam, osrc, otgt = orc.encode(video, ref_img, cam_keep=O.mask_keep(g["enc_cam_noise"], 0.5), obj_keep=O.mask_keep(g["enc_obj_noise"], 0.8))
+    assert cam.shape == g["enc_camera"].shape == (2, 16, 8, 8)
+    for a, b in ((cam, g["enc_camera"]), (osrc, g["enc_obj_src"]), (otgt, g["enc_obj_tgt"])):
+        assert float((a - b).abs().max() / b.abs().max()) < 2e-5

@@ -585,6 +585,36 @@ def test_amdmodel_golden(dev, golden, name):
     assert rel(zt, g[name + "_zt"]) <= TOL_F32 and torch.equal(zj, t("video"))
 
 
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, TOL_F32), (torch.bfloat16, TOL_BF16)])
+def test_amdmodel_camera_and_rec_golden(dev, golden, dtype, tol):
+    """f3: AMDModel_Camera (model_AMD.py:894-1661; both denoisers, 'decouple' camera stream) and AMDModel_Rec (2840-3125; the
+    non-diffusion AMDReconstructTransformerModel, transformer.py:703-854, need_norm_out encoders) against the unmodified
+    reference: training forward + losses, 3-step sample."""
+    import hivae_b200 as hv
+    g = golden("amd_model_camera")
+    t = lambda k: g[k].to(dev)
+    ts = torch.tensor([411.0]).repeat_interleave(4)
+    for dmt in ("spatial", "default"):
+        m = hv.AMDModel_Camera(**dict(configs.AMDMODEL_CAMERA, diffusion_model_type=dmt))
+        m.load_state_dict(synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 8))
+        m.to(dev).set_compute_dtype(dtype)
+        _fix_noise(m, g["z0"])
+        m.prepare_timestep = lambda batch_size, device, time_step=None: (torch.tensor([411.0]) if batch_size == 1 else ts).to(device)
+        kw = dict(video_grey=t("video_grey"), ref_img_grey=t("ref_img_grey"), camera_mask=t("camera_mask"))
+        pre, vel, ld = m(t("video"), t("ref_img"), **kw)
+        assert rel(pre, g[dmt + "_pre"]) <= tol, dmt
+        assert abs(float(ld["loss"]) - float(g[dmt + "_loss"][0])) <= tol * float(g[dmt + "_loss"][0])
+        zi, zt, zj = m.sample(t("video"), t("ref_img"), sample_step=3, **kw)
+        assert rel(zt, g[dmt + "_zt"]) <= tol and rel(zj, g[dmt + "_zj"]) <= 1e-5 and torch.equal(zi, t("ref_img_grey"))
+    gr = golden("amd_model_rec")
+    m = hv.AMDModel_Rec(**configs.AMDMODEL_REC)
+    m.load_state_dict(synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 9))
+    m.to(dev).set_compute_dtype(dtype)
+    pre, zj, ld = m(gr["video"].to(dev), gr["ref_img"].to(dev))
+    assert rel(pre, gr["pre"]) <= tol and set(ld) == {"loss", "rec_loss"}
+    assert abs(float(ld["loss"]) - float(gr["loss"])) <= tol * float(gr["loss"])
+
+
 def test_adaln_modules_standalone(dev):
     """AMDLayerNormZero / _OneVariable / 2Condition (modules.py:881-956) and AdaLayerNorm(chunk_dim=1)
     (958-1013) as stand-alone modules against the reference formulas, fp32 1e-5."""

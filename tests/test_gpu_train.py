@@ -218,6 +218,25 @@ def test_random_masking_golden(dev, golden, dtype, monkeypatch):
         assert abs(float(ld["loss"]) - float(g["loss"][0])) <= tol * float(g["loss"][0])
 
 
+def test_temporal_encoder_random_masking(dev, monkeypatch):
+    """MotionEncoderLearnTokenTemporalTransformer.random_masking (transformer.py:369-397; AMDModel's encoder) against the oracle
+    with the same noise"""
+    import hivae_b200 as hv
+    from hivae_b200 import transformer as T
+    kw = dict(img_height=32, img_width=32, img_inchannel=4, img_patch_size=2, motion_token_num=4, motion_channel=16,
+              need_norm_out=True, video_frames=4, num_attention_heads=2, attention_head_dim=64, num_layers=2)
+    m = hv.MotionEncoderLearnTokenTemporalTransformer(**kw)
+    sd = synth.synth_state_dict(((k, v.shape) for k, v in m.state_dict().items()), 3)
+    m.load_state_dict(sd)
+    m.to(dev)
+    x = torch.randn(2, 8, 4, 32, 32, generator=torch.Generator().manual_seed(12))
+    noise = torch.rand(16, 256, generator=torch.Generator().manual_seed(13))
+    monkeypatch.setattr(T, "mask_noise", lambda N, L, device: noise.to(device))
+    y = m(x.to(dev), mask_ratio=0.6)
+    ref = O.temporal_motion_encoder({"e." + k: v for k, v in sd.items()}, "e", x, 2, 4, keep=O.mask_keep(noise, 0.6))
+    assert y.shape == ref.shape and _err(y, ref)[0] <= 1e-4
+
+
 def test_linear_grads_odd_token_count(dev):
     """a token count that is not a multiple of 8: the contraction dimension of the weight-gradient GEMM is
     zero-padded; bf16 operands, fp64 reference"""
