@@ -42,6 +42,7 @@ SIGNATURES = {
     "hv_idwt2_haar": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "hv_freq_split3d": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp]),
     "hv_ln_modulate": (_i, [_vp, _i64, _i64, _i, _i, _i, _vp, _vp, _f, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _i, _vp]),
+    "hv_ln_modulate_save": (_i, [_vp, _i64, _i64, _i, _i, _i, _vp, _vp, _f, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp]),
     "hv_patch_embed": (_i, [_vp, _i, _vp, _i, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _i, _i64, _i, _i, _vp]),
     "hv_final_head": (_i, [_vp, _i64, _i64, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _vp, _i64, _i, _i, _vp, _vp, _i, _i, _i, _vp, _vp, _f, _vp]),
     "hv_timestep_embed": (_i, [_vp, _i64, _i, _vp, _i, _vp]),
@@ -67,6 +68,7 @@ SIGNATURES = {
     "hv_rope": (_i, [_vp, _vp, _i64, _i, _i, _i, _i64, _i, _f, _vp]),
     "hv_linear_f32": (_i, [_vp, _i, _i64, _vp, _i64, _i64, _i, _i, C.POINTER(HvEpilogue), _vp]),
     "hv_linear_bf16": (_i, [_vp, _i64, _vp, _i64, _i64, _i, _i, C.POINTER(HvEpilogue), _vp]),
+    "hv_linear_bf16_tn": (_i, [_vp, _i64, _vp, _i64, _i64, _i, _i64, C.POINTER(HvEpilogue), _vp]),
     "hv_reduce_workspace_doubles": (_i, []),
     "hv_mse_loss": (_i, [_vp, _vp, _i64, _vp, _vp, _vp]),
     "hv_grad_norm_clip_coef": (_i, [_vp, _i64, _f, _f, _vp, _vp, _vp]),

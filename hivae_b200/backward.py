@@ -15,6 +15,7 @@ from .ops import _chk_cuda, _dt, _p, _stream
 
 
 _SPLITK = os.environ.get("HV_WGRAD_SPLITK", "1") != "0"
+_TN = os.environ.get("HV_WGRAD_TN", "1") != "0"   # weight gradients on MN-major operands (no transposed copies); 0 = round-1 path
 
 
 def _timed(name):
@@ -321,6 +322,27 @@ def linear_grads(ctx, dy, x, w, dw=None, db=None, need_dx=True, dx_accum=None, t
         x_w = ops.convert(x.contiguous(), ctx.buf(tag + "_x16", (M, K), wd))
     else:
         dy_w, x_w = dy, x
+    dws = None if dw is None else (dw if isinstance(dw, (list, tuple)) else [dw])
+    if wd == torch.bfloat16 and _TN and ops.tn_ok(dy_w, x_w) and (dws is None or all(t.shape[0] % 8 == 0 for t in dws)):
+        # dW = dY^T X straight from dY and X as they lie in memory (MN-major tcgen05 operands): no transposed copies, any
+        # token count (TMA zero-fills the tail of the contraction)
+        if db is not None:
+            cs = colsum(dy)
+            dbs, o = (db if isinstance(db, (list, tuple)) else [db]), 0
+            for t in dbs:
+                ops.axpy(1.0, cs[o:o + t.numel()], t.view(-1))
+                o += t.numel()
+        o = 0
+        for t in dws or ():
+            n = t.shape[0]
+            t2 = t.view(n, K)
+            assert t2.dtype == torch.float32 and t2.is_contiguous()
+            e = ops.epi_residual(ops.Rows(t2.view(1, n, K), 0, n))
+            tiles = -(-n // 256) * -(-K // 256)
+            e.k_split = splitk if splitk is not None else max(1, min(16, 74 // tiles, M // 512))
+            ops.linear_tn(dy_w[:, o:o + n], x_w, e)
+            o += n
+        return dx
     Mp = -(-M // 8) * 8 if wd == torch.bfloat16 else M
     dyT = ctx.buf(tag + "_dyT", (N, Mp), wd)
     if Mp != M:
@@ -343,7 +365,7 @@ def linear_grads(ctx, dy, x, w, dw=None, db=None, need_dx=True, dx_accum=None, t
         if Mp != M:
             xT[:, M:].zero_()
         transpose2d(x_w, out=xT)
-        dws, o = (dw if isinstance(dw, (list, tuple)) else [dw]), 0
+        o = 0
         for t in dws:
             n = t.shape[0]
             t2 = t.view(n, K)

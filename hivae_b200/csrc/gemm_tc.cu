@@ -225,7 +225,10 @@ template <int BN, int MODEX, int CTAS>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_r, const __grid_constant__ CUtensorMap tmap_r2, long long M, int N, int K,
-               int use_reduce, const __grid_constant__ HvEpiDev epi) {
+               int use_reduce, int tn, const __grid_constant__ HvEpiDev epi) {
+    // tn != 0: "transposed-operand" product for weight gradients, out[M x N] = At^T Bt with At (K x M) and Bt (K x N) both
+    // row-major (K = tokens): the operands are MN-major in shared memory — TMA boxes of [64 tokens][64 columns = 128 B] —
+    // so dW = dY^T X needs no transposed copies of dY and X (round 1 paid three bf16 transposes per Linear)
     constexpr int MODE = MODEX & ~MODE_DUAL;
     constexpr bool DUAL = (MODEX & MODE_DUAL) != 0;  // second (pre-activation) output through tmap_r2; TMA-store path only
     constexpr int STAGES = num_stages<BN, MODEX, CTAS>();
@@ -283,7 +286,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 const int m0 = (int)(t / n_blocks) * TILE_M + (int)rank * BM, n0 = (int)(t % n_blocks) * BN + (int)rank * BNL;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
-                    if (CTAS == 2) {
+                    if (tn) {  // boxes of [64 k rows][64 columns]: 2 for the 128 rows of A, BNL / 64 for this CTA's share of B
+                        if (CTAS == 2) {
+                            const uint32_t bar = tc::mapa(tc::smem_u32(&full_bar[s]), 0);
+                            if (rank == 0) tc::mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+#pragma unroll
+                            for (int b = 0; b < BM / 64; ++b) tc::tma_load_2d_pair(smem_a(s) + b * 8192, &tmap_a, bar, m0 + 64 * b, kb * BK);
+#pragma unroll
+                            for (int b = 0; b < BNL / 64; ++b) tc::tma_load_2d_pair(smem_b(s) + b * 8192, &tmap_b, bar, n0 + 64 * b, kb * BK);
+                        } else {
+                            tc::mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+#pragma unroll
+                            for (int b = 0; b < BM / 64; ++b) tc::tma_load_2d(smem_a(s) + b * 8192, &tmap_a, &full_bar[s], m0 + 64 * b, kb * BK);
+#pragma unroll
+                            for (int b = 0; b < BNL / 64; ++b) tc::tma_load_2d(smem_b(s) + b * 8192, &tmap_b, &full_bar[s], n0 + 64 * b, kb * BK);
+                        }
+                    } else if (CTAS == 2) {
                         // both CTAs' bytes complete on the leader's barrier, which the leader armed for the pair
                         const uint32_t bar = tc::mapa(tc::smem_u32(&full_bar[s]), 0);
                         if (rank == 0) tc::mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
@@ -301,7 +319,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     } else if (warp == 1) {
         // ===================================================== MMA issuer (leader CTA only)
         if (lane == 0 && rank == 0) {
-            constexpr uint32_t idesc = tc::make_idesc_bf16(TILE_M, BN);
+            const uint32_t idesc = tc::make_idesc_bf16(TILE_M, BN) | (tn ? (3u << 15) : 0u);  // bits 15 / 16: A / B are MN-major
             int s = 0; uint32_t ph = 0; int a = 0; uint32_t aph = 0;
             for (long long it = unit; it < num_items; it += units) {
                 const int kb0 = (int)(it / num_tiles) * kb_per, kb1 = kb0 + kb_per < num_kb ? kb0 + kb_per : num_kb;
@@ -311,12 +329,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 for (int kb = kb0; kb < kb1; ++kb) {
                     tc::mbar_wait(&full_bar[s], ph);
                     tc::fence_after_sync();
-                    const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(smem_a(s)));
-                    const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(smem_b(s)));
+                    const uint64_t da = tn ? tc::make_smem_desc_mn128(tc::smem_u32(smem_a(s)), 8192) : tc::make_smem_desc_k128(tc::smem_u32(smem_a(s)));
+                    const uint64_t db = tn ? tc::make_smem_desc_mn128(tc::smem_u32(smem_b(s)), 8192) : tc::make_smem_desc_k128(tc::smem_u32(smem_b(s)));
+                    const uint64_t kstep = tn ? 128 : 2;  // K = 16 step: 16 rows x 128 B (MN-major) / 32 B inside the swizzle row (K-major), in 16-byte units
 #pragma unroll
-                    for (int k = 0; k < BK / 16; ++k) {  // +32 B per K=16 step inside the 128 B swizzle row
-                        if (CTAS == 2) tc::umma_bf16_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, ((kb - kb0) | k) != 0);
-                        else tc::umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, ((kb - kb0) | k) != 0);
+                    for (int k = 0; k < BK / 16; ++k) {
+                        if (CTAS == 2) tc::umma_bf16_pair(d_tmem, da + kstep * k, db + kstep * k, idesc, ((kb - kb0) | k) != 0);
+                        else tc::umma_bf16(d_tmem, da + kstep * k, db + kstep * k, idesc, ((kb - kb0) | k) != 0);
                     }
                     // frees the smem stage (in both CTAs) once these MMAs retire
                     if (CTAS == 2) tc::umma_commit_pair(&empty_bar[s]); else tc::umma_commit(&empty_bar[s]);
@@ -576,7 +595,7 @@ int max_pairs() {
 
 template <int BN, int MODE, int CTAS>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, const CUtensorMap& tr2, int use_reduce, int64_t M, int N,
-           int K, const HvEpiDev& d, cudaStream_t st) {
+           int K, const HvEpiDev& d, cudaStream_t st, int tn = 0) {
     auto kern = gemm_tc_kernel<BN, MODE, CTAS>;
     static bool configured = false;
     if (!configured) {
@@ -587,7 +606,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, 
     if constexpr (CTAS == 1) {
         const int sms = hv_num_sms();
         const int grid = (int)(tiles < sms ? tiles : sms);
-        kern<<<grid, THREADS, smem_bytes<BN, MODE, CTAS>(), st>>>(ta, tb, tr, tr2, (long long)M, N, K, use_reduce, d);
+        kern<<<grid, THREADS, smem_bytes<BN, MODE, CTAS>(), st>>>(ta, tb, tr, tr2, (long long)M, N, K, use_reduce, tn, d);
     } else {
         const int pairs = max_pairs<BN, MODE>();
         const int units = (int)(tiles < pairs ? tiles : pairs);
@@ -597,7 +616,7 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, 
         at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.gridDim = dim3(2 * units); cfg.blockDim = dim3(THREADS);
         cfg.dynamicSmemBytes = smem_bytes<BN, MODE, CTAS>(); cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
-        HV_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tr, tr2, (long long)M, N, K, use_reduce, d));
+        HV_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tr, tr2, (long long)M, N, K, use_reduce, tn, d));
     }
     HV_LAUNCH_CHECK();
     return HV_OK;
@@ -605,11 +624,11 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, 
 
 template <int MODE>
 int launch_mode(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, const CUtensorMap& tr2, int use_reduce, int64_t M,
-                int N, int K, const HvEpiDev& d, cudaStream_t st, int BN, int ctas) {
-    if (ctas == 2) return launch<256, MODE, 2>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st);
-    if (BN == 256) return launch<256, MODE, 1>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st);
+                int N, int K, const HvEpiDev& d, cudaStream_t st, int BN, int ctas, int tn = 0) {
+    if (ctas == 2) return launch<256, MODE, 2>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st, tn);
+    if (BN == 256) return launch<256, MODE, 1>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st, tn);
     if constexpr ((MODE & MODE_DUAL) != 0) { hv_set_error("hv_linear_bf16: dual output needs BN = 256"); return HV_EINVAL; }
-    else return launch<128, MODE, 1>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st);
+    else return launch<128, MODE, 1>(ta, tb, tr, tr2, use_reduce, M, N, K, d, st, tn);
 }
 
 // HV_GEMM_CTAS=1 forces the single-CTA kernel, HV_GEMM_REDUCE=0 the read-modify-write residual epilogue (A/B testing)
@@ -681,4 +700,46 @@ extern "C" int hv_linear_bf16(const void* A, int64_t lda, const void* W, int64_t
         case HV_EPI_RESIDUAL: return launch_mode<HV_EPI_RESIDUAL>(ta, tb, tr, tr, use_reduce, M, N, K, d, st, BN, ctas);
         default: return launch_mode<HV_EPI_QKNORM>(ta, tb, tr, tr, use_reduce, M, N, K, d, st, BN, ctas);
     }
+}
+
+// out[M x N] (+)= At^T Bt with At (K x M, row stride ldat) and Bt (K x N, row stride ldbt) both row-major bf16: the weight
+// gradient dW = dY^T X of nn.Linear (autograd of the Linears at model/modules.py:699-719) without transposed operand copies.
+// The contraction dimension K (tokens) may be anything (TMA zero-fills past the end); M, N, ldat, ldbt multiples of 8,
+// 16-byte aligned bases.  Epilogues: HV_EPI_STORE (fp32 / bf16) or HV_EPI_RESIDUAL without bias / gate (accumulate into an
+// fp32 M x N matrix, optionally split over K with `k_split` work items per tile, reduce-added in arrival order).
+extern "C" int hv_linear_bf16_tn(const void* At, int64_t ldat, const void* Bt, int64_t ldbt, int64_t M, int N, int64_t K,
+                                 const HvEpilogue* epi, void* stream) {
+    HV_REQUIRE(M > 0 && N > 0 && K > 0 && ldat >= M && ldbt >= N && K < (1ll << 31) && M < (1ll << 31), "hv_linear_bf16_tn: bad sizes");
+    HV_REQUIRE(M % 8 == 0 && N % 8 == 0 && ldat % 8 == 0 && ldbt % 8 == 0, "hv_linear_bf16_tn: M, N, ldat, ldbt must be multiples of 8 (16-byte TMA strides)");
+    HV_REQUIRE((reinterpret_cast<uintptr_t>(At) & 15) == 0 && (reinterpret_cast<uintptr_t>(Bt) & 15) == 0, "hv_linear_bf16_tn: operands must be 16-byte aligned");
+    HvEpiDev d;
+    int rc = hv_epilogue_prepare(epi, M, N, d, "hv_linear_bf16_tn");
+    if (rc) return rc;
+    HV_REQUIRE((d.e.mode == HV_EPI_STORE || d.e.mode == HV_EPI_RESIDUAL) && !d.e.out2, "hv_linear_bf16_tn: STORE or RESIDUAL epilogue only");
+    static const int want_ctas = env_int("HV_GEMM_CTAS", 2), want_reduce = env_int("HV_GEMM_REDUCE", 1);
+    const int BN = N > 128 ? 256 : 128;
+    const int ctas = (want_ctas == 2 && N > 128 && M > 256) ? 2 : 1;
+    CUtensorMap ta, tb, tr;
+    // the operands as K-row matrices: inner (contiguous) dimension = the output row / column index, boxes of 64 x 64
+    if ((rc = hv_make_tmap_bf16(At, K, (int)M, ldat, 64, &ta)) != HV_OK) return rc;
+    if ((rc = hv_make_tmap_bf16(Bt, K, N, ldbt, 64, &tb)) != HV_OK) return rc;
+    int use_reduce = 0;
+    if (d.e.mode == HV_EPI_RESIDUAL && want_reduce && d.vec_ok && d.e.L >= 32) {
+        if ((rc = make_tmap_residual(d.e.res, N, d.e.L, M / d.e.L, d.e.frame_rows, d.e.row_off, &tr)) != HV_OK) return rc;
+        use_reduce = 1;
+    } else {
+        tr = ta;
+    }
+    if (d.e.k_split > 1) {
+        HV_REQUIRE(d.e.mode == HV_EPI_RESIDUAL && !d.e.bias && !d.e.gate, "hv_linear_bf16_tn: k_split needs a plain residual epilogue (no bias, no gate)");
+        const int num_kb = (int)((K + 63) / 64);
+        int S = (use_reduce && d.e.k_split <= num_kb) ? d.e.k_split : (use_reduce ? num_kb : 1);
+        const int per = (num_kb + S - 1) / S;
+        d.e.k_split = (num_kb + per - 1) / per;
+    } else {
+        d.e.k_split = 1;
+    }
+    cudaStream_t st = hv_stream(stream);
+    if (d.e.mode == HV_EPI_STORE) return launch_mode<HV_EPI_STORE>(ta, tb, tr, tr, use_reduce, M, N, (int)K, d, st, BN, ctas, 1);
+    return launch_mode<HV_EPI_RESIDUAL>(ta, tb, tr, tr, use_reduce, M, N, (int)K, d, st, BN, ctas, 1);
 }

@@ -10,7 +10,7 @@ __global__ void __launch_bounds__(256) ln_modulate_kernel(
     const float* __restrict__ ln_w, const float* __restrict__ ln_b, float eps,
     const float* __restrict__ ada, long long ada_ld, int shift_col_mot, int scale_col_mot,
     int shift_col_img, int scale_col_img, int img_start, int img_len, int cond_div, int cond_mul,
-    OutT* __restrict__ out) {
+    OutT* __restrict__ out, float* __restrict__ save) {
     const int lane = threadIdx.x & 31;
     const long long r = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5);
     if (r >= rows) return;
@@ -24,6 +24,7 @@ __global__ void __launch_bounds__(256) ln_modulate_kernel(
     for (int j = 0; j < MAXNV; ++j)
         if (j < nv) {
             v[j] = xp[j * 32 + lane];
+            if (save) reinterpret_cast<float4*>(save + r * D)[j * 32 + lane] = v[j];  // training forward: the rows entering the norm
             sum += (v[j].x + v[j].y) + (v[j].z + v[j].w);
         }
     const float mean = hv_warp_sum(sum) / (float)D;
@@ -85,7 +86,7 @@ __global__ void __launch_bounds__(256, 2) ln_modulate2_kernel(
     const float* __restrict__ ln_w, const float* __restrict__ ln_b, float eps,
     const float* __restrict__ ada, long long ada_ld, int shift_col_mot, int scale_col_mot,
     int shift_col_img, int scale_col_img, int img_start, int img_len, int cond_div, int cond_mul,
-    LnSeg sg, OutT* __restrict__ out) {
+    LnSeg sg, OutT* __restrict__ out, float* __restrict__ save) {
     __shared__ float4 sA[NV * 32], sB[NV * 32];
     const int lane = threadIdx.x & 31, k0 = 2 * (threadIdx.x >> 5);
     // ---- which rows does this CTA own?  (dense output row, residual-buffer row, count)
@@ -173,14 +174,18 @@ __global__ void __launch_bounds__(256, 2) ln_modulate2_kernel(
         z.z = fmaf((v[j].z - mv) * rv, A.z, B.z); z.w = fmaf((v[j].w - mv) * rv, A.w, B.w);
         emit(o0, c4, y);
         if (two) emit(o0 + D, c4, z);
+        if (save) {  // training forward: keep the fp32 rows entering the norm (the backward's x), dense
+            reinterpret_cast<float4*>(save + (rd + k0) * D)[c4] = u[j];
+            if (two) reinterpret_cast<float4*>(save + (rd + k0 + 1) * D)[c4] = v[j];
+        }
     }
 }
 
-extern "C" int hv_ln_modulate(const float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D,
-                              const float* ln_w, const float* ln_b, float eps,
-                              const float* ada, int64_t ada_ld, int shift_col_mot, int scale_col_mot,
-                              int shift_col_img, int scale_col_img, int img_start, int img_len,
-                              int cond_div, int cond_mul, void* out, int out_dtype, void* stream) {
+static int ln_modulate_impl(const float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D,
+                            const float* ln_w, const float* ln_b, float eps,
+                            const float* ada, int64_t ada_ld, int shift_col_mot, int scale_col_mot,
+                            int shift_col_img, int scale_col_img, int img_start, int img_len,
+                            int cond_div, int cond_mul, void* out, int out_dtype, float* save, void* stream) {
     HV_REQUIRE(D > 0 && D % 128 == 0 && D <= 2048, "hv_ln_modulate: D=%d must be a multiple of 128 and <= 2048", D);
     HV_REQUIRE(frames >= 0 && L >= 0 && row_off >= 0 && row_off + L <= frame_rows, "hv_ln_modulate: bad row range");
     HV_REQUIRE(out_dtype == HV_F32 || out_dtype == HV_BF16, "hv_ln_modulate: bad out dtype");
@@ -209,15 +214,15 @@ extern "C" int hv_ln_modulate(const float* res, int64_t frames, int64_t frame_ro
             img_start = is; img_len = sg.b;  // the kernel derives the segment starts from these
         }
         dim3 grid((unsigned)ctas), block(256);
-        if (out_dtype == HV_F32) { if (nv == 8) ln_modulate2_kernel<8, float><<<grid, block, 0, st>>>(LN_ARGS, (float*)out); else ln_modulate2_kernel<4, float><<<grid, block, 0, st>>>(LN_ARGS, (float*)out); }
-        else { if (nv == 8) ln_modulate2_kernel<8, __nv_bfloat16><<<grid, block, 0, st>>>(LN_ARGS, (__nv_bfloat16*)out); else ln_modulate2_kernel<4, __nv_bfloat16><<<grid, block, 0, st>>>(LN_ARGS, (__nv_bfloat16*)out); }
+        if (out_dtype == HV_F32) { if (nv == 8) ln_modulate2_kernel<8, float><<<grid, block, 0, st>>>(LN_ARGS, (float*)out, save); else ln_modulate2_kernel<4, float><<<grid, block, 0, st>>>(LN_ARGS, (float*)out, save); }
+        else { if (nv == 8) ln_modulate2_kernel<8, __nv_bfloat16><<<grid, block, 0, st>>>(LN_ARGS, (__nv_bfloat16*)out, save); else ln_modulate2_kernel<4, __nv_bfloat16><<<grid, block, 0, st>>>(LN_ARGS, (__nv_bfloat16*)out, save); }
         HV_LAUNCH_CHECK();
         return HV_OK;
     }
     dim3 grid((unsigned)((rows + 7) / 8)), block(256);
 #define LN_LAUNCH(MAXNV, T)                                                                                   \
     ln_modulate_kernel<MAXNV, T><<<grid, block, 0, st>>>(res, rows, map, D, ln_w, ln_b, eps, ada, ada_ld,     \
-        shift_col_mot, scale_col_mot, shift_col_img, scale_col_img, img_start, img_len, cond_div, cond_mul, (T*)out)
+        shift_col_mot, scale_col_mot, shift_col_img, scale_col_img, img_start, img_len, cond_div, cond_mul, (T*)out, save)
     if (out_dtype == HV_F32) {
         if (nv <= 4) LN_LAUNCH(4, float); else if (nv <= 8) LN_LAUNCH(8, float); else LN_LAUNCH(16, float);
     } else {
@@ -226,6 +231,26 @@ extern "C" int hv_ln_modulate(const float* res, int64_t frames, int64_t frame_ro
 #undef LN_LAUNCH
     HV_LAUNCH_CHECK();
     return HV_OK;
+}
+
+extern "C" int hv_ln_modulate(const float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D,
+                              const float* ln_w, const float* ln_b, float eps,
+                              const float* ada, int64_t ada_ld, int shift_col_mot, int scale_col_mot,
+                              int shift_col_img, int scale_col_img, int img_start, int img_len,
+                              int cond_div, int cond_mul, void* out, int out_dtype, void* stream) {
+    return ln_modulate_impl(res, frames, frame_rows, row_off, L, D, ln_w, ln_b, eps, ada, ada_ld, shift_col_mot, scale_col_mot,
+                            shift_col_img, scale_col_img, img_start, img_len, cond_div, cond_mul, out, out_dtype, nullptr, stream);
+}
+// training forward: the same kernel also writes the fp32 rows it normalises to `save` (dense, frames * L x D) — what the
+// backward of the norm needs — instead of a separate gather pass over the residual stream
+extern "C" int hv_ln_modulate_save(const float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D,
+                                   const float* ln_w, const float* ln_b, float eps,
+                                   const float* ada, int64_t ada_ld, int shift_col_mot, int scale_col_mot,
+                                   int shift_col_img, int scale_col_img, int img_start, int img_len,
+                                   int cond_div, int cond_mul, void* out, int out_dtype, float* save, void* stream) {
+    HV_REQUIRE(save != nullptr, "hv_ln_modulate_save: save is NULL");
+    return ln_modulate_impl(res, frames, frame_rows, row_off, L, D, ln_w, ln_b, eps, ada, ada_ld, shift_col_mot, scale_col_mot,
+                            shift_col_img, scale_col_img, img_start, img_len, cond_div, cond_mul, out, out_dtype, save, stream);
 }
 
 // ---------------------------------------------------------------------------------------------

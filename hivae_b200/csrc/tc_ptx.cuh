@@ -120,6 +120,18 @@ __device__ __forceinline__ uint64_t make_smem_desc_k128(uint32_t saddr) {
     d |= (uint64_t)2 << 61;                   // layout type SWIZZLE_128B
     return d;
 }
+// MN-major operand tile with SWIZZLE_128B (cute: Swizzle<3,4,3> o ((8,n),(8,k)):((1,LBO),(8,SBO)) in 16-byte units): the
+// MN dimension is contiguous in memory; a TMA box of [rows = K][64 elements = 128 B] is one "atom column" of 64 MN
+// elements; 8-row (K) groups are 1024 B apart (SBO), successive 64-element chunks along MN are `lbo_bytes` apart (LBO).
+__device__ __forceinline__ uint64_t make_smem_desc_mn128(uint32_t saddr, uint32_t lbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
 // kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, shape M x N
 __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);

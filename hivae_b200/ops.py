@@ -192,15 +192,19 @@ class Ada:
     cond_mul: int = 1
 
 
-def ln_modulate(rows, ln_w, ln_b, eps, out, ada=None, shift_mot=0, scale_mot=0, shift_img=0, scale_img=0):
-    _chk_cuda(rows.res, ln_w, ln_b, out)
+def ln_modulate(rows, ln_w, ln_b, eps, out, ada=None, shift_mot=0, scale_mot=0, shift_img=0, scale_img=0, save=None):
+    """save: optional fp32 (M, D) buffer that receives the rows entering the norm (training forward)"""
+    _chk_cuda(rows.res, ln_w, ln_b, out, save)
     t = ada.table if ada is not None else None
-    tok = _prof("ln_modulate", 0, rows.M * rows.D * (4 + out.element_size()))
-    _lib.check(_lib.load().hv_ln_modulate(
-        _p(rows.res), rows.frames, rows.frame_rows, rows.row_off, rows.L, rows.D, _p(ln_w), _p(ln_b), float(eps),
-        _p(t), t.shape[1] if t is not None else 0, shift_mot, scale_mot, shift_img, scale_img,
-        rows.img_start, rows.img_len, ada.cond_div if ada else 1, ada.cond_mul if ada else 1,
-        _p(out), _dt(out), _stream()))
+    tok = _prof("ln_modulate", 0, rows.M * rows.D * (4 + out.element_size() + (4 if save is not None else 0)))
+    args = (_p(rows.res), rows.frames, rows.frame_rows, rows.row_off, rows.L, rows.D, _p(ln_w), _p(ln_b), float(eps),
+            _p(t), t.shape[1] if t is not None else 0, shift_mot, scale_mot, shift_img, scale_img,
+            rows.img_start, rows.img_len, ada.cond_div if ada else 1, ada.cond_mul if ada else 1, _p(out), _dt(out))
+    if save is None:
+        _lib.check(_lib.load().hv_ln_modulate(*args, _stream()))
+    else:
+        assert save.dtype == torch.float32 and tuple(save.shape) == (rows.M, rows.D)
+        _lib.check(_lib.load().hv_ln_modulate_save(*args, _p(save), _stream()))
     _prof_end(tok)
     return out
 
@@ -369,6 +373,26 @@ def linear(A, W, epi):
         tok = _prof("gemm_simt", 2.0 * M * N * K, 4.0 * (M * K + N * K + M * N))
         _lib.check(lib.hv_linear_f32(_p(A), _dt(A), A.stride(0), _p(W), W.stride(0), M, N, K, C.byref(epi), _stream()))
     _prof_end(tok)
+
+
+def linear_tn(At, Bt, epi):
+    """epilogue(At^T @ Bt) for row-major bf16 At (K, M), Bt (K, N): the weight gradient dY^T X without transposed copies"""
+    _lib.require_device()
+    for t in (At, Bt):
+        if not t.is_cuda or t.dim() != 2 or t.stride(1) != 1 or t.dtype != torch.bfloat16:
+            raise RuntimeError("hivae_b200.linear_tn needs 2-D bf16 CUDA tensors with unit column stride")
+    K, M = At.shape
+    N = Bt.shape[1]
+    assert Bt.shape[0] == K
+    tok = _prof("gemm_tc", 2.0 * M * N * K, 2.0 * K * (M + N) + 4.0 * M * N)
+    _lib.check(_lib.load().hv_linear_bf16_tn(_p(At), At.stride(0), _p(Bt), Bt.stride(0), M, N, K, C.byref(epi), _stream()))
+    _prof_end(tok)
+
+
+def tn_ok(At, Bt):
+    return (At.dtype == Bt.dtype == torch.bfloat16 and At.stride(1) == 1 and Bt.stride(1) == 1 and At.shape[1] % 8 == 0
+            and Bt.shape[1] % 8 == 0 and At.stride(0) % 8 == 0 and Bt.stride(0) % 8 == 0 and At.data_ptr() % 16 == 0
+            and Bt.data_ptr() % 16 == 0)
 
 
 # ------------------------------------------------------------------ attention

@@ -86,8 +86,8 @@ def block_train(tape, ctx, bp, rows, drows, geom, sink, pfx, tag, ada=None, dada
     sv = lambda name, shape, dtype=None: ctx.buf("sv_%s_%s" % (tag, name), shape, dtype or cd)
     F = bp.w1.shape[0]
 
-    x0 = ops.rows_gather(rows, sv("x0", (M, D), torch.float32))
-    xn1 = ops.ln_modulate(rows, bp.n1w, bp.n1b, bp.eps, sv("xn1", (M, D)), ada, **c1)
+    x0 = sv("x0", (M, D), torch.float32)   # the rows entering norm1, written by the LayerNorm kernel itself
+    xn1 = ops.ln_modulate(rows, bp.n1w, bp.n1b, bp.eps, sv("xn1", (M, D)), ada, save=x0, **c1)
     if bp.kind == "cross":
         Mk = kv.shape[0]
         q_pre, q = sv("q_pre", (M, D)), sv("q", (M, D))
@@ -111,8 +111,8 @@ def block_train(tape, ctx, bp, rows, drows, geom, sink, pfx, tag, ada=None, dada
         B.gate_residual(rows, y1, ada, *g1)
     else:
         ops.linear(att, bp.wo, ops.epi_residual(rows, bp.bo))
-    x1 = ops.rows_gather(rows, sv("x1", (M, D), torch.float32))
-    xn2 = ops.ln_modulate(rows, bp.n2w, bp.n2b, bp.eps, sv("xn2", (M, D)), ada, **c2)
+    x1 = sv("x1", (M, D), torch.float32)
+    xn2 = ops.ln_modulate(rows, bp.n2w, bp.n2b, bp.eps, sv("xn2", (M, D)), ada, save=x1, **c2)
     hpre, h = sv("hpre", (M, F)), sv("h", (M, F))
     ops.linear(xn2, bp.w1, ops.epi_store(h, bp.b1, gelu=True, pre=hpre))   # GELU output + pre-GELU activations
     if gated:

@@ -98,6 +98,13 @@ int hv_ln_modulate(const float* res, int64_t frames, int64_t frame_rows, int row
                    int shift_col_img, int scale_col_img, int img_start, int img_len,
                    int cond_div, int cond_mul, void* out, int out_dtype, void* stream);
 
+/* the same, for the training forward: also writes the fp32 rows entering the norm to `save` (dense frames*L x D) */
+int hv_ln_modulate_save(const float* res, int64_t frames, int64_t frame_rows, int row_off, int L, int D,
+                        const float* ln_w, const float* ln_b, float eps,
+                        const float* ada, int64_t ada_ld, int shift_col_mot, int scale_col_mot,
+                        int shift_col_img, int scale_col_img, int img_start, int img_len,
+                        int cond_div, int cond_mul, void* out, int out_dtype, float* save, void* stream);
+
 /* PatchEmbed (model/modules.py:858-879) = Conv2d(k=s=p) + bias, fused with the
  * 2-D sincos and temporal sincos adds of transformer.py:1985-1988 / 130-141 /
  * 506-514.  Input channels come from two NCHW tensors (in1: C1 channels, in2: C2
@@ -281,6 +288,13 @@ int hv_linear_f32(const void* A, int a_dtype, int64_t lda, const float* W, int64
  * lda/ldw % 8 == 0, 16-byte aligned bases. */
 int hv_linear_bf16(const void* A, int64_t lda, const void* W, int64_t ldw,
                    int64_t M, int N, int K, const HvEpilogue* epi, void* stream);
+
+/* Weight-gradient form of the same kernel: out[M x N] (+)= At^T Bt with At (K x M) and Bt (K x N) row-major bf16 — dW = dY^T X
+ * of nn.Linear's backward with dY and X used as they lie in memory (MN-major tcgen05 operands, no transposed copies).
+ * K (tokens) arbitrary; M, N, ldat, ldbt % 8 == 0, 16-byte aligned bases.  Epilogue: HV_EPI_STORE, or HV_EPI_RESIDUAL
+ * without bias / gate (accumulates into fp32, `k_split` allowed). */
+int hv_linear_bf16_tn(const void* At, int64_t ldat, const void* Bt, int64_t ldbt, int64_t M, int N, int64_t K,
+                      const HvEpilogue* epi, void* stream);
 
 /* ------------------------------------------------------------------ attention
  * softmax(Q K^T * scale) V per (sequence, head), head_dim = hd, no dropout

@@ -257,6 +257,30 @@ def test_linear_grads_odd_token_count(dev):
         assert _err(dw, 2 * (dyd.t() @ xd))[0] <= 1e-2
 
 
+def test_linear_tn_weight_gradient_gemm(dev):
+    """hv_linear_bf16_tn: out (+)= At^T Bt on MN-major tcgen05 operands (dW = dY^T X without transposed copies) against fp64:
+    single CTA and CTA-pair tiles, ragged token counts (TMA zero fill), column-sliced operands, split-K accumulation"""
+    from hivae_b200 import ops
+    gen = torch.Generator().manual_seed(11)
+    for K, M, N, ks in ((1000, 256, 128, 1), (4099, 512, 384, 4), (777, 1024, 1024, 3), (64, 128, 64, 1), (35072 // 8, 3072, 1024, 8)):
+        At = torch.randn(K, M, generator=gen).to(dev).bfloat16()
+        Bt = torch.randn(K, N, generator=gen).to(dev).bfloat16()
+        ref = At.double().t() @ Bt.double()
+        out = torch.empty(M, N, device=dev)
+        ops.linear_tn(At, Bt, ops.epi_store(out))
+        assert _err(out, ref)[0] <= 2e-3, (K, M, N)
+        acc = torch.ones(M, N, device=dev)
+        e = ops.epi_residual(ops.Rows(acc.view(1, M, N), 0, M))
+        e.k_split = ks
+        ops.linear_tn(At, Bt, e)
+        assert _err(acc, ref + 1.0)[0] <= 2e-3, (K, M, N, ks)
+    wide = torch.randn(500, 768, generator=gen).to(dev).bfloat16()   # a column slice as At (the q / k / v blocks of d(qkv))
+    Bt = torch.randn(500, 256, generator=gen).to(dev).bfloat16()
+    out = torch.empty(256, 256, device=dev)
+    ops.linear_tn(wide[:, 256:512], Bt, ops.epi_store(out))
+    assert _err(out, wide[:, 256:512].double().t() @ Bt.double())[0] <= 2e-3
+
+
 def test_block_forward_after_adamw_step_uses_new_weights(dev):
     """FlatArena + AdamW update the parameters through raw pointers; the prepared bf16 / packed copies of
     a block must follow"""
