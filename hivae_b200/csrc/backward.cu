@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(256) colsum_partial_bf16x2_kernel(const __nv_b
         partial[(long long)blockIdx.y * N + n + ty] = s;
     }
 }
-// bf16, eight columns per thread (16-byte loads, a warp reads 512 B of a row), four rows in flight per thread;
+// bf16, eight columns per thread (16-byte loads, a warp reads 512 B of a row), eight rows in flight per thread;
 // N, ld multiples of 8 and a 16-byte aligned base
 __global__ void __launch_bounds__(256) colsum_partial_bf16x8_kernel(const __nv_bfloat16* __restrict__ x, long long M, int N, long long ld,
                                                                     float* __restrict__ partial) {
@@ -157,12 +157,12 @@ __global__ void __launch_bounds__(256) colsum_partial_bf16x8_kernel(const __nv_b
         const long long step = (long long)gridDim.y * 8;
         long long m = blockIdx.y * 8ll + ty;
         const __nv_bfloat16* p = x + n;
-        for (; m + 3 * step < M; m += 4 * step) {
-            uint4 v[4];
+        for (; m + 7 * step < M; m += 8 * step) {  // eight 16-byte loads in flight per thread (64 KB per SM at 2 CTAs)
+            uint4 v[8];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(p + (m + u * step) * ld));
+            for (int u = 0; u < 8; ++u) v[u] = __ldg(reinterpret_cast<const uint4*>(p + (m + u * step) * ld));
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < 8; ++u) {
                 const uint32_t w[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
