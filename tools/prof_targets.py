@@ -54,6 +54,23 @@ elif what == "dwt":
     for _ in range(reps):
         bands, ll = hv.dwt_pyramid(x, 3)
         hv.iwt_pyramid(bands, ll)
+elif what == "attn_bwd_dit":
+    from hivae_b200 import backward as Bk
+    frames, L, D, H = 64, 274, 1024, 16  # DiT object block, 4 clips (train step)
+    M = frames * L
+    qkv = torch.randn(M, 3 * D, device=dev).bfloat16()
+    o, do = torch.randn(M, D, device=dev).bfloat16(), torch.randn(M, D, device=dev).bfloat16()
+    g = engine.dense_geom(frames, L)
+    for _ in range(reps):
+        Bk.attention_backward(qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:], o, do, g.seqs, H, L, L, g.qmap, g.kvmap, 0.125)
+elif what == "wgrad":
+    M = 17536  # 4 clips x 16 frames x 274 tokens
+    dy, x = torch.randn(M, 4 * D, device=dev).bfloat16(), torch.randn(M, D, device=dev).bfloat16()
+    dw = torch.zeros(4 * D, D, device=dev)
+    for _ in range(reps):
+        e = ops.epi_residual(ops.Rows(dw.view(1, 4 * D, D), 0, 4 * D))
+        e.k_split = 1
+        ops.linear_tn(dy, x, e)
 elif what == "attn_bwd":
     from hivae_b200 import backward as Bk
     frames, L, D, H = 128, 264, 512, 8  # object motion encoder, 4 clips
