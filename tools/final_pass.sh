@@ -25,7 +25,10 @@ bash tools/ncu_one.sh gemm_ff1 gemm_tc_kernel
 bash tools/ncu_one.sh gemm_out gemm_tc_kernel
 bash tools/ncu_one.sh wgrad gemm_tc_kernel
 bash tools/ncu_one.sh attn attn_tc_kernel
-bash tools/ncu_one.sh attn_bwd_dit 'attn_bwd_d'
+bash tools/ncu_one.sh attn_bwd_dit attn_bwd_dq_tc
+cp gpurun_out/prof_attn_bwd_dit.ncu-rep gpurun_out/prof_attn_bwd_dq.ncu-rep 2>/dev/null
+bash tools/ncu_one.sh attn_bwd_dit attn_bwd_dkv_tc
+mv gpurun_out/prof_attn_bwd_dit.ncu-rep gpurun_out/prof_attn_bwd_dkv.ncu-rep 2>/dev/null
 bash tools/ncu_one.sh ln ln_modulate
 bash tools/ncu_one.sh dwt 'pyramid|dwt2'
 ls -la gpurun_out | head -80
