@@ -259,6 +259,7 @@ def _train_leg(torch, dist, dev, m, rank, world, timed, steps=3, warmup=2):
     fn = lambda: step.step(video, ref_img)
     for _ in range(warmup):
         out = fn()
+    tuned = step.tune_schedule(video, ref_img)     # untimed: picks when the gradient buckets go out (N > 1 only)
     ms = timed(fn, steps) / steps
     rec = {"workload": "configs[4]: train step, default model 695M, bf16 compute / fp32 master + AdamW, %d clips per GPU, "
                        "synthetic latents, random init" % TRAIN_CLIPS_PER_GPU,
@@ -279,19 +280,15 @@ def _train_leg(torch, dist, dev, m, rank, world, timed, steps=3, warmup=2):
             red.finish()
         only_allreduce()
         ms_ar = timed(only_allreduce, steps) / steps
-        modes = {}
-        for name, frac in (("fine_grained_ddp_style", 0.0), ("all_at_the_end", 1.0)):
-            red.issue_after = frac
-            fn()
-            modes[name] = round(timed(fn, steps) / steps - ms_local, 3)
-        red.issue_after = 0.9
+        chosen = red.issue_after
+        names = {0.0: "fine_grained_ddp_style", 0.9: "coarse_denoiser_then_encoders", 1.0: "all_at_the_end"}
         busbw = 2.0 * (world - 1) / world * step.arena.numel * 4 / (ms_ar * 1e6)
         rec.update(allreduce_ms=round(ms_ar, 3), allreduce_exposed_ms=round(max(ms - ms_local, 0.0), 3),
                    ms_per_step_without_collective=round(ms_local, 2), allreduce_busbw_gbs=round(busbw, 1),
                    buckets=len(red.buckets),
-                   schedule="coarse: the denoiser's buckets (first 90 %) go out when its backward is done and overlap the "
-                            "encoders' backward, the rest at the end",
-                   allreduce_exposed_ms_other_schedules=modes)
+                   schedule="%s (issue_after=%.1f), picked by TrainStep.tune_schedule in the warm-up: forward+backward ms per "
+                            "candidate, max over ranks" % (names.get(chosen, "custom"), chosen),
+                   schedule_candidates_fwd_bwd_ms={names.get(c, str(c)): round(v, 3) for c, v in tuned.items()})
     return rec if rank == 0 else None
 
 

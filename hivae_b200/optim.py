@@ -328,6 +328,34 @@ class TrainStep:
         scale = self.reducer.finish() if self.reducer is not None else 1.0
         return loss, rec, scale
 
+    def tune_schedule(self, video, ref_img, candidates=(0.0, 0.9, 1.0), steps=2):
+        """Pick the all-reduce issue point (GradAllReducer.issue_after) that gives the shortest forward+backward on THIS
+        box: each candidate is run `steps` times after one untimed pass, timed with CUDA events, max over ranks.  Nothing is
+        applied to the weights (no clip / AdamW), so it can run at any point of a job.  Which schedule wins depends on how
+        many SMs NCCL takes for the ring/NVLS kernel at this world size, hence measured instead of assumed.
+        Returns {candidate: ms}."""
+        import torch.distributed as dist
+        if self.reducer is None or self.reducer.world == 1 or not video.is_cuda:
+            return {}
+        out = {}
+        for c in candidates:
+            self.reducer.issue_after = c
+            self.forward_backward(video, ref_img)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            dist.barrier(self.reducer.group)
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(steps):
+                self.forward_backward(video, ref_img)
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1) / steps], device=video.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.reducer.group)
+            out[c] = float(t)
+        self.reducer.issue_after = min(out, key=out.get)   # the same on every rank: t is the max over ranks
+        self.arena.zero_grad()
+        return out
+
     def step(self, video, ref_img, time_step=None, noise=None):
         """returns {'loss', 'diff_loss', 'rec_loss', 'grad_norm'} as 0-dim device tensors (no host synchronisation)"""
         loss, rec, scale = self.forward_backward(video, ref_img, time_step, noise)
