@@ -277,71 +277,78 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const uint32_t tmem_base = tmem_slot;
 
     if (warp == 0) {
-        // ===================================================== TMA producer (one per CTA)
-        if (lane == 0) {
+        // ===================================================== TMA producer (one per CTA).  All 32 lanes run the loop with
+        // warp-uniform values and one elected lane issues (tc_ptx.cuh *_w): under `if (lane == 0)` ptxas wraps every TMA /
+        // MMA instruction in an ELECT + R2UR.BROADCAST loop (270 clk per MMA against 65, tools/probes/mma_probe.cu)
+        {
             int s = 0; uint32_t ph = 0;
+            const uint32_t sbase = tc::smem_u32(smem);
             for (long long it = unit; it < num_items; it += units) {
                 const long long t = it % num_tiles;
-                const int kb0 = (int)(it / num_tiles) * kb_per, kb1 = kb0 + kb_per < num_kb ? kb0 + kb_per : num_kb;
-                const int m0 = (int)(t / n_blocks) * TILE_M + (int)rank * BM, n0 = (int)(t % n_blocks) * BN + (int)rank * BNL;
+                const int kb0 = (int)tc::warp_uniform((uint32_t)((int)(it / num_tiles) * kb_per)), kb1 = kb0 + kb_per < num_kb ? kb0 + kb_per : num_kb;
+                const int m0 = (int)tc::warp_uniform((uint32_t)((int)(t / n_blocks) * TILE_M + (int)rank * BM));
+                const int n0 = (int)tc::warp_uniform((uint32_t)((int)(t % n_blocks) * BN + (int)rank * BNL));
                 for (int kb = kb0; kb < kb1; ++kb) {
                     tc::mbar_wait(&empty_bar[s], ph ^ 1);
+                    const uint32_t sa = sbase + (uint32_t)(s * STAGE_BYTES), sb = sa + BM * BK * 2;
                     if (tn) {  // boxes of [64 k rows][64 columns]: 2 for the 128 rows of A, BNL / 64 for this CTA's share of B
                         if (CTAS == 2) {
                             const uint32_t bar = tc::mapa(tc::smem_u32(&full_bar[s]), 0);
-                            if (rank == 0) tc::mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
+                            if (rank == 0) tc::mbar_expect_tx_w(&full_bar[s], 2 * STAGE_BYTES);
 #pragma unroll
-                            for (int b = 0; b < BM / 64; ++b) tc::tma_load_2d_pair(smem_a(s) + b * 8192, &tmap_a, bar, m0 + 64 * b, kb * BK);
+                            for (int b = 0; b < BM / 64; ++b) tc::tma_load_2d_pair_w(sa + b * 8192, &tmap_a, bar, m0 + 64 * b, kb * BK);
 #pragma unroll
-                            for (int b = 0; b < BNL / 64; ++b) tc::tma_load_2d_pair(smem_b(s) + b * 8192, &tmap_b, bar, n0 + 64 * b, kb * BK);
+                            for (int b = 0; b < BNL / 64; ++b) tc::tma_load_2d_pair_w(sb + b * 8192, &tmap_b, bar, n0 + 64 * b, kb * BK);
                         } else {
-                            tc::mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                            tc::mbar_expect_tx_w(&full_bar[s], STAGE_BYTES);
 #pragma unroll
-                            for (int b = 0; b < BM / 64; ++b) tc::tma_load_2d(smem_a(s) + b * 8192, &tmap_a, &full_bar[s], m0 + 64 * b, kb * BK);
+                            for (int b = 0; b < BM / 64; ++b) tc::tma_load_2d_w(sa + b * 8192, &tmap_a, &full_bar[s], m0 + 64 * b, kb * BK);
 #pragma unroll
-                            for (int b = 0; b < BNL / 64; ++b) tc::tma_load_2d(smem_b(s) + b * 8192, &tmap_b, &full_bar[s], n0 + 64 * b, kb * BK);
+                            for (int b = 0; b < BNL / 64; ++b) tc::tma_load_2d_w(sb + b * 8192, &tmap_b, &full_bar[s], n0 + 64 * b, kb * BK);
                         }
                     } else if (CTAS == 2) {
                         // both CTAs' bytes complete on the leader's barrier, which the leader armed for the pair
                         const uint32_t bar = tc::mapa(tc::smem_u32(&full_bar[s]), 0);
-                        if (rank == 0) tc::mbar_expect_tx(&full_bar[s], 2 * STAGE_BYTES);
-                        tc::tma_load_2d_pair(smem_a(s), &tmap_a, bar, kb * BK, m0);
-                        tc::tma_load_2d_pair(smem_b(s), &tmap_b, bar, kb * BK, n0);
+                        if (rank == 0) tc::mbar_expect_tx_w(&full_bar[s], 2 * STAGE_BYTES);
+                        tc::tma_load_2d_pair_w(sa, &tmap_a, bar, kb * BK, m0);
+                        tc::tma_load_2d_pair_w(sb, &tmap_b, bar, kb * BK, n0);
                     } else {
-                        tc::mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                        tc::tma_load_2d(smem_a(s), &tmap_a, &full_bar[s], kb * BK, m0);
-                        tc::tma_load_2d(smem_b(s), &tmap_b, &full_bar[s], kb * BK, n0);
+                        tc::mbar_expect_tx_w(&full_bar[s], STAGE_BYTES);
+                        tc::tma_load_2d_w(sa, &tmap_a, &full_bar[s], kb * BK, m0);
+                        tc::tma_load_2d_w(sb, &tmap_b, &full_bar[s], kb * BK, n0);
                     }
                     if (++s == STAGES) { s = 0; ph ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ===================================================== MMA issuer (leader CTA only)
-        if (lane == 0 && rank == 0) {
+        // ===================================================== MMA issuer (leader CTA only; warp-converged, one elected lane issues)
+        if (rank == 0) {
             const uint32_t idesc = tc::make_idesc_bf16(TILE_M, BN) | (tn ? (3u << 15) : 0u);  // bits 15 / 16: A / B are MN-major
+            const uint32_t tbase = tc::warp_uniform(tmem_base), sbase = tc::smem_u32(smem);
             int s = 0; uint32_t ph = 0; int a = 0; uint32_t aph = 0;
             for (long long it = unit; it < num_items; it += units) {
-                const int kb0 = (int)(it / num_tiles) * kb_per, kb1 = kb0 + kb_per < num_kb ? kb0 + kb_per : num_kb;
+                const int kb0 = (int)tc::warp_uniform((uint32_t)((int)(it / num_tiles) * kb_per)), kb1 = kb0 + kb_per < num_kb ? kb0 + kb_per : num_kb;
                 if (CTAS == 2) tc::mbar_wait_cluster(&tmem_empty_bar[a], aph ^ 1); else tc::mbar_wait(&tmem_empty_bar[a], aph ^ 1);
                 tc::fence_after_sync();
-                const uint32_t d_tmem = tmem_base + (uint32_t)(a * BN);
+                const uint32_t d_tmem = tbase + (uint32_t)(a * BN);
                 for (int kb = kb0; kb < kb1; ++kb) {
                     tc::mbar_wait(&full_bar[s], ph);
                     tc::fence_after_sync();
-                    const uint64_t da = tn ? tc::make_smem_desc_mn128(tc::smem_u32(smem_a(s)), 8192) : tc::make_smem_desc_k128(tc::smem_u32(smem_a(s)));
-                    const uint64_t db = tn ? tc::make_smem_desc_mn128(tc::smem_u32(smem_b(s)), 8192) : tc::make_smem_desc_k128(tc::smem_u32(smem_b(s)));
+                    const uint32_t sa = sbase + (uint32_t)(s * STAGE_BYTES), sb = sa + BM * BK * 2;
+                    const uint64_t da = tn ? tc::make_smem_desc_mn128(sa, 8192) : tc::make_smem_desc_k128(sa);
+                    const uint64_t db = tn ? tc::make_smem_desc_mn128(sb, 8192) : tc::make_smem_desc_k128(sb);
                     const uint64_t kstep = tn ? 128 : 2;  // K = 16 step: 16 rows x 128 B (MN-major) / 32 B inside the swizzle row (K-major), in 16-byte units
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) {
-                        if (CTAS == 2) tc::umma_bf16_pair(d_tmem, da + kstep * k, db + kstep * k, idesc, ((kb - kb0) | k) != 0);
-                        else tc::umma_bf16(d_tmem, da + kstep * k, db + kstep * k, idesc, ((kb - kb0) | k) != 0);
+                        if (CTAS == 2) tc::umma_bf16_pair_w(d_tmem, da + kstep * k, db + kstep * k, idesc, ((kb - kb0) | k) != 0);
+                        else tc::umma_bf16_w(d_tmem, da + kstep * k, db + kstep * k, idesc, ((kb - kb0) | k) != 0);
                     }
                     // frees the smem stage (in both CTAs) once these MMAs retire
-                    if (CTAS == 2) tc::umma_commit_pair(&empty_bar[s]); else tc::umma_commit(&empty_bar[s]);
+                    if (CTAS == 2) tc::umma_commit_pair_w(&empty_bar[s]); else tc::umma_commit_w(&empty_bar[s]);
                     if (++s == STAGES) { s = 0; ph ^= 1; }
                 }
-                if (CTAS == 2) tc::umma_commit_pair(&tmem_full_bar[a]); else tc::umma_commit(&tmem_full_bar[a]);  // accumulator complete
+                if (CTAS == 2) tc::umma_commit_pair_w(&tmem_full_bar[a]); else tc::umma_commit_w(&tmem_full_bar[a]);  // accumulator complete
                 if ((a ^= 1) == 0) aph ^= 1;
             }
         }
