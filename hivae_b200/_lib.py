@@ -71,6 +71,8 @@ SIGNATURES = {
     "hv_linear_bf16_tn": (_i, [_vp, _i64, _vp, _i64, _i64, _i, _i64, C.POINTER(HvEpilogue), _vp]),
     "hv_reduce_workspace_doubles": (_i, []),
     "hv_mse_loss": (_i, [_vp, _vp, _i64, _vp, _vp, _vp]),
+    "hv_mse_loss_static": (_i, [_vp, _vp, _i64, _vp, _vp]),
+    "hv_mse_loss_static_max_elements": (_i, []),
     "hv_grad_norm_clip_coef": (_i, [_vp, _i64, _f, _f, _vp, _vp, _vp]),
     "hv_adamw_clip": (_i, [_vp, _vp, _vp, _vp, _i64, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, _i64, _f, _vp, _vp]),
     "hv_scale_by_device": (_i, [_vp, _i64, _vp, _f, _vp]),

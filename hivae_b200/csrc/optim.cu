@@ -143,6 +143,50 @@ extern "C" int hv_mse_loss(const float* pre, const float* gt, int64_t n, double*
     return HV_OK;
 }
 
+// ---- hv_mse_loss_static: hv_mse_loss for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that
+// forbid cudaMalloc).  No counterpart in the reference.  The fp64 partial sums
+// live in a file-scope device array instead of a caller-provided workspace: HV_MSE_STATIC_MAX_PARTIALS doubles = 8 KB, held by
+// every GPU that loads the library until the process exits.  In host code `g_mse_static_scratch` is only a host-side
+// stand-in for the symbol, NOT a device address: the device address is looked up once per device, with that device
+// current, through cudaGetSymbolAddress and cached; that pointer is what the kernels get.
+// Every call shares the array: calls that overlap on the GPU (different streams, or concurrent graph launches) race.
+// Nothing has to be cleared between calls: the first kernel overwrites partials [0, grid) and the second reads exactly
+// those, so stale values of an earlier (larger) call are never read.
+constexpr int HV_MSE_STATIC_MAX_PARTIALS = 1024;
+static __device__ __align__(256) double g_mse_static_scratch[HV_MSE_STATIC_MAX_PARTIALS];
+
+extern "C" int hv_mse_loss_static_max_elements() { return HV_MSE_STATIC_MAX_PARTIALS * TPB * 4; }
+
+extern "C" int hv_mse_loss_static(const float* pre, const float* gt, int64_t n, float* out, void* stream) {
+    HV_REQUIRE(n > 0 && pre && gt && out, "hv_mse_loss_static: bad arguments");
+    HV_REQUIRE(((reinterpret_cast<uintptr_t>(pre) | reinterpret_cast<uintptr_t>(gt)) & 15) == 0, "hv_mse_loss_static: inputs must be 16-byte aligned");
+    const int grid = stream_grid(n >> 2);  // same launch geometry as hv_mse_loss: bit-identical result
+    if (grid > HV_MSE_STATIC_MAX_PARTIALS) {
+        hv_set_error("hv_mse_loss_static: %lld elements need %d partial sums, the static scratch holds %d (at most %d elements; "
+                     "use hv_mse_loss with a caller-provided workspace for larger inputs)",
+                     (long long)n, grid, HV_MSE_STATIC_MAX_PARTIALS, HV_MSE_STATIC_MAX_PARTIALS * TPB * 4);
+        return HV_EINVAL;
+    }
+    constexpr int MAX_DEVICES = 64;
+    static double* scratch_of[MAX_DEVICES] = {};  // device address of the symbol, per device
+    int dev = -1;
+    HV_CUDA(cudaGetDevice(&dev));
+    HV_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "hv_mse_loss_static: device ordinal out of range");
+    if (scratch_of[dev] == nullptr) {  // set-up, once per device, with that device current (do it before a graph capture)
+        double* ptr = nullptr;
+        HV_CUDA(cudaGetSymbolAddress((void**)&ptr, g_mse_static_scratch));
+        HV_REQUIRE(ptr != nullptr, "hv_mse_loss_static: cudaGetSymbolAddress returned a null address");
+        scratch_of[dev] = ptr;
+    }
+    double* ws = scratch_of[dev];
+    cudaStream_t st = hv_stream(stream);
+    sumsq_partial_kernel<0><<<grid, TPB, 0, st>>>(pre, gt, n, ws);
+    HV_LAUNCH_CHECK();
+    sumsq_final_kernel<0><<<1, TPB, 0, st>>>(ws, grid, (double)n, 0.f, out);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
 // out[0] = ||grad_scale * g||_2 over the flat gradient arena, out[1] = min(1, max_norm / (out[0] + 1e-6))
 // (torch.nn.utils.clip_grad_norm_, called through accelerator.clip_grad_norm_ at train_amd.py:492)
 extern "C" int hv_grad_norm_clip_coef(const float* g, int64_t n, float grad_scale, float max_norm, double* workspace,

@@ -326,6 +326,14 @@ int hv_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, con
 int hv_reduce_workspace_doubles(void);
 /* out[0] = mean((pre-gt)^2): model/loss.py:13-14 (F.mse_loss), the diff_loss / rec_loss of model_AMD.py:1997-2000 */
 int hv_mse_loss(const float* pre, const float* gt, int64_t n, double* workspace, float* out, void* stream);
+/* hv_mse_loss without a caller-provided workspace and without ANY allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, serving loops).
+ * The fp64 partial sums live in a static device array of 1024 doubles (8 KB per GPU that loads the library, until exit);
+ * inputs that need more (n > hv_mse_loss_static_max_elements() = 1 048 576 on a B200) are rejected with HV_EINVAL.
+ * Same result as hv_mse_loss, bit for bit.  All calls share the array: calls that overlap on the GPU race.  The first
+ * call on a device looks the array's address up (cudaGetSymbolAddress): make it before a graph capture begins. */
+int hv_mse_loss_static(const float* pre, const float* gt, int64_t n, float* out, void* stream);
+int hv_mse_loss_static_max_elements(void);
 /* out[0] = ||grad_scale*g||_2, out[1] = min(1, max_norm/(out[0]+1e-6)): torch.nn.utils.clip_grad_norm_
  * behind accelerator.clip_grad_norm_ (train_amd.py:491-492).  out: 2 floats on the device. */
 int hv_grad_norm_clip_coef(const float* g, int64_t n, float grad_scale, float max_norm, double* workspace,
