@@ -154,7 +154,7 @@ __device__ __forceinline__ void issue_s_like(uint32_t d_tmem, const uint8_t* a_t
         const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(b_rows + r0 * 128));
         const uint32_t idesc = tc::make_idesc_bf16(QT, cols);
 #pragma unroll
-        for (int k = 0; k < HD / 16; ++k) tc::umma_bf16(d_tmem + (uint32_t)r0, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, k != 0);
+        for (int k = 0; k < HD / 16; ++k) tc::umma_bf16_w(d_tmem + (uint32_t)r0, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, k != 0);
     }
 }
 // PV-like product: D[128 x 64] = A[128 x kdim] B[kdim x 64], A staged K-major in 64-column chunks, B = [kdim rows][64] rows of
@@ -164,7 +164,7 @@ __device__ __forceinline__ void issue_pv_like(uint32_t d_tmem, const uint8_t* a_
     for (int j = 0; j < kdim / 16; ++j) {
         const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(a_stage + (j >> 2) * TBYTES)) + (uint64_t)(2 * (j & 3));
         const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(b_rows + j * 2048));
-        tc::umma_bf16(d_tmem, da, db, idesc, j != 0);
+        tc::umma_bf16_w(d_tmem, da, db, idesc, j != 0);
     }
 }
 
@@ -221,47 +221,47 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
-    const uint32_t tmem_base = tmem_slot;
+    const uint32_t tmem_base = tc::warp_uniform(tmem_slot);  // uniform register: operand of warp-converged MMA issue
 
     if (warp >= 10) {
         regs_service();  // idle members of the service warpgroup
     } else if (warp == 9) {
         // ===================================================== TMA producer
         regs_service();
-        if (lane == 0) {
+        {   // all 32 lanes, warp-uniform values; one elected lane issues (tc_ptx.cuh *_w)
             long long T = 0, it = 0;
             for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
                 const long long seq = w / a.heads;
                 const int col = (int)(w - seq * a.heads) * HD;
                 const long long qrow0 = seq * a.q_sa, kvrow0 = seq * a.kv_sa;
                 tc::mbar_wait(&kv_free, (uint32_t)((it & 1) ^ 1));
-                tc::mbar_expect_tx(&kv_full, 2 * KP32 * 128);
+                tc::mbar_expect_tx_w(&kv_full, 2 * KP32 * 128);
                 for (int j = 0; j < KP32 / 32; ++j) {
-                    tc::tma_load_2d(Ks + j * 4096, &tk, &kv_full, col, (int)(kvrow0 + j * 32));
-                    tc::tma_load_2d(Vs + j * 4096, &tv, &kv_full, col, (int)(kvrow0 + j * 32));
+                    tc::tma_load_2d_w(tc::smem_u32(Ks + j * 4096), &tk, &kv_full, col, (int)(kvrow0 + j * 32));
+                    tc::tma_load_2d_w(tc::smem_u32(Vs + j * 4096), &tv, &kv_full, col, (int)(kvrow0 + j * 32));
                 }
                 for (int i = 0; i < nq; ++i, ++T) {
                     tc::mbar_wait(&q_free, (uint32_t)((T & 1) ^ 1));
-                    tc::mbar_expect_tx(&q_full, TBYTES);
-                    for (int j = 0; j < 4; ++j) tc::tma_load_2d(Qs + j * 4096, &tq, &q_full, col, (int)(qrow0 + i * QT + j * 32));
+                    tc::mbar_expect_tx_w(&q_full, TBYTES);
+                    for (int j = 0; j < 4; ++j) tc::tma_load_2d_w(tc::smem_u32(Qs + j * 4096), &tq, &q_full, col, (int)(qrow0 + i * QT + j * 32));
                     tc::mbar_wait(&do_free, (uint32_t)((T & 1) ^ 1));
-                    tc::mbar_expect_tx(&do_full, TBYTES);
-                    for (int j = 0; j < 4; ++j) tc::tma_load_2d(dOs + j * 4096, &tdo, &do_full, col, (int)(qrow0 + i * QT + j * 32));
+                    tc::mbar_expect_tx_w(&do_full, TBYTES);
+                    for (int j = 0; j < 4; ++j) tc::tma_load_2d_w(tc::smem_u32(dOs + j * 4096), &tdo, &do_full, col, (int)(qrow0 + i * QT + j * 32));
                 }
             }
         }
     } else if (warp == 8) {
         // ===================================================== MMA issuer
         regs_service();
-        if (lane == 0) {
+        {   // all 32 lanes, warp-uniform values; one elected lane issues (tc_ptx.cuh *_w)
             long long T = 0, it = 0;
             bool ahead = false;  // S of the current tile was already issued (before the previous tile's dQ)
             auto issue_s = [&](long long Tn) {
                 tc::mbar_wait(&q_full, (uint32_t)(Tn & 1));
                 tc::fence_after_sync();
                 issue_s_like(tmem_base + S_COL, Qs, Ks, KP, HB);           // S = Q K^T
-                tc::umma_commit(&s_full);
-                tc::umma_commit(&q_free);
+                tc::umma_commit_w(&s_full);
+                tc::umma_commit_w(&q_free);
             };
             for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
                 tc::mbar_wait(&kv_full, (uint32_t)(it & 1));
@@ -272,15 +272,15 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                     tc::mbar_wait(&s_free, ph);                            // P~ is in registers, S may be overwritten
                     tc::fence_after_sync();
                     issue_s_like(tmem_base + S_COL, dOs, Vs, KP, HB);      // dP = dO V^T
-                    tc::umma_commit(&dp_full);
-                    tc::umma_commit(&do_free);
+                    tc::umma_commit_w(&dp_full);
+                    tc::umma_commit_w(&do_free);
                     tc::mbar_wait(&ds_full, ph);                           // dS~ staged, dP consumed; the previous dQ was read back
                     tc::fence_after_sync();
                     ahead = i + 1 < nq;
                     if (ahead) issue_s(T + 1);                             // next tile of the same item first: the compute warps need it first
                     issue_pv_like(tmem_base + ACC_COL, dSs, Ks, KP);       // dQ~ = dS~ K
-                    tc::umma_commit(&dq_full);
-                    if (i == nq - 1) tc::umma_commit(&kv_free);
+                    tc::umma_commit_w(&dq_full);
+                    if (i == nq - 1) tc::umma_commit_w(&kv_free);
                 }
             }
         }
@@ -436,31 +436,31 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_cons
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
-    const uint32_t tmem_base = tmem_slot;
+    const uint32_t tmem_base = tc::warp_uniform(tmem_slot);  // uniform register: operand of warp-converged MMA issue
 
     if (warp >= 10) {
         regs_service();  // idle members of the service warpgroup
     } else if (warp == 9) {
         // ===================================================== TMA producer
         regs_service();
-        if (lane == 0) {
+        {   // all 32 lanes, warp-uniform values; one elected lane issues (tc_ptx.cuh *_w)
             long long T = 0, it = 0;
             for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
                 const long long seq = w / a.heads;
                 const int col = (int)(w - seq * a.heads) * HD;
                 const long long qrow0 = seq * a.q_sa, kvrow0 = seq * a.kv_sa;
                 tc::mbar_wait(&qdo_free, (uint32_t)((it & 1) ^ 1));
-                tc::mbar_expect_tx(&qdo_full, 2 * QP32 * 128);
+                tc::mbar_expect_tx_w(&qdo_full, 2 * QP32 * 128);
                 for (int j = 0; j < QP32 / 32; ++j) {
-                    tc::tma_load_2d(Qs + j * 4096, &tq, &qdo_full, col, (int)(qrow0 + j * 32));
-                    tc::tma_load_2d(dOs + j * 4096, &tdo, &qdo_full, col, (int)(qrow0 + j * 32));
+                    tc::tma_load_2d_w(tc::smem_u32(Qs + j * 4096), &tq, &qdo_full, col, (int)(qrow0 + j * 32));
+                    tc::tma_load_2d_w(tc::smem_u32(dOs + j * 4096), &tdo, &qdo_full, col, (int)(qrow0 + j * 32));
                 }
                 for (int t = 0; t < nk; ++t, ++T) {
                     tc::mbar_wait(&kt_free, (uint32_t)((T & 1) ^ 1));
-                    tc::mbar_expect_tx(&kt_full, 2 * TBYTES);
+                    tc::mbar_expect_tx_w(&kt_full, 2 * TBYTES);
                     for (int j = 0; j < 4; ++j) {
-                        tc::tma_load_2d(Kt + j * 4096, &tk, &kt_full, col, (int)(kvrow0 + t * QT + j * 32));
-                        tc::tma_load_2d(Vt + j * 4096, &tv, &kt_full, col, (int)(kvrow0 + t * QT + j * 32));
+                        tc::tma_load_2d_w(tc::smem_u32(Kt + j * 4096), &tk, &kt_full, col, (int)(kvrow0 + t * QT + j * 32));
+                        tc::tma_load_2d_w(tc::smem_u32(Vt + j * 4096), &tv, &kt_full, col, (int)(kvrow0 + t * QT + j * 32));
                     }
                 }
             }
@@ -468,14 +468,14 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_cons
     } else if (warp == 8) {
         // ===================================================== MMA issuer
         regs_service();
-        if (lane == 0) {
+        {   // all 32 lanes, warp-uniform values; one elected lane issues (tc_ptx.cuh *_w)
             long long T = 0, it = 0;
             bool ahead = false;
             auto issue_st = [&](long long Tn) {
                 tc::mbar_wait(&kt_full, (uint32_t)(Tn & 1));
                 tc::fence_after_sync();
                 issue_s_like(tmem_base + S_COL, Kt, Qs, QP, HB);            // S^T = K_t Q^T
-                tc::umma_commit(&st_full);
+                tc::umma_commit_w(&st_full);
             };
             for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
                 tc::mbar_wait(&qdo_full, (uint32_t)(it & 1));
@@ -485,17 +485,17 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_cons
                     tc::mbar_wait(&p_full, ph);                             // P^T in registers + staged; accumulators of the previous tile read back
                     tc::fence_after_sync();
                     issue_s_like(tmem_base + S_COL, Vt, dOs, QP, HB);       // dP^T = V_t dO^T over the S^T columns
-                    tc::umma_commit(&dpt_full);
-                    tc::umma_commit(&kt_free);                              // K_t / V_t retire: the producer prefetches the next key tile
+                    tc::umma_commit_w(&dpt_full);
+                    tc::umma_commit_w(&kt_free);                              // K_t / V_t retire: the producer prefetches the next key tile
                     issue_pv_like(tmem_base + ACC_COL, Ps, dOs, QP);        // dV_t = P^T dO
-                    tc::umma_commit(&dv_done);
+                    tc::umma_commit_w(&dv_done);
                     tc::mbar_wait(&ds_full, ph);                            // dS^T staged (after dv_done), dP^T consumed
                     tc::fence_after_sync();
                     ahead = t + 1 < nk;
                     if (ahead) issue_st(T + 1);
                     issue_pv_like(tmem_base + ACC_COL + HD, Ps, Qs, QP);    // dK_t = dS^T Q
-                    tc::umma_commit(&acc_full);
-                    if (t == nk - 1) tc::umma_commit(&qdo_free);
+                    tc::umma_commit_w(&acc_full);
+                    if (t == nk - 1) tc::umma_commit_w(&qdo_free);
                 }
             }
         }

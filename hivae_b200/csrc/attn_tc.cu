@@ -116,20 +116,20 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
     tc::fence_before_sync();
     __syncthreads();
     tc::fence_after_sync();
-    const uint32_t tmem_base = tmem_slot;
+    const uint32_t tmem_base = tc::warp_uniform(tmem_slot);  // uniform register: operand of warp-converged MMA issue
 
     if (warp == 9) {
-        // ===================================================== TMA producer
-        if (lane == 0) {
+        // ===================================================== TMA producer (all 32 lanes, one elected lane issues: tc_ptx.cuh *_w)
+        {
             long long T = 0, it = 0;
             auto load_q = [&](long long qrow0, int col, int i) {
                 const int b = (int)(T & 1);
                 tc::mbar_wait(&q_free[b], (uint32_t)(((T >> 1) & 1) ^ 1));
-                tc::mbar_expect_tx(&q_full[b], QBYTES);
+                tc::mbar_expect_tx_w(&q_full[b], QBYTES);
                 const bool tail = a.Lq - i * QT <= 32;  // tail tile: the same 32-row box goes to all four lane quarters
 #pragma unroll
                 for (int j = 0; j < QT / 32; ++j)
-                    tc::tma_load_2d(Qs + b * QBYTES + j * 4096, &tq, &q_full[b], col, (int)(qrow0 + i * QT + (tail ? 0 : j * 32)));
+                    tc::tma_load_2d_w(tc::smem_u32(Qs + b * QBYTES + j * 4096), &tq, &q_full[b], col, (int)(qrow0 + i * QT + (tail ? 0 : j * 32)));
                 ++T;
             };
             for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
@@ -138,21 +138,21 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                 const long long qrow0 = seq * a.q_sa, kvrow0 = seq * a.kv_sa;
                 const int kb = (int)(it & 1);
                 tc::mbar_wait(&k_free[kb], (uint32_t)(((it >> 1) & 1) ^ 1));
-                tc::mbar_expect_tx(&k_full[kb], KP32 * 128);
+                tc::mbar_expect_tx_w(&k_full[kb], KP32 * 128);
                 for (int j = 0; j < KP32 / 32; ++j)
-                    tc::tma_load_2d(Ks + kb * KP32 * 128 + j * 4096, &tk, &k_full[kb], col, (int)(kvrow0 + j * 32));
+                    tc::tma_load_2d_w(tc::smem_u32(Ks + kb * KP32 * 128 + j * 4096), &tk, &k_full[kb], col, (int)(kvrow0 + j * 32));
                 load_q(qrow0, col, 0);
                 if (nq > 1) load_q(qrow0, col, 1);
                 tc::mbar_wait(&v_free, (uint32_t)((it & 1) ^ 1));
-                tc::mbar_expect_tx(&v_full, KP32 * 128);
+                tc::mbar_expect_tx_w(&v_full, KP32 * 128);
                 for (int j = 0; j < KP32 / 32; ++j)
-                    tc::tma_load_2d(Vs + j * 4096, &tv, &v_full, col, (int)(kvrow0 + j * 32));
+                    tc::tma_load_2d_w(tc::smem_u32(Vs + j * 4096), &tv, &v_full, col, (int)(kvrow0 + j * 32));
                 for (int i = 2; i < nq; ++i) load_q(qrow0, col, i);
             }
         }
     } else if (warp == 8) {
         // ===================================================== MMA issuer
-        if (lane == 0 && total > 0) {
+        if (total > 0) {  // all 32 lanes with warp-uniform values, one elected lane issues (tc_ptx.cuh *_w)
             auto issue_s = [&](long long T, int h) {  // S(T), key half h -> ring buffer (2T + h) % 3
                 const long long it = T / nq;
                 const int ncols = h ? KP - HB : HB;
@@ -162,22 +162,22 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                     const uint32_t idesc = tc::make_idesc_bf16(QT, ncols);
                     const uint32_t d = tmem_base + S_COL + (uint32_t)((2 * T + h) % 3) * SBUF;
 #pragma unroll
-                    for (int k = 0; k < HD / 16; ++k) tc::umma_bf16(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, k != 0);
+                    for (int k = 0; k < HD / 16; ++k) tc::umma_bf16_w(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, k != 0);
                 }
-                tc::umma_commit(&s_full[T & 1][h]);  // one barrier per (tile parity, half): never more than one phase ahead of a waiter
+                tc::umma_commit_w(&s_full[T & 1][h]);  // one barrier per (tile parity, half): never more than one phase ahead of a waiter
             };
             auto issue_pv = [&]() {
                 constexpr uint32_t idesc = tc::make_idesc_bf16_bmn(QT, HD);
                 for (int j = 0; j < KP / 16; ++j) {
                     const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(Ps + (j >> 2) * QBYTES)) + (uint64_t)(2 * (j & 3));
                     const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(Vs + j * 2048));  // 16 keys x 128 B, MN-major
-                    tc::umma_bf16(tmem_base + O_COL, da, db, idesc, j != 0);
+                    tc::umma_bf16_w(tmem_base + O_COL, da, db, idesc, j != 0);
                 }
-                tc::umma_commit(&o_full);
+                tc::umma_commit_w(&o_full);
             };
             auto after_s = [&](long long T) {  // both halves of S(T) issued: its Q buffer and (last tile) its K buffer retire with them
-                tc::umma_commit(&q_free[T & 1]);
-                if (T % nq == nq - 1) tc::umma_commit(&k_free[(T / nq) & 1]);
+                tc::umma_commit_w(&q_free[T & 1]);
+                if (T % nq == nq - 1) tc::umma_commit_w(&k_free[(T / nq) & 1]);
             };
             tc::mbar_wait(&k_full[0], 0);
             tc::mbar_wait(&q_full[0], 0);
@@ -200,7 +200,7 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ C
                 // is only read back after their next max pass
                 if (T + 1 < total) { issue_s(T + 1, 1); after_s(T + 1); }
                 issue_pv();
-                if (i == nq - 1) tc::umma_commit(&v_free);
+                if (i == nq - 1) tc::umma_commit_w(&v_free);
             }
         }
     } else {
