@@ -75,6 +75,7 @@ SIGNATURES = {
     "hv_mse_loss_static_max_elements": (_i, []),
     "hv_grad_norm_clip_coef": (_i, [_vp, _i64, _f, _f, _vp, _vp, _vp]),
     "hv_adamw_clip": (_i, [_vp, _vp, _vp, _vp, _i64, C.c_double, C.c_double, C.c_double, C.c_double, C.c_double, _i64, _f, _vp, _vp]),
+    "hv_adamw_clip_devstate": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, C.c_double, C.c_double, C.c_double, C.c_double, _f, _vp, _vp]),
     "hv_scale_by_device": (_i, [_vp, _i64, _vp, _f, _vp]),
     "hv_train_chunk_rows": (_i, []),
     "hv_gate_bwd": (_i, [_vp, _i64, _i64, _i, _i, _i, _vp, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp, _i, _vp, _vp, _i64, _vp]),

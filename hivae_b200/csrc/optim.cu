@@ -91,9 +91,20 @@ __device__ __forceinline__ void adam_one(float& p, float g, float& m, float& v, 
     p = p + (-a.step_size) * (m / denom);
 }
 
+// device-resident optimizer state for replayed CUDA graphs (hv_adamw_clip_devstate): state[0] = step count, state[1] = lr;
+// one thread advances the step and forms the step-dependent scalars in double exactly as the host path does
+__global__ void adam_state_kernel(double* __restrict__ state, float* __restrict__ derived, double beta1, double beta2, double weight_decay) {
+    const double step = state[0] + 1.0, lr = state[1];
+    state[0] = step;
+    derived[0] = (float)(1.0 - lr * weight_decay);          // decay
+    derived[1] = (float)(lr / (1.0 - pow(beta1, step)));    // step_size
+    derived[2] = (float)sqrt(1.0 - pow(beta2, step));       // bc2_sqrt
+}
+
 __global__ void __launch_bounds__(TPB) adamw_clip_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                          float* __restrict__ v, long long n, AdamArgs a,
-                                                         const float* __restrict__ clip_coef) {
+                                                         const float* __restrict__ clip_coef, const float* __restrict__ derived = nullptr) {
+    if (derived) { a.decay = __ldg(derived); a.step_size = __ldg(derived + 1); a.bc2_sqrt = __ldg(derived + 2); }
     const float coef = clip_coef ? __ldg(clip_coef) : 1.0f;
     const long long n4 = n >> 2;
     float4* p4 = reinterpret_cast<float4*>(p);
@@ -216,6 +227,26 @@ extern "C" int hv_adamw_clip(float* p, const float* g, float* m, float* v, int64
     a.step_size = (float)(lr / bc1);
     a.bc2_sqrt = (float)sqrt(bc2);
     adamw_clip_kernel<<<stream_grid(n >> 2), TPB, 0, hv_stream(stream)>>>(p, g, m, v, n, a, clip_coef);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
+// hv_adamw_clip with the step count and the learning rate in DEVICE memory (state: 2 doubles {steps done, lr}; derived:
+// 3 floats of scratch), so that a captured CUDA graph of the whole train step can be replayed: each launch advances
+// state[0] by one and uses bias corrections of the new step; the host changes lr by writing state[1].
+extern "C" int hv_adamw_clip_devstate(float* p, const float* g, float* m, float* v, int64_t n, double* state, float* derived,
+                                      double beta1, double beta2, double eps, double weight_decay, float grad_scale,
+                                      const float* clip_coef, void* stream) {
+    HV_REQUIRE(n > 0 && p && g && m && v && state && derived, "hv_adamw_clip_devstate: bad arguments");
+    HV_REQUIRE(((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0,
+               "hv_adamw_clip_devstate: arenas must be 16-byte aligned");
+    AdamArgs a;
+    a.decay = 1.f; a.step_size = 0.f; a.bc2_sqrt = 1.f;  // replaced by `derived` in the kernel
+    a.omb1 = (float)(1.0 - beta1); a.beta2 = (float)beta2; a.omb2 = (float)(1.0 - beta2); a.eps = (float)eps; a.grad_scale = grad_scale;
+    cudaStream_t st = hv_stream(stream);
+    adam_state_kernel<<<1, 1, 0, st>>>(state, derived, beta1, beta2, weight_decay);
+    HV_LAUNCH_CHECK();
+    adamw_clip_kernel<<<stream_grid(n >> 2), TPB, 0, st>>>(p, g, m, v, n, a, clip_coef, derived);
     HV_LAUNCH_CHECK();
     return HV_OK;
 }

@@ -123,6 +123,25 @@ class AdamW:
         self.exp_avg_sq = torch.zeros_like(self.arena.flat)
         self.step_count = 0
         self.param_groups = [{"lr": lr, "betas": betas, "eps": eps, "weight_decay": weight_decay, "params": self.arena.params}]
+        self._state = None      # device-resident {steps done, lr} (fp64) once enable_device_state() was called
+        self._derived = None
+
+    def enable_device_state(self):
+        """Keep the step count and the learning rate in device memory (hv_adamw_clip_devstate): needed for a step that is
+        replayed from a CUDA graph, where host scalars would be frozen at their capture-time values.  Change the learning
+        rate with set_lr() afterwards (a scheduler that writes param_groups[0]['lr'] is picked up by step() in eager mode
+        only)."""
+        dev = self.arena.flat.device
+        self._state = torch.tensor([float(self.step_count), float(self.param_groups[0]["lr"])], dtype=torch.float64, device=dev)
+        self._derived = torch.zeros(4, dtype=torch.float32, device=dev)
+        self._state_lr = float(self.param_groups[0]["lr"])
+
+    def set_lr(self, lr):
+        self.param_groups[0]["lr"] = lr
+        self.lr = lr
+        if self._state is not None and float(lr) != self._state_lr:
+            self._state[1:2].fill_(float(lr))
+            self._state_lr = float(lr)
 
     def step(self, grad_scale=1.0):
         _lib.require_device()
@@ -132,6 +151,16 @@ class AdamW:
         self.step_count += 1
         g = self.param_groups[0]
         clip = C.c_void_p(a.clip.data_ptr() + 4) if a.clip is not None else None
+        if self._state is not None:
+            if not torch.cuda.is_current_stream_capturing():
+                self.set_lr(g["lr"])
+            _lib.check(_lib.load().hv_adamw_clip_devstate(_p(a.flat), _p(a.grad), _p(self.exp_avg), _p(self.exp_avg_sq), a.numel,
+                                                          _p(self._state), _p(self._derived), float(g["betas"][0]), float(g["betas"][1]),
+                                                          float(g["eps"]), float(g["weight_decay"]), float(grad_scale), clip, _stream(a.flat)))
+            a.clip = None
+            from . import engine
+            engine.bump_weight_epoch()
+            return
         _lib.check(_lib.load().hv_adamw_clip(_p(a.flat), _p(a.grad), _p(self.exp_avg), _p(self.exp_avg_sq), a.numel,
                                              float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
                                              float(g["weight_decay"]), self.step_count, float(grad_scale), clip, _stream(a.flat)))
@@ -301,6 +330,15 @@ class TrainStep:
         use_dist = dist.is_initialized() if distributed is None else distributed
         self.reducer = GradAllReducer(self.arena, bucket_mb=bucket_mb, group=group, issue_after=issue_after) if use_dist else None
         self.last = {}
+        self._graph, self._graph_key, self._gv, self._gr, self._gt, self._gout = None, None, None, None, None, None
+
+    def _draw_time_step(self, n, t, dev):
+        """the reference's draws, in its order (model_AMD.py:1961-1965): on the HOST generator, then copied to the device"""
+        m = self.model
+        time_step = m.prepare_timestep(batch_size=n * t, device=dev)
+        if m.diffusion_model_type != "default":
+            time_step = m.prepare_timestep(batch_size=n, device=dev).repeat_interleave(t)
+        return time_step
 
     def forward_backward(self, video, ref_img, time_step=None, noise=None):
         """forward + backward + gradient all-reduce; leaves the (averaged, unclipped) gradients in the arena and returns
@@ -311,10 +349,8 @@ class TrainStep:
         n, t = video.shape[:2]
         dev = video.device
         zj = video.flatten(0, 1).float().contiguous()
-        if time_step is None:  # the reference's draws, in its order (model_AMD.py:1961-1965)
-            time_step = m.prepare_timestep(batch_size=zj.shape[0], device=dev)
-            if m.diffusion_model_type != "default":
-                time_step = m.prepare_timestep(batch_size=n, device=dev).repeat_interleave(t)
+        if time_step is None:
+            time_step = self._draw_time_step(n, t, dev)
         zt, vel = m.scheduler.get_train_tuple(z0=noise, z1=zj, time_step=time_step)
         self.arena.zero_grad()
         run = train.TrainRun(m)
@@ -355,6 +391,56 @@ class TrainStep:
         self.reducer.issue_after = min(out, key=out.get)   # the same on every rank: t is the max over ranks
         self.arena.zero_grad()
         return out
+
+    # ---- the whole step as ONE CUDA graph.  A step is ~3900 kernel launches through ctypes; the host needs ~110 ms to enqueue
+    # them, about what the GPU needs to run them, so the eager step is launch-bound.  Replaying a captured graph removes the
+    # host from the loop.  What makes the step capturable: no host synchronisation anywhere in it, time steps / noise / masks
+    # (time steps drawn on the host before the replay into a static buffer, noise / masks by torch's graph-safe CUDA generator), the AdamW step count and learning rate in device memory.
+    def capture(self, video, ref_img):
+        """Capture step() for batches of this shape.  Leaves parameters, AdamW moments, step count and the RNG stream as they
+        were (they are snapshotted around the warm-up step that the capture needs)."""
+        dev = video.device
+        if self.opt._state is None:
+            self.opt.enable_device_state()
+        self._gv, self._gr = video.clone(), ref_img.clone()
+        cpu_rng = torch.get_rng_state()
+        self._gt = self._draw_time_step(video.shape[0], video.shape[1], dev).clone()  # static input: drawn on the host per replay
+        torch.set_rng_state(cpu_rng)
+        snap = [t.clone() for t in (self.arena.flat, self.opt.exp_avg, self.opt.exp_avg_sq, self.opt._state)]
+        steps, rng = self.opt.step_count, torch.cuda.get_rng_state(dev)
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):   # eager warm-up: every buffer, weight copy and kernel attribute exists before the capture
+            self.step(self._gv, self._gr, time_step=self._gt)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._gout = self.step(self._gv, self._gr, time_step=self._gt)
+        for dst, src in zip((self.arena.flat, self.opt.exp_avg, self.opt.exp_avg_sq, self.opt._state), snap):
+            dst.copy_(src)
+        self.opt.step_count = steps
+        torch.cuda.set_rng_state(rng, dev)
+        from . import engine
+        engine.bump_weight_epoch()
+        self._graph_key = (tuple(video.shape), tuple(ref_img.shape), video.dtype, ref_img.dtype)
+
+    def step_graphed(self, video, ref_img):
+        """step() replayed from a CUDA graph (captured on first use per batch shape); same return value, the tensors are
+        overwritten by the next call"""
+        key = (tuple(video.shape), tuple(ref_img.shape), video.dtype, ref_img.dtype)
+        if self._graph is None or self._graph_key != key:
+            self.capture(video, ref_img)
+        self.opt.set_lr(self.opt.param_groups[0]["lr"])
+        self._gt.copy_(self._draw_time_step(video.shape[0], video.shape[1], video.device))  # host draw, as in the eager step
+        self._gv.copy_(video, non_blocking=True)
+        self._gr.copy_(ref_img, non_blocking=True)
+        self._graph.replay()
+        self.opt.step_count += 1
+        from . import engine
+        engine.bump_weight_epoch()   # eager users of the model (sample, encode) must refresh their bf16 weight copies
+        self.last = self._gout
+        return self._gout
 
     def step(self, video, ref_img, time_step=None, noise=None):
         """returns {'loss', 'diff_loss', 'rec_loss', 'grad_norm'} as 0-dim device tensors (no host synchronisation)"""

@@ -344,6 +344,11 @@ int hv_grad_norm_clip_coef(const float* g, int64_t n, float grad_scale, float ma
  * Hyper-parameters are doubles: torch forms 1-beta, 1-lr*wd, lr/bias_correction in Python doubles and rounds once. */
 int hv_adamw_clip(float* p, const float* g, float* m, float* v, int64_t n, double lr, double beta1, double beta2,
                   double eps, double weight_decay, int64_t step, float grad_scale, const float* clip_coef, void* stream);
+/* hv_adamw_clip with the step count and learning rate in device memory (state: 2 doubles {steps done, lr}; derived: 3 floats
+ * of scratch): every launch advances the step by one, so a captured CUDA graph of the train step (train_amd.py:459-496)
+ * can be replayed; same update as hv_adamw_clip */
+int hv_adamw_clip_devstate(float* p, const float* g, float* m, float* v, int64_t n, double* state, float* derived, double beta1,
+                           double beta2, double eps, double weight_decay, float grad_scale, const float* clip_coef, void* stream);
 /* x *= coef[0] * extra: materialises the clip in the gradient arena (torch's observable in-place scaling) */
 int hv_scale_by_device(float* x, int64_t n, const float* coef, float extra, void* stream);
 

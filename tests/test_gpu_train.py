@@ -352,3 +352,49 @@ def test_pipeline_windowed_sample(dev):
         assert _err(out[0, 1 + 16 * k:17 + 16 * k], ozt.reshape(16, 4, 32, 32))[0] <= 1e-4, k
     one = pipe.sample_latents(z[:17], video_sample_step=3)
     assert _err(one[0, 1:], out[0, 1:17])[0] <= 1e-5
+
+
+def test_graphed_train_step_equals_eager(dev, golden):
+    """TrainStep.step_graphed (the whole step replayed from one CUDA graph, AdamW step count / lr in device memory) ==
+    TrainStep.step, over three steps on changing batches; capturing leaves weights, moments and step count untouched; with
+    torch's generator the time steps / noise change from replay to replay (nothing random is frozen into the graph)."""
+    from hivae_b200 import optim
+    g = golden("train_step_small")
+    n = g["steps"].numel()
+    batches = []
+    for seed in (1, 2, 3):
+        v, r = synth.split_clip(synth.synth_clip_latents(n, seed=seed))
+        batches.append((v.to(dev), r.to(dev)))
+    runs = {}
+    for mode in ("eager", "graph"):
+        m, sd = _small(dev, torch.float32)
+        _fix(m, g["z0"].to(dev), g["steps"], n)  # fixed time steps and noise (already on the device): both modes see the same draws
+        step = optim.TrainStep(m, lr=1e-4, max_grad_norm=1.0, distributed=False)
+        losses = []
+        if mode == "graph":
+            step.capture(*batches[0])
+            for k, p in m.named_parameters():
+                assert torch.equal(p.detach().cpu(), sd[k]), "capture changed " + k
+            assert step.opt.step_count == 0 and float(step.opt._state[0]) == 0.0
+        for i, (v, r) in enumerate(batches):
+            if i == 2:
+                step.opt.set_lr(5e-5)  # a learning-rate change must reach the replayed graph
+            out = step.step_graphed(v, r) if mode == "graph" else step.step(v, r)
+            losses.append((float(out["loss"]), float(out["grad_norm"])))
+        assert step.opt.step_count == 3
+        runs[mode] = (losses, {k: p.detach().cpu().clone() for k, p in m.named_parameters()}, sd)
+    (le, pe, sd), (lg, pg, _) = runs["eager"], runs["graph"]
+    for (a, b), (c, d) in zip(le, lg):
+        assert abs(a - c) <= 1e-5 * abs(a) and abs(b - d) <= 1e-4 * abs(b), (le, lg)
+    assert len({round(x[0], 6) for x in le}) == 3  # the three batches give three different losses
+    rows = []
+    for k in pe:
+        de, dg = pe[k] - sd[k], pg[k] - sd[k]
+        rows.append((k, _err(dg, de)[1], _err(dg, de)[1]))
+    _report(rows, 2e-3, "parameter deltas after three steps, graph replay vs eager (rms)")
+    # real random draws: the replays must not repeat the capture-time time steps / noise
+    m, _ = _small(dev, torch.float32)
+    step = optim.TrainStep(m, lr=1e-4, max_grad_norm=1.0, distributed=False)
+    torch.manual_seed(11)
+    seen = [float(step.step_graphed(*batches[0])["loss"]) for _ in range(3)]
+    assert len({round(x, 5) for x in seen}) == 3, seen

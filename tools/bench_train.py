@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--config", default="default")
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--profile", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="replay the step from one CUDA graph (TrainStep.step_graphed)")
     a = ap.parse_args()
     dev = torch.device("cuda:0")
     cfg = configs.CONFIGS[a.config]
@@ -33,8 +34,9 @@ def main():
     video, ref_img = video.to(dev), ref_img.to(dev)
     torch.manual_seed(0)
     losses = []
+    run = step.step_graphed if a.graph else step.step
     for i in range(a.warmup):
-        losses.append(float(step.step(video, ref_img)["loss"]))
+        losses.append(float(run(video, ref_img)["loss"]))
     torch.cuda.synchronize()
     from hivae_b200 import ops
     if a.profile:
@@ -44,13 +46,13 @@ def main():
     t0 = time.time()
     e0.record()
     for i in range(a.steps):
-        out = step.step(video, ref_img)
+        out = run(video, ref_img)
     e1.record()
     host = (time.time() - t0) / a.steps * 1e3   # time the host needs to ENQUEUE a step (no synchronisation inside the loop)
     torch.cuda.synchronize()
     wall = (time.time() - t0) / a.steps * 1e3
     ms = e0.elapsed_time(e1) / a.steps
-    rec = {"config": a.config, "dtype": a.dtype, "clips": a.clips, "ms_per_step": round(ms, 2), "wall_ms_per_step": round(wall, 2), "host_enqueue_ms_per_step": round(host, 2),
+    rec = {"config": a.config, "dtype": a.dtype, "graph": bool(a.graph), "clips": a.clips, "ms_per_step": round(ms, 2), "wall_ms_per_step": round(wall, 2), "host_enqueue_ms_per_step": round(host, 2),
            "clips_per_s": round(a.clips / ms * 1e3, 3), "tflops_at_13.5_per_clip": round(13.5 * a.clips / ms * 1e3, 1),
            "launches_per_step": (ops.launch_count() - n0) // a.steps, "loss": [round(x, 5) for x in losses] + [round(float(out["loss"]), 5)],
            "grad_norm": round(float(out["grad_norm"]), 4), "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2)}
