@@ -341,6 +341,41 @@ class AMDModel_New(_ConfigModel):
                            return_meta_info=return_meta_info)
 
 
+    @torch.no_grad()
+    def sample_graphed(self, video, ref_img, sample_step=50, start_step=None):
+        """sample() replayed from ONE CUDA graph per (batch shape, sample_step, start_step, weights): encode + the whole Euler
+        loop are ~270 launches per step through ctypes, which bounds small batches by the host (1-2 clips per GPU: SURVEY 7
+        step 6).  Everything in sample() already runs on the device without host synchronisation (the start noise comes from
+        torch's graph-safe CUDA generator), so the capture is the eager code unchanged.  Returns (zi, zt, zj) like sample();
+        the tensors are owned by the graph and overwritten by the next call with the same key."""
+        from . import engine
+        dev = video.device
+        key = (tuple(video.shape), tuple(ref_img.shape), video.dtype, ref_img.dtype, int(sample_step), start_step,
+               engine.params_version(self))
+        cache = self.__dict__.setdefault("_sample_graphs", {})
+        ent = cache.get(key)
+        if ent is None:
+            for k in [k for k in cache if k[:6] == key[:6]]:
+                del cache[k]   # same shapes, older weights: the graph would read stale prepared weight copies
+            gv, gr = video.clone(), ref_img.clone()
+            rng = torch.cuda.get_rng_state(dev)
+            side = torch.cuda.Stream(dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):  # eager warm-up: weight copies, workspaces and kernel attributes exist before the capture
+                self.sample(gv, gr, sample_step=sample_step, start_step=start_step)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                out = self.sample(gv, gr, sample_step=sample_step, start_step=start_step)
+            torch.cuda.set_rng_state(rng, dev)
+            ent = cache[key] = (graph, gv, gr, out)
+        graph, gv, gr, out = ent
+        gv.copy_(video, non_blocking=True)
+        gr.copy_(ref_img, non_blocking=True)
+        graph.replay()
+        return out
+
     # ------------------------------------------------------------------ small helpers of the reference class
     def prepare_encoder_input(self, video):
         """model_AMD.py:2804-2814: consecutive frame pairs stacked on the channel axis, (b*(t-1), 2c, h, w)"""

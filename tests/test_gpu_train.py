@@ -398,3 +398,33 @@ def test_graphed_train_step_equals_eager(dev, golden):
     torch.manual_seed(11)
     seen = [float(step.step_graphed(*batches[0])["loss"]) for _ in range(3)]
     assert len({round(x, 5) for x in seen}) == 3, seen
+
+
+def test_sample_graphed_equals_sample(dev):
+    """AMDModel_New.sample_graphed (encode + Euler loop replayed from one CUDA graph) == sample on the same generator state,
+    on two different batches through the same graph; a weight change invalidates the graph"""
+    from hivae_b200 import engine
+    m, _ = _small(dev, torch.bfloat16)
+    outs = {}
+    for mode in ("eager", "graph", "graph"):
+        res = []
+        for seed in (1, 2):
+            v, r = synth.split_clip(synth.synth_clip_latents(2, seed=seed))
+            v, r = v.to(dev), r.to(dev)
+            torch.manual_seed(100 + seed)
+            fn = m.sample_graphed if mode == "graph" else m.sample
+            with torch.no_grad():
+                res.append(fn(v, r, sample_step=4)[1].float().cpu().clone())
+        outs.setdefault(mode, []).append(res)
+    e = outs["eager"][0]
+    for res in outs["graph"]:
+        for a, b in zip(res, e):
+            assert torch.equal(a, b)
+    assert not torch.equal(e[0], e[1])
+    assert len(m._sample_graphs) == 1
+    engine.bump_weight_epoch()
+    v, r = synth.split_clip(synth.synth_clip_latents(2, seed=1))
+    torch.manual_seed(101)
+    with torch.no_grad():
+        again = m.sample_graphed(v.to(dev), r.to(dev), sample_step=4)[1].float().cpu()
+    assert len(m._sample_graphs) == 1 and torch.equal(again, e[0])
