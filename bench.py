@@ -253,6 +253,8 @@ def _train_leg(torch, dist, dev, m, rank, world, timed, steps=3, warmup=2):
     clip_grad_norm_(1.0) -> AdamW.  Also timed: the same step without the collective (difference = exposed all-reduce)
     and the all-reduce of the whole arena alone."""
     from hivae_b200 import optim, synth
+    m.__dict__.pop("_sample_graphs", None)  # the inference graphs (and their memory pools) are stale once the weights train
+    torch.cuda.empty_cache()
     step = optim.TrainStep(m, lr=1e-4, max_grad_norm=1.0, distributed=world > 1)
     video, ref_img = synth.split_clip(synth.synth_clip_latents(TRAIN_CLIPS_PER_GPU, seed=101 + rank).to(dev))
     torch.manual_seed(1234)  # every rank draws the same time steps / noise stream, like the reference's set_seed (train_amd.py:154)
@@ -261,17 +263,16 @@ def _train_leg(torch, dist, dev, m, rank, world, timed, steps=3, warmup=2):
         out = eager()
     tuned = step.tune_schedule(video, ref_img)     # untimed: picks when the gradient buckets go out (N > 1 only)
     ms_eager = timed(eager, steps) / steps
-    # the step replayed from one CUDA graph (TrainStep.step_graphed): ~3900 ctypes launches per step make the eager step
-    # launch-bound.  N > 1 keeps the eager step (gradient buckets are issued from Python as the backward reports them).
-    graphed = world == 1
-    fn = (lambda: step.step_graphed(video, ref_img)) if graphed else eager
-    if graphed:
-        for _ in range(2):
-            out = fn()
-    ms = timed(fn, steps) / steps if graphed else ms_eager
+    # the step replayed from ONE CUDA graph per rank (TrainStep.step_graphed; the NCCL bucket all-reduces are captured with it):
+    # ~3900 ctypes launches per step make the eager step launch-bound
+    fn = lambda: step.step_graphed(video, ref_img)
+    for _ in range(2):
+        out = fn()
+    ms = timed(fn, steps) / steps
     rec = {"workload": "configs[4]: train step, default model 695M, bf16 compute / fp32 master + AdamW, %d clips per GPU, "
                        "synthetic latents, random init" % TRAIN_CLIPS_PER_GPU,
-           "ms_per_step": round(ms, 2), "cuda_graph": graphed, "ms_per_step_eager": round(ms_eager, 2), "clips_per_s": round(TRAIN_CLIPS_PER_GPU * world / ms * 1e3, 3),
+           "ms_per_step": round(ms, 2), "cuda_graph": True, "ms_per_step_eager": round(ms_eager, 2),
+           "clips_per_s": round(TRAIN_CLIPS_PER_GPU * world / ms * 1e3, 3),
            "tflops_per_gpu": round(TRAIN_TFLOP_PER_CLIP * TRAIN_CLIPS_PER_GPU / ms * 1e3, 1),
            "frac_of_sustained_peak": round(TRAIN_TFLOP_PER_CLIP * TRAIN_CLIPS_PER_GPU / ms * 1e3 / _peaks()["tf_sustained"], 4),
            "loss": round(float(out["loss"]), 5), "grad_norm": round(float(out["grad_norm"]), 4),
@@ -279,9 +280,10 @@ def _train_leg(torch, dist, dev, m, rank, world, timed, steps=3, warmup=2):
            "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2)}
     if world > 1:
         red = step.reducer
-        step.reducer = None
-        ms_local = timed(fn, steps) / steps           # same step, gradients left un-reduced
-        step.reducer = red
+        step.reducer, step._graph = None, None
+        fn()                                          # re-captured without the collective
+        ms_local = timed(fn, steps) / steps           # same graphed step, gradients left un-reduced
+        step.reducer, step._graph = red, None
 
         def only_allreduce():
             red.begin({})
@@ -294,8 +296,8 @@ def _train_leg(torch, dist, dev, m, rank, world, timed, steps=3, warmup=2):
         rec.update(allreduce_ms=round(ms_ar, 3), allreduce_exposed_ms=round(max(ms - ms_local, 0.0), 3),
                    ms_per_step_without_collective=round(ms_local, 2), allreduce_busbw_gbs=round(busbw, 1),
                    buckets=len(red.buckets),
-                   schedule="%s (issue_after=%.1f), picked by TrainStep.tune_schedule in the warm-up: forward+backward ms per "
-                            "candidate, max over ranks" % (names.get(chosen, "custom"), chosen),
+                   schedule="%s (issue_after=%.1f), picked by TrainStep.tune_schedule in the warm-up: eager forward+backward ms per "
+                            "candidate, max over ranks; the chosen issue order is what the graph captures" % (names.get(chosen, "custom"), chosen),
                    schedule_candidates_fwd_bwd_ms={names.get(c, str(c)): round(v, 3) for c, v in tuned.items()})
     return rec if rank == 0 else None
 
@@ -402,7 +404,7 @@ def run_ours(args):
     if rank == 0:
         torch.cuda.synchronize()
         ops.PROFILE = []
-        step_resident()
+        m.sample(*synth.split_clip(z_dev), sample_step=SAMPLE_STEPS)   # eager: per-launch CUDA events need the ctypes launches
         torch.cuda.synchronize()
         summ = ops.profile_summary(ops.PROFILE)
         ops.PROFILE = None

@@ -14,7 +14,7 @@ timeout -k 5 300 python tools/bench_attn_shapes.py > gpurun_out/attn_shapes.txt 
 timeout -k 5 300 python tools/attn_bwd_phases.py > gpurun_out/attn_bwd_phases.txt 2>&1
 timeout -k 5 400 python tools/bench_train.py --clips 4 --steps 3 --profile > gpurun_out/bench_train_profile.json 2>/dev/null; echo "bench train exit=$?"
 timeout -k 5 900 python tests/tools/library_bar.py > gpurun_out/library_bar.json 2> gpurun_out/library_bar.err; echo "library bar exit=$?"
-CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-train --no-secondary --ncu-range"
+CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-train --no-secondary --no-graph --ncu-range"
 timeout -k 5 300 $CMD > gpurun_out/plain.log 2>&1 &&
 timeout -k 5 900 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launch.log 2>&1
 echo "launch list exit=$?"
