@@ -103,6 +103,7 @@ static int launch_simt(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
 
 int hv_attention_flash_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st);  // attn_flash.cu
 int hv_attention_tc_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st);     // attn_tc.cu (1 = launched, 0 = not applicable)
+int hv_attention_tc2_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st);    // attn_tc2.cu (same convention; tried first)
 int hv_attention_small_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st);  // attn_small.cu (same convention)
 
 extern "C" int hv_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
@@ -116,8 +117,8 @@ extern "C" int hv_attention(const void* q, int64_t ldq, const void* k, int64_t l
     AttnArgs a{q, k, v, out, ldq, ldk, ldv, ldo, heads, hd, Lq, Lkv, *qmap, *kvmap, scale, mask};
     cudaStream_t st = hv_stream(stream);
     if (dtype == HV_BF16) {
-        const int rc = (Lq <= 16 && Lkv <= 16) ? hv_attention_small_bf16(a, seqs, st)
-                       : (Lkv >= 48 ? hv_attention_tc_bf16(a, seqs, st) : 0);
+        int rc = (Lq <= 16 && Lkv <= 16) ? hv_attention_small_bf16(a, seqs, st) : (Lkv >= 48 ? hv_attention_tc2_bf16(a, seqs, st) : 0);
+        if (rc == 0 && Lkv >= 48) rc = hv_attention_tc_bf16(a, seqs, st);
         if (rc != 0) return rc < 0 ? rc : HV_OK;
     }
     if (dtype == HV_BF16 && hd == 64 && mask == nullptr && Lkv >= 48 &&
