@@ -24,7 +24,10 @@
 // and P goes through shared memory (rows 0..31 only), P V as an SS MMA.
 // Measured (tools/probes/mma_probe.cu, tmem_probe.cu): an M = 128 MMA issues every 65-88 clk whatever N <= 128 is, so the
 // 18 N = 64 MMAs of P V cost as much as 18 N = 128 ones; MUFU.EX2 runs at 15.8 / clk / SM, which puts the floor of the
-// exponentials of a 128 x 288 tile at 2330 clk of the ~5900 a tile takes here.
+// exponentials of a 128 x 288 tile at 2330 clk of the ~5500 a tile takes here.  Same-box A/B against attn_tc.cu (128 sequences
+// x 16 heads): L = 256 0.097 against 0.108 ms (354 / 319 TFLOP/s), L = 274 0.144 against 0.149 ms; switching single parts off
+// (profiles/r02_j_attn_tc2_parts.txt) shows a tile is bound by the chain of hand-overs P(T) -> P V(T) -> S(T+1).H1 -> exp, not by
+// MUFU or TMEM throughput: with stores, exponentials, epilogue and bounds all off it still takes 3700 clk.
 //
 // Warp roles (352 threads): warps 0..7 softmax + epilogue (TMEM lane quarter = warp % 4, key half = warp / 4),
 // warp 8 = MMA issuer + TMEM owner, warp 9 = TMA producer, warp 10 = norms / bounds.  Warps 8 and 9 run with all 32
@@ -70,21 +73,29 @@ __device__ __forceinline__ void ld16_wait(uint32_t (&r)[16]) {
                  :
                  : "memory");
 }
-// sum of squares of row r of a [rows x 64] bf16 tile stored by TMA with SWIZZLE_128B (32-row boxes back to back);
-// the chunk order is rotated per lane so that a warp reading 32 consecutive rows is bank-conflict free
+// UPPER BOUND of the sum of squares of row r of a [rows x 64] bf16 tile stored by TMA with SWIZZLE_128B (32-row boxes back to
+// back), within +-1.6 %: packed bf16x2 fused multiply-adds (one instruction per two elements, 8 independent chains of 4),
+// partial sums widened to fp32 at the end.  All terms are positive, so every rounding is a RELATIVE error of at most 2^-8 of
+// the partial sum: (1 + 2^-8)^4 - 1 = 1.6 %; the caller folds that into its head room.  The chunk order is rotated per lane
+// so that a warp reading 32 consecutive rows is bank-conflict free.
 __device__ __forceinline__ float row_sumsq(const uint8_t* tile, int r, int lane) {
     const uint8_t* p = tile + (r >> 3) * 1024 + (r & 7) * 128;
-    float s0 = 0.f, s1 = 0.f;
+    uint32_t acc[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const uint4 u = *reinterpret_cast<const uint4*>(p + (((j ^ lane) & 7) << 4));
         const uint32_t w[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-            const float lo = __uint_as_float(w[e] << 16), hi = __uint_as_float(w[e] & 0xffff0000u);
-            s0 = fmaf(lo, lo, s0);
-            s1 = fmaf(hi, hi, s1);
+            uint32_t& c = acc[(j & 1) * 4 + e];
+            asm("fma.rn.bf16x2 %0, %1, %1, %0;" : "+r"(c) : "r"(w[e]));
         }
+    }
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        s0 += __uint_as_float(acc[i] << 16);
+        s1 += __uint_as_float(acc[i] & 0xffff0000u);
     }
     return s0 + s1;
 }
@@ -170,7 +181,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
     } else if (warp == 10) {
         // ===================================================== norms: m_i * log2(e) = |q_i| * max_j |k_j| * scale * log2(e)
         int T = 0, it = 0;
-        const float sl2 = fabsf(a.sl2) * 1.001f;  // 1e-3 head room for the rounding of the norms and of S
+        const float sl2 = fabsf(a.sl2) * 1.02f;   // head room: 0.8 % for each of the two norms (row_sumsq is within 1.6 %) + the rounding of S
         for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
             const int kb = it & 1;
             tc::mbar_wait(&k_full[kb], (uint32_t)((it >> 1) & 1));
@@ -209,8 +220,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                     const uint64_t db = tc::make_smem_desc_k128(k_s + (uint32_t)((it & 1) * KP32 * 128 + h * HB * 128));
                     const uint32_t idesc = tc::make_idesc_bf16(QT, ncols);
                     const uint32_t d = tmem_base + S_COL + (uint32_t)((2 * T + h) % 3) * SBUF;
-#pragma unroll
-                    for (int k = 0; k < HD / 16; ++k) tc::umma_bf16_w(d, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, k != 0);
+                    tc::umma_bf16_w4(d, da, db, idesc);   // the four K = 16 steps of head_dim 64 under ONE election
                 }
                 tc::umma_commit_w(&s_full[T & 1][h]);
             };
@@ -228,7 +238,14 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                     for (int h = 0; h < 2; ++h) {
                         const int n16 = (h ? KP - HB : HB) >> 4;
                         const uint32_t pa = tmem_base + S_COL + (uint32_t)((2 * T + h) % 3) * SBUF;
-                        for (int j = 0; j < n16; ++j) {
+                        const int nj = n16;
+                        int j = 0;
+                        for (; j + 4 <= nj; j += 4) {   // four K = 16 steps per election
+                            const uint64_t db = tc::make_smem_desc_k128(v_s + (uint32_t)((h * hb + j) * 2048));
+                            tc::umma_bf16_ts_w4(tmem_base + O_COL, pa + (uint32_t)(8 * j), db, idesc, acc);
+                            acc = 1;
+                        }
+                        for (; j < nj; ++j) {
                             const uint64_t db = tc::make_smem_desc_k128(v_s + (uint32_t)((h * hb + j) * 2048));
                             tc::umma_bf16_ts_w(tmem_base + O_COL, pa + (uint32_t)(8 * j), db, idesc, acc);
                             acc = 1;
@@ -443,9 +460,9 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
 }  // namespace
 
 // returns 1 if the shape is handled here (and launched), 0 if the caller should use another kernel, < 0 on error.
-// HV_ATTN_TC2=1 switches this design on (otherwise the dispatcher takes attn_tc.cu), HV_ATTN_EXACT=1 forces the maximum pass.
+// HV_ATTN_TC2=0 switches this design off (the dispatcher then takes attn_tc.cu), HV_ATTN_EXACT=1 forces the maximum pass.
 int hv_attention_tc2_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
-    static const bool off = [] { const char* e = getenv("HV_ATTN_TC2"); return !(e && atoi(e) != 0); }();  // opt-in until GPU-verified
+    static const bool off = [] { const char* e = getenv("HV_ATTN_TC2"); return e && atoi(e) == 0; }();
     static const int force_exact = [] { const char* e = getenv("HV_ATTN_EXACT"); return e ? atoi(e) : 0; }();
     if (off) return 0;
     const HvSeqMap &qm = a.qmap, &km = a.kvmap;

@@ -161,6 +161,25 @@ __device__ __forceinline__ void umma_bf16_w(uint32_t tmem_d, uint64_t desc_a, ui
         "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// D = A B over K = 64: the four K = 16 steps of a K-major SWIZZLE_128B tile pair (descriptor start + 32 B per step) issued
+// under ONE election — elect.sync per instruction costs ~70 clk per MMA whatever N is (tools/probes/mma_probe.cu)
+__device__ __forceinline__ void umma_bf16_w4(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc) {
+    asm volatile(
+        "{\n"
+        ".reg .pred e, pz, po;\n"
+        ".reg .b64 a1, a2, a3, b1, b2, b3;\n"
+        "add.u64 a1, %1, 2; add.u64 a2, %1, 4; add.u64 a3, %1, 6;\n"
+        "add.u64 b1, %2, 2; add.u64 b2, %2, 4; add.u64 b3, %2, 6;\n"
+        "setp.ne.b32 pz, 0, 0;\n"
+        "setp.eq.b32 po, 0, 0;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, pz;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, po;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], a2, b2, %3, po;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], a3, b3, %3, po;\n"
+        "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc)
+        : "memory");
+}
 // A operand read from TENSOR MEMORY (K-major only): lane = row of A, every 32-bit column holds two consecutive bf16 K
 // elements (low half = even k), so one K = 16 instruction reads 8 columns starting at `tmem_a`
 __device__ __forceinline__ void umma_bf16_ts_w(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
@@ -170,6 +189,26 @@ __device__ __forceinline__ void umma_bf16_ts_w(uint32_t tmem_d, uint32_t tmem_a,
         "elect.sync _|e, 0xffffffff;\n"
         "setp.ne.b32 p, %4, 0;\n"
         "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// four consecutive K = 16 steps of a P V-like product under ONE election: A from tensor memory (8 columns per step), B an
+// MN-major tile whose 16-row K groups are 2048 B apart (descriptor start + 128 per step); `accumulate` applies to the first
+__device__ __forceinline__ void umma_bf16_ts_w4(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred e, p, po;\n"
+        ".reg .b32 a1, a2, a3;\n"
+        ".reg .b64 b1, b2, b3;\n"
+        "add.u32 a1, %1, 8; add.u32 a2, %1, 16; add.u32 a3, %1, 24;\n"
+        "add.u64 b1, %2, 128; add.u64 b2, %2, 256; add.u64 b3, %2, 384;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "setp.eq.b32 po, 0, 0;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [a1], b1, %3, po;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [a2], b2, %3, po;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [a3], b3, %3, po;\n"
         "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }

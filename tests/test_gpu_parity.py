@@ -973,3 +973,21 @@ def test_attention_backward_strided_geometry(dev, dtype, tol):
     dq, dk, dv = Bk.attention_backward(q.to(dev), k.to(dev), v.to(dev), o.detach().to(dtype).to(dev), do.to(dev),
                                        geom.seqs, H, T_, T_, geom.qmap, geom.kvmap, 0.125)
     assert rel(dq, qr.grad.float()) <= tol and rel(dk, kr.grad.float()) <= tol and rel(dv, vr.grad.float()) <= tol
+
+
+@pytest.mark.parametrize("B,H,Lq,Lkv", [(3, 2, 274, 274), (2, 4, 256, 256), (5, 3, 288, 288), (2, 2, 129, 200), (3, 1, 160, 48), (1, 2, 20, 274)])
+@pytest.mark.parametrize("qscale", [1.0, 12.0])
+def test_attention_tc2_bound_and_exact_paths(dev, B, H, Lq, Lkv, qscale):
+    """attn_tc2.cu subtracts a Cauchy-Schwarz bound |q_i| max_j |k_j| scale instead of the row maximum (softmax is invariant to
+    the constant) and falls back to the exact maximum per tile when the bound could underflow: qscale 12 makes
+    |q| |k| scale log2(e) ~ 138 > 56 and forces that path; both must match fp64 within the bf16 tolerance."""
+    from hivae_b200 import ops
+    g = _gen(B * H + Lq + Lkv)
+    D = H * 64
+    q = (torch.randn(B * Lq, D, generator=g) * qscale).bfloat16()
+    k, v = torch.randn(B * Lkv, D, generator=g).bfloat16(), torch.randn(B * Lkv, D, generator=g).bfloat16()
+    ref = _ref_attention(q.float().view(B, Lq, H, 64).transpose(1, 2), k.float().view(B, Lkv, H, 64).transpose(1, 2),
+                         v.float().view(B, Lkv, H, 64).transpose(1, 2), 0.125).transpose(1, 2).reshape(B * Lq, D)
+    out = torch.empty(B * Lq, D, device=dev, dtype=torch.bfloat16)
+    ops.attention(q.to(dev), k.to(dev), v.to(dev), out, B, H, 64, Lq, Lkv, ops.seq_map(1, Lq, 0, 1), ops.seq_map(1, Lkv, 0, 1), 0.125)
+    assert rel(out, ref) <= 1e-2

@@ -1,5 +1,3 @@
 mkdir -p gpurun_out
-HV_ATTN_TC2=1 timeout -k 5 300 python tools/attn_tc2_check.py > gpurun_out/attn_tc2_check.txt 2>&1; echo "v2 exit=$?"; cat gpurun_out/attn_tc2_check.txt
-HV_ATTN_TC2=1 HV_ATTN_EXACT=1 timeout -k 5 300 python tools/attn_tc2_check.py > gpurun_out/attn_tc2_check_exact.txt 2>&1; echo "v2 exact exit=$?"; tail -12 gpurun_out/attn_tc2_check_exact.txt
-timeout -k 5 300 python tools/attn_tc2_check.py > gpurun_out/attn_tc2_check_v1.txt 2>&1; echo "v1 exit=$?"; tail -11 gpurun_out/attn_tc2_check_v1.txt
-bash tools/probes/run_probes.sh
+timeout -k 5 1500 python -m pytest tests -x -q -m gpu > gpurun_out/pytest_gpu_full.log 2>&1; echo "pytest exit=$?"; tail -5 gpurun_out/pytest_gpu_full.log
+timeout -k 5 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit=$?"; tail -n 3 gpurun_out/smoke.log
