@@ -684,7 +684,8 @@ int hv_attention_bwd_tc_bf16(const void* q, long long ldq, const void* k, long l
     const int KP32 = (a.KP + 31) & ~31, QP32 = (a.QP + 31) & ~31;
     const int smem_dq = 2 * TBYTES + 2 * KP32 * 128 + ((a.KP + 63) >> 6) * TBYTES + 1024;
     const int smem_dkv = 2 * QP32 * 128 + 2 * TBYTES + ((a.QP + 63) >> 6) * TBYTES + 1024;
-    static int conf_dq = 0, conf_dkv = 0;
+    static int conf_dq_of[HV_MAX_DEVICES] = {}, conf_dkv_of[HV_MAX_DEVICES] = {};  // function attributes are per device
+    int &conf_dq = conf_dq_of[hv_device_slot()], &conf_dkv = conf_dkv_of[hv_device_slot()];
     if (conf_dq < smem_dq) { HV_CUDA(cudaFuncSetAttribute(attn_bwd_dq_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dq)); conf_dq = smem_dq; }
     if (conf_dkv < smem_dkv) { HV_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_dkv)); conf_dkv = smem_dkv; }
     const int sms = hv_num_sms();

@@ -196,7 +196,8 @@ int hv_attention_small_bwd_bf16(const void* q, long long ldq, const void* k, lon
     a.ldq = ldq; a.ldk = ldk; a.ldv = ldv; a.ldo = ldo; a.lddo = lddo; a.lddq = lddq; a.lddk = lddk; a.lddv = lddv;
     a.heads = heads; a.Lq = Lq; a.Lkv = Lkv; a.qmap = qm; a.kvmap = km; a.scale = scale;
     const int smem = WARPS_B * WARP_SMEM;
-    static bool configured = false;
+    static bool configured_of[HV_MAX_DEVICES] = {};  // function attributes are per device
+    bool& configured = configured_of[hv_device_slot()];
     if (!configured) { HV_CUDA(cudaFuncSetAttribute(attn_small_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); configured = true; }
     dim3 grid((unsigned)seqs, (unsigned)((heads + WARPS_B - 1) / WARPS_B));
     attn_small_bwd_kernel<<<grid, WARPS_B * 32, smem, st>>>(a);

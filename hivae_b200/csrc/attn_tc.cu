@@ -442,7 +442,8 @@ int hv_attention_tc_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
     t.dbg = hv_attn_prof_buffer();
     const int KP32 = (t.KP + 31) & ~31, nchunks = (t.KP + 63) >> 6;
     const int smem = 2 * QBYTES + 3 * KP32 * 128 + nchunks * QBYTES + 1024;
-    static int configured = 0;
+    static int configured_of[HV_MAX_DEVICES] = {};  // function attributes are per device
+    int& configured = configured_of[hv_device_slot()];
     if (configured < smem) {
         HV_CUDA(cudaFuncSetAttribute(attn_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         HV_CUDA(cudaFuncSetAttribute(attn_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

@@ -492,7 +492,8 @@ int hv_attention_tc2_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
     const int last = a.Lq % QT;
     const bool has_tail = last >= 1 && last <= 32;
     const int smem = 2 * QBYTES + 3 * KP32 * 128 + (has_tail ? nchunks * QBYTES : 0) + 1024;
-    static int configured = 0;
+    static int configured_of[HV_MAX_DEVICES] = {};  // function attributes are per device
+    int& configured = configured_of[hv_device_slot()];
     if (configured < smem) {
         HV_CUDA(cudaFuncSetAttribute(attn_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = smem;

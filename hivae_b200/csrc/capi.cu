@@ -14,17 +14,24 @@ void hv_set_error(const char* fmt, ...) {
 }
 void hv_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
+int hv_device_slot() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) dev = 0;
+    return dev < HV_MAX_DEVICES ? dev : HV_MAX_DEVICES - 1;
+}
+
 int hv_num_sms() {
-    static int sms = 0;
-    if (sms == 0) {
+    static int sms[HV_MAX_DEVICES] = {};  // per device: one process may drive several GPUs
+    const int slot = hv_device_slot();
+    if (sms[slot] == 0) {
         int dev = 0, n = 0;
         if (cudaGetDevice(&dev) == cudaSuccess &&
             cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
-            sms = n;
+            sms[slot] = n;
         else
-            sms = 148;
+            sms[slot] = 148;
     }
-    return sms;
+    return sms[slot];
 }
 
 extern "C" const char* hv_last_error(void) { return g_err; }

@@ -582,8 +582,9 @@ namespace {
 // CTA pairs that can be co-resident (one CTA per SM, clusters of 2 inside a TPC)
 template <int BN, int MODE>
 int max_pairs() {
-    static int pairs = -1;
-    if (pairs < 0) {
+    static int pairs_of[HV_MAX_DEVICES] = {};  // 0 = not computed yet, per device
+    int& pairs = pairs_of[hv_device_slot()];
+    if (pairs <= 0) {
         cudaLaunchConfig_t cfg = {};
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
@@ -604,7 +605,8 @@ template <int BN, int MODE, int CTAS>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, const CUtensorMap& tr2, int use_reduce, int64_t M, int N,
            int K, const HvEpiDev& d, cudaStream_t st, int tn = 0) {
     auto kern = gemm_tc_kernel<BN, MODE, CTAS>;
-    static bool configured = false;
+    static bool configured_of[HV_MAX_DEVICES] = {};  // function attributes are per device
+    bool& configured = configured_of[hv_device_slot()];
     if (!configured) {
         HV_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<BN, MODE, CTAS>()));
         configured = true;

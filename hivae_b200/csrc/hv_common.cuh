@@ -40,6 +40,8 @@ void hv_count_launch();
 
 static inline cudaStream_t hv_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 int hv_num_sms();
+int hv_device_slot();  // current device ordinal clamped to [0, HV_MAX_DEVICES): index of the per-device host caches
+constexpr int HV_MAX_DEVICES = 64;
 
 // ---------------------------------------------------------------- device helpers
 __device__ __forceinline__ float hv_warp_sum(float v) {

@@ -2,6 +2,7 @@ mkdir -p gpurun_out
 N=$(nvidia-smi -L | wc -l)
 echo "GPUs: $N"
 timeout -k 5 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 tools/ddp_check.py > gpurun_out/ddp_check_n$N.json 2> gpurun_out/ddp_check_n$N.err; echo "ddp check exit=$?"; cat gpurun_out/ddp_check_n$N.json
+timeout -k 5 420 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29521 tools/ddp_graph_check.py > gpurun_out/ddp_graph_check_n$N.json 2> gpurun_out/ddp_graph_check_n$N.err; echo "ddp graph check exit=$?"; cat gpurun_out/ddp_graph_check_n$N.json
 timeout -k 5 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/bench_n$N.json 2> gpurun_out/bench_n$N.err; echo "bench n=$N exit=$?"; tail -n 3 gpurun_out/bench_n$N.err; cat gpurun_out/bench_n$N.json
 # BASELINE configs[2]: 32 clips sharded over the GPUs, 10 / 25 / 50 Euler steps
 C=$((32 / N))
