@@ -88,19 +88,21 @@ __device__ __forceinline__ void epi_block_reduce(const HvEpiDev& d, const CUtens
             for (int j = 0; j < 32; ++j) if (col0 + j < N) acc[j] *= __ldg(g + j);
         }
     }
-    if (lane == 0) tc::bulk_wait_read0();  // the previous reduce has finished reading the staging tile
+    tc::bulk_wait_read0();  // the previous reduce has finished reading the staging tile (all lanes: only the issuing lane has groups)
     __syncwarp();
 #pragma unroll
     for (int k = 0; k < 8; ++k)
         *stage_ptr(stage, lane, k) = make_float4(acc[4 * k], acc[4 * k + 1], acc[4 * k + 2], acc[4 * k + 3]);
     tc::fence_proxy_async();
     __syncwarp();
-    if (lane == 0) {
+    {   // warp-converged: every lane forms the (warp-uniform) coordinates, one elected lane issues the reduce(s) and commits
         const long long f0 = row0 / e.L;
         const int i0 = (int)(row0 - f0 * e.L), s = e.L - i0;
-        if (row0 < M) tc::tma_reduce_add_3d(tmap_r, stage, col0, i0, (int)f0);
-        if (s < 32 && row0 + s < M) tc::tma_reduce_add_3d(tmap_r, stage + s * 32, col0, 0, (int)(f0 + 1));
-        tc::bulk_commit();
+        const uint32_t st = tc::warp_uniform(tc::smem_u32(stage));
+        const int c0 = (int)tc::warp_uniform((uint32_t)col0), f = (int)tc::warp_uniform((uint32_t)f0);
+        const int ii = (int)tc::warp_uniform((uint32_t)i0), ss = (int)tc::warp_uniform((uint32_t)s);
+        const uint32_t do1 = tc::warp_uniform(row0 < M ? 1u : 0u), do2 = tc::warp_uniform((s < 32 && row0 + s < M) ? 1u : 0u);
+        tc::tma_reduce_add_3d_x2_commit_w(tmap_r, st, c0, ii, f, do1, st + (uint32_t)(ss * 32 * 4), c0, 0, f + 1, do2);
     }
 }
 
@@ -111,9 +113,8 @@ __device__ __forceinline__ void epi_block_reduce(const HvEpiDev& d, const CUtens
 template <int PENDING = 0>
 __device__ __forceinline__ void epi_block_tma_store(const CUtensorMap* tmap_c, float* stage, int lane, long long row0,
                                                     int col0, const float (&lo)[32], const float (&hi)[32]) {
-    if (lane == 0) {  // the previous store from THIS staging tile has finished reading it
-        if (PENDING == 0) tc::bulk_wait_read0(); else tc::bulk_wait_read1();
-    }
+    // the previous store from THIS staging tile has finished reading it (all lanes: only the issuing lane has groups)
+    if (PENDING == 0) tc::bulk_wait_read0(); else tc::bulk_wait_read1();
     __syncwarp();
     uint8_t* rowp = reinterpret_cast<uint8_t*>(stage) + lane * 128;
 #pragma unroll
@@ -127,10 +128,8 @@ __device__ __forceinline__ void epi_block_tma_store(const CUtensorMap* tmap_c, f
     }
     tc::fence_proxy_async();
     __syncwarp();
-    if (lane == 0) {
-        tc::tma_store_2d(tmap_c, stage, col0, (int)row0);
-        tc::bulk_commit();
-    }
+    tc::tma_store_2d_commit_w(tmap_c, tc::warp_uniform(tc::smem_u32(stage)), (int)tc::warp_uniform((uint32_t)col0),
+                              (int)tc::warp_uniform((uint32_t)row0));  // one elected lane stores and commits
 }
 
 template <int MODE>
@@ -477,7 +476,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             }
             if ((a ^= 1) == 0) aph ^= 1;
         }
-        if ((reduce || tma_store) && lane == 0) tc::bulk_wait0();  // every bulk store / reduce of this warp has landed before the CTA retires
+        if (reduce || tma_store) tc::bulk_wait0();  // every bulk store / reduce of this warp has landed before the CTA retires
     }
     tc::fence_before_sync();
     if (CTAS == 2) tc::cluster_sync(); else __syncthreads();

@@ -362,6 +362,35 @@ __device__ __forceinline__ void tma_store_2d(const void* tmap, const void* smem_
                  ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
                  : "memory");
 }
+// warp-converged epilogue issue: ONE elected lane issues the TMA store / reduce(s) AND commits them to its bulk group in the
+// same asm block (bulk groups are per thread).  The matching waits are executed by ALL lanes (bulk_wait_*): lanes without
+// groups return at once, so it does not matter which lane was elected.
+__device__ __forceinline__ void tma_store_2d_commit_w(const void* tmap, uint32_t smem_src, int c0, int c1) {
+    asm volatile(
+        "{\n"
+        ".reg .pred e;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];\n"
+        "@e cp.async.bulk.commit_group;\n"
+        "}\n" ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_src), "r"(c0), "r"(c1)
+        : "memory");
+}
+// up to two reduce-adds (a 32-row block that crosses a frame boundary splits in two), each under its own flag
+__device__ __forceinline__ void tma_reduce_add_3d_x2_commit_w(const void* tmap, uint32_t src1, int a0, int a1, int a2, uint32_t do1,
+                                                              uint32_t src2, int b0, int b1, int b2, uint32_t do2) {
+    asm volatile(
+        "{\n"
+        ".reg .pred e, p1, p2;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "setp.ne.and.b32 p1, %5, 0, e;\n"
+        "setp.ne.and.b32 p2, %10, 0, e;\n"
+        "@p1 cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];\n"
+        "@p2 cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%7, %8, %9}], [%6];\n"
+        "@e cp.async.bulk.commit_group;\n"
+        "}\n" ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(src1), "r"(a0), "r"(a1), "r"(a2), "r"(do1), "r"(src2), "r"(b0), "r"(b1),
+        "r"(b2), "r"(do2)
+        : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
