@@ -266,6 +266,7 @@ def _train_leg(torch, dist, dev, m, rank, world, timed, steps=3, warmup=2):
     # the step replayed from ONE CUDA graph per rank (TrainStep.step_graphed; the NCCL bucket all-reduces are captured with it):
     # ~3900 ctypes launches per step make the eager step launch-bound
     fn = lambda: step.step_graphed(video, ref_img)
+    tuned_graph = step.tune_schedule_graphed(video, ref_img)   # untimed; the order that is best for the REPLAYED step (N > 1 only)
     for _ in range(2):
         out = fn()
     ms = timed(fn, steps) / steps
@@ -296,9 +297,10 @@ def _train_leg(torch, dist, dev, m, rank, world, timed, steps=3, warmup=2):
         rec.update(allreduce_ms=round(ms_ar, 3), allreduce_exposed_ms=round(max(ms - ms_local, 0.0), 3),
                    ms_per_step_without_collective=round(ms_local, 2), allreduce_busbw_gbs=round(busbw, 1),
                    buckets=len(red.buckets),
-                   schedule="%s (issue_after=%.1f), picked by TrainStep.tune_schedule in the warm-up: eager forward+backward ms per "
-                            "candidate, max over ranks; the chosen issue order is what the graph captures" % (names.get(chosen, "custom"), chosen),
-                   schedule_candidates_fwd_bwd_ms={names.get(c, str(c)): round(v, 3) for c, v in tuned.items()})
+                   schedule="%s (issue_after=%.1f), picked by TrainStep.tune_schedule_graphed in the warm-up: every candidate order "
+                            "captured and replayed, ms per step, max over ranks" % (names.get(chosen, "custom"), chosen),
+                   schedule_candidates_graph_ms={names.get(c, str(c)): round(v, 3) for c, v in tuned_graph.items()},
+                   schedule_candidates_eager_fwd_bwd_ms={names.get(c, str(c)): round(v, 3) for c, v in tuned.items()})
     return rec if rank == 0 else None
 
 

@@ -425,6 +425,46 @@ class TrainStep:
         engine.bump_weight_epoch()
         self._graph_key = (tuple(video.shape), tuple(ref_img.shape), video.dtype, ref_img.dtype)
 
+    def tune_schedule_graphed(self, video, ref_img, candidates=(0.0, 0.9, 1.0), steps=3):
+        """tune_schedule for the graphed step: the issue order of the gradient buckets is frozen into the captured graph, and
+        which order exposes least differs between the eager step (host-bound, gaps everywhere) and the replayed one.  Every
+        candidate is captured, replayed `steps` times (CUDA events, max over ranks), the best one is kept.  Parameters, AdamW
+        moments, step count and the RNG streams are restored afterwards.  Returns {candidate: ms}."""
+        import torch.distributed as dist
+        if self.reducer is None or self.reducer.world == 1 or not video.is_cuda:
+            return {}
+        dev = video.device
+        if self.opt._state is None:
+            self.opt.enable_device_state()
+        snap = [t.clone() for t in (self.arena.flat, self.opt.exp_avg, self.opt.exp_avg_sq, self.opt._state)]
+        count, rng, cpu_rng = self.opt.step_count, torch.cuda.get_rng_state(dev), torch.get_rng_state()
+        out = {}
+        for c in candidates:
+            self.reducer.issue_after, self._graph = c, None
+            self.step_graphed(video, ref_img)   # capture + first replay
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            dist.barrier(self.reducer.group)
+            torch.cuda.synchronize(dev)
+            e0.record()
+            for _ in range(steps):
+                self.step_graphed(video, ref_img)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            t = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.reducer.group)
+            out[c] = float(t)
+        best = min(out, key=out.get)              # the same on every rank: t is the max over ranks
+        if best != self.reducer.issue_after:
+            self.reducer.issue_after, self._graph = best, None   # re-captured on the next step_graphed
+        for dst, src in zip((self.arena.flat, self.opt.exp_avg, self.opt.exp_avg_sq, self.opt._state), snap):
+            dst.copy_(src)
+        self.opt.step_count = count
+        torch.cuda.set_rng_state(rng, dev)
+        torch.set_rng_state(cpu_rng)
+        from . import engine
+        engine.bump_weight_epoch()
+        return out
+
     def step_graphed(self, video, ref_img):
         """step() replayed from a CUDA graph (captured on first use per batch shape); same return value, the tensors are
         overwritten by the next call"""
