@@ -146,6 +146,8 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem_base = tc::warp_uniform(tmem_slot);
+    tc::grid_dep_wait();     // PDL: the prologue above overlapped the previous kernel's tail
+    tc::grid_dep_launch();   // persistent grid, fully resident
 
     if (warp == 9) {
         // ===================================================== TMA producer (all 32 lanes, one elected lane issues)
@@ -500,7 +502,13 @@ int hv_attention_tc2_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
     }
     const int sms = hv_num_sms();
     const int grid = (int)(t.items < sms ? t.items : sms);
-    attn_tc2_kernel<<<grid, THREADS, smem, st>>>(tq, tk, tv, t);
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cfg.attrs = at; cfg.numAttrs = hv_pdl_enabled() ? 1 : 0;
+    HV_CUDA(cudaLaunchKernelEx(&cfg, attn_tc2_kernel, tq, tk, tv, t));
     HV_LAUNCH_CHECK();
     return 1;
 }

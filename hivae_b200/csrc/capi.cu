@@ -1,4 +1,5 @@
 // Library-level plumbing of the C ABI: error string, device check, launch counter.
+#include <cstdlib>
 #include "hv_common.cuh"
 #include <atomic>
 #include <string.h>
@@ -13,6 +14,13 @@ void hv_set_error(const char* fmt, ...) {
     va_end(ap);
 }
 void hv_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+bool hv_pdl_enabled() {
+    // opt-in: measured on one B200, same box, graph replay (profiles/r02_l_pdl_ab.txt): 11.28 -> 10.97 clips/s and 97.3 -> 99.0 ms
+    // per train step WITH programmatic dependent launch; only the eager train step gained (113.5 -> 111.3 ms)
+    static const bool on = [] { const char* e = getenv("HV_PDL"); return e && atoi(e) != 0; }();
+    return on;
+}
 
 int hv_device_slot() {
     int dev = 0;

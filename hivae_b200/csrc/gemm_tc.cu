@@ -274,6 +274,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     if (CTAS == 2) tc::cluster_sync(); else __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem_base = tmem_slot;
+    tc::grid_dep_wait();     // PDL: everything above overlapped the previous kernel's tail; global memory is touched only below
+    tc::grid_dep_launch();   // persistent grid, fully resident: the next kernel's CTAs may take the SMs as these CTAs exit
 
     if (warp == 0) {
         // ===================================================== TMA producer (one per CTA).  All 32 lanes run the loop with
@@ -614,16 +616,24 @@ int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tr, 
     if constexpr (CTAS == 1) {
         const int sms = hv_num_sms();
         const int grid = (int)(tiles < sms ? tiles : sms);
-        kern<<<grid, THREADS, smem_bytes<BN, MODE, CTAS>(), st>>>(ta, tb, tr, tr2, (long long)M, N, K, use_reduce, tn, d);
+        cudaLaunchConfig_t cfg = {};
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(THREADS);
+        cfg.dynamicSmemBytes = smem_bytes<BN, MODE, CTAS>(); cfg.stream = st; cfg.attrs = at; cfg.numAttrs = hv_pdl_enabled() ? 1 : 0;
+        HV_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tr, tr2, (long long)M, N, K, use_reduce, tn, d));
     } else {
         const int pairs = max_pairs<BN, MODE>();
         const int units = (int)(tiles < pairs ? tiles : pairs);
         cudaLaunchConfig_t cfg = {};
-        cudaLaunchAttribute at[1];
+        cudaLaunchAttribute at[2];
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[1].val.programmaticStreamSerializationAllowed = 1;
         cfg.gridDim = dim3(2 * units); cfg.blockDim = dim3(THREADS);
-        cfg.dynamicSmemBytes = smem_bytes<BN, MODE, CTAS>(); cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
+        cfg.dynamicSmemBytes = smem_bytes<BN, MODE, CTAS>(); cfg.stream = st; cfg.attrs = at; cfg.numAttrs = hv_pdl_enabled() ? 2 : 1;
         HV_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, tr, tr2, (long long)M, N, K, use_reduce, tn, d));
     }
     HV_LAUNCH_CHECK();

@@ -40,8 +40,22 @@ void hv_count_launch();
 
 static inline cudaStream_t hv_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 int hv_num_sms();
+bool hv_pdl_enabled();  // HV_PDL=1 switches programmatic dependent launch on (measured slower under graph replay, see capi.cu)
 int hv_device_slot();  // current device ordinal clamped to [0, HV_MAX_DEVICES): index of the per-device host caches
 constexpr int HV_MAX_DEVICES = 64;
+
+// launch with programmatic dependent launch allowed (tc_ptx.cuh grid_dep_wait): the kernel MUST execute griddepcontrol.wait
+// before its first global-memory access
+template <typename... KArgs, typename... Args>
+inline cudaError_t hv_launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cfg.attrs = at; cfg.numAttrs = hv_pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
 
 // ---------------------------------------------------------------- device helpers
 __device__ __forceinline__ float hv_warp_sum(float v) {

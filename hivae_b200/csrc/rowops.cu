@@ -88,6 +88,8 @@ __global__ void __launch_bounds__(256, 2) ln_modulate2_kernel(
     int shift_col_img, int scale_col_img, int img_start, int img_len, int cond_div, int cond_mul,
     LnSeg sg, OutT* __restrict__ out, float* __restrict__ save) {
     __shared__ float4 sA[NV * 32], sB[NV * 32];
+    asm volatile("griddepcontrol.wait;" ::: "memory");  // PDL (hv_launch_pdl): launched while the previous kernel drains; no early trigger,
+                                                        // the grid is larger than one wave (hv_common.cuh / tc_ptx.cuh)
     const int lane = threadIdx.x & 31, k0 = 2 * (threadIdx.x >> 5);
     // ---- which rows does this CTA own?  (dense output row, residual-buffer row, count)
     long long rd, rr;   // first dense row / first residual row of the CTA
@@ -214,8 +216,8 @@ static int ln_modulate_impl(const float* res, int64_t frames, int64_t frame_rows
             img_start = is; img_len = sg.b;  // the kernel derives the segment starts from these
         }
         dim3 grid((unsigned)ctas), block(256);
-        if (out_dtype == HV_F32) { if (nv == 8) ln_modulate2_kernel<8, float><<<grid, block, 0, st>>>(LN_ARGS, (float*)out, save); else ln_modulate2_kernel<4, float><<<grid, block, 0, st>>>(LN_ARGS, (float*)out, save); }
-        else { if (nv == 8) ln_modulate2_kernel<8, __nv_bfloat16><<<grid, block, 0, st>>>(LN_ARGS, (__nv_bfloat16*)out, save); else ln_modulate2_kernel<4, __nv_bfloat16><<<grid, block, 0, st>>>(LN_ARGS, (__nv_bfloat16*)out, save); }
+        if (out_dtype == HV_F32) { if (nv == 8) HV_CUDA(hv_launch_pdl(ln_modulate2_kernel<8, float>, dim3(grid), dim3(block), 0, st, LN_ARGS, (float*)out, save)); else HV_CUDA(hv_launch_pdl(ln_modulate2_kernel<4, float>, dim3(grid), dim3(block), 0, st, LN_ARGS, (float*)out, save)); }
+        else { if (nv == 8) HV_CUDA(hv_launch_pdl(ln_modulate2_kernel<8, __nv_bfloat16>, dim3(grid), dim3(block), 0, st, LN_ARGS, (__nv_bfloat16*)out, save)); else HV_CUDA(hv_launch_pdl(ln_modulate2_kernel<4, __nv_bfloat16>, dim3(grid), dim3(block), 0, st, LN_ARGS, (__nv_bfloat16*)out, save)); }
         HV_LAUNCH_CHECK();
         return HV_OK;
     }

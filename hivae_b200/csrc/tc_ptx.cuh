@@ -9,6 +9,16 @@ namespace tc {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// ---------------------------------------------------------------- programmatic dependent launch (PDL)
+// A kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while its predecessor in the stream
+// still runs: grid_dep_wait() blocks until every prerequisite grid has completed and flushed its memory, so it must precede
+// the first access to global memory (reads AND writes); what stands before it (barrier init, TMEM allocation, tensor-map
+// prefetch) overlaps the predecessor's tail.  grid_dep_launch() lets the NEXT kernel's CTAs be scheduled as this kernel's
+// CTAs exit; only for kernels whose whole grid is resident (persistent, <= 1 CTA per SM), otherwise waiting successor CTAs
+// could starve this kernel's unscheduled CTAs.  Both are no-ops in a kernel launched without the attribute.
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------------------------------------------------------- mbarrier
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
