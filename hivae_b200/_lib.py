@@ -52,6 +52,7 @@ SIGNATURES = {
     "hv_rows_scatter": (_i, [_vp, _i64, _i64, _vp, _vp, _i64, _i64, _i, _i, _i, _vp]),
     "hv_rows_gather": (_i, [_vp, _i64, _i64, _i, _i, _i, _vp, _vp]),
     "hv_attn_prof_read": (_i, [_vp]),
+    "hv_attn_timeline_read": (_i, [_vp]),
     "hv_attn_bwd_prof_read": (_i, [_vp]),
     "hv_headnorm64_bwd": (_i, [_vp, _i64, _vp, _i64, _vp, _f, _i64, _i, _vp, _i64, _i, _vp, _vp, _vp, _vp]),
     "hv_attention_bwd": (_i, [_vp, _i64] * 8 + [_i, _i64, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp]),

@@ -54,6 +54,7 @@ struct Tc2Args {
     long long items;
     float sl2;
     int force_exact;  // HV_ATTN_EXACT=1: always take the maximum pass (tests)
+    unsigned long long* tl;  // HV_ATTN_TIMELINE=1: clock64 stamps of CTA 0, 64 tiles x 16 events (tools/attn_timeline.py)
 };
 
 __device__ __forceinline__ void ld16_issue(uint32_t taddr, uint32_t (&r)[16]) {
@@ -105,6 +106,7 @@ __device__ __forceinline__ float warp_max(float v) {
     return v;
 }
 
+template <bool PROF>  // PROF: timeline stamps (a separate instantiation, the production kernel carries none of it)
 __global__ void __launch_bounds__(THREADS, 1)
 attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                 const __grid_constant__ CUtensorMap tv, const Tc2Args a) {
@@ -148,6 +150,10 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
     const uint32_t tmem_base = tc::warp_uniform(tmem_slot);
     tc::grid_dep_wait();     // PDL: the prologue above overlapped the previous kernel's tail
     tc::grid_dep_launch();   // persistent grid, fully resident
+    auto stamp = [&](int tile, int ev) {  // events: 0-4 key half 0 (S ready, exp done, arrived, o_full seen, epilogue done), 6-8 key half 1,
+                                          // 11 bounds done, 12-15 MMA warp (p_full seen, P V issued, S.H1 issued, top of iteration)
+        if (PROF && a.tl != nullptr && blockIdx.x == 0 && lane == 0 && tile < 64) a.tl[tile * 16 + ev] = (unsigned long long)clock64();
+    };
 
     if (warp == 9) {
         // ===================================================== TMA producer (all 32 lanes, one elected lane issues)
@@ -209,6 +215,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                 if (lane == 0) exact_f[slot] = (a.force_exact || !(mb <= BOUND_MAX)) ? 1 : 0;
                 __syncwarp();
                 if (lane == 0) { tc::mbar_arrive(&n_full[slot]); tc::mbar_arrive(&q_free[b]); }
+                stamp(T, 11);
             }
         }
     } else if (warp == 8) {
@@ -266,6 +273,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
             issue_s(0, 0, 0); issue_s(0, 0, 1); after_s(0, 0, 0);
             int it = 0, i = 0;  // item / tile-in-item of tile T
             for (int T = 0; T < ntiles; ++T) {
+                stamp(T, 15);
                 const bool last_of_item = i + 1 == nq;
                 const int it1 = last_of_item ? it + 1 : it, i1 = last_of_item ? 0 : i + 1;  // of tile T + 1
                 if (T + 1 < ntiles) {
@@ -277,9 +285,12 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                 tc::mbar_wait(&p_full, (uint32_t)(T & 1));  // P(T) written; O(T-1) read back
                 if (i == 0) tc::mbar_wait(&v_full, (uint32_t)(it & 1));
                 tc::fence_after_sync();
+                stamp(T, 12);
                 issue_pv(T, a.Lq - i * QT <= 32);
+                stamp(T, 13);
                 // S(T+1).H1 goes into the ring buffer of S(T).H0, which now holds P(T).H0: behind P V(T) in the pipe
                 if (T + 1 < ntiles) { issue_s(T + 1, it1, 1); after_s(T + 1, it1, i1); }
+                stamp(T, 14);
                 if (last_of_item) tc::umma_commit_w(&v_free);
                 it = it1; i = i1;
             }
@@ -301,6 +312,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
         auto epilogue = [&]() {
             tc::mbar_wait(&o_full, (uint32_t)(pend_T & 1));
             tc::fence_after_sync();
+            if (q == 0) stamp(pend_T, 3);
             if (pend_active) {  // warp-uniform (tcgen05.ld is .sync.aligned); only the store is per-row
                 const int sb = pend_T & 1;
                 float sum;
@@ -326,6 +338,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                 }
             }
             tc::fence_before_sync();
+            if (q == 0) stamp(pend_T, 4);
         };
         for (long long w = blockIdx.x; w < a.items; w += gridDim.x) {
             const long long seq = w / a.heads;
@@ -342,6 +355,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                 float msc = qn[slot][row];
                 tc::mbar_wait(&s_full[T & 1][h], (uint32_t)((T >> 1) & 1));
                 tc::fence_after_sync();
+                if (q == 0) stamp(T, h * 6 + 0);
                 if (exact) {
                     // ---- exact path: row maximum over this thread's keys, exchanged through shared memory
                     float mx = -INFINITY;
@@ -403,34 +417,69 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                             make_uint4(hv_pack_bf16(v[8], v[9]), hv_pack_bf16(v[10], v[11]), hv_pack_bf16(v[12], v[13]), hv_pack_bf16(v[14], v[15]));
                     }
                 } else if (active && c_begin < c_end) {
-                    // P(c .. c+15) goes to columns (c - c_begin) / 2 .. +7 of the same half-buffer: always behind the reads
-                    auto emit = [&](uint32_t (&r)[16], int c) {
-                        float v[16];
-                        expo(r, c, v);
+                    // P(c .. c+15) goes to columns (c - c_begin) / 2 .. +7 of the same half-buffer: always behind the reads.
+                    // Software-pipelined by hand: one warp per SM sub-partition runs this loop most of the time (the other one is
+                    // in a different phase), so nothing hides the 16 MUFU.EX2 of a chunk (8 clk each) but this warp's OWN
+                    // independent work: the row sums, the bf16 packing and the P store of chunk i-1 are issued inside the MUFU
+                    // phase of chunk i (measured before: 331 clk per chunk against the MUFU bound of 128, tools/attn_timeline.py).
+                    auto ex = [&](const uint32_t (&r)[16], float (&e)[16]) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) e[j] = tc::ex2_approx(fmaf(__uint_as_float(r[j]), a.sl2, -msc));
+                    };
+                    auto finish = [&](const float (&v)[16], int c) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) sum4[j] += (v[j] + v[j + 4]) + (v[j + 8] + v[j + 12]);
                         uint32_t pk[8];
 #pragma unroll
                         for (int j = 0; j < 8; ++j) pk[j] = hv_pack_bf16(v[2 * j], v[2 * j + 1]);
                         tc::tmem_st8(s_base + (uint32_t)((c - c_begin) >> 1), pk);
                     };
-                    uint32_t va[16], vb[16];
+                    const int lk16 = a.Lkv & ~15;
+                    const int cfe = c_end < lk16 ? c_end : lk16;   // end of the fully valid chunks of this thread's key range
                     int c = c_begin;
-                    ld16_issue(s_addr + c, va);
-                    while (true) {
+                    if (c < cfe) {
+                        uint32_t va[16], vb[16];
+                        float ea[16], eb[16];
+                        ld16_issue(s_addr + c, va);
                         ld16_wait(va);
-                        bool more = c + 16 < c_end;
+                        bool more = c + 16 < cfe;
                         if (more) ld16_issue(s_addr + c + 16, vb);
-                        emit(va, c);
-                        if (!more) break;
+                        ex(va, ea);
+                        bool in_b = false;   // the chunk that still has to be finished sits in eb (else ea)
+                        while (more) {
+                            c += 16;
+                            ld16_wait(vb);
+                            more = c + 16 < cfe;
+                            if (more) ld16_issue(s_addr + c + 16, va);
+                            ex(vb, eb);
+                            finish(ea, c - 16);
+                            in_b = true;
+                            if (!more) break;
+                            c += 16;
+                            ld16_wait(va);
+                            more = c + 16 < cfe;
+                            if (more) ld16_issue(s_addr + c + 16, vb);
+                            ex(va, ea);
+                            finish(eb, c - 16);
+                            in_b = false;
+                        }
+                        if (in_b) finish(eb, c); else finish(ea, c);
                         c += 16;
-                        ld16_wait(vb);
-                        more = c + 16 < c_end;
-                        if (more) ld16_issue(s_addr + c + 16, va);
-                        emit(vb, c);
-                        if (!more) break;
-                        c += 16;
+                    }
+                    if (c < c_end) {  // the one partially valid chunk (Lkv not a multiple of 16), masked
+                        uint32_t va[16];
+                        ld16_issue(s_addr + c, va);
+                        ld16_wait(va);
+                        float v[16];
+                        expo(va, c, v);
+                        uint32_t pk[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) pk[j] = hv_pack_bf16(v[2 * j], v[2 * j + 1]);
+                        tc::tmem_st8(s_base + (uint32_t)((c - c_begin) >> 1), pk);
                     }
                 }
                 ssum[T & 1][h][row] = (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
+                if (q == 0) stamp(T, h * 6 + 1);
                 if (h == 0 && pend) epilogue();      // O(T-1), all 64 columns: off the critical path (see above)
                 // ---- publish: P(T) complete (and O(T-1) read back) -> the MMA warp may issue P V(T)
                 tc::tmem_st_wait();
@@ -438,6 +487,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                 if (tail) tc::fence_proxy_async();   // P of a tail tile: generic-proxy stores -> visible to the tensor core
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&p_full);
+                if (q == 0) stamp(T, h * 6 + 2);
                 if (h == 0) {
                     const int qr = i * QT + row;
                     pend = true;
@@ -460,6 +510,16 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
 }
 
 }  // namespace
+
+static unsigned long long* g_tl = nullptr;
+// HV_ATTN_TIMELINE=1: copies the stamps of the last launches (64 tiles x 16 events of CTA 0) to host[1024] and clears them
+extern "C" int hv_attn_timeline_read(unsigned long long* host) {
+    if (!g_tl) return 0;
+    cudaDeviceSynchronize();
+    cudaMemcpy(host, g_tl, 1024 * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+    cudaMemset(g_tl, 0, 1024 * sizeof(unsigned long long));
+    return 1;
+}
 
 // returns 1 if the shape is handled here (and launched), 0 if the caller should use another kernel, < 0 on error.
 // HV_ATTN_TC2=0 switches this design off (the dispatcher then takes attn_tc.cu), HV_ATTN_EXACT=1 forces the maximum pass.
@@ -490,6 +550,9 @@ int hv_attention_tc2_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
     t.items = seqs * a.heads;
     t.sl2 = a.scale * 1.4426950408889634f;
     t.force_exact = force_exact;
+    static const bool timeline = [] { const char* e = getenv("HV_ATTN_TIMELINE"); return e && atoi(e) != 0; }();
+    if (timeline && !g_tl && cudaMalloc(&g_tl, 1024 * sizeof(unsigned long long)) == cudaSuccess) cudaMemset(g_tl, 0, 1024 * sizeof(unsigned long long));
+    t.tl = timeline ? g_tl : nullptr;
     const int KP32 = (t.KP + 31) & ~31, nchunks = (t.KP + 63) >> 6;
     const int last = a.Lq % QT;
     const bool has_tail = last >= 1 && last <= 32;
@@ -497,7 +560,8 @@ int hv_attention_tc2_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
     static int configured_of[HV_MAX_DEVICES] = {};  // function attributes are per device
     int& configured = configured_of[hv_device_slot()];
     if (configured < smem) {
-        HV_CUDA(cudaFuncSetAttribute(attn_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        HV_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        HV_CUDA(cudaFuncSetAttribute(attn_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = smem;
     }
     const int sms = hv_num_sms();
@@ -508,7 +572,8 @@ int hv_attention_tc2_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.gridDim = dim3(grid); cfg.blockDim = dim3(THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cfg.attrs = at; cfg.numAttrs = hv_pdl_enabled() ? 1 : 0;
-    HV_CUDA(cudaLaunchKernelEx(&cfg, attn_tc2_kernel, tq, tk, tv, t));
+    if (t.tl) HV_CUDA(cudaLaunchKernelEx(&cfg, attn_tc2_kernel<true>, tq, tk, tv, t));
+    else HV_CUDA(cudaLaunchKernelEx(&cfg, attn_tc2_kernel<false>, tq, tk, tv, t));
     HV_LAUNCH_CHECK();
     return 1;
 }

@@ -216,6 +216,8 @@ int hv_maxpool2_bwd(const float* x, const float* dy, float* dx, int64_t planes, 
  * counters (148 CTAs x 2 key halves x 8 u64: wait S, max pass, max exchange, O epilogue, exp pass, publish P, full
  * tiles, tail tiles); this copies them to `host` and clears them.  Returns 0 when profiling is off. */
 int hv_attn_prof_read(unsigned long long* host);
+/* HV_ATTN_TIMELINE=1: clock64 stamps of CTA 0 of the last attn_tc2 launches (64 tiles x 16 events) -> host[1024]; 0 when off */
+int hv_attn_timeline_read(unsigned long long* host);
 /* the same for the tcgen05 attention BACKWARD kernels (HV_ATTN_BWD_PROF=1): 2 kernels (dq, dkv) x 148 CTAs x 16 u64 */
 int hv_attn_bwd_prof_read(unsigned long long* host);
 

@@ -1,9 +1,4 @@
 mkdir -p gpurun_out
-timeout -k 5 1500 python -m pytest tests -x -q -m gpu > gpurun_out/pytest_gpu_full.log 2>&1; echo "pytest exit=$?"; tail -4 gpurun_out/pytest_gpu_full.log
-for P in 0 1 0 1; do
-HV_PDL=$P timeout -k 5 600 python bench.py --steps 3 --warmup 3 --no-secondary --no-cpu-baseline > gpurun_out/bench_pdl$P.json 2>gpurun_out/bench_pdl$P.err; echo "bench pdl=$P exit=$?"
-python - <<PY
-import json
-d=json.load(open("gpurun_out/bench_pdl$P.json")); print("PDL=$P", round(d["value"],3), "clips/s", round(d["ms_per_step"],1), "ms  clk", d["clocks"]["sm_mhz"], " train", d["train"]["ms_per_step"], "eager", d["train"]["ms_per_step_eager"])
-PY
-done
+for L in 256 274; do L=$L timeout 120 python tools/attn_timeline.py > gpurun_out/attn_tc2_timeline_L$L.txt 2>&1; sed -n 1,1p gpurun_out/attn_tc2_timeline_L$L.txt; sed -n 6,9p gpurun_out/attn_tc2_timeline_L$L.txt; tail -1 gpurun_out/attn_tc2_timeline_L$L.txt; done
+timeout 300 python tools/attn_tc2_check.py > gpurun_out/attn_tc2_check.txt 2>&1; grep "worst\|FAIL\|frames 128" gpurun_out/attn_tc2_check.txt
+HV_ATTN_TC2=0 timeout 300 python tools/attn_tc2_check.py 2>&1 | grep "frames 128" | sed 's/^/v1 /'
