@@ -28,6 +28,11 @@
 // x 16 heads): L = 256 0.097 against 0.108 ms (354 / 319 TFLOP/s), L = 274 0.144 against 0.149 ms; switching single parts off
 // (profiles/r02_j_attn_tc2_parts.txt) shows a tile is bound by the chain of hand-overs P(T) -> P V(T) -> S(T+1).H1 -> exp, not by
 // MUFU or TMEM throughput: with stores, exponentials, epilogue and bounds all off it still takes 3700 clk.
+// Timeline of the final kernel (tools/attn_timeline.py, profiles/r02_m_*): 5200 clk per tile at L = 256 = hand-over 80-460 +
+// P V issue 1240-1420 (16 TS-mode MMAs at 88 clk) + S.H1 410 + exp pass of the key-half-1 warps 2230 (8 chunks of 16 keys at
+// ~275 clk; 331 before the loop was software-pipelined) + arrive 120.  Tried and rejected on the same box: forcing the program
+// order MUFU group / finish part / MUFU group ... through value-neutral LOP3 dependencies (ptxas otherwise emits the 16
+// MUFU.EX2 of a chunk back to back): 0.093-0.094 ms against 0.091 ms, exp pass 2500 clk — the chunk time is not MUFU issue order.
 //
 // Warp roles (352 threads): warps 0..7 softmax + epilogue (TMEM lane quarter = warp % 4, key half = warp / 4),
 // warp 8 = MMA issuer + TMEM owner, warp 9 = TMA producer, warp 10 = norms / bounds.  Warps 8 and 9 run with all 32
