@@ -153,15 +153,21 @@ __device__ __forceinline__ void issue_s_like(uint32_t d_tmem, const uint8_t* a_t
         if (cols <= 0) continue;
         const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(b_rows + r0 * 128));
         const uint32_t idesc = tc::make_idesc_bf16(QT, cols);
-#pragma unroll
-        for (int k = 0; k < HD / 16; ++k) tc::umma_bf16_w(d_tmem + (uint32_t)r0, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, k != 0);
+        tc::umma_bf16_w4(d_tmem + (uint32_t)r0, da, db, idesc);  // the four K = 16 steps of head_dim 64 under one election
     }
 }
 // PV-like product: D[128 x 64] = A[128 x kdim] B[kdim x 64], A staged K-major in 64-column chunks, B = [kdim rows][64] rows of
 // 128 B as TMA delivers them (MN-major operand)
 __device__ __forceinline__ void issue_pv_like(uint32_t d_tmem, const uint8_t* a_stage, const uint8_t* b_rows, int kdim) {
     constexpr uint32_t idesc = tc::make_idesc_bf16_bmn(QT, HD);
-    for (int j = 0; j < kdim / 16; ++j) {
+    const int n16 = kdim / 16;
+    int j = 0;
+    for (; j + 4 <= n16; j += 4) {  // one 64-column chunk of A = four K = 16 steps, one election (elect.sync costs ~70 clk per MMA)
+        const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(a_stage + (j >> 2) * TBYTES));
+        const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(b_rows + j * 2048));
+        tc::umma_bf16_pv_w4(d_tmem, da, db, idesc, j != 0);
+    }
+    for (; j < n16; ++j) {
         const uint64_t da = tc::make_smem_desc_k128(tc::smem_u32(a_stage + (j >> 2) * TBYTES)) + (uint64_t)(2 * (j & 3));
         const uint64_t db = tc::make_smem_desc_k128(tc::smem_u32(b_rows + j * 2048));
         tc::umma_bf16_w(d_tmem, da, db, idesc, j != 0);

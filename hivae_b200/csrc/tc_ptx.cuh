@@ -202,6 +202,26 @@ __device__ __forceinline__ void umma_bf16_ts_w(uint32_t tmem_d, uint32_t tmem_a,
         "}\n" ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// four consecutive K = 16 steps of a P V-like product with BOTH operands in shared memory under ONE election: A a K-major
+// SWIZZLE_128B chunk (descriptor + 2 per step), B an MN-major tile whose 16-row K groups are 2048 B apart (+ 128 per step);
+// `accumulate` applies to the first step
+__device__ __forceinline__ void umma_bf16_pv_w4(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred e, p, po;\n"
+        ".reg .b64 a1, a2, a3, b1, b2, b3;\n"
+        "add.u64 a1, %1, 2; add.u64 a2, %1, 4; add.u64 a3, %1, 6;\n"
+        "add.u64 b1, %2, 128; add.u64 b2, %2, 256; add.u64 b3, %2, 384;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "setp.eq.b32 po, 0, 0;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], a1, b1, %3, po;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], a2, b2, %3, po;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], a3, b3, %3, po;\n"
+        "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // four consecutive K = 16 steps of a P V-like product under ONE election: A from tensor memory (8 columns per step), B an
 // MN-major tile whose 16-row K groups are 2048 B apart (descriptor start + 128 per step); `accumulate` applies to the first
 __device__ __forceinline__ void umma_bf16_ts_w4(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {

@@ -24,7 +24,7 @@ echo "train launch list exit=$?"
 bash tools/ncu_one.sh gemm_ff1 gemm_tc_kernel
 bash tools/ncu_one.sh gemm_out gemm_tc_kernel
 bash tools/ncu_one.sh wgrad gemm_tc_kernel
-bash tools/ncu_one.sh attn attn_tc_kernel
+bash tools/ncu_one.sh attn attn_tc2_kernel
 bash tools/ncu_one.sh attn_bwd_dit attn_bwd_dq_tc
 cp gpurun_out/prof_attn_bwd_dit.ncu-rep gpurun_out/prof_attn_bwd_dq.ncu-rep 2>/dev/null
 bash tools/ncu_one.sh attn_bwd_dit attn_bwd_dkv_tc

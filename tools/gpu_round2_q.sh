@@ -1,6 +1,5 @@
 mkdir -p gpurun_out
-for rep in 1 2; do
-timeout 300 python tools/attn_tc2_check.py > gpurun_out/attn_tc2_check.txt 2>&1; grep "worst\|FAIL\|frames 128" gpurun_out/attn_tc2_check.txt | sed 's/^/v2 /'
-HV_ATTN_TC2=0 timeout 300 python tools/attn_tc2_check.py 2>&1 | grep "frames 128" | sed 's/^/v1 /'
-done
-L=256 timeout 120 python tools/attn_timeline.py > gpurun_out/attn_tc2_timeline_L256.txt 2>&1; sed -n 6,9p gpurun_out/attn_tc2_timeline_L256.txt; tail -1 gpurun_out/attn_tc2_timeline_L256.txt
+timeout -k 5 900 python -m pytest tests -x -q -m gpu -k "attention or block or train or golden" > gpurun_out/pytest_attn.log 2>&1; echo "pytest exit=$?"; tail -3 gpurun_out/pytest_attn.log
+timeout -k 5 300 python tools/bench_attn_shapes.py > gpurun_out/attn_shapes.txt 2>&1; echo "shapes exit=$?"; cat gpurun_out/attn_shapes.txt
+timeout -k 5 300 python tools/bench_train.py --steps 5 --graph > gpurun_out/bench_train_graph.json 2> gpurun_out/bench_train_graph.err; echo "train exit=$?"; cut -c1-400 gpurun_out/bench_train_graph.json
+bash tools/ncu_one.sh attn attn_tc2_kernel
