@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ CUtensorMap tk,
                 const __grid_constant__ CUtensorMap tv, const Tc2Args a) {
     extern __shared__ uint8_t smem_raw[];
-    __shared__ __align__(8) uint64_t q_full[2], q_free[2], k_full[2], k_free[2], v_full, v_free, s_full[2][2], p_full, o_full, n_full[4];
+    __shared__ __align__(8) uint64_t q_full[2], q_free[2], k_full[2], k_free[2], v_full, v_free, s_full[2][2], p_full[2], o_full, n_full[4];
     __shared__ uint32_t tmem_slot;
     __shared__ float qn[4][QT];      // per tile (ring of 4): the bound m_i * log2(e) of every query row
     __shared__ int exact_f[4];       // per tile: bound too large -> exact maximum pass
@@ -145,7 +145,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
 #pragma unroll
         for (int i = 0; i < 4; ++i) tc::mbar_init(&n_full[i], 1);
         tc::mbar_init(&v_full, 1); tc::mbar_init(&v_free, 1);
-        tc::mbar_init(&p_full, 8); tc::mbar_init(&o_full, 1);           // p_full: one arrival per softmax warp
+        tc::mbar_init(&p_full[0], 4); tc::mbar_init(&p_full[1], 4); tc::mbar_init(&o_full, 1);  // p_full[h]: one arrival per softmax warp of key half h
         tc::fence_barrier_init();
     }
     if (warp == 8) tc::tmem_alloc(&tmem_slot, TMEM_COLS);
@@ -238,35 +238,32 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                 }
                 tc::umma_commit_w(&s_full[T & 1][h]);
             };
-            auto issue_pv = [&](int T, bool tail) {
-                constexpr uint32_t idesc = tc::make_idesc_bf16_bmn(QT, HD);
-                if (tail) {  // P in shared memory (rows 0..31 of every 64-key chunk)
-                    for (int j = 0; j < KP / 16; ++j) {
-                        const uint64_t da = tc::make_smem_desc_k128(p_s + (uint32_t)((j >> 2) * QBYTES)) + (uint64_t)(2 * (j & 3));
-                        const uint64_t db = tc::make_smem_desc_k128(v_s + (uint32_t)(j * 2048));  // 16 keys x 128 B, MN-major
-                        tc::umma_bf16_w(tmem_base + O_COL, da, db, idesc, j != 0);
-                    }
-                } else {     // P in tensor memory, in place over the first half of the columns of its S half-buffer
-                    uint32_t acc = 0;
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const int n16 = (h ? KP - HB : HB) >> 4;
-                        const uint32_t pa = tmem_base + S_COL + (uint32_t)((2 * T + h) % 3) * SBUF;
-                        const int nj = n16;
-                        int j = 0;
-                        for (; j + 4 <= nj; j += 4) {   // four K = 16 steps per election
-                            const uint64_t db = tc::make_smem_desc_k128(v_s + (uint32_t)((h * hb + j) * 2048));
-                            tc::umma_bf16_ts_w4(tmem_base + O_COL, pa + (uint32_t)(8 * j), db, idesc, acc);
-                            acc = 1;
-                        }
-                        for (; j < nj; ++j) {
-                            const uint64_t db = tc::make_smem_desc_k128(v_s + (uint32_t)((h * hb + j) * 2048));
-                            tc::umma_bf16_ts_w(tmem_base + O_COL, pa + (uint32_t)(8 * j), db, idesc, acc);
-                            acc = 1;
-                        }
-                    }
+            // P V(T) is issued PER KEY HALF as soon as that half of P is complete: the key-half-0 warps arrive ~1000 clk before
+            // the key-half-1 warps (they get their S earlier), so half of the P V issue time leaves the critical chain
+            // P(T).H1 -> P V -> S(T+1).H1 -> exp.  The arrival of the key-half-0 warps also says "O(T-1) has been read back".
+            constexpr uint32_t idesc_pv = tc::make_idesc_bf16_bmn(QT, HD);
+            auto issue_pv_tail = [&]() {  // P in shared memory (rows 0..31 of every 64-key chunk), keys of all eight warps
+                for (int j = 0; j < KP / 16; ++j) {
+                    const uint64_t da = tc::make_smem_desc_k128(p_s + (uint32_t)((j >> 2) * QBYTES)) + (uint64_t)(2 * (j & 3));
+                    const uint64_t db = tc::make_smem_desc_k128(v_s + (uint32_t)(j * 2048));  // 16 keys x 128 B, MN-major
+                    tc::umma_bf16_w(tmem_base + O_COL, da, db, idesc_pv, j != 0);
                 }
-                tc::umma_commit_w(&o_full);
+            };
+            auto issue_pv_half = [&](int T, int h) {  // P in tensor memory, in place over the first half of the columns of its S half-buffer
+                const int nj = (h ? KP - HB : HB) >> 4;
+                const uint32_t pa = tmem_base + S_COL + (uint32_t)((2 * T + h) % 3) * SBUF;
+                uint32_t acc = h ? 1u : 0u;   // half 0 starts the accumulator (it is never empty: HB >= 16)
+                int j = 0;
+                for (; j + 4 <= nj; j += 4) {   // four K = 16 steps per election
+                    const uint64_t db = tc::make_smem_desc_k128(v_s + (uint32_t)((h * hb + j) * 2048));
+                    tc::umma_bf16_ts_w4(tmem_base + O_COL, pa + (uint32_t)(8 * j), db, idesc_pv, acc);
+                    acc = 1;
+                }
+                for (; j < nj; ++j) {
+                    const uint64_t db = tc::make_smem_desc_k128(v_s + (uint32_t)((h * hb + j) * 2048));
+                    tc::umma_bf16_ts_w(tmem_base + O_COL, pa + (uint32_t)(8 * j), db, idesc_pv, acc);
+                    acc = 1;
+                }
             };
             auto after_s = [&](int T, int it, int i) {  // both halves of S(T) issued: its Q buffer and (last tile) its K buffer retire with them
                 tc::umma_commit_w(&q_free[T & 1]);
@@ -287,11 +284,22 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                     tc::fence_after_sync();
                     issue_s(T + 1, it1, 0);  // ring buffer of S(T-1).H1 = P(T-1).H1: P V(T-1) is ahead of it in the (in-order) MMA pipe
                 }
-                tc::mbar_wait(&p_full, (uint32_t)(T & 1));  // P(T) written; O(T-1) read back
+                tc::mbar_wait(&p_full[0], (uint32_t)(T & 1));  // P(T).H0 written; O(T-1) read back
                 if (i == 0) tc::mbar_wait(&v_full, (uint32_t)(it & 1));
                 tc::fence_after_sync();
-                stamp(T, 12);
-                issue_pv(T, a.Lq - i * QT <= 32);
+                if (a.Lq - i * QT <= 32) {   // tail tile: every warp holds keys of both halves
+                    tc::mbar_wait(&p_full[1], (uint32_t)(T & 1));
+                    tc::fence_after_sync();
+                    stamp(T, 12);
+                    issue_pv_tail();
+                } else {
+                    issue_pv_half(T, 0);
+                    tc::mbar_wait(&p_full[1], (uint32_t)(T & 1));  // P(T).H1 written
+                    tc::fence_after_sync();
+                    stamp(T, 12);
+                    issue_pv_half(T, 1);
+                }
+                tc::umma_commit_w(&o_full);
                 stamp(T, 13);
                 // S(T+1).H1 goes into the ring buffer of S(T).H0, which now holds P(T).H0: behind P V(T) in the pipe
                 if (T + 1 < ntiles) { issue_s(T + 1, it1, 1); after_s(T + 1, it1, i1); }
@@ -491,7 +499,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                 tc::fence_before_sync();
                 if (tail) tc::fence_proxy_async();   // P of a tail tile: generic-proxy stores -> visible to the tensor core
                 __syncwarp();
-                if (lane == 0) tc::mbar_arrive(&p_full);
+                if (lane == 0) tc::mbar_arrive(&p_full[h]);
                 if (q == 0) stamp(T, h * 6 + 2);
                 if (h == 0) {
                     const int qr = i * QT + row;
