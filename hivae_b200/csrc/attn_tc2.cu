@@ -174,17 +174,28 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                 tc::tma_load_2d_w(q_s + (uint32_t)(b * QBYTES + j * 4096), &tq, &q_full[b], col, qrow0 + i * QT + (tail ? 0 : j * 32));
             ++T;
         };
+        // K is double-buffered across items and requested ONE ITEM AHEAD, before the wait for the single V buffer: the bounds warp
+        // needs K(it+1) (row norms of ~280 keys, ~3000 clk) before the first tile of item it+1 can start its exp pass; requested
+        // behind V(it) it arrived ~3000 clk later and the key-half-1 warps waited ~1300 clk at every item boundary
+        // (tools/attn_timeline.py).
+        auto request_k = [&](long long w, int item) {
+            const int seq = (int)(w / a.heads);
+            const int col = (int)(w - (long long)seq * a.heads) * HD;
+            const int kvrow0 = (int)(seq * a.kv_sa);
+            const int kb = item & 1;
+            tc::mbar_wait(&k_free[kb], (uint32_t)(((item >> 1) & 1) ^ 1));
+            tc::mbar_expect_tx_w(&k_full[kb], KP32 * 128);
+            for (int j = 0; j < KP32 / 32; ++j)
+                tc::tma_load_2d_w(k_s + (uint32_t)(kb * KP32 * 128 + j * 4096), &tk, &k_full[kb], col, kvrow0 + j * 32);
+        };
+        if ((long long)blockIdx.x < a.items) request_k(blockIdx.x, 0);
         for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
             const int seq = (int)(w / a.heads);
             const int col = (int)(w - (long long)seq * a.heads) * HD;
             const int qrow0 = (int)(seq * a.q_sa), kvrow0 = (int)(seq * a.kv_sa);  // < 2^31 rows (checked on the host)
-            const int kb = it & 1;
-            tc::mbar_wait(&k_free[kb], (uint32_t)(((it >> 1) & 1) ^ 1));
-            tc::mbar_expect_tx_w(&k_full[kb], KP32 * 128);
-            for (int j = 0; j < KP32 / 32; ++j)
-                tc::tma_load_2d_w(k_s + (uint32_t)(kb * KP32 * 128 + j * 4096), &tk, &k_full[kb], col, kvrow0 + j * 32);
             load_q(qrow0, col, 0);
             if (nq > 1) load_q(qrow0, col, 1);
+            if (w + gridDim.x < a.items) request_k(w + gridDim.x, it + 1);
             tc::mbar_wait(&v_free, (uint32_t)((it & 1) ^ 1));
             tc::mbar_expect_tx_w(&v_full, KP32 * 128);
             for (int j = 0; j < KP32 / 32; ++j)
@@ -198,14 +209,17 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
         for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
             const int kb = it & 1;
             tc::mbar_wait(&k_full[kb], (uint32_t)((it >> 1) & 1));
+            stamp(T, 9);
             float km = 0.f;
             for (int r = lane; r < a.Lkv; r += 32) km = fmaxf(km, row_sumsq(Ks + kb * KP32 * 128, r, lane));
             const float kmax = sqrtf(warp_max(km));
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&k_free[kb]);
+            stamp(T, 10);
             for (int i = 0; i < nq; ++i, ++T) {
                 const int b = T & 1, slot = T & 3;
                 tc::mbar_wait(&q_full[b], (uint32_t)((T >> 1) & 1));
+                stamp(T, 5);
                 const int rem = a.Lq - i * QT;
                 const bool tail = rem <= 32;
                 float mb = 0.f;

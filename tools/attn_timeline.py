@@ -23,9 +23,9 @@ run(); torch.cuda.synchronize()
 assert _lib.load().hv_attn_timeline_read(buf.ctypes.data_as(C.c_void_p)) == 1
 t = buf.reshape(64, 16).astype(np.int64)
 t0 = t[t > 0].min()
-names = {11: "bounds", 15: "mma top", 0: "h0 S rdy", 1: "h0 exp", 2: "h0 arrive", 6: "h1 S rdy", 7: "h1 exp", 8: "h1 arrive", 12: "mma p_full",
+names = {9: "n k_full", 10: "n K done", 5: "n q_full", 11: "bounds", 15: "mma top", 0: "h0 S rdy", 1: "h0 exp", 2: "h0 arrive", 6: "h1 S rdy", 7: "h1 exp", 8: "h1 arrive", 12: "mma p_full",
          13: "pv issued", 14: "s.h1 iss", 3: "h0 o_full", 4: "h0 epi"}
-order = [11, 15, 0, 1, 2, 6, 7, 8, 12, 13, 14, 3, 4]
+order = [9, 10, 5, 11, 15, 0, 1, 2, 6, 7, 8, 12, 13, 14, 3, 4]
 print("L = %d; " % L + " | ".join(names[i] for i in order))
 for T in range(10, 22):
     print("tile %2d: " % T + " ".join("%8d" % (t[T, i] - t0 if t[T, i] else -1) for i in order))
