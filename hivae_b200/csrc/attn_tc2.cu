@@ -34,8 +34,8 @@
 // order MUFU group / finish part / MUFU group ... through value-neutral LOP3 dependencies (ptxas otherwise emits the 16
 // MUFU.EX2 of a chunk back to back): 0.093-0.094 ms against 0.091 ms, exp pass 2500 clk — the chunk time is not MUFU issue order.
 //
-// Warp roles (352 threads): warps 0..7 softmax + epilogue (TMEM lane quarter = warp % 4, key half = warp / 4),
-// warp 8 = MMA issuer + TMEM owner, warp 9 = TMA producer, warp 10 = norms / bounds.  Warps 8 and 9 run with all 32
+// Warp roles (384 threads): warps 0..7 softmax + epilogue (TMEM lane quarter = warp % 4, key half = warp / 4),
+// warp 8 = MMA issuer + TMEM owner, warp 9 = TMA producer, warps 10 / 11 = norms / bounds (rows split between them).  Warps 8 and 9 run with all 32
 // lanes converged and warp-uniform operands; one elected lane issues (tc_ptx.cuh *_w).
 #include <cuda.h>
 #include <cstdlib>
@@ -46,7 +46,7 @@ int hv_make_tmap_bf16(const void* ptr, long long rows, int K, long long ld, int 
 
 namespace {
 
-constexpr int QT = 128, HD = 64, KMAX = 288, THREADS = 352;
+constexpr int QT = 128, HD = 64, KMAX = 288, THREADS = 384;
 constexpr int O_COL = 0, S_COL = 64, SBUF = 144;
 constexpr uint32_t TMEM_COLS = 512;
 constexpr int QBYTES = QT * 128;
@@ -119,7 +119,8 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
     __shared__ __align__(8) uint64_t q_full[2], q_free[2], k_full[2], k_free[2], v_full, v_free, s_full[2][2], p_full[2], o_full, n_full[4];
     __shared__ uint32_t tmem_slot;
     __shared__ float qn[4][QT];      // per tile (ring of 4): the bound m_i * log2(e) of every query row
-    __shared__ int exact_f[4];       // per tile: bound too large -> exact maximum pass
+    __shared__ int exact_f[4][2];    // per tile and bounds warp: bound too large -> exact maximum pass
+    __shared__ float kpart[2][2];    // per item parity and bounds warp: max_j |k_j|^2 over that warp's keys
     __shared__ float smax[2][QT], ssum[2][2][QT];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -138,12 +139,12 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
         tc::prefetch_tmap(&tq); tc::prefetch_tmap(&tk); tc::prefetch_tmap(&tv);
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
-            tc::mbar_init(&q_full[i], 1); tc::mbar_init(&q_free[i], 2);   // free: MMA commit + norm warp
-            tc::mbar_init(&k_full[i], 1); tc::mbar_init(&k_free[i], 2);
+            tc::mbar_init(&q_full[i], 1); tc::mbar_init(&q_free[i], 3);   // free: MMA commit + the two bounds warps
+            tc::mbar_init(&k_full[i], 1); tc::mbar_init(&k_free[i], 3);
             tc::mbar_init(&s_full[i][0], 1); tc::mbar_init(&s_full[i][1], 1);
         }
 #pragma unroll
-        for (int i = 0; i < 4; ++i) tc::mbar_init(&n_full[i], 1);
+        for (int i = 0; i < 4; ++i) tc::mbar_init(&n_full[i], 2);   // one arrival per bounds warp
         tc::mbar_init(&v_full, 1); tc::mbar_init(&v_free, 1);
         tc::mbar_init(&p_full[0], 4); tc::mbar_init(&p_full[1], 4); tc::mbar_init(&o_full, 1);  // p_full[h]: one arrival per softmax warp of key half h
         tc::fence_barrier_init();
@@ -202,39 +203,47 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                 tc::tma_load_2d_w(v_s + (uint32_t)(j * 4096), &tv, &v_full, col, kvrow0 + j * 32);
             for (int i = 2; i < nq; ++i) load_q(qrow0, col, i);
         }
-    } else if (warp == 10) {
-        // ===================================================== norms: m_i * log2(e) = |q_i| * max_j |k_j| * scale * log2(e)
+    } else if (warp >= 10) {
+        // ===================================================== bounds: m_i * log2(e) = |q_i| * max_j |k_j| * scale * log2(e)
+        // TWO warps (10, 11: different SM sub-partitions) split the key rows and the query rows: one warp needed ~3300 clk for
+        // the keys of an item and ~2600 for the 128 query rows of a tile (it shares its scheduler with two softmax warps),
+        // which delayed the first tile of every item (tools/attn_timeline.py)
+        const int nw = warp - 10;
         int T = 0, it = 0;
-        const float sl2 = fabsf(a.sl2) * 1.02f;   // head room: 0.8 % for each of the two norms (row_sumsq is within 1.6 %) + the rounding of S
+        const float sl2 = fabsf(a.sl2) * 1.02f;   // head room: 0.8 % for each of the two norms (row_sumsq is within 1.6 %) + sqrt.approx + the rounding of S
+        auto sqrt_fast = [](float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; };
         for (long long w = blockIdx.x; w < a.items; w += gridDim.x, ++it) {
             const int kb = it & 1;
             tc::mbar_wait(&k_full[kb], (uint32_t)((it >> 1) & 1));
-            stamp(T, 9);
+            if (nw == 0) stamp(T, 9);
             float km = 0.f;
-            for (int r = lane; r < a.Lkv; r += 32) km = fmaxf(km, row_sumsq(Ks + kb * KP32 * 128, r, lane));
-            const float kmax = sqrtf(warp_max(km));
+            for (int r = lane + 32 * nw; r < a.Lkv; r += 64) km = fmaxf(km, row_sumsq(Ks + kb * KP32 * 128, r, lane));
+            km = warp_max(km);
+            if (lane == 0) kpart[kb][nw] = km;
+            tc::named_bar_sync(3, 64);             // the two bounds warps (a warp is never more than one item ahead of the other)
+            const float kmax = sqrt_fast(fmaxf(kpart[kb][0], kpart[kb][1]));
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(&k_free[kb]);
-            stamp(T, 10);
+            if (nw == 0) stamp(T, 10);
             for (int i = 0; i < nq; ++i, ++T) {
                 const int b = T & 1, slot = T & 3;
                 tc::mbar_wait(&q_full[b], (uint32_t)((T >> 1) & 1));
-                stamp(T, 5);
+                if (nw == 0) stamp(T, 5);
                 const int rem = a.Lq - i * QT;
                 const bool tail = rem <= 32;
                 float mb = 0.f;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 2 * nw; j < 2 * nw + 2; ++j) {
                     const int r = j * 32 + lane;
-                    const float m = sqrtf(row_sumsq(Qs + b * QBYTES, r, lane)) * kmax * sl2;
+                    const float m = sqrt_fast(row_sumsq(Qs + b * QBYTES, r, lane)) * kmax * sl2;
                     qn[slot][r] = m;
                     if ((tail ? lane : r) < rem) mb = fmaxf(mb, m);   // rows past the sequence hold other data
                 }
                 mb = warp_max(mb);
-                if (lane == 0) exact_f[slot] = (a.force_exact || !(mb <= BOUND_MAX)) ? 1 : 0;
+                if (lane == 0) exact_f[slot][nw] = (a.force_exact || !(mb <= BOUND_MAX)) ? 1 : 0;
                 __syncwarp();
                 if (lane == 0) { tc::mbar_arrive(&n_full[slot]); tc::mbar_arrive(&q_free[b]); }
-                stamp(T, 11);
+                if (nw == 0) stamp(T, 11);
             }
         }
     } else if (warp == 8) {
@@ -378,7 +387,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                 const uint32_t s_base = t_lane + S_COL + (uint32_t)((2 * T + h) % 3) * SBUF;  // column of key c_begin; P in place
                 const uint32_t s_addr = s_base - (uint32_t)c_begin;
                 tc::mbar_wait(&n_full[slot], (uint32_t)((T >> 2) & 1));
-                const bool exact = exact_f[slot] != 0;
+                const bool exact = (exact_f[slot][0] | exact_f[slot][1]) != 0;
                 float msc = qn[slot][row];
                 tc::mbar_wait(&s_full[T & 1][h], (uint32_t)((T >> 1) & 1));
                 tc::fence_after_sync();
