@@ -24,15 +24,18 @@
 // and P goes through shared memory (rows 0..31 only), P V as an SS MMA.
 // Measured (tools/probes/mma_probe.cu, tmem_probe.cu): an M = 128 MMA issues every 65-88 clk whatever N <= 128 is, so the
 // 18 N = 64 MMAs of P V cost as much as 18 N = 128 ones; MUFU.EX2 runs at 15.8 / clk / SM, which puts the floor of the
-// exponentials of a 128 x 288 tile at 2330 clk of the ~5500 a tile takes here.  Same-box A/B against attn_tc.cu (128 sequences
-// x 16 heads): L = 256 0.097 against 0.108 ms (354 / 319 TFLOP/s), L = 274 0.144 against 0.149 ms; switching single parts off
-// (profiles/r02_j_attn_tc2_parts.txt) shows a tile is bound by the chain of hand-overs P(T) -> P V(T) -> S(T+1).H1 -> exp, not by
-// MUFU or TMEM throughput: with stores, exponentials, epilogue and bounds all off it still takes 3700 clk.
-// Timeline of the final kernel (tools/attn_timeline.py, profiles/r02_m_*): 5200 clk per tile at L = 256 = hand-over 80-460 +
-// P V issue 1240-1420 (16 TS-mode MMAs at 88 clk) + S.H1 410 + exp pass of the key-half-1 warps 2230 (8 chunks of 16 keys at
-// ~275 clk; 331 before the loop was software-pipelined) + arrive 120.  Tried and rejected on the same box: forcing the program
-// order MUFU group / finish part / MUFU group ... through value-neutral LOP3 dependencies (ptxas otherwise emits the 16
-// MUFU.EX2 of a chunk back to back): 0.093-0.094 ms against 0.091 ms, exp pass 2500 clk — the chunk time is not MUFU issue order.
+// exponentials of a 128 x 288 tile at 2330 clk.  Same-box A/B against attn_tc.cu (128 sequences x 16 heads,
+// profiles/r02_q_attn_ab.txt): L = 256 0.077 against 0.107 ms (447 / 321 TFLOP/s), L = 274 0.117 against 0.150 ms (336 / 263).
+// How it got there, every step read off the timeline of CTA 0 (HV_ATTN_TIMELINE=1, tools/attn_timeline.py, profiles/r02_[mpq]_*):
+//   0.097 / 0.144  first version of this design (one pass, P in TMEM, O read back by the key-half-0 warps)
+//   0.091 / 0.134  exp loop software-pipelined by hand: row sums / packing / P store of chunk i-1 inside the MUFU phase of
+//                  chunk i (331 -> 275 clk per 16-key chunk; one warp per SM sub-partition runs it most of the time)
+//   0.087 / 0.125  P V issued per key half as soon as that half of P is complete (two p_full barriers)
+//   0.083 / 0.125  K of the next item requested BEFORE the wait for the single V buffer (it arrived ~3000 clk late)
+//   0.077 / 0.117  two bounds warps + sqrt.approx: the bounds of an item's first tile are ready before its S
+// What a tile costs now (L = 256, ~4300 clk): exp pass of the key-half-1 warps ~2350 (8 chunks at ~290 clk against the MUFU
+// bound of 128), P V.H1 issue ~750, S(T+1).H1 issue ~400, hand-overs ~500.  Tried and rejected: forcing the program order
+// MUFU group / finish part / MUFU group through value-neutral LOP3 dependencies (0.093 against 0.091 at that stage).
 //
 // Warp roles (384 threads): warps 0..7 softmax + epilogue (TMEM lane quarter = warp % 4, key half = warp / 4),
 // warp 8 = MMA issuer + TMEM owner, warp 9 = TMA producer, warps 10 / 11 = norms / bounds (rows split between them).  Warps 8 and 9 run with all 32
