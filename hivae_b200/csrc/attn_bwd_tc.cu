@@ -356,9 +356,14 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                 float sum = 0.f;
                 for_chunks(s_addr, c_begin, c_end, [&](int k, int c, const uint32_t (&va)[16]) {
                     float p[16];
+                    if (c + 16 <= a.Lkv) {   // every chunk but (at most) the last one: no per-element mask
 #pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        p[j] = (c + j < a.Lkv) ? tc::ex2_approx(fmaf(__uint_as_float(va[j]), a.sl2, -msc)) : 0.f;
+                        for (int j = 0; j < 16; ++j) p[j] = tc::ex2_approx(fmaf(__uint_as_float(va[j]), a.sl2, -msc));
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            p[j] = (c + j < a.Lkv) ? tc::ex2_approx(fmaf(__uint_as_float(va[j]), a.sl2, -msc)) : 0.f;
+                    }
 #pragma unroll
                     for (int j = 0; j < 8; ++j) preg[8 * k + j] = hv_pack_bf16(p[2 * j], p[2 * j + 1]);
                     sum += ((p[0] + p[1]) + (p[2] + p[3])) + ((p[4] + p[5]) + (p[6] + p[7]))
@@ -539,7 +544,9 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_cons
             // arrived on ds_full of its last tile after reading them)
             tc::named_bar_sync(1, 256);
             for (int i = threadIdx.x; i < QP; i += 256) {
-                const float2 s = i < a.Lq ? reinterpret_cast<const float2*>(a.stats)[w * a.Lq + i] : make_float2(0.f, 0.f);
+                // padded query columns: lse = +1e30 makes exp2(S c - lse) exactly 0 without a per-element mask (S is finite there:
+                // rows of the next sequence or TMA zero fill)
+                const float2 s = i < a.Lq ? reinterpret_cast<const float2*>(a.stats)[w * a.Lq + i] : make_float2(1e30f, 0.f);
                 sLse[i] = s.x; sD[i] = s.y;
             }
             tc::named_bar_sync(1, 256);
@@ -564,8 +571,7 @@ attn_bwd_dkv_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_cons
                     }
                     float p[16];
 #pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        p[j] = (c + j < a.Lq) ? tc::ex2_approx(fmaf(__uint_as_float(va[j]), a.sl2, -ls[j])) : 0.f;
+                    for (int j = 0; j < 16; ++j) p[j] = tc::ex2_approx(fmaf(__uint_as_float(va[j]), a.sl2, -ls[j]));
 #pragma unroll
                     for (int j = 0; j < 8; ++j) preg[8 * k + j] = hv_pack_bf16(p[2 * j], p[2 * j + 1]);
                 });
