@@ -56,6 +56,7 @@ SIGNATURES = {
     "hv_attn_bwd_prof_read": (_i, [_vp]),
     "hv_headnorm64_bwd": (_i, [_vp, _i64, _vp, _i64, _vp, _f, _i64, _i, _vp, _i64, _i, _vp, _vp, _vp, _vp]),
     "hv_attention_bwd": (_i, [_vp, _i64] * 8 + [_i, _i64, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp]),
+    "hv_attention_bwd_lse": (_i, [_vp, _i64] * 8 + [_i, _i64, _i, _i, _i, _i, _vp, _vp, _f, _vp, _i, _vp]),
     "hv_transpose2d": (_i, [_vp, _vp, _i64, _i64, _i64, _i64, _i, _vp]),
     "hv_transpose2d_colsum": (_i, [_vp, _vp, _i64, _i64, _i64, _i64, _i, _vp, _vp, _vp]),
     "hv_colsum_slices": (_i, []),
@@ -91,6 +92,8 @@ SIGNATURES = {
     "hv_maxpool2_bwd": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
     "hv_attention": (_i, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i, _i64, _i, _i, _i, _i,
                           C.POINTER(HvSeqMap), C.POINTER(HvSeqMap), _f, _vp, _vp]),
+    "hv_attention_lse": (_i, [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _i64, _i, _i64, _i, _i, _i, _i,
+                              C.POINTER(HvSeqMap), C.POINTER(HvSeqMap), _f, _vp, _vp, _vp]),
 }
 
 _lib = None

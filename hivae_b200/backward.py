@@ -132,7 +132,8 @@ def layernorm_backward(x, dy, weight, eps, dx=None, accumulate=False, affine_gra
 
 
 @_timed("attention_bwd")
-def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, scale, dq=None, dk=None, dv=None):
+def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, scale, dq=None, dk=None, dv=None, stats=None,
+                       have_lse=False):
     """Gradients of ops.attention (head_dim 64, no mask): q / k / v / out / dout are 2-D (rows, heads*64) views in one
     dtype (bf16 or fp32) with unit column stride -> (dq, dk, dv) of the same dtype, dense (rows, heads*64)."""
     _lib.require_device()
@@ -142,11 +143,15 @@ def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, sc
     dq, dk, dv = new(dq, q), new(dk, k), new(dv, v)   # callers may pass column slices of a wider gradient matrix
     for t in (dq, dk, dv):
         assert t.is_cuda and t.dim() == 2 and t.stride(1) == 1 and t.dtype == q.dtype and t.shape[1] == heads * 64
-    stats = torch.empty(seqs * heads * Lq * 2, dtype=torch.float32, device=q.device)
-    _lib.check(_lib.load().hv_attention_bwd(
+    # stats + have_lse: the workspace that ops.attention(..., lse=stats) filled in the forward (it returned True)
+    assert not have_lse or stats is not None
+    if stats is None:
+        stats = torch.empty(seqs * heads * Lq * 2, dtype=torch.float32, device=q.device)
+    assert stats.is_cuda and stats.dtype == torch.float32 and stats.is_contiguous() and stats.numel() >= seqs * heads * Lq * 2
+    _lib.check(_lib.load().hv_attention_bwd_lse(
         _p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0), _p(dout), dout.stride(0),
         _p(dq), dq.stride(0), _p(dk), dk.stride(0), _p(dv), dv.stride(0), _dt(q), seqs, heads, 64, Lq, Lkv,
-        C.byref(qmap), C.byref(kvmap), float(scale), _p(stats), _stream()))
+        C.byref(qmap), C.byref(kvmap), float(scale), _p(stats), 1 if have_lse else 0, _stream()))
     return dq, dk, dv
 
 

@@ -527,7 +527,7 @@ int launch_bwd(const BwdArgs& a, int64_t seqs, cudaStream_t st) {
 int hv_attention_bwd_tc_bf16(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                              const void* o, long long ldo, const void* dout, long long lddo, void* dq, long long lddq,
                              void* dk, long long lddk, void* dv, long long lddv, long long seqs, int heads, int Lq, int Lkv,
-                             const HvSeqMap& qm, const HvSeqMap& km, float scale, float* stats, cudaStream_t st);  // attn_bwd_tc.cu
+                             const HvSeqMap& qm, const HvSeqMap& km, float scale, float* stats, int have_lse, cudaStream_t st);  // attn_bwd_tc.cu
 
 int hv_attention_small_bwd_bf16(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                                 const void* o, long long ldo, const void* dout, long long lddo, void* dq, long long lddq,
@@ -536,11 +536,11 @@ int hv_attention_small_bwd_bf16(const void* q, long long ldq, const void* k, lon
 
 // Gradients of out = softmax(q k^T * scale) v for head_dim 64 (no mask).  All matrices are (rows, heads*64) with their own
 // leading dimension, one dtype (HV_F32 / HV_BF16); `stats` = seqs * heads * Lq * 2 floats of workspace.
-extern "C" int hv_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
-                                const void* out, int64_t ldo, const void* dout, int64_t lddo,
-                                void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, int dtype,
-                                int64_t seqs, int heads, int hd, int Lq, int Lkv, const HvSeqMap* qmap, const HvSeqMap* kvmap,
-                                float scale, float* stats, void* stream) {
+static int attention_bwd_dispatch(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                                  const void* out, int64_t ldo, const void* dout, int64_t lddo,
+                                  void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, int dtype,
+                                  int64_t seqs, int heads, int hd, int Lq, int Lkv, const HvSeqMap* qmap, const HvSeqMap* kvmap,
+                                  float scale, float* stats, int have_lse, void* stream) {
     HV_REQUIRE(hd == HDB, "hv_attention_bwd: head_dim %d != 64", hd);
     HV_REQUIRE(seqs >= 0 && heads > 0 && heads <= 65535 && seqs <= 65535 && Lq > 0 && Lkv > 0, "hv_attention_bwd: bad sizes");
     HV_REQUIRE(qmap && kvmap && qmap->sdiv > 0 && kvmap->sdiv > 0 && stats, "hv_attention_bwd: bad sequence maps / workspace");
@@ -554,8 +554,29 @@ extern "C" int hv_attention_bwd(const void* q, int64_t ldq, const void* k, int64
                                                *qmap, *kvmap, scale, hv_stream(stream));  // L <= 16: one warp per (sequence, head)
     if (rs != 0) return rs < 0 ? rs : HV_OK;
     const int rt = hv_attention_bwd_tc_bf16(q, ldq, k, ldk, v, ldv, out, ldo, dout, lddo, dq, lddq, dk, lddk, dv, lddv, seqs, heads, Lq, Lkv,
-                                            *qmap, *kvmap, scale, stats, hv_stream(stream));
+                                            *qmap, *kvmap, scale, stats, have_lse, hv_stream(stream));
     if (rt != 0) return rt < 0 ? rt : HV_OK;
     const int rc = launch_bwd_mma(a, seqs, hv_stream(stream));  // shape / alignment outside the tcgen05 kernels
     return rc == 1 ? launch_bwd<__nv_bfloat16>(a, seqs, hv_stream(stream)) : rc;
+}
+
+extern "C" int hv_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                                const void* out, int64_t ldo, const void* dout, int64_t lddo,
+                                void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, int dtype,
+                                int64_t seqs, int heads, int hd, int Lq, int Lkv, const HvSeqMap* qmap, const HvSeqMap* kvmap,
+                                float scale, float* stats, void* stream) {
+    return attention_bwd_dispatch(q, ldq, k, ldk, v, ldv, out, ldo, dout, lddo, dq, lddq, dk, lddk, dv, lddv, dtype, seqs, heads, hd, Lq, Lkv,
+                                  qmap, kvmap, scale, stats, 0, stream);
+}
+
+// hv_attention_bwd for a forward that ran through hv_attention_lse and returned 1: element 0 of every `stats` row already holds
+// the log2-domain log-sum-exp, so the tcgen05 dq kernel skips its row-maximum pass and both cross-warp exchanges (kernels that
+// do not use it recompute it).  have_lse = 0 is hv_attention_bwd.
+extern "C" int hv_attention_bwd_lse(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                                    const void* out, int64_t ldo, const void* dout, int64_t lddo,
+                                    void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, int dtype,
+                                    int64_t seqs, int heads, int hd, int Lq, int Lkv, const HvSeqMap* qmap, const HvSeqMap* kvmap,
+                                    float scale, float* stats, int have_lse, void* stream) {
+    return attention_bwd_dispatch(q, ldq, k, ldk, v, ldv, out, ldo, dout, lddo, dq, lddq, dk, lddk, dv, lddv, dtype, seqs, heads, hd, Lq, Lkv,
+                                  qmap, kvmap, scale, stats, have_lse != 0, stream);
 }

@@ -47,6 +47,7 @@ struct BwdTc {
     long long items;             // seqs * heads
     float sl2, scale;            // scale * log2(e), scale
     float* stats;                // [item][Lq][2] = (log2-domain log-sum-exp, D)
+    int have_lse;                // element 0 was written by the forward (hv_attention_lse): the dq kernel skips its maximum / sum passes
     unsigned long long* dbg;     // phase cycle counters (HV_ATTN_BWD_PROF=1) or nullptr: [kernel][cta][16]
 };
 
@@ -331,8 +332,10 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                 tc::mbar_wait(&s_full, ph);
                 tc::fence_after_sync();
                 BWD_TICK(1);   // wait S
-                // ---- pass 1: row maximum over this thread's key half
+                // ---- pass 1: row maximum over this thread's key half (skipped when the forward handed over the log-sum-exp: then
+                // P = exp2(S c - lse) is already normalised and neither the maximum nor the row sum is needed)
                 float mx = -INFINITY;
+                if (!a.have_lse)
                 for_chunks(s_addr, c_begin, c_end, [&](int, int c, const uint32_t (&va)[16]) {
                     if (c + 16 <= a.Lkv) {
                         float m4[4];
@@ -345,11 +348,17 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                         for (int j = 0; j < 16; ++j) if (c + j < a.Lkv) mx = fmaxf(mx, __uint_as_float(va[j]));
                     }
                 });
-                smax[h][row] = mx;
-                BWD_TICK(2);   // pass 1
-                tc::named_bar_sync(1, 256);
-                mx = fmaxf(mx, smax[h ^ 1][row]);
-                const float msc = mx * a.sl2;
+                float msc;
+                if (a.have_lse) {
+                    msc = valid ? __ldg(st) : 1e30f;   // rows past the sequence: P = 0
+                    BWD_TICK(2);
+                } else {
+                    smax[h][row] = mx;
+                    BWD_TICK(2);   // pass 1
+                    tc::named_bar_sync(1, 256);
+                    mx = fmaxf(mx, smax[h ^ 1][row]);
+                    msc = mx * a.sl2;
+                }
                 BWD_TICK(3);   // max exchange
                 // ---- pass 2: P~ = exp2(S c - max c) -> registers (packed bf16), row sum
                 uint32_t preg[72];
@@ -373,10 +382,13 @@ attn_bwd_dq_tc_kernel(const __grid_constant__ CUtensorMap tq, const __grid_const
                 tc::fence_before_sync();
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&s_free);
-                ssum[h][row] = sum;
-                tc::named_bar_sync(1, 256);
-                const float l = sum + ssum[h ^ 1][row];
-                if (h == 0 && valid) st[0] = msc + __log2f(l);
+                float l = 1.f;
+                if (!a.have_lse) {
+                    ssum[h][row] = sum;
+                    tc::named_bar_sync(1, 256);
+                    l = sum + ssum[h ^ 1][row];
+                    if (h == 0 && valid) st[0] = msc + __log2f(l);
+                }
                 BWD_TICK(5);   // sum exchange + stats
                 // ---- the previous tile's dQ (its MMA was issued behind this tile's S and is long done)
                 if (pend) epilogue();
@@ -667,7 +679,7 @@ extern "C" int hv_attn_bwd_prof_read(unsigned long long* host) {
 int hv_attention_bwd_tc_bf16(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
                              const void* o, long long ldo, const void* dout, long long lddo, void* dq, long long lddq,
                              void* dk, long long lddk, void* dv, long long lddv, long long seqs, int heads, int Lq, int Lkv,
-                             const HvSeqMap& qm, const HvSeqMap& km, float scale, float* stats, cudaStream_t st) {
+                             const HvSeqMap& qm, const HvSeqMap& km, float scale, float* stats, int have_lse, cudaStream_t st) {
     static const bool enabled = [] { const char* e = getenv("HV_ATTN_BWD_TC"); return !(e && atoi(e) == 0); }();
     if (!enabled) return 0;
     const bool dense = qm.sdiv == 1 && qm.sc == 1 && km.sdiv == 1 && km.sc == 1;
@@ -692,6 +704,7 @@ int hv_attention_bwd_tc_bf16(const void* q, long long ldq, const void* k, long l
     a.items = seqs * heads;
     a.sl2 = scale * 1.4426950408889634f; a.scale = scale;
     a.stats = stats;
+    a.have_lse = have_lse;
     a.dbg = bwd_prof_buffer();
     const int KP32 = (a.KP + 31) & ~31, QP32 = (a.QP + 31) & ~31;
     const int smem_dq = 2 * TBYTES + 2 * KP32 * 128 + ((a.KP + 63) >> 6) * TBYTES + 1024;

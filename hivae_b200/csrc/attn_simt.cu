@@ -106,18 +106,28 @@ int hv_attention_tc_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st);     
 int hv_attention_tc2_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st);    // attn_tc2.cu (same convention; tried first)
 int hv_attention_small_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st);  // attn_small.cu (same convention)
 
-extern "C" int hv_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
-                            void* out, int64_t ldo, int dtype, int64_t seqs, int heads, int hd, int Lq, int Lkv,
-                            const HvSeqMap* qmap, const HvSeqMap* kvmap, float scale, const float* mask, void* stream) {
+// shared body of hv_attention / hv_attention_lse; *wrote_lse <- 1 when the kernel that ran filled a.lse_stats
+static int attention_dispatch(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                              void* out, int64_t ldo, int dtype, int64_t seqs, int heads, int hd, int Lq, int Lkv,
+                              const HvSeqMap* qmap, const HvSeqMap* kvmap, float scale, const float* mask, float* stats,
+                              int* wrote_lse, void* stream) {
     HV_REQUIRE(seqs >= 0 && heads > 0 && Lq >= 0 && Lkv > 0, "hv_attention: bad sizes");
     HV_REQUIRE(qmap && kvmap && qmap->sdiv > 0 && kvmap->sdiv > 0, "hv_attention: bad sequence maps");
     HV_REQUIRE(dtype == HV_F32 || dtype == HV_BF16, "hv_attention: bad dtype");
     HV_REQUIRE(seqs * ((Lq + 15) / 16) < (1ll << 31) && heads <= 65535, "hv_attention: grid too large");
+    *wrote_lse = 0;
     if (seqs == 0 || Lq == 0) return HV_OK;
     AttnArgs a{q, k, v, out, ldq, ldk, ldv, ldo, heads, hd, Lq, Lkv, *qmap, *kvmap, scale, mask};
     cudaStream_t st = hv_stream(stream);
     if (dtype == HV_BF16) {
-        int rc = (Lq <= 16 && Lkv <= 16) ? hv_attention_small_bf16(a, seqs, st) : (Lkv >= 48 ? hv_attention_tc2_bf16(a, seqs, st) : 0);
+        int rc = 0;
+        if (Lq <= 16 && Lkv <= 16) rc = hv_attention_small_bf16(a, seqs, st);
+        else if (Lkv >= 48) {
+            a.lse_stats = stats;
+            rc = hv_attention_tc2_bf16(a, seqs, st);
+            if (rc == 1 && stats) *wrote_lse = 1;
+            a.lse_stats = nullptr;
+        }
         if (rc == 0 && Lkv >= 48) rc = hv_attention_tc_bf16(a, seqs, st);
         if (rc != 0) return rc < 0 ? rc : HV_OK;
     }
@@ -125,4 +135,22 @@ extern "C" int hv_attention(const void* q, int64_t ldq, const void* k, int64_t l
         (ldq % 8 == 0) && (ldk % 8 == 0) && (ldv % 8 == 0) && (ldo % 2 == 0))
         return hv_attention_flash_bf16(a, seqs, st);
     return dtype == HV_F32 ? launch_simt<float>(a, seqs, st) : launch_simt<__nv_bfloat16>(a, seqs, st);
+}
+
+extern "C" int hv_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                            void* out, int64_t ldo, int dtype, int64_t seqs, int heads, int hd, int Lq, int Lkv,
+                            const HvSeqMap* qmap, const HvSeqMap* kvmap, float scale, const float* mask, void* stream) {
+    int wrote = 0;
+    return attention_dispatch(q, ldq, k, ldk, v, ldv, out, ldo, dtype, seqs, heads, hd, Lq, Lkv, qmap, kvmap, scale, mask, nullptr, &wrote, stream);
+}
+
+// hv_attention that also hands the per-row log-sum-exp to the backward: `stats` is the workspace hv_attention_bwd takes
+// (seqs * heads * Lq * 2 floats); returns 1 when element 0 of every row was written (then call hv_attention_bwd_lse with
+// have_lse = 1 and the backward skips its own maximum / sum passes), 0 when the kernel that ran does not produce it, < 0 on error
+extern "C" int hv_attention_lse(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                                void* out, int64_t ldo, int dtype, int64_t seqs, int heads, int hd, int Lq, int Lkv,
+                                const HvSeqMap* qmap, const HvSeqMap* kvmap, float scale, const float* mask, float* stats, void* stream) {
+    int wrote = 0;
+    const int rc = attention_dispatch(q, ldq, k, ldk, v, ldv, out, ldo, dtype, seqs, heads, hd, Lq, Lkv, qmap, kvmap, scale, mask, stats, &wrote, stream);
+    return rc != HV_OK ? rc : wrote;
 }

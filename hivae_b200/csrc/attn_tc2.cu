@@ -62,6 +62,7 @@ struct Tc2Args {
     long long items;
     float sl2;
     int force_exact;  // HV_ATTN_EXACT=1: always take the maximum pass (tests)
+    float* lse;       // optional [item][Lq][2] floats: element 0 <- msc + log2(sum) per query row (for the backward)
     unsigned long long* tl;  // HV_ATTN_TIMELINE=1: clock64 stamps of CTA 0, 64 tiles x 16 events (tools/attn_timeline.py)
 };
 
@@ -347,6 +348,8 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
         // deferred epilogue of the previous tile (key-half-0 warps only)
         bool pend = false, pend_store = false, pend_active = false, pend_tail = false;
         __nv_bfloat16* pend_ptr = nullptr;
+        float* pend_lse = nullptr;
+        float pend_msc = 0.f;
         int pend_T = 0;
         auto epilogue = [&]() {
             tc::mbar_wait(&o_full, (uint32_t)(pend_T & 1));
@@ -363,6 +366,7 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                     sum = ssum[sb][0][row] + ssum[sb][1][row];
                 }
                 const float inv = 1.f / sum;
+                if (pend_store && pend_lse != nullptr) *pend_lse = pend_msc + __log2f(sum);  // log2-domain log-sum-exp of the row
 #pragma unroll
                 for (int half = 0; half < 2; ++half) {
                     float o[32];
@@ -535,6 +539,8 @@ attn_tc2_kernel(const __grid_constant__ CUtensorMap tq, const __grid_constant__ 
                     pend_tail = tail;
                     pend_store = qr < a.Lq;
                     pend_ptr = a.out + (seq * a.q_sa + qr) * a.ldo + head * HD;
+                    pend_lse = a.lse ? a.lse + (w * a.Lq + (qr < a.Lq ? qr : 0)) * 2 : nullptr;
+                    pend_msc = msc;
                 }
             }
         }
@@ -589,6 +595,7 @@ int hv_attention_tc2_bf16(const AttnArgs& a, int64_t seqs, cudaStream_t st) {
     t.items = seqs * a.heads;
     t.sl2 = a.scale * 1.4426950408889634f;
     t.force_exact = force_exact;
+    t.lse = a.lse_stats;
     static const bool timeline = [] { const char* e = getenv("HV_ATTN_TIMELINE"); return e && atoi(e) != 0; }();
     if (timeline && !g_tl && cudaMalloc(&g_tl, 1024 * sizeof(unsigned long long)) == cudaSuccess) cudaMemset(g_tl, 0, 1024 * sizeof(unsigned long long));
     t.tl = timeline ? g_tl : nullptr;

@@ -402,10 +402,22 @@ def seq_map(sdiv, sa, sb, sc):
     return m
 
 
-def attention(q, k, v, out, seqs, heads, hd, Lq, Lkv, qmap, kvmap, scale, mask=None):
-    """q/k/v/out are 2-D (rows, cols) views whose column 0 is head 0; row strides are taken from the views."""
+def attention(q, k, v, out, seqs, heads, hd, Lq, Lkv, qmap, kvmap, scale, mask=None, lse=None):
+    """q/k/v/out are 2-D (rows, cols) views whose column 0 is head 0; row strides are taken from the views.
+    lse: optional fp32 workspace of seqs * heads * Lq * 2 floats (the `stats` of backward.attention_backward); the call then
+    returns True when the kernel that ran left the per-row log-sum-exp there (hv_attention_lse), which lets the backward skip
+    its own maximum / sum passes, else False (the output is complete either way).  Without `lse` it returns `out`."""
     _lib.require_device()
     tok = _prof("attention_L%d" % Lkv, 4.0 * seqs * heads * Lq * Lkv * hd, q.element_size() * heads * hd * seqs * (2.0 * Lq + 2.0 * Lkv))
+    if lse is not None:
+        assert lse.is_cuda and lse.dtype == torch.float32 and lse.is_contiguous() and lse.numel() >= seqs * heads * Lq * 2
+        rc = _lib.load().hv_attention_lse(_p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0),
+                                          _dt(q), seqs, heads, hd, Lq, Lkv, C.byref(qmap), C.byref(kvmap), float(scale),
+                                          _p(mask), _p(lse), _stream())
+        if rc < 0:
+            _lib.check(rc)
+        _prof_end(tok)
+        return rc == 1
     _lib.check(_lib.load().hv_attention(_p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(out), out.stride(0),
                                         _dt(q), seqs, heads, hd, Lq, Lkv, C.byref(qmap), C.byref(kvmap), float(scale),
                                         _p(mask), _stream()))

@@ -103,7 +103,10 @@ def block_train(tape, ctx, bp, rows, drows, geom, sink, pfx, tag, ada=None, dada
         qv, kk, vv = qkv[:, :D], qkv[:, D:2 * D], qkv[:, 2 * D:]
         q_pre, k_pre = qkv_pre[:, :D], qkv_pre[:, D:2 * D]
     att = sv("att", (M, D))
-    ops.attention(qv, kk, vv, att, geom.seqs, bp.heads, hd, geom.Lq, geom.Lkv, geom.qmap, geom.kvmap, scale)
+    # the forward hands its per-row log-sum-exp to the backward where its kernel produces it (tcgen05 path): the dq kernel then
+    # skips its row-maximum pass and both cross-warp exchanges
+    att_stats = sv("att_stats", (geom.seqs * bp.heads * geom.Lq * 2,), torch.float32) if cd == torch.bfloat16 else None
+    have_lse = ops.attention(qv, kk, vv, att, geom.seqs, bp.heads, hd, geom.Lq, geom.Lkv, geom.qmap, geom.kvmap, scale, lse=att_stats) is True
     y1 = y2 = None
     if gated:
         y1 = sv("y1", (M, D))
@@ -138,7 +141,8 @@ def block_train(tape, ctx, bp, rows, drows, geom, sink, pfx, tag, ada=None, dada
         dqp = ctx.buf("bw_dqp", (M, D)) if cross else dproj[:, :D]
         dkp, dvv = (dproj[:, :D], dproj[:, D:]) if cross else (dproj[:, D:2 * D], dproj[:, 2 * D:])
         dq, dk, _ = B.attention_backward(qv, kk, vv, att, datt, geom.seqs, bp.heads, geom.Lq, geom.Lkv, geom.qmap, geom.kvmap,
-                                         scale, dq=ctx.buf("bw_dq", (M, D)), dk=ctx.buf("bw_dk", (Mk, D)), dv=dvv)
+                                         scale, dq=ctx.buf("bw_dq", (M, D)), dk=ctx.buf("bw_dk", (Mk, D)), dv=dvv,
+                                         stats=att_stats, have_lse=have_lse)
         for pre_, d_, w_, out_, nm in ((q_pre, dq, bp.qn_w, dqp, "attn1.norm_q."), (k_pre, dk, bp.kn_w, dkp, "attn1.norm_k.")):
             _, dw_, db_ = B.headnorm64_backward(pre_, d_, w_, bp.heads, out=out_)
             if g(nm + "weight") is not None:

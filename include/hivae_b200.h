@@ -320,6 +320,20 @@ int hv_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, con
                      void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, int dtype,
                      int64_t seqs, int heads, int hd, int Lq, int Lkv, const HvSeqMap* qmap, const HvSeqMap* kvmap,
                      float scale, float* stats, void* stream);
+/* Forward that hands its per-row log-sum-exp to the backward (the training forward of the blocks, model/modules.py:699-707,
+ * 1043-1051 under autograd): hv_attention + `stats` = the workspace hv_attention_bwd takes.  Returns 1 when element 0 of every
+ * (sequence, head, query row) pair of `stats` was written (tcgen05 kernel attn_tc2.cu), 0 when the kernel that ran does not
+ * produce it (the output is complete either way), < 0 on error. */
+int hv_attention_lse(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                     void* out, int64_t ldo, int dtype, int64_t seqs, int heads, int hd, int Lq, int Lkv,
+                     const HvSeqMap* qmap, const HvSeqMap* kvmap, float scale, const float* mask, float* stats, void* stream);
+/* hv_attention_bwd after hv_attention_lse returned 1 (have_lse = 1): the tcgen05 dq kernel skips its row-maximum pass and both
+ * cross-warp exchanges; have_lse = 0 is hv_attention_bwd. */
+int hv_attention_bwd_lse(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                     const void* out, int64_t ldo, const void* dout, int64_t lddo,
+                     void* dq, int64_t lddq, void* dk, int64_t lddk, void* dv, int64_t lddv, int dtype,
+                     int64_t seqs, int heads, int hd, int Lq, int Lkv, const HvSeqMap* qmap, const HvSeqMap* kvmap,
+                     float scale, float* stats, int have_lse, void* stream);
 
 
 /* ------------------------------------------------------------------ train-step tail (train_amd.py:489-496)

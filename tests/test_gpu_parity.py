@@ -991,3 +991,39 @@ def test_attention_tc2_bound_and_exact_paths(dev, B, H, Lq, Lkv, qscale):
     out = torch.empty(B * Lq, D, device=dev, dtype=torch.bfloat16)
     ops.attention(q.to(dev), k.to(dev), v.to(dev), out, B, H, 64, Lq, Lkv, ops.seq_map(1, Lq, 0, 1), ops.seq_map(1, Lkv, 0, 1), 0.125)
     assert rel(out, ref) <= 1e-2
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,H,Lq,Lkv", [(3, 2, 274, 274), (2, 4, 100, 49), (2, 8, 264, 264), (2, 2, 256, 256), (1, 2, 20, 274)])
+@pytest.mark.parametrize("qscale", [0.8, 12.0])
+def test_attention_forward_lse_handover_to_backward(dev, B, H, Lq, Lkv, qscale):
+    """hv_attention_lse + hv_attention_bwd_lse: the forward leaves the per-row log-sum-exp in the backward's workspace and the
+    tcgen05 dq kernel skips its own maximum / sum passes.  The handed-over values equal the reference log-sum-exp, and dq / dk /
+    dv still match torch autograd (fp64 on the same rounded inputs); qscale 12 takes the forward's exact-maximum path."""
+    from hivae_b200 import backward as Bk, ops
+    g = _gen(73)
+    D = H * 64
+    q = (torch.randn(B * Lq, D, generator=g) * qscale).bfloat16()
+    k = (torch.randn(B * Lkv, D, generator=g) * 0.8).bfloat16()
+    v = torch.randn(B * Lkv, D, generator=g).bfloat16()
+    do = torch.randn(B * Lq, D, generator=g).bfloat16()
+    with torch.enable_grad():
+        qr, kr, vr = (t.double().requires_grad_() for t in (q, k, v))
+        hq = qr.view(B, Lq, H, 64).transpose(1, 2)
+        hk, hv_ = kr.view(B, Lkv, H, 64).transpose(1, 2), vr.view(B, Lkv, H, 64).transpose(1, 2)
+        s = hq @ hk.transpose(-1, -2) * 0.125
+        o = (torch.softmax(s, -1) @ hv_).transpose(1, 2).reshape(B * Lq, D)
+        (o * do.double()).sum().backward()
+    qm, km = ops.seq_map(1, Lq, 0, 1), ops.seq_map(1, Lkv, 0, 1)
+    qd, kd, vd = q.to(dev), k.to(dev), v.to(dev)
+    out = torch.empty(B * Lq, D, device=dev, dtype=torch.bfloat16)
+    stats = torch.full((B * H * Lq * 2,), float("nan"), device=dev)
+    wrote = ops.attention(qd, kd, vd, out, B, H, 64, Lq, Lkv, qm, km, 0.125, lse=stats)
+    assert rel(out, o.detach().float()) <= 1e-2
+    if Lkv >= 48:   # the tcgen05 forward handles these shapes and must hand the values over
+        assert wrote is True
+        lse2 = (torch.logsumexp(s.detach(), -1) * 1.4426950408889634).float()          # (B, H, Lq), log2 domain
+        got = stats.view(B, H, Lq, 2)[..., 0].cpu()
+        assert float((got - lse2).abs().max()) <= 2e-3 * max(1.0, float(lse2.abs().max()))
+    dq, dk, dv = Bk.attention_backward(qd, kd, vd, out, do.to(dev), B, H, Lq, Lkv, qm, km, 0.125, stats=stats, have_lse=wrote is True)
+    assert rel(dq, qr.grad.float()) <= TOL_BF16 and rel(dk, kr.grad.float()) <= TOL_BF16 and rel(dv, vr.grad.float()) <= TOL_BF16
