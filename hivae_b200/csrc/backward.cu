@@ -394,11 +394,11 @@ __global__ void __launch_bounds__(256) headnorm_bwd_kernel(const T* __restrict__
 
 // bf16 with 16-byte alignment: eight lanes per row (one 16-byte load of x and of dy per lane), four rows per warp, so the
 // four row reductions cost three shuffles each for four rows at once
-__global__ void __launch_bounds__(256) headnorm_bwd_bf16x8_kernel(const __nv_bfloat16* __restrict__ x, long long ldx,
+__global__ void __launch_bounds__(512, 2) headnorm_bwd_bf16x8_kernel(const __nv_bfloat16* __restrict__ x, long long ldx,
                                                                   const __nv_bfloat16* __restrict__ dy, long long lddy,
                                                                   const float* __restrict__ w, float eps, long long tokens, int heads,
                                                                   __nv_bfloat16* __restrict__ dx, long long lddx, float* __restrict__ partial) {
-    __shared__ float sh[8][128];
+    __shared__ float sh[16][128];   // 16 warps: 32 warps per SM at two CTAs (16 at 256 threads left the loads latency-bound)
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, sub = lane & 7, rg = lane >> 3;
     float wv[8], dwa[8] = {}, dba[8] = {};
 #pragma unroll
@@ -408,45 +408,60 @@ __global__ void __launch_bounds__(256) headnorm_bwd_bf16x8_kernel(const __nv_bfl
         v += __shfl_xor_sync(0xffffffffu, v, 1); v += __shfl_xor_sync(0xffffffffu, v, 2); v += __shfl_xor_sync(0xffffffffu, v, 4);
         return v;
     };
-    for (long long r0 = (blockIdx.x * 8ll + warp) * 4; r0 < rows; r0 += (long long)gridDim.x * 32) {
+    // two row groups per trip, the loads of both issued before any arithmetic: one 16-byte load of x and of dy per thread
+    // and twelve dependent shuffles per group left too few bytes in flight (49 % of the HBM copy rate)
+    struct Grp { bool valid; long long t; int c; uint4 a, b; };
+    auto fetch = [&](long long r0) {
+        Grp g;
         const long long r = r0 + rg;
-        const bool valid = r < rows;
-        const long long t = valid ? r / heads : 0;
-        const int c = valid ? (int)(r - t * heads) * 64 + 8 * sub : 0;
-        float xv[8] = {}, dv[8] = {};
-        if (valid) {
-            const uint4 a = *reinterpret_cast<const uint4*>(x + t * ldx + c), b = *reinterpret_cast<const uint4*>(dy + t * lddy + c);
-            const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, bw[4] = {b.x, b.y, b.z, b.w};
+        g.valid = r < rows;
+        g.t = g.valid ? r / heads : 0;
+        g.c = g.valid ? (int)(r - g.t * heads) * 64 + 8 * sub : 0;
+        g.a = g.b = make_uint4(0u, 0u, 0u, 0u);
+        if (g.valid) { g.a = *reinterpret_cast<const uint4*>(x + g.t * ldx + g.c); g.b = *reinterpret_cast<const uint4*>(dy + g.t * lddy + g.c); }
+        return g;
+    };
+    auto process = [&](const Grp& gp) {
+        float xv[8], dv[8];
+        const uint32_t aw[4] = {gp.a.x, gp.a.y, gp.a.z, gp.a.w}, bw[4] = {gp.b.x, gp.b.y, gp.b.z, gp.b.w};
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float2 fa = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&aw[j]));
-                const float2 fb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&bw[j]));
-                xv[2 * j] = fa.x; xv[2 * j + 1] = fa.y; dv[2 * j] = fb.x; dv[2 * j + 1] = fb.y;
-            }
+        for (int j = 0; j < 4; ++j) {
+            const float2 fa = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&aw[j]));
+            const float2 fb = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&bw[j]));
+            xv[2 * j] = fa.x; xv[2 * j + 1] = fa.y; dv[2 * j] = fb.x; dv[2 * j + 1] = fb.y;
         }
-        float s = 0.f;
+        // the four row sums in ONE round of shuffles (three dependent steps instead of twelve): sum x, sum x^2, sum g, sum g x
+        // (g = dy w); var = E[x^2] - mean^2 is accurate enough for a bf16 result (the fp32 kernel keeps the two-pass form)
+        float g[8], s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s += xv[j];
-        const float mean = red8(s) * (1.f / 64.f);
-        float q = 0.f;
+        for (int j = 0; j < 8; ++j) { g[j] = dv[j] * wv[j]; s0 += xv[j]; s1 = fmaf(xv[j], xv[j], s1); s2 += g[j]; s3 = fmaf(g[j], xv[j], s3); }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { xv[j] -= mean; q += xv[j] * xv[j]; }
-        const float rstd = rsqrtf(red8(q) * (1.f / 64.f) + eps);
-        float g[8], s1 = 0.f, s2 = 0.f;
+        for (int o = 1; o < 8; o <<= 1) {
+            s0 += __shfl_xor_sync(0xffffffffu, s0, o); s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+            s2 += __shfl_xor_sync(0xffffffffu, s2, o); s3 += __shfl_xor_sync(0xffffffffu, s3, o);
+        }
+        const float mean = s0 * (1.f / 64.f);
+        const float rstd = rsqrtf(fmaxf(s1 * (1.f / 64.f) - mean * mean, 0.f) + eps);
+        const float c1 = s2 * (1.f / 64.f), c2 = rstd * (s3 - mean * s2) * (1.f / 64.f);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { xv[j] *= rstd; g[j] = dv[j] * wv[j]; s1 += g[j]; s2 += g[j] * xv[j]; }
-        const float c1 = red8(s1) * (1.f / 64.f), c2 = red8(s2) * (1.f / 64.f);
-        if (valid) {
+        for (int j = 0; j < 8; ++j) xv[j] = (xv[j] - mean) * rstd;
+        if (gp.valid) {
             uint32_t o[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const __nv_bfloat162 v = __floats2bfloat162_rn(rstd * (g[2 * j] - c1 - xv[2 * j] * c2), rstd * (g[2 * j + 1] - c1 - xv[2 * j + 1] * c2));
                 o[j] = *reinterpret_cast<const uint32_t*>(&v);
             }
-            *reinterpret_cast<uint4*>(dx + t * lddx + c) = make_uint4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<uint4*>(dx + gp.t * lddx + gp.c) = make_uint4(o[0], o[1], o[2], o[3]);
 #pragma unroll
             for (int j = 0; j < 8; ++j) { dwa[j] += dv[j] * xv[j]; dba[j] += dv[j]; }
         }
+    };
+    const long long stride = (long long)gridDim.x * 64;
+    for (long long r0 = (blockIdx.x * 16ll + warp) * 4; r0 < rows; r0 += 2 * stride) {   // r0 is warp-uniform
+        const Grp g0 = fetch(r0), g1 = fetch(r0 + stride);   // rows past the end: valid = false, zeros
+        process(g0);
+        process(g1);
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -461,7 +476,7 @@ __global__ void __launch_bounds__(256) headnorm_bwd_bf16x8_kernel(const __nv_bfl
     if (threadIdx.x < 128) {
         float t = 0.f;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) t += sh[i][threadIdx.x];
+        for (int i = 0; i < 16; ++i) t += sh[i][threadIdx.x];
         partial[(long long)blockIdx.x * 128 + threadIdx.x] = t;
     }
 }
@@ -479,10 +494,10 @@ extern "C" int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int
     const long long rows = tokens * heads;
     auto al16 = [](const void* p, int64_t ld) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0 && ld % 8 == 0; };
     const bool x8 = dtype == HV_BF16 && al16(x, ldx) && al16(dy, lddy) && al16(dx, lddx);
-    const long long per_cta = x8 ? 32 : 8;
+    const long long per_cta = x8 ? 64 : 8;
     if (ctas > (rows + per_cta - 1) / per_cta) ctas = (int)((rows + per_cta - 1) / per_cta);
     cudaStream_t st = hv_stream(stream);
-    if (x8) headnorm_bwd_bf16x8_kernel<<<ctas, 256, 0, st>>>((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy, w, eps, tokens, heads, (__nv_bfloat16*)dx, lddx, workspace);
+    if (x8) headnorm_bwd_bf16x8_kernel<<<ctas, 512, 0, st>>>((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy, w, eps, tokens, heads, (__nv_bfloat16*)dx, lddx, workspace);
     else if (dtype == HV_F32) headnorm_bwd_kernel<float><<<ctas, 256, 0, st>>>((const float*)x, ldx, (const float*)dy, lddy, w, eps, tokens, heads, (float*)dx, lddx, workspace);
     else headnorm_bwd_kernel<__nv_bfloat16><<<ctas, 256, 0, st>>>((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy, w, eps, tokens, heads, (__nv_bfloat16*)dx, lddx, workspace);
     HV_LAUNCH_CHECK();
