@@ -55,12 +55,14 @@ SIGNATURES = {
     "hv_attn_timeline_read": (_i, [_vp]),
     "hv_attn_bwd_prof_read": (_i, [_vp]),
     "hv_headnorm64_bwd": (_i, [_vp, _i64, _vp, _i64, _vp, _f, _i64, _i, _vp, _i64, _i, _vp, _vp, _vp, _vp]),
+    "hv_headnorm64_bwd_acc": (_i, [_vp, _i64, _vp, _i64, _vp, _f, _i64, _i, _vp, _i64, _i, _vp, _vp, _vp, _i, _vp]),
     "hv_attention_bwd": (_i, [_vp, _i64] * 8 + [_i, _i64, _i, _i, _i, _i, _vp, _vp, _f, _vp, _vp]),
     "hv_attention_bwd_lse": (_i, [_vp, _i64] * 8 + [_i, _i64, _i, _i, _i, _i, _vp, _vp, _f, _vp, _i, _vp]),
     "hv_transpose2d": (_i, [_vp, _vp, _i64, _i64, _i64, _i64, _i, _vp]),
     "hv_transpose2d_colsum": (_i, [_vp, _vp, _i64, _i64, _i64, _i64, _i, _vp, _vp, _vp]),
     "hv_colsum_slices": (_i, []),
     "hv_colsum": (_i, [_vp, _i64, _i, _i64, _i, _vp, _vp, _vp]),
+    "hv_colsum_acc": (_i, [_vp, _i64, _i, _i64, _i, _vp, _vp, _i, _vp, _i, _vp, _i, _vp]),
     "hv_gelu_tanh_bwd": (_i, [_vp, _vp, _vp, _i64, _i, _i, _vp]),
     "hv_layernorm_bwd_ctas": (_i, []),
     "hv_layernorm_bwd": (_i, [_vp, _vp, _i, _vp, _f, _i64, _i, _vp, _i, _vp, _vp, _vp, _vp]),

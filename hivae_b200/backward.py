@@ -72,6 +72,25 @@ def colsum(x):
     return out
 
 
+def colsum_into(x, dests, accumulate=True):
+    """column sums of x (M, N) written (or added, accumulate=True) straight into up to three contiguous fp32 destinations that
+    together cover the N columns in order: the bias gradient(s) of a (packed) Linear go into their gradient-arena slots
+    without a temporary and an axpy per destination"""
+    _lib.require_device()
+    assert x.dim() == 2 and x.is_cuda and x.stride(1) == 1 and 1 <= len(dests) <= 3
+    M, N = x.shape
+    assert sum(t.numel() for t in dests) == N
+    for t in dests:
+        assert t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()
+    lib = _lib.load()
+    ws = torch.empty(lib.hv_colsum_slices() * N, dtype=torch.float32, device=x.device)
+    d = list(dests) + [None] * (3 - len(dests))
+    n0 = dests[0].numel()
+    n1 = dests[1].numel() if len(dests) > 1 else 0
+    _lib.check(lib.hv_colsum_acc(_p(x), M, N, x.stride(0), _dt(x), _p(ws), _p(d[0]), n0, _p(d[1]) if d[1] is not None else None, n1,
+                                 _p(d[2]) if d[2] is not None else None, 1 if accumulate else 0, _stream()))
+
+
 def linear_backward(dy, x, w, need_dx=True, dx_dtype=torch.bfloat16, w_t=None):
     """Gradients of y = x @ w.T + b for bf16 operands (fp32 accumulation on the tensor cores):
     dy (M, N), x (M, K), w (N, K)  ->  dx (M, K) in `dx_dtype`, dw (N, K) fp32, db (N,) fp32.
@@ -156,7 +175,7 @@ def attention_backward(q, k, v, out, dout, seqs, heads, Lq, Lkv, qmap, kvmap, sc
 
 
 @_timed("headnorm_bwd")
-def headnorm64_backward(x, dy, weight, heads, eps=1e-6, out=None):
+def headnorm64_backward(x, dy, weight, heads, eps=1e-6, out=None, dw_acc=None, db_acc=None):
     """backward of the per-head LayerNorm(64) of q / k (QK-norm): x (pre-norm), dy are (tokens, heads*64) views (bf16 or
     fp32, unit column stride) -> (dx dense, dw (64,), db (64,))"""
     _lib.require_device()
@@ -166,6 +185,14 @@ def headnorm64_backward(x, dy, weight, heads, eps=1e-6, out=None):
     dx = torch.empty(x.shape, dtype=x.dtype, device=x.device) if out is None else out   # `out`: e.g. the q columns of d(qkv)
     assert dx.shape == x.shape and dx.dtype == x.dtype and dx.stride(1) == 1
     ws = torch.empty((lib.hv_layernorm_bwd_ctas() + 1) * 128, dtype=torch.float32, device=x.device)
+    if dw_acc is not None or db_acc is not None:
+        # dw / db are ADDED to the given fp32 (64,) tensors (gradient-arena slots); a missing one is not computed
+        for t in (dw_acc, db_acc):
+            assert t is None or (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() and t.numel() == 64)
+        _lib.check(lib.hv_headnorm64_bwd_acc(_p(x), x.stride(0), _p(dy), dy.stride(0), _p(weight), float(eps), x.shape[0], heads,
+                                             _p(dx), dx.stride(0), _dt(x), _p(ws), _p(dw_acc) if dw_acc is not None else None,
+                                             _p(db_acc) if db_acc is not None else None, 1, _stream()))
+        return dx, dw_acc, db_acc
     dw, db = (torch.empty(64, dtype=torch.float32, device=x.device) for _ in range(2))
     _lib.check(lib.hv_headnorm64_bwd(_p(x), x.stride(0), _p(dy), dy.stride(0), _p(weight), float(eps), x.shape[0], heads,
                                      _p(dx), dx.stride(0), _dt(x), _p(ws), _p(dw), _p(db), _stream()))
@@ -332,11 +359,14 @@ def linear_grads(ctx, dy, x, w, dw=None, db=None, need_dx=True, dx_accum=None, t
         # dW = dY^T X straight from dY and X as they lie in memory (MN-major tcgen05 operands): no transposed copies, any
         # token count (TMA zero-fills the tail of the contraction)
         if db is not None:
-            cs = colsum(dy)
-            dbs, o = (db if isinstance(db, (list, tuple)) else [db]), 0
-            for t in dbs:
-                ops.axpy(1.0, cs[o:o + t.numel()], t.view(-1))
-                o += t.numel()
+            dbs = list(db) if isinstance(db, (list, tuple)) else [db]
+            if len(dbs) <= 3 and all(t.is_contiguous() and t.dtype == torch.float32 for t in dbs):
+                colsum_into(dy, [t.view(-1) for t in dbs])   # += straight into the gradient slots
+            else:
+                cs, o = colsum(dy), 0
+                for t in dbs:
+                    ops.axpy(1.0, cs[o:o + t.numel()], t.view(-1))
+                    o += t.numel()
         o = 0
         for t in dws or ():
             n = t.shape[0]

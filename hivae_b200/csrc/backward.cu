@@ -200,6 +200,18 @@ __global__ void colsum_final_kernel(const float* __restrict__ partial, int S, in
     out[n] = s;
 }
 
+// colsum_final_kernel with up to three destination ranges (columns [0, n0) -> o0, [n0, n0 + n1) -> o1, the rest -> o2) and an
+// optional += : bias gradients go straight into their slots of the gradient arena (q / k / v biases are separate tensors)
+__global__ void colsum_final_acc_kernel(const float* __restrict__ partial, int S, int N, float* __restrict__ o0, int n0,
+                                        float* __restrict__ o1, int n1, float* __restrict__ o2, int accumulate) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    float s = 0.f;
+    for (int i = 0; i < S; ++i) s += partial[(long long)i * N + n];
+    float* dst = n < n0 ? o0 + n : (n < n0 + n1 ? o1 + (n - n0) : o2 + (n - n0 - n1));
+    *dst = accumulate ? *dst + s : s;
+}
+
 // the same reduction for many slices (S in the hundreds): 32 columns x 8 row groups per CTA, fixed summation order
 __global__ void __launch_bounds__(256) colsum_final_wide_kernel(const float* __restrict__ partial, int S, int N, float* __restrict__ out) {
     __shared__ float sh[8][33];
@@ -219,7 +231,7 @@ __global__ void __launch_bounds__(256) colsum_final_wide_kernel(const float* __r
 
 // same wide reduction, the first `split` sums going to out_a and the rest to out_b (dw / db of a norm; either may be NULL)
 __global__ void __launch_bounds__(256) colsum_final2_kernel(const float* __restrict__ partial, int S, int N, int split,
-                                                            float* __restrict__ out_a, float* __restrict__ out_b) {
+                                                            float* __restrict__ out_a, float* __restrict__ out_b, int accumulate = 0) {
     __shared__ float sh[8][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5, n = blockIdx.x * 32 + tx;
     float a = 0.f;
@@ -231,8 +243,8 @@ __global__ void __launch_bounds__(256) colsum_final2_kernel(const float* __restr
         float t = 0.f;
 #pragma unroll
         for (int i = 0; i < 8; ++i) t += sh[i][tx];
-        if (n < split) { if (out_a) out_a[n] = t; }
-        else if (out_b) out_b[n - split] = t;
+        if (n < split) { if (out_a) out_a[n] = accumulate ? out_a[n] + t : t; }
+        else if (out_b) out_b[n - split] = accumulate ? out_b[n - split] + t : t;
     }
 }
 
@@ -486,8 +498,8 @@ __global__ void __launch_bounds__(512, 2) headnorm_bwd_bf16x8_kernel(const __nv_
 // backward of the per-head LayerNorm(64) of q / k (QK-norm): x, dy, dx are (tokens, heads*64) views with their own leading
 // dimensions and one dtype; dw, db (64 each, fp32) are summed over tokens AND heads (the affine is shared by all heads).
 // workspace = (hv_layernorm_bwd_ctas() + 1) * 128 floats.
-extern "C" int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int64_t lddy, const float* w, float eps, int64_t tokens,
-                                 int heads, void* dx, int64_t lddx, int dtype, float* workspace, float* dw, float* db, void* stream) {
+static int headnorm64_bwd_impl(const void* x, int64_t ldx, const void* dy, int64_t lddy, const float* w, float eps, int64_t tokens,
+                               int heads, void* dx, int64_t lddx, int dtype, float* workspace, float* dw, float* db, int accumulate, void* stream) {
     HV_REQUIRE(tokens >= 0 && heads > 0 && x && dy && dx && workspace && (dtype == HV_F32 || dtype == HV_BF16), "hv_headnorm64_bwd: bad arguments");
     if (tokens == 0) return HV_OK;
     int ctas = hv_layernorm_bwd_ctas();
@@ -502,10 +514,21 @@ extern "C" int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int
     else headnorm_bwd_kernel<__nv_bfloat16><<<ctas, 256, 0, st>>>((const __nv_bfloat16*)x, ldx, (const __nv_bfloat16*)dy, lddy, w, eps, tokens, heads, (__nv_bfloat16*)dx, lddx, workspace);
     HV_LAUNCH_CHECK();
     if (dw || db) {
-        colsum_final2_kernel<<<4, 256, 0, st>>>(workspace, ctas, 128, 64, dw, db);
+        colsum_final2_kernel<<<4, 256, 0, st>>>(workspace, ctas, 128, 64, dw, db, accumulate);
         HV_LAUNCH_CHECK();
     }
     return HV_OK;
+}
+
+extern "C" int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int64_t lddy, const float* w, float eps, int64_t tokens,
+                                 int heads, void* dx, int64_t lddx, int dtype, float* workspace, float* dw, float* db, void* stream) {
+    return headnorm64_bwd_impl(x, ldx, dy, lddy, w, eps, tokens, heads, dx, lddx, dtype, workspace, dw, db, 0, stream);
+}
+// hv_headnorm64_bwd with dw / db ADDED to their destinations (accumulate != 0): the gradient arena slots of norm_q / norm_k
+extern "C" int hv_headnorm64_bwd_acc(const void* x, int64_t ldx, const void* dy, int64_t lddy, const float* w, float eps, int64_t tokens,
+                                     int heads, void* dx, int64_t lddx, int dtype, float* workspace, float* dw, float* db, int accumulate,
+                                     void* stream) {
+    return headnorm64_bwd_impl(x, ldx, dy, lddy, w, eps, tokens, heads, dx, lddx, dtype, workspace, dw, db, accumulate, stream);
 }
 
 extern "C" int hv_transpose2d(const void* in, void* out, int64_t rows, int64_t cols, int64_t ld_in, int64_t ld_out, int dtype, void* stream) {
@@ -544,8 +567,10 @@ extern "C" int hv_transpose2d_colsum(const void* in, void* out, int64_t rows, in
 extern "C" int hv_colsum_slices() { return hv_num_sms() * 2; }
 
 // out[n] = sum_m x[m][n]  (bias gradient of nn.Linear); workspace: hv_colsum_slices() * N floats
-extern "C" int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype, float* workspace, float* out, void* stream) {
+static int colsum_impl(const void* x, int64_t M, int N, int64_t ld, int dtype, float* workspace, float* out, int n0, float* out1, int n1,
+                       float* out2, int accumulate, void* stream) {
     HV_REQUIRE(M >= 0 && N > 0 && ld >= N && workspace && out && (dtype == HV_F32 || dtype == HV_BF16), "hv_colsum: bad arguments");
+    HV_REQUIRE(n0 >= 0 && n1 >= 0 && n0 + n1 <= N && (n0 >= N || out1) && (n0 + n1 >= N || out2), "hv_colsum_acc: destination ranges do not cover the columns");
     int S = hv_colsum_slices();
     const bool x2 = dtype == HV_BF16 && (N % 2 == 0) && (ld % 2 == 0) && (reinterpret_cast<uintptr_t>(x) & 3) == 0;
     const bool x8 = dtype == HV_BF16 && (N % 8 == 0) && (ld % 8 == 0) && (reinterpret_cast<uintptr_t>(x) & 15) == 0 && M >= 2048;
@@ -561,9 +586,21 @@ extern "C" int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype,
     else if (x2) colsum_partial_bf16x2_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, M, N, ld, workspace);
     else colsum_partial_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)x, M, N, ld, workspace);
     HV_LAUNCH_CHECK();
-    colsum_final_kernel<<<(N + 255) / 256, 256, 0, st>>>(workspace, S, N, out);
+    if (n0 >= N && !accumulate) colsum_final_kernel<<<(N + 255) / 256, 256, 0, st>>>(workspace, S, N, out);
+    else colsum_final_acc_kernel<<<(N + 255) / 256, 256, 0, st>>>(workspace, S, N, out, n0, out1, n1, out2, accumulate);
     HV_LAUNCH_CHECK();
     return HV_OK;
+}
+
+extern "C" int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype, float* workspace, float* out, void* stream) {
+    return colsum_impl(x, M, N, ld, dtype, workspace, out, N, nullptr, 0, nullptr, 0, stream);
+}
+// hv_colsum into up to three destinations (columns [0, n0) -> out0, [n0, n0 + n1) -> out1, the rest -> out2; n0 = N for one),
+// added to what is there when accumulate != 0: bias gradients straight into the gradient arena (train_amd.py:489 accumulates
+// into .grad the same way)
+extern "C" int hv_colsum_acc(const void* x, int64_t M, int N, int64_t ld, int dtype, float* workspace, float* out0, int n0, float* out1,
+                             int n1, float* out2, int accumulate, void* stream) {
+    return colsum_impl(x, M, N, ld, dtype, workspace, out0, n0, out1, n1, out2, accumulate, stream);
 }
 
 // dx = dy * gelu_tanh'(pre)   (FeedForward's GELU(approximate="tanh"), modules.py:712-719 through diffusers)

@@ -144,10 +144,15 @@ def block_train(tape, ctx, bp, rows, drows, geom, sink, pfx, tag, ada=None, dada
                                          scale, dq=ctx.buf("bw_dq", (M, D)), dk=ctx.buf("bw_dk", (Mk, D)), dv=dvv,
                                          stats=att_stats, have_lse=have_lse)
         for pre_, d_, w_, out_, nm in ((q_pre, dq, bp.qn_w, dqp, "attn1.norm_q."), (k_pre, dk, bp.kn_w, dkp, "attn1.norm_k.")):
-            _, dw_, db_ = B.headnorm64_backward(pre_, d_, w_, bp.heads, out=out_)
-            if g(nm + "weight") is not None:
-                ops.axpy(1.0, dw_, g(nm + "weight"))
-                ops.axpy(1.0, db_, g(nm + "bias"))
+            gw, gb = g(nm + "weight"), g(nm + "bias")
+            if gw is not None and gb is not None and gw.is_contiguous() and gb.is_contiguous():
+                B.headnorm64_backward(pre_, d_, w_, bp.heads, out=out_, dw_acc=gw.view(-1), db_acc=gb.view(-1))  # += into the gradient slots
+            else:
+                _, dw_, db_ = B.headnorm64_backward(pre_, d_, w_, bp.heads, out=out_)
+                if gw is not None:
+                    ops.axpy(1.0, dw_, gw)
+                if gb is not None:
+                    ops.axpy(1.0, db_, gb)
         if cross:
             dxn1 = B.linear_grads(ctx, dqp, xn1, bp.wq, g("attn1.to_q.weight"), g("attn1.to_q.bias"), tag="bw_wq")
             B.linear_grads(ctx, dproj, kv, bp.wkv, _lst(g, "attn1.to_k.weight", "attn1.to_v.weight"),

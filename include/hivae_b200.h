@@ -153,6 +153,11 @@ int hv_transpose2d_colsum(const void* in, void* out, int64_t rows, int64_t cols,
 /* bias gradient: out[n] = sum_m x[m][n]; workspace = hv_colsum_slices() * N floats */
 int hv_colsum_slices(void);
 int hv_colsum(const void* x, int64_t M, int N, int64_t ld, int dtype, float* workspace, float* out, void* stream);
+/* hv_colsum into up to three destinations (columns [0, n0) -> out0, [n0, n0 + n1) -> out1, the rest -> out2; n0 = N for a single
+ * one), added to what is there when accumulate != 0: bias gradients straight into their .grad slots (the q / k / v biases of a
+ * packed projection are separate tensors), as loss.backward() accumulates at train_amd.py:489 */
+int hv_colsum_acc(const void* x, int64_t M, int N, int64_t ld, int dtype, float* workspace, float* out0, int n0, float* out1,
+                  int n1, float* out2, int accumulate, void* stream);
 /* dx = dy * d/dx gelu_tanh(pre)  (diffusers GELU(approximate="tanh") inside FeedForward, modules.py:712-719) */
 int hv_gelu_tanh_bwd(const void* pre, const void* dy, void* dx, int64_t n, int dtype_in, int dtype_out, void* stream);
 /* nn.LayerNorm backward over dense fp32 rows (D % 128 == 0, D <= 1024): dx written (or accumulated), dw / db optional.
@@ -166,6 +171,9 @@ int hv_layernorm_bwd(const float* x, const void* dy, int dy_dtype, const float* 
  * heads.  workspace = (hv_layernorm_bwd_ctas() + 1) * 128 floats */
 int hv_headnorm64_bwd(const void* x, int64_t ldx, const void* dy, int64_t lddy, const float* w, float eps, int64_t tokens,
                       int heads, void* dx, int64_t lddx, int dtype, float* workspace, float* dw, float* db, void* stream);
+/* hv_headnorm64_bwd with dw / db added to their destinations when accumulate != 0 */
+int hv_headnorm64_bwd_acc(const void* x, int64_t ldx, const void* dy, int64_t lddy, const float* w, float eps, int64_t tokens,
+                      int heads, void* dx, int64_t lddx, int dtype, float* workspace, float* dw, float* db, int accumulate, void* stream);
 
 /* ---- backward of the adaLN-Zero blocks (AMDTransformerBlock / BasicDiTBlock, model/modules.py:1065-1109, 1160-1188) and of
  * the small layers around them; csrc/train_ops.cu.  Same row addressing as the forward ("frames" above).  Every reduction

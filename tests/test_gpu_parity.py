@@ -882,6 +882,34 @@ def test_headnorm64_backward_vs_autograd(dev, dtype, tol, H):
     assert rel(dw, wr.grad.float()) <= (1e-5 if dtype == torch.float32 else 1e-2) and rel(db, br.grad.float()) <= 1e-5
 
 
+@pytest.mark.gpu
+def test_accumulating_reductions_equal_temporary_plus_add(dev):
+    """hv_colsum_acc / hv_headnorm64_bwd_acc add the reduced sums straight into their destinations (the gradient-arena slots);
+    the result is the very fp32 value `dest + temporary` gives: bit-exact"""
+    from hivae_b200 import backward as Bk
+    g = _gen(82)
+    for M, N, parts in ((2501, 3072, (1024, 1024, 1024)), (517, 520, (520,)), (4096, 1024, (512, 512)), (33, 129, (100, 29))):
+        x = torch.randn(M, N, generator=g).to(torch.bfloat16).to(dev)
+        cs = Bk.colsum(x)
+        base = [torch.randn(n, generator=g).to(dev) for n in parts]
+        want = torch.cat(base) + cs
+        dests = [t.clone() for t in base]
+        Bk.colsum_into(x, dests)
+        assert torch.equal(torch.cat(dests), want), (M, N, parts)
+        Bk.colsum_into(x, dests, accumulate=False)
+        assert torch.equal(torch.cat(dests), cs)
+    H, T_ = 4, 777
+    for dtype in (torch.bfloat16, torch.float32):
+        qkv = (torch.randn(T_, 3 * H * 64, generator=g) * 1.3).to(dtype).to(dev)
+        dy = torch.randn(T_, H * 64, generator=g).to(dtype).to(dev)
+        w = (torch.randn(64, generator=g) * 0.3 + 1.0).to(dev)
+        dx, dw, db = Bk.headnorm64_backward(qkv[:, :H * 64], dy, w, H)
+        bw, bb = torch.randn(64, generator=g).to(dev), torch.randn(64, generator=g).to(dev)
+        aw, ab = bw.clone(), bb.clone()
+        dx2, _, _ = Bk.headnorm64_backward(qkv[:, :H * 64], dy, w, H, dw_acc=aw, db_acc=ab)
+        assert torch.equal(dx, dx2) and torch.equal(aw, bw + dw) and torch.equal(ab, bb + db)
+
+
 def _ref_block(x, P, heads, enc=None):
     """modules.py:721-743 (basic) / 817-840 (cross: K/V from the un-normalised encoder_hidden_state) with the diffusers
     Attention / FeedForward of modules.py:699-719 written out (fp64 autograd reference)"""
