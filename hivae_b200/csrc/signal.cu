@@ -1,5 +1,6 @@
 // Haar DWT / IDWT (model/wavelet.py) and the 3-D Gaussian frequency split
 // (model/frequency_utils.py) — HBM-bound, 128-bit vectorised kernels.
+#include <cstdlib>
 #include <type_traits>
 #include "hv_common.cuh"
 
@@ -659,6 +660,244 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_slab32_kernel(const float
     }
 }
 
+// Tensor-core variant for the shapes of the path (T in {8, 16, 32}, H = W in {16, 32}).  The SIMT kernels above are bound by
+// the FMA pipe: 96 FMAs per element against 12 B of HBM traffic is 55 % of the HBM roofline at best, 19 % measured.  Each of
+// the three circulant passes is a (lines x n) . (n x n) matrix product, so it goes to the tensor cores as m16n8k8 TF32
+// `mma.sync` tiles with the 3xTF32 split (x = hi + lo, both TF32; hi.lo + lo.hi + hi.hi accumulated in fp32: ~1e-6 relative,
+// the golden test's bound is 1e-5).  This is the legacy tensor path on purpose: the operands are 32 x 32 fp32 matrices that
+// change layout between the passes, the op stays HBM / L2 bound, and tcgen05 would need split operands staged in swizzled
+// shared memory three times over.
+//   CTA = (volume, slab of TC = 16 output frames), 8 warps, the slab lives in shared memory between the passes:
+//   T pass: out[tt][col] = sum_k Ct[t0 + tt][k] x[k][col]      A = Ct rows (registers), B = x straight from global / L2
+//   H pass: out[h'][w]   = sum_h Ch[h'][h] s[tt][h][w]         A = Ch (registers), B = slab columns; in place, a warp owns
+//                                                               whole 8-column blocks
+//   W pass: out[h][w']   = sum_w s[tt][h][w] Cw[w'][w]         A = slab rows (float2 loads, k-permuted), B = Cw (registers);
+//                                                               in place, a warp owns whole 16-row blocks
+//   last:   low = slab, high = x - low                          128-bit coalesced loads and stores
+// `slab_idx` (XOR swizzle for N = 32, padded rows for N = 16) keeps every fragment load / store bank-conflict free.
+__device__ __forceinline__ void split_tf32(float v, uint32_t& hi, uint32_t& lo) {
+    // hi = v rounded to TF32 (nearest, ties away: add half an ulp of the 10-bit mantissa, clear the 13 low bits), lo = v - hi
+    // exactly; the tensor core ignores the 13 low mantissa bits of lo (|lo| <= 2^-11 |v|, so that costs 2^-21 |v|, either sign).
+    // `cvt.rna.tf32.f32` would do the same with inf / nan handling, at five instructions instead of two per conversion.
+    hi = (__float_as_uint(v) + 0x1000u) & 0xffffe000u;
+    lo = __float_as_uint(v - __uint_as_float(hi));
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+// d += a . b with both operands split: the two small cross terms first, the big term last
+__device__ __forceinline__ void mma_3xtf32(float (&d)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4],
+                                           uint32_t bh0, uint32_t bh1, uint32_t bl0, uint32_t bl1) {
+    mma_tf32(d, al, bh0, bh1);
+    mma_tf32(d, ah, bl0, bl1);
+    mma_tf32(d, ah, bh0, bh1);
+}
+
+// slab addressing: element (h, w) of a frame.  N = 32: rows of 32 floats with the 8-float column blocks XOR-swizzled by h & 3
+// (no row padding: a 16-frame slab is 66 KB, three CTAs per SM); N = 16: row pitch 24.  Either way the fragment accesses of the
+// three passes ((k = t rows) x (n = g columns) loads, (m = g rows) x float2 stores / loads) hit 32 distinct banks.
+template <int N>
+__device__ __forceinline__ int slab_idx(int h, int w) {
+    return N == 32 ? h * 32 + (w ^ ((h & 3) << 3)) : h * 24 + w;
+}
+
+template <int T, int N>
+__global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* __restrict__ x, const float* __restrict__ ct,
+                                                                  const float* __restrict__ ch, const float* __restrict__ cw,
+                                                                  float* __restrict__ lo, float* __restrict__ hi) {
+    constexpr int TC = T >= 16 ? 16 : 8, SLABS = T / TC, HW = N * N, FP = (N == 32 ? N * 32 : N * 24) + 4;
+    constexpr int KT = T / 8, KN = N / 8, MT = N / 16;
+    extern __shared__ __align__(16) float S[];     // TC frames, frame pitch FP
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const long long v = blockIdx.x / SLABS;
+    const int t0 = (int)(blockIdx.x % SLABS) * TC;
+    const float* xv = x + v * (long long)T * HW;
+    // ---- T pass: A = rows t0 .. t0 + 15 of Ct (rows 8 .. 15 are zero when the slab has 8 frames).  A warp takes 32 columns
+    // at a time as four n-tiles whose n index is permuted (tile nt, index g <-> column 4 g + nt): one 128-bit load per k row
+    // feeds all four tiles, and a lane's outputs are eight consecutive columns (two 128-bit stores per frame).
+    {
+        uint32_t ah[KT][4], al[KT][4];
+#pragma unroll
+        for (int ks = 0; ks < KT; ++ks) {
+            const float* r0 = ct + (t0 + g) * T + 8 * ks + t;
+            const float* r1 = ct + (t0 + (TC == 16 ? g + 8 : g)) * T + 8 * ks + t;
+            split_tf32(__ldg(r0), ah[ks][0], al[ks][0]);
+            split_tf32(__ldg(r0 + 4), ah[ks][2], al[ks][2]);
+            split_tf32(TC == 16 ? __ldg(r1) : 0.f, ah[ks][1], al[ks][1]);
+            split_tf32(TC == 16 ? __ldg(r1 + 4) : 0.f, ah[ks][3], al[ks][3]);
+        }
+        for (int j = warp; j < HW / 32; j += 8) {
+            float4 b[KT][2];
+#pragma unroll
+            for (int ks = 0; ks < KT; ++ks) {
+                const float* src = xv + (long long)(8 * ks + t) * HW + 32 * j + 4 * g;
+                b[ks][0] = __ldg(reinterpret_cast<const float4*>(src));
+                b[ks][1] = __ldg(reinterpret_cast<const float4*>(src + 4 * HW));
+            }
+            float acc[4][4];
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < KT; ++ks) {
+                const float b0[4] = {b[ks][0].x, b[ks][0].y, b[ks][0].z, b[ks][0].w};
+                const float b1[4] = {b[ks][1].x, b[ks][1].y, b[ks][1].z, b[ks][1].w};
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt) {
+                    uint32_t bh0, bl0, bh1, bl1;
+                    split_tf32(b0[nt], bh0, bl0);
+                    split_tf32(b1[nt], bh1, bl1);
+                    mma_3xtf32(acc[nt], ah[ks], al[ks], bh0, bh1, bl0, bl1);
+                }
+            }
+            const int col = 32 * j + 8 * t;
+            float* dst = S + g * FP + slab_idx<N>(col / N, col % N);
+            *reinterpret_cast<float4*>(dst) = make_float4(acc[0][0], acc[1][0], acc[2][0], acc[3][0]);
+            *reinterpret_cast<float4*>(dst + 4) = make_float4(acc[0][1], acc[1][1], acc[2][1], acc[3][1]);
+            if (TC == 16) {
+                *reinterpret_cast<float4*>(dst + 8 * FP) = make_float4(acc[0][2], acc[1][2], acc[2][2], acc[3][2]);
+                *reinterpret_cast<float4*>(dst + 8 * FP + 4) = make_float4(acc[0][3], acc[1][3], acc[2][3], acc[3][3]);
+            }
+        }
+    }
+    __syncthreads();
+    // ---- H pass, in place: a warp owns whole column blocks (frame tt, 8 columns): it reads the block (all rows), multiplies
+    // it by every row tile of Ch (registers) and writes it back, so that no other warp ever touches the block.  The loads of
+    // the next block are issued before the MMAs of this one.
+    {
+        constexpr int ITEMS = TC * KN;
+        uint32_t ah[MT][KN][4], al[MT][KN][4];
+#pragma unroll
+        for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+            for (int ks = 0; ks < KN; ++ks) {
+                const float* r0 = ch + (16 * mt + g) * N + 8 * ks + t;
+                split_tf32(__ldg(r0), ah[mt][ks][0], al[mt][ks][0]);
+                split_tf32(__ldg(r0 + 8 * N), ah[mt][ks][1], al[mt][ks][1]);
+                split_tf32(__ldg(r0 + 4), ah[mt][ks][2], al[mt][ks][2]);
+                split_tf32(__ldg(r0 + 8 * N + 4), ah[mt][ks][3], al[mt][ks][3]);
+            }
+        float b[KN][2], bn[KN][2];
+        auto fetch = [&](float (&d)[KN][2], int it) {
+            const float* fr = S + (it / KN) * FP;
+            const int w = 8 * (it % KN) + g;
+#pragma unroll
+            for (int ks = 0; ks < KN; ++ks) {
+                d[ks][0] = fr[slab_idx<N>(8 * ks + t, w)];
+                d[ks][1] = fr[slab_idx<N>(8 * ks + t + 4, w)];
+            }
+        };
+        fetch(b, warp);
+        for (int it = warp; it < ITEMS; it += 8) {
+            __syncwarp();
+            if (it + 8 < ITEMS) fetch(bn, it + 8);
+            float acc[MT][2][4];                    // per row tile two chains: even / odd k-steps
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+                for (int c = 0; c < 2; ++c) acc[mt][c][0] = acc[mt][c][1] = acc[mt][c][2] = acc[mt][c][3] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < KN; ++ks) {
+                uint32_t bh0, bl0, bh1, bl1;
+                split_tf32(b[ks][0], bh0, bl0);
+                split_tf32(b[ks][1], bh1, bl1);
+#pragma unroll
+                for (int mt = 0; mt < MT; ++mt) mma_3xtf32(acc[mt][ks & 1], ah[mt][ks], al[mt][ks], bh0, bh1, bl0, bl1);
+            }
+            float* fr = S + (it / KN) * FP;
+            const int w = 8 * (it % KN) + 2 * t;
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) {
+                *reinterpret_cast<float2*>(fr + slab_idx<N>(16 * mt + g, w)) =
+                    make_float2(acc[mt][0][0] + acc[mt][1][0], acc[mt][0][1] + acc[mt][1][1]);
+                *reinterpret_cast<float2*>(fr + slab_idx<N>(16 * mt + g + 8, w)) =
+                    make_float2(acc[mt][0][2] + acc[mt][1][2], acc[mt][0][3] + acc[mt][1][3]);
+            }
+#pragma unroll
+            for (int ks = 0; ks < KN; ++ks) { b[ks][0] = bn[ks][0]; b[ks][1] = bn[ks][1]; }
+        }
+    }
+    __syncthreads();
+    // ---- W pass, in place as well: a warp owns 16 rows of a frame: A = those rows, B = Cw^T (all of it, registers).  Within
+    // a k-step the MMA's k index t <-> w = 2t and t + 4 <-> w = 2t + 1, so that a lane's two A values of a row are one
+    // float2 (conflict-free, half the loads).
+    {
+        constexpr int ITEMS = TC * MT;
+        uint32_t bh[KN][KN][2], bl[KN][KN][2];      // [n-tile][k-step]
+#pragma unroll
+        for (int nt = 0; nt < KN; ++nt)
+#pragma unroll
+            for (int ks = 0; ks < KN; ++ks) {
+                const float* r = cw + (8 * nt + g) * N + 8 * ks + 2 * t;
+                split_tf32(__ldg(r), bh[nt][ks][0], bl[nt][ks][0]);
+                split_tf32(__ldg(r + 1), bh[nt][ks][1], bl[nt][ks][1]);
+            }
+        for (int it = warp; it < ITEMS; it += 8) {
+            float* fr = S + (it / MT) * FP;
+            const int r0 = 16 * (it % MT) + g;
+            float2 a[KN][2];
+#pragma unroll
+            for (int ks = 0; ks < KN; ++ks) {
+                a[ks][0] = *reinterpret_cast<const float2*>(fr + slab_idx<N>(r0, 8 * ks + 2 * t));
+                a[ks][1] = *reinterpret_cast<const float2*>(fr + slab_idx<N>(r0 + 8, 8 * ks + 2 * t));
+            }
+            float acc[KN][4];
+#pragma unroll
+            for (int nt = 0; nt < KN; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < KN; ++ks) {
+                uint32_t ah[4], al[4];
+                split_tf32(a[ks][0].x, ah[0], al[0]);
+                split_tf32(a[ks][1].x, ah[1], al[1]);
+                split_tf32(a[ks][0].y, ah[2], al[2]);
+                split_tf32(a[ks][1].y, ah[3], al[3]);
+#pragma unroll
+                for (int nt = 0; nt < KN; ++nt)    // the n-tiles are independent accumulation chains
+                    mma_3xtf32(acc[nt], ah, al, bh[nt][ks][0], bh[nt][ks][1], bl[nt][ks][0], bl[nt][ks][1]);
+            }
+            __syncwarp();
+#pragma unroll
+            for (int nt = 0; nt < KN; ++nt) {
+                const int w = 8 * nt + 2 * t;
+                *reinterpret_cast<float2*>(fr + slab_idx<N>(r0, w)) = make_float2(acc[nt][0], acc[nt][1]);
+                *reinterpret_cast<float2*>(fr + slab_idx<N>(r0 + 8, w)) = make_float2(acc[nt][2], acc[nt][3]);
+            }
+        }
+    }
+    __syncthreads();
+    // ---- low = slab, high = x - low: 128-bit accesses, whole lines, four loads of x in flight per thread
+    {
+        const long long off = v * (long long)T * HW + (long long)t0 * HW;
+        constexpr int Q = TC * HW / 4;              // float4 per slab
+        for (int i = threadIdx.x; i < Q; i += 1024) {
+            float4 xx[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (i + 256 * u < Q) xx[u] = __ldg(reinterpret_cast<const float4*>(x + off) + i + 256 * u);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (i + 256 * u >= Q) break;
+                const int e = 4 * (i + 256 * u), tt = e / HW, rem = e % HW;
+                const float4 l = *reinterpret_cast<const float4*>(S + tt * FP + slab_idx<N>(rem / N, rem % N));
+                reinterpret_cast<float4*>(lo + off)[i + 256 * u] = l;
+                reinterpret_cast<float4*>(hi + off)[i + 256 * u] = make_float4(xx[u].x - l.x, xx[u].y - l.y, xx[u].z - l.z, xx[u].w - l.w);
+            }
+        }
+    }
+}
+
+template <int T, int N>
+static int freq_split3d_mma_launch(const float* x, const float* ct, const float* ch, const float* cw, float* lo, float* hi,
+                                   int64_t vols, cudaStream_t st) {
+    constexpr int TC = T >= 16 ? 16 : 8;
+    constexpr size_t smem = (size_t)TC * ((N == 32 ? N * 32 : N * 24) + 4) * sizeof(float);
+    HV_CUDA(cudaFuncSetAttribute(freq_split3d_mma_kernel<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    freq_split3d_mma_kernel<T, N><<<(unsigned)(vols * (T / TC)), 256, smem, st>>>(x, ct, ch, cw, lo, hi);
+    HV_LAUNCH_CHECK();
+    return HV_OK;
+}
+
 extern "C" int hv_freq_split3d(const float* x, const float* ct, const float* ch, const float* cw,
                                float* lo, float* hi, int64_t vols, int T, int H, int W, void* stream) {
     HV_REQUIRE(vols >= 0 && T > 0 && H > 0 && W > 0, "hv_freq_split3d: bad sizes");
@@ -670,6 +909,17 @@ extern "C" int hv_freq_split3d(const float* x, const float* ct, const float* ch,
     size_t smem = (size_t)(3 * MAXN * MAXN + (size_t)T * H * (W + 1)) * sizeof(float);
     HV_REQUIRE(smem <= 227 * 1024, "hv_freq_split3d: volume %dx%dx%d needs %zu B of shared memory (> 227 KB)", T, H, W, smem);
     cudaStream_t st = hv_stream(stream);
+    // tensor-core path (HV_FREQ_TC=0 keeps the SIMT kernels, =1 forces the tensor kernel, for A/B runs); 128-bit accesses need 16-byte aligned volumes
+    const char* tc_env = getenv("HV_FREQ_TC");
+    const bool aligned16 = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(lo) | reinterpret_cast<uintptr_t>(hi)) & 15) == 0;
+    // a 32^3 launch that cannot fill the SMs with 16-frame slabs stays on the SIMT kernel (8-frame slabs, twice the CTAs):
+    // 1040 against 770 GB/s at 32 volumes, 1457 against 1913 at 128 (`profiles/r02_x_bench_freq.txt`)
+    const bool too_small = T == 32 && H == 32 && vols * 2 < hv_num_sms() && !(tc_env && tc_env[0] == '1');
+    if (H == W && aligned16 && !too_small && !(tc_env && tc_env[0] == '0')) {
+#define HV_FREQ_CASE(TT, NN) if (T == TT && H == NN) return freq_split3d_mma_launch<TT, NN>(x, ct, ch, cw, lo, hi, vols, st);
+        HV_FREQ_CASE(32, 32) HV_FREQ_CASE(16, 32) HV_FREQ_CASE(8, 32) HV_FREQ_CASE(32, 16) HV_FREQ_CASE(16, 16) HV_FREQ_CASE(8, 16)
+#undef HV_FREQ_CASE
+    }
     if (T == 32 && H == 32 && W == 32) {  // circulant taps in registers (row 0 of each matrix)
         freq_split3d_slab32_kernel<<<(unsigned)(vols * 4), 256, 0, st>>>(x, ct, ch, cw, lo, hi);
         HV_LAUNCH_CHECK();

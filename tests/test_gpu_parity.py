@@ -180,6 +180,22 @@ def test_freq_split_properties_full_size(dev):
     assert float(lo0.abs().max()) == 0.0 and torch.equal(hi0, x[:1])
 
 
+@pytest.mark.parametrize("T,N", [(32, 32), (16, 32), (8, 32), (32, 16), (16, 16), (8, 16)])
+def test_freq_split_tensor_core_shapes(dev, T, N, monkeypatch):
+    """every instance of the 3xTF32 tensor-core kernel (T in {8, 16, 32}, H = W in {16, 32}) against the oracle's FFT split
+    (frequency_utils.py:84-108) with anisotropic cut-offs, and against the SIMT kernels on the same input"""
+    import hivae_b200 as hv
+    x = torch.randn(3, 2, T, N, N, generator=_gen(7))
+    lpf = O.gaussian_lpf([T, N, N], 0.4, 0.7)
+    olo, ohi = O.freq_split3d(x, lpf)
+    monkeypatch.setenv("HV_FREQ_TC", "1")       # a launch this small would otherwise stay on the SIMT kernel
+    lo, hi = hv.freq_3d_filter(x.to(dev), lpf)
+    assert rel(lo, olo) <= 1e-5 and rel(hi, ohi) <= 1e-5 and rel(lo + hi, x) <= 1e-6
+    monkeypatch.setenv("HV_FREQ_TC", "0")
+    slo, shi = hv.freq_3d_filter(x.to(dev), lpf)
+    assert rel(lo, slo) <= 3e-6 and rel(hi, shi) <= 3e-6
+
+
 # =============================================================================== GEMM + epilogues
 def _ref_linear(A, W, b):
     y = A.double() @ W.double().t()

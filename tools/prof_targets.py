@@ -1,5 +1,5 @@
 """One or two launches of a chosen kernel at the DiT's shapes, for `ncu -k regex:<kernel> --set full` captures.
-usage: python tools/prof_targets.py attn|ln|small|gemm_out|gemm_ff1|gemm_qkv|dwt|attn_bwd"""
+usage: python tools/prof_targets.py attn|ln|small|gemm_out|gemm_ff1|gemm_qkv|dwt|freq|attn_bwd"""
 import sys, os, math
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -49,6 +49,11 @@ elif what.startswith("gemm"):
             ops.linear(A, W, ops.epi_store(outb, bias, gelu=True))
         else:
             ops.linear(A, W, ops.epi_qknorm(outb, bias, ln[0], ln[1], ln[0], ln[1], D, D))
+elif what == "freq":
+    from hivae_b200.frequency_utils import freq_split_gauss
+    x = torch.randn(128, 4, 32, 32, 32, device=dev)
+    for _ in range(reps):
+        freq_split_gauss(x, 0.6, 0.6)
 elif what == "dwt":
     x = torch.randn(33, 3, 512, 512, device=dev)
     for _ in range(reps):

@@ -10,3 +10,4 @@ timeout -k 5 900 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err
 timeout -k 5 400 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "reference arm exit=$?"; cut -c1-300 gpurun_out/bench_reference.json
 timeout -k 5 300 python tools/bench_gemm.py > gpurun_out/bench_gemm.log 2>&1; echo "bench_gemm exit=$?"
 timeout -k 5 300 python tools/bench_attn_shapes.py > gpurun_out/attn_shapes.txt 2>&1; echo "attn shapes exit=$?"
+timeout -k 5 200 python tools/bench_freq.py > gpurun_out/bench_freq.txt 2>&1; echo "bench_freq exit=$?"; cut -c1-200 gpurun_out/bench_freq.txt | head -6
