@@ -695,6 +695,13 @@ __device__ __forceinline__ void mma_3xtf32(float (&d)[4], const uint32_t (&ah)[4
     mma_tf32(d, ah, bh0, bh1);
 }
 
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
 // slab addressing: element (h, w) of a frame.  N = 32: rows of 32 floats with the 8-float column blocks XOR-swizzled by h & 3
 // (no row padding: a 16-frame slab is 66 KB, three CTAs per SM); N = 16: row pitch 24.  Either way the fragment accesses of the
 // three passes ((k = t rows) x (n = g columns) loads, (m = g rows) x float2 stores / loads) hit 32 distinct banks.
@@ -728,14 +735,28 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* _
             split_tf32(TC == 16 ? __ldg(r1) : 0.f, ah[ks][1], al[ks][1]);
             split_tf32(TC == 16 ? __ldg(r1 + 4) : 0.f, ah[ks][3], al[ks][3]);
         }
+        // x reaches the warp through its own staging buffer (T rows of 32 columns, row pitch 40 floats: conflict-free 128-bit
+        // fragment reads): `cp.async` of the next 32 columns is in flight while these 32 are multiplied
+        float* stg = S + TC * FP + warp * (T * 40);
+        auto stage = [&](int j) {
+#pragma unroll
+            for (int i = 0; i < T / 4; ++i) {
+                const int c = lane + 32 * i, row = c >> 3, ch = c & 7;
+                cp_async16(stg + row * 40 + 4 * ch, xv + (long long)row * HW + 32 * j + 4 * ch);
+            }
+        };
+        stage(warp);
         for (int j = warp; j < HW / 32; j += 8) {
+            cp_async_wait_all();
+            __syncwarp();
             float4 b[KT][2];
 #pragma unroll
             for (int ks = 0; ks < KT; ++ks) {
-                const float* src = xv + (long long)(8 * ks + t) * HW + 32 * j + 4 * g;
-                b[ks][0] = __ldg(reinterpret_cast<const float4*>(src));
-                b[ks][1] = __ldg(reinterpret_cast<const float4*>(src + 4 * HW));
+                b[ks][0] = *reinterpret_cast<const float4*>(stg + (8 * ks + t) * 40 + 4 * g);
+                b[ks][1] = *reinterpret_cast<const float4*>(stg + (8 * ks + t + 4) * 40 + 4 * g);
             }
+            __syncwarp();
+            if (j + 8 < HW / 32) stage(j + 8);
             float acc[4][4];
 #pragma unroll
             for (int nt = 0; nt < 4; ++nt) acc[nt][0] = acc[nt][1] = acc[nt][2] = acc[nt][3] = 0.f;
@@ -760,6 +781,14 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* _
                 *reinterpret_cast<float4*>(dst + 8 * FP + 4) = make_float4(acc[0][3], acc[1][3], acc[2][3], acc[3][3]);
             }
         }
+    }
+    // the staging buffers are free now: each warp fills its own with the next piece of the slab's x (the epilogue's high = x - low)
+    constexpr int XP = (8 * T * 40 < TC * HW ? 8 * T * 40 : TC * HW), PW = XP / 8;   // floats of x staged: in all, per warp
+    {
+        const long long off = v * (long long)T * HW + (long long)t0 * HW;
+        float* stg = S + TC * FP + warp * (T * 40);
+        for (int c = lane; c < PW / 4; c += 32) cp_async16(stg + 4 * c, x + off + warp * PW + 4 * c);
+        asm volatile("cp.async.commit_group;" ::: "memory");
     }
     __syncthreads();
     // ---- H pass, in place: a warp owns whole column blocks (frame tt, 8 columns): it reads the block (all rows), multiplies
@@ -865,24 +894,32 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* _
             }
         }
     }
+    cp_async_wait_all();                            // this thread's share of the staged x has landed
     __syncthreads();
-    // ---- low = slab, high = x - low: 128-bit accesses, whole lines, four loads of x in flight per thread
+    // ---- low = slab, high = x - low: 128-bit accesses, whole lines; the head of x comes from the staging area, the rest from
+    // global memory with four loads in flight per thread
     {
         const long long off = v * (long long)T * HW + (long long)t0 * HW;
-        constexpr int Q = TC * HW / 4;              // float4 per slab
-        for (int i = threadIdx.x; i < Q; i += 1024) {
+        constexpr int Q = TC * HW / 4, Q0 = XP / 4;       // float4 per slab; the first Q0 of them are staged
+        const float* xst = S + TC * FP;
+        auto emit = [&](int i, const float4& xx) {
+            const int e = 4 * i, tt = e / HW, rem = e % HW;
+            const float4 l = *reinterpret_cast<const float4*>(S + tt * FP + slab_idx<N>(rem / N, rem % N));
+            reinterpret_cast<float4*>(lo + off)[i] = l;
+            reinterpret_cast<float4*>(hi + off)[i] = make_float4(xx.x - l.x, xx.y - l.y, xx.z - l.z, xx.w - l.w);
+        };
+        for (int i = Q0 + threadIdx.x; i < Q; i += 1024) {
             float4 xx[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u)
                 if (i + 256 * u < Q) xx[u] = __ldg(reinterpret_cast<const float4*>(x + off) + i + 256 * u);
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (i + 256 * u >= Q) break;
-                const int e = 4 * (i + 256 * u), tt = e / HW, rem = e % HW;
-                const float4 l = *reinterpret_cast<const float4*>(S + tt * FP + slab_idx<N>(rem / N, rem % N));
-                reinterpret_cast<float4*>(lo + off)[i + 256 * u] = l;
-                reinterpret_cast<float4*>(hi + off)[i + 256 * u] = make_float4(xx[u].x - l.x, xx[u].y - l.y, xx[u].z - l.z, xx[u].w - l.w);
-            }
+            for (int u = 0; u < 4; ++u)
+                if (i + 256 * u < Q) emit(i + 256 * u, xx[u]);
+        }
+        for (int i = threadIdx.x; i < Q0; i += 256) {
+            const int w = (4 * i) / PW;                   // the warp that staged this piece, in its own buffer
+            emit(i, *reinterpret_cast<const float4*>(xst + w * (T * 40) + (4 * i - w * PW)));
         }
     }
 }
@@ -891,7 +928,7 @@ template <int T, int N>
 static int freq_split3d_mma_launch(const float* x, const float* ct, const float* ch, const float* cw, float* lo, float* hi,
                                    int64_t vols, cudaStream_t st) {
     constexpr int TC = T >= 16 ? 16 : 8;
-    constexpr size_t smem = (size_t)TC * ((N == 32 ? N * 32 : N * 24) + 4) * sizeof(float);
+    constexpr size_t smem = ((size_t)TC * ((N == 32 ? N * 32 : N * 24) + 4) + 8 * T * 40) * sizeof(float);   // slab + staging
     HV_CUDA(cudaFuncSetAttribute(freq_split3d_mma_kernel<T, N>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     freq_split3d_mma_kernel<T, N><<<(unsigned)(vols * (T / TC)), 256, smem, st>>>(x, ct, ch, cw, lo, hi);
     HV_LAUNCH_CHECK();
