@@ -782,6 +782,18 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* _
             }
         }
     }
+    // the constants of the next pass are requested before the barrier, so that their L2 latency overlaps the wait
+    float chr_[MT][KN][4];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+        for (int ks = 0; ks < KN; ++ks) {
+            const float* r0 = ch + (16 * mt + g) * N + 8 * ks + t;
+            chr_[mt][ks][0] = __ldg(r0);
+            chr_[mt][ks][1] = __ldg(r0 + 8 * N);
+            chr_[mt][ks][2] = __ldg(r0 + 4);
+            chr_[mt][ks][3] = __ldg(r0 + 8 * N + 4);
+        }
     // the staging buffers are free now: each warp fills its own with the next piece of the slab's x (the epilogue's high = x - low)
     constexpr int XP = (8 * T * 40 < TC * HW ? 8 * T * 40 : TC * HW), PW = XP / 8;   // floats of x staged: in all, per warp
     {
@@ -801,11 +813,10 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* _
         for (int mt = 0; mt < MT; ++mt)
 #pragma unroll
             for (int ks = 0; ks < KN; ++ks) {
-                const float* r0 = ch + (16 * mt + g) * N + 8 * ks + t;
-                split_tf32(__ldg(r0), ah[mt][ks][0], al[mt][ks][0]);
-                split_tf32(__ldg(r0 + 8 * N), ah[mt][ks][1], al[mt][ks][1]);
-                split_tf32(__ldg(r0 + 4), ah[mt][ks][2], al[mt][ks][2]);
-                split_tf32(__ldg(r0 + 8 * N + 4), ah[mt][ks][3], al[mt][ks][3]);
+                split_tf32(chr_[mt][ks][0], ah[mt][ks][0], al[mt][ks][0]);
+                split_tf32(chr_[mt][ks][1], ah[mt][ks][1], al[mt][ks][1]);
+                split_tf32(chr_[mt][ks][2], ah[mt][ks][2], al[mt][ks][2]);
+                split_tf32(chr_[mt][ks][3], ah[mt][ks][3], al[mt][ks][3]);
             }
         float b[KN][2], bn[KN][2];
         auto fetch = [&](float (&d)[KN][2], int it) {
@@ -847,6 +858,12 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* _
             for (int ks = 0; ks < KN; ++ks) { b[ks][0] = bn[ks][0]; b[ks][1] = bn[ks][1]; }
         }
     }
+    float2 cwr_[KN][KN];                            // Cw^T fragments, requested before the barrier (8-byte aligned pairs)
+#pragma unroll
+    for (int nt = 0; nt < KN; ++nt)
+#pragma unroll
+        for (int ks = 0; ks < KN; ++ks)
+            cwr_[nt][ks] = __ldg(reinterpret_cast<const float2*>(cw + (8 * nt + g) * N + 8 * ks + 2 * t));
     __syncthreads();
     // ---- W pass, in place as well: a warp owns 16 rows of a frame: A = those rows, B = Cw^T (all of it, registers).  Within
     // a k-step the MMA's k index t <-> w = 2t and t + 4 <-> w = 2t + 1, so that a lane's two A values of a row are one
@@ -858,9 +875,8 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* _
         for (int nt = 0; nt < KN; ++nt)
 #pragma unroll
             for (int ks = 0; ks < KN; ++ks) {
-                const float* r = cw + (8 * nt + g) * N + 8 * ks + 2 * t;
-                split_tf32(__ldg(r), bh[nt][ks][0], bl[nt][ks][0]);
-                split_tf32(__ldg(r + 1), bh[nt][ks][1], bl[nt][ks][1]);
+                split_tf32(cwr_[nt][ks].x, bh[nt][ks][0], bl[nt][ks][0]);
+                split_tf32(cwr_[nt][ks].y, bh[nt][ks][1], bl[nt][ks][1]);
             }
         for (int it = warp; it < ITEMS; it += 8) {
             float* fr = S + (it / MT) * FP;
@@ -894,33 +910,31 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* _
             }
         }
     }
+    // the part of x that is not staged is requested before the barrier too
+    constexpr int Q = TC * HW / 4, Q0 = XP / 4, NG = (Q - Q0 + 255) / 256;   // float4 per slab; staged; per thread from global
+    const long long xoff = v * (long long)T * HW + (long long)t0 * HW;
+    float4 xg[NG > 0 ? NG : 1];
+#pragma unroll
+    for (int u = 0; u < NG; ++u)
+        if (Q0 + threadIdx.x + 256 * u < Q) xg[u] = __ldg(reinterpret_cast<const float4*>(x + xoff) + Q0 + threadIdx.x + 256 * u);
     cp_async_wait_all();                            // this thread's share of the staged x has landed
     __syncthreads();
-    // ---- low = slab, high = x - low: 128-bit accesses, whole lines; the head of x comes from the staging area, the rest from
-    // global memory with four loads in flight per thread
+    // ---- low = slab, high = x - low: 128-bit accesses, whole lines; the head of x comes from the staging area
     {
-        const long long off = v * (long long)T * HW + (long long)t0 * HW;
-        constexpr int Q = TC * HW / 4, Q0 = XP / 4;       // float4 per slab; the first Q0 of them are staged
         const float* xst = S + TC * FP;
         auto emit = [&](int i, const float4& xx) {
             const int e = 4 * i, tt = e / HW, rem = e % HW;
             const float4 l = *reinterpret_cast<const float4*>(S + tt * FP + slab_idx<N>(rem / N, rem % N));
-            reinterpret_cast<float4*>(lo + off)[i] = l;
-            reinterpret_cast<float4*>(hi + off)[i] = make_float4(xx.x - l.x, xx.y - l.y, xx.z - l.z, xx.w - l.w);
+            reinterpret_cast<float4*>(lo + xoff)[i] = l;
+            reinterpret_cast<float4*>(hi + xoff)[i] = make_float4(xx.x - l.x, xx.y - l.y, xx.z - l.z, xx.w - l.w);
         };
-        for (int i = Q0 + threadIdx.x; i < Q; i += 1024) {
-            float4 xx[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (i + 256 * u < Q) xx[u] = __ldg(reinterpret_cast<const float4*>(x + off) + i + 256 * u);
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (i + 256 * u < Q) emit(i + 256 * u, xx[u]);
-        }
         for (int i = threadIdx.x; i < Q0; i += 256) {
             const int w = (4 * i) / PW;                   // the warp that staged this piece, in its own buffer
             emit(i, *reinterpret_cast<const float4*>(xst + w * (T * 40) + (4 * i - w * PW)));
         }
+#pragma unroll
+        for (int u = 0; u < NG; ++u)
+            if (Q0 + threadIdx.x + 256 * u < Q) emit(Q0 + threadIdx.x + 256 * u, xg[u]);
     }
 }
 
