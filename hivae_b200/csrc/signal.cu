@@ -725,16 +725,6 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* _
     // at a time as four n-tiles whose n index is permuted (tile nt, index g <-> column 4 g + nt): one 128-bit load per k row
     // feeds all four tiles, and a lane's outputs are eight consecutive columns (two 128-bit stores per frame).
     {
-        uint32_t ah[KT][4], al[KT][4];
-#pragma unroll
-        for (int ks = 0; ks < KT; ++ks) {
-            const float* r0 = ct + (t0 + g) * T + 8 * ks + t;
-            const float* r1 = ct + (t0 + (TC == 16 ? g + 8 : g)) * T + 8 * ks + t;
-            split_tf32(__ldg(r0), ah[ks][0], al[ks][0]);
-            split_tf32(__ldg(r0 + 4), ah[ks][2], al[ks][2]);
-            split_tf32(TC == 16 ? __ldg(r1) : 0.f, ah[ks][1], al[ks][1]);
-            split_tf32(TC == 16 ? __ldg(r1 + 4) : 0.f, ah[ks][3], al[ks][3]);
-        }
         // x reaches the warp through its own staging buffer (T rows of 32 columns, row pitch 40 floats: conflict-free 128-bit
         // fragment reads): `cp.async` of the next 32 columns is in flight while these 32 are multiplied
         float* stg = S + TC * FP + warp * (T * 40);
@@ -746,6 +736,16 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_mma_kernel(const float* _
             }
         };
         stage(warp);
+        uint32_t ah[KT][4], al[KT][4];
+#pragma unroll
+        for (int ks = 0; ks < KT; ++ks) {
+            const float* r0 = ct + (t0 + g) * T + 8 * ks + t;
+            const float* r1 = ct + (t0 + (TC == 16 ? g + 8 : g)) * T + 8 * ks + t;
+            split_tf32(__ldg(r0), ah[ks][0], al[ks][0]);
+            split_tf32(__ldg(r0 + 4), ah[ks][2], al[ks][2]);
+            split_tf32(TC == 16 ? __ldg(r1) : 0.f, ah[ks][1], al[ks][1]);
+            split_tf32(TC == 16 ? __ldg(r1 + 4) : 0.f, ah[ks][3], al[ks][3]);
+        }
         for (int j = warp; j < HW / 32; j += 8) {
             cp_async_wait_all();
             __syncwarp();
