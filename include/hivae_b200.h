@@ -80,7 +80,12 @@ int hv_idwt2_haar(const void* ll, const void* hl, const void* lh, const void* hh
  * T,H,W), ifftn(fftn(x)*LPF).real equals three 1-D circular convolutions;
  * ct/ch/cw are the T x T, H x H, W x W circulant matrices (fp32, row-major) the
  * host derives from the mask.  x, lo, hi: vols x T x H x W fp32; hi = x - lo.
- * Requires T*H*W*4 bytes <= 200 KB (one volume per CTA in shared memory). */
+ * Requires T*H*W*4 bytes <= 200 KB (one volume per CTA in shared memory).
+ * T in {8,16,32} with H = W in {16,32} and 16-byte aligned buffers run the three
+ * passes on the tensor cores (3xTF32 split, ~1e-6 relative; the reference's FFT
+ * path agrees to 1e-5); everything else, and 32^3 launches too small to fill the
+ * SMs, runs the fp32 SIMT kernels.  Environment HV_FREQ_TC=0 / =1 forces the SIMT
+ * / the tensor kernel (A/B measurements, tools/bench_freq.py). */
 int hv_freq_split3d(const float* x, const float* ct, const float* ch, const float* cw,
                     float* lo, float* hi, int64_t vols, int T, int H, int W, void* stream);
 
