@@ -378,3 +378,51 @@ def test_oracle_random_masking_matches_reference_fixture(golden):
     assert cam.shape == g["enc_camera"].shape == (2, 16, 8, 8)
     for a, b in ((cam, g["enc_camera"]), (osrc, g["enc_obj_src"]), (otgt, g["enc_obj_tgt"])):
         assert float((a - b).abs().max() / b.abs().max()) < 2e-5
+
+
+def test_freq_split_mma_index_arithmetic_emulated():
+    """tools/emulate_freq_mma.py walks the loops of freq_split3d_mma_kernel (csrc/signal.cu) lane by lane with exact
+    products placed through the PTX m16n8k8 fragment layout: the n-permuted T pass, the k-permuted W pass and the swizzled
+    slab must reproduce three plain matrix products for every template instance, and write every output exactly once"""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("emulate_freq_mma", os.path.join(ROOT, "tools", "emulate_freq_mma.py"))
+    emu = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(emu)
+    for T, N in emu.INSTANCES:
+        err, unwritten, rec = emu.emulate(T, N)
+        assert err < 1e-12 and unwritten == 0 and rec < 1e-12, (T, N, err, unwritten, rec)
+
+
+def test_freq_split_3xtf32_error_budget():
+    """numerical design of the tensor-core frequency split, on the CPU: operands split as in split_tf32 (csrc/signal.cu: hi =
+    round-to-nearest TF32 by integer add + mask, lo = x - hi with its 13 low mantissa bits ignored by the tensor core),
+    products hi.hi + hi.lo + lo.hi accumulated in fp32 over the three circulant passes of frequency_utils.py:84-108; the
+    result has to stay an order of magnitude inside the 1e-5 bound of the golden test"""
+    from hivae_b200 import frequency_utils as F
+
+    def split(a):
+        bits = a.astype(np.float32).view(np.uint32)
+        hi = ((bits + np.uint32(0x1000)) & np.uint32(0xFFFFE000)).view(np.float32)
+        lo = ((a.astype(np.float32) - hi).view(np.uint32) & np.uint32(0xFFFFE000)).view(np.float32)   # hardware truncation
+        return hi, lo
+
+    def mm3(c, x):     # c (n, n) applied along axis 0 of x (n, m); fp32 accumulation
+        ch_, cl_ = split(c)
+        xh, xl = split(x)
+        return (cl_ @ xh + ch_ @ xl + ch_ @ xh).astype(np.float32)
+
+    rng = np.random.default_rng(3)
+    T = H = W = 32
+    x = rng.standard_normal((T, H, W)).astype(np.float32)
+    mats = [F._circulant(F._gauss_1d(n, d)).astype(np.float32) for n, d in ((T, 0.6), (H, 0.6), (W, 0.6))]
+    y = mm3(mats[0], x.reshape(T, H * W)).reshape(T, H, W)
+    y = mm3(mats[1], y.transpose(1, 0, 2).reshape(H, T * W)).reshape(H, T, W).transpose(1, 0, 2)
+    y = mm3(mats[2], np.ascontiguousarray(y.transpose(2, 0, 1)).reshape(W, T * H)).reshape(W, T, H).transpose(1, 2, 0)
+    ref = np.einsum('at,thw->ahw', mats[0].astype(np.float64), x.astype(np.float64))
+    ref = np.einsum('bh,ahw->abw', mats[1].astype(np.float64), ref)
+    ref = np.einsum('cw,abw->abc', mats[2].astype(np.float64), ref)
+    err = np.abs(y - ref).max() / np.abs(ref).max()
+    assert err < 1e-6, err
+    # and against the oracle's FFT formulation of the reference
+    olo, _ = O.freq_split3d(torch.from_numpy(x)[None, None], O.gaussian_lpf([T, H, W], 0.6, 0.6))
+    assert float(np.abs(y - olo[0, 0].numpy()).max() / np.abs(ref).max()) < 2e-6
