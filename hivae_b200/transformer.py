@@ -447,7 +447,7 @@ class AMDDiffusionTransformerModelImgSpatialTempMotion(_HvModule):
         if obj_src is not None:
             l = obj_tgt.shape[1]
             M.Lo = 2 * l + 2
-            M.obj = ctx.buf("dit_minit_obj", (N, M.Lo, D), torch.float32)
+            M.obj = torch.empty((N, M.Lo, D), dtype=torch.float32, device=device)   # owned by M (every row is written below)
             src = engine.small_linear(ctx, obj_src.reshape(N * l, -1).float().contiguous(), P.ow, P.ob, "dit_osrc")
             ops.rows_scatter(src, l, 1, P.mpos[1:1 + l], Rows(M.obj, 1, l))
             tgt = engine.small_linear(ctx, obj_tgt.reshape(N * l, -1).float().contiguous(), P.ow, P.ob, "dit_otgt")
@@ -457,7 +457,7 @@ class AMDDiffusionTransformerModelImgSpatialTempMotion(_HvModule):
         if camera is not None:
             M.Lc = camera.shape[2]
             cam = camera.reshape(N * M.Lc, -1).float().contiguous()  # 'n t s d -> (n t) s d'
-            M.cam = engine.small_linear(ctx, cam, P.cw, P.cb, "dit_minit_cam")
+            M.cam = engine.small_linear(ctx, cam, P.cw, P.cb, "dit_minit_cam").clone()   # out of the shared workspace: two M can coexist
         return M
 
     # -- step 2 (every Euler step) -----------------------------------------------------------------
