@@ -675,6 +675,11 @@ __global__ void __launch_bounds__(256, 2) freq_split3d_slab32_kernel(const float
 //                                                               in place, a warp owns whole 16-row blocks
 //   last:   low = slab, high = x - low                          128-bit coalesced loads and stores
 // `slab_idx` (XOR swizzle for N = 32, padded rows for N = 16) keeps every fragment load / store bank-conflict free.
+// Measured (profiles/r02_x_ncu_freq_split3d.md, r02_y_bench_freq.txt): 2511 GB/s of algorithmic traffic at 512 volumes of
+// 32^3 = 38 % of HBM (SIMT kernels 1742), legacy tensor pipe 47 % active; m16n8k8 TF32 issues at 0.5 / clk / SM, so the
+// formulation tops out at 86 % of the HBM roofline.  The T pass (waiting for x) is the largest phase; tried and kept, in
+// order: XOR-swizzled slab, two-instruction split, n-permuted 128-bit loads, warp-owned blocks instead of pair barriers,
+// cp.async staging, requests hoisted above the CTA barriers.  tools/emulate_freq_mma.py replays the index arithmetic on the host.
 __device__ __forceinline__ void split_tf32(float v, uint32_t& hi, uint32_t& lo) {
     // hi = v rounded to TF32 (nearest, ties away: add half an ulp of the 10-bit mantissa, clear the 13 low bits), lo = v - hi
     // exactly; the tensor core ignores the 13 low mantissa bits of lo (|lo| <= 2^-11 |v|, so that costs 2^-21 |v|, either sign).
