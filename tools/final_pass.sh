@@ -31,4 +31,5 @@ bash tools/ncu_one.sh attn_bwd_dit attn_bwd_dkv_tc
 mv gpurun_out/prof_attn_bwd_dit.ncu-rep gpurun_out/prof_attn_bwd_dkv.ncu-rep 2>/dev/null
 bash tools/ncu_one.sh ln ln_modulate
 bash tools/ncu_one.sh dwt 'pyramid|dwt2'
+bash tools/ncu_one.sh freq freq_split3d_mma
 ls -la gpurun_out | head -80
